@@ -1,0 +1,86 @@
+// common.cuh — shared state, error plumbing and launch helpers for libwaffe2cuda.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <atomic>
+#include "../../include/waffe2cuda.h"
+
+namespace wf2 {
+
+constexpr int kMaxRank = WF2CU_MAX_RANK;
+constexpr int kNumSMs = 148;  // B200
+
+struct State {
+  bool inited = false;
+  int device = -1;
+  int sm_count = kNumSMs;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  void* scratch = nullptr;       // reduction partials
+  size_t scratch_bytes = 0;
+  unsigned int* counters = nullptr;  // last-block tickets (zeroed, self-resetting)
+  void* l2flush = nullptr;
+  size_t l2flush_bytes = 0;
+  std::atomic<int64_t> launches{0};
+  std::atomic<size_t> bytes_in_use{0};
+  int gemm_mode = 0;
+};
+State& S();
+
+int set_error(int code, const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define WF2_CUDA(call)                                                     \
+  do {                                                                     \
+    cudaError_t _e = (call);                                               \
+    if (_e != cudaSuccess) return wf2::cuda_fail(_e, #call, __FILE__, __LINE__); \
+  } while (0)
+
+#define WF2_REQUIRE_INIT()                                                  \
+  do {                                                                     \
+    if (!wf2::S().inited)                                                  \
+      return wf2::set_error(WF2CU_ERR_NOT_INITIALISED,                     \
+                            "libwaffe2cuda: wf2cu_init has not succeeded (no B200 / no CPU fallback)"); \
+  } while (0)
+
+#define WF2_CHECK(cond, ...)                                               \
+  do {                                                                     \
+    if (!(cond)) return wf2::set_error(WF2CU_ERR_INVALID, __VA_ARGS__);    \
+  } while (0)
+
+// call after every kernel launch
+inline int post_launch(const char* name) {
+  S().launches.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, name, __FILE__, __LINE__);
+  return 0;
+}
+
+int ensure_scratch(size_t bytes);
+
+inline float* fptr(const wf2cu_view* v) { return reinterpret_cast<float*>(v->base) + v->offset; }
+
+// ---- iteration-space plan shared by all strided kernels -------------------------------
+// After normalisation: size-1 axes dropped, adjacent axes merged when every operand allows it.
+constexpr int kMaxOperands = 8;
+struct Plan {
+  int rank;                       // >= 1
+  int nops;
+  int64_t shape[kMaxRank];
+  int64_t stride[kMaxOperands][kMaxRank];
+  int64_t numel;
+};
+
+// Build a merged plan over n equal-shape views. Returns 0 or error.
+int build_plan(const wf2cu_view* const* views, int n, Plan* out, const char* who);
+
+inline int64_t view_numel(const wf2cu_view* v) {
+  int64_t n = 1;
+  for (int i = 0; i < v->rank; ++i) n *= v->shape[i];
+  return n;
+}
+
+}  // namespace wf2

@@ -1,0 +1,504 @@
+// reduce.cu — `!sum` / `!mean` and every other "AddNode whose destination has stride 0".
+//
+// In the reference a reduction is not a node: `!sum` zero-fills `out` with `A*=scal out 0`, views
+// it with `(:broadcast n)` on the reduced axes and runs `A+=B out* x`
+// (`source/base-impl/reduction.lisp:60-79`); the C kernel then sees incx = 0, skips its SIMD body
+// and accumulates `x[0] = x[0] + y[i]` sequentially (`cl-waffe2-simd.c:159,205-212`).  A parallel
+// element-wise kernel on such a destination would race, so wf2cu_ew_binary classifies by the
+// destination strides and lands here.  Summation is a fixed-shape tree (warp shuffle -> block ->
+// optional second stage), i.e. deterministic, and differs from the reference's sequential order
+// by O(log n) roundings instead of O(n) (SURVEY §7 hard part d).
+//
+// Kernels (all HBM-bound, one pass over x):
+//   rows : kept axes outermost, ONE reduced axis innermost & contiguous  (sum :axis 1, :axis t)
+//   cols : [batch,] ONE reduced axis, then kept contiguous axis          (sum :axis 0, 4-D :axis 1)
+//   gen  : any other mix of kept/reduced axes (warp per output element)
+#include "common.cuh"
+#include "math.cuh"
+
+namespace wf2 {
+
+struct MSum {
+  __device__ __forceinline__ static float id() { return 0.f; }
+  __device__ __forceinline__ static float op(float a, float b) { return __fadd_rn(a, b); }
+};
+struct MProd {
+  __device__ __forceinline__ static float id() { return 1.f; }
+  __device__ __forceinline__ static float op(float a, float b) { return __fmul_rn(a, b); }
+};
+
+// how the reduced total t meets the old destination value d
+enum { FIN_ADD = 0, FIN_SUB, FIN_MUL, FIN_DIV, FIN_SET };
+struct Fin {
+  int mode;
+  float divisor;  // applied last when != 0
+  __device__ __forceinline__ float operator()(float d, float t) const {
+    float r;
+    switch (mode) {
+      case FIN_ADD: r = __fadd_rn(d, t); break;
+      case FIN_SUB: r = __fsub_rn(d, t); break;
+      case FIN_MUL: r = __fmul_rn(d, t); break;
+      case FIN_DIV: r = __fdiv_rn(d, t); break;
+      default: r = t;
+    }
+    if (divisor != 0.f) r = __fdiv_rn(r, divisor);
+    return r;
+  }
+};
+
+template <class M>
+__device__ __forceinline__ float warp_reduce(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = M::op(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+template <class M, int THREADS>
+__device__ __forceinline__ float block_reduce(float v, float* smem /* THREADS/32 floats */) {
+  v = warp_reduce<M>(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) smem[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    float t = (lane < THREADS / 32) ? smem[lane] : M::id();
+    t = warp_reduce<M>(t);
+    if (lane == 0) smem[0] = t;
+  }
+  __syncthreads();
+  const float r = smem[0];
+  __syncthreads();
+  return r;
+}
+
+// ------------------------------------------------------------------ rows
+struct RowArgs {
+  const float* src;
+  float* dst;        // final destination (kept-axes strided)
+  float* partial;    // [rows * chunks] when chunks > 1
+  int nkept;         // 0..4 kept axes
+  uint32_t kshape[4];
+  int64_t kstride_src[4], kstride_dst[4];
+  int64_t cols;      // reduced extent, src stride 1
+  int64_t chunk_len; // columns per chunk (multiple of 4)
+  uint32_t chunks;
+  int vec;           // 1: float4 loads legal for every row
+};
+
+template <class M, int THREADS>
+__global__ void __launch_bounds__(THREADS) reduce_rows_kernel(const __grid_constant__ RowArgs a, const Fin fin) {
+  __shared__ float smem[THREADS / 32];
+  const uint32_t chunk = blockIdx.x % a.chunks;
+  uint32_t row = blockIdx.x / a.chunks;
+  const uint32_t row_id = row;
+  int64_t so = 0, dofs = 0;
+  for (int d = a.nkept - 1; d >= 0; --d) {
+    const uint32_t q = row / a.kshape[d];
+    const uint32_t r = row - q * a.kshape[d];
+    row = q;
+    so += (int64_t)r * a.kstride_src[d];
+    dofs += (int64_t)r * a.kstride_dst[d];
+  }
+  const int64_t c0 = (int64_t)chunk * a.chunk_len;
+  int64_t c1 = c0 + a.chunk_len;
+  if (c1 > a.cols) c1 = a.cols;
+  const float* p = a.src + so;
+  float acc0 = M::id(), acc1 = M::id(), acc2 = M::id(), acc3 = M::id();
+  if (a.vec) {
+    const int64_t v0 = c0 >> 2, v1 = c1 >> 2;  // c0 multiple of 4; tail handled below
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    int64_t i = v0 + threadIdx.x;
+    // 4 independent 128-bit loads in flight per thread
+    for (; i + 3 * THREADS < v1; i += 4 * THREADS) {
+      const float4 x0 = p4[i], x1 = p4[i + THREADS], x2 = p4[i + 2 * THREADS], x3 = p4[i + 3 * THREADS];
+      acc0 = M::op(acc0, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
+      acc1 = M::op(acc1, M::op(M::op(x1.x, x1.y), M::op(x1.z, x1.w)));
+      acc2 = M::op(acc2, M::op(M::op(x2.x, x2.y), M::op(x2.z, x2.w)));
+      acc3 = M::op(acc3, M::op(M::op(x3.x, x3.y), M::op(x3.z, x3.w)));
+    }
+    for (; i < v1; i += THREADS) {
+      const float4 x0 = p4[i];
+      acc0 = M::op(acc0, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
+    }
+    for (int64_t c = (v1 << 2) + threadIdx.x; c < c1; c += THREADS) acc1 = M::op(acc1, p[c]);
+  } else {
+    for (int64_t c = c0 + threadIdx.x; c < c1; c += THREADS) acc0 = M::op(acc0, p[c]);
+  }
+  float acc = M::op(M::op(acc0, acc1), M::op(acc2, acc3));
+  acc = block_reduce<M, THREADS>(acc, smem);
+  if (threadIdx.x == 0) {
+    if (a.chunks > 1) a.partial[(int64_t)row_id * a.chunks + chunk] = acc;
+    else a.dst[dofs] = fin(a.dst[dofs], acc);
+  }
+}
+
+// several short rows per CTA: one warp per row
+template <class M>
+__global__ void __launch_bounds__(256) reduce_rows_warp_kernel(const __grid_constant__ RowArgs a, const Fin fin, uint32_t nrows) {
+  const uint32_t row_id = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row_id >= nrows) return;
+  const int lane = threadIdx.x & 31;
+  uint32_t row = row_id;
+  int64_t so = 0, dofs = 0;
+  for (int d = a.nkept - 1; d >= 0; --d) {
+    const uint32_t q = row / a.kshape[d];
+    const uint32_t r = row - q * a.kshape[d];
+    row = q;
+    so += (int64_t)r * a.kstride_src[d];
+    dofs += (int64_t)r * a.kstride_dst[d];
+  }
+  const float* p = a.src + so;
+  float acc = M::id();
+  if (a.vec) {
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    const int64_t v1 = a.cols >> 2;
+    for (int64_t i = lane; i < v1; i += 32) {
+      const float4 x = p4[i];
+      acc = M::op(acc, M::op(M::op(x.x, x.y), M::op(x.z, x.w)));
+    }
+    for (int64_t c = (v1 << 2) + lane; c < a.cols; c += 32) acc = M::op(acc, p[c]);
+  } else {
+    for (int64_t c = lane; c < a.cols; c += 32) acc = M::op(acc, p[c]);
+  }
+  acc = warp_reduce<M>(acc);
+  if (lane == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
+}
+
+// second stage for rows: dst[row] = fin(dst[row], reduce(partial[row, 0..chunks)))
+template <class M>
+__global__ void __launch_bounds__(256) reduce_rows_final_kernel(const __grid_constant__ RowArgs a, const Fin fin) {
+  __shared__ float smem[8];
+  uint32_t row = blockIdx.x;
+  const float* p = a.partial + (int64_t)row * a.chunks;
+  float acc = M::id();
+  for (uint32_t c = threadIdx.x; c < a.chunks; c += 256) acc = M::op(acc, p[c]);
+  acc = block_reduce<M, 256>(acc, smem);
+  if (threadIdx.x == 0) {
+    int64_t dofs = 0;
+    for (int d = a.nkept - 1; d >= 0; --d) {
+      const uint32_t q = row / a.kshape[d];
+      const uint32_t r = row - q * a.kshape[d];
+      row = q;
+      dofs += (int64_t)r * a.kstride_dst[d];
+    }
+    a.dst[dofs] = fin(a.dst[dofs], acc);
+  }
+}
+
+// ------------------------------------------------------------------ cols
+struct ColArgs {
+  const float* src;
+  float* dst;
+  float* partial;          // [batch][splits][K] when splits > 1
+  int64_t B, R, K;         // batch, reduced, kept (contiguous)
+  int64_t sB_src, sR_src;  // src strides (kept stride is 1)
+  int64_t sB_dst;          // dst batch stride (kept stride is 1)
+  uint32_t splits;         // CTAs along R
+  int64_t rows_per_split;
+  int vec;
+};
+
+// block = 32 (x: columns, float4 each when vec) x 8 (y: rows)
+template <class M>
+__global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant__ ColArgs a, const Fin fin) {
+  __shared__ float4 sm[8][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t b = blockIdx.z;
+  const uint32_t split = blockIdx.y;
+  const int64_t r0 = (int64_t)split * a.rows_per_split;
+  int64_t r1 = r0 + a.rows_per_split;
+  if (r1 > a.R) r1 = a.R;
+  const float* base = a.src + b * a.sB_src;
+  float4 acc = make_float4(M::id(), M::id(), M::id(), M::id());
+  float4 acc2 = acc;
+  if (a.vec) {
+    const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * 4;
+    if (col < a.K) {
+      int64_t r = r0 + ty;
+      for (; r + 8 < r1; r += 16) {
+        const float4 x = *reinterpret_cast<const float4*>(base + r * a.sR_src + col);
+        const float4 y = *reinterpret_cast<const float4*>(base + (r + 8) * a.sR_src + col);
+        acc.x = M::op(acc.x, x.x); acc.y = M::op(acc.y, x.y); acc.z = M::op(acc.z, x.z); acc.w = M::op(acc.w, x.w);
+        acc2.x = M::op(acc2.x, y.x); acc2.y = M::op(acc2.y, y.y); acc2.z = M::op(acc2.z, y.z); acc2.w = M::op(acc2.w, y.w);
+      }
+      for (; r < r1; r += 8) {
+        const float4 x = *reinterpret_cast<const float4*>(base + r * a.sR_src + col);
+        acc.x = M::op(acc.x, x.x); acc.y = M::op(acc.y, x.y); acc.z = M::op(acc.z, x.z); acc.w = M::op(acc.w, x.w);
+      }
+    }
+    acc.x = M::op(acc.x, acc2.x); acc.y = M::op(acc.y, acc2.y); acc.z = M::op(acc.z, acc2.z); acc.w = M::op(acc.w, acc2.w);
+  } else {
+    // scalar columns: each thread owns column blockIdx.x*128 + tx + 32*k, k = 0..3 (kept in .x..w)
+    const int64_t cb = (int64_t)blockIdx.x * 128 + tx;
+    for (int64_t r = r0 + ty; r < r1; r += 8) {
+      const float* rowp = base + r * a.sR_src;
+      if (cb < a.K) acc.x = M::op(acc.x, rowp[cb]);
+      if (cb + 32 < a.K) acc.y = M::op(acc.y, rowp[cb + 32]);
+      if (cb + 64 < a.K) acc.z = M::op(acc.z, rowp[cb + 64]);
+      if (cb + 96 < a.K) acc.w = M::op(acc.w, rowp[cb + 96]);
+    }
+  }
+  sm[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) {
+      const float4 o = sm[k][tx];
+      acc.x = M::op(acc.x, o.x); acc.y = M::op(acc.y, o.y); acc.z = M::op(acc.z, o.z); acc.w = M::op(acc.w, o.w);
+    }
+    float* outp;
+    const bool final_stage = (a.splits == 1);
+    if (final_stage) outp = a.dst + b * a.sB_dst;
+    else outp = a.partial + (b * a.splits + split) * a.K;
+    if (a.vec) {
+      const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * 4;
+      if (col < a.K) {
+        if (final_stage) {
+          float4 d = *reinterpret_cast<float4*>(outp + col);
+          d.x = fin(d.x, acc.x); d.y = fin(d.y, acc.y); d.z = fin(d.z, acc.z); d.w = fin(d.w, acc.w);
+          *reinterpret_cast<float4*>(outp + col) = d;
+        } else {
+          *reinterpret_cast<float4*>(outp + col) = acc;
+        }
+      }
+    } else {
+      const int64_t cb = (int64_t)blockIdx.x * 128 + tx;
+      const float vals[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int64_t c = cb + 32 * k;
+        if (c < a.K) outp[c] = final_stage ? fin(outp[c], vals[k]) : vals[k];
+      }
+    }
+  }
+}
+
+template <class M>
+__global__ void __launch_bounds__(256) reduce_cols_final_kernel(const __grid_constant__ ColArgs a, const Fin fin) {
+  const int64_t c = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  const int64_t b = blockIdx.y;
+  if (c >= a.K) return;
+  const float* p = a.partial + b * a.splits * a.K + c;
+  float acc = M::id();
+  for (uint32_t s = 0; s < a.splits; ++s) acc = M::op(acc, p[(int64_t)s * a.K]);
+  float* d = a.dst + b * a.sB_dst + c;
+  *d = fin(*d, acc);
+}
+
+// ------------------------------------------------------------------ generic
+struct GenRedArgs {
+  const float* src;
+  float* dst;
+  int nkept, nred;
+  int64_t kshape[kMaxRank], kstride_src[kMaxRank], kstride_dst[kMaxRank];
+  int64_t rshape[kMaxRank], rstride_src[kMaxRank];
+  int64_t nout, nredel;
+};
+
+template <class M>
+__global__ void __launch_bounds__(256) reduce_gen_kernel(const __grid_constant__ GenRedArgs a, const Fin fin) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps_total = (int64_t)gridDim.x * 8;
+  for (int64_t o = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); o < a.nout; o += warps_total) {
+    int64_t rem = o, so = 0, dofs = 0;
+    for (int d = a.nkept - 1; d >= 0; --d) {
+      const int64_t q = rem / a.kshape[d], r = rem - q * a.kshape[d];
+      rem = q; so += r * a.kstride_src[d]; dofs += r * a.kstride_dst[d];
+    }
+    float acc = M::id();
+    for (int64_t i = lane; i < a.nredel; i += 32) {
+      int64_t rr = i, off = so;
+      for (int d = a.nred - 1; d >= 0; --d) {
+        const int64_t q = rr / a.rshape[d], r = rr - q * a.rshape[d];
+        rr = q; off += r * a.rstride_src[d];
+      }
+      acc = M::op(acc, a.src[off]);
+    }
+    acc = warp_reduce<M>(acc);
+    if (lane == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
+  }
+}
+
+// ------------------------------------------------------------------ host dispatch
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+bool has_reduction_axes(const wf2cu_view* dst) {
+  for (int i = 0; i < dst->rank; ++i)
+    if (dst->stride[i] == 0 && dst->shape[i] > 1) return true;
+  return false;
+}
+
+template <class M>
+static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, const char* who) {
+  const wf2cu_view* views[2] = {dst, src};
+  Plan p;
+  int rc = build_plan(views, 2, &p, who);
+  if (rc) return rc;
+  if (p.numel == 0) return 0;
+  State& s = S();
+  float* dptr = fptr(dst);
+  const float* sptr = fptr(src);
+  // classify axes
+  bool red[kMaxRank];
+  int nred = 0;
+  for (int d = 0; d < p.rank; ++d) { red[d] = (p.stride[0][d] == 0 && p.shape[d] > 1); nred += red[d]; }
+  const int last = p.rank - 1;
+
+  // ---- rows: exactly one reduced axis, innermost, src contiguous there; <= 4 kept axes
+  if (nred == 1 && red[last] && p.stride[1][last] == 1 && p.rank - 1 <= 4) {
+    RowArgs a;
+    memset(&a, 0, sizeof(a));
+    a.src = sptr; a.dst = dptr;
+    a.nkept = p.rank - 1;
+    int64_t rows = 1;
+    bool vec = al16(sptr);
+    for (int d = 0; d < last; ++d) {
+      a.kshape[d] = (uint32_t)p.shape[d];
+      a.kstride_src[d] = p.stride[1][d];
+      a.kstride_dst[d] = p.stride[0][d];
+      rows *= p.shape[d];
+      if (p.stride[1][d] % 4 != 0) vec = false;
+    }
+    a.cols = p.shape[last];
+    a.vec = vec ? 1 : 0;
+    if (rows < (int64_t(1) << 31)) {
+      if (a.cols <= 1024 && rows >= 64) {
+        a.chunks = 1; a.chunk_len = a.cols;
+        reduce_rows_warp_kernel<M><<<(unsigned)((rows + 7) / 8), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+        return post_launch(who);
+      }
+      // split long rows when there are too few of them to fill 148 SMs
+      uint32_t chunks = 1;
+      const int64_t target_ctas = (int64_t)s.sm_count * 8;
+      if (rows < target_ctas && a.cols >= 8192) {
+        int64_t want = (target_ctas + rows - 1) / rows;
+        const int64_t maxc = a.cols / 4096;  // >= 4096 columns per chunk
+        if (want > maxc) want = maxc;
+        if (want < 1) want = 1;
+        chunks = (uint32_t)want;
+      }
+      int64_t chunk_len = (a.cols + chunks - 1) / chunks;
+      chunk_len = (chunk_len + 3) & ~int64_t(3);
+      chunks = (uint32_t)((a.cols + chunk_len - 1) / chunk_len);
+      a.chunks = chunks; a.chunk_len = chunk_len;
+      if (chunks > 1) {
+        rc = ensure_scratch((size_t)rows * chunks * sizeof(float));
+        if (rc) return rc;
+        a.partial = (float*)s.scratch;
+      }
+      reduce_rows_kernel<M, 256><<<(unsigned)(rows * chunks), 256, 0, s.stream>>>(a, fin);
+      rc = post_launch(who);
+      if (rc) return rc;
+      if (chunks > 1) {
+        reduce_rows_final_kernel<M><<<(unsigned)rows, 256, 0, s.stream>>>(a, fin);
+        rc = post_launch(who);
+      }
+      return rc;
+    }
+  }
+  // ---- cols: [B,] R, K with K contiguous in both, R reduced, B kept
+  if (nred == 1 && p.rank >= 2 && p.rank <= 3 && red[p.rank - 2] && p.stride[0][last] == 1 && p.stride[1][last] == 1) {
+    ColArgs a;
+    memset(&a, 0, sizeof(a));
+    a.src = sptr; a.dst = dptr;
+    a.K = p.shape[last]; a.R = p.shape[last - 1];
+    a.sR_src = p.stride[1][last - 1];
+    if (p.rank == 3) { a.B = p.shape[0]; a.sB_src = p.stride[1][0]; a.sB_dst = p.stride[0][0]; }
+    else { a.B = 1; }
+    bool vec = al16(sptr) && al16(dptr) && (a.K % 4 == 0) && (a.sR_src % 4 == 0) && (a.sB_src % 4 == 0) && (a.sB_dst % 4 == 0);
+    a.vec = vec ? 1 : 0;
+    const int64_t colblocks = (a.K + 127) / 128;
+    const int64_t target_ctas = (int64_t)s.sm_count * 4;
+    int64_t splits = 1;
+    if (colblocks * a.B < target_ctas) {
+      splits = (target_ctas + colblocks * a.B - 1) / (colblocks * a.B);
+      const int64_t maxs = (a.R + 31) / 32;  // >= 32 rows per split
+      if (splits > maxs) splits = maxs;
+      if (splits < 1) splits = 1;
+    }
+    int64_t rps = (a.R + splits - 1) / splits;
+    splits = (a.R + rps - 1) / rps;
+    a.splits = (uint32_t)splits; a.rows_per_split = rps;
+    if (a.B < 65536 && splits < 65536) {
+      if (splits > 1) {
+        rc = ensure_scratch((size_t)a.B * splits * a.K * sizeof(float));
+        if (rc) return rc;
+        a.partial = (float*)s.scratch;
+      }
+      dim3 grid((unsigned)colblocks, (unsigned)splits, (unsigned)a.B);
+      reduce_cols_kernel<M><<<grid, 256, 0, s.stream>>>(a, fin);
+      rc = post_launch(who);
+      if (rc) return rc;
+      if (splits > 1) {
+        dim3 g2((unsigned)((a.K + 255) / 256), (unsigned)a.B);
+        reduce_cols_final_kernel<M><<<g2, 256, 0, s.stream>>>(a, fin);
+        rc = post_launch(who);
+      }
+      return rc;
+    }
+  }
+  // ---- generic
+  GenRedArgs g;
+  memset(&g, 0, sizeof(g));
+  g.src = sptr; g.dst = dptr;
+  g.nout = 1; g.nredel = 1;
+  for (int d = 0; d < p.rank; ++d) {
+    if (red[d]) {
+      g.rshape[g.nred] = p.shape[d]; g.rstride_src[g.nred] = p.stride[1][d]; g.nredel *= p.shape[d]; ++g.nred;
+    } else {
+      g.kshape[g.nkept] = p.shape[d]; g.kstride_src[g.nkept] = p.stride[1][d]; g.kstride_dst[g.nkept] = p.stride[0][d];
+      g.nout *= p.shape[d]; ++g.nkept;
+    }
+  }
+  int64_t grid = (g.nout + 7) / 8;
+  const int64_t cap = (int64_t)s.sm_count * 16;
+  if (grid > cap) grid = cap;
+  reduce_gen_kernel<M><<<(unsigned)grid, 256, 0, s.stream>>>(g, fin);
+  return post_launch(who);
+}
+
+int reduce_binary(int op, const wf2cu_view* dst, const wf2cu_view* src) {
+  switch (op) {
+    case WF2CU_ADD: return reduce_impl<MSum>(dst, src, Fin{FIN_ADD, 0.f}, "wf2cu_ew_binary(add,reduce)");
+    case WF2CU_SUB: return reduce_impl<MSum>(dst, src, Fin{FIN_SUB, 0.f}, "wf2cu_ew_binary(sub,reduce)");
+    case WF2CU_MUL: return reduce_impl<MProd>(dst, src, Fin{FIN_MUL, 0.f}, "wf2cu_ew_binary(mul,reduce)");
+    case WF2CU_DIV: return reduce_impl<MProd>(dst, src, Fin{FIN_DIV, 0.f}, "wf2cu_ew_binary(div,reduce)");
+    case WF2CU_COPY: {
+      // sequential `x[0] = y[i]` leaves the LAST element along every reduced axis
+      wf2cu_view d = *dst, s = *src;
+      for (int i = 0; i < d.rank; ++i)
+        if (d.stride[i] == 0 && d.shape[i] > 1) {
+          s.offset += s.stride[i] * (s.shape[i] - 1);
+          s.shape[i] = 1; d.shape[i] = 1;
+        }
+      return wf2cu_ew_binary(WF2CU_COPY, &d, &s);
+    }
+    default: return set_error(WF2CU_ERR_INVALID, "wf2cu_ew_binary: unknown op %d", op);
+  }
+}
+
+}  // namespace wf2
+
+using namespace wf2;
+
+extern "C" {
+
+int wf2cu_reduce_sum(const wf2cu_view* x, const wf2cu_view* out_bcast, int accumulate, float divisor) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(x && out_bcast, "wf2cu_reduce_sum: null view");
+  WF2_CHECK(x->rank == out_bcast->rank, "wf2cu_reduce_sum: rank mismatch (%d vs %d)", x->rank, out_bcast->rank);
+  // accept out given with extent-1 axes instead of (:broadcast n): widen them to stride 0
+  wf2cu_view o = *out_bcast;
+  for (int i = 0; i < o.rank; ++i)
+    if (o.shape[i] == 1 && x->shape[i] != 1) { o.shape[i] = x->shape[i]; o.stride[i] = 0; }
+  Fin fin{accumulate ? FIN_ADD : FIN_SET, divisor};
+  if (!has_reduction_axes(&o)) {
+    // nothing to reduce: out <- [out +] x [/ divisor]
+    int rc = accumulate ? wf2cu_ew_binary(WF2CU_ADD, &o, x) : wf2cu_ew_binary(WF2CU_COPY, &o, x);
+    if (rc) return rc;
+    if (divisor != 0.f) return wf2cu_ew_scalar(WF2CU_DIV, &o, divisor);
+    return 0;
+  }
+  return reduce_impl<MSum>(&o, x, fin, "wf2cu_reduce_sum");
+}
+
+}  // extern "C"

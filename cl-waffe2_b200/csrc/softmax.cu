@@ -1,0 +1,326 @@
+// softmax.cu — `!softmax` as ONE pass over HBM.
+//
+// The reference has no softmax node; `(!softmax x :avoid-overflow t :axis 1)` is the composite
+//     x1 = x - mean(x, axis) ; e = exp(x1) ; z = sum(e, axis) ; e / z
+// (`source/nn/activation.lisp:126-159`; note: MEAN-shift, not max-shift), or with
+// `:avoid-overflow nil`:  e = exp(x) ; e / sum(e, axis)  (used by softmax-cross-entropy,
+// `source/nn/criterion.lisp:163`).  That is >= 8 full memory passes on the CPU path (two disguised
+// reductions + 5 element-wise nodes).  Here a row lives in registers between the three phases,
+// so traffic is the algorithmic minimum: one read + one write.
+//
+// The arithmetic keeps the reference's operation order per element: mean = sum/n (true divide),
+// x - mean, expf, e / z (true divide); only the two sums are trees instead of sequential.
+#include "common.cuh"
+#include "math.cuh"
+
+namespace wf2 {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+template <int THREADS>
+__device__ __forceinline__ float block_sum(float v, float* smem) {
+  v = warp_sum(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) smem[w] = v;
+  __syncthreads();
+  float t = (lane < THREADS / 32) ? smem[lane] : 0.f;
+  t = warp_sum(t);   // every warp computes the same total
+  __syncthreads();
+  return t;
+}
+
+struct SmRowArgs {
+  const float* x;
+  float* out;
+  int nouter;                 // 0..4 outer axes
+  uint32_t oshape[4];
+  int64_t ostride_x[4], ostride_o[4];
+  int64_t cols;
+  uint32_t rows;
+  int avoid_overflow;
+};
+
+__device__ __forceinline__ void decode_row(const SmRowArgs& a, uint32_t row, int64_t& xo, int64_t& oo) {
+  xo = 0; oo = 0;
+  for (int d = a.nouter - 1; d >= 0; --d) {
+    const uint32_t q = row / a.oshape[d];
+    const uint32_t r = row - q * a.oshape[d];
+    row = q;
+    xo += (int64_t)r * a.ostride_x[d];
+    oo += (int64_t)r * a.ostride_o[d];
+  }
+}
+
+// one CTA per row, row cached in registers as float4s: cols <= THREADS * 4 * VPT
+template <int THREADS, int VPT>
+__global__ void __launch_bounds__(THREADS) softmax_row_block_kernel(const __grid_constant__ SmRowArgs a) {
+  __shared__ float smem[THREADS / 32];
+  int64_t xo, oo;
+  decode_row(a, blockIdx.x, xo, oo);
+  const float4* xp = reinterpret_cast<const float4*>(a.x + xo);
+  float4* op = reinterpret_cast<float4*>(a.out + oo);
+  const int64_t n4 = a.cols >> 2;
+  float4 v[VPT];
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int64_t i = threadIdx.x + (int64_t)k * THREADS;
+    v[k] = (i < n4) ? xp[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (a.avoid_overflow) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) s = __fadd_rn(s, __fadd_rn(__fadd_rn(v[k].x, v[k].y), __fadd_rn(v[k].z, v[k].w)));
+    s = block_sum<THREADS>(s, smem);
+    const float mean = __fdiv_rn(s, (float)a.cols);
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      v[k].x = __fsub_rn(v[k].x, mean); v[k].y = __fsub_rn(v[k].y, mean);
+      v[k].z = __fsub_rn(v[k].z, mean); v[k].w = __fsub_rn(v[k].w, mean);
+    }
+  }
+  float z = 0.f;
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int64_t i = threadIdx.x + (int64_t)k * THREADS;
+    if (i < n4) {
+      v[k].x = expf(v[k].x); v[k].y = expf(v[k].y); v[k].z = expf(v[k].z); v[k].w = expf(v[k].w);
+      z = __fadd_rn(z, __fadd_rn(__fadd_rn(v[k].x, v[k].y), __fadd_rn(v[k].z, v[k].w)));
+    }
+  }
+  z = block_sum<THREADS>(z, smem);
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int64_t i = threadIdx.x + (int64_t)k * THREADS;
+    if (i < n4) {
+      float4 r;
+      r.x = __fdiv_rn(v[k].x, z); r.y = __fdiv_rn(v[k].y, z); r.z = __fdiv_rn(v[k].z, z); r.w = __fdiv_rn(v[k].w, z);
+      op[i] = r;
+    }
+  }
+}
+
+// one warp per row, scalar register cache: cols <= 1024, any alignment, strided inner axis allowed
+struct SmWarpExtra { int64_t sx, so; };
+__global__ void __launch_bounds__(256) softmax_row_warp_kernel(const __grid_constant__ SmRowArgs a, const SmWarpExtra e) {
+  const uint32_t row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= a.rows) return;
+  const int lane = threadIdx.x & 31;
+  int64_t xo, oo;
+  decode_row(a, row, xo, oo);
+  const float* xp = a.x + xo;
+  float* op = a.out + oo;
+  float v[32];
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    const int64_t c = lane + 32 * k;
+    v[k] = (c < a.cols) ? xp[c * e.sx] : 0.f;
+  }
+  if (a.avoid_overflow) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) s = __fadd_rn(s, v[k]);
+    s = warp_sum(s);
+    const float mean = __fdiv_rn(s, (float)a.cols);
+#pragma unroll
+    for (int k = 0; k < 32; ++k) v[k] = __fsub_rn(v[k], mean);
+  }
+  float z = 0.f;
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    const int64_t c = lane + 32 * k;
+    if (c < a.cols) { v[k] = expf(v[k]); z = __fadd_rn(z, v[k]); }
+  }
+  z = warp_sum(z);
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    const int64_t c = lane + 32 * k;
+    if (c < a.cols) op[c * e.so] = __fdiv_rn(v[k], z);
+  }
+}
+
+// long rows: three passes over global/L2 (row does not fit the register cache)
+__global__ void __launch_bounds__(512) softmax_row_stream_kernel(const __grid_constant__ SmRowArgs a, const SmWarpExtra e) {
+  __shared__ float smem[16];
+  int64_t xo, oo;
+  decode_row(a, blockIdx.x, xo, oo);
+  const float* xp = a.x + xo;
+  float* op = a.out + oo;
+  float mean = 0.f;
+  if (a.avoid_overflow) {
+    float s = 0.f;
+    for (int64_t c = threadIdx.x; c < a.cols; c += 512) s = __fadd_rn(s, xp[c * e.sx]);
+    s = block_sum<512>(s, smem);
+    mean = __fdiv_rn(s, (float)a.cols);
+  }
+  float z = 0.f;
+  for (int64_t c = threadIdx.x; c < a.cols; c += 512) {
+    float t = xp[c * e.sx];
+    if (a.avoid_overflow) t = __fsub_rn(t, mean);
+    z = __fadd_rn(z, expf(t));
+  }
+  z = block_sum<512>(z, smem);
+  for (int64_t c = threadIdx.x; c < a.cols; c += 512) {
+    float t = xp[c * e.sx];
+    if (a.avoid_overflow) t = __fsub_rn(t, mean);
+    op[c * e.so] = __fdiv_rn(expf(t), z);
+  }
+}
+
+// softmax over a NON-innermost axis: one thread per (outer, inner) lane, loops over R.
+// Adjacent threads take adjacent inner elements, so loads coalesce when the inner stride is 1.
+struct SmLaneArgs {
+  const float* x;
+  float* out;
+  int nlane;                       // lane axes (all axes except the softmax axis), <= 7
+  int64_t lshape[kMaxRank], lstride_x[kMaxRank], lstride_o[kMaxRank];
+  int64_t R, sR_x, sR_o;
+  int64_t nlanes;
+  int avoid_overflow;
+};
+
+template <int RCACHE>
+__global__ void __launch_bounds__(256) softmax_lane_kernel(const __grid_constant__ SmLaneArgs a) {
+  const int64_t gstride = (int64_t)gridDim.x * 256;
+  for (int64_t l = (int64_t)blockIdx.x * 256 + threadIdx.x; l < a.nlanes; l += gstride) {
+    int64_t rem = l, xo = 0, oo = 0;
+    for (int d = a.nlane - 1; d >= 0; --d) {
+      const int64_t q = rem / a.lshape[d], r = rem - q * a.lshape[d];
+      rem = q; xo += r * a.lstride_x[d]; oo += r * a.lstride_o[d];
+    }
+    const float* xp = a.x + xo;
+    float* op = a.out + oo;
+    if (RCACHE > 0) {
+      float v[RCACHE > 0 ? RCACHE : 1];
+#pragma unroll
+      for (int k = 0; k < RCACHE; ++k) v[k] = (k < a.R) ? xp[k * a.sR_x] : 0.f;
+      if (a.avoid_overflow) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < RCACHE; ++k) if (k < a.R) s = __fadd_rn(s, v[k]);
+        const float mean = __fdiv_rn(s, (float)a.R);
+#pragma unroll
+        for (int k = 0; k < RCACHE; ++k) v[k] = __fsub_rn(v[k], mean);
+      }
+      float z = 0.f;
+#pragma unroll
+      for (int k = 0; k < RCACHE; ++k) if (k < a.R) { v[k] = expf(v[k]); z = __fadd_rn(z, v[k]); }
+#pragma unroll
+      for (int k = 0; k < RCACHE; ++k) if (k < a.R) op[k * a.sR_o] = __fdiv_rn(v[k], z);
+    } else {
+      float mean = 0.f;
+      if (a.avoid_overflow) {
+        float s = 0.f;
+        for (int64_t k = 0; k < a.R; ++k) s = __fadd_rn(s, xp[k * a.sR_x]);
+        mean = __fdiv_rn(s, (float)a.R);
+      }
+      float z = 0.f;
+      for (int64_t k = 0; k < a.R; ++k) {
+        float t = xp[k * a.sR_x];
+        if (a.avoid_overflow) t = __fsub_rn(t, mean);
+        z = __fadd_rn(z, expf(t));
+      }
+      for (int64_t k = 0; k < a.R; ++k) {
+        float t = xp[k * a.sR_x];
+        if (a.avoid_overflow) t = __fsub_rn(t, mean);
+        op[k * a.sR_o] = __fdiv_rn(expf(t), z);
+      }
+    }
+  }
+}
+
+static inline bool al16s(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace wf2
+
+using namespace wf2;
+
+extern "C" int wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(x && out && x->base && out->base, "wf2cu_softmax: null view");
+  WF2_CHECK(x->rank == out->rank && x->rank >= 1 && x->rank <= kMaxRank, "wf2cu_softmax: bad rank");
+  const int rank = x->rank;
+  if (axis < 0) axis += rank;
+  WF2_CHECK(axis >= 0 && axis < rank, "wf2cu_softmax: axis %d out of range for rank %d", axis, rank);
+  int64_t numel = 1;
+  for (int i = 0; i < rank; ++i) {
+    WF2_CHECK(x->shape[i] == out->shape[i], "wf2cu_softmax: shape mismatch on axis %d", i);
+    numel *= x->shape[i];
+  }
+  if (numel == 0) return 0;
+  State& s = S();
+  const float* xp = fptr(x);
+  float* op = fptr(out);
+  const int64_t R = x->shape[axis];
+  // is the softmax axis the innermost non-trivial one?
+  bool innermost = true;
+  for (int i = axis + 1; i < rank; ++i) if (x->shape[i] != 1) innermost = false;
+  if (innermost) {
+    SmRowArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = xp; a.out = op; a.cols = R; a.avoid_overflow = avoid_overflow;
+    // merge outer axes
+    int n = 0;
+    int64_t rows = 1;
+    bool ok = true;
+    bool strides4 = true;
+    for (int i = 0; i < axis; ++i) {
+      const int64_t e = x->shape[i];
+      if (e == 1) continue;
+      rows *= e;
+      if (n > 0 && a.ostride_x[n - 1] == x->stride[i] * e && a.ostride_o[n - 1] == out->stride[i] * e) {
+        a.oshape[n - 1] *= (uint32_t)e; a.ostride_x[n - 1] = x->stride[i]; a.ostride_o[n - 1] = out->stride[i];
+      } else {
+        if (n == 4) { ok = false; break; }
+        a.oshape[n] = (uint32_t)e; a.ostride_x[n] = x->stride[i]; a.ostride_o[n] = out->stride[i]; ++n;
+      }
+    }
+    for (int i = 0; i < n; ++i) if (a.ostride_x[i] % 4 || a.ostride_o[i] % 4) strides4 = false;
+    if (ok && rows < (int64_t(1) << 31)) {
+      a.nouter = n; a.rows = (uint32_t)rows;
+      const int64_t sx = x->stride[axis], so = out->stride[axis];
+      const bool vec = (sx == 1 && so == 1 && R % 4 == 0 && al16s(xp) && al16s(op) && strides4);
+      SmWarpExtra e{sx, so};
+      if (R <= 1024 && !(vec && R > 256)) {
+        softmax_row_warp_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, s.stream>>>(a, e);
+        return post_launch("wf2cu_softmax(row,warp)");
+      }
+      if (vec && R <= 1024) {
+        softmax_row_block_kernel<128, 2><<<(unsigned)rows, 128, 0, s.stream>>>(a);
+        return post_launch("wf2cu_softmax(row,block128)");
+      }
+      if (vec && R <= 4096) {
+        softmax_row_block_kernel<256, 4><<<(unsigned)rows, 256, 0, s.stream>>>(a);
+        return post_launch("wf2cu_softmax(row,block256)");
+      }
+      if (vec && R <= 16384) {
+        softmax_row_block_kernel<512, 8><<<(unsigned)rows, 512, 0, s.stream>>>(a);
+        return post_launch("wf2cu_softmax(row,block512)");
+      }
+      softmax_row_stream_kernel<<<(unsigned)rows, 512, 0, s.stream>>>(a, e);
+      return post_launch("wf2cu_softmax(row,stream)");
+    }
+  }
+  // lane kernel
+  SmLaneArgs a;
+  memset(&a, 0, sizeof(a));
+  a.x = xp; a.out = op; a.R = R; a.sR_x = x->stride[axis]; a.sR_o = out->stride[axis];
+  a.avoid_overflow = avoid_overflow;
+  a.nlanes = 1;
+  for (int i = 0; i < rank; ++i) {
+    if (i == axis || x->shape[i] == 1) continue;
+    a.lshape[a.nlane] = x->shape[i]; a.lstride_x[a.nlane] = x->stride[i]; a.lstride_o[a.nlane] = out->stride[i];
+    a.nlanes *= x->shape[i]; ++a.nlane;
+  }
+  int64_t grid = (a.nlanes + 255) / 256;
+  const int64_t cap = (int64_t)s.sm_count * 16;
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  if (R <= 16) softmax_lane_kernel<16><<<(unsigned)grid, 256, 0, s.stream>>>(a);
+  else if (R <= 64) softmax_lane_kernel<64><<<(unsigned)grid, 256, 0, s.stream>>>(a);
+  else softmax_lane_kernel<0><<<(unsigned)grid, 256, 0, s.stream>>>(a);
+  return post_launch("wf2cu_softmax(lane)");
+}

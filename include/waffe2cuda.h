@@ -1,0 +1,211 @@
+/*
+ * waffe2cuda.h — C ABI of libwaffe2cuda.so, the B200 (sm_100a) device library behind
+ * cl-waffe2's `CUDATensor` backend.
+ *
+ * This is the drop-in boundary: what `source/backends/cuda/*.lisp` binds through CFFI
+ * (`cl-waffe2_b200/lisp/`), exactly where the reference binds `cl-waffe2-simd.so`
+ * (`cl-waffe2-simd/api.lisp:63-274`) and Fortran-ABI BLAS
+ * (`source/backends/cpu/blas-functions.lisp:8-38`).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, no C++/torch types.
+ *  - every entry point returns int: 0 = ok, non-zero = error; the message is in
+ *    wf2cu_last_error() (thread-local).  The reference's C kernels return void and have no
+ *    error channel (`cl-waffe2-simd.c:153-155`); the Lisp side turns a non-zero status into a
+ *    condition so the VM's `runtime-error` wrapper (`source/vm/vm.lisp:230-256`) shows it.
+ *  - all work is enqueued asynchronously on ONE stream per process; the only host syncs are
+ *    wf2cu_d2h, wf2cu_get_f32, wf2cu_sync and the timer read-out.
+ *  - compute dtype is fp32 (the reference's `:float`); `:uint32` appears only as ArgMax output.
+ *  - there is no CPU fallback: without a B200 wf2cu_init fails and every entry point after it
+ *    returns WF2CU_ERR_NOT_INITIALISED.
+ */
+#ifndef WAFFE2CUDA_H
+#define WAFFE2CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WF2CU_MAX_RANK 8
+
+/* status codes */
+enum {
+  WF2CU_OK = 0,
+  WF2CU_ERR_CUDA = 1,            /* a CUDA runtime call failed                      */
+  WF2CU_ERR_INVALID = 2,         /* bad argument (rank, shape mismatch, null, ...)   */
+  WF2CU_ERR_UNSUPPORTED = 3,     /* well-formed request this library does not cover  */
+  WF2CU_ERR_NOT_INITIALISED = 4, /* wf2cu_init has not succeeded in this process     */
+  WF2CU_ERR_COMM = 5             /* NCCL failure / communicator missing              */
+};
+
+/*
+ * Strided view descriptor.  Lowered from an AbstractTensor
+ * (`source/vm/generic-tensor/tensor.lisp:40-111`): element (i0..i_{r-1}) of the view lives at
+ *     base[ offset + sum_k stride[k] * i_k ]          (element units, fp32)
+ * where the host has already folded the reference's view algebra into the numbers:
+ *     stride[k] = tensor-stride_k * (range_nth(view_k,1) - range_nth(view_k,0))   (0 on :broadcast)
+ *     offset    = tensor-initial-offset + sum_k tensor-stride_k * range_nth(view_k,0)
+ * (`do-compiled-loop.lisp:170-298`, `iterator/range.lisp:72-96`).  Strides may be 0
+ * (broadcast) or negative (reversed slice).  This replaces the per-row
+ * `ViewInstruction{offset,size,by}` a reference leaf receives (`view.lisp:50-69`).
+ */
+typedef struct wf2cu_view {
+  void*   base;
+  int64_t offset;
+  int32_t rank;
+  int32_t reserved;
+  int64_t shape[WF2CU_MAX_RANK];
+  int64_t stride[WF2CU_MAX_RANK];
+} wf2cu_view;
+
+/* ---- binary arithmetic: replaces waffe2_s{add,sub,mul,div} / scopy_
+ *      (`cl-waffe2-simd.c:153-250`, `backends/cpu/arithmetic.lisp:65-142`) ---- */
+enum { WF2CU_ADD = 0, WF2CU_SUB = 1, WF2CU_MUL = 2, WF2CU_DIV = 3, WF2CU_COPY = 4 };
+
+/* ---- unary math: replaces waffe2_s{sin..sqrt} (`cl-waffe2-simd.c:586-706`),
+ *      nodes of `base-impl/mathematics.lisp:13-257` ---- */
+enum {
+  WF2CU_SIN = 0, WF2CU_COS, WF2CU_TAN, WF2CU_ASIN, WF2CU_ACOS, WF2CU_ATAN,
+  WF2CU_SINH, WF2CU_COSH, WF2CU_TANH, WF2CU_ABS, WF2CU_EXP, WF2CU_LOGE,
+  WF2CU_LOG2, WF2CU_LOG10, WF2CU_LOG1P, WF2CU_SQRT, WF2CU_CBRT,
+  WF2CU_SIGN, WF2CU_SQUARE,           /* LispTensor-only nodes in the reference */
+  WF2CU_NEG, WF2CU_RECIP,             /* helpers used by fused programs          */
+  WF2CU_UNARY_COUNT
+};
+
+/* ---- compare: replaces waffe2_s{eq,lt,le,gt,ge}[ _scal ] (`cl-waffe2-simd.c:385-576`) ---- */
+enum { WF2CU_EQ = 0, WF2CU_LT = 1, WF2CU_LE = 2, WF2CU_GT = 3, WF2CU_GE = 4 };
+
+/* ===================== runtime ===================== */
+int  wf2cu_init(int device);                 /* select device, create the stream; fails without sm_100 */
+int  wf2cu_shutdown(void);
+const char* wf2cu_last_error(void);
+int  wf2cu_device_count(int* out);
+int  wf2cu_device_name(char* buf, size_t buflen);
+int  wf2cu_sync(void);
+int  wf2cu_stream(void** out_cudaStream);    /* the library's stream, for event timing by callers */
+int  wf2cu_set_stream(void* cudaStream);     /* adopt a caller-owned stream (NULL = back to own) */
+int  wf2cu_launch_count(int64_t* out);       /* kernels launched by this library since init      */
+
+/* storage: the `vec` of a CUDATensor.  Zero-filled like LispTensor's
+ * `:initial-element 0` (`backends/lisp/tensor.lisp:20-28`); refcounted because the VM aliases
+ * storage with (setf (tensor-vec a) (tensor-vec b)) (`vm/optimize-ir.lisp:4-18`). */
+int  wf2cu_malloc(size_t bytes, void** out);
+int  wf2cu_retain(void* dev);
+int  wf2cu_release(void* dev);               /* frees at refcount 0 */
+int  wf2cu_free(void* dev);                  /* == release           */
+int  wf2cu_memset0(void* dev, size_t offset_bytes, size_t bytes);
+int  wf2cu_h2d(void* dev, size_t offset_bytes, const void* host, size_t bytes);
+int  wf2cu_d2h(const void* dev, size_t offset_bytes, void* host, size_t bytes);   /* syncs */
+int  wf2cu_d2d(void* dst, size_t dst_off, const void* src, size_t src_off, size_t bytes);
+int  wf2cu_get_f32(const void* dev, int64_t index, float* out);                    /* vref, syncs */
+int  wf2cu_set_f32(void* dev, int64_t index, float value);                         /* (setf vref) */
+int  wf2cu_host_alloc(size_t bytes, void** out);   /* pinned staging for h2d/d2h */
+int  wf2cu_host_free(void* host);
+int  wf2cu_mem_in_use(size_t* bytes);
+
+/* timing on the library stream (CUDA events) */
+int  wf2cu_timer_start(void);
+int  wf2cu_timer_stop(float* elapsed_ms);    /* syncs on the stop event */
+int  wf2cu_l2_flush(void);                   /* writes a >L2 scratch buffer */
+
+/* CUDA-graph capture of a static instruction sequence (`vm/vm.lisp:260-289`) */
+int  wf2cu_graph_begin(void);
+int  wf2cu_graph_end(void** out_exec);
+int  wf2cu_graph_launch(void* exec);
+int  wf2cu_graph_destroy(void* exec);
+
+/* ===================== element-wise ===================== */
+/* dst <- dst OP src over views of equal shape.  Axes where dst has stride 0 and extent > 1 are
+ * REDUCTION axes: the reference runs `x[0] = x[0] OP y[i]` sequentially there
+ * (`cl-waffe2-simd.c:159,205-212`); here they are classified and tree-reduced
+ * (ADD, SUB, MUL; COPY keeps the last element).  This is how `!sum` arrives
+ * (`base-impl/reduction.lisp:60-79`). */
+int  wf2cu_ew_binary(int op, const wf2cu_view* dst, const wf2cu_view* src);
+/* out <- a OP b, the fused form of MoveTensorNode + {Add,Sub,Mul,Div}Node
+ * (`base-impl/arithmetic.lisp:150-152`).  out must not have reduction axes. */
+int  wf2cu_ew_binary3(int op, const wf2cu_view* out, const wf2cu_view* a, const wf2cu_view* b);
+/* dst <- dst OP scalar: the `A*=scal` family without the 4-byte H2D of `Scalar->MatNode`
+ * (`base-impl/fundamental.lisp:525-533`). */
+int  wf2cu_ew_scalar(int op, const wf2cu_view* dst, float scalar);
+int  wf2cu_fill(const wf2cu_view* dst, float value);
+/* dst <- f(src) */
+int  wf2cu_ew_unary(int fn, const wf2cu_view* src, const wf2cu_view* dst);
+/* dst <- src ^ n  (ExptNode, `backends/cpu/mathematics.lisp:55-75`) */
+int  wf2cu_pow(const wf2cu_view* src, const wf2cu_view* dst, float n);
+/* dst <- (x CMP y) ? then : else ; y == NULL compares against `scal`
+ * (`backends/cpu/logical.lisp:37-84`) */
+int  wf2cu_cmp(int op, const wf2cu_view* x, const wf2cu_view* y, float scal,
+               const wf2cu_view* dst, float then_value, float else_value);
+
+/* Fused element-wise chain: one pass over `nviews` equal-shape views running a register
+ * program.  Each instruction is 4 x int32: {opcode, dst_reg, a_reg, b_reg_or_imm_bits}.
+ * See WF2CU_P_* below.  Up to 16 registers, 64 instructions, 8 views. */
+enum {
+  WF2CU_P_LOAD = 0,   /* r[dst] = view[a]                          */
+  WF2CU_P_STORE,      /* view[a] = r[dst]                          */
+  WF2CU_P_IMM,        /* r[dst] = bits(b) as float                 */
+  WF2CU_P_ADD, WF2CU_P_SUB, WF2CU_P_MUL, WF2CU_P_DIV,   /* r[dst] = r[a] op r[b] (rn, no fma contraction) */
+  WF2CU_P_UNARY,      /* r[dst] = f_b(r[a]), b = WF2CU_SIN...      */
+  WF2CU_P_POW,        /* r[dst] = pow(r[a], r[b])                  */
+  WF2CU_P_CMPSEL,     /* r[dst] = (r[a] CMP r[b]) ? 1 : 0 ; CMP in bits 8.. of opcode */
+  WF2CU_P_MOV         /* r[dst] = r[a]                             */
+};
+int  wf2cu_fused(const int32_t* program, int n_instr, const wf2cu_view* views, int nviews);
+
+/* ===================== reductions / composites ===================== */
+/* out <- [out +] sum(x) over the axes where out has stride 0 or extent 1 vs x; the fused form of
+ * `A*=scal out 0` + `A+=B out* x` (`base-impl/reduction.lisp:60-79`).  scale multiplies the
+ * result (1/count gives `!mean`, `reduction.lisp:81-136`; division is done as a true divide by
+ * `divisor` when divisor != 0 to match `!div`). */
+int  wf2cu_reduce_sum(const wf2cu_view* x, const wf2cu_view* out_bcast, int accumulate, float divisor);
+/* `!softmax` (`nn/activation.lisp:126-159`): mean-shift (avoid_overflow) or plain, over `axis`. */
+int  wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow);
+/* MaxValue/MinValue/ArgMax/ArgMin over the last axis (`backends/cpu/matrix-ops.lisp:240-369`).
+ * out has x's shape with the last axis of extent 1; arg variants write uint32 indices. */
+int  wf2cu_reduce_maxmin(int is_min, const wf2cu_view* x, const wf2cu_view* out);
+int  wf2cu_argmaxmin(int is_min, const wf2cu_view* x, const wf2cu_view* out_u32);
+
+/* ===================== MatmulNode ===================== */
+/* C[b] <- op(A[b]) . op(B[b]), row-major, alpha=1 beta=0, replaces the reference's
+ * `sgemm_` call (`backends/cpu/matrix-ops.lisp:58-79`): op(A) is m x k, op(B) is k x n,
+ * C is m x n; trans flag = the operand is stored transposed (`LazyTransposeNode`).
+ * ld* in elements; batch strides in elements (0 = shared operand).
+ * Numerics: fp32-faithful (3xTF32 split on tcgen05, or exact fp32 FMA for shapes the tensor
+ * path does not take). */
+int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
+                const void* A, int64_t a_off, int64_t lda,
+                const void* B, int64_t b_off, int64_t ldb,
+                void* C, int64_t c_off, int64_t ldc,
+                int64_t batch, int64_t stride_a, int64_t stride_b, int64_t stride_c);
+/* 0 = auto, 1 = force fp32 SIMT path, 2 = force tcgen05 3xTF32, 3 = tcgen05 1xTF32 (not parity-grade) */
+int  wf2cu_gemm_set_mode(int mode);
+
+/* ===================== optimizers (fused chains of `optimizers/impls/*.lisp`) ===================== */
+/* p <- p - lr * g        (`sgd.lisp:20-26`) */
+int  wf2cu_sgd_step(void* param, int64_t p_off, const void* grad, int64_t g_off, int64_t n, float lr);
+/* Adam as written in `adam.lisp:45-116`:  m <- b1 m + (1-b1) g ; v <- b2 v + (1-b2) g^2 ;
+ * p <- p - lr_t * m / (sqrt(v) + eps), lr_t computed by the host.  grad_scale pre-multiplies g
+ * (1/world for the data-parallel mean). */
+int  wf2cu_adam_step(void* param, int64_t p_off, const void* grad, int64_t g_off,
+                     void* m, int64_t m_off, void* v, int64_t v_off, int64_t n,
+                     float lr_t, float beta1, float beta2, float eps, float grad_scale);
+
+/* `GPT2PositionalEmbedding` (`examples/gpt-2/utils.lisp:19-112`):
+ * out[b,p,:] = wte[round(ctx[b,p]),:] + wpe[p,:] ; token ids are floats. */
+int  wf2cu_embedding_gather(const void* ctx, int64_t batch, int64_t seq, const void* wte,
+                            const void* wpe, int64_t dim, void* out);
+
+/* ===================== multi-GPU (batch-sharded MLP step) ===================== */
+int  wf2cu_comm_unique_id(void* out128);                       /* rank 0: 128-byte NCCL id   */
+int  wf2cu_comm_init(int rank, int world, const void* id128);  /* one process per GPU        */
+int  wf2cu_allreduce_sum_f32(void* buf, int64_t offset, int64_t count);  /* on the stream    */
+int  wf2cu_comm_destroy(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WAFFE2CUDA_H */
