@@ -337,9 +337,17 @@ int wf2cu_l2_flush(void) {
   return 0;
 }
 
+// launches recorded while capturing are credited on every replay
+static std::unordered_map<void*, int64_t>& graph_launches() {
+  static std::unordered_map<void*, int64_t> m;
+  return m;
+}
+static int64_t g_capture_start = 0;
+
 int wf2cu_graph_begin(void) {
   WF2_REQUIRE_INIT();
   WF2_CUDA(cudaStreamBeginCapture(S().stream, cudaStreamCaptureModeThreadLocal));
+  g_capture_start = S().launches.load();
   return 0;
 }
 
@@ -351,6 +359,12 @@ int wf2cu_graph_end(void** out_exec) {
   cudaError_t e = cudaGraphInstantiate(&ex, g, 0);
   cudaGraphDestroy(g);
   if (e != cudaSuccess) return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__);
+  const int64_t captured = S().launches.load() - g_capture_start;
+  S().launches.fetch_sub(captured);  // nothing ran yet
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    graph_launches()[(void*)ex] = captured;
+  }
   *out_exec = (void*)ex;
   return 0;
 }
@@ -358,12 +372,21 @@ int wf2cu_graph_end(void** out_exec) {
 int wf2cu_graph_launch(void* exec) {
   WF2_REQUIRE_INIT();
   WF2_CUDA(cudaGraphLaunch((cudaGraphExec_t)exec, S().stream));
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = graph_launches().find(exec);
+    if (it != graph_launches().end()) S().launches.fetch_add(it->second);
+  }
   return 0;
 }
 
 int wf2cu_graph_destroy(void* exec) {
   WF2_REQUIRE_INIT();
   WF2_CUDA(cudaGraphExecDestroy((cudaGraphExec_t)exec));
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    graph_launches().erase(exec);
+  }
   return 0;
 }
 
