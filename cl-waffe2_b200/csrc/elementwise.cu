@@ -79,32 +79,37 @@ template <int NIN> struct GenArgs {
 // ---------------------------------------------------------------- vec kernel
 template <int NIN, class F>
 __global__ void __launch_bounds__(kThreads) ew_vec_kernel(const F f, const __grid_constant__ VecArgs<NIN> a) {
-  const int64_t base = (int64_t)blockIdx.x * (kThreads * kUnroll) + threadIdx.x;
+  // n4 < 2^31 is guaranteed by the dispatcher: all index math below is 32-bit
+  const uint32_t base = blockIdx.x * (uint32_t)(kThreads * kUnroll) + threadIdx.x;
+  const uint32_t n4 = (uint32_t)a.n4;
   float4 v[NIN > 0 ? NIN : 1][kUnroll];
   int64_t ooff[kUnroll];
 #pragma unroll
   for (int u = 0; u < kUnroll; ++u) {
-    const int64_t idx = base + (int64_t)u * kThreads;
+    const uint32_t idx = base + (uint32_t)u * kThreads;
     ooff[u] = -1;
-    if (idx < a.n4) {
+    if (idx < n4) {
       uint32_t c4;
       int64_t o_out = 0;
       int64_t o_in[NIN > 0 ? NIN : 1];
 #pragma unroll
       for (int j = 0; j < NIN; ++j) o_in[j] = 0;
       if (a.outer_rank == 0) {
-        c4 = (uint32_t)idx;
+        c4 = idx;
       } else {
-        uint32_t row = (uint32_t)(idx / a.inner4);
-        c4 = (uint32_t)(idx - (int64_t)row * a.inner4);
-        for (int d = a.outer_rank - 1; d >= 0; --d) {
-          uint32_t q = row / a.oshape[d];
-          uint32_t r = row - q * a.oshape[d];
+        uint32_t row = idx / a.inner4;
+        c4 = idx - row * a.inner4;
+        for (int d = a.outer_rank - 1; d > 0; --d) {
+          const uint32_t q = row / a.oshape[d];
+          const uint32_t r = row - q * a.oshape[d];
           row = q;
           o_out += (int64_t)r * a.ostride_out[d];
 #pragma unroll
           for (int j = 0; j < NIN; ++j) o_in[j] += (int64_t)r * a.ostride_in[j][d];
         }
+        o_out += (int64_t)row * a.ostride_out[0];
+#pragma unroll
+        for (int j = 0; j < NIN; ++j) o_in[j] += (int64_t)row * a.ostride_in[j][0];
       }
       ooff[u] = o_out + (int64_t)c4 * 4;
 #pragma unroll
@@ -223,6 +228,89 @@ __global__ void __launch_bounds__(256) ew_tr_kernel(const F f, const __grid_cons
   }
 }
 
+// Vectorised variant: 64(J) x 64(I) tile, 128-bit global accesses on both sides, 16 elements per
+// thread in flight.  Needs I % 4 == 0, J % 4 == 0 and 16-byte aligned rows for every operand.
+template <int NIN, class F>
+__global__ void __launch_bounds__(256) ew_tr4_kernel(const F f, const __grid_constant__ TrArgs<NIN> a) {
+  __shared__ float tile[NIN > 0 ? NIN : 1][64][65];   // [i][j], pitch 65: conflict-light both ways
+  uint32_t bid = blockIdx.x;
+  const uint32_t ti = bid % a.tilesI; bid /= a.tilesI;
+  const uint32_t tj = bid % a.tilesJ; bid /= a.tilesJ;
+  int64_t o_out = 0;
+  int64_t o_in[NIN > 0 ? NIN : 1];
+#pragma unroll
+  for (int j = 0; j < NIN; ++j) o_in[j] = 0;
+  for (int d = a.nbatch - 1; d >= 0; --d) {
+    const uint32_t q = bid / a.bshape[d];
+    const uint32_t r = bid - q * a.bshape[d];
+    bid = q;
+    o_out += (int64_t)r * a.bstride_out[d];
+#pragma unroll
+    for (int j = 0; j < NIN; ++j) o_in[j] += (int64_t)r * a.bstride_in[j][d];
+  }
+  const int lx = (threadIdx.x & 15) * 4;   // 4-wide column group inside the tile
+  const int ly = threadIdx.x >> 4;         // 0..15
+  const int64_t i0 = (int64_t)ti * 64, j0 = (int64_t)tj * 64;
+  // phase 1: staged inputs are contiguous along J: float4 loads along J, scattered to tile[i][j..j+3]
+#pragma unroll
+  for (int j = 0; j < NIN; ++j) {
+    if (a.tr_mask & (1u << j)) {
+      float4 t[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int64_t gi = i0 + ly + 16 * k, gj = j0 + lx;
+        t[k] = (gi < a.I && gj < a.J)
+                   ? *reinterpret_cast<const float4*>(a.in[j] + o_in[j] + gi * a.sI_in[j] + gj)
+                   : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float* row = &tile[j][ly + 16 * k][lx];
+        row[0] = t[k].x; row[1] = t[k].y; row[2] = t[k].z; row[3] = t[k].w;
+      }
+    }
+  }
+  __syncthreads();
+  // phase 2: float4 along I for the output and the non-staged inputs
+  float4 direct[NIN > 0 ? NIN : 1][4];
+#pragma unroll
+  for (int j = 0; j < NIN; ++j) {
+    if (!(a.tr_mask & (1u << j))) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int64_t gj = j0 + ly + 16 * k, gi = i0 + lx;
+        if (gi < a.I && gj < a.J) {
+          if (a.sI_in[j] == 0) {
+            const float sv = a.in[j][o_in[j] + gj * a.sJ_in[j]];
+            direct[j][k] = make_float4(sv, sv, sv, sv);
+          } else {
+            direct[j][k] = *reinterpret_cast<const float4*>(a.in[j] + o_in[j] + gj * a.sJ_in[j] + gi);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int jj = ly + 16 * k;
+    const int64_t gj = j0 + jj, gi = i0 + lx;
+    if (gi < a.I && gj < a.J) {
+      float r[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float x[NIN > 0 ? NIN : 1];
+#pragma unroll
+        for (int j = 0; j < NIN; ++j) {
+          if (a.tr_mask & (1u << j)) x[j] = tile[j][lx + e][jj];
+          else x[j] = (e == 0) ? direct[j][k].x : (e == 1) ? direct[j][k].y : (e == 2) ? direct[j][k].z : direct[j][k].w;
+        }
+        r[e] = f(x);
+      }
+      *reinterpret_cast<float4*>(a.out + o_out + gj * a.sJ_out + gi) = make_float4(r[0], r[1], r[2], r[3]);
+    }
+  }
+}
+
 // ---------------------------------------------------------------- dispatch
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
@@ -312,11 +400,23 @@ int launch_ew(const F& f, const wf2cu_view* out, const wf2cu_view* const* ins, c
         a.sJ_in[j] = p.stride[1 + j][J];
         if (a.sJ_in[j] == 1 && a.sI_in[j] != 1 && a.sI_in[j] != 0) a.tr_mask |= (1u << j);
       }
-      a.tilesI = (uint32_t)((a.I + 31) / 32);
-      a.tilesJ = (uint32_t)((a.J + 31) / 32);
+      // 128-bit variant: every extent/stride a multiple of 4 and 16-byte aligned bases
+      bool v4 = (a.I % 4 == 0) && (a.J % 4 == 0) && aligned16(optr) && (a.sJ_out % 4 == 0) && a.I >= 64 && a.J >= 64;
+      for (int b = 0; b < nb && v4; ++b) if (a.bstride_out[b] % 4) v4 = false;
+      for (int j = 0; j < NIN && v4; ++j) {
+        if (!aligned16(iptr[j])) v4 = false;
+        for (int b = 0; b < nb; ++b) if (a.bstride_in[j][b] % 4) v4 = false;
+        if (a.tr_mask & (1u << j)) { if (a.sI_in[j] % 4) v4 = false; }
+        else if (a.sI_in[j] == 1) { if (a.sJ_in[j] % 4) v4 = false; }
+        else if (a.sI_in[j] != 0) v4 = false;
+      }
+      const int tile = v4 ? 64 : 32;
+      a.tilesI = (uint32_t)((a.I + tile - 1) / tile);
+      a.tilesJ = (uint32_t)((a.J + tile - 1) / tile);
       const int64_t grid = (int64_t)a.tilesI * a.tilesJ * nbatch_total;
       if (nb <= 3 && grid < (int64_t(1) << 31)) {
-        ew_tr_kernel<NIN, F><<<(unsigned)grid, 256, 0, s.stream>>>(f, a);
+        if (v4) ew_tr4_kernel<NIN, F><<<(unsigned)grid, 256, 0, s.stream>>>(f, a);
+        else ew_tr_kernel<NIN, F><<<(unsigned)grid, 256, 0, s.stream>>>(f, a);
         return post_launch(who);
       }
     }

@@ -82,6 +82,7 @@ struct RowArgs {
   int64_t chunk_len; // columns per chunk (multiple of 4)
   uint32_t chunks;
   int vec;           // 1: float4 loads legal for every row
+  unsigned int* counters;  // per-row tickets for the fused second stage (chunks > 1)
 };
 
 template <class M, int THREADS>
@@ -108,6 +109,18 @@ __global__ void __launch_bounds__(THREADS) reduce_rows_kernel(const __grid_const
     const float4* p4 = reinterpret_cast<const float4*>(p);
     int64_t i = v0 + threadIdx.x;
     // 4 independent 128-bit loads in flight per thread
+    for (; i + 7 * THREADS < v1; i += 8 * THREADS) {   // 8 independent 128-bit loads in flight
+      float4 x[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) x[k] = p4[i + k * THREADS];
+#pragma unroll
+      for (int k = 0; k < 8; k += 4) {
+        acc0 = M::op(acc0, M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w)));
+        acc1 = M::op(acc1, M::op(M::op(x[k + 1].x, x[k + 1].y), M::op(x[k + 1].z, x[k + 1].w)));
+        acc2 = M::op(acc2, M::op(M::op(x[k + 2].x, x[k + 2].y), M::op(x[k + 2].z, x[k + 2].w)));
+        acc3 = M::op(acc3, M::op(M::op(x[k + 3].x, x[k + 3].y), M::op(x[k + 3].z, x[k + 3].w)));
+      }
+    }
     for (; i + 3 * THREADS < v1; i += 4 * THREADS) {
       const float4 x0 = p4[i], x1 = p4[i + THREADS], x2 = p4[i + 2 * THREADS], x3 = p4[i + 3 * THREADS];
       acc0 = M::op(acc0, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
@@ -125,9 +138,29 @@ __global__ void __launch_bounds__(THREADS) reduce_rows_kernel(const __grid_const
   }
   float acc = M::op(M::op(acc0, acc1), M::op(acc2, acc3));
   acc = block_reduce<M, THREADS>(acc, smem);
+  if (a.chunks == 1) {
+    if (threadIdx.x == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
+    return;
+  }
+  // chunks > 1: publish the partial; the LAST CTA of this row folds all partials in a fixed order
+  // (deterministic) and resets the ticket, so no second launch is needed.
+  __shared__ bool is_last;
   if (threadIdx.x == 0) {
-    if (a.chunks > 1) a.partial[(int64_t)row_id * a.chunks + chunk] = acc;
-    else a.dst[dofs] = fin(a.dst[dofs], acc);
+    a.partial[(int64_t)row_id * a.chunks + chunk] = acc;
+    __threadfence();
+    const unsigned int t = atomicAdd(&a.counters[row_id], 1u);
+    is_last = (t == a.chunks - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const float* pp = a.partial + (int64_t)row_id * a.chunks;
+  float v = M::id();
+  for (uint32_t c = threadIdx.x; c < a.chunks; c += THREADS) v = M::op(v, __ldcg(pp + c));
+  v = block_reduce<M, THREADS>(v, smem);
+  if (threadIdx.x == 0) {
+    a.dst[dofs] = fin(a.dst[dofs], v);
+    a.counters[row_id] = 0;
   }
 }
 
@@ -151,10 +184,20 @@ __global__ void __launch_bounds__(256) reduce_rows_warp_kernel(const __grid_cons
   if (a.vec) {
     const float4* p4 = reinterpret_cast<const float4*>(p);
     const int64_t v1 = a.cols >> 2;
-    for (int64_t i = lane; i < v1; i += 32) {
+    float b1 = M::id(), b2 = M::id(), b3 = M::id();
+    int64_t i = lane;
+    for (; i + 96 < v1; i += 128) {
+      const float4 x0 = p4[i], x1 = p4[i + 32], x2 = p4[i + 64], x3 = p4[i + 96];
+      acc = M::op(acc, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
+      b1 = M::op(b1, M::op(M::op(x1.x, x1.y), M::op(x1.z, x1.w)));
+      b2 = M::op(b2, M::op(M::op(x2.x, x2.y), M::op(x2.z, x2.w)));
+      b3 = M::op(b3, M::op(M::op(x3.x, x3.y), M::op(x3.z, x3.w)));
+    }
+    for (; i < v1; i += 32) {
       const float4 x = p4[i];
       acc = M::op(acc, M::op(M::op(x.x, x.y), M::op(x.z, x.w)));
     }
+    acc = M::op(M::op(acc, b1), M::op(b2, b3));
     for (int64_t c = (v1 << 2) + lane; c < a.cols; c += 32) acc = M::op(acc, p[c]);
   } else {
     for (int64_t c = lane; c < a.cols; c += 32) acc = M::op(acc, p[c]);
@@ -163,24 +206,56 @@ __global__ void __launch_bounds__(256) reduce_rows_warp_kernel(const __grid_cons
   if (lane == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
 }
 
-// second stage for rows: dst[row] = fin(dst[row], reduce(partial[row, 0..chunks)))
-template <class M>
-__global__ void __launch_bounds__(256) reduce_rows_final_kernel(const __grid_constant__ RowArgs a, const Fin fin) {
+// Tile kernel for rows that fit a register tile: a CTA of 256 threads takes RPC rows, TPR = 256/RPC
+// threads per row, and every thread issues ALL of its (up to 8) 128-bit loads before the first add,
+// so a resident SM has ~256 KB of loads in flight.  Needs a.vec and cols/4 <= TPR * 8.
+template <class M, int RPC>
+__global__ void __launch_bounds__(256) reduce_rows_tile_kernel(const __grid_constant__ RowArgs a, const Fin fin, uint32_t nrows) {
+  constexpr int TPR = 256 / RPC;
+  constexpr int WPR = TPR / 32;                 // warps per row
   __shared__ float smem[8];
-  uint32_t row = blockIdx.x;
-  const float* p = a.partial + (int64_t)row * a.chunks;
-  float acc = M::id();
-  for (uint32_t c = threadIdx.x; c < a.chunks; c += 256) acc = M::op(acc, p[c]);
-  acc = block_reduce<M, 256>(acc, smem);
-  if (threadIdx.x == 0) {
-    int64_t dofs = 0;
-    for (int d = a.nkept - 1; d >= 0; --d) {
-      const uint32_t q = row / a.kshape[d];
-      const uint32_t r = row - q * a.kshape[d];
-      row = q;
-      dofs += (int64_t)r * a.kstride_dst[d];
-    }
-    a.dst[dofs] = fin(a.dst[dofs], acc);
+  const int sub = threadIdx.x / TPR;            // row slot inside the CTA
+  const int t = threadIdx.x % TPR;
+  const uint32_t row_id = blockIdx.x * RPC + sub;
+  const bool live = row_id < nrows;
+  int64_t so = 0, dofs = 0;
+  uint32_t row = live ? row_id : 0;
+  for (int d = a.nkept - 1; d >= 0; --d) {
+    const uint32_t q = row / a.kshape[d];
+    const uint32_t r = row - q * a.kshape[d];
+    row = q;
+    so += (int64_t)r * a.kstride_src[d];
+    dofs += (int64_t)r * a.kstride_dst[d];
+  }
+  const float4* p4 = reinterpret_cast<const float4*>(a.src + so);
+  const int64_t v1 = a.cols >> 2;
+  float4 x[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int64_t i = t + (int64_t)k * TPR;
+    x[k] = (live && i < v1) ? p4[i] : make_float4(M::id(), M::id(), M::id(), M::id());
+  }
+  float acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] = M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w));
+  float v = M::op(M::op(M::op(acc[0], acc[1]), M::op(acc[2], acc[3])), M::op(M::op(acc[4], acc[5]), M::op(acc[6], acc[7])));
+  if (live) {
+    const float* p = a.src + so;
+    for (int64_t c = (v1 << 2) + t; c < a.cols; c += TPR) v = M::op(v, p[c]);
+  }
+  v = warp_reduce<M>(v);
+  if (WPR == 1) {
+    if (live && (threadIdx.x & 31) == 0) a.dst[dofs] = fin(a.dst[dofs], v);
+    return;
+  }
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) smem[w] = v;
+  __syncthreads();
+  if (t == 0 && live) {
+    float r = smem[sub * WPR];
+#pragma unroll
+    for (int k = 1; k < WPR; ++k) r = M::op(r, smem[sub * WPR + k]);
+    a.dst[dofs] = fin(a.dst[dofs], r);
   }
 }
 
@@ -195,6 +270,7 @@ struct ColArgs {
   uint32_t splits;         // CTAs along R
   int64_t rows_per_split;
   int vec;
+  unsigned int* counters;  // per (batch, column-block) tickets: the last split folds the partials
 };
 
 // block = 32 (x: columns, float4 each when vec) x 8 (y: rows)
@@ -214,16 +290,23 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
     const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * 4;
     if (col < a.K) {
       int64_t r = r0 + ty;
-      for (; r + 8 < r1; r += 16) {
+      float4 acc3 = acc2, acc4 = acc2;
+      for (; r + 24 < r1; r += 32) {   // 4 independent 128-bit loads in flight
         const float4 x = *reinterpret_cast<const float4*>(base + r * a.sR_src + col);
         const float4 y = *reinterpret_cast<const float4*>(base + (r + 8) * a.sR_src + col);
+        const float4 z = *reinterpret_cast<const float4*>(base + (r + 16) * a.sR_src + col);
+        const float4 w = *reinterpret_cast<const float4*>(base + (r + 24) * a.sR_src + col);
         acc.x = M::op(acc.x, x.x); acc.y = M::op(acc.y, x.y); acc.z = M::op(acc.z, x.z); acc.w = M::op(acc.w, x.w);
         acc2.x = M::op(acc2.x, y.x); acc2.y = M::op(acc2.y, y.y); acc2.z = M::op(acc2.z, y.z); acc2.w = M::op(acc2.w, y.w);
+        acc3.x = M::op(acc3.x, z.x); acc3.y = M::op(acc3.y, z.y); acc3.z = M::op(acc3.z, z.z); acc3.w = M::op(acc3.w, z.w);
+        acc4.x = M::op(acc4.x, w.x); acc4.y = M::op(acc4.y, w.y); acc4.z = M::op(acc4.z, w.z); acc4.w = M::op(acc4.w, w.w);
       }
       for (; r < r1; r += 8) {
         const float4 x = *reinterpret_cast<const float4*>(base + r * a.sR_src + col);
         acc.x = M::op(acc.x, x.x); acc.y = M::op(acc.y, x.y); acc.z = M::op(acc.z, x.z); acc.w = M::op(acc.w, x.w);
       }
+      acc2.x = M::op(acc2.x, M::op(acc3.x, acc4.x)); acc2.y = M::op(acc2.y, M::op(acc3.y, acc4.y));
+      acc2.z = M::op(acc2.z, M::op(acc3.z, acc4.z)); acc2.w = M::op(acc2.w, M::op(acc3.w, acc4.w));
     }
     acc.x = M::op(acc.x, acc2.x); acc.y = M::op(acc.y, acc2.y); acc.z = M::op(acc.z, acc2.z); acc.w = M::op(acc.w, acc2.w);
   } else {
@@ -239,16 +322,14 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
   }
   sm[ty][tx] = acc;
   __syncthreads();
+  const bool final_stage = (a.splits == 1);
   if (ty == 0) {
 #pragma unroll
     for (int k = 1; k < 8; ++k) {
       const float4 o = sm[k][tx];
       acc.x = M::op(acc.x, o.x); acc.y = M::op(acc.y, o.y); acc.z = M::op(acc.z, o.z); acc.w = M::op(acc.w, o.w);
     }
-    float* outp;
-    const bool final_stage = (a.splits == 1);
-    if (final_stage) outp = a.dst + b * a.sB_dst;
-    else outp = a.partial + (b * a.splits + split) * a.K;
+    float* outp = final_stage ? a.dst + b * a.sB_dst : a.partial + (b * a.splits + split) * a.K;
     if (a.vec) {
       const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * 4;
       if (col < a.K) {
@@ -268,6 +349,65 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
         const int64_t c = cb + 32 * k;
         if (c < a.K) outp[c] = final_stage ? fin(outp[c], vals[k]) : vals[k];
       }
+    }
+  }
+  if (final_stage || a.counters == nullptr) return;
+  // fused second stage: the last split to arrive for this (batch, column block) folds all partials
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int t = atomicAdd(&a.counters[b * gridDim.x + blockIdx.x], 1u);
+    is_last = (t == a.splits - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  {
+    // columns of this block: 128; thread (tx, ty): column group tx (4 columns), splits ty, ty+8, ...
+    const float* pb = a.partial + b * a.splits * a.K;
+    float4 t4 = make_float4(M::id(), M::id(), M::id(), M::id());
+    const int64_t colv = ((int64_t)blockIdx.x * 32 + tx) * 4;
+    for (uint32_t sp = ty; sp < a.splits; sp += 8) {
+      const float* q = pb + (int64_t)sp * a.K;
+      if (a.vec) {
+        if (colv < a.K) {
+          const float4 o = __ldcg(reinterpret_cast<const float4*>(q + colv));
+          t4.x = M::op(t4.x, o.x); t4.y = M::op(t4.y, o.y); t4.z = M::op(t4.z, o.z); t4.w = M::op(t4.w, o.w);
+        }
+      } else {
+        const int64_t cb = (int64_t)blockIdx.x * 128 + tx;
+        if (cb < a.K) t4.x = M::op(t4.x, __ldcg(q + cb));
+        if (cb + 32 < a.K) t4.y = M::op(t4.y, __ldcg(q + cb + 32));
+        if (cb + 64 < a.K) t4.z = M::op(t4.z, __ldcg(q + cb + 64));
+        if (cb + 96 < a.K) t4.w = M::op(t4.w, __ldcg(q + cb + 96));
+      }
+    }
+    sm[ty][tx] = t4;
+    __syncthreads();
+    if (ty == 0) {
+#pragma unroll
+      for (int k = 1; k < 8; ++k) {
+        const float4 o = sm[k][tx];
+        t4.x = M::op(t4.x, o.x); t4.y = M::op(t4.y, o.y); t4.z = M::op(t4.z, o.z); t4.w = M::op(t4.w, o.w);
+      }
+      float* outp = a.dst + b * a.sB_dst;
+      if (a.vec) {
+        if (colv < a.K) {
+          float4 d = *reinterpret_cast<float4*>(outp + colv);
+          d.x = fin(d.x, t4.x); d.y = fin(d.y, t4.y); d.z = fin(d.z, t4.z); d.w = fin(d.w, t4.w);
+          *reinterpret_cast<float4*>(outp + colv) = d;
+        }
+      } else {
+        const int64_t cb = (int64_t)blockIdx.x * 128 + tx;
+        const float vals[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int64_t c = cb + 32 * k;
+          if (c < a.K) outp[c] = fin(outp[c], vals[k]);
+        }
+      }
+      if (tx == 0) a.counters[b * gridDim.x + blockIdx.x] = 0;
     }
   }
 }
@@ -361,38 +501,49 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
     a.cols = p.shape[last];
     a.vec = vec ? 1 : 0;
     if (rows < (int64_t(1) << 31)) {
-      if (a.cols <= 1024 && rows >= 64) {
+      // register-tile kernel: all loads of a row tile issued up front
+      if (a.vec && a.cols <= 8192 && rows * a.cols >= (int64_t(1) << 16)) {
+        const int64_t v1 = a.cols >> 2;
+        a.chunks = 1; a.chunk_len = a.cols;
+        if (v1 <= 256) {
+          reduce_rows_tile_kernel<M, 8><<<(unsigned)((rows + 7) / 8), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+        } else if (v1 <= 512) {
+          reduce_rows_tile_kernel<M, 4><<<(unsigned)((rows + 3) / 4), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+        } else if (v1 <= 1024) {
+          reduce_rows_tile_kernel<M, 2><<<(unsigned)((rows + 1) / 2), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+        } else {
+          reduce_rows_tile_kernel<M, 1><<<(unsigned)rows, 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+        }
+        return post_launch(who);
+      }
+      const int64_t fill = (int64_t)s.sm_count * 16;   // warps needed to keep every SM busy
+      if ((a.cols <= 1024 && rows >= 64) || (rows >= fill && a.cols <= 65536)) {
         a.chunks = 1; a.chunk_len = a.cols;
         reduce_rows_warp_kernel<M><<<(unsigned)((rows + 7) / 8), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
         return post_launch(who);
       }
-      // split long rows when there are too few of them to fill 148 SMs
+      // split long rows when there are too few of them to fill 148 SMs; a chunk is a whole number
+      // of 4096-float units (256 threads x 4 float4 x 4 loads in flight)
       uint32_t chunks = 1;
+      int64_t chunk_len = a.cols;
       const int64_t target_ctas = (int64_t)s.sm_count * 8;
-      if (rows < target_ctas && a.cols >= 8192) {
+      if (rows < target_ctas && a.cols >= 8192 && rows <= 4096) {
+        const int64_t units = (a.cols + 8191) / 8192;
         int64_t want = (target_ctas + rows - 1) / rows;
-        const int64_t maxc = a.cols / 4096;  // >= 4096 columns per chunk
-        if (want > maxc) want = maxc;
-        if (want < 1) want = 1;
-        chunks = (uint32_t)want;
+        if (want > units) want = units;
+        const int64_t upc = (units + want - 1) / want;   // units per chunk
+        chunk_len = upc * 8192;
+        chunks = (uint32_t)((a.cols + chunk_len - 1) / chunk_len);
       }
-      int64_t chunk_len = (a.cols + chunks - 1) / chunks;
-      chunk_len = (chunk_len + 3) & ~int64_t(3);
-      chunks = (uint32_t)((a.cols + chunk_len - 1) / chunk_len);
       a.chunks = chunks; a.chunk_len = chunk_len;
       if (chunks > 1) {
         rc = ensure_scratch((size_t)rows * chunks * sizeof(float));
         if (rc) return rc;
         a.partial = (float*)s.scratch;
+        a.counters = s.counters;
       }
       reduce_rows_kernel<M, 256><<<(unsigned)(rows * chunks), 256, 0, s.stream>>>(a, fin);
-      rc = post_launch(who);
-      if (rc) return rc;
-      if (chunks > 1) {
-        reduce_rows_final_kernel<M><<<(unsigned)rows, 256, 0, s.stream>>>(a, fin);
-        rc = post_launch(who);
-      }
-      return rc;
+      return post_launch(who);
     }
   }
   // ---- cols: [B,] R, K with K contiguous in both, R reduced, B kept
@@ -407,7 +558,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
     bool vec = al16(sptr) && al16(dptr) && (a.K % 4 == 0) && (a.sR_src % 4 == 0) && (a.sB_src % 4 == 0) && (a.sB_dst % 4 == 0);
     a.vec = vec ? 1 : 0;
     const int64_t colblocks = (a.K + 127) / 128;
-    const int64_t target_ctas = (int64_t)s.sm_count * 4;
+    const int64_t target_ctas = (int64_t)s.sm_count * 8;
     int64_t splits = 1;
     if (colblocks * a.B < target_ctas) {
       splits = (target_ctas + colblocks * a.B - 1) / (colblocks * a.B);
@@ -419,16 +570,18 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
     splits = (a.R + rps - 1) / rps;
     a.splits = (uint32_t)splits; a.rows_per_split = rps;
     if (a.B < 65536 && splits < 65536) {
+      const bool fused2 = splits > 1 && colblocks * a.B <= 4096;
       if (splits > 1) {
         rc = ensure_scratch((size_t)a.B * splits * a.K * sizeof(float));
         if (rc) return rc;
         a.partial = (float*)s.scratch;
+        a.counters = fused2 ? s.counters : nullptr;
       }
       dim3 grid((unsigned)colblocks, (unsigned)splits, (unsigned)a.B);
       reduce_cols_kernel<M><<<grid, 256, 0, s.stream>>>(a, fin);
       rc = post_launch(who);
       if (rc) return rc;
-      if (splits > 1) {
+      if (splits > 1 && !fused2) {
         dim3 g2((unsigned)((a.K + 255) / 256), (unsigned)a.B);
         reduce_cols_final_kernel<M><<<g2, 256, 0, s.stream>>>(a, fin);
         rc = post_launch(who);

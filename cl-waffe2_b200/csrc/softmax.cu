@@ -293,8 +293,8 @@ extern "C" int wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axi
         return post_launch("wf2cu_softmax(row,block128)");
       }
       if (vec && R <= 4096) {
-        softmax_row_block_kernel<256, 4><<<(unsigned)rows, 256, 0, s.stream>>>(a);
-        return post_launch("wf2cu_softmax(row,block256)");
+        softmax_row_block_kernel<128, 8><<<(unsigned)rows, 128, 0, s.stream>>>(a);
+        return post_launch("wf2cu_softmax(row,block128x8)");
       }
       if (vec && R <= 16384) {
         softmax_row_block_kernel<512, 8><<<(unsigned)rows, 512, 0, s.stream>>>(a);

@@ -187,7 +187,9 @@ def _red_check(got, oracle, truth, sumabs, tol=1e-5):
 
 @pytest.mark.parametrize("shape,axis", [((64, 300), 1), ((64, 300), 0), ((64, 300), True), ((5, 7, 9), 1),
                                         ((5, 7, 9), (0, 2)), ((4, 2048), 1), ((2000, 8), 0), ((3, 1031), -1),
-                                        ((100, 100, 10), True)])
+                                        ((100, 100, 10), True), ((512, 4096), 1), ((300, 1000), 1), ((100, 8192), 1),
+                                        ((70, 2048), -1), ((3, 100000), 1), ((1, 300000), True), ((4096, 512), 0),
+                                        ((6, 64, 4096), 2), ((6, 300, 640), 1)])
 def test_sum_axes(gpu, L, shape, axis):
     d = RNG.normal(size=shape).astype(np.float32)
     gx, ox = pair(gpu, L, shape, d)
