@@ -632,3 +632,35 @@ def argmaxmin(name: str, x: OTensor) -> np.ndarray:
     a = np.abs(arr)
     idx = a.argmax(axis=1) if name == "max" else a.argmin(axis=1)
     return idx.astype(np.uint32).reshape(x.shape[:-1] + [1])
+
+
+# ======================================================================================
+# MatMulNode — backends/cpu/matrix-ops.lisp:12-237
+# ======================================================================================
+def _sgemm(a2: np.ndarray, b2: np.ndarray, ta: bool, tb: bool) -> np.ndarray:
+    """One `sgemm_` call exactly as CPUTensor issues it for row-major storage
+    (matrix-ops.lisp:58-79): the operands are swapped and the row-major buffers are handed to the
+    column-major BLAS untouched, `sgemm_(transB, transA, n, m, k, 1.0, B, ldb, A, lda, 0.0, C, ldc)`.
+    OpenBLAS is not vendored by the reference (system `libblas`, no pinned version); the stand-in is
+    the OpenBLAS bundled with scipy."""
+    from scipy.linalg import blas
+    a2 = np.ascontiguousarray(a2, dtype=np.float32)
+    b2 = np.ascontiguousarray(b2, dtype=np.float32)
+    c_t = blas.sgemm(1.0, b2.T, a2.T, trans_a=1 if tb else 0, trans_b=1 if ta else 0)  # (n, m) column-major
+    return np.ascontiguousarray(c_t.T)
+
+
+def matmul(a: OTensor, b: OTensor, ta: bool = False, tb: bool = False) -> OTensor:
+    """`(!matmul a b)` with `(!t ·)` flags: C[~ i k] <- A[~ i j] B[~ j k], one sgemm per batch index
+    (`call-with-view :at-least-dim 2`); viewed/permuted operands are made contiguous first."""
+    A = a.to_numpy()
+    B = b.to_numpy()
+    batch_shape = list(A.shape[:-2]) if A.ndim >= B.ndim else list(B.shape[:-2])
+    A3 = A.reshape((-1,) + A.shape[-2:])
+    B3 = B.reshape((-1,) + B.shape[-2:])
+    nb = max(A3.shape[0], B3.shape[0])
+    outs = []
+    for i in range(nb):
+        outs.append(_sgemm(A3[i % A3.shape[0]], B3[i % B3.shape[0]], ta, tb))
+    C = np.stack(outs).reshape(batch_shape + list(outs[0].shape))
+    return make_tensor(list(C.shape), data=C)

@@ -1,0 +1,167 @@
+"""CPU-only checks of the product's host side: the view algebra / lowering of CUDATensor against
+the oracle's restatement of the reference (no device memory is touched: tensors adopt a fake
+pointer), and the C ABI: the library loads, exports every symbol include/waffe2cuda.h declares, and
+refuses to compute without a B200 (no CPU fallback)."""
+import ctypes
+import importlib
+import itertools
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import loopnest as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def fake_tensor(wf, shape, order="column"):
+    n = int(np.prod(shape))
+    return wf.CUDATensor(wf.Storage(n * 4, ptr=0x10000), shape, order=order)
+
+
+def lowered_offsets(t):
+    """Flat storage offsets of every visible element, from the lowered wf2cu_view."""
+    lv = t.lower()
+    shape = [lv.shape[i] for i in range(lv.rank)]
+    off = np.full(shape if shape else (1,), lv.offset, dtype=np.int64)
+    for ax in range(lv.rank):
+        sh = [1] * lv.rank
+        sh[ax] = shape[ax]
+        off = off + (np.arange(shape[ax], dtype=np.int64) * lv.stride[ax]).reshape(sh)
+    return off
+
+
+def oracle_offsets(t):
+    """Same, from the oracle's mref arithmetic (tensor.lisp:671-693)."""
+    n = len(t.vec)
+    t.vec[:] = np.arange(n, dtype=np.float32)
+    return t.to_numpy().astype(np.int64)
+
+
+SUBS_2D = [
+    (True, True), ([2, 14], [4, 28]), ([0, 20, 2], True), (True, [0, 36, -1]), ([1, 19, -3], [2, 34, 4]),
+    (3, [8, 16]), ([5, 6], True), ([0, -1], [1, -2]), (True, [36, 0, 2]), ([19, 1, 3], [0, 36, 5]),
+]
+
+
+@pytest.mark.parametrize("subs", SUBS_2D)
+@pytest.mark.parametrize("order", ["column", "row"])
+def test_view_lowering_matches_oracle(wf, subs, order):
+    g = wf.view(fake_tensor(wf, (20, 36), order), *subs)
+    o = L.view(L.make_tensor([20, 36], order=order), *subs)
+    assert g.shape == o.shape
+    np.testing.assert_array_equal(lowered_offsets(g), oracle_offsets(o))
+
+
+def test_view_of_view_and_broadcast(wf):
+    g0, o0 = fake_tensor(wf, (10, 12)), L.make_tensor([10, 12])
+    chain = [([1, 9], [2, 12]), ([1, 5], [0, 6, 2]), (True, [0, 2])]
+    g, o = g0, o0
+    for s in chain:
+        g, o = wf.view(g, *s), L.view(o, *s)
+        assert g.shape == o.shape
+        np.testing.assert_array_equal(lowered_offsets(g), oracle_offsets(o))
+    gb = wf.view(fake_tensor(wf, (7, 1)), True, [":broadcast", 5])
+    ob = L.view(L.make_tensor([7, 1]), True, [":broadcast", 5])
+    assert gb.shape == ob.shape == [7, 5]
+    np.testing.assert_array_equal(lowered_offsets(gb), oracle_offsets(ob))
+    lv = gb.lower()
+    assert lv.stride[1] == 0 and lv.stride[0] == 1
+
+
+@pytest.mark.parametrize("perm", list(itertools.permutations([2, 1, 0])))
+def test_permute_lowering_matches_oracle(wf, perm):
+    g = wf.permute(fake_tensor(wf, (3, 4, 5)), *perm)
+    o = L.permute(L.make_tensor([3, 4, 5]), *perm)
+    assert g.shape == o.shape
+    np.testing.assert_array_equal(lowered_offsets(g), oracle_offsets(o))
+
+
+def test_transpose_flexible_permute(wf):
+    g = wf.transpose(fake_tensor(wf, (2, 3, 4, 5)))
+    o = L.transpose(L.make_tensor([2, 3, 4, 5]))
+    assert g.shape == o.shape == [2, 3, 5, 4]
+    np.testing.assert_array_equal(lowered_offsets(g), oracle_offsets(o))
+    with pytest.raises(ValueError):
+        wf.permute(fake_tensor(wf, (2, 3)), 0, 0)
+
+
+def test_range_algebra_matches_oracle(wf):
+    for f, t, s in itertools.product(range(0, 7), range(0, 7), (-3, -2, -1, 1, 2, 3)):
+        if f == t:
+            continue
+        r = (f, t, s)
+        assert wf.range_size(r) == L.range_size(L.make_range(*r))
+        for i in range(3):
+            assert wf.range_nth(r, i) == L.range_nth(L.make_range(*r), i)
+
+
+def test_strides(wf):
+    assert wf.calc_strides([2, 3, 4], "column") == [12, 4, 1]
+    assert wf.calc_strides([2, 3, 4], "row") == [1, 2, 6]
+
+
+def test_reshape_requires_contiguous(wf):
+    t = fake_tensor(wf, (4, 6))
+    assert wf.reshape_contiguous(t, (3, 8)).shape == [3, 8]
+    assert wf.reshape_contiguous(t, (2, -1)).shape == [2, 12]
+    with pytest.raises(ValueError):
+        wf.reshape_contiguous(wf.view(t, [0, 2], [0, 3]), (6,))
+    with pytest.raises(ValueError):
+        wf.reshape_contiguous(t, (5, 5))
+
+
+# ------------------------------------------------------------------ the C ABI
+def declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "waffe2cuda.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(wf2cu_[a-z0-9_]+)\s*\(", hdr)))
+
+
+def test_library_exports_every_declared_symbol(wf):
+    lib = wf._lib.load()
+    names = declared_symbols()
+    assert len(names) >= 45
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/waffe2cuda.h but not exported"
+    # and every prototype the Python binding uses is declared in the header
+    assert set(wf._lib.PROTOTYPES) | {"wf2cu_last_error"} <= set(names)
+
+
+def test_view_struct_layout_matches_header(wf):
+    V = wf._lib.View
+    assert ctypes.sizeof(V) == 8 + 8 + 4 + 4 + 8 * 8 + 8 * 8
+    assert V.shape.offset == 24 and V.stride.offset == 24 + 64
+
+
+def test_no_cpu_fallback_without_device(wf):
+    """Without a B200 every compute entry point must fail loudly, never compute on the host."""
+    lib = wf._lib.load()
+    n = ctypes.c_int(0)
+    lib.wf2cu_device_count(ctypes.byref(n))
+    if n.value > 0:
+        pytest.skip("a CUDA device is visible; this check is for the CPU-only container")
+    with pytest.raises(wf.Wf2CudaError):
+        wf.init(0)
+    buf = (ctypes.c_float * 16)()
+    v = wf._lib.make_view(ctypes.addressof(buf), 0, [4, 4], [4, 1])
+    assert lib.wf2cu_ew_binary(0, ctypes.byref(v), ctypes.byref(v)) == 4      # WF2CU_ERR_NOT_INITIALISED
+    assert b"no CPU fallback" in lib.wf2cu_last_error()
+    assert lib.wf2cu_gemm(0, 0, 4, 4, 4, buf, 0, 4, buf, 0, 4, buf, 0, 4, 1, 0, 0, 0) == 4
+    assert list(buf) == [0.0] * 16
+
+
+def test_product_does_not_import_oracle():
+    """The oracle is test infrastructure: nothing under cl-waffe2_b200/ may reference it."""
+    pkg = os.path.join(ROOT, "cl-waffe2_b200")
+    for dirpath, _, files in os.walk(pkg):
+        if "_obj" in dirpath:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".lisp")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+                assert "oracle/" not in src and "libwaffe2_port" not in src and "libwaffe2simd_ref" not in src, f
