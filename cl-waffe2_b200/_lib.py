@@ -53,7 +53,7 @@ PROTOTYPES = {
     "wf2cu_gemm": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i64, i64, i64],
     "wf2cu_gemm_set_mode": [i32],
     "wf2cu_sgd_step": [vp, i64, vp, i64, i64, f32],
-    "wf2cu_adam_step": [vp, i64, vp, i64, vp, i64, vp, i64, i64, f32, f32, f32, f32, f32],
+    "wf2cu_adam_step": [vp, i64, vp, i64, vp, i64, vp, i64, i64, f32, vp, f32, f32, f32, f32],
     "wf2cu_embedding_gather": [vp, i64, i64, vp, vp, i64, vp],
     "wf2cu_comm_unique_id": [vp], "wf2cu_comm_init": [i32, i32, vp],
     "wf2cu_allreduce_sum_f32": [vp, i64, i64], "wf2cu_comm_destroy": [],

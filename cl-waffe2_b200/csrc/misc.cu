@@ -97,21 +97,30 @@ __global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const f
     p[i] = __fsub_rn(p[i], __fmul_rn(g[i], lr));
 }
 
-// Adam (`optimizers/impls/adam.lisp:45-67`), operation order as written there:
-//   m <- b1*m + (1-b1)*g ; v <- b2*v + (1-b2)*g^2 ; p <- p - lr_t * m / (sqrt(v) + eps)
+// Adam exactly as the reference composes it (`optimizers/impls/adam.lisp:45-67,96-116`):
+//   Adam-Step-M     : m <- m + (g - m) * (1 - b1)
+//   Adam-Step-V     : v <- v + (1 - b2) * (g*g - v)
+//   Adam-Step-Param : p <- p - (m * lr_t) / (eps + sqrt(v))
+// lr_t = lr * sqrt(1 - b2^n) / (1 - b1^n) is computed on the host (`adam-step-lr`, :81-94); it is
+// read from device memory when lr_dev != NULL so a captured CUDA graph can be replayed with a new
+// value every step.  Three `defmodel-as` composites per parameter (9 memory passes) become one
+// kernel over the whole flat parameter bucket.
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                    float* __restrict__ m, float* __restrict__ v, int64_t n,
-                                                   float lr_t, float b1, float b2, float eps, float gscale) {
+                                                   float lr_t, const float* __restrict__ lr_dev, float b1, float b2,
+                                                   float eps, float gscale) {
+  if (lr_dev) lr_t = *lr_dev;
   const float omb1 = __fsub_rn(1.0f, b1), omb2 = __fsub_rn(1.0f, b2);
   const int64_t stride = (int64_t)gridDim.x * 256;
   for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
     float gi = g[i];
     if (gscale != 1.0f) gi = __fmul_rn(gi, gscale);
-    const float mi = __fadd_rn(__fmul_rn(b1, m[i]), __fmul_rn(omb1, gi));
-    const float vi = __fadd_rn(__fmul_rn(b2, v[i]), __fmul_rn(omb2, __fmul_rn(gi, gi)));
+    const float m0 = m[i], v0 = v[i];
+    const float mi = __fadd_rn(m0, __fmul_rn(__fsub_rn(gi, m0), omb1));
+    const float vi = __fadd_rn(v0, __fmul_rn(omb2, __fsub_rn(__fmul_rn(gi, gi), v0)));
     m[i] = mi; v[i] = vi;
-    const float denom = __fadd_rn(__fsqrt_rn(vi), eps);
-    p[i] = __fsub_rn(p[i], __fdiv_rn(__fmul_rn(lr_t, mi), denom));
+    const float denom = __fadd_rn(eps, __fsqrt_rn(vi));
+    p[i] = __fsub_rn(p[i], __fdiv_rn(__fmul_rn(mi, lr_t), denom));
   }
 }
 
@@ -233,8 +242,8 @@ int wf2cu_sgd_step(void* param, int64_t p_off, const void* grad, int64_t g_off, 
 }
 
 int wf2cu_adam_step(void* param, int64_t p_off, const void* grad, int64_t g_off, void* m, int64_t m_off,
-                    void* v, int64_t v_off, int64_t n, float lr_t, float beta1, float beta2, float eps,
-                    float grad_scale) {
+                    void* v, int64_t v_off, int64_t n, float lr_t, const void* lr_t_dev, float beta1, float beta2,
+                    float eps, float grad_scale) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(param && grad && m && v && n >= 0, "wf2cu_adam_step: bad arguments");
   if (n == 0) return 0;
@@ -242,8 +251,8 @@ int wf2cu_adam_step(void* param, int64_t p_off, const void* grad, int64_t g_off,
   const int64_t cap = (int64_t)S().sm_count * 8;
   if (grid > cap) grid = cap;
   adam_kernel<<<(unsigned)grid, 256, 0, S().stream>>>((float*)param + p_off, (const float*)grad + g_off,
-                                                     (float*)m + m_off, (float*)v + v_off, n, lr_t, beta1, beta2,
-                                                     eps, grad_scale);
+                                                     (float*)m + m_off, (float*)v + v_off, n, lr_t,
+                                                     (const float*)lr_t_dev, beta1, beta2, eps, grad_scale);
   return post_launch("wf2cu_adam_step");
 }
 

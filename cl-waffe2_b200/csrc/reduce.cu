@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(THREADS) reduce_rows_kernel(const __grid_const
       float4 x[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) x[k] = p4[i + k * THREADS];
+      asm volatile("" ::: "memory");
 #pragma unroll
       for (int k = 0; k < 8; k += 4) {
         acc0 = M::op(acc0, M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w)));
@@ -235,10 +236,17 @@ __global__ void __launch_bounds__(256) reduce_rows_tile_kernel(const __grid_cons
     const int64_t i = t + (int64_t)k * TPR;
     x[k] = (live && i < v1) ? p4[i] : make_float4(M::id(), M::id(), M::id(), M::id());
   }
-  float acc[8];
+  asm volatile("" ::: "memory");   // keep all 8 loads ahead of the first add (ptxas otherwise serialises them)
+  // first level pairs load k with load k+4, so no add can issue before all 8 loads are out
+  // (ptxas otherwise splits them into two batches of 4 to stay at 32 registers)
+  float4 h[4];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) acc[k] = M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w));
-  float v = M::op(M::op(M::op(acc[0], acc[1]), M::op(acc[2], acc[3])), M::op(M::op(acc[4], acc[5]), M::op(acc[6], acc[7])));
+  for (int k = 0; k < 4; ++k)
+    h[k] = make_float4(M::op(x[k].x, x[k + 4].x), M::op(x[k].y, x[k + 4].y), M::op(x[k].z, x[k + 4].z), M::op(x[k].w, x[k + 4].w));
+  float acc[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) acc[k] = M::op(M::op(h[k].x, h[k].y), M::op(h[k].z, h[k].w));
+  float v = M::op(M::op(acc[0], acc[1]), M::op(acc[2], acc[3]));
   if (live) {
     const float* p = a.src + so;
     for (int64_t c = (v1 << 2) + t; c < a.cols; c += TPR) v = M::op(v, p[c]);
@@ -296,6 +304,7 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
         const float4 y = *reinterpret_cast<const float4*>(base + (r + 8) * a.sR_src + col);
         const float4 z = *reinterpret_cast<const float4*>(base + (r + 16) * a.sR_src + col);
         const float4 w = *reinterpret_cast<const float4*>(base + (r + 24) * a.sR_src + col);
+        asm volatile("" ::: "memory");
         acc.x = M::op(acc.x, x.x); acc.y = M::op(acc.y, x.y); acc.z = M::op(acc.z, x.z); acc.w = M::op(acc.w, x.w);
         acc2.x = M::op(acc2.x, y.x); acc2.y = M::op(acc2.y, y.y); acc2.z = M::op(acc2.z, y.z); acc2.w = M::op(acc2.w, y.w);
         acc3.x = M::op(acc3.x, z.x); acc3.y = M::op(acc3.y, z.y); acc3.z = M::op(acc3.z, z.z); acc3.w = M::op(acc3.w, z.w);

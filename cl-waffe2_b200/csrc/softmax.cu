@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(THREADS) softmax_row_block_kernel(const __grid
     const int64_t i = threadIdx.x + (int64_t)k * THREADS;
     v[k] = (i < n4) ? xp[i] : make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  asm volatile("" ::: "memory");   // all row loads in flight before the first use
   if (a.avoid_overflow) {
     float s = 0.f;
 #pragma unroll

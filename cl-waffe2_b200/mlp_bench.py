@@ -1,0 +1,110 @@
+"""MLP training-step benchmark (BASELINE.json config 4: MNIST MLP 784-256-256-10, softmax-cross-entropy,
+Adam, batch 1024 synthetic inputs, batch-sharded over 1/2/4/8 B200 with a NCCL gradient allreduce).
+Called from bench.py; returns a dict for the `mlp` key of the JSON line."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, nn
+
+DIMS = [784, 256, 256, 10]
+
+
+def _comm_init(dist, rank: int, world: int):
+    """One NCCL communicator per process (one process per GPU); the 128-byte id travels over the
+    torch.distributed plumbing."""
+    import torch
+    lib = _lib.load()
+    buf = (C.c_ubyte * 128)()
+    if rank == 0:
+        _lib.check(lib.wf2cu_comm_unique_id(buf))
+    t = torch.tensor(list(buf), dtype=torch.uint8, device="cuda")
+    dist.broadcast(t, src=0)
+    ids = bytes(t.cpu().tolist())
+    _lib.check(lib.wf2cu_comm_init(rank, world, C.create_string_buffer(ids, 128)))
+
+
+def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
+    lib = _lib.load()
+    chk = _lib.check
+    rng = np.random.default_rng(seed + 17 * rank)          # each rank owns a different shard
+    X = rng.uniform(0, 1, size=(per_gpu_batch, DIMS[0])).astype(np.float32)
+    Y = np.eye(DIMS[-1], dtype=np.float32)[rng.integers(DIMS[-1], size=per_gpu_batch)]
+    model = nn.MLPSequence(DIMS, "relu", seed=1234)        # same seed everywhere: replicas start identical
+    step = nn.CompiledStep(model, "softmax-cross-entropy-sum", nn.Adam(model.arena, lr=1e-3), X.shape, Y.shape, world=world)
+    step.set_inputs(X, Y)
+
+    def barrier():
+        chk(lib.wf2cu_sync())
+        if dist is not None:
+            dist.barrier()
+
+    def max_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(warmup, 3)):
+        step.step()
+    first_loss = None
+    barrier()
+    l0 = C.c_int64(); l1 = C.c_int64()
+    chk(lib.wf2cu_launch_count(C.byref(l0)))
+    chk(lib.wf2cu_timer_start())
+    for _ in range(steps):
+        step.step()
+    ms = C.c_float()
+    chk(lib.wf2cu_timer_stop(C.byref(ms)))
+    chk(lib.wf2cu_launch_count(C.byref(l1)))
+    barrier()
+    dev_ms = max_ranks(ms.value) / steps
+    loss_after = step.loss_value()
+
+    # e2e: the batch comes from pinned host memory every step and the loss goes back to the host
+    hx = C.c_void_p(); hy = C.c_void_p()
+    chk(lib.wf2cu_host_alloc(X.nbytes, C.byref(hx))); chk(lib.wf2cu_host_alloc(Y.nbytes, C.byref(hy)))
+    C.memmove(hx.value, X.ctypes.data, X.nbytes); C.memmove(hy.value, Y.ctypes.data, Y.nbytes)
+    out = C.c_float()
+
+    def e2e_step():
+        chk(lib.wf2cu_h2d(step.x.vec.ptr, 0, hx, X.nbytes))
+        chk(lib.wf2cu_h2d(step.y.vec.ptr, 0, hy, Y.nbytes))
+        step.step()
+        chk(lib.wf2cu_get_f32(step.loss.vec.ptr, step.loss.lower().offset, C.byref(out)))
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    chk(lib.wf2cu_timer_start())
+    for _ in range(steps):
+        e2e_step()
+    chk(lib.wf2cu_timer_stop(C.byref(ms)))
+    barrier()
+    e2e_ms = max_ranks(ms.value) / steps
+    chk(lib.wf2cu_host_free(hx)); chk(lib.wf2cu_host_free(hy))
+    gb = per_gpu_batch * world
+    return {"per_gpu_batch": per_gpu_batch, "global_batch": gb, "ms_per_step": dev_ms,
+            "samples_per_s": gb / (dev_ms * 1e-3), "e2e_ms_per_step": e2e_ms, "e2e_samples_per_s": gb / (e2e_ms * 1e-3),
+            "h2d_bytes_per_step": int(X.nbytes + Y.nbytes), "d2h_bytes_per_step": 4,
+            "launches_per_step": (l1.value - l0.value) / steps, "loss_after": loss_after,
+            "pool_bytes": step.pool.nbytes()}
+
+
+def run(wf, dist, rank: int, world: int, steps: int = 200, warmup: int = 20) -> dict:
+    if world > 1:
+        _comm_init(dist, rank, world)
+    res = {"model": "MNIST MLP 784-256-256-10, relu, softmax-cross-entropy (!sum), Adam lr 1e-3, fp32",
+           "data": "synthetic U(0,1) inputs, one-hot labels", "n_gpus": world,
+           "collective": "one NCCL allreduce(sum) of the 269,322-float gradient bucket per step, inside the CUDA graph"
+           if world > 1 else None}
+    res["weak"] = _run_one(dist, rank, world, 1024, steps, warmup)                 # 1024 per GPU
+    if world > 1 and 1024 % world == 0:
+        res["strong"] = _run_one(dist, rank, world, 1024 // world, steps, warmup)  # 1024 global
+    if world > 1:
+        _lib.check(_lib.load().wf2cu_comm_destroy())
+    return res

@@ -1,0 +1,421 @@
+"""Training-step layer: reverse-mode nodes, `LinearLayer`, losses, optimizers and the compiled
+(CUDA-graph) step for the MLP configs (C1 `examples/mlp_sin_wave.lisp`, C4 `examples/mnist/mlp.lisp`).
+
+This mirrors what runs *unchanged* on top of the backend in the reference — `cl-waffe2/nn`
+(`/root/reference/source/nn/regression.lisp:14-55`, `activation.lisp:11-43`, `criterion.lisp:53-188`) and
+`cl-waffe2/optimizers` (`optimizers/impls/{sgd,adam}.lisp`) — restated in Python over the C ABI so the
+step can be driven and measured here.  Backward formulas are the nodes' own
+(`base-impl/arithmetic.lisp:57-103`, `matrix-ops.lisp:6-95`, `criterion.lisp:81-106`).
+
+B200-first choices (SURVEY §7 hard parts e, f; §8e, §8f-1/2):
+  * parameters and gradients live in ONE arena each, so Adam/SGD is one kernel over the bucket and
+    the data-parallel gradient allreduce is one NCCL call;
+  * every temporary comes from a StaticPool (the VMAllocation analogue), so forward + backward +
+    allreduce + optimizer is a fixed launch sequence, captured once into a CUDA graph;
+  * host scalars that change per step (Adam's lr_t) are read from device memory by the kernel.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Callable, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib, ops
+from .tensor import CUDATensor, StaticPool, Storage, make_tensor, tensor_at, view
+
+_P = _lib
+
+
+# ------------------------------------------------------------------------------- tape
+class Tape:
+    """Reverse-mode record of one forward pass (`forward->reverse-mode`, vm/compile.lisp:110-158)."""
+
+    def __init__(self):
+        self.nodes: List[Callable[[], None]] = []
+        self.touched: List[CUDATensor] = []
+
+    def reset(self):
+        for t in self.touched:
+            t._has_grad = False
+        self.nodes.clear()
+        self.touched.clear()
+
+
+_tape: Optional[Tape] = None
+
+
+def _tracked(t: CUDATensor) -> bool:
+    return bool(getattr(t, "requires_grad", False) or getattr(t, "_track", False))
+
+
+def _mark(out: CUDATensor, *inputs: CUDATensor) -> bool:
+    track = _tape is not None and any(_tracked(i) for i in inputs)
+    out._track = track
+    return track
+
+
+def _accumulate(t: CUDATensor, compute: Callable[[CUDATensor, bool], None]) -> None:
+    """Gradient adder (`vm/utils.lisp:109-142`): the first contribution is written (Move), later
+    ones are added."""
+    if not _tracked(t):
+        return
+    if t.grad is None:
+        t.grad = make_tensor(t.shape)
+    compute(t.grad, bool(getattr(t, "_has_grad", False)))
+    t._has_grad = True
+    _tape.touched.append(t)
+
+
+# ------------------------------------------------------------------------------- nodes
+def linear(x: CUDATensor, weight: CUDATensor, bias: Optional[CUDATensor]) -> CUDATensor:
+    """`step-linear` (nn/regression.lisp:14-18): y = x @ W^T + b, W is (out in)."""
+    out = ops.matmul(x, ops.t(weight))
+    if bias is not None:
+        ops.add_(out, view(_as_row(bias), [":broadcast", out.shape[0]], True))
+    if _mark(out, x, weight, *([bias] if bias is not None else [])):
+        def bw():
+            dout = out.grad
+            # MatMulNode backward: dA = dout . B^T, dB = A^T . dout with B = (!t W)
+            _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight))
+            _accumulate(weight, lambda g, acc: _gemm_into(g, acc, ops.t(dout), x))
+            if bias is not None:
+                # the (!flexible bias) broadcast view accumulates dout over the batch axis
+                def bias_grad(g, acc):
+                    gb = view(_as_row(g), [":broadcast", dout.shape[0]], True)
+                    _lib.check(_lib.load().wf2cu_reduce_sum(C.byref(dout.lower()), C.byref(gb.lower()), 1 if acc else 0, 0.0))
+                _accumulate(bias, bias_grad)
+        _tape.nodes.append(bw)
+    return out
+
+
+def _as_row(b: CUDATensor) -> CUDATensor:
+    """(out) -> (1 out) without moving data (`!flexible` + rank-up, base-impl/fundamental.lisp)."""
+    if b.dims() == 2:
+        return b
+    t = tensor_at(b.vec, b.lower().offset, [1, b.shape[0]])
+    return t
+
+
+def _gemm_into(g: CUDATensor, acc: bool, a, b) -> None:
+    if not acc:
+        ops.matmul(a, b, out=g)
+    else:
+        ops.add_(g, ops.matmul(a, b))
+
+
+def relu(x: CUDATensor) -> CUDATensor:
+    """`!relu` = x * (x > 0) (nn/activation.lisp:11-26); backward of the MulNode: dx = dout * mask."""
+    out = ops.relu(x)
+    if _mark(out, x):
+        def bw():
+            def f(g, acc):
+                prog = [(_P.P_LOAD, 0, 0, 0), (_P.P_IMM, 1, 0, ops._imm(0.0)), (_P.P_CMPSEL | (_P.CMP["gt"] << 8), 1, 0, 1),
+                        (_P.P_LOAD, 2, 1, 0), (_P.P_MUL, 1, 2, 1)]
+                if acc:
+                    prog += [(_P.P_LOAD, 3, 2, 0), (_P.P_ADD, 1, 3, 1)]
+                prog += [(_P.P_STORE, 1, 2, 0)]
+                ops.fused(prog, [x, out.grad, g])
+            _accumulate(x, f)
+        _tape.nodes.append(bw)
+    return out
+
+
+def sigmoid(x: CUDATensor) -> CUDATensor:
+    """`!sigmoid` (nn/activation.lisp:43); backward folded to dout * s * (1 - s)."""
+    out = ops.sigmoid(x)
+    if _mark(out, x):
+        def bw():
+            def f(g, acc):
+                prog = [(_P.P_LOAD, 0, 0, 0), (_P.P_IMM, 1, 0, ops._imm(1.0)), (_P.P_SUB, 1, 1, 0), (_P.P_MUL, 1, 0, 1),
+                        (_P.P_LOAD, 2, 1, 0), (_P.P_MUL, 1, 2, 1)]
+                if acc:
+                    prog += [(_P.P_LOAD, 3, 2, 0), (_P.P_ADD, 1, 3, 1)]
+                prog += [(_P.P_STORE, 1, 2, 0)]
+                ops.fused(prog, [out, out.grad, g])
+            _accumulate(x, f)
+        _tape.nodes.append(bw)
+    return out
+
+
+def softmax_cross_entropy(x: CUDATensor, labels: CUDATensor, delta: float = 1e-7) -> CUDATensor:
+    """`softmax-cross-entropy` (nn/criterion.lisp:164-188, Softmax-Cross-Entropy-Node :89-117):
+    z = softmax(x, avoid-overflow nil); out = -1 * (labels * log(z + delta)).
+    Backward (`sce-diff-static`, :81-87): dx = (dy * (z - labels)) / batch-size."""
+    z = ops.softmax(x, avoid_overflow=False, axis=1)
+    out = make_tensor(x.shape)
+    prog = [(_P.P_LOAD, 0, 0, 0), (_P.P_IMM, 1, 0, ops._imm(delta)), (_P.P_ADD, 0, 0, 1),
+            (_P.P_UNARY, 0, 0, _P.UNARY["loge"]), (_P.P_LOAD, 2, 1, 0), (_P.P_MUL, 0, 2, 0),
+            (_P.P_IMM, 1, 0, ops._imm(-1.0)), (_P.P_MUL, 0, 1, 0), (_P.P_STORE, 0, 2, 0)]
+    ops.fused(prog, [z, labels, out])
+    if _mark(out, x):
+        batch = float(x.shape[-2])
+
+        def bw():
+            def f(g, acc):
+                p = [(_P.P_LOAD, 0, 0, 0), (_P.P_LOAD, 1, 1, 0), (_P.P_SUB, 0, 0, 1), (_P.P_LOAD, 2, 2, 0),
+                     (_P.P_MUL, 0, 2, 0), (_P.P_IMM, 1, 0, ops._imm(batch)), (_P.P_DIV, 0, 0, 1)]
+                if acc:
+                    p += [(_P.P_LOAD, 3, 3, 0), (_P.P_ADD, 0, 3, 0)]
+                p += [(_P.P_STORE, 0, 3, 0)]
+                ops.fused(p, [z, labels, out.grad, g])
+            _accumulate(x, f)
+        _tape.nodes.append(bw)
+    return out
+
+
+def reduce_sum(x: CUDATensor, mean: bool = False) -> CUDATensor:
+    """`(!sum x)` / `(!mean x)` to a (1 .. 1) tensor; backward broadcasts dout (and divides by the
+    count for mean: the `!div` node's dx = dout / n)."""
+    out = ops.mean(x) if mean else ops.sum(x)
+    if _mark(out, x):
+        n = float(x.numel())
+
+        def bw():
+            gb = view(out.grad, *[[":broadcast", s] for s in x.shape])
+
+            def f(g, acc):
+                if mean:
+                    tmp = ops.div(gb, n)
+                    if acc:
+                        ops.add_(g, tmp)
+                    else:
+                        ops.move_(g, tmp)
+                elif acc:
+                    ops.add_(g, gb)
+                else:
+                    ops.move_(g, gb)
+            _accumulate(x, f)
+        _tape.nodes.append(bw)
+    return out
+
+
+def mse(x: CUDATensor, y: CUDATensor, reduction: str = "mean") -> CUDATensor:
+    """`mse` (nn/criterion.lisp:53-79): l = x - y; reduction(l * l).  Backward: MulNode gives
+    (dout*l) to both operands (the same tensor l), SubNode gives (dl, -dl)."""
+    l = ops.sub(x, y)
+    sq = ops.mul(l, l)
+    tracked = _mark(sq, x, y)
+    if tracked:
+        def bw():
+            d = sq.grad
+
+            def fx(g, acc):
+                prog = [(_P.P_LOAD, 0, 0, 0), (_P.P_LOAD, 1, 1, 0), (_P.P_MUL, 0, 1, 0), (_P.P_ADD, 0, 0, 0)]
+                if acc:
+                    prog += [(_P.P_LOAD, 2, 2, 0), (_P.P_ADD, 0, 2, 0)]
+                prog += [(_P.P_STORE, 0, 2, 0)]
+                ops.fused(prog, [l, d, g])
+
+            def fy(g, acc):
+                prog = [(_P.P_LOAD, 0, 0, 0), (_P.P_LOAD, 1, 1, 0), (_P.P_MUL, 0, 1, 0), (_P.P_ADD, 0, 0, 0),
+                        (_P.P_UNARY, 0, 0, _P.UNARY["neg"])]
+                if acc:
+                    prog += [(_P.P_LOAD, 2, 2, 0), (_P.P_ADD, 0, 2, 0)]
+                prog += [(_P.P_STORE, 0, 2, 0)]
+                ops.fused(prog, [l, d, g])
+            _accumulate(x, fx)
+            _accumulate(y, fy)
+        _tape.nodes.append(bw)
+    if reduction == "mean":
+        return reduce_sum(sq, mean=True)
+    if reduction == "sum":
+        return reduce_sum(sq)
+    return sq
+
+
+# ------------------------------------------------------------------------------- parameters
+class ParameterArena:
+    """All parameters in one storage, all gradients in another (the allocator hook that
+    makes a single gradient bucket possible)."""
+
+    def __init__(self, shapes: Sequence[Sequence[int]]):
+        sizes = [int(np.prod(s)) for s in shapes]
+        self.offsets = [0]
+        for n in sizes:
+            # keep every tensor 16-byte aligned inside the bucket
+            self.offsets.append(self.offsets[-1] + ((n + 3) & ~3))
+        self.total = self.offsets[-1]
+        _lib.init(_lib._inited_device if _lib._inited_device is not None else 0)
+        self.param_store = Storage(self.total * 4)
+        self.grad_store = Storage(self.total * 4)
+        self.params: List[CUDATensor] = []
+        for shp, off in zip(shapes, self.offsets):
+            p = tensor_at(self.param_store, off, shp, requires_grad=True)
+            p.grad = tensor_at(self.grad_store, off, shp)
+            self.params.append(p)
+
+
+def xavier_uniform(rng: np.random.Generator, out_f: int, in_f: int) -> np.ndarray:
+    """`xavier-uniform` (distributions/weights.lisp): U(-a, a), a = sqrt(6 / (in + out)).  Sampled on the
+    host with a seeded numpy RNG (SBCL's RNG is not reproducible outside SBCL) and uploaded in bulk."""
+    a = math.sqrt(6.0 / (in_f + out_f))
+    return rng.uniform(-a, a, size=(out_f, in_f)).astype(np.float32)
+
+
+def bias_uniform(rng: np.random.Generator, out_f: int) -> np.ndarray:
+    """U(-k, k), k = sqrt(1 / out-features) (nn/regression.lisp:51-55)."""
+    k = math.sqrt(1.0 / out_f)
+    return rng.uniform(-k, k, size=(out_f,)).astype(np.float32)
+
+
+def mlp_init_arrays(dims: Sequence[int], seed: int = 0):
+    """Host arrays [(W, b), ...] for an MLP with layer widths `dims`."""
+    rng = np.random.default_rng(seed)
+    return [(xavier_uniform(rng, dims[i + 1], dims[i]), bias_uniform(rng, dims[i + 1])) for i in range(len(dims) - 1)]
+
+
+class MLPSequence:
+    """`MLP-Sequence` (examples/mnist/mlp.lisp:12-19) / the sin-wave MLP (examples/mlp_sin_wave.lisp:41-52):
+    LinearLayer -> activation -> ... -> LinearLayer."""
+
+    def __init__(self, dims: Sequence[int], activation: str = "relu", init=None, seed: int = 0):
+        self.dims = list(dims)
+        self.activation = {"relu": relu, "sigmoid": sigmoid}[activation]
+        init = init if init is not None else mlp_init_arrays(dims, seed)
+        shapes = []
+        for i in range(len(dims) - 1):
+            shapes += [(dims[i + 1], dims[i]), (dims[i + 1],)]
+        self.arena = ParameterArena(shapes)
+        for i, (w, b) in enumerate(init):
+            self.arena.params[2 * i].copy_from_numpy(w)
+            self.arena.params[2 * i + 1].copy_from_numpy(b)
+
+    def parameters(self) -> List[CUDATensor]:
+        return self.arena.params
+
+    def __call__(self, x: CUDATensor) -> CUDATensor:
+        p = self.arena.params
+        n = len(self.dims) - 1
+        for i in range(n):
+            x = linear(x, p[2 * i], p[2 * i + 1])
+            if i != n - 1:
+                x = self.activation(x)
+        return x
+
+
+# ------------------------------------------------------------------------------- optimizers
+class SGD:
+    """`SGD` (optimizers/impls/sgd.lisp:4-35) over the whole bucket."""
+
+    def __init__(self, arena: ParameterArena, lr: float = 1e-3):
+        self.arena, self.lr = arena, float(lr)
+
+    def pre_step(self):
+        pass
+
+    def step(self, grad_scale: float = 1.0):
+        a = self.arena
+        lib = _lib.load()
+        if grad_scale != 1.0:
+            g = tensor_at(a.grad_store, 0, [a.total])
+            ops.mul_(g, grad_scale)
+        _lib.check(lib.wf2cu_sgd_step(a.param_store.ptr, 0, a.grad_store.ptr, 0, a.total, self.lr))
+
+
+class Adam:
+    """`Adam` (optimizers/impls/adam.lisp:5-116) over the whole bucket; lr_t lives in device memory."""
+
+    def __init__(self, arena: ParameterArena, lr=1e-3, eps=1e-7, beta1=0.9, beta2=0.999):
+        self.arena = arena
+        self.lr, self.eps, self.b1, self.b2 = (float(np.float32(v)) for v in (lr, eps, beta1, beta2))
+        self.n = 0
+        self.m = Storage(arena.total * 4)
+        self.v = Storage(arena.total * 4)
+        self.lr_t = Storage(4)
+
+    def lr_at(self, n: int) -> float:
+        """`adam-step-lr` (adam.lisp:81-94) in single precision."""
+        f = np.float32
+        b1n, b2n = f(self.b1) ** f(n), f(self.b2) ** f(n)
+        return float(f(self.lr) * (np.sqrt(f(1.0) - f(b2n)) / (f(1.0) - f(b1n))))
+
+    def pre_step(self):
+        """Host part of a step: bump N and publish lr_t (4-byte H2D; outside the captured graph)."""
+        self.n += 1
+        _lib.check(_lib.load().wf2cu_set_f32(self.lr_t.ptr, 0, self.lr_at(self.n)))
+
+    def step(self, grad_scale: float = 1.0):
+        a = self.arena
+        _lib.check(_lib.load().wf2cu_adam_step(a.param_store.ptr, 0, a.grad_store.ptr, 0, self.m.ptr, 0, self.v.ptr, 0,
+                                               a.total, 0.0, self.lr_t.ptr, self.b1, self.b2, self.eps, grad_scale))
+
+
+# ------------------------------------------------------------------------------- compiled step
+class CompiledStep:
+    """`build` + `forward`/`backward`/`call-optimizer!` of the reference
+    (vm/generic-tensor/acceptor.lisp:307-508) for one (model, loss, optimizer) triple with static input
+    shapes: the launch sequence is traced once under a StaticPool and replayed as a CUDA graph.
+
+    world > 1: batch-sharded data parallelism — every rank runs the same graph on its shard; the
+    gradient bucket is summed with one NCCL allreduce inside the graph and scaled by 1/world in the
+    optimizer kernel."""
+
+    def __init__(self, model: MLPSequence, loss: str, optimizer, x_shape, y_shape, world: int = 1, use_graph: bool = True):
+        self.model, self.loss_kind, self.opt, self.world = model, loss, optimizer, int(world)
+        self.x = make_tensor(x_shape)
+        self.y = make_tensor(y_shape)
+        self.pool = StaticPool()
+        self.tape = Tape()
+        self.loss: Optional[CUDATensor] = None
+        self.graph = None
+        self.use_graph = use_graph
+        self._runs = 0
+
+    def _loss(self, out: CUDATensor) -> CUDATensor:
+        if self.loss_kind == "softmax-cross-entropy-sum":      # examples/mnist/mlp.lisp:24-28
+            return reduce_sum(softmax_cross_entropy(out, self.y))
+        if self.loss_kind == "mse-mean":                       # examples/mlp_sin_wave.lisp
+            return mse(out, self.y, reduction="mean")
+        raise ValueError(self.loss_kind)
+
+    def _trace(self):
+        """forward, backward, [allreduce], optimizer: all launches of one step."""
+        global _tape
+        lib = _lib.load()
+        self.tape.reset()
+        _tape = self.tape
+        try:
+            with self.pool:
+                loss = self._loss(self.model(self.x))
+                loss.grad = make_tensor(loss.shape)
+                ops.fill_(loss.grad, 1.0)
+                loss._has_grad = True
+                for node in reversed(self.tape.nodes):
+                    node()
+                if self.world > 1:
+                    a = self.model.arena
+                    _lib.check(lib.wf2cu_allreduce_sum_f32(a.grad_store.ptr, 0, a.total))
+                self.opt.step(1.0 / self.world if self.world > 1 else 1.0)
+        finally:
+            _tape = None
+        self.loss = loss
+
+    def set_inputs(self, x: np.ndarray, y: np.ndarray):
+        self.x.copy_from_numpy(x)
+        self.y.copy_from_numpy(y)
+
+    def step(self):
+        """One training step on the inputs currently in self.x / self.y (asynchronous)."""
+        lib = _lib.load()
+        self.opt.pre_step()
+        if not self.use_graph or self._runs == 0:
+            self._trace()                       # first run allocates the static plan
+        else:
+            if self.graph is None:
+                self.pool.frozen = True
+                ex = C.c_void_p()
+                _lib.check(lib.wf2cu_graph_begin())
+                try:
+                    self._trace()
+                finally:
+                    rc = lib.wf2cu_graph_end(C.byref(ex))
+                _lib.check(rc)
+                self.graph = ex
+            _lib.check(lib.wf2cu_graph_launch(self.graph))
+        self._runs += 1
+
+    def loss_value(self) -> float:
+        """`->scal` of the loss: one 4-byte D2H, the only sync of a step."""
+        return self.loss.vref(self.loss.lower().offset)

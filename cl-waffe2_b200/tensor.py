@@ -274,12 +274,59 @@ class CUDATensor:
         a = np.asarray(arr, dtype=np.float32).reshape(self.orig_shape)
         flat = a.reshape(-1) if self.order == "column" else a.reshape(-1, order="F")
         flat = np.ascontiguousarray(flat)
-        _lib.check(_lib.load().wf2cu_h2d(self.vec.ptr, 0, flat.ctypes.data, flat.nbytes))
+        _lib.check(_lib.load().wf2cu_h2d(self.vec.ptr, self.initial_offset * 4, flat.ctypes.data, flat.nbytes))
         _lib.check(_lib.load().wf2cu_sync())  # `flat` may be a temporary
         return self
 
     def __repr__(self):
         return f"<CUDATensor {self.shape} order={self.order} permute={self.permute_order}>"
+
+
+# --------------------------------------------------------------------------- static allocation
+class StaticPool:
+    """Static memory plan of a compiled step — the analogue of `VMAllocation` /
+    `with-static-allocation` (`source/vm/allocation.lisp:46-171`): the first run under the pool
+    allocates, every later run hands out the same buffers in the same order, so the launch
+    sequence has fixed addresses and can be captured into a CUDA graph.  Like the reference's
+    pool, reused buffers are NOT re-zeroed; every producer overwrites its output."""
+
+    def __init__(self):
+        self.slots = []      # [(nbytes, Storage)]
+        self.cursor = 0
+        self.frozen = False
+
+    def take(self, nbytes: int) -> Storage:
+        if self.cursor < len(self.slots):
+            nb, st = self.slots[self.cursor]
+            if nb != nbytes:
+                raise RuntimeError(f"StaticPool: allocation #{self.cursor} changed size ({nb} -> {nbytes}); "
+                                   "the compiled step is not static")
+            self.cursor += 1
+            return st
+        if self.frozen:
+            raise RuntimeError("StaticPool: new allocation after the plan was frozen (inside graph capture)")
+        st = Storage(nbytes)
+        self.slots.append((nbytes, st))
+        self.cursor += 1
+        return st
+
+    def __enter__(self):
+        global _active_pool
+        self._prev = _active_pool
+        _active_pool = self
+        self.cursor = 0
+        return self
+
+    def __exit__(self, *exc):
+        global _active_pool
+        _active_pool = self._prev
+        return False
+
+    def nbytes(self) -> int:
+        return sum(nb for nb, _ in self.slots)
+
+
+_active_pool = None
 
 
 # --------------------------------------------------------------------------- constructors
@@ -290,7 +337,10 @@ def make_tensor(shape, data=None, order="column", requires_grad=False, initial_e
     n = 1
     for s in shape:
         n *= s
-    t = CUDATensor(Storage(max(n, 1) * 4), shape, order=order, requires_grad=requires_grad)
+    nbytes = max(n, 1) * 4
+    st = _active_pool.take(nbytes) if (_active_pool is not None and data is None and initial_element is None) \
+        else Storage(nbytes)
+    t = CUDATensor(st, shape, order=order, requires_grad=requires_grad)
     if data is not None:
         t.copy_from_numpy(data)
     elif initial_element not in (None, 0, 0.0):
@@ -374,3 +424,11 @@ def reshape_contiguous(t: CUDATensor, shape) -> CUDATensor:
     out = CUDATensor(t.vec, shape, order="column")
     out.initial_offset = t.lower().offset
     return out
+
+
+def tensor_at(storage: Storage, offset: int, shape, requires_grad=False) -> CUDATensor:
+    """A contiguous tensor living at element `offset` of an existing storage (how parameters and
+    gradients are laid out in one arena so the optimizer and the allreduce see ONE bucket)."""
+    t = CUDATensor(storage, [int(s) for s in shape], order="column", requires_grad=requires_grad)
+    t.initial_offset = int(offset)
+    return t

@@ -187,12 +187,14 @@ int  wf2cu_gemm_set_mode(int mode);
 /* ===================== optimizers (fused chains of `optimizers/impls/*.lisp`) ===================== */
 /* p <- p - lr * g        (`sgd.lisp:20-26`) */
 int  wf2cu_sgd_step(void* param, int64_t p_off, const void* grad, int64_t g_off, int64_t n, float lr);
-/* Adam as written in `adam.lisp:45-116`:  m <- b1 m + (1-b1) g ; v <- b2 v + (1-b2) g^2 ;
- * p <- p - lr_t * m / (sqrt(v) + eps), lr_t computed by the host.  grad_scale pre-multiplies g
- * (1/world for the data-parallel mean). */
+/* Adam as written in `adam.lisp:45-116`:  m <- m + (g - m)(1 - b1) ; v <- v + (1 - b2)(g^2 - v) ;
+ * p <- p - (m * lr_t) / (eps + sqrt(v)), lr_t computed by the host (`adam-step-lr`).  When
+ * lr_t_dev != NULL the kernel reads lr_t from that device float instead (so a captured CUDA graph
+ * can be replayed with a fresh value).  grad_scale pre-multiplies g (1/world for the data-parallel
+ * mean). */
 int  wf2cu_adam_step(void* param, int64_t p_off, const void* grad, int64_t g_off,
                      void* m, int64_t m_off, void* v, int64_t v_off, int64_t n,
-                     float lr_t, float beta1, float beta2, float eps, float grad_scale);
+                     float lr_t, const void* lr_t_dev, float beta1, float beta2, float eps, float grad_scale);
 
 /* `GPT2PositionalEmbedding` (`examples/gpt-2/utils.lisp:19-112`):
  * out[b,p,:] = wte[round(ctx[b,p]),:] + wpe[p,:] ; token ids are floats. */

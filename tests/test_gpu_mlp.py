@@ -1,0 +1,84 @@
+"""GPU parity of the MLP training step (configs C1 and C4): the compiled CUDA-graph step
+against the oracle's node-by-node restatement on the same host-generated weights and data.
+Tolerance: per-step loss within 1e-4 relative (the GEMM bar) over the compared steps."""
+import importlib
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _nn(gpu):
+    return importlib.import_module("cl-waffe2_b200.nn")
+
+
+def test_c1_sin_wave_sgd_matches_oracle(gpu):
+    # examples/mlp_sin_wave.lisp:41-78 — 100 -> 10 -> 1, sigmoid, MSE(mean), SGD lr 1e-3, batch 100
+    nn = _nn(gpu)
+    from oracle.mlp import OracleMLP
+    i = np.arange(100 * 100, dtype=np.float32)
+    X = np.sin(np.float32(0.01) * i + np.float32(0.1)).reshape(100, 100).astype(np.float32)
+    Y = np.cos(np.float32(0.01) * np.arange(100, dtype=np.float32) + np.float32(0.1)).reshape(100, 1).astype(np.float32)
+    init = nn.mlp_init_arrays([100, 10, 1], seed=1)
+    model = nn.MLPSequence([100, 10, 1], "sigmoid", init=init)
+    step = nn.CompiledStep(model, "mse-mean", nn.SGD(model.arena, lr=1e-3), X.shape, Y.shape)
+    step.set_inputs(X, Y)
+    ref = OracleMLP([100, 10, 1], "sigmoid", init, "mse-mean", opt="sgd", lr=1e-3)
+    ours, theirs = [], []
+    for _ in range(30):
+        step.step()
+        ours.append(step.loss_value())
+        theirs.append(ref.step(X, Y))
+    np.testing.assert_allclose(ours, theirs, rtol=1e-4)
+    assert ours[-1] < ours[0]                     # nn/t/regression.lisp:429-454: loss decreases
+    assert step.graph is not None                 # replayed as a CUDA graph from the 2nd step on
+    for p, q in zip(model.parameters(), [ref.W[0], ref.b[0], ref.W[1], ref.b[1]]):
+        np.testing.assert_allclose(p.to_numpy().ravel(), q.vec, rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("use_graph", [True, False])
+def test_c4_mnist_mlp_adam_matches_oracle(gpu, use_graph):
+    # examples/mnist/mlp.lisp:12-36 — 784-256-256-10, relu, softmax-cross-entropy (!sum), Adam lr 1e-3
+    nn = _nn(gpu)
+    from oracle.mlp import OracleMLP
+    rng = np.random.default_rng(0)
+    B = 64
+    X = rng.uniform(0, 1, size=(B, 784)).astype(np.float32)
+    Y = np.eye(10, dtype=np.float32)[rng.integers(10, size=B)]
+    dims = [784, 256, 256, 10]
+    init = nn.mlp_init_arrays(dims, seed=2)
+    model = nn.MLPSequence(dims, "relu", init=init)
+    step = nn.CompiledStep(model, "softmax-cross-entropy-sum", nn.Adam(model.arena, lr=1e-3), X.shape, Y.shape,
+                           use_graph=use_graph)
+    step.set_inputs(X, Y)
+    ref = OracleMLP(dims, "relu", init, "softmax-cross-entropy-sum", opt="adam", lr=1e-3)
+    ours, theirs = [], []
+    for _ in range(12):
+        step.step()
+        ours.append(step.loss_value())
+        theirs.append(ref.step(X, Y))
+    np.testing.assert_allclose(ours, theirs, rtol=1e-4)
+    assert ours[-1] < 0.7 * ours[0]
+
+
+def test_gradients_match_oracle(gpu):
+    nn = _nn(gpu)
+    from oracle.mlp import OracleMLP
+    rng = np.random.default_rng(3)
+    dims = [40, 24, 8]
+    X = rng.normal(size=(16, 40)).astype(np.float32)
+    Y = np.eye(8, dtype=np.float32)[rng.integers(8, size=16)]
+    init = nn.mlp_init_arrays(dims, seed=4)
+    model = nn.MLPSequence(dims, "relu", init=init)
+    opt = nn.SGD(model.arena, lr=0.0)             # lr 0: parameters stay put, gradients are what we compare
+    step = nn.CompiledStep(model, "softmax-cross-entropy-sum", opt, X.shape, Y.shape, use_graph=False)
+    step.set_inputs(X, Y)
+    step.step()
+    ref = OracleMLP(dims, "relu", init, "softmax-cross-entropy-sum", opt="sgd", lr=0.0)
+    loss, gW, gb = ref.forward_backward(X, Y)
+    assert abs(step.loss_value() - loss) <= 1e-4 * abs(loss)
+    got = [p.grad.to_numpy().ravel() for p in model.parameters()]
+    exp = [gW[0].vec, gb[0].vec, gW[1].vec, gb[1].vec]
+    for g, e in zip(got, exp):
+        np.testing.assert_allclose(g, e, rtol=1e-4, atol=1e-6)

@@ -351,14 +351,21 @@ def test_sgd_adam_steps(gpu):
     np.testing.assert_array_equal(p.to_numpy(), (p0 - g0 * np.float32(1e-3)).astype(np.float32))
     p, m, v = gpu.from_numpy(p0), gpu.make_tensor((n,)), gpu.make_tensor((n,))
     b1, b2, eps, lr = np.float32(0.9), np.float32(0.999), np.float32(1e-7), np.float32(1e-3)
-    gpu._lib.check(lib.wf2cu_adam_step(p.vec.ptr, 0, g.vec.ptr, 0, m.vec.ptr, 0, v.vec.ptr, 0, n, lr, b1, b2, eps, 1.0))
+    gpu._lib.check(lib.wf2cu_adam_step(p.vec.ptr, 0, g.vec.ptr, 0, m.vec.ptr, 0, v.vec.ptr, 0, n, lr, None, b1, b2, eps, 1.0))
     one = np.float32(1)
-    me = b1 * np.zeros(n, np.float32) + (one - b1) * g0
-    ve = b2 * np.zeros(n, np.float32) + (one - b2) * (g0 * g0)
-    pe = p0 - (lr * me) / (np.sqrt(ve) + eps)
+    m0 = np.zeros(n, np.float32); v0 = np.zeros(n, np.float32)
+    me = m0 + (g0 - m0) * (one - b1)                      # Adam-Step-M, adam.lisp:45-51
+    ve = v0 + (one - b2) * (g0 * g0 - v0)                 # Adam-Step-V, :53-59
+    pe = p0 - (me * lr) / (eps + np.sqrt(ve))             # Adam-Step-Param, :61-67
     np.testing.assert_array_equal(m.to_numpy(), me.astype(np.float32))
     np.testing.assert_array_equal(v.to_numpy(), ve.astype(np.float32))
     assert int(ulp_diff(p.to_numpy(), pe.astype(np.float32)).max()) <= 1
+    # lr_t read from device memory (graph-replay path)
+    p2, m2, v2 = gpu.from_numpy(p0), gpu.make_tensor((n,)), gpu.make_tensor((n,))
+    lrd = gpu.from_numpy(np.array([lr], np.float32))
+    gpu._lib.check(lib.wf2cu_adam_step(p2.vec.ptr, 0, g.vec.ptr, 0, m2.vec.ptr, 0, v2.vec.ptr, 0, n, 123.0, lrd.vec.ptr,
+                                       b1, b2, eps, 1.0))
+    np.testing.assert_array_equal(p2.to_numpy(), p.to_numpy())
 
 
 # ---------------------------------------------------------------- errors, not fallbacks
