@@ -60,6 +60,7 @@ inline int post_launch(const char* name) {
 }
 
 int ensure_scratch(size_t bytes);
+void gemm_tc_release();   // gemm_tc.cu: frees the hi/lo plane workspaces
 
 inline float* fptr(const wf2cu_view* v) { return reinterpret_cast<float*>(v->base) + v->offset; }
 

@@ -163,6 +163,7 @@ int wf2cu_shutdown(void) {
     for (auto& kv : blocks()) cudaFree(kv.first);
     blocks().clear();
   }
+  gemm_tc_release();
   if (s.scratch) cudaFree(s.scratch);
   if (s.counters) cudaFree(s.counters);
   if (s.l2flush) cudaFree(s.l2flush);
