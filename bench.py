@@ -194,6 +194,46 @@ def dist_env():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 
 
+
+def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
+    """C3: `!matmul` (N N)x(N N) fp32 through wf2cu_gemm (auto mode -> tcgen05 3xTF32).  flops = 2N^3
+    (algorithmic); the tensor pipe executes 3 TF32 passes, so pipe-level = 3x.  Peak: TF32 dense =
+    1/2 x the measured bf16 figure of MEASURED_PEAKS.json (no TF32 figure is driver-measured);
+    cuBLAS TF32 on this pool measured 715 TFLOP/s (profiles/r01_cublas_gemm_peaks.log)."""
+    import ctypes as C
+    lib = wf._lib.load()
+    chk = wf._lib.check
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    bf16 = float(json.load(open(p))["bf16_tflops"]) if os.path.exists(p) else 1590.0
+    tf32_peak = bf16 / 2
+    rng = np.random.default_rng(3)
+    cases = []
+    for N in sizes:
+        A = wf.from_numpy(rng.uniform(-1, 1, size=(N, N)).astype(np.float32))
+        B = wf.from_numpy(rng.uniform(-1, 1, size=(N, N)).astype(np.float32))
+        o = wf.make_tensor((N, N))
+        for _ in range(3):
+            wf.ops.matmul(A, B, out=o)
+        reps = 10 if N <= 4096 else 5
+        best = None
+        for _ in range(2):
+            chk(lib.wf2cu_timer_start())
+            for _ in range(reps):
+                wf.ops.matmul(A, B, out=o)
+            ms = C.c_float()
+            chk(lib.wf2cu_timer_stop(C.byref(ms)))
+            best = ms.value / reps if best is None else min(best, ms.value / reps)
+        tf = 2.0 * N ** 3 / (best * 1e-3) / 1e12
+        cases.append({"N": N, "ms": best, "tflops": tf, "frac_of_tf32_peak": tf / tf32_peak, "pipe_tflops": 3 * tf,
+                      "pipe_frac": 3 * tf / tf32_peak})
+        del A, B, o
+    top = cases[-1]
+    return {"workload": "c3_matmul_NxN_f32 (split planes + tcgen05 3xTF32, both launches timed)", "cases": cases,
+            "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::tf32, 3 passes)", "achieved": top["tflops"],
+                         "peak": tf32_peak, "unit": "TFLOP/s", "frac": top["frac_of_tf32_peak"], "pipe_frac": top["pipe_frac"],
+                         "peak_source": "0.5 x MEASURED_PEAKS.json bf16_tflops (TF32 dense); of measured", "N": top["N"],
+                         "traffic": None}}
+
 # ------------------------------------------------------------------------------- reference arm
 def run_reference(args):
     rank, _, world = dist_env()
@@ -378,6 +418,11 @@ def run_ours(args):
         except ModuleNotFoundError:
             mlp = {"unavailable": "MLP training step not built yet"}
 
+    # ---- MatmulNode sweep (C3), single GPU only
+    gemm = None
+    if args.gemm and world == 1:
+        gemm = gemm_sweep(wf)
+
     # ---- CPU baseline (rank 0, N=1): the oracle on one host core, bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -406,7 +451,7 @@ def run_ours(args):
                        "launch": "one step captured into a CUDA graph and replayed",
                        "parallelism": "replicas only" if world > 1 else "single GPU"},
             "roofline": roofline, "cases": per_case, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(), "mlp": mlp,
+            "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(), "mlp": mlp, "gemm": gemm,
         }
         print(json.dumps(line))
     if dist is not None:
@@ -426,6 +471,7 @@ def main():
     ap.add_argument("--cpu-size", type=int, default=4096)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--mlp", type=int, default=1)
+    ap.add_argument("--gemm", type=int, default=1)
     ap.add_argument("--mlp-steps", type=int, default=200)
     ap.add_argument("--mlp-warmup", type=int, default=20)
     args = ap.parse_args()

@@ -1,0 +1,114 @@
+;;;; cffi.lisp — CFFI bindings of include/waffe2cuda.h (1:1), loader and status -> condition.
+;;;; Counterpart of `cl-waffe2-simd/api.lisp:63-274` + `cl-waffe2-simd/shared-object.lisp:3-12`.
+(in-package :cl-waffe2/backends.cuda)
+
+(define-foreign-library libwaffe2cuda
+  (t (:default "libwaffe2cuda")))
+
+(defconstant +max-rank+ 8)
+
+(defcstruct wf2cu-view
+  (base     :pointer)
+  (offset   :int64)
+  (rank     :int32)
+  (reserved :int32)
+  (shape    :int64 :count 8)
+  (stride   :int64 :count 8))
+
+(define-condition cuda-backend-error (error)
+  ((code :initarg :code) (message :initarg :message))
+  (:report (lambda (c s)
+	     (format s "libwaffe2cuda: status ~a: ~a" (slot-value c 'code) (slot-value c 'message)))))
+
+(defcfun ("wf2cu_last_error" %last-error) :string)
+
+(defmacro defwf2 (name (&rest args))
+  "Bind int wf2cu_<name>(args...) as %<name>, and <name> which signals on a non-zero status.
+The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`)."
+  (let* ((cname (format nil "wf2cu_~a" (substitute #\_ #\- (string-downcase (symbol-name name)))))
+	 (raw   (intern (format nil "%~a" name)))
+	 (vars  (mapcar #'car args)))
+    `(progn
+       (defcfun (,cname ,raw) :int ,@args)
+       (declaim (inline ,name))
+       (defun ,name ,vars
+	 (let ((rc (,raw ,@vars)))
+	   (unless (zerop rc)
+	     (error 'cuda-backend-error :code rc :message (%last-error)))
+	   rc)))))
+
+;; runtime
+(defwf2 init ((device :int)))
+(defwf2 shutdown ())
+(defwf2 sync ())
+(defwf2 device-name ((buf :pointer) (buflen :size)))
+(defwf2 launch-count ((out :pointer)))
+;; storage
+(defwf2 malloc ((bytes :size) (out :pointer)))
+(defwf2 retain ((dev :pointer)))
+(defwf2 release ((dev :pointer)))
+(defwf2 memset0 ((dev :pointer) (offset-bytes :size) (bytes :size)))
+(defwf2 h2d ((dev :pointer) (offset-bytes :size) (host :pointer) (bytes :size)))
+(defwf2 d2h ((dev :pointer) (offset-bytes :size) (host :pointer) (bytes :size)))
+(defwf2 d2d ((dst :pointer) (dst-off :size) (src :pointer) (src-off :size) (bytes :size)))
+(defwf2 get-f32 ((dev :pointer) (index :int64) (out :pointer)))
+(defwf2 set-f32 ((dev :pointer) (index :int64) (value :float)))
+;; graphs
+(defwf2 graph-begin ())
+(defwf2 graph-end ((out-exec :pointer)))
+(defwf2 graph-launch ((exec :pointer)))
+(defwf2 graph-destroy ((exec :pointer)))
+;; element-wise
+(defwf2 ew-binary ((op :int) (dst :pointer) (src :pointer)))
+(defwf2 ew-binary3 ((op :int) (out :pointer) (a :pointer) (b :pointer)))
+(defwf2 ew-scalar ((op :int) (dst :pointer) (scalar :float)))
+(defwf2 fill ((dst :pointer) (value :float)))
+(defwf2 ew-unary ((fn :int) (src :pointer) (dst :pointer)))
+(defwf2 pow ((src :pointer) (dst :pointer) (n :float)))
+(defwf2 cmp ((op :int) (x :pointer) (y :pointer) (scal :float) (dst :pointer) (then :float) (else :float)))
+(defwf2 fused ((program :pointer) (n-instr :int) (views :pointer) (nviews :int)))
+;; reductions / composites
+(defwf2 reduce-sum ((x :pointer) (out :pointer) (accumulate :int) (divisor :float)))
+(defwf2 softmax ((x :pointer) (out :pointer) (axis :int) (avoid-overflow :int)))
+(defwf2 reduce-maxmin ((is-min :int) (x :pointer) (out :pointer)))
+(defwf2 argmaxmin ((is-min :int) (x :pointer) (out :pointer)))
+;; MatmulNode
+(defwf2 gemm ((trans-a :int) (trans-b :int) (m :int64) (n :int64) (k :int64)
+	      (a :pointer) (a-off :int64) (lda :int64)
+	      (b :pointer) (b-off :int64) (ldb :int64)
+	      (c :pointer) (c-off :int64) (ldc :int64)
+	      (batch :int64) (stride-a :int64) (stride-b :int64) (stride-c :int64)))
+;; optimizers
+(defwf2 sgd-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64) (n :int64) (lr :float)))
+(defwf2 adam-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64)
+		   (m :pointer) (m-off :int64) (v :pointer) (v-off :int64) (n :int64)
+		   (lr-t :float) (lr-t-dev :pointer) (beta1 :float) (beta2 :float) (eps :float) (grad-scale :float)))
+(defwf2 embedding-gather ((ctx :pointer) (batch :int64) (seq :int64) (wte :pointer) (wpe :pointer) (dim :int64) (out :pointer)))
+;; multi-GPU
+(defwf2 comm-unique-id ((out128 :pointer)))
+(defwf2 comm-init ((rank :int) (world :int) (id128 :pointer)))
+(defwf2 allreduce-sum-f32 ((buf :pointer) (offset :int64) (count :int64)))
+(defwf2 comm-destroy ())
+
+;; enums of waffe2cuda.h
+(defconstant +add+ 0) (defconstant +sub+ 1) (defconstant +mul+ 2) (defconstant +div+ 3) (defconstant +copy+ 4)
+(defparameter *unary-codes*
+  '(:sin 0 :cos 1 :tan 2 :asin 3 :acos 4 :atan 5 :sinh 6 :cosh 7 :tanh 8 :abs 9 :exp 10 :loge 11
+    :log2 12 :log10 13 :log1p 14 :sqrt 15 :cbrt 16 :sign 17 :square 18 :neg 19 :recip 20))
+(defun cmp-code (condition)
+  "Same mapping as `cond->fname` (`source/backends/cpu/logical.lisp:28-35`)."
+  (cond ((eql condition #'=) 0) ((eql condition #'<) 1) ((eql condition #'<=) 2)
+	((eql condition #'>) 3) ((eql condition #'>=) 4)
+	(t (error "CUDATensor: unsupported comparison ~a" condition))))
+
+(defun load-cuda-backend (&key (device 0))
+  "Load the library and select the device.  On failure: warn and leave the backend disabled, as
+`cl-waffe2-simd/shared-object.lisp:3-12` does."
+  (handler-case
+      (progn
+	(use-foreign-library libwaffe2cuda)
+	(init device)
+	(setf *cuda-available-p* t))
+    (error (c)
+      (warn "cl-waffe2/backends.cuda: CUDATensor is disabled (~a)" c)
+      (setf *cuda-available-p* nil))))

@@ -340,6 +340,59 @@ def test_matmul_batched(gpu):
     np.testing.assert_allclose(r, A @ W.T, rtol=1e-4, atol=1e-5)
 
 
+@pytest.fixture
+def tensor_gemm(gpu):
+    """Force the tcgen05 3xTF32 path (mode 2) so small shapes cannot fall back to the SIMT kernel."""
+    lib = gpu._lib.load()
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(2))
+    yield gpu
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+
+
+@pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("m,n,k", [(128, 256, 32), (130, 70, 33), (100, 300, 77), (384, 520, 256), (1024, 256, 784)])
+def test_matmul_tcgen05_3xtf32(tensor_gemm, ta, tb, m, n, k):
+    """MatmulNode on the tensor cores vs fp64 truth; tolerance 1e-4 relative to max|C| (north_star),
+    and within 2e-5 for k <= 2048 (measured model: 3e-7 + 8e-9 k)."""
+    gpu = tensor_gemm
+    A = RNG.uniform(-1, 1, size=(k, m) if ta else (m, k)).astype(np.float32)
+    B = RNG.uniform(-1, 1, size=(n, k) if tb else (k, n)).astype(np.float32)
+    ga, gb = gpu.from_numpy(A), gpu.from_numpy(B)
+    r = gpu.ops.matmul(gpu.ops.t(ga) if ta else ga, gpu.ops.t(gb) if tb else gb).to_numpy()
+    truth = (A.T if ta else A).astype(np.float64) @ (B.T if tb else B).astype(np.float64)
+    err = np.abs(r - truth).max() / np.abs(truth).max()
+    assert err <= 2e-5, err
+
+
+def test_matmul_tcgen05_batched_and_shared_operand(tensor_gemm):
+    gpu = tensor_gemm
+    A = RNG.uniform(-1, 1, size=(2, 3, 200, 96)).astype(np.float32)
+    B = RNG.uniform(-1, 1, size=(2, 3, 96, 264)).astype(np.float32)
+    r = gpu.ops.matmul(gpu.from_numpy(A), gpu.from_numpy(B)).to_numpy()
+    np.testing.assert_allclose(r, A.astype(np.float64) @ B.astype(np.float64), rtol=0, atol=2e-5 * 10)
+    W = RNG.uniform(-1, 1, size=(520, 96)).astype(np.float32)      # LinearLayer: x @ (!t W), W shared by the batch
+    r = gpu.ops.matmul(gpu.from_numpy(A), gpu.ops.t(gpu.from_numpy(W))).to_numpy()
+    np.testing.assert_allclose(r, A.astype(np.float64) @ W.T.astype(np.float64), rtol=0, atol=2e-5 * 10)
+
+
+def test_matmul_tcgen05_exact_small_integers(tensor_gemm):
+    """The reference's golden style (base-impl/t/arithmetic.lisp:116-149): integer-valued operands give exact results."""
+    gpu = tensor_gemm
+    A = RNG.integers(-8, 9, size=(128, 64)).astype(np.float32)
+    B = RNG.integers(-8, 9, size=(64, 256)).astype(np.float32)
+    r = gpu.ops.matmul(gpu.from_numpy(A), gpu.from_numpy(B)).to_numpy()
+    np.testing.assert_array_equal(r, A @ B)
+
+
+def test_matmul_large_k_accumulation(tensor_gemm):
+    gpu = tensor_gemm
+    A = RNG.uniform(-1, 1, size=(128, 8192)).astype(np.float32)
+    B = RNG.uniform(-1, 1, size=(8192, 256)).astype(np.float32)
+    r = gpu.ops.matmul(gpu.from_numpy(A), gpu.from_numpy(B)).to_numpy()
+    truth = A.astype(np.float64) @ B.astype(np.float64)
+    assert np.abs(r - truth).max() / np.abs(truth).max() <= 1e-4
+
+
 # ---------------------------------------------------------------- optimizers
 def test_sgd_adam_steps(gpu):
     n = 1000
