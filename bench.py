@@ -267,8 +267,17 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------- our arm
+def stage(msg: str):
+    """Progress marker on stderr (WF2_BENCH_TRACE=1): tells where a multi-rank run stopped."""
+    if os.environ.get("WF2_BENCH_TRACE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')} t={time.time() % 1000:.1f}] {msg}", file=sys.stderr, flush=True)
+
+
 def run_ours(args):
     rank, local_rank, world = dist_env()
+    if os.environ.get("WF2_BENCH_TRACE"):
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ.get("WF2_BENCH_TRACE_AFTER", "90")), exit=False, file=sys.stderr)
     if world != args.gpus and world > 1:
         args.gpus = world
     wf = importlib.import_module("cl-waffe2_b200")
@@ -297,8 +306,10 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    stage("process group ready")
     n = args.size
     sw = GpuSweep(wf, n)
+    stage("sweep buffers uploaded")
     launches0 = C.c_int64()
 
     def capture(fn):
@@ -334,6 +345,7 @@ def run_ours(args):
             for _ in range(20):
                 chk(lib.wf2cu_graph_launch(step_graph))
             chk(lib.wf2cu_sync())
+    stage("sweep timed")
     total_ms = max_over_ranks(float(ms.value))
     ms_per_step = total_ms / args.steps
     bytes_step = sw.bytes_per_step()
@@ -409,6 +421,7 @@ def run_ours(args):
            "h2d_bytes_per_step": 2 * nb, "d2h_bytes_per_step": d2h_bytes,
            "api": "cl-waffe2_b200.ops (one libwaffe2cuda C-ABI call per node) + wf2cu_h2d/wf2cu_d2h from pinned host memory"}
 
+    stage("e2e timed")
     # ---- MLP training step (the sharded path)
     mlp = None
     if args.mlp:
@@ -418,6 +431,7 @@ def run_ours(args):
         except ModuleNotFoundError:
             mlp = {"unavailable": "MLP training step not built yet"}
 
+    stage("mlp done")
     # ---- MatmulNode sweep (C3), single GPU only
     gemm = None
     if args.gemm and world == 1:

@@ -12,10 +12,10 @@ The directory name is not a Python identifier; import it with
 """
 from . import _lib
 from ._lib import Wf2CudaError, init, shutdown
-from .tensor import (CUDATensor, StaticPool, Storage, T, tensor_at, ax_plus_b, calc_strides, from_numpy, make_tensor, permute,
+from .tensor import (CUDATensor, StaticPool, Storage, T, tensor_at, as_strided, ax_plus_b, calc_strides, from_numpy, make_tensor, permute,
                      range_nth, range_size, reshape_contiguous, transpose, view)
 from . import ops
 
-__all__ = ["_lib", "Wf2CudaError", "init", "shutdown", "CUDATensor", "StaticPool", "Storage", "tensor_at", "T", "ax_plus_b", "calc_strides",
+__all__ = ["_lib", "Wf2CudaError", "init", "shutdown", "CUDATensor", "StaticPool", "Storage", "tensor_at", "as_strided", "T", "ax_plus_b", "calc_strides",
            "from_numpy", "make_tensor", "permute", "range_nth", "range_size", "reshape_contiguous", "transpose",
            "view", "ops"]

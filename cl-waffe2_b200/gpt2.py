@@ -1,0 +1,171 @@
+"""GPT-2 forward on CUDATensor (BASELINE.json config 5: examples/gpt-2, GPT-2 small, random-init
+weights, seq 1024, batch 8), composed from the backend's nodes exactly as the reference example
+composes them — including its quirks, reproduced as written:
+
+  * `SelfAttention` (examples/gpt-2/utils.lisp:222-244): w = Q.K ; w / N where N = the LAST axis
+    of w (sequence length, not sqrt(head_dim)) ; `(!softmax w :avoid-overflow nil)` with the
+    default `:axis 1`, i.e. normalised over the HEADS axis of the (B H N N) tensor ; no causal mask.
+  * `split-heads` / `merge-heads` (utils.lisp:204-220): slice of the fused QKV projection,
+    reshape to heads, permute; K is permuted to (B H d N).
+  * `LayerNorm-Revisit` (utils.lisp:114-127) and nn `LayerNorm` (source/nn/norms.lisp:44-85):
+    u = mean(x,-1); s = mean((x-u)^2,-1); (x-u)/sqrt(s+eps) * g + b, eps = 1e-5.
+  * `!gelu-lisptanh` (utils.lisp:129-137): 0.5 x (1 + tanh(sqrt(2/pi)(x + 0.044715 x^3))).
+  * `GPT2PositionalEmbedding` (utils.lisp:19-112): out[b,p,:] = wte[round(ctx[b,p])] + wpe[p];
+    token ids are floats.
+  * `lm-head` (model.lisp:191-192): x . wte^T.
+
+Each step below is one call of the C ABI (one kernel, or split+GEMM for `!matmul`)."""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from . import _lib, ops
+from .tensor import CUDATensor, as_strided, from_numpy, make_tensor, reshape_contiguous, view, T
+
+CONFIG_SMALL = dict(n_vocab=50257, n_ctx=1024, n_emb=768, n_head=12, n_layer=12)
+
+
+def init_weights(cfg: Dict[str, int], seed: int = 0, std: float = 0.02) -> Dict[str, np.ndarray]:
+    """Random-init weights with the shapes the example loads from .npy (model.lisp:64-86,145-160):
+    N(0, 0.02) matrices, LayerNorm gains 1 + N(0,0.02), biases N(0, 0.02).  Host arrays, so the same
+    numbers feed the oracle and the device."""
+    rng = np.random.default_rng(seed)
+    E, V, C, L = cfg["n_emb"], cfg["n_vocab"], cfg["n_ctx"], cfg["n_layer"]
+    f = lambda *s: rng.normal(0.0, std, size=s).astype(np.float32)
+    w = {"wte": f(V, E), "wpe": f(C, E), "ln_f.g": (1 + f(E)).astype(np.float32), "ln_f.b": f(E)}
+    for i in range(L):
+        p = f"h{i}."
+        w[p + "ln_1.g"] = (1 + f(E)).astype(np.float32); w[p + "ln_1.b"] = f(E)
+        w[p + "ln_2.g"] = (1 + f(E)).astype(np.float32); w[p + "ln_2.b"] = f(E)
+        w[p + "attn.c_attn.w"] = f(E, 3 * E); w[p + "attn.c_attn.b"] = f(3 * E)
+        w[p + "attn.c_proj.w"] = f(E, E); w[p + "attn.c_proj.b"] = f(E)
+        w[p + "mlp.c_fc.w"] = f(E, 4 * E); w[p + "mlp.c_fc.b"] = f(4 * E)
+        w[p + "mlp.c_proj.w"] = f(4 * E, E); w[p + "mlp.c_proj.b"] = f(E)
+    return w
+
+
+def _bcast_last(vec1d: CUDATensor, like: CUDATensor) -> CUDATensor:
+    """`(%transform b[i] -> [~ i])`: a (E) vector broadcast over every leading axis of `like`."""
+    r = like.dims()
+    t = reshape_contiguous(vec1d, [1] * (r - 1) + [like.shape[-1]])
+    return view(t, *([[":broadcast", n] for n in like.shape[:-1]] + [T]))
+
+
+def _bcast_keep(stat: CUDATensor, like: CUDATensor) -> CUDATensor:
+    """A keepdims statistic (... 1) broadcast along the last axis of `like`."""
+    return view(stat, *([T] * (like.dims() - 1) + [[":broadcast", like.shape[-1]]]))
+
+
+def layer_norm(x: CUDATensor, g: CUDATensor, b: CUDATensor, eps: float = 1e-5) -> CUDATensor:
+    """LayerNorm-Revisit (examples/gpt-2/utils.lisp:114-127), node by node."""
+    shape = x.shape
+    u = make_tensor(shape[:-1] + [1])
+    ops.mean(x, axis=-1, out=u)
+    d = ops.sub(x, _bcast_keep(u, x))                       # x - u
+    sq = ops.expt(d, 2)                                     # (!expt (!sub x u) 2)
+    s = make_tensor(shape[:-1] + [1])
+    ops.mean(sq, axis=-1, out=s)
+    ops.add_(s, eps)                                        # s + eps
+    ops.unary("sqrt", s, out=s)
+    ops.div_(d, _bcast_keep(s, x))                          # (x - u) / sqrt(s + eps)
+    ops.mul_(d, _bcast_last(g, x))
+    ops.add_(d, _bcast_last(b, x))
+    return d
+
+
+def split_heads(qkv: CUDATensor, which: str, n_head: int) -> CUDATensor:
+    """utils.lisp:204-215.  qkv: dense (B N 3E).  Q, V -> (B H N d); K -> (B H d N).  Views only."""
+    B, N, E3 = qkv.shape
+    E = E3 // 3
+    d = E // n_head
+    off = {"Q": 0, "K": E, "V": 2 * E}[which]
+    if which == "K":
+        return as_strided(qkv, [B, n_head, d, N], [N * E3, d, 1, E3], off)
+    return as_strided(qkv, [B, n_head, N, d], [N * E3, d, E3, 1], off)
+
+
+def merge_heads(x: CUDATensor) -> CUDATensor:
+    """utils.lisp:217-220: (B H N d) -> permute (B N H d) -> reshape (B N E) (one transpose copy)."""
+    B, H, N, d = x.shape
+    xc = ops.contiguous(x)
+    p = as_strided(xc, [B, N, H, d], [H * N * d, d, N * d, 1], 0)
+    return reshape_contiguous(ops.copy(p), [B, N, H * d])
+
+
+def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
+    """SelfAttention (utils.lisp:222-244) without a past: as written in the example."""
+    Q = split_heads(qkv, "Q", n_head)
+    K = split_heads(qkv, "K", n_head)
+    V = split_heads(qkv, "V", n_head)
+    w = ops.matmul(Q, K)                                    # (B H N N); operands made contiguous (adjust-layout)
+    ops.div_(w, float(w.shape[-1]))                         # (!div w (make-tensor N))
+    ops.softmax(w, avoid_overflow=False, axis=1, out=w)     # default axis=1 -> over heads
+    a = ops.matmul(w, V)                                    # (B H N d)
+    return merge_heads(a)
+
+
+def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor) -> CUDATensor:
+    """`(!matmul x w)` + `(!add (%transform b[i] -> [~ i]))` (model.lisp:118-120)."""
+    y = ops.matmul(x, w)                                    # (B N in) . (in out): W shared by the batch
+    ops.add_(y, _bcast_last(b, y))
+    return y
+
+
+class GPT2Layer:
+    """model.lisp:47-137."""
+
+    def __init__(self, weights: Dict[str, np.ndarray], i: int, n_head: int):
+        p = f"h{i}."
+        g = lambda k: from_numpy(weights[p + k])
+        self.n_head = n_head
+        self.ln_1_g, self.ln_1_b, self.ln_2_g, self.ln_2_b = g("ln_1.g"), g("ln_1.b"), g("ln_2.g"), g("ln_2.b")
+        self.attn_w, self.attn_b = g("attn.c_attn.w"), g("attn.c_attn.b")
+        self.proj_w, self.proj_b = g("attn.c_proj.w"), g("attn.c_proj.b")
+        self.fc_w, self.fc_b = g("mlp.c_fc.w"), g("mlp.c_fc.b")
+        self.fc_proj_w, self.fc_proj_b = g("mlp.c_proj.w"), g("mlp.c_proj.b")
+
+    def __call__(self, x: CUDATensor) -> CUDATensor:
+        h = layer_norm(x, self.ln_1_g, self.ln_1_b)
+        qkv = _linear(h, self.attn_w, self.attn_b)
+        a = self_attention(qkv, self.n_head)
+        a = _linear(a, self.proj_w, self.proj_b)
+        x = ops.add(x, a)                                   # residual
+        h = layer_norm(x, self.ln_2_g, self.ln_2_b)
+        m = _linear(h, self.fc_w, self.fc_b)
+        ops.gelu(m, out=m)
+        m = _linear(m, self.fc_proj_w, self.fc_proj_b)
+        return ops.add(x, m)                                # residual
+
+
+class GPT2:
+    """model.lisp:139-192: embedding -> n_layer blocks -> LayerNorm [-> lm-head]."""
+
+    def __init__(self, cfg: Dict[str, int] = None, weights: Optional[Dict[str, np.ndarray]] = None, seed: int = 0):
+        self.cfg = dict(CONFIG_SMALL if cfg is None else cfg)
+        w = weights if weights is not None else init_weights(self.cfg, seed)
+        self.wte, self.wpe = from_numpy(w["wte"]), from_numpy(w["wpe"])
+        self.ln_g, self.ln_b = from_numpy(w["ln_f.g"]), from_numpy(w["ln_f.b"])
+        self.layers: List[GPT2Layer] = [GPT2Layer(w, i, self.cfg["n_head"]) for i in range(self.cfg["n_layer"])]
+
+    def embed(self, ctx: CUDATensor) -> CUDATensor:
+        """GPT2PositionalEmbedding (utils.lisp:19-112); ctx: (B N) float token ids."""
+        B, N = ctx.shape
+        E = self.cfg["n_emb"]
+        out = make_tensor([B, N, E])
+        lc = ctx.lower()
+        _lib.check(_lib.load().wf2cu_embedding_gather(ctx.vec.ptr + 4 * lc.offset, B, N, self.wte.vec.ptr,
+                                                      self.wpe.vec.ptr, E, out.vec.ptr))
+        return out
+
+    def forward(self, ctx: CUDATensor, lm_head: bool = False) -> CUDATensor:
+        x = self.embed(ctx)
+        for layer in self.layers:
+            x = layer(x)
+        x = layer_norm(x, self.ln_g, self.ln_b)
+        if lm_head:
+            x = ops.matmul(x, ops.t(self.wte))              # (B N E) . (V E)^T
+        return x
+
+    __call__ = forward

@@ -26,8 +26,15 @@ def _comm_init(dist, rank: int, world: int):
     _lib.check(lib.wf2cu_comm_init(rank, world, C.create_string_buffer(ids, 128)))
 
 
+def _stage(msg):
+    import os, sys, time
+    if os.environ.get("WF2_BENCH_TRACE"):
+        print(f"[mlp rank {os.environ.get('RANK', '0')} t={time.time() % 1000:.1f}] {msg}", file=sys.stderr, flush=True)
+
+
 def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
     lib = _lib.load()
+    _stage(f"run_one batch={per_gpu_batch}")
     chk = _lib.check
     rng = np.random.default_rng(seed + 17 * rank)          # each rank owns a different shard
     X = rng.uniform(0, 1, size=(per_gpu_batch, DIMS[0])).astype(np.float32)
@@ -49,8 +56,11 @@ def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    for _ in range(max(warmup, 3)):
+    for i in range(max(warmup, 3)):
         step.step()
+        if i < 3:
+            chk(lib.wf2cu_sync())
+            _stage(f"warm-up step {i} done")
     first_loss = None
     barrier()
     l0 = C.c_int64(); l1 = C.c_int64()
@@ -97,7 +107,9 @@ def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
 
 def run(wf, dist, rank: int, world: int, steps: int = 200, warmup: int = 20) -> dict:
     if world > 1:
+        _stage("comm init")
         _comm_init(dist, rank, world)
+        _stage("comm ready")
     res = {"model": "MNIST MLP 784-256-256-10, relu, softmax-cross-entropy (!sum), Adam lr 1e-3, fp32",
            "data": "synthetic U(0,1) inputs, one-hot labels", "n_gpus": world,
            "collective": "one NCCL allreduce(sum) of the 269,322-float gradient bucket per step, inside the CUDA graph"

@@ -432,3 +432,15 @@ def tensor_at(storage: Storage, offset: int, shape, requires_grad=False) -> CUDA
     t = CUDATensor(storage, [int(s) for s in shape], order="column", requires_grad=requires_grad)
     t.initial_offset = int(offset)
     return t
+
+
+def as_strided(t: CUDATensor, shape, strides, offset: int = 0) -> CUDATensor:
+    """A tensor over t's storage with explicit element strides — what a chain of `!view` (slice) +
+    `!reshape` + `!permute` leaves in `tensor-stride` / `tensor-initial-offset`
+    (examples/gpt-2/utils.lisp:204-220 `split-heads`), built in one step.  `offset` is relative to
+    t's own base offset; t must be a dense tensor."""
+    base = t.lower().offset
+    out = CUDATensor(t.vec, [int(s) for s in shape], order="column")
+    out.stride = [int(s) for s in strides]
+    out.initial_offset = int(base + offset)
+    return out

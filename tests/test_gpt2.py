@@ -1,0 +1,91 @@
+"""GPT-2 forward (BASELINE.json config 5).  The reference has no tests or golden vectors for its
+GPT-2 example (it needs downloaded weights), so the checker is oracle/gpt2.py — a numpy
+restatement of examples/gpt-2/{model,utils}.lisp — in fp64; tolerance 1e-3 relative to max|h|
+on the final hidden state (deep fp32 chain)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from oracle import gpt2 as O
+
+CFG = dict(n_vocab=211, n_ctx=48, n_emb=64, n_head=4, n_layer=3)
+
+
+def _weights(cfg, seed=0):
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    return g.init_weights(cfg, seed)
+
+
+# ------------------------------------------------------------------ oracle self-checks (CPU)
+def test_oracle_attention_is_normalised_over_heads():
+    """(!softmax w :avoid-overflow nil) with the default axis=1 on a 4-D tensor: sums over HEADS are 1
+    (examples/gpt-2/utils.lisp:236-242), not over keys."""
+    rng = np.random.default_rng(0)
+    w = rng.normal(size=(2, 4, 5, 5))
+    s = O.softmax_no_shift(w, axis=1)
+    np.testing.assert_allclose(s.sum(axis=1), 1.0, rtol=1e-12)
+    assert not np.allclose(s.sum(axis=-1), 1.0)
+
+
+def test_oracle_split_merge_heads_roundtrip():
+    rng = np.random.default_rng(1)
+    x = rng.normal(size=(2, 6, 3 * 16))
+    q, k, v = (O.split_heads(x, w, 4) for w in "QKV")
+    assert q.shape == (2, 4, 6, 4) and k.shape == (2, 4, 4, 6) and v.shape == (2, 4, 6, 4)
+    np.testing.assert_array_equal(O.merge_heads(q), x[..., :16])
+    np.testing.assert_array_equal(O.merge_heads(k.transpose(0, 1, 3, 2)), x[..., 16:32])
+
+
+def test_oracle_layernorm_and_embedding():
+    rng = np.random.default_rng(2)
+    x = rng.normal(size=(3, 5, 32))
+    y = O.layer_norm(x, np.ones(32), np.zeros(32))
+    np.testing.assert_allclose(y.mean(-1), 0, atol=1e-12)
+    np.testing.assert_allclose(y.var(-1), 1, rtol=1e-4)
+    wte, wpe = rng.normal(size=(10, 4)), rng.normal(size=(7, 4))
+    ctx = np.array([[0.0, 9.0, 3.2]])           # float ids, rounded (utils.lisp:60-75)
+    e = O.embed(ctx, wte, wpe)
+    np.testing.assert_array_equal(e[0, 2], wte[3] + wpe[2])
+
+
+def test_oracle_fp32_tracks_fp64():
+    W = _weights(CFG)
+    ctx = np.random.default_rng(3).integers(0, CFG["n_vocab"], size=(2, 16)).astype(np.float32)
+    h64 = O.forward(ctx, W, CFG, np.float64)
+    h32 = O.forward(ctx, W, CFG, np.float32)
+    assert np.abs(h32 - h64).max() / np.abs(h64).max() < 1e-4
+
+
+# ------------------------------------------------------------------ device parity
+@pytest.mark.gpu
+@pytest.mark.parametrize("lm_head", [False, True])
+def test_gpt2_forward_matches_oracle(gpu, lm_head):
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    W = _weights(CFG, seed=5)
+    ctx = np.random.default_rng(4).integers(0, CFG["n_vocab"], size=(3, 24)).astype(np.float32)
+    model = g.GPT2(CFG, W)
+    out = model(gpu.from_numpy(ctx), lm_head=lm_head).to_numpy()
+    truth = O.forward(ctx, W, CFG, np.float64, lm_head=lm_head)
+    assert out.shape == truth.shape
+    err = np.abs(out - truth).max() / np.abs(truth).max()
+    ref = np.abs(O.forward(ctx, W, CFG, np.float32, lm_head=lm_head) - truth).max() / np.abs(truth).max()
+    assert err <= 1e-3, (err, ref)
+    assert err <= max(50 * ref, 2e-5), (err, ref)
+
+
+@pytest.mark.gpu
+def test_gpt2_blocks_on_tensor_cores(gpu):
+    """Same forward with the tcgen05 3xTF32 path forced for every !matmul."""
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    cfg = dict(n_vocab=300, n_ctx=128, n_emb=128, n_head=4, n_layer=2)
+    W = _weights(cfg, seed=6)
+    ctx = np.random.default_rng(7).integers(0, cfg["n_vocab"], size=(2, 128)).astype(np.float32)
+    lib = gpu._lib.load()
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(2))
+    try:
+        out = g.GPT2(cfg, W)(gpu.from_numpy(ctx)).to_numpy()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    truth = O.forward(ctx, W, cfg, np.float64)
+    assert np.abs(out - truth).max() / np.abs(truth).max() <= 1e-3
