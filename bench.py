@@ -234,6 +234,55 @@ def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
                          "peak_source": "0.5 x MEASURED_PEAKS.json bf16_tflops (TF32 dense); of measured", "N": top["N"],
                          "traffic": None}}
 
+
+def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3):
+    """C5: examples/gpt-2 GPT-2 small forward (hidden states, as `(call model prev)` returns them),
+    random-init weights, fp32, B=8, N=1024, semantics as the example writes them.  The launch sequence
+    runs under a StaticPool (the reference's static allocation) and is replayed as one CUDA graph."""
+    import ctypes as C
+    lib = wf._lib.load()
+    chk = wf._lib.check
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    cfg = dict(g.CONFIG_SMALL)
+    model = g.GPT2(cfg, seed=0)
+    rng = np.random.default_rng(11)
+    ctx = wf.from_numpy(rng.integers(0, cfg["n_vocab"], size=(batch, seq)).astype(np.float32))
+    pool = wf.StaticPool()
+    l0 = C.c_int64(); l1 = C.c_int64()
+    for _ in range(2):                       # 1st run allocates the plan + GEMM workspace, 2nd checks it is static
+        chk(lib.wf2cu_launch_count(C.byref(l0)))
+        with pool:
+            out = model(ctx)
+        chk(lib.wf2cu_launch_count(C.byref(l1)))
+    chk(lib.wf2cu_sync())
+    pool.frozen = True
+    ex = C.c_void_p()
+    chk(lib.wf2cu_graph_begin())
+    try:
+        with pool:
+            out = model(ctx)
+    finally:
+        rc = lib.wf2cu_graph_end(C.byref(ex))
+    chk(rc)
+    chk(lib.wf2cu_graph_launch(ex))
+    best = None
+    for _ in range(reps):
+        chk(lib.wf2cu_timer_start())
+        chk(lib.wf2cu_graph_launch(ex))
+        ms = C.c_float()
+        chk(lib.wf2cu_timer_stop(C.byref(ms)))
+        best = ms.value if best is None else min(best, ms.value)
+    h = out.to_numpy()
+    chk(lib.wf2cu_graph_destroy(ex))
+    # matmul flops of one forward: per layer qkv + attn-proj + fc + fc-proj, plus QK^T and PV
+    E, L, H = cfg["n_emb"], cfg["n_layer"], cfg["n_head"]
+    T = batch * seq
+    flops = L * (2 * T * E * 3 * E + 2 * T * E * E + 2 * 2 * T * E * 4 * E + 2 * 2 * batch * H * seq * seq * (E // H))
+    return {"workload": f"gpt2_small_forward_b{batch}_n{seq}_f32 (hidden states, random-init weights)", "ms_per_forward": best,
+            "tokens_per_s": T / (best * 1e-3), "launches_per_forward": int(l1.value - l0.value),
+            "matmul_tflops": flops / (best * 1e-3) / 1e12, "pool_bytes": pool.nbytes(),
+            "finite": bool(np.isfinite(h).all()), "hidden_absmax": float(np.abs(h).max())}
+
 # ------------------------------------------------------------------------------- reference arm
 def run_reference(args):
     rank, _, world = dist_env()
@@ -437,6 +486,14 @@ def run_ours(args):
     if args.gemm and world == 1:
         gemm = gemm_sweep(wf)
 
+    gpt2 = None
+    if args.gpt2 and world == 1:
+        stage("gpt2")
+        try:
+            gpt2 = gpt2_forward_bench(wf)
+        except Exception as e:                       # reported, never silently dropped
+            gpt2 = {"error": repr(e)}
+
     # ---- CPU baseline (rank 0, N=1): the oracle on one host core, bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -465,7 +522,7 @@ def run_ours(args):
                        "launch": "one step captured into a CUDA graph and replayed",
                        "parallelism": "replicas only" if world > 1 else "single GPU"},
             "roofline": roofline, "cases": per_case, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(), "mlp": mlp, "gemm": gemm,
+            "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(), "mlp": mlp, "gemm": gemm, "gpt2": gpt2,
         }
         print(json.dumps(line))
     if dist is not None:
@@ -486,6 +543,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--mlp", type=int, default=1)
     ap.add_argument("--gemm", type=int, default=1)
+    ap.add_argument("--gpt2", type=int, default=1)
     ap.add_argument("--mlp-steps", type=int, default=200)
     ap.add_argument("--mlp-warmup", type=int, default=20)
     args = ap.parse_args()

@@ -22,6 +22,7 @@ struct Nccl {
   fn_comm_init_rank comm_init_rank = nullptr;
   fn_all_reduce all_reduce = nullptr;
   fn_comm_destroy comm_destroy = nullptr;
+  fn_comm_destroy comm_abort = nullptr;
   fn_error_string error_string = nullptr;
   NcclComm comm = nullptr;
   int rank = -1, world = 0;
@@ -38,6 +39,7 @@ static int load_nccl() {
   g_nccl.comm_init_rank = (fn_comm_init_rank)dlsym(g_nccl.handle, "ncclCommInitRank");
   g_nccl.all_reduce = (fn_all_reduce)dlsym(g_nccl.handle, "ncclAllReduce");
   g_nccl.comm_destroy = (fn_comm_destroy)dlsym(g_nccl.handle, "ncclCommDestroy");
+  g_nccl.comm_abort = (fn_comm_destroy)dlsym(g_nccl.handle, "ncclCommAbort");
   g_nccl.error_string = (fn_error_string)dlsym(g_nccl.handle, "ncclGetErrorString");
   if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.all_reduce || !g_nccl.comm_destroy)
     return set_error(WF2CU_ERR_COMM, "NCCL library lacks a required symbol");
@@ -94,8 +96,12 @@ int wf2cu_allreduce_sum_f32(void* buf, int64_t offset, int64_t count) {
 
 int wf2cu_comm_destroy(void) {
   if (g_nccl.comm) {
+    // All work on the library stream is drained first.  ncclCommDestroy blocks for ever while a CUDA
+    // graph that captured a collective of this communicator is still instantiated (measured on
+    // B200 / NCCL 2.28.9), so tear down with ncclCommAbort, which does not wait on graph references.
     cudaStreamSynchronize(S().stream);
-    g_nccl.comm_destroy(g_nccl.comm);
+    if (g_nccl.comm_abort) g_nccl.comm_abort(g_nccl.comm);
+    else g_nccl.comm_destroy(g_nccl.comm);
     g_nccl.comm = nullptr;
   }
   return 0;

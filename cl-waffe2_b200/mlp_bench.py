@@ -98,6 +98,7 @@ def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
     e2e_ms = max_ranks(ms.value) / steps
     chk(lib.wf2cu_host_free(hx)); chk(lib.wf2cu_host_free(hy))
     gb = per_gpu_batch * world
+    step.close()
     return {"per_gpu_batch": per_gpu_batch, "global_batch": gb, "ms_per_step": dev_ms,
             "samples_per_s": gb / (dev_ms * 1e-3), "e2e_ms_per_step": e2e_ms, "e2e_samples_per_s": gb / (e2e_ms * 1e-3),
             "h2d_bytes_per_step": int(X.nbytes + Y.nbytes), "d2h_bytes_per_step": 4,

@@ -226,17 +226,34 @@ def mse(x: CUDATensor, y: CUDATensor, reduction: str = "mean") -> CUDATensor:
 
 
 # ------------------------------------------------------------------------------- parameters
+def bucket_layout(shapes: Sequence[Sequence[int]]):
+    """Element offsets of each parameter inside the flat bucket (every tensor 16-byte aligned) and the
+    bucket length.  Pure host logic: the same layout is used for parameters, gradients and Adam state,
+    and is what the NCCL allreduce sums over."""
+    offsets = [0]
+    for s in shapes:
+        n = int(np.prod(s))
+        offsets.append(offsets[-1] + ((n + 3) & ~3))
+    return offsets[:-1], offsets[-1]
+
+
+def shard_rows(global_batch: int, rank: int, world: int):
+    """Rows [lo, hi) of the global batch owned by `rank` (batch sharding of SURVEY §8e; the reference
+    expresses a minibatch the same way with `tensor-displace-to`, examples/mnist/mlp.lisp:46-48)."""
+    if global_batch % world:
+        raise ValueError(f"global batch {global_batch} is not divisible by world size {world}")
+    per = global_batch // world
+    return rank * per, (rank + 1) * per
+
+
 class ParameterArena:
     """All parameters in one storage, all gradients in another (the allocator hook that
     makes a single gradient bucket possible)."""
 
     def __init__(self, shapes: Sequence[Sequence[int]]):
-        sizes = [int(np.prod(s)) for s in shapes]
-        self.offsets = [0]
-        for n in sizes:
-            # keep every tensor 16-byte aligned inside the bucket
-            self.offsets.append(self.offsets[-1] + ((n + 3) & ~3))
-        self.total = self.offsets[-1]
+        offs, total = bucket_layout(shapes)
+        self.offsets = offs + [total]
+        self.total = total
         _lib.init(_lib._inited_device if _lib._inited_device is not None else 0)
         self.param_store = Storage(self.total * 4)
         self.grad_store = Storage(self.total * 4)
@@ -415,6 +432,13 @@ class CompiledStep:
                 self.graph = ex
             _lib.check(lib.wf2cu_graph_launch(self.graph))
         self._runs += 1
+
+    def close(self):
+        """Destroy the captured graph (must happen before the communicator it references goes away)."""
+        if self.graph is not None:
+            _lib.check(_lib.load().wf2cu_sync())
+            _lib.check(_lib.load().wf2cu_graph_destroy(self.graph))
+            self.graph = None
 
     def loss_value(self) -> float:
         """`->scal` of the loss: one 4-byte D2H, the only sync of a step."""
