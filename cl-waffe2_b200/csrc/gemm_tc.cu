@@ -342,6 +342,165 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
   }
 }
 
+// ------------------------------------------------------------------ step 2b: 256 x 256 tile variant
+// Why: the 128x256 kernel needs 96 KiB of operands per 1536 tensor-cycles = 62.5 B/clk per SM, which is the
+// SM's whole L2 read port; ncu showed the tensor pipe idle 26 % of a tile waiting for TMA
+// (profiles/r01_gemm_ncu.md).  A 256x256 tile (two M=128 MMAs sharing each B slice) needs
+// 64 KiB per 1536 cycles = 42.7 B/clk.  k-block = 16 floats (64-byte rows, SWIZZLE_64B) so that
+// 3 stages x 64 KiB fit; the two 128x256 accumulators fill TMEM (512 columns), so the epilogue is
+// not overlapped with the next tile's MMAs (<= 2 % at K = 4096).
+constexpr int T2M = 256, T2N = 256, T2K = 16, T2_STAGES = 3;
+constexpr int T2_PLANE = 256 * T2K * 4;                 // 16 KiB: 256 rows x 64 B
+constexpr int T2_STAGE_BYTES = 4 * T2_PLANE;            // A_hi A_lo B_hi B_lo = 64 KiB
+constexpr int T2_SMEM_BYTES = T2_STAGES * T2_STAGE_BYTES + 1024 + 256;
+
+// K-major SWIZZLE_64B descriptor: SBO = 8 rows x 64 B = 512, layout_type = 4
+__device__ __forceinline__ uint64_t make_desc_sw64(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(512 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)4 << 61;
+  return d;
+}
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
+                  const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
+                  const __grid_constant__ TcArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_STAGES * T2_STAGE_BYTES);
+  uint64_t* full = bars;                       // [T2_STAGES]
+  uint64_t* empty = bars + T2_STAGES;          // [T2_STAGES]
+  uint64_t* acc_full = bars + 2 * T2_STAGES;   // [1]
+  uint64_t* acc_empty = acc_full + 1;          // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = a.tiles_m * a.tiles_n * a.batch;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < T2_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init(acc_empty, 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t tx_bytes = a.passes == 3 ? T2_STAGE_BYTES : 2 * T2_PLANE;
+      int s = 0; uint32_t ph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int b, mt, nt;
+        tile_coords(t, a, b, mt, nt);
+        const int ba = a.a_bcast ? 0 : b, bb = a.b_bcast ? 0 : b;
+        for (int kb = 0; kb < a.nkb; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* st = smem + s * T2_STAGE_BYTES;
+          mbar_expect_tx(&full[s], tx_bytes);
+          tma_load_3d(&map_ah, &full[s], st, kb * T2K, mt * T2M, ba);
+          tma_load_3d(&map_bh, &full[s], st + 2 * T2_PLANE, kb * T2K, nt * T2N, bb);
+          if (a.passes == 3) {
+            tma_load_3d(&map_al, &full[s], st + T2_PLANE, kb * T2K, mt * T2M, ba);
+            tma_load_3d(&map_bl, &full[s], st + 3 * T2_PLANE, kb * T2K, nt * T2N, bb);
+          }
+          if (++s == T2_STAGES) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      uint32_t aph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        mbar_wait(acc_empty, aph ^ 1);          // both accumulators drained by the epilogue
+        tc_fence_after();
+        for (int kb = 0; kb < a.nkb; ++kb) {
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t st = smem_u32(smem + s * T2_STAGE_BYTES);
+          const uint64_t dbh = make_desc_sw64(st + 2 * T2_PLANE), dbl = make_desc_sw64(st + 3 * T2_PLANE);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {         // rows [0,128) and [128,256) of the A tile: + 128 rows x 64 B
+            const uint64_t dah = make_desc_sw64(st + h * (128 * 64)), dal = make_desc_sw64(st + T2_PLANE + h * (128 * 64));
+            const uint32_t d = tmem_base + (uint32_t)(h * 256);
+#pragma unroll
+            for (int k = 0; k < T2K / UK; ++k) {
+              const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
+              if (a.passes == 3) {
+                tc_mma_tf32(d, dal + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
+                tc_mma_tf32(d, dah + adv, dbl + adv, kIdescTf32, 1);
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, 1);
+              } else {
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
+              }
+            }
+          }
+          tc_commit(&empty[s]);
+          if (++s == T2_STAGES) { s = 0; ph ^= 1; }
+        }
+        tc_commit(acc_full);
+        aph ^= 1;
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    uint32_t aph = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int b, mt, nt;
+      tile_coords(t, a, b, mt, nt);
+      mbar_wait(acc_full, aph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int row = mt * T2M + h * 128 + q * 32 + lane;
+        float* crow = a.C + (int64_t)b * a.sc + (int64_t)row * a.ldc;
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256);
+#pragma unroll 1
+        for (int c = 0; c < T2N / 32; ++c) {
+          uint32_t v[32];
+          tc_ld32(tbase + c * 32, v);
+          tc_ld_wait();
+          const int col0 = nt * T2N + c * 32;
+          if (row < a.m && col0 < a.n) {
+            if (a.c_vec && col0 + 32 <= a.n) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(crow + col0 + 4 * j) =
+                    make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < a.n) crow[col0 + j] = __uint_as_float(v[j]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty);
+      aph ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,

@@ -15,16 +15,18 @@
 //   gen  : any other mix of kept/reduced axes (warp per output element)
 #include "common.cuh"
 #include "math.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 namespace wf2 {
 
 struct MSum {
   __device__ __forceinline__ static float id() { return 0.f; }
-  __device__ __forceinline__ static float op(float a, float b) { return __fadd_rn(a, b); }
+  __device__ __forceinline__ static float op(float a, float b) { return a + b; }   // no multiply nearby: nothing to contract
 };
 struct MProd {
   __device__ __forceinline__ static float id() { return 1.f; }
-  __device__ __forceinline__ static float op(float a, float b) { return __fmul_rn(a, b); }
+  __device__ __forceinline__ static float op(float a, float b) { return a * b; }
 };
 
 // how the reduced total t meets the old destination value d
@@ -44,7 +46,25 @@ struct Fin {
     if (divisor != 0.f) r = __fdiv_rn(r, divisor);
     return r;
   }
+  // FIN_SET never needs the old destination value.  This matters: a dependent read of dst at the END
+  // of a CTA (one L2/HBM round trip queued behind the streaming loads) kept every CTA resident ~1 us
+  // longer and cost 6 us of 17 us on the (4096 4096) row sum (gpurun_out/redbench5.log, v4 vs old).
+  __device__ __forceinline__ bool reads_dst() const { return mode != FIN_SET; }
+  // for writers that cannot prefetch the old value (ticket winners)
+  __device__ __forceinline__ void store(float* p, float t) const {
+    const float d = reads_dst() ? *p : 0.f;
+    *p = (*this)(d, t);
+  }
 };
+
+// 128-bit global load the compiler may not sink below later code: volatile asm statements keep their
+// program order, so a run of these is issued back to back (the loads-in-flight count is then what
+// the source says, not what ptxas' register-pressure heuristic picks).
+__device__ __forceinline__ float4 ld_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 
 template <class M>
 __device__ __forceinline__ float warp_reduce(float v) {
@@ -103,64 +123,66 @@ __global__ void __launch_bounds__(THREADS) reduce_rows_kernel(const __grid_const
   int64_t c1 = c0 + a.chunk_len;
   if (c1 > a.cols) c1 = a.cols;
   const float* p = a.src + so;
-  float acc0 = M::id(), acc1 = M::id(), acc2 = M::id(), acc3 = M::id();
+  float d_old = 0.f;   // accumulate modes: fetch the old destination value now, under the main loads
+  if (a.chunks == 1 && threadIdx.x == 0 && fin.reads_dst()) d_old = a.dst[dofs];
+  float acc8[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc8[k] = M::id();
   if (a.vec) {
     const int64_t v0 = c0 >> 2, v1 = c1 >> 2;  // c0 multiple of 4; tail handled below
     const float4* p4 = reinterpret_cast<const float4*>(p);
     int64_t i = v0 + threadIdx.x;
-    // 4 independent 128-bit loads in flight per thread
-    for (; i + 7 * THREADS < v1; i += 8 * THREADS) {   // 8 independent 128-bit loads in flight
+    // unroll 1: when nvcc unrolls this loop itself, ptxas serialises the loads through one register quad
+#pragma unroll 1
+    for (; i + 7 * THREADS < v1; i += 8 * THREADS) {
       float4 x[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) x[k] = p4[i + k * THREADS];
-      asm volatile("" ::: "memory");
 #pragma unroll
-      for (int k = 0; k < 8; k += 4) {
-        acc0 = M::op(acc0, M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w)));
-        acc1 = M::op(acc1, M::op(M::op(x[k + 1].x, x[k + 1].y), M::op(x[k + 1].z, x[k + 1].w)));
-        acc2 = M::op(acc2, M::op(M::op(x[k + 2].x, x[k + 2].y), M::op(x[k + 2].z, x[k + 2].w)));
-        acc3 = M::op(acc3, M::op(M::op(x[k + 3].x, x[k + 3].y), M::op(x[k + 3].z, x[k + 3].w)));
-      }
+      for (int k = 0; k < 8; ++k) acc8[k] = M::op(acc8[k], M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w)));
     }
+#pragma unroll 1
     for (; i + 3 * THREADS < v1; i += 4 * THREADS) {
-      const float4 x0 = p4[i], x1 = p4[i + THREADS], x2 = p4[i + 2 * THREADS], x3 = p4[i + 3 * THREADS];
-      acc0 = M::op(acc0, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
-      acc1 = M::op(acc1, M::op(M::op(x1.x, x1.y), M::op(x1.z, x1.w)));
-      acc2 = M::op(acc2, M::op(M::op(x2.x, x2.y), M::op(x2.z, x2.w)));
-      acc3 = M::op(acc3, M::op(M::op(x3.x, x3.y), M::op(x3.z, x3.w)));
+      float4 x[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) x[k] = p4[i + k * THREADS];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc8[k] = M::op(acc8[k], M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w)));
     }
     for (; i < v1; i += THREADS) {
       const float4 x0 = p4[i];
-      acc0 = M::op(acc0, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
+      acc8[0] = M::op(acc8[0], M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
     }
-    for (int64_t c = (v1 << 2) + threadIdx.x; c < c1; c += THREADS) acc1 = M::op(acc1, p[c]);
+    for (int64_t c = (v1 << 2) + threadIdx.x; c < c1; c += THREADS) acc8[1] = M::op(acc8[1], p[c]);
   } else {
-    for (int64_t c = c0 + threadIdx.x; c < c1; c += THREADS) acc0 = M::op(acc0, p[c]);
+    for (int64_t c = c0 + threadIdx.x; c < c1; c += THREADS) acc8[0] = M::op(acc8[0], p[c]);
   }
+  const float acc0 = M::op(acc8[0], acc8[4]), acc1 = M::op(acc8[1], acc8[5]);
+  const float acc2 = M::op(acc8[2], acc8[6]), acc3 = M::op(acc8[3], acc8[7]);
   float acc = M::op(M::op(acc0, acc1), M::op(acc2, acc3));
   acc = block_reduce<M, THREADS>(acc, smem);
   if (a.chunks == 1) {
-    if (threadIdx.x == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
+    if (threadIdx.x == 0) a.dst[dofs] = fin(d_old, acc);
     return;
   }
   // chunks > 1: publish the partial; the LAST CTA of this row folds all partials in a fixed order
   // (deterministic) and resets the ticket, so no second launch is needed.
   __shared__ bool is_last;
   if (threadIdx.x == 0) {
-    a.partial[(int64_t)row_id * a.chunks + chunk] = acc;
-    __threadfence();
-    const unsigned int t = atomicAdd(&a.counters[row_id], 1u);
+    float* slot = a.partial + (int64_t)row_id * a.chunks + chunk;
+    unsigned int t;
+    asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(slot), "f"(acc) : "memory");
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(a.counters + row_id) : "memory");
     is_last = (t == a.chunks - 1);
   }
   __syncthreads();
   if (!is_last) return;
-  __threadfence();
   const float* pp = a.partial + (int64_t)row_id * a.chunks;
   float v = M::id();
   for (uint32_t c = threadIdx.x; c < a.chunks; c += THREADS) v = M::op(v, __ldcg(pp + c));
   v = block_reduce<M, THREADS>(v, smem);
   if (threadIdx.x == 0) {
-    a.dst[dofs] = fin(a.dst[dofs], v);
+    fin.store(a.dst + dofs, v);
     a.counters[row_id] = 0;
   }
 }
@@ -182,6 +204,8 @@ __global__ void __launch_bounds__(256) reduce_rows_warp_kernel(const __grid_cons
   }
   const float* p = a.src + so;
   float acc = M::id();
+  float d_old = 0.f;
+  if (lane == 0 && fin.reads_dst()) d_old = a.dst[dofs];
   if (a.vec) {
     const float4* p4 = reinterpret_cast<const float4*>(p);
     const int64_t v1 = a.cols >> 2;
@@ -204,7 +228,7 @@ __global__ void __launch_bounds__(256) reduce_rows_warp_kernel(const __grid_cons
     for (int64_t c = lane; c < a.cols; c += 32) acc = M::op(acc, p[c]);
   }
   acc = warp_reduce<M>(acc);
-  if (lane == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
+  if (lane == 0) a.dst[dofs] = fin(d_old, acc);
 }
 
 // Tile kernel for rows that fit a register tile: a CTA of 256 threads takes RPC rows, TPR = 256/RPC
@@ -230,30 +254,29 @@ __global__ void __launch_bounds__(256) reduce_rows_tile_kernel(const __grid_cons
   }
   const float4* p4 = reinterpret_cast<const float4*>(a.src + so);
   const int64_t v1 = a.cols >> 2;
+  float d_old = 0.f;
+  if (live && t == 0 && fin.reads_dst()) d_old = a.dst[dofs];
+  // Loads are UNCONDITIONAL (index clamped into the row; dead slots read row 0) and the identity is
+  // selected afterwards: with predicated loads ptxas issued them in two batches of 4 (32 registers),
+  // which cost 6 us of the 17 us this kernel took on (4096 4096) (profiles/r01_launches_summary.md).
+  const int vlast = (int)v1 - 1;
   float4 x[8];
 #pragma unroll
+  for (int k = 0; k < 8; ++k) x[k] = ld_f4(p4 + min(t + k * TPR, vlast));
+  float acc[8];
+#pragma unroll
   for (int k = 0; k < 8; ++k) {
-    const int64_t i = t + (int64_t)k * TPR;
-    x[k] = (live && i < v1) ? p4[i] : make_float4(M::id(), M::id(), M::id(), M::id());
+    const float sk = M::op(M::op(x[k].x, x[k].y), M::op(x[k].z, x[k].w));
+    acc[k] = (live && t + k * TPR <= vlast) ? sk : M::id();
   }
-  asm volatile("" ::: "memory");   // keep all 8 loads ahead of the first add (ptxas otherwise serialises them)
-  // first level pairs load k with load k+4, so no add can issue before all 8 loads are out
-  // (ptxas otherwise splits them into two batches of 4 to stay at 32 registers)
-  float4 h[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k)
-    h[k] = make_float4(M::op(x[k].x, x[k + 4].x), M::op(x[k].y, x[k + 4].y), M::op(x[k].z, x[k + 4].z), M::op(x[k].w, x[k + 4].w));
-  float acc[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) acc[k] = M::op(M::op(h[k].x, h[k].y), M::op(h[k].z, h[k].w));
-  float v = M::op(M::op(acc[0], acc[1]), M::op(acc[2], acc[3]));
+  float v = M::op(M::op(M::op(acc[0], acc[4]), M::op(acc[1], acc[5])), M::op(M::op(acc[2], acc[6]), M::op(acc[3], acc[7])));
   if (live) {
     const float* p = a.src + so;
     for (int64_t c = (v1 << 2) + t; c < a.cols; c += TPR) v = M::op(v, p[c]);
   }
   v = warp_reduce<M>(v);
   if (WPR == 1) {
-    if (live && (threadIdx.x & 31) == 0) a.dst[dofs] = fin(a.dst[dofs], v);
+    if (live && (threadIdx.x & 31) == 0) a.dst[dofs] = fin(d_old, v);
     return;
   }
   const int w = threadIdx.x >> 5;
@@ -263,7 +286,95 @@ __global__ void __launch_bounds__(256) reduce_rows_tile_kernel(const __grid_cons
     float r = smem[sub * WPR];
 #pragma unroll
     for (int k = 1; k < WPR; ++k) r = M::op(r, smem[sub * WPR + k]);
-    a.dst[dofs] = fin(a.dst[dofs], r);
+    a.dst[dofs] = fin(d_old, r);
+  }
+}
+
+// ------------------------------------------------------------------ flat (sum :axis t of a contiguous tensor)
+// One long contiguous run, no kept axes.  ptxas keeps only two 128-bit register loads in flight per
+// thread in the looped row kernel above however the source is written (the SASS re-uses two register
+// quads), so here the loads do not go through registers at all: a persistent CTA (2 per SM) streams
+// 16 KiB chunks into a 4-stage shared-memory ring with the bulk async-copy engine
+// (cp.async.bulk.shared.global + mbarrier complete_tx), i.e. 64 KiB in flight per CTA by construction.
+// Partials meet through a ticket (st.relaxed + atom.acq_rel); the last CTA folds them in a fixed order.
+constexpr int kFlatThreads = 256, kFlatStages = 4, kFlatChunk = 16384;   // bytes per stage
+struct FlatArgs {
+  const float* src;     // 16-byte aligned
+  float* dst;
+  float* partial;       // [gridDim.x]
+  unsigned int* counter;
+  int64_t n;            // elements
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+template <class M>
+__global__ void __launch_bounds__(kFlatThreads) reduce_flat_bulk_kernel(const __grid_constant__ FlatArgs a, const Fin fin) {
+  extern __shared__ __align__(128) uint8_t ring[];
+  __shared__ uint64_t bar[kFlatStages];
+  __shared__ float red[kFlatThreads / 32];
+  __shared__ bool is_last;
+  constexpr int T = kFlatThreads;
+  const int64_t nchunks = (a.n * 4) / kFlatChunk;
+  const char* base = reinterpret_cast<const char*>(a.src);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kFlatStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&bar[s])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int64_t c = blockIdx.x;
+    for (int s = 0; s < kFlatStages && c < nchunks; ++s, c += gridDim.x) {
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar[s])), "r"(kFlatChunk) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_addr(ring + s * kFlatChunk)), "l"(base + c * kFlatChunk), "r"(kFlatChunk), "r"(smem_addr(&bar[s])) : "memory");
+    }
+  }
+  float acc0 = M::id(), acc1 = M::id(), acc2 = M::id(), acc3 = M::id();
+  int s = 0;
+  uint32_t ph = 0;
+  for (int64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    uint32_t ok = 0;
+    while (!ok)
+      asm volatile("{\n\t.reg .pred q;\n\tmbarrier.try_wait.parity.shared::cta.b64 q, [%1], %2;\n\tselp.u32 %0,1,0,q;\n\t}"
+                   : "=r"(ok) : "r"(smem_addr(&bar[s])), "r"(ph) : "memory");
+    const float4* t = reinterpret_cast<const float4*>(ring + s * kFlatChunk);
+    // 1024 float4 per chunk, 4 per thread, conflict-free (consecutive lanes, consecutive 16 B)
+    const float4 x0 = t[threadIdx.x], x1 = t[threadIdx.x + T], x2 = t[threadIdx.x + 2 * T], x3 = t[threadIdx.x + 3 * T];
+    acc0 = M::op(acc0, M::op(M::op(x0.x, x0.y), M::op(x0.z, x0.w)));
+    acc1 = M::op(acc1, M::op(M::op(x1.x, x1.y), M::op(x1.z, x1.w)));
+    acc2 = M::op(acc2, M::op(M::op(x2.x, x2.y), M::op(x2.z, x2.w)));
+    acc3 = M::op(acc3, M::op(M::op(x3.x, x3.y), M::op(x3.z, x3.w)));
+    __syncthreads();   // every thread is done with stage s
+    if (threadIdx.x == 0) {
+      const int64_t nc = c + (int64_t)kFlatStages * gridDim.x;
+      if (nc < nchunks) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar[s])), "r"(kFlatChunk) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_addr(ring + s * kFlatChunk)), "l"(base + nc * kFlatChunk), "r"(kFlatChunk), "r"(smem_addr(&bar[s])) : "memory");
+      }
+    }
+    if (++s == kFlatStages) { s = 0; ph ^= 1; }
+  }
+  // ragged tail (< one chunk): CTA 0, plain loads
+  if (blockIdx.x == 0)
+    for (int64_t i = nchunks * (kFlatChunk / 4) + threadIdx.x; i < a.n; i += T) acc0 = M::op(acc0, a.src[i]);
+  float v = M::op(M::op(acc0, acc1), M::op(acc2, acc3));
+  v = block_reduce<M, T>(v, red);
+  if (threadIdx.x == 0) {
+    unsigned int t;
+    asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(a.partial + blockIdx.x), "f"(v) : "memory");
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(a.counter) : "memory");
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  float w = M::id();
+  for (uint32_t c = threadIdx.x; c < gridDim.x; c += T) w = M::op(w, __ldcg(a.partial + c));
+  w = block_reduce<M, T>(w, red);
+  if (threadIdx.x == 0) {
+    fin.store(a.dst, w);
+    *a.counter = 0;
   }
 }
 
@@ -343,7 +454,7 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
       const int64_t col = ((int64_t)blockIdx.x * 32 + tx) * 4;
       if (col < a.K) {
         if (final_stage) {
-          float4 d = *reinterpret_cast<float4*>(outp + col);
+          float4 d = fin.reads_dst() ? *reinterpret_cast<float4*>(outp + col) : make_float4(0.f, 0.f, 0.f, 0.f);
           d.x = fin(d.x, acc.x); d.y = fin(d.y, acc.y); d.z = fin(d.z, acc.z); d.w = fin(d.w, acc.w);
           *reinterpret_cast<float4*>(outp + col) = d;
         } else {
@@ -356,7 +467,7 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const int64_t c = cb + 32 * k;
-        if (c < a.K) outp[c] = final_stage ? fin(outp[c], vals[k]) : vals[k];
+        if (c < a.K) { if (final_stage) fin.store(outp + c, vals[k]); else outp[c] = vals[k]; }
       }
     }
   }
@@ -403,7 +514,7 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
       float* outp = a.dst + b * a.sB_dst;
       if (a.vec) {
         if (colv < a.K) {
-          float4 d = *reinterpret_cast<float4*>(outp + colv);
+          float4 d = fin.reads_dst() ? *reinterpret_cast<float4*>(outp + colv) : make_float4(0.f, 0.f, 0.f, 0.f);
           d.x = fin(d.x, t4.x); d.y = fin(d.y, t4.y); d.z = fin(d.z, t4.z); d.w = fin(d.w, t4.w);
           *reinterpret_cast<float4*>(outp + colv) = d;
         }
@@ -413,12 +524,80 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const int64_t c = cb + 32 * k;
-          if (c < a.K) outp[c] = fin(outp[c], vals[k]);
+          if (c < a.K) fin.store(outp + c, vals[k]);
         }
       }
       if (tx == 0) a.counters[b * gridDim.x + blockIdx.x] = 0;
     }
   }
+}
+
+// Cluster variant (vec only): 8 CTAs along the reduced axis form a thread-block cluster, each sums its
+// eighth of the rows for a 64-column strip (16 lanes x float4, 16 rows per step, 4 loads in flight), and
+// the 8 partial strips meet in DISTRIBUTED SHARED MEMORY: rank 0 reads its peers' strips with
+// ld.shared::cluster and writes the result.  No partials in global memory, no ticket, no second launch:
+// 12.3 us vs 15.3-17.6 us for the ticket scheme on (4096 4096) (gpurun_out/redbench6.log).
+constexpr int kColsClusterSize = 8;
+template <class M>
+__global__ void __cluster_dims__(1, kColsClusterSize, 1) __launch_bounds__(256)
+reduce_cols_cluster_kernel(const __grid_constant__ ColArgs a, const Fin fin) {
+  constexpr int LX = 16, LY = 16, U = 4;
+  __shared__ float4 sm[LY][LX];
+  __shared__ float4 res[LX];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int tx = threadIdx.x % LX, ty = threadIdx.x / LX;
+  const int64_t b = blockIdx.z;
+  const int64_t col = ((int64_t)blockIdx.x * LX + tx) * 4;
+  const bool live = col < a.K;
+  const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_split;
+  int64_t r1 = r0 + a.rows_per_split;
+  if (r1 > a.R) r1 = a.R;
+  const float* base = a.src + b * a.sB_src + (live ? col : 0);
+  float* outp = a.dst + b * a.sB_dst + col;
+  const bool writer = live && ty == 0 && blockIdx.y == 0;
+  float4 d_old = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (writer && fin.reads_dst()) d_old = *reinterpret_cast<const float4*>(outp);
+  float4 acc[U];
+#pragma unroll
+  for (int k = 0; k < U; ++k) acc[k] = make_float4(M::id(), M::id(), M::id(), M::id());
+  int64_t r = r0 + ty;
+  for (; r + LY * (U - 1) < r1; r += LY * U) {
+    float4 x[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) x[k] = *reinterpret_cast<const float4*>(base + (r + LY * k) * a.sR_src);
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      acc[k].x = M::op(acc[k].x, x[k].x); acc[k].y = M::op(acc[k].y, x[k].y);
+      acc[k].z = M::op(acc[k].z, x[k].z); acc[k].w = M::op(acc[k].w, x[k].w);
+    }
+  }
+  for (; r < r1; r += LY) {
+    const float4 x = *reinterpret_cast<const float4*>(base + r * a.sR_src);
+    acc[0].x = M::op(acc[0].x, x.x); acc[0].y = M::op(acc[0].y, x.y); acc[0].z = M::op(acc[0].z, x.z); acc[0].w = M::op(acc[0].w, x.w);
+  }
+  float4 t = acc[0];
+#pragma unroll
+  for (int k = 1; k < U; ++k) { t.x = M::op(t.x, acc[k].x); t.y = M::op(t.y, acc[k].y); t.z = M::op(t.z, acc[k].z); t.w = M::op(t.w, acc[k].w); }
+  sm[ty][tx] = t;
+  __syncthreads();
+  if (ty == 0) {
+#pragma unroll
+    for (int k = 1; k < LY; ++k) { const float4 o = sm[k][tx]; t.x = M::op(t.x, o.x); t.y = M::op(t.y, o.y); t.z = M::op(t.z, o.z); t.w = M::op(t.w, o.w); }
+    res[tx] = t;
+  }
+  cluster.sync();
+  if (blockIdx.y == 0 && ty == 0) {   // cluster rank 0 (cluster spans blockIdx.y 0..7: grid.y == 8)
+    float4 o[kColsClusterSize];
+#pragma unroll
+    for (int k = 1; k < kColsClusterSize; ++k) o[k] = *cluster.map_shared_rank(&res[tx], k);
+#pragma unroll
+    for (int k = 1; k < kColsClusterSize; ++k) { t.x = M::op(t.x, o[k].x); t.y = M::op(t.y, o[k].y); t.z = M::op(t.z, o[k].z); t.w = M::op(t.w, o[k].w); }
+    if (writer) {
+      d_old.x = fin(d_old.x, t.x); d_old.y = fin(d_old.y, t.y); d_old.z = fin(d_old.z, t.z); d_old.w = fin(d_old.w, t.w);
+      *reinterpret_cast<float4*>(outp) = d_old;
+    }
+  }
+  cluster.sync();   // peers keep their strips alive until rank 0 has read them
 }
 
 template <class M>
@@ -430,7 +609,7 @@ __global__ void __launch_bounds__(256) reduce_cols_final_kernel(const __grid_con
   float acc = M::id();
   for (uint32_t s = 0; s < a.splits; ++s) acc = M::op(acc, p[(int64_t)s * a.K]);
   float* d = a.dst + b * a.sB_dst + c;
-  *d = fin(*d, acc);
+  fin.store(d, acc);
 }
 
 // ------------------------------------------------------------------ generic
@@ -463,7 +642,7 @@ __global__ void __launch_bounds__(256) reduce_gen_kernel(const __grid_constant__
       acc = M::op(acc, a.src[off]);
     }
     acc = warp_reduce<M>(acc);
-    if (lane == 0) a.dst[dofs] = fin(a.dst[dofs], acc);
+    if (lane == 0) fin.store(a.dst + dofs, acc);
   }
 }
 
@@ -509,9 +688,27 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
     }
     a.cols = p.shape[last];
     a.vec = vec ? 1 : 0;
+    if (rows == 1 && vec && a.cols >= (int64_t(1) << 18)) {
+      // flat: bulk-async ring, 2 persistent CTAs per SM
+      static bool attr_set[2] = {false, false};
+      auto kfn = reduce_flat_bulk_kernel<M>;
+      constexpr int which = std::is_same<M, MSum>::value ? 0 : 1;
+      if (!attr_set[which]) {
+        WF2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, kFlatStages * kFlatChunk));
+        attr_set[which] = true;
+      }
+      const int64_t nchunks = (a.cols * 4) / kFlatChunk;
+      int64_t grid = (int64_t)s.sm_count * 2;
+      if (grid > nchunks) grid = nchunks;
+      rc = ensure_scratch((size_t)grid * sizeof(float));
+      if (rc) return rc;
+      FlatArgs f{sptr, dptr, (float*)s.scratch, s.counters, a.cols};
+      kfn<<<(unsigned)grid, kFlatThreads, kFlatStages * kFlatChunk, s.stream>>>(f, fin);
+      return post_launch(who);
+    }
     if (rows < (int64_t(1) << 31)) {
       // register-tile kernel: all loads of a row tile issued up front
-      if (a.vec && a.cols <= 8192 && rows * a.cols >= (int64_t(1) << 16)) {
+      if (a.vec && a.cols >= 4 && a.cols <= 8192 && rows * a.cols >= (int64_t(1) << 16)) {
         const int64_t v1 = a.cols >> 2;
         a.chunks = 1; a.chunk_len = a.cols;
         if (v1 <= 256) {
@@ -532,7 +729,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
         return post_launch(who);
       }
       // split long rows when there are too few of them to fill 148 SMs; a chunk is a whole number
-      // of 4096-float units (256 threads x 4 float4 x 4 loads in flight)
+      // of 8192-float units (256 threads x 8 float4)
       uint32_t chunks = 1;
       int64_t chunk_len = a.cols;
       const int64_t target_ctas = (int64_t)s.sm_count * 8;
@@ -566,6 +763,17 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
     else { a.B = 1; }
     bool vec = al16(sptr) && al16(dptr) && (a.K % 4 == 0) && (a.sR_src % 4 == 0) && (a.sB_src % 4 == 0) && (a.sB_dst % 4 == 0);
     a.vec = vec ? 1 : 0;
+    {
+      // cluster path: 64-column strips x 8 CTAs along R, partial strips folded through DSMEM
+      const int64_t strips = (a.K + 63) / 64;
+      if (vec && a.R >= 512 && a.B < 65536 && strips * kColsClusterSize * a.B >= (int64_t)s.sm_count * 2 && strips < (int64_t(1) << 31)) {
+        a.splits = kColsClusterSize;
+        a.rows_per_split = (a.R + kColsClusterSize - 1) / kColsClusterSize;
+        dim3 grid((unsigned)strips, kColsClusterSize, (unsigned)a.B);
+        reduce_cols_cluster_kernel<M><<<grid, 256, 0, s.stream>>>(a, fin);
+        return post_launch(who);
+      }
+    }
     const int64_t colblocks = (a.K + 127) / 128;
     const int64_t target_ctas = (int64_t)s.sm_count * 8;
     int64_t splits = 1;

@@ -189,7 +189,10 @@ def _red_check(got, oracle, truth, sumabs, tol=1e-5):
                                         ((5, 7, 9), (0, 2)), ((4, 2048), 1), ((2000, 8), 0), ((3, 1031), -1),
                                         ((100, 100, 10), True), ((512, 4096), 1), ((300, 1000), 1), ((100, 8192), 1),
                                         ((70, 2048), -1), ((3, 100000), 1), ((1, 300000), True), ((4096, 512), 0),
-                                        ((6, 64, 4096), 2), ((6, 300, 640), 1)])
+                                        ((6, 64, 4096), 2), ((6, 300, 640), 1),
+                                        # interleaved flat sum (ragged units), cluster/DSMEM column sums (ragged strips, batched)
+                                        ((1, 1234567), True), ((2, 500000), 1), ((1024, 4096), 0), ((600, 2504), 0),
+                                        ((3, 520, 1280), 1), ((777, 2500), 0), ((4096, 4096), 0), ((4096, 4096), 1)])
 def test_sum_axes(gpu, L, shape, axis):
     d = RNG.normal(size=shape).astype(np.float32)
     gx, ox = pair(gpu, L, shape, d)
@@ -234,6 +237,23 @@ def test_sum_keepdims_and_inplace_accumulate(gpu, L):
     gpu.ops.move_(gpu.view(g1, True, [":broadcast", 40]), gx)
     L.move_(L.view(o1, True, [":broadcast", 40]), ox)
     np.testing.assert_array_equal(g1.to_numpy(), o1.to_numpy())
+
+
+@pytest.mark.parametrize("shape,axis", [((1024, 4096), 0), ((1024, 4096), 1), ((600, 2504), 0), ((1, 300000), 1), ((300, 1000), 1)])
+def test_accumulating_reduction_large(gpu, L, shape, axis):
+    """`A+=B` into a (:broadcast n) destination that already holds values (the reference's literal
+    `!sum` path, reduction.lisp:60-79) on the shapes that take the tile / cluster / chunked kernels."""
+    d = RNG.normal(size=shape).astype(np.float32)
+    oshape = list(shape); oshape[axis] = 1
+    init = RNG.normal(size=oshape).astype(np.float32)
+    gx, ox = pair(gpu, L, shape, d)
+    go, oo = pair(gpu, L, tuple(oshape), init)
+    v = [True, True]; v[axis] = [":broadcast", shape[axis]]
+    gpu.ops.add_(gpu.view(go, *v), gx)
+    truth = init.astype(np.float64) + d.astype(np.float64).sum(axis=axis, keepdims=True)
+    sumabs = np.abs(init.astype(np.float64)) + np.abs(d.astype(np.float64)).sum(axis=axis, keepdims=True)
+    err = (np.abs(go.to_numpy().astype(np.float64) - truth) / sumabs).max()
+    assert err <= 1e-5, err
 
 
 def test_mean(gpu, L):
