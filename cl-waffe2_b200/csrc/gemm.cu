@@ -10,6 +10,8 @@
 //                  the tensor path does not take (tiny / unaligned shapes such as the 10-wide
 //                  classifier head).
 #include "common.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 namespace wf2 {
 
@@ -110,6 +112,168 @@ __global__ void __launch_bounds__(256) sgemm_simt_kernel(const __grid_constant__
   }
 }
 
+// ------------------------------------------------------------------ small / skinny problems: 64x64 tiles, cluster split-K
+// The MLP training step (BASELINE config 4) is made of GEMMs with 4..64 output tiles — (1024 x 256 x 784),
+// (256 x 256 x 1024), (10 x 256 x 1024) ... — which left 140 of 148 SMs idle in the kernels above (170 us
+// for the 10 x 256 x 1024 weight gradient on 2 CTAs, profiles/r01_mlp_launches_before.md).  Here a tile
+// is 64 x 64 (4 x 4 per thread) and the K axis is split over a THREAD-BLOCK CLUSTER of up to 8 CTAs:
+// every CTA accumulates its K slice, parks the partial tile in shared memory, and after one
+// cluster barrier each CTA sums one strip of the tile over all peers through distributed shared
+// memory, in slice order (deterministic), and writes C.  No partials in global memory, no atomics.
+constexpr int SBM = 64, SBN = 64, SBK = 16, SSTAGES = 4;
+constexpr int SLD = SBM + 4;                       // padded row of a staged k-slice
+constexpr int STAGE_FLOATS = 2 * SBK * SLD;        // A slice + B slice
+
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  const int n = valid ? 4 : 0;                     // src-size 0: the 4 bytes are zero-filled, nothing is read
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+
+__global__ void __launch_bounds__(256) sgemm_splitk_kernel(const __grid_constant__ GemmArgs g, const int ksplit, const int64_t kchunk) {
+  // 4-stage cp.async ring of k-slices (A as [k][m], B as [k][n]); after the main loop the same storage
+  // holds this CTA's 64 x 64 partial tile for the cluster fold.
+  __shared__ __align__(16) float ring[SSTAGES * STAGE_FLOATS];
+  static_assert(SSTAGES * STAGE_FLOATS >= SBM * SBN, "partial tile must fit the ring");
+  const int ks = (int)(blockIdx.z % ksplit);
+  const int64_t b = blockIdx.z / ksplit;
+  const float* A = g.A + b * g.sa;
+  const float* B = g.B + b * g.sb;
+  float* C = g.C + b * g.sc;
+  const int64_t m0 = (int64_t)blockIdx.y * SBM, n0 = (int64_t)blockIdx.x * SBN;
+  const int64_t kbeg = (int64_t)ks * kchunk;
+  const int64_t kend = kbeg + kchunk < g.k ? kbeg + kchunk : g.k;
+  const int nkb = kend > kbeg ? (int)((kend - kbeg + SBK - 1) / SBK) : 0;
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;           // 16 x 16 threads, 4 x 4 outputs each
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  // Each thread copies 4 elements of A and 4 of B per k-slice, 4 bytes at a time (no alignment
+  // demands on lda/ldb/offsets), coalesced along the operand's contiguous axis.
+  const float* pa[4]; const float* pb[4];
+  int oa[4], ob[4], ka[4], kb_[4];
+  bool va[4], vb[4];
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int e = tid + it * 256;
+    int kk, mm;
+    if (!g.ta) { kk = e & (SBK - 1); mm = e >> 4; } else { mm = e & (SBM - 1); kk = e >> 6; }
+    const int64_t gm = m0 + mm;
+    va[it] = gm < g.m; ka[it] = kk; oa[it] = kk * SLD + mm;
+    pa[it] = va[it] ? (g.ta ? A + (kbeg + kk) * g.lda + gm : A + gm * g.lda + kbeg + kk) : A;
+    int kb, nn;
+    if (!g.tb) { nn = e & (SBN - 1); kb = e >> 6; } else { kb = e & (SBK - 1); nn = e >> 4; }
+    const int64_t gn = n0 + nn;
+    vb[it] = gn < g.n; kb_[it] = kb; ob[it] = SBK * SLD + kb * SLD + nn;
+    pb[it] = vb[it] ? (g.tb ? B + gn * g.ldb + kbeg + kb : B + (kbeg + kb) * g.ldb + gn) : B;
+  }
+  const int64_t stepa = g.ta ? (int64_t)SBK * g.lda : SBK, stepb = g.tb ? SBK : (int64_t)SBK * g.ldb;
+  auto issue = [&](int blk) {
+    float* st = ring + (blk % SSTAGES) * STAGE_FLOATS;
+    const int64_t k0 = kbeg + (int64_t)blk * SBK;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const bool oka = va[it] && k0 + ka[it] < kend, okb = vb[it] && k0 + kb_[it] < kend;
+      cp_async4(st + oa[it], oka ? pa[it] + blk * stepa : A, oka);
+      cp_async4(st + ob[it], okb ? pb[it] + blk * stepb : B, okb);
+    }
+  };
+#pragma unroll
+  for (int sgs = 0; sgs < SSTAGES - 1; ++sgs) {
+    if (sgs < nkb) issue(sgs);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (int blk = 0; blk < nkb; ++blk) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(SSTAGES - 2) : "memory");
+    __syncthreads();                                // slice blk has landed; slice blk-1's stage is free
+    if (blk + SSTAGES - 1 < nkb) issue(blk + SSTAGES - 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    const float* as = ring + (blk % SSTAGES) * STAGE_FLOATS;
+    const float* bs = as + SBK * SLD;
+#pragma unroll
+    for (int kk = 0; kk < SBK; ++kk) {
+      const float4 a4 = *reinterpret_cast<const float4*>(as + kk * SLD + ty * 4);
+      const float4 b4 = *reinterpret_cast<const float4*>(bs + kk * SLD + tx * 4);
+      const float a[4] = {a4.x, a4.y, a4.z, a4.w}, bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+  }
+
+  if (ksplit == 1) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t gm = m0 + ty * 4 + i;
+      if (gm >= g.m) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int64_t gn = n0 + tx * 4 + j;
+        if (gn < g.n) C[gm * g.ldc + gn] = acc[i][j];
+      }
+    }
+    return;
+  }
+  // ---- split-K: partial tile -> shared memory, fold across the cluster through DSMEM
+  cg::cluster_group cluster = cg::this_cluster();
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();                                  // everyone is done reading the ring
+  float (*Ps)[SBN] = reinterpret_cast<float (*)[SBN]>(ring);
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    *reinterpret_cast<float4*>(&Ps[ty * 4 + i][tx * 4]) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  cluster.sync();
+  const int rows_per = SBM / ksplit;                // this CTA folds rows [ks*rows_per, (ks+1)*rows_per)
+  for (int e = tid; e < rows_per * (SBN / 4); e += 256) {
+    const int r = ks * rows_per + e / (SBN / 4), c4 = (e % (SBN / 4)) * 4;
+    float4 t = *reinterpret_cast<const float4*>(cluster.map_shared_rank(&Ps[r][c4], 0));
+    for (int p = 1; p < ksplit; ++p) {
+      const float4 o = *reinterpret_cast<const float4*>(cluster.map_shared_rank(&Ps[r][c4], p));
+      t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w;
+    }
+    const int64_t gm = m0 + r, gn = n0 + c4;
+    if (gm < g.m) {
+      float* cp = C + gm * g.ldc + gn;
+      const float v[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (gn + j < g.n) cp[j] = v[j];
+    }
+  }
+  cluster.sync();                                   // nobody leaves while a peer may still read its tile
+}
+
+// 0 = not taken.  Picks the cluster split-K kernel when the 128x128 grid would leave most SMs idle.
+static int sgemm_small_try(const GemmArgs& g, int64_t batch) {
+  const int64_t big_tiles = ((g.m + BM - 1) / BM) * ((g.n + BN - 1) / BN) * batch;
+  if (big_tiles >= S().sm_count) return 0;
+  const int64_t tiles = ((g.m + SBM - 1) / SBM) * ((g.n + SBN - 1) / SBN);
+  if (batch * 8 >= 65536) return 0;
+  int ksplit = 1;
+  while (ksplit < 8 && tiles * batch * ksplit * 2 <= (int64_t)S().sm_count * 2 && g.k / (ksplit * 2) >= 32) ksplit *= 2;
+  int64_t kchunk = (g.k + ksplit - 1) / ksplit;
+  kchunk = (kchunk + SBK - 1) / SBK * SBK;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)((g.n + SBN - 1) / SBN), (unsigned)((g.m + SBM - 1) / SBM), (unsigned)(batch * ksplit));
+  cfg.blockDim = dim3(256, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = S().stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)ksplit;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, sgemm_splitk_kernel, g, ksplit, kchunk);
+  if (e != cudaSuccess) return -cuda_fail(e, "cudaLaunchKernelEx(sgemm_splitk_kernel)", __FILE__, __LINE__);
+  const int rc = post_launch("wf2cu_gemm(simt split-k)");
+  return rc ? -rc : 1;
+}
+
 }  // namespace wf2
 
 using namespace wf2;
@@ -144,6 +308,11 @@ int wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const 
   }
   WF2_CHECK(batch < 65536, "wf2cu_gemm: batch %lld too large for the SIMT path", (long long)batch);
   GemmArgs g{a, b, c, m, n, k, lda, ldb, ldc, stride_a, stride_b, stride_c, trans_a ? 1 : 0, trans_b ? 1 : 0};
+  {
+    const int r = sgemm_small_try(g, batch);
+    if (r < 0) return -r;
+    if (r == 1) return 0;
+  }
   dim3 grid((unsigned)((n + BN - 1) / BN), (unsigned)((m + BM - 1) / BM), (unsigned)batch);
   sgemm_simt_kernel<<<grid, 256, 0, S().stream>>>(g);
   return post_launch("wf2cu_gemm(simt)");

@@ -569,7 +569,9 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   if (mode == 0) {
     // the tensor path pays two extra passes over the operands and wants >= 1 wave of 128x256 tiles
     if (m < 64 || n < 64 || k < 32) return 0;
-    if (2.0 * (double)m * (double)n * (double)k * (double)batch < 2.5e8) return 0;
+    // below ~1 GFLOP the cluster split-K fp32 kernel (gemm.cu) wins: 21 us vs 35 us on (1024 256 784),
+    // 15 us vs 26 us on 512^3; above it the tensor path does: 44 us vs 87 us on 1024^3 (gpurun_out/gemm_small2.log)
+    if (2.0 * (double)m * (double)n * (double)k * (double)batch < 1.0e9) return 0;
   }
   if (!g_encode) {
     void* fn = nullptr;
