@@ -476,7 +476,7 @@ def run_ours(args):
     if args.mlp:
         try:
             mlp_mod = importlib.import_module("cl-waffe2_b200.mlp_bench")
-            mlp = mlp_mod.run(wf, dist, rank, world, steps=args.mlp_steps, warmup=args.mlp_warmup)
+            mlp = mlp_mod.run(wf, dist, rank, world, steps=args.mlp_steps, warmup=args.mlp_warmup, exchange=args.exchange)
         except ModuleNotFoundError:
             mlp = {"unavailable": "MLP training step not built yet"}
 
@@ -544,6 +544,8 @@ def main():
     ap.add_argument("--mlp", type=int, default=1)
     ap.add_argument("--gemm", type=int, default=1)
     ap.add_argument("--gpt2", type=int, default=1)
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N>1 gradient exchange: p2p = fused peer-memory allreduce+Adam kernel, nccl = ncclAllReduce + Adam")
     ap.add_argument("--mlp-steps", type=int, default=200)
     ap.add_argument("--mlp-warmup", type=int, default=20)
     args = ap.parse_args()

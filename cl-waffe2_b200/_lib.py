@@ -57,6 +57,9 @@ PROTOTYPES = {
     "wf2cu_embedding_gather": [vp, i64, i64, vp, vp, i64, vp],
     "wf2cu_comm_unique_id": [vp], "wf2cu_comm_init": [i32, i32, vp],
     "wf2cu_allreduce_sum_f32": [vp, i64, i64], "wf2cu_comm_destroy": [],
+    "wf2cu_p2p_export": [vp, vp], "wf2cu_p2p_signal_export": [vp], "wf2cu_p2p_attach": [i32, i32, vp, vp, vp, vp, vp],
+    "wf2cu_p2p_allreduce_adam_step": [vp, i64, i64, vp, i64, vp, i64, i64, f32, vp, f32, f32, f32],
+    "wf2cu_p2p_status": [C.POINTER(i32)], "wf2cu_p2p_detach": [],
 }
 
 # enums of include/waffe2cuda.h

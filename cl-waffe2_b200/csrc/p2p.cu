@@ -1,0 +1,284 @@
+// p2p.cu — the data-parallel step's exchange + optimizer as ONE kernel over NVLink peer memory.
+//
+// after backward every rank holds the gradient bucket of its batch shard; the global step
+// is allreduce(sum) x 1/world, then the identical Adam update on every rank.  The NCCL route
+// (comm.cu) is a collective launch followed by the optimizer launch.  Here every rank maps its peers'
+// gradient arenas (CUDA IPC, one process per GPU; NVSwitch gives each pair full bandwidth), and one
+// kernel per rank
+//   1. tells its peers "my gradients are complete" and waits for theirs  (st.release.sys / ld.acquire.sys
+//      on a small signal page in each rank's memory),
+//   2. owns shard `rank` of the bucket (1/world of it): reads that shard from ALL ranks' arenas with
+//      128-bit loads over NVLink, sums in rank order, scales by 1/world, applies Adam with its own
+//      m/v shard (optimizer state and optimizer math are sharded world ways), and stores the updated
+//      parameters into EVERY replica's parameter arena (remote 128-bit stores) — reduce-scatter,
+//      optimizer and all-gather in one pass, 2 x 1/world of the bucket per rank over NVLink
+//      (0.27 MB at N = 8 instead of the 7.5 MB a read-everything scheme moves),
+//   3. tells its peers "my shard is written, I am done reading" and waits for theirs, so the next
+//      forward sees the new parameters and the next backward may overwrite the gradient arena.
+// Each element is computed by exactly one rank and copied, so the replicas stay bit-identical.
+// The reference has no distributed code; this file is new work.
+#include "common.cuh"
+
+namespace wf2 {
+
+constexpr int kMaxPeers = 8;
+constexpr unsigned long long kSpinLimitNs = 2000000000ull;   // 2 s: a lost peer must not hang the GPU
+
+struct SignalPage {                 // lives in each rank's device memory, written by its peers
+  uint32_t ready[16];               // ready[r] = epoch for which rank r's gradients are complete
+  uint32_t done[16];                // done[r]  = epoch for which rank r has finished reading my arena
+};
+
+struct P2PState {
+  int rank = -1, world = 0;
+  void* peer_grad_base[kMaxPeers] = {};     // mapped allocation bases (self: the local pointer)
+  void* peer_param_base[kMaxPeers] = {};
+  bool opened_param[kMaxPeers] = {};
+  SignalPage* peer_signal[kMaxPeers] = {};
+  bool opened_grad[kMaxPeers] = {}, opened_signal[kMaxPeers] = {};
+  SignalPage* my_signal = nullptr;
+  uint32_t* local = nullptr;                // [0] epoch, [1] ticket, [2] timeout flag
+};
+static P2PState g_p2p;
+
+struct P2PArgs {
+  float* param; float* m; float* v;
+  const float* lr_dev;
+  float lr_t, b1, b2, eps, gscale;
+  int64_t n;                                // elements (the arenas are padded to a multiple of 4)
+  int world, rank;
+  const float* grads[kMaxPeers];
+  float* params[kMaxPeers];                 // every replica's parameter arena (params[rank] == param)
+  SignalPage* signals[kMaxPeers];
+  uint32_t* local;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// wait until *p has reached epoch e (wrap-safe); false on timeout
+__device__ __forceinline__ bool wait_epoch(const uint32_t* p, uint32_t e) {
+  const unsigned long long t0 = now_ns();
+  while ((int32_t)(ld_acquire_sys(p) - e) < 0) {
+    if (now_ns() - t0 > kSpinLimitNs) return false;
+    __nanosleep(64);
+  }
+  return true;
+}
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+  float4 v;   // L1 no-allocate: every line is read once, and a stale line must never be served next step
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ float adam_one(float gi, float& m, float& v, float p, float lr_t, float omb1, float omb2, float eps) {
+  // exactly adam_kernel (misc.cu), i.e. optimizers/impls/adam.lisp:45-67
+  const float mi = __fadd_rn(m, __fmul_rn(__fsub_rn(gi, m), omb1));
+  const float vi = __fadd_rn(v, __fmul_rn(omb2, __fsub_rn(__fmul_rn(gi, gi), v)));
+  m = mi; v = vi;
+  return __fsub_rn(p, __fdiv_rn(__fmul_rn(mi, lr_t), __fadd_rn(eps, __fsqrt_rn(vi))));
+}
+
+__global__ void __launch_bounds__(256) allreduce_adam_kernel(const __grid_constant__ P2PArgs a) {
+  __shared__ uint32_t epoch_s;
+  __shared__ int ok_s;
+  __shared__ bool last_s;
+  if (threadIdx.x == 0) { epoch_s = a.local[0] + 1; ok_s = 1; }
+  __syncthreads();
+  const uint32_t e = epoch_s;
+  // ---- 1. gradients complete everywhere?  (the kernel follows this rank's backward in stream order)
+  if (blockIdx.x == 0 && threadIdx.x < a.world) st_release_sys(&a.signals[threadIdx.x]->ready[a.rank], e);
+  if (threadIdx.x < a.world)
+    if (!wait_epoch(&a.signals[a.rank]->ready[threadIdx.x], e)) { ok_s = 0; a.local[2] = 1; }
+  __syncthreads();
+  // ---- 2. my shard: sum over ranks in rank order, x 1/world, Adam, parameters out to every replica
+  if (ok_s) {
+    const float lr_t = a.lr_dev ? *a.lr_dev : a.lr_t;
+    const float omb1 = __fsub_rn(1.0f, a.b1), omb2 = __fsub_rn(1.0f, a.b2);
+    const int64_t n4 = (a.n + 3) >> 2;
+    const int64_t per = (n4 + a.world - 1) / a.world;
+    const int64_t lo = per * a.rank, hi = lo + per < n4 ? lo + per : n4;
+    const int64_t stride = (int64_t)gridDim.x * 256;
+    for (int64_t base = lo + (int64_t)blockIdx.x * 256; base < hi; base += stride) {   // uniform trip count per CTA
+      const int64_t i = base + threadIdx.x;
+      const bool live = i < hi;
+      float4 x[kMaxPeers];
+#pragma unroll
+      for (int r = 0; r < kMaxPeers; ++r)
+        if (r < a.world && live) x[r] = ld_peer(reinterpret_cast<const float4*>(a.grads[r]) + i);
+      // All remote loads are issued before the barrier and consumed after it, so the (up to 8) NVLink
+      // round trips of a thread overlap instead of being serialised by the register allocator.
+      __syncthreads();
+      if (live) {
+        float4 g = x[0];
+#pragma unroll
+        for (int r = 1; r < kMaxPeers; ++r)
+          if (r < a.world) { g.x = __fadd_rn(g.x, x[r].x); g.y = __fadd_rn(g.y, x[r].y); g.z = __fadd_rn(g.z, x[r].z); g.w = __fadd_rn(g.w, x[r].w); }
+        if (a.gscale != 1.0f) { g.x = __fmul_rn(g.x, a.gscale); g.y = __fmul_rn(g.y, a.gscale); g.z = __fmul_rn(g.z, a.gscale); g.w = __fmul_rn(g.w, a.gscale); }
+        float4 m = reinterpret_cast<float4*>(a.m)[i], v = reinterpret_cast<float4*>(a.v)[i], p = reinterpret_cast<float4*>(a.param)[i];
+        p.x = adam_one(g.x, m.x, v.x, p.x, lr_t, omb1, omb2, a.eps);
+        p.y = adam_one(g.y, m.y, v.y, p.y, lr_t, omb1, omb2, a.eps);
+        p.z = adam_one(g.z, m.z, v.z, p.z, lr_t, omb1, omb2, a.eps);
+        p.w = adam_one(g.w, m.w, v.w, p.w, lr_t, omb1, omb2, a.eps);
+        reinterpret_cast<float4*>(a.m)[i] = m; reinterpret_cast<float4*>(a.v)[i] = v;
+#pragma unroll
+        for (int r = 0; r < kMaxPeers; ++r)
+          if (r < a.world) reinterpret_cast<float4*>(a.params[r])[i] = p;
+      }
+    }
+  }
+  // ---- 3. last CTA of this rank: "shard written, done reading" to everyone, wait for everyone, advance the epoch
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();          // this CTA's remote parameter stores are ordered before its ticket
+    const unsigned int t = atomicAdd(&a.local[1], 1u);
+    last_s = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last_s) return;
+  __threadfence_system();            // ... and all CTAs' stores before the done flags below
+  if (threadIdx.x < a.world) st_release_sys(&a.signals[threadIdx.x]->done[a.rank], e);
+  if (threadIdx.x < a.world)
+    if (!wait_epoch(&a.signals[a.rank]->done[threadIdx.x], e)) a.local[2] = 1;
+  __syncthreads();
+  if (threadIdx.x == 0) { a.local[1] = 0; a.local[0] = e; }
+}
+
+static void p2p_close() {
+  P2PState& p = g_p2p;
+  for (int r = 0; r < kMaxPeers; ++r) {
+    if (p.opened_grad[r]) cudaIpcCloseMemHandle(p.peer_grad_base[r]);
+    if (p.opened_param[r]) cudaIpcCloseMemHandle(p.peer_param_base[r]);
+    if (p.opened_signal[r]) cudaIpcCloseMemHandle(p.peer_signal[r]);
+    p.opened_grad[r] = p.opened_signal[r] = p.opened_param[r] = false;
+    p.peer_grad_base[r] = nullptr; p.peer_signal[r] = nullptr; p.peer_param_base[r] = nullptr;
+  }
+  p.rank = -1; p.world = 0;
+}
+
+}  // namespace wf2
+
+using namespace wf2;
+
+extern "C" {
+
+int wf2cu_p2p_export(void* dev_alloc, void* handle64) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(dev_alloc && handle64, "wf2cu_p2p_export: null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+  cudaIpcMemHandle_t h;
+  WF2_CUDA(cudaIpcGetMemHandle(&h, dev_alloc));
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+
+int wf2cu_p2p_signal_export(void* handle64) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(handle64, "wf2cu_p2p_signal_export: null argument");
+  P2PState& p = g_p2p;
+  if (!p.my_signal) {
+    WF2_CUDA(cudaMalloc(&p.my_signal, 4096));
+    WF2_CUDA(cudaMemset(p.my_signal, 0, 4096));
+    WF2_CUDA(cudaMalloc(&p.local, 256));
+    WF2_CUDA(cudaMemset(p.local, 0, 256));
+  }
+  cudaIpcMemHandle_t h;
+  WF2_CUDA(cudaIpcGetMemHandle(&h, p.my_signal));
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+
+int wf2cu_p2p_attach(int rank, int world, void* local_grad_alloc, void* local_param_alloc, const void* grad_handles,
+                     const void* param_handles, const void* signal_handles) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "wf2cu_p2p_attach: bad rank/world (%d/%d, at most %d peers)", rank, world, kMaxPeers);
+  WF2_CHECK(local_grad_alloc && local_param_alloc && grad_handles && param_handles && signal_handles, "wf2cu_p2p_attach: null argument");
+  P2PState& p = g_p2p;
+  if (p.world) return set_error(WF2CU_ERR_COMM, "wf2cu_p2p_attach: already attached (call wf2cu_p2p_detach)");
+  if (!p.my_signal) return set_error(WF2CU_ERR_COMM, "wf2cu_p2p_attach: call wf2cu_p2p_signal_export first");
+  // a fresh attachment starts at epoch 0 on every rank
+  WF2_CUDA(cudaMemset(p.my_signal, 0, 4096));
+  WF2_CUDA(cudaMemset(p.local, 0, 256));
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) { p.peer_grad_base[r] = local_grad_alloc; p.peer_param_base[r] = local_param_alloc; p.peer_signal[r] = p.my_signal; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)grad_handles + 64 * r, 64);
+    cudaError_t e = cudaIpcOpenMemHandle(&p.peer_grad_base[r], h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { p2p_close(); return cuda_fail(e, "cudaIpcOpenMemHandle(gradient arena)", __FILE__, __LINE__); }
+    p.opened_grad[r] = true;
+    memcpy(&h, (const char*)param_handles + 64 * r, 64);
+    e = cudaIpcOpenMemHandle(&p.peer_param_base[r], h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { p2p_close(); return cuda_fail(e, "cudaIpcOpenMemHandle(parameter arena)", __FILE__, __LINE__); }
+    p.opened_param[r] = true;
+    memcpy(&h, (const char*)signal_handles + 64 * r, 64);
+    void* sp = nullptr;
+    e = cudaIpcOpenMemHandle(&sp, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { p2p_close(); return cuda_fail(e, "cudaIpcOpenMemHandle(signal page)", __FILE__, __LINE__); }
+    p.peer_signal[r] = (SignalPage*)sp;
+    p.opened_signal[r] = true;
+  }
+  p.rank = rank; p.world = world;
+  WF2_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int wf2cu_p2p_allreduce_adam_step(void* param, int64_t p_off, int64_t g_off, void* m, int64_t m_off, void* v, int64_t v_off,
+                                  int64_t n, float lr_t, const void* lr_t_dev, float beta1, float beta2, float eps) {
+  WF2_REQUIRE_INIT();
+  P2PState& p = g_p2p;
+  if (!p.world) return set_error(WF2CU_ERR_COMM, "wf2cu_p2p_allreduce_adam_step: not attached (call wf2cu_p2p_attach)");
+  WF2_CHECK(param && m && v && n >= 0, "wf2cu_p2p_allreduce_adam_step: bad arguments");
+  WF2_CHECK(((p_off | g_off | m_off | v_off) & 3) == 0, "wf2cu_p2p_allreduce_adam_step: offsets must be multiples of 4 elements");
+  if (n == 0) return 0;
+  P2PArgs a;
+  memset(&a, 0, sizeof(a));
+  a.param = (float*)param + p_off; a.m = (float*)m + m_off; a.v = (float*)v + v_off;
+  a.lr_dev = (const float*)lr_t_dev; a.lr_t = lr_t; a.b1 = beta1; a.b2 = beta2; a.eps = eps;
+  a.gscale = 1.0f / (float)p.world;
+  a.n = n; a.world = p.world; a.rank = p.rank;
+  for (int r = 0; r < p.world; ++r) {
+    a.grads[r] = (const float*)p.peer_grad_base[r] + g_off; a.params[r] = (float*)p.peer_param_base[r] + p_off;
+    a.signals[r] = p.peer_signal[r];
+  }
+  if (a.params[p.rank] != a.param) return set_error(WF2CU_ERR_INVALID, "wf2cu_p2p_allreduce_adam_step: param is not the arena given to wf2cu_p2p_attach");
+  a.local = p.local;
+  const int64_t n4 = (n + 3) >> 2;
+  const int64_t per = (n4 + p.world - 1) / p.world;
+  int64_t grid = (per + 255) / 256;
+  const int64_t cap = (int64_t)S().sm_count * 4;
+  if (grid > cap) grid = cap;
+  allreduce_adam_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(a);
+  return post_launch("wf2cu_p2p_allreduce_adam_step");
+}
+
+int wf2cu_p2p_status(int* timed_out) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(timed_out, "wf2cu_p2p_status: null out");
+  *timed_out = 0;
+  if (!g_p2p.local) return 0;
+  uint32_t flag = 0;
+  WF2_CUDA(cudaStreamSynchronize(S().stream));
+  WF2_CUDA(cudaMemcpy(&flag, g_p2p.local + 2, 4, cudaMemcpyDeviceToHost));
+  *timed_out = (int)flag;
+  return 0;
+}
+
+int wf2cu_p2p_detach(void) {
+  if (g_p2p.world) {
+    cudaStreamSynchronize(S().stream);
+    p2p_close();
+  }
+  return 0;
+}
+
+}  // extern "C"

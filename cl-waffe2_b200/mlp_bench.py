@@ -32,7 +32,17 @@ def _stage(msg):
         print(f"[mlp rank {os.environ.get('RANK', '0')} t={time.time() % 1000:.1f}] {msg}", file=sys.stderr, flush=True)
 
 
-def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
+def _all_gather_bytes(dist, world):
+    def f(b: bytes):
+        import torch
+        t = torch.tensor(list(b), dtype=torch.uint8, device="cuda")
+        outs = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outs, t)
+        return [bytes(o.cpu().tolist()) for o in outs]
+    return f
+
+
+def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0, exchange="nccl"):
     lib = _lib.load()
     _stage(f"run_one batch={per_gpu_batch}")
     chk = _lib.check
@@ -40,7 +50,10 @@ def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
     X = rng.uniform(0, 1, size=(per_gpu_batch, DIMS[0])).astype(np.float32)
     Y = np.eye(DIMS[-1], dtype=np.float32)[rng.integers(DIMS[-1], size=per_gpu_batch)]
     model = nn.MLPSequence(DIMS, "relu", seed=1234)        # same seed everywhere: replicas start identical
-    step = nn.CompiledStep(model, "softmax-cross-entropy-sum", nn.Adam(model.arena, lr=1e-3), X.shape, Y.shape, world=world)
+    step = nn.CompiledStep(model, "softmax-cross-entropy-sum", nn.Adam(model.arena, lr=1e-3), X.shape, Y.shape, world=world,
+                           exchange=exchange)
+    if world > 1 and exchange == "p2p":
+        nn.p2p_attach(model.arena, rank, world, _all_gather_bytes(dist, world))
     step.set_inputs(X, Y)
 
     def barrier():
@@ -99,25 +112,44 @@ def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0):
     chk(lib.wf2cu_host_free(hx)); chk(lib.wf2cu_host_free(hy))
     gb = per_gpu_batch * world
     step.close()
-    return {"per_gpu_batch": per_gpu_batch, "global_batch": gb, "ms_per_step": dev_ms,
+    p2p_timeout = False
+    if world > 1 and exchange == "p2p":
+        p2p_timeout = nn.p2p_timed_out()
+        barrier()
+        nn.p2p_detach()
+    # replicas must stay identical: checksum of the parameter arena, compared across ranks
+    psum = float(np.abs(model.arena.params[0].to_numpy()).sum())
+    if dist is not None:
+        import torch
+        t = torch.tensor([psum, -psum], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        in_sync = bool(t[0].item() == -t[1].item())
+    else:
+        in_sync = True
+    return {"exchange": exchange if world > 1 else None, "replicas_identical": in_sync, "p2p_timed_out": p2p_timeout,"per_gpu_batch": per_gpu_batch, "global_batch": gb, "ms_per_step": dev_ms,
             "samples_per_s": gb / (dev_ms * 1e-3), "e2e_ms_per_step": e2e_ms, "e2e_samples_per_s": gb / (e2e_ms * 1e-3),
             "h2d_bytes_per_step": int(X.nbytes + Y.nbytes), "d2h_bytes_per_step": 4,
             "launches_per_step": (l1.value - l0.value) / steps, "loss_after": loss_after,
             "pool_bytes": step.pool.nbytes()}
 
 
-def run(wf, dist, rank: int, world: int, steps: int = 200, warmup: int = 20) -> dict:
+def run(wf, dist, rank: int, world: int, steps: int = 200, warmup: int = 20, exchange: str = "p2p") -> dict:
     if world > 1:
         _stage("comm init")
         _comm_init(dist, rank, world)
         _stage("comm ready")
     res = {"model": "MNIST MLP 784-256-256-10, relu, softmax-cross-entropy (!sum), Adam lr 1e-3, fp32",
            "data": "synthetic U(0,1) inputs, one-hot labels", "n_gpus": world,
-           "collective": "one NCCL allreduce(sum) of the 269,322-float gradient bucket per step, inside the CUDA graph"
+           "collective": ("one kernel per rank inside the CUDA graph: sum of all ranks' 269,322-float gradient arenas over "
+                          "NVLink peer memory (CUDA IPC) + 1/world + Adam (csrc/p2p.cu); weak_nccl = the same step with "
+                          "ncclAllReduce + Adam" if exchange == "p2p" else
+                          "one NCCL allreduce(sum) of the 269,322-float gradient bucket per step, inside the CUDA graph")
            if world > 1 else None}
-    res["weak"] = _run_one(dist, rank, world, 1024, steps, warmup)                 # 1024 per GPU
+    res["weak"] = _run_one(dist, rank, world, 1024, steps, warmup, exchange=exchange)                 # 1024 per GPU
     if world > 1 and 1024 % world == 0:
-        res["strong"] = _run_one(dist, rank, world, 1024 // world, steps, warmup)  # 1024 global
+        res["strong"] = _run_one(dist, rank, world, 1024 // world, steps, warmup, exchange=exchange)  # 1024 global
+    if world > 1 and exchange == "p2p":
+        res["weak_nccl"] = _run_one(dist, rank, world, 1024, steps, warmup, exchange="nccl")          # the library baseline
     if world > 1:
         _lib.check(_lib.load().wf2cu_comm_destroy())
     return res

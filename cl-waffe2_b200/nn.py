@@ -358,6 +358,45 @@ class Adam:
         _lib.check(_lib.load().wf2cu_adam_step(a.param_store.ptr, 0, a.grad_store.ptr, 0, self.m.ptr, 0, self.v.ptr, 0,
                                                a.total, 0.0, self.lr_t.ptr, self.b1, self.b2, self.eps, grad_scale))
 
+    def step_p2p(self):
+        """Data-parallel step as ONE kernel: sum of all ranks' gradient arenas over NVLink peer memory,
+        x 1/world, Adam on the local replica (csrc/p2p.cu).  Needs `p2p_attach` first."""
+        a = self.arena
+        _lib.check(_lib.load().wf2cu_p2p_allreduce_adam_step(a.param_store.ptr, 0, 0, self.m.ptr, 0, self.v.ptr, 0,
+                                                             a.total, 0.0, self.lr_t.ptr, self.b1, self.b2, self.eps))
+
+
+def p2p_attach(arena: ParameterArena, rank: int, world: int, all_gather_bytes) -> None:
+    """Map every peer's gradient arena and signal page into this process (CUDA IPC).
+    `all_gather_bytes(b: bytes) -> List[bytes]` is the host transport for the 64-byte handles
+    (torch.distributed in bench.py; anything that can move 192 bytes per rank works)."""
+    lib = _lib.load()
+    hg = C.create_string_buffer(64)
+    hp = C.create_string_buffer(64)
+    hs = C.create_string_buffer(64)
+    _lib.check(lib.wf2cu_p2p_export(arena.grad_store.ptr, hg))
+    _lib.check(lib.wf2cu_p2p_export(arena.param_store.ptr, hp))
+    _lib.check(lib.wf2cu_p2p_signal_export(hs))
+    blobs = all_gather_bytes(hg.raw + hp.raw + hs.raw)
+    if len(blobs) != world or any(len(b) != 192 for b in blobs):
+        raise ValueError("p2p_attach: all_gather_bytes must return one 192-byte blob per rank")
+    grads = b"".join(b[:64] for b in blobs)
+    params = b"".join(b[64:128] for b in blobs)
+    sigs = b"".join(b[128:] for b in blobs)
+    _lib.check(lib.wf2cu_p2p_attach(rank, world, arena.grad_store.ptr, arena.param_store.ptr,
+                                    C.create_string_buffer(grads, len(grads)), C.create_string_buffer(params, len(params)),
+                                    C.create_string_buffer(sigs, len(sigs))))
+
+
+def p2p_detach() -> None:
+    _lib.check(_lib.load().wf2cu_p2p_detach())
+
+
+def p2p_timed_out() -> bool:
+    f = C.c_int(0)
+    _lib.check(_lib.load().wf2cu_p2p_status(C.byref(f)))
+    return bool(f.value)
+
 
 # ------------------------------------------------------------------------------- compiled step
 class CompiledStep:
@@ -369,8 +408,12 @@ class CompiledStep:
     gradient bucket is summed with one NCCL allreduce inside the graph and scaled by 1/world in the
     optimizer kernel."""
 
-    def __init__(self, model: MLPSequence, loss: str, optimizer, x_shape, y_shape, world: int = 1, use_graph: bool = True):
+    def __init__(self, model: MLPSequence, loss: str, optimizer, x_shape, y_shape, world: int = 1, use_graph: bool = True,
+                 exchange: str = "nccl"):
         self.model, self.loss_kind, self.opt, self.world = model, loss, optimizer, int(world)
+        if exchange not in ("nccl", "p2p"):
+            raise ValueError(f"exchange must be 'nccl' or 'p2p', got {exchange!r}")
+        self.exchange = exchange
         self.x = make_tensor(x_shape)
         self.y = make_tensor(y_shape)
         self.pool = StaticPool()
@@ -401,10 +444,13 @@ class CompiledStep:
                 loss._has_grad = True
                 for node in reversed(self.tape.nodes):
                     node()
-                if self.world > 1:
-                    a = self.model.arena
-                    _lib.check(lib.wf2cu_allreduce_sum_f32(a.grad_store.ptr, 0, a.total))
-                self.opt.step(1.0 / self.world if self.world > 1 else 1.0)
+                if self.world > 1 and self.exchange == "p2p":
+                    self.opt.step_p2p()         # exchange + 1/world + Adam in one kernel over peer memory
+                else:
+                    if self.world > 1:
+                        a = self.model.arena
+                        _lib.check(lib.wf2cu_allreduce_sum_f32(a.grad_store.ptr, 0, a.total))
+                    self.opt.step(1.0 / self.world if self.world > 1 else 1.0)
         finally:
             _tape = None
         self.loss = loss

@@ -207,6 +207,29 @@ int  wf2cu_comm_init(int rank, int world, const void* id128);  /* one process pe
 int  wf2cu_allreduce_sum_f32(void* buf, int64_t offset, int64_t count);  /* on the stream    */
 int  wf2cu_comm_destroy(void);
 
+/* Exchange + optimizer as ONE kernel over NVLink peer memory (new work; the reference has no
+ * distributed code — the step it replaces is `call-optimizer!` after `backward`,
+ * `vm/generic-tensor/acceptor.lisp:466-508`, run once per replica).  One process per GPU:
+ *   1. every rank: wf2cu_p2p_export(gradient arena), wf2cu_p2p_export(parameter arena) and
+ *      wf2cu_p2p_signal_export() -> three 64-byte CUDA-IPC handles; the host all-gathers them (any transport);
+ *   2. wf2cu_p2p_attach(rank, world, local arenas, 3 x (world x 64 B))   (world <= 8);
+ *   3. per step, after backward: wf2cu_p2p_allreduce_adam_step — waits until every rank's gradients are
+ *      complete; rank r sums shard r of the bucket over all ranks' arenas in rank order, scales by
+ *      1/world, applies Adam (same formula as wf2cu_adam_step) with its m/v shard and stores the new
+ *      parameters into every replica; then waits until every rank has written its shard, so replicas
+ *      stay bit-identical and the gradient arena can be reused by the next backward.
+ * A peer that never arrives makes the kernel give up after 2 s and raises the flag wf2cu_p2p_status
+ * reports (the GPU is never left spinning).  g_off, p_off, m_off, v_off: element offsets, multiples of 4. */
+int  wf2cu_p2p_export(void* dev_alloc, void* handle64);
+int  wf2cu_p2p_signal_export(void* handle64);
+int  wf2cu_p2p_attach(int rank, int world, void* local_grad_alloc, void* local_param_alloc,
+                      const void* grad_handles, const void* param_handles, const void* signal_handles);
+int  wf2cu_p2p_allreduce_adam_step(void* param, int64_t p_off, int64_t g_off, void* m, int64_t m_off,
+                                   void* v, int64_t v_off, int64_t n, float lr_t, const void* lr_t_dev,
+                                   float beta1, float beta2, float eps);
+int  wf2cu_p2p_status(int* timed_out);
+int  wf2cu_p2p_detach(void);
+
 #ifdef __cplusplus
 }
 #endif

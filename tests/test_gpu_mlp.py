@@ -82,3 +82,21 @@ def test_gradients_match_oracle(gpu):
     exp = [gW[0].vec, gb[0].vec, gW[1].vec, gb[1].vec]
     for g, e in zip(got, exp):
         np.testing.assert_allclose(g, e, rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_p2p_fused_allreduce_adam_two_ranks():
+    """csrc/p2p.cu on 2 GPUs (skipped on a 1-GPU box): the fused peer-memory reduce-scatter + Adam + all-gather
+    kernel is bitwise equal to a numpy emulation, equal to the NCCL route at world 2, replicas bit-identical."""
+    import subprocess, sys, os
+    import ctypes as C
+    wf = importlib.import_module("cl-waffe2_b200")
+    n = C.c_int(0)
+    wf._lib.check(wf._lib.load().wf2cu_device_count(C.byref(n)))
+    if n.value < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(root, "scripts", "p2p_check.py")],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
