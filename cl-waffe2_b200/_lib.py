@@ -52,6 +52,9 @@ PROTOTYPES = {
     "wf2cu_reduce_maxmin": [i32, VP, VP], "wf2cu_argmaxmin": [i32, VP, VP],
     "wf2cu_gemm": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i64, i64, i64],
     "wf2cu_gemm_set_mode": [i32],
+    "wf2cu_gemm_ex": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i32, vp, i64, i64],
+    "wf2cu_sce_sum_forward": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, f32],
+    "wf2cu_sce_backward": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32],
     "wf2cu_sgd_step": [vp, i64, vp, i64, i64, f32],
     "wf2cu_adam_step": [vp, i64, vp, i64, vp, i64, vp, i64, i64, f32, vp, f32, f32, f32, f32],
     "wf2cu_embedding_gather": [vp, i64, i64, vp, vp, i64, vp],

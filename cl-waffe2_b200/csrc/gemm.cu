@@ -25,7 +25,28 @@ struct GemmArgs {
   const float* A; const float* B; float* C;
   int64_t m, n, k, lda, ldb, ldc, sa, sb, sc;
   int ta, tb;
+  // fused epilogue (wf2cu_gemm_ex): v = acc [+ bias[col]] ; [v = v * (v > 0)] ; [v = v * (mask[row, col] > 0)]
+  const float* bias; const float* mask; int64_t ldmask; int act;
 };
+
+// `!relu` is x * (where x > 0 then 1 else 0) (nn/activation.lisp:11-26): a true multiply, so a negative
+// x gives -0.0 exactly as the reference's MulNode does.
+__device__ __forceinline__ float epilogue(const GemmArgs& g, float v, int64_t gm, int64_t gn) {
+  if (g.bias) v = __fadd_rn(v, g.bias[gn]);
+  if (g.act == 1) v = __fmul_rn(v, v > 0.f ? 1.f : 0.f);
+  if (g.mask) v = __fmul_rn(v, g.mask[gm * g.ldmask + gn] > 0.f ? 1.f : 0.f);
+  return v;
+}
+
+// the same epilogue as its own pass, for GEMMs that ran on the tensor-core path
+__global__ void __launch_bounds__(256) gemm_epilogue_kernel(const __grid_constant__ GemmArgs g) {
+  const int64_t total = g.m * g.n;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+    const int64_t gm = i / g.n, gn = i - gm * g.n;
+    float* c = g.C + gm * g.ldc + gn;
+    *c = epilogue(g, *c, gm, gn);
+  }
+}
 
 __global__ void __launch_bounds__(256) sgemm_simt_kernel(const __grid_constant__ GemmArgs g) {
   __shared__ float As[BK][BM + 4];
@@ -107,7 +128,7 @@ __global__ void __launch_bounds__(256) sgemm_simt_kernel(const __grid_constant__
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int64_t gn = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
-      if (gn < g.n) C[gm * g.ldc + gn] = acc[i][j];
+      if (gn < g.n) C[gm * g.ldc + gn] = epilogue(g, acc[i][j], gm, gn);
     }
   }
 }
@@ -214,7 +235,7 @@ __global__ void __launch_bounds__(256) sgemm_splitk_kernel(const __grid_constant
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int64_t gn = n0 + tx * 4 + j;
-        if (gn < g.n) C[gm * g.ldc + gn] = acc[i][j];
+        if (gn < g.n) C[gm * g.ldc + gn] = epilogue(g, acc[i][j], gm, gn);
       }
     }
     return;
@@ -242,7 +263,7 @@ __global__ void __launch_bounds__(256) sgemm_splitk_kernel(const __grid_constant
       const float v[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        if (gn + j < g.n) cp[j] = v[j];
+        if (gn + j < g.n) cp[j] = epilogue(g, v[j], gm, gn + j);
     }
   }
   cluster.sync();                                   // nobody leaves while a peer may still read its tile
@@ -286,28 +307,38 @@ int wf2cu_gemm_set_mode(int mode) {
   return 0;
 }
 
-int wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
-               const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc, int64_t batch,
-               int64_t stride_a, int64_t stride_b, int64_t stride_c) {
+static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
+                     const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc, int64_t batch,
+                     int64_t stride_a, int64_t stride_b, int64_t stride_c, const float* bias, int act, const float* mask,
+                     int64_t ldmask, const char* who) {
   WF2_REQUIRE_INIT();
-  WF2_CHECK(A && B && C, "wf2cu_gemm: null operand");
-  WF2_CHECK(m >= 0 && n >= 0 && k >= 0 && batch >= 0, "wf2cu_gemm: negative extent");
+  WF2_CHECK(A && B && C, "%s: null operand", who);
+  WF2_CHECK(m >= 0 && n >= 0 && k >= 0 && batch >= 0, "%s: negative extent", who);
   WF2_CHECK(lda >= (trans_a ? m : k) && ldb >= (trans_b ? k : n) && ldc >= n,
-            "wf2cu_gemm: leading dimension too small (lda=%lld ldb=%lld ldc=%lld for m=%lld n=%lld k=%lld ta=%d tb=%d)",
+            "%s: leading dimension too small (lda=%lld ldb=%lld ldc=%lld for m=%lld n=%lld k=%lld ta=%d tb=%d)", who,
             (long long)lda, (long long)ldb, (long long)ldc, (long long)m, (long long)n, (long long)k, trans_a, trans_b);
   if (m == 0 || n == 0 || batch == 0) return 0;
   const float* a = (const float*)A + a_off;
   const float* b = (const float*)B + b_off;
   float* c = (float*)C + c_off;
+  const bool epi = bias || act || mask;
+  WF2_CHECK(!epi || batch == 1, "%s: the fused epilogue takes unbatched operands (batch=%lld)", who, (long long)batch);
+  GemmArgs g{a, b, c, m, n, k, lda, ldb, ldc, stride_a, stride_b, stride_c, trans_a ? 1 : 0, trans_b ? 1 : 0, bias, mask, ldmask, act};
   const int mode = S().gemm_mode;
   if (mode != 1) {
     const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode);
     if (r < 0) return -r;
-    if (r == 1) return 0;
-    if (mode >= 2) return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_gemm: tensor-core path forced but declined this shape/alignment");
+    if (r == 1) {
+      if (!epi) return 0;
+      int64_t grid = (m * n + 255) / 256;
+      const int64_t cap = (int64_t)S().sm_count * 8;
+      if (grid > cap) grid = cap;
+      gemm_epilogue_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(g);
+      return post_launch("wf2cu_gemm_ex(epilogue)");
+    }
+    if (mode >= 2) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: tensor-core path forced but declined this shape/alignment", who);
   }
-  WF2_CHECK(batch < 65536, "wf2cu_gemm: batch %lld too large for the SIMT path", (long long)batch);
-  GemmArgs g{a, b, c, m, n, k, lda, ldb, ldc, stride_a, stride_b, stride_c, trans_a ? 1 : 0, trans_b ? 1 : 0};
+  WF2_CHECK(batch < 65536, "%s: batch %lld too large for the SIMT path", who, (long long)batch);
   {
     const int r = sgemm_small_try(g, batch);
     if (r < 0) return -r;
@@ -316,6 +347,23 @@ int wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const 
   dim3 grid((unsigned)((n + BN - 1) / BN), (unsigned)((m + BM - 1) / BM), (unsigned)batch);
   sgemm_simt_kernel<<<grid, 256, 0, S().stream>>>(g);
   return post_launch("wf2cu_gemm(simt)");
+}
+
+int wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
+               const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc, int64_t batch,
+               int64_t stride_a, int64_t stride_b, int64_t stride_c) {
+  return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, batch, stride_a, stride_b, stride_c,
+                   nullptr, 0, nullptr, 0, "wf2cu_gemm");
+}
+
+int wf2cu_gemm_ex(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
+                  const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc,
+                  const void* bias, int64_t bias_off, int act, const void* mask, int64_t mask_off, int64_t ldmask) {
+  WF2_CHECK(act == 0 || act == 1, "wf2cu_gemm_ex: act %d not in {0 none, 1 relu}", act);
+  WF2_CHECK(!mask || ldmask >= n, "wf2cu_gemm_ex: ldmask %lld < n %lld", (long long)ldmask, (long long)n);
+  return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
+                   bias ? (const float*)bias + bias_off : nullptr, act, mask ? (const float*)mask + mask_off : nullptr, ldmask,
+                   "wf2cu_gemm_ex");
 }
 
 }  // extern "C"

@@ -235,6 +235,81 @@ __global__ void __launch_bounds__(256) softmax_lane_kernel(const __grid_constant
 
 static inline bool al16s(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
+// ------------------------------------------------------------------ softmax-cross-entropy, summed
+// `(!sum (softmax-cross-entropy x labels))` as the MNIST example composes its loss
+// (examples/mnist/mlp.lisp:24-28; nn/criterion.lisp:89-117,164-188): z = softmax(x, avoid-overflow nil),
+// out = -1 * (labels * log(z + delta)), loss = sum(out).  Three node launches (softmax, the fused
+// log/mul chain, `!sum`) become one kernel: a warp per row keeps the row in registers, the row
+// losses meet through a last-block ticket in a fixed order.  z is written because the backward
+// (`sce-diff-static`, :81-87) needs it.
+struct SceArgs {
+  const float* x; const float* labels; float* z; float* loss; float* partial; unsigned int* counter;
+  int64_t rows, cols;
+  float delta;
+};
+
+__global__ void __launch_bounds__(256) sce_sum_forward_kernel(const __grid_constant__ SceArgs a) {
+  __shared__ float smem[8];
+  __shared__ bool is_last;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  float rl = 0.f;
+  if (row < a.rows) {
+    const float* xp = a.x + row * a.cols;
+    const float* lp = a.labels + row * a.cols;
+    float* zp = a.z + row * a.cols;
+    float v[32];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      const int64_t c = lane + 32 * k;
+      v[k] = 0.f;
+      if (c < a.cols) { v[k] = expf(xp[c]); s = __fadd_rn(s, v[k]); }
+    }
+    s = warp_sum(s);
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      const int64_t c = lane + 32 * k;
+      if (c < a.cols) {
+        const float z = __fdiv_rn(v[k], s);
+        zp[c] = z;
+        rl = __fadd_rn(rl, __fmul_rn(-1.0f, __fmul_rn(lp[c], logf(__fadd_rn(z, a.delta)))));
+      }
+    }
+  }
+  rl = warp_sum(rl);
+  if (lane == 0) smem[threadIdx.x >> 5] = rl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = smem[0];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) t = __fadd_rn(t, smem[k]);
+    unsigned int tk;
+    asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(a.partial + blockIdx.x), "f"(t) : "memory");
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(tk) : "l"(a.counter) : "memory");
+    is_last = (tk == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  float w = 0.f;
+  for (uint32_t c = threadIdx.x; c < gridDim.x; c += 256) w = __fadd_rn(w, __ldcg(a.partial + c));
+  w = block_sum<256>(w, smem);
+  if (threadIdx.x == 0) { a.loss[0] = w; *a.counter = 0; }
+}
+
+// `sce-diff-static` (criterion.lisp:81-87): dx = (dy * (z - labels)) / batch, dy the (broadcast) scalar
+// gradient of the summed loss, read from device memory.
+__global__ void __launch_bounds__(256) sce_backward_kernel(const float* __restrict__ z, const float* __restrict__ labels,
+                                                           const float* __restrict__ dy, float* __restrict__ dx, int64_t n,
+                                                           float batch, int accumulate) {
+  const float d = *dy;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    float g = __fdiv_rn(__fmul_rn(d, __fsub_rn(z[i], labels[i])), batch);
+    if (accumulate) g = __fadd_rn(dx[i], g);
+    dx[i] = g;
+  }
+}
+
 }  // namespace wf2
 
 using namespace wf2;
@@ -324,4 +399,34 @@ extern "C" int wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axi
   else if (R <= 64) softmax_lane_kernel<64><<<(unsigned)grid, 256, 0, s.stream>>>(a);
   else softmax_lane_kernel<0><<<(unsigned)grid, 256, 0, s.stream>>>(a);
   return post_launch("wf2cu_softmax(lane)");
+}
+
+extern "C" int wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
+                                     void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(x && labels && z && loss && rows >= 0 && cols >= 1, "wf2cu_sce_sum_forward: bad arguments");
+  if (cols > 1024) return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_sce_sum_forward: %lld classes > 1024; compose softmax, the log chain and !sum instead", (long long)cols);
+  const int64_t grid = rows == 0 ? 1 : (rows + 7) / 8;
+  WF2_CHECK(grid < (int64_t(1) << 31), "wf2cu_sce_sum_forward: too many rows");
+  int rc = ensure_scratch((size_t)grid * sizeof(float));
+  if (rc) return rc;
+  State& s = S();
+  SceArgs a{(const float*)x + x_off, (const float*)labels + l_off, (float*)z + z_off, (float*)loss + loss_off, (float*)s.scratch,
+            s.counters + 4095, rows, cols, delta};
+  sce_sum_forward_kernel<<<(unsigned)grid, 256, 0, s.stream>>>(a);
+  return post_launch("wf2cu_sce_sum_forward");
+}
+
+extern "C" int wf2cu_sce_backward(const void* z, int64_t z_off, const void* labels, int64_t l_off, const void* dy, int64_t dy_off,
+                                  void* dx, int64_t dx_off, int64_t rows, int64_t cols, int accumulate) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(z && labels && dy && dx && rows >= 0 && cols >= 0, "wf2cu_sce_backward: bad arguments");
+  const int64_t n = rows * cols;
+  if (n == 0) return 0;
+  int64_t grid = (n + 255) / 256;
+  const int64_t cap = (int64_t)S().sm_count * 8;
+  if (grid > cap) grid = cap;
+  sce_backward_kernel<<<(unsigned)grid, 256, 0, S().stream>>>((const float*)z + z_off, (const float*)labels + l_off,
+                                                             (const float*)dy + dy_off, (float*)dx + dx_off, n, (float)rows, accumulate);
+  return post_launch("wf2cu_sce_backward");
 }

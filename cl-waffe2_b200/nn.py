@@ -45,6 +45,13 @@ class Tape:
 
 _tape: Optional[Tape] = None
 
+# Node-level fusion (what the backend's `on-finalizing-compiling` pass does to the instruction sequence,
+# cl-waffe2_b200/lisp/fusion.lisp): LinearLayer's MatMul + bias add (+ the `!relu` after it) become one
+# wf2cu_gemm_ex; the `!relu` backward rides on the dX GEMM that produces its incoming gradient;
+# `(!sum (softmax-cross-entropy ...))` is one kernel forward and one backward.  FUSE = False issues one
+# launch per node, exactly as the unfused instruction sequence would (both are tested against the oracle).
+FUSE = True
+
 
 def _tracked(t: CUDATensor) -> bool:
     return bool(getattr(t, "requires_grad", False) or getattr(t, "_track", False))
@@ -58,27 +65,56 @@ def _mark(out: CUDATensor, *inputs: CUDATensor) -> bool:
 
 def _accumulate(t: CUDATensor, compute: Callable[[CUDATensor, bool], None]) -> None:
     """Gradient adder (`vm/utils.lisp:109-142`): the first contribution is written (Move), later
-    ones are added."""
+    ones are added.  A tensor produced by a fused `... + !relu` node carries `_relu_out`: its incoming
+    gradient is multiplied by (out > 0) — by the producing GEMM's epilogue when `compute` can do that
+    (it then sets `_mask_done`), by one extra element-wise launch otherwise."""
     if not _tracked(t):
         return
     if t.grad is None:
         t.grad = make_tensor(t.shape)
-    compute(t.grad, bool(getattr(t, "_has_grad", False)))
+    acc = bool(getattr(t, "_has_grad", False))
+    masked = getattr(t, "_relu_out", False)
+    t._mask_done = False
+    if masked and acc:
+        tmp = make_tensor(t.shape)          # a second contribution: mask it on its own, then add
+        compute(tmp, False)
+        if not t._mask_done:
+            _mask_mul(tmp, t)
+        ops.add_(t.grad, tmp)
+    else:
+        compute(t.grad, acc)
+        if masked and not t._mask_done:
+            _mask_mul(t.grad, t)
     t._has_grad = True
     _tape.touched.append(t)
 
 
+def _mask_mul(g: CUDATensor, out: CUDATensor) -> None:
+    """g <- g * (out > 0 ? 1 : 0)"""
+    prog = [(_P.P_LOAD, 0, 0, 0), (_P.P_IMM, 1, 0, ops._imm(0.0)), (_P.P_CMPSEL | (_P.CMP["gt"] << 8), 1, 0, 1),
+            (_P.P_LOAD, 2, 1, 0), (_P.P_MUL, 1, 2, 1), (_P.P_STORE, 1, 1, 0)]
+    ops.fused(prog, [out, g])
+
+
 # ------------------------------------------------------------------------------- nodes
-def linear(x: CUDATensor, weight: CUDATensor, bias: Optional[CUDATensor]) -> CUDATensor:
-    """`step-linear` (nn/regression.lisp:14-18): y = x @ W^T + b, W is (out in)."""
-    out = ops.matmul(x, ops.t(weight))
-    if bias is not None:
-        ops.add_(out, view(_as_row(bias), [":broadcast", out.shape[0]], True))
+def linear(x: CUDATensor, weight: CUDATensor, bias: Optional[CUDATensor], fuse_relu: bool = False) -> CUDATensor:
+    """`step-linear` (nn/regression.lisp:14-18): y = x @ W^T + b, W is (out in).
+    fuse_relu: the `!relu` that follows is folded in (FUSE only); `out` is then the activation and its
+    incoming gradient gets the (out > 0) mask (out > 0 <=> pre-activation > 0)."""
+    if FUSE and x.dims() == 2:
+        out = ops.matmul(x, ops.t(weight), bias=bias, relu=fuse_relu)
+    else:
+        assert not fuse_relu
+        out = ops.matmul(x, ops.t(weight))
+        if bias is not None:
+            ops.add_(out, view(_as_row(bias), [":broadcast", out.shape[0]], True))
     if _mark(out, x, weight, *([bias] if bias is not None else [])):
+        out._relu_out = bool(fuse_relu)
+
         def bw():
             dout = out.grad
             # MatMulNode backward: dA = dout . B^T, dB = A^T . dout with B = (!t W)
-            _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight))
+            _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
             _accumulate(weight, lambda g, acc: _gemm_into(g, acc, ops.t(dout), x))
             if bias is not None:
                 # the (!flexible bias) broadcast view accumulates dout over the batch axis
@@ -98,11 +134,14 @@ def _as_row(b: CUDATensor) -> CUDATensor:
     return t
 
 
-def _gemm_into(g: CUDATensor, acc: bool, a, b) -> None:
+def _gemm_into(g: CUDATensor, acc: bool, a, b, target: Optional[CUDATensor] = None) -> None:
+    mask = target if (FUSE and target is not None and getattr(target, "_relu_out", False) and g.dims() == 2) else None
     if not acc:
-        ops.matmul(a, b, out=g)
+        ops.matmul(a, b, out=g, relu_mask=mask)
     else:
-        ops.add_(g, ops.matmul(a, b))
+        ops.add_(g, ops.matmul(a, b, relu_mask=mask))
+    if mask is not None:
+        target._mask_done = True
 
 
 def relu(x: CUDATensor) -> CUDATensor:
@@ -160,6 +199,29 @@ def softmax_cross_entropy(x: CUDATensor, labels: CUDATensor, delta: float = 1e-7
                     p += [(_P.P_LOAD, 3, 3, 0), (_P.P_ADD, 0, 3, 0)]
                 p += [(_P.P_STORE, 0, 3, 0)]
                 ops.fused(p, [z, labels, out.grad, g])
+            _accumulate(x, f)
+        _tape.nodes.append(bw)
+    return out
+
+
+def softmax_cross_entropy_sum(x: CUDATensor, labels: CUDATensor, delta: float = 1e-7) -> CUDATensor:
+    """`(!sum (softmax-cross-entropy x labels))` as one kernel forward (z saved) and one backward
+    (`sce-diff-static` with the summed loss' scalar gradient) — wf2cu_sce_sum_forward / wf2cu_sce_backward."""
+    lib = _lib.load()
+    rows, cols = x.shape[-2], x.shape[-1]
+    if x.dims() != 2 or cols > 1024 or not (x.is_contiguous() and labels.is_contiguous()):
+        return reduce_sum(softmax_cross_entropy(x, labels, delta))
+    z = make_tensor(x.shape)
+    out = make_tensor([1, 1])
+    _lib.check(lib.wf2cu_sce_sum_forward(x.vec.ptr, x.lower().offset, labels.vec.ptr, labels.lower().offset,
+                                         z.vec.ptr, z.lower().offset, out.vec.ptr, out.lower().offset, rows, cols, float(delta)))
+    if _mark(out, x):
+        def bw():
+            dy = out.grad
+
+            def f(g, acc):
+                _lib.check(lib.wf2cu_sce_backward(z.vec.ptr, z.lower().offset, labels.vec.ptr, labels.lower().offset,
+                                                  dy.vec.ptr, dy.lower().offset, g.vec.ptr, g.lower().offset, rows, cols, 1 if acc else 0))
             _accumulate(x, f)
         _tape.nodes.append(bw)
     return out
@@ -306,8 +368,9 @@ class MLPSequence:
         p = self.arena.params
         n = len(self.dims) - 1
         for i in range(n):
-            x = linear(x, p[2 * i], p[2 * i + 1])
-            if i != n - 1:
+            fuse = FUSE and i != n - 1 and self.activation is relu and x.dims() == 2
+            x = linear(x, p[2 * i], p[2 * i + 1], fuse_relu=fuse)
+            if i != n - 1 and not fuse:
                 x = self.activation(x)
         return x
 
@@ -425,6 +488,8 @@ class CompiledStep:
 
     def _loss(self, out: CUDATensor) -> CUDATensor:
         if self.loss_kind == "softmax-cross-entropy-sum":      # examples/mnist/mlp.lisp:24-28
+            if FUSE:
+                return softmax_cross_entropy_sum(out, self.y)
             return reduce_sum(softmax_cross_entropy(out, self.y))
         if self.loss_kind == "mse-mean":                       # examples/mlp_sin_wave.lisp
             return mse(out, self.y, reduction="mean")

@@ -259,9 +259,12 @@ def _mat_operand(x: CUDATensor):
     raise AssertionError("unreachable")
 
 
-def matmul(a, b, out: Optional[CUDATensor] = None) -> CUDATensor:
+def matmul(a, b, out: Optional[CUDATensor] = None, bias: Optional[CUDATensor] = None, relu: bool = False,
+           relu_mask: Optional[CUDATensor] = None) -> CUDATensor:
     """`(!matmul a b)` with `(!t ·)` operands (base-impl/matrix-ops.lisp:6-173):
-    C[~ i k] <- A[~ i j] . B[~ j k], alpha=1, beta=0."""
+    C[~ i k] <- A[~ i j] . B[~ j k], alpha=1, beta=0.
+    bias / relu / relu_mask fold the node that follows into the epilogue (wf2cu_gemm_ex): `+ bias` per column
+    (LinearLayer, nn/regression.lisp:14-18), `!relu` of the result, or `* (mask > 0)` (the `!relu` backward)."""
     ta = isinstance(a, LazyT)
     tb = isinstance(b, LazyT)
     A = a.x if ta else a
@@ -288,6 +291,22 @@ def matmul(a, b, out: Optional[CUDATensor] = None) -> CUDATensor:
     if o.shape != bshape + [m, n] or not o.is_contiguous():
         raise ValueError(f"!matmul: out must be a contiguous {bshape + [m, n]} tensor, got {o.shape}")
     lo = o.lower()
+    if bias is not None or relu or relu_mask is not None:
+        if batch != 1:
+            raise ValueError("!matmul: the fused epilogue takes unbatched operands")
+        bp, boff = (None, 0)
+        if bias is not None:
+            if bias.numel() != n or not bias.is_contiguous():
+                raise ValueError(f"!matmul: bias must be a contiguous {n}-element tensor, got {bias.shape}")
+            bp, boff = bias.vec.ptr, bias.lower().offset
+        mp, moff, ldm = (None, 0, 0)
+        if relu_mask is not None:
+            if relu_mask.shape != [m, n] or not relu_mask.is_contiguous():
+                raise ValueError(f"!matmul: relu_mask must be a contiguous {[m, n]} tensor, got {relu_mask.shape}")
+            mp, moff, ldm = relu_mask.vec.ptr, relu_mask.lower().offset, n
+        _lib.check(_L().wf2cu_gemm_ex(1 if ta else 0, 1 if tb else 0, m, n, k, A.vec.ptr, la.offset, lda,
+                                      B.vec.ptr, lb.offset, ldb, o.vec.ptr, lo.offset, n, bp, boff, 1 if relu else 0, mp, moff, ldm))
+        return o
     _lib.check(_L().wf2cu_gemm(1 if ta else 0, 1 if tb else 0, m, n, k,
                                A.vec.ptr, la.offset, lda, B.vec.ptr, lb.offset, ldb,
                                o.vec.ptr, lo.offset, n, batch, sa, sb, m * n))

@@ -183,6 +183,23 @@ int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
                 int64_t batch, int64_t stride_a, int64_t stride_b, int64_t stride_c);
 /* 0 = auto, 1 = force fp32 SIMT path, 2 = force tcgen05 3xTF32, 3 = tcgen05 1xTF32 (not parity-grade) */
 int  wf2cu_gemm_set_mode(int mode);
+/* MatmulNode with the node that follows it folded into the epilogue (what the backend's
+ * `on-finalizing-compiling` pass emits for LinearLayer, `nn/regression.lisp:14-18`, and for the
+ * `!relu` that follows / precedes it, `nn/activation.lisp:11-26`):
+ *   C = op(A) op(B) [+ bias[col]]  ;  act = 1: C = C * (C > 0 ? 1 : 0)  ;  mask != NULL: C = C * (mask[row,col] > 0 ? 1 : 0)
+ * (the last form is the MulNode backward of `!relu` applied to dX = dout . W).  Unbatched. */
+int  wf2cu_gemm_ex(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
+                   const void* A, int64_t a_off, int64_t lda, const void* B, int64_t b_off, int64_t ldb,
+                   void* C, int64_t c_off, int64_t ldc, const void* bias, int64_t bias_off, int act,
+                   const void* mask, int64_t mask_off, int64_t ldmask);
+/* `(!sum (softmax-cross-entropy x labels))` (`nn/criterion.lisp:89-117,164-188`; the MNIST example's
+ * loss, `examples/mnist/mlp.lisp:24-28`) in one kernel: z = softmax(x) row-wise (avoid-overflow nil),
+ * loss[0] = sum(-1 * labels * log(z + delta)); x, labels, z contiguous (rows cols), cols <= 1024.
+ * wf2cu_sce_backward is `sce-diff-static` (:81-87): dx = (dy[0] * (z - labels)) / rows. */
+int  wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
+                           void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta);
+int  wf2cu_sce_backward(const void* z, int64_t z_off, const void* labels, int64_t l_off, const void* dy, int64_t dy_off,
+                        void* dx, int64_t dx_off, int64_t rows, int64_t cols, int accumulate);
 
 /* ===================== optimizers (fused chains of `optimizers/impls/*.lisp`) ===================== */
 /* p <- p - lr * g        (`sgd.lisp:20-26`) */

@@ -1,4 +1,4 @@
-python -m pytest tests -m gpu -x -q > gpurun_out/q_pytest.log 2>&1; echo "pytest rc=$?"; tail -n 3 gpurun_out/q_pytest.log
+python -m pytest tests -m gpu -x -q > gpurun_out/q_pytest.log 2>&1; echo "pytest rc=$?"; tail -n 30 gpurun_out/q_pytest.log
 python scripts/mlp_profile.py > gpurun_out/mlp_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/mlp_launches.csv python scripts/mlp_profile.py > gpurun_out/mlp_ncu.log 2>&1
 tail -n 2 gpurun_out/mlp_plain.log gpurun_out/mlp_ncu.log

@@ -37,8 +37,19 @@ def test_c1_sin_wave_sgd_matches_oracle(gpu):
         np.testing.assert_allclose(p.to_numpy().ravel(), q.vec, rtol=1e-4, atol=1e-6)
 
 
+@pytest.fixture(params=[True, False], ids=["fused", "node-by-node"])
+def fuse(request, gpu):
+    """Both instruction sequences: with the backend's node fusions (GEMM epilogues, one-kernel loss) and
+    one launch per node."""
+    nn = _nn(gpu)
+    old = nn.FUSE
+    nn.FUSE = request.param
+    yield request.param
+    nn.FUSE = old
+
+
 @pytest.mark.parametrize("use_graph", [True, False])
-def test_c4_mnist_mlp_adam_matches_oracle(gpu, use_graph):
+def test_c4_mnist_mlp_adam_matches_oracle(gpu, use_graph, fuse):
     # examples/mnist/mlp.lisp:12-36 — 784-256-256-10, relu, softmax-cross-entropy (!sum), Adam lr 1e-3
     nn = _nn(gpu)
     from oracle.mlp import OracleMLP
@@ -62,7 +73,7 @@ def test_c4_mnist_mlp_adam_matches_oracle(gpu, use_graph):
     assert ours[-1] < 0.7 * ours[0]
 
 
-def test_gradients_match_oracle(gpu):
+def test_gradients_match_oracle(gpu, fuse):
     nn = _nn(gpu)
     from oracle.mlp import OracleMLP
     rng = np.random.default_rng(3)
@@ -82,6 +93,33 @@ def test_gradients_match_oracle(gpu):
     exp = [gW[0].vec, gb[0].vec, gW[1].vec, gb[1].vec]
     for g, e in zip(got, exp):
         np.testing.assert_allclose(g, e, rtol=1e-4, atol=1e-6)
+
+
+def test_gemm_epilogues(gpu):
+    """wf2cu_gemm_ex: + bias, !relu, and the relu-backward mask, on the SIMT split-K path and (forced) on the
+    tensor path with its separate epilogue pass; against numpy with the reference's relu = x * (x > 0)."""
+    import ctypes as C
+    wf = gpu
+    rng = np.random.default_rng(5)
+    lib = wf._lib.load()
+    for (m, n, k), mode in [((100, 70, 33), 0), ((1024, 256, 784), 0), ((256, 512, 128), 2)]:
+        A = rng.normal(size=(m, k)).astype(np.float32)
+        W = rng.normal(size=(n, k)).astype(np.float32)
+        b = rng.normal(size=(n,)).astype(np.float32)
+        M = rng.normal(size=(m, n)).astype(np.float32)
+        ga, gw, gb, gm = (wf.from_numpy(a) for a in (A, W, b, M))
+        wf._lib.check(lib.wf2cu_gemm_set_mode(mode))
+        try:
+            pre = (A.astype(np.float64) @ W.T.astype(np.float64))
+            tol = dict(rtol=2e-4, atol=2e-4 * np.abs(pre).max())
+            r = wf.ops.matmul(ga, wf.ops.t(gw), bias=gb).to_numpy()
+            np.testing.assert_allclose(r, pre + b, **tol)
+            r = wf.ops.matmul(ga, wf.ops.t(gw), bias=gb, relu=True).to_numpy()
+            np.testing.assert_allclose(r, np.maximum(pre + b, 0), **tol)
+            r = wf.ops.matmul(ga, wf.ops.t(gw), relu_mask=gm).to_numpy()
+            np.testing.assert_allclose(r, pre * (M > 0), **tol)
+        finally:
+            wf._lib.check(lib.wf2cu_gemm_set_mode(0))
 
 
 @pytest.mark.gpu
