@@ -18,6 +18,9 @@ namespace wf2 {
 // implemented in gemm_tc.cu; returns 1 when it handled the problem, 0 when it declines, <0 error
 int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B,
                 int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode);
+// gemm_tc.cu: one-launch tcgen05 kernel for small problems (in-kernel hi/lo split, cluster split-K, fused epilogue)
+int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
+                      float* C, int64_t ldc, const float* bias, int act, const float* mask, int64_t ldmask);
 
 constexpr int BM = 128, BN = 128, BK = 16;
 
@@ -302,7 +305,7 @@ using namespace wf2;
 extern "C" {
 
 int wf2cu_gemm_set_mode(int mode) {
-  WF2_CHECK(mode >= 0 && mode <= 3, "wf2cu_gemm_set_mode: mode %d not in 0..3", mode);
+  WF2_CHECK(mode >= 0 && mode <= 4, "wf2cu_gemm_set_mode: mode %d not in 0..4", mode);
   S().gemm_mode = mode;
   return 0;
 }
@@ -325,6 +328,18 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   WF2_CHECK(!epi || batch == 1, "%s: the fused epilogue takes unbatched operands (batch=%lld)", who, (long long)batch);
   GemmArgs g{a, b, c, m, n, k, lda, ldb, ldc, stride_a, stride_b, stride_c, trans_a ? 1 : 0, trans_b ? 1 : 0, bias, mask, ldmask, act};
   const int mode = S().gemm_mode;
+  // auto: 50 MFLOP..1 GFLOP -> fused tcgen05 kernel (14.6 vs 22.3 us on 1024x256x784, 8.6 vs 10.2 us on 1024x256x256;
+  // below 50 MFLOP its ~5 us floor loses to the SIMT split-K kernel: 7.9 vs 6.9 us on 1024x10x256; gpurun_out/gemm_small5.log)
+  // mode: 0 auto | 1 fp32 SIMT | 2 tcgen05 3xTF32 (planes + persistent kernel) | 3 tcgen05 1xTF32 | 4 tcgen05 fused small kernel
+  {
+    const double flops = 2.0 * (double)m * (double)n * (double)k;
+    if (batch == 1 && (mode == 4 || (mode == 0 && flops >= 5.0e7 && flops < 1.0e9))) {
+      const int r = gemm_tc_fused_try(trans_a ? 1 : 0, trans_b ? 1 : 0, m, n, k, a, lda, b, ldb, c, ldc, bias, act, mask, ldmask);
+      if (r < 0) return -r;
+      if (r == 1) return 0;
+    }
+    if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (batched or out of range)", who);
+  }
   if (mode != 1) {
     const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode);
     if (r < 0) return -r;

@@ -501,6 +501,289 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   }
 }
 
+// ------------------------------------------------------------------ step 3: fused small-problem kernel
+// The MLP training step's GEMMs (C4: 1024x256x784 ... 10x256x1024) are 0.005-0.4 GFLOP each: too small for
+// two extra launches that write hi/lo planes, and too few 128x256 tiles to fill 148 SMs.  Here ONE launch
+// does everything for a 128 x 64 tile and one K slice:
+//   all 8 warps : load the fp32 operands straight from global memory (any transpose flags, bounds and
+//                 alignment), split them into TF32 hi/lo in registers and store the four planes into
+//                 shared memory in the K-major SWIZZLE_128B layout the UMMA descriptors expect
+//                 (generic-proxy stores + fence.proxy.async), double buffered, next block's global
+//                 loads in flight under the current MMAs;
+//   one thread  : 3 x tcgen05.mma kind::tf32 128x64x8 per 8-wide k step into a 64-column TMEM accumulator;
+//   warps 0-3   : tcgen05.ld the accumulator into a shared-memory tile;
+//   split-K     : the K axis is spread over a thread-block cluster (<= 8 CTAs); partial tiles are folded
+//                 through distributed shared memory in slice order, and the fused epilogue (bias / relu /
+//                 relu-mask) is applied on the way out.
+constexpr int FM = 128, FN = 64;
+constexpr int F_A_PLANE = FM * TK * 4;                    // 16 KiB
+constexpr int F_B_PLANE = FN * TK * 4;                    // 8 KiB
+constexpr int F_STAGE = 2 * F_A_PLANE + 2 * F_B_PLANE;    // 48 KiB
+constexpr int F_STAGES = 2;
+constexpr int F_PLD = FN + 4;                             // padded row of the partial tile (floats)
+constexpr int F_SMEM = F_STAGES * F_STAGE + 1024 + 128;
+constexpr uint32_t kIdescTf32F = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(FN >> 3) << 17) | ((uint32_t)(FM >> 4) << 24);
+static_assert(FM * F_PLD * 4 <= F_STAGE, "partial tile must fit stage 0");
+
+struct FusedGemmArgs {
+  const float* A; const float* B; float* C;
+  int64_t lda, ldb, ldc;
+  int m, n, k;
+  int ta, tb;
+  int a_vec, b_vec;          // operand rows are 16-byte aligned: 128-bit global loads
+  int ksplit, kchunk;        // cluster size along z, K per slice (multiple of 32)
+  const float* bias; const float* mask; int64_t ldmask; int act;
+};
+
+// byte offset of element (r, k) inside a K-major SWIZZLE_128B plane (128-byte rows, 16-byte chunks XOR r%8)
+__device__ __forceinline__ uint32_t sw128_off(int r, int k) {
+  return (uint32_t)(r * 128 + ((((k >> 2) ^ (r & 7)) << 4) | ((k & 3) << 2)));
+}
+
+// Per-thread view of one operand tile (ROWS x 32 per k-block), fixed for the whole K slice: thread t owns
+// ROWS/32 16-byte chunks.  kmajor (element (r, k) at src[r*ld + k]): a chunk is 4 consecutive k of one row;
+// otherwise ((r, k) at src[k*ld + r]) it is 4 consecutive rows of one k, lanes running along k so that the
+// transposing shared-memory stores are conflict free.  Pointers, swizzled shared-memory offsets and
+// validity are computed once; a k-block then costs one add per chunk.
+template <int ROWS>
+struct FTile {
+  const float* p[ROWS / 32];     // this chunk's first element in the slice's first k-block
+  int nv[ROWS / 32];             // valid elements along the chunk's row axis: kmajor 4 or 0, else 0..4
+  // (k of the chunk's first element inside a k-block and its shared-memory offset are recomputed from
+  //  threadIdx: a few bit operations, cheaper than 12 more live registers)
+  __device__ __forceinline__ int kk_of(int it) const { const int q = threadIdx.x + it * 256; return kmajor ? 4 * (q & 7) : (q & 31); }
+  int64_t step;                  // elements to advance per k-block
+  bool kmajor, vec;
+  __device__ __forceinline__ void init(const float* src, int64_t ld, bool kmaj, bool v, int r0, int rmax, int kbeg) {
+    kmajor = kmaj; vec = v;
+    step = kmaj ? TK : (int64_t)TK * ld;
+#pragma unroll
+    for (int it = 0; it < ROWS / 32; ++it) {
+      const int q = threadIdx.x + it * 256;
+      if (kmaj) {
+        const int c = q & 7, r = q >> 3, gr = r0 + r;
+        nv[it] = gr < rmax ? 4 : 0;
+        p[it] = src + (int64_t)(gr < rmax ? gr : 0) * ld + kbeg + 4 * c;
+      } else {
+        const int k = q & 31, rq = q >> 5, gr = r0 + 4 * rq;
+        nv[it] = gr >= rmax ? 0 : (rmax - gr >= 4 ? 4 : rmax - gr);
+        p[it] = src + (int64_t)(kbeg + k) * ld + (gr < rmax ? gr : 0);
+      }
+    }
+  }
+  // blk: k-block index inside the slice; krem = kend - (kbeg + blk*32) (> 0)
+  __device__ __forceinline__ void load(float4 (&reg)[ROWS / 32], int blk, int krem) const {
+    const bool fullk = krem >= TK;
+#pragma unroll
+    for (int it = 0; it < ROWS / 32; ++it) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float* q = p[it] + blk * step;
+      const int kk = kk_of(it);
+      if (nv[it] == 4 && vec && (fullk || (kmajor ? kk + 3 < krem : kk < krem))) {
+        v = *reinterpret_cast<const float4*>(q);
+      } else if (nv[it] > 0) {
+        if (kmajor) {
+          const int left = krem - kk;
+          if (left > 0) v.x = q[0];
+          if (left > 1) v.y = q[1];
+          if (left > 2) v.z = q[2];
+          if (left > 3) v.w = q[3];
+        } else if (kk < krem) {
+          v.x = q[0];
+          if (nv[it] > 1) v.y = q[1];
+          if (nv[it] > 2) v.z = q[2];
+          if (nv[it] > 3) v.w = q[3];
+        }
+      }
+      reg[it] = v;
+    }
+  }
+  // hi = x with the 13 low mantissa bits cleared (a TF32 number), lo = x - hi (exact).  lo is stored as is: the
+  // tensor core reads 19 bits of it, an error of 2^-10 |lo| <= 2^-20 |x|, the same order as the split itself.
+  __device__ __forceinline__ static void split(float x, float& hi, float& lo) {
+    hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+    lo = (fabsf(x) <= 3.0e38f) ? x - hi : 0.f;           // inf / nan live in hi only
+  }
+  __device__ __forceinline__ void store(const float4 (&reg)[ROWS / 32], uint8_t* hi, uint8_t* lo) const {
+#pragma unroll
+    for (int it = 0; it < ROWS / 32; ++it) {
+      float4 h, l;
+      split(reg[it].x, h.x, l.x); split(reg[it].y, h.y, l.y); split(reg[it].z, h.z, l.z); split(reg[it].w, h.w, l.w);
+      const int q = threadIdx.x + it * 256;
+      if (kmajor) {
+        const uint32_t o = sw128_off(q >> 3, 4 * (q & 7));
+        *reinterpret_cast<float4*>(hi + o) = h;
+        *reinterpret_cast<float4*>(lo + o) = l;
+      } else {
+        const float hh[4] = {h.x, h.y, h.z, h.w}, ll[4] = {l.x, l.y, l.z, l.w};
+        const int k = q & 31, rq = q >> 5;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t o = sw128_off(4 * rq + j, k);
+          *reinterpret_cast<float*>(hi + o) = hh[j];
+          *reinterpret_cast<float*>(lo + o) = ll[j];
+        }
+      }
+    }
+  }
+};
+
+__device__ __forceinline__ float f_epilogue(const FusedGemmArgs& g, float v, int64_t gm, int64_t gn) {
+  if (g.bias) v = __fadd_rn(v, g.bias[gn]);
+  if (g.act == 1) v = __fmul_rn(v, v > 0.f ? 1.f : 0.f);
+  if (g.mask) v = __fmul_rn(v, g.mask[gm * g.ldmask + gn] > 0.f ? 1.f : 0.f);
+  return v;
+}
+
+__global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_constant__ FusedGemmArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* freed = reinterpret_cast<uint64_t*>(smem + F_STAGES * F_STAGE);   // [2] MMAs that read stage s have retired
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(freed + F_STAGES);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ks = (int)blockIdx.z;                       // grid.z == ksplit == cluster size
+  const int m0 = blockIdx.y * FM, n0 = blockIdx.x * FN;
+  const int kbeg = ks * g.kchunk;
+  const int kend = min(g.k, kbeg + g.kchunk);
+  const int nkb = kend > kbeg ? (kend - kbeg + TK - 1) / TK : 0;
+  const bool a_kmajor = !g.ta, b_kmajor = g.tb != 0;    // A is (m k) row-major unless transposed; B^T is (n k) when tb
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < F_STAGES; ++s) mbar_init(&freed[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(64) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // K blocks are taken in groups of 4: the global loads of a group are issued before its first conversion, so
+  // the global-memory latency is paid once per 128 k (with the usual K slice of <= 128 per CTA: once).
+  constexpr int GB = 4;
+  FTile<FM> ta_;
+  FTile<FN> tb_;
+  ta_.init(g.A, g.lda, a_kmajor, g.a_vec != 0, m0, g.m, kbeg);
+  tb_.init(g.B, g.ldb, b_kmajor, g.b_vec != 0, n0, g.n, kbeg);
+  uint32_t ph0 = 0, ph1 = 0;                            // parity of freed[0] / freed[1]
+  for (int kg = 0; kg < nkb; kg += GB) {
+    float4 ra[GB][FM / 32], rb[GB][FN / 32];
+#pragma unroll
+    for (int u = 0; u < GB; ++u)
+      if (kg + u < nkb) {
+        const int krem = kend - (kbeg + (kg + u) * TK);
+        ta_.load(ra[u], kg + u, krem);
+        tb_.load(rb[u], kg + u, krem);
+      }
+#pragma unroll
+    for (int u = 0; u < GB; ++u) {
+      const int kb = kg + u;
+      if (kb < nkb) {                                   // uniform across the CTA
+        const int s = kb & 1;
+        uint8_t* st = smem + s * F_STAGE;
+        if (kb >= F_STAGES) {                           // the MMAs of block kb-2 must be done reading this stage
+          if (s == 0) { mbar_wait(&freed[0], ph0); ph0 ^= 1; } else { mbar_wait(&freed[1], ph1); ph1 ^= 1; }
+          tc_fence_after();
+        }
+        ta_.store(ra[u], st, st + F_A_PLANE);
+        tb_.store(rb[u], st + 2 * F_A_PLANE, st + 2 * F_A_PLANE + F_B_PLANE);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          tc_fence_after();
+          const uint32_t sa = smem_u32(st);
+          const uint64_t dah = make_desc_sw128(sa), dal = make_desc_sw128(sa + F_A_PLANE);
+          const uint64_t dbh = make_desc_sw128(sa + 2 * F_A_PLANE), dbl = make_desc_sw128(sa + 2 * F_A_PLANE + F_B_PLANE);
+#pragma unroll
+          for (int k = 0; k < TK / UK; ++k) {
+            const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
+            tc_mma_tf32(tmem_base, dal + adv, dbh + adv, kIdescTf32F, (kb | k) != 0);
+            tc_mma_tf32(tmem_base, dah + adv, dbl + adv, kIdescTf32F, 1);
+            tc_mma_tf32(tmem_base, dah + adv, dbh + adv, kIdescTf32F, 1);
+          }
+          tc_commit(&freed[s]);
+        }
+      }
+    }
+  }
+  // ---- all MMAs retired?  (the last commit covers every earlier one)
+  if (nkb > 0) {
+    // commits retire in order, so waiting for the last block's commit covers every MMA; the other
+    // stage's last phase is consumed too so that no arrival is left pending
+    if (nkb >= 2) { mbar_wait(&freed[0], ph0); mbar_wait(&freed[1], ph1); }
+    else mbar_wait(&freed[0], ph0);
+    tc_fence_after();
+  }
+  __syncthreads();
+  // ---- accumulator -> shared-memory partial tile Ps[128][F_PLD] (stage 0 is free now)
+  float* Ps = reinterpret_cast<float*>(smem);
+  if (warp < 4) {
+    const int row = warp * 32 + lane;
+    float* pr = Ps + row * F_PLD;
+    if (nkb > 0) {
+      const uint32_t tbase = tmem_base + ((uint32_t)(warp * 32) << 16);
+#pragma unroll
+      for (int c = 0; c < FN / 32; ++c) {
+        uint32_t v[32];
+        tc_ld32(tbase + c * 32, v);
+        tc_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(pr + c * 32 + 4 * j) =
+              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < FN / 4; ++j) *reinterpret_cast<float4*>(pr + 4 * j) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  tc_fence_before();
+  // ---- fold the K slices (cluster) and write C
+  const int ksplit = g.ksplit;
+  if (ksplit > 1) {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  } else {
+    __syncthreads();
+  }
+  const int rows_per = FM / ksplit;                     // this CTA writes rows [ks*rows_per, (ks+1)*rows_per) of the tile
+  for (int e = threadIdx.x; e < rows_per * (FN / 4); e += 256) {
+    const int r = ks * rows_per + e / (FN / 4), c4 = (e % (FN / 4)) * 4;
+    const uint32_t local = smem_u32(Ps + r * F_PLD + c4);
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p = 0; p < ksplit; ++p) {
+      float4 o;
+      if (ksplit > 1) {
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(p));
+        asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w) : "r"(remote) : "memory");
+      } else {
+        o = *reinterpret_cast<const float4*>(Ps + r * F_PLD + c4);
+      }
+      if (p == 0) t = o;
+      else { t.x = __fadd_rn(t.x, o.x); t.y = __fadd_rn(t.y, o.y); t.z = __fadd_rn(t.z, o.z); t.w = __fadd_rn(t.w, o.w); }
+    }
+    const int64_t gm = m0 + r, gn = n0 + c4;
+    if (gm < g.m) {
+      float* cp = g.C + gm * g.ldc + gn;
+      const float v[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (gn + j < g.n) cp[j] = f_epilogue(g, v[j], gm, gn + j);
+    }
+  }
+  if (ksplit > 1)   // nobody leaves (or frees its shared memory) while a peer may still read its tile
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(64) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -622,6 +905,47 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   const int grid = (int)(total < S().sm_count ? total : S().sm_count);
   gemm_tc_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, t);
   rc = post_launch("wf2cu_gemm(tcgen05)");
+  return rc ? -rc : 1;
+}
+
+// returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
+int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
+                      float* C, int64_t ldc, const float* bias, int act, const float* mask, int64_t ldmask) {
+  if (m < 1 || n < 1 || k < 1 || m > (1 << 24) || n > (1 << 24) || k > (1 << 24)) return 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
+    if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_tc_fused_kernel)", __FILE__, __LINE__);
+    attr_set = true;
+  }
+  const int64_t tiles = ((m + FM - 1) / FM) * ((n + FN - 1) / FN);
+  if (tiles > 65535 * 4) return 0;
+  const int nkb_total = (int)((k + TK - 1) / TK);
+  int ksplit = 1;
+  // spread K over a cluster while the grid is below ~2 CTAs per SM and every slice keeps >= 2 k-blocks
+  while (ksplit < 8 && tiles * ksplit * 2 <= (int64_t)S().sm_count * 2 && nkb_total / (ksplit * 2) >= 2) ksplit *= 2;
+  const int kchunk = ((nkb_total + ksplit - 1) / ksplit) * TK;
+  FusedGemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = A; g.B = B; g.C = C; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.m = (int)m; g.n = (int)n; g.k = (int)k; g.ta = ta; g.tb = tb;
+  g.a_vec = ((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (lda & 3) == 0) ? 1 : 0;
+  g.b_vec = ((reinterpret_cast<uintptr_t>(B) & 15) == 0 && (ldb & 3) == 0) ? 1 : 0;
+  g.ksplit = ksplit; g.kchunk = kchunk;
+  g.bias = bias; g.mask = mask; g.ldmask = ldmask; g.act = act;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)((n + FN - 1) / FN), (unsigned)((m + FM - 1) / FM), (unsigned)ksplit);
+  cfg.blockDim = dim3(256, 1, 1);
+  cfg.dynamicSmemBytes = F_SMEM;
+  cfg.stream = S().stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)ksplit;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_fused_kernel, g);
+  if (e != cudaSuccess) return -cuda_fail(e, "cudaLaunchKernelEx(gemm_tc_fused_kernel)", __FILE__, __LINE__);
+  const int rc = post_launch("wf2cu_gemm(tcgen05 fused)");
   return rc ? -rc : 1;
 }
 

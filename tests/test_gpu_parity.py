@@ -384,6 +384,33 @@ def test_matmul_tcgen05_3xtf32(tensor_gemm, ta, tb, m, n, k):
     assert err <= 2e-5, err
 
 
+@pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("m,n,k", [(3, 5, 4), (128, 64, 32), (130, 70, 33), (100, 300, 77), (1024, 256, 784), (10, 256, 1024),
+                                   (256, 784, 1024), (64, 64, 4096), (257, 129, 300)])
+def test_matmul_tcgen05_fused_small_kernel(gpu, ta, tb, m, n, k):
+    """mode 4: the one-launch tcgen05 kernel (in-kernel hi/lo split into swizzled shared memory, cluster
+    split-K folded through DSMEM) on ragged and transposed shapes; bar 1e-4 (north_star), measured ~1e-6."""
+    import ctypes as C
+    lib = gpu._lib.load()
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(4))
+    try:
+        rng = np.random.default_rng(m * 7 + n * 3 + k)
+        A = rng.uniform(-1, 1, size=((k, m) if ta else (m, k))).astype(np.float32)
+        B = rng.uniform(-1, 1, size=((n, k) if tb else (k, n))).astype(np.float32)
+        ga, gb = gpu.from_numpy(A), gpu.from_numpy(B)
+        r = gpu.ops.matmul(gpu.ops.t(ga) if ta else ga, gpu.ops.t(gb) if tb else gb).to_numpy()
+        truth = (A.T if ta else A).astype(np.float64) @ (B.T if tb else B).astype(np.float64)
+        err = np.abs(r - truth).max() / np.abs(truth).max()
+        assert err <= 2e-5, err
+        # special values stay where they belong: an inf in A poisons exactly its row
+        if m >= 3 and not ta:
+            A2 = A.copy(); A2[1, 0] = np.inf
+            r2 = gpu.ops.matmul(gpu.from_numpy(A2), gpu.ops.t(gb) if tb else gb).to_numpy()
+            assert np.isfinite(r2[0]).all() and not np.isfinite(r2[1]).any()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+
+
 def test_matmul_tcgen05_batched_and_shared_operand(tensor_gemm):
     gpu = tensor_gemm
     A = RNG.uniform(-1, 1, size=(2, 3, 200, 96)).astype(np.float32)
