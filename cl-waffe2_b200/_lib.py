@@ -45,6 +45,7 @@ PROTOTYPES = {
     "wf2cu_timer_start": [], "wf2cu_timer_stop": [C.POINTER(f32)], "wf2cu_l2_flush": [],
     "wf2cu_graph_begin": [], "wf2cu_graph_end": [C.POINTER(vp)], "wf2cu_graph_launch": [vp],
     "wf2cu_graph_destroy": [vp],
+    "wf2cu_branch_begin": [i32], "wf2cu_branch_end": [i32], "wf2cu_branch_join": [i32],
     "wf2cu_ew_binary": [i32, VP, VP], "wf2cu_ew_binary3": [i32, VP, VP, VP], "wf2cu_ew_scalar": [i32, VP, f32],
     "wf2cu_fill": [VP, f32], "wf2cu_ew_unary": [i32, VP, VP], "wf2cu_pow": [VP, VP, f32],
     "wf2cu_cmp": [i32, VP, VP, f32, VP, f32, f32], "wf2cu_fused": [C.POINTER(C.c_int32), i32, VP, i32],

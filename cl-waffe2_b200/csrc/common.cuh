@@ -11,6 +11,8 @@ namespace wf2 {
 
 constexpr int kMaxRank = WF2CU_MAX_RANK;
 constexpr int kNumSMs = 148;  // B200
+constexpr int kBranches = 4;   // main + 3 side streams; each owns a quarter of the scratch buffer and of the tickets
+constexpr int kCountersPerBranch = 4096;
 
 struct State {
   bool inited = false;
@@ -27,6 +29,11 @@ struct State {
   std::atomic<int64_t> launches{0};
   std::atomic<size_t> bytes_in_use{0};
   int gemm_mode = 0;
+  // side branches (wf2cu_branch_begin/end/join): independent work of a compiled step on its own stream
+  cudaStream_t main_stream = nullptr;             // where launches return to after wf2cu_branch_end
+  cudaStream_t side[kBranches] = {};
+  cudaEvent_t fork_ev[kBranches] = {}, join_ev[kBranches] = {};
+  int branch = 0;                                 // 0 = main, 1..kBranches-1 = side
 };
 State& S();
 
@@ -59,7 +66,9 @@ inline int post_launch(const char* name) {
   return 0;
 }
 
-int ensure_scratch(size_t bytes);
+int ensure_scratch(size_t bytes);           // per branch: the buffer holds kBranches regions of at least `bytes`
+void* scratch_base();                        // the current branch's region (valid after ensure_scratch)
+unsigned int* counters_base();               // the current branch's kCountersPerBranch tickets
 void gemm_tc_release();   // gemm_tc.cu: frees the hi/lo plane workspaces
 
 inline float* fptr(const wf2cu_view* v) { return reinterpret_cast<float*>(v->base) + v->offset; }

@@ -849,6 +849,9 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode) {
   // mode: 0 auto, 2 force 3xTF32, 3 force 1xTF32
   if (k < 1 || m > (1 << 30) || n > (1 << 30) || k > (1 << 30) || batch > 65535) return 0;
+  // the hi/lo plane workspace is one buffer: only the main stream may use it (a side branch of a compiled
+  // step takes the SIMT / fused kernels instead)
+  if (S().branch != 0) return 0;
   if (mode == 0) {
     // the tensor path pays two extra passes over the operands and wants >= 1 wave of 128x256 tiles
     if (m < 64 || n < 64 || k < 32) return 0;

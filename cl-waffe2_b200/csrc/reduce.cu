@@ -702,7 +702,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
       if (grid > nchunks) grid = nchunks;
       rc = ensure_scratch((size_t)grid * sizeof(float));
       if (rc) return rc;
-      FlatArgs f{sptr, dptr, (float*)s.scratch, s.counters, a.cols};
+      FlatArgs f{sptr, dptr, (float*)scratch_base(), counters_base(), a.cols};
       kfn<<<(unsigned)grid, kFlatThreads, kFlatStages * kFlatChunk, s.stream>>>(f, fin);
       return post_launch(who);
     }
@@ -745,8 +745,8 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
       if (chunks > 1) {
         rc = ensure_scratch((size_t)rows * chunks * sizeof(float));
         if (rc) return rc;
-        a.partial = (float*)s.scratch;
-        a.counters = s.counters;
+        a.partial = (float*)scratch_base();
+        a.counters = counters_base();
       }
       reduce_rows_kernel<M, 256><<<(unsigned)(rows * chunks), 256, 0, s.stream>>>(a, fin);
       return post_launch(who);
@@ -791,8 +791,8 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
       if (splits > 1) {
         rc = ensure_scratch((size_t)a.B * splits * a.K * sizeof(float));
         if (rc) return rc;
-        a.partial = (float*)s.scratch;
-        a.counters = fused2 ? s.counters : nullptr;
+        a.partial = (float*)scratch_base();
+        a.counters = fused2 ? counters_base() : nullptr;
       }
       dim3 grid((unsigned)colblocks, (unsigned)splits, (unsigned)a.B);
       reduce_cols_kernel<M><<<grid, 256, 0, s.stream>>>(a, fin);

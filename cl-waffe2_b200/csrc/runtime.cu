@@ -31,14 +31,22 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
 
 int ensure_scratch(size_t bytes) {
   State& s = S();
-  if (s.scratch_bytes >= bytes) return 0;
+  bytes = (bytes + 255) & ~size_t(255);
+  if (s.scratch_bytes / kBranches >= bytes) return 0;
   // Growing while a graph is being captured is not allowed; callers size for the worst case up front.
   if (s.scratch) WF2_CUDA(cudaFree(s.scratch));
-  size_t want = bytes < (size_t(8) << 20) ? (size_t(8) << 20) : bytes;
+  size_t want = bytes * kBranches < (size_t(8) << 20) ? (size_t(8) << 20) : bytes * kBranches;
   WF2_CUDA(cudaMalloc(&s.scratch, want));
   s.scratch_bytes = want;
   return 0;
 }
+
+void* scratch_base() {
+  State& s = S();
+  return (char*)s.scratch + (size_t)s.branch * ((s.scratch_bytes / kBranches) & ~size_t(255));
+}
+
+unsigned int* counters_base() { return S().counters + (size_t)S().branch * kCountersPerBranch; }
 
 // ---- plan building: drop extent-1 axes, merge neighbours that are jointly contiguous ---------
 int build_plan(const wf2cu_view* const* views, int n, Plan* out, const char* who) {
@@ -146,8 +154,14 @@ int wf2cu_init(int device) {
   s.stream = s.own_stream;
   WF2_CUDA(cudaEventCreate(&s.ev0));
   WF2_CUDA(cudaEventCreate(&s.ev1));
-  WF2_CUDA(cudaMalloc(&s.counters, 4096 * sizeof(unsigned int)));
-  WF2_CUDA(cudaMemset(s.counters, 0, 4096 * sizeof(unsigned int)));
+  WF2_CUDA(cudaMalloc(&s.counters, (size_t)kBranches * kCountersPerBranch * sizeof(unsigned int)));
+  WF2_CUDA(cudaMemset(s.counters, 0, (size_t)kBranches * kCountersPerBranch * sizeof(unsigned int)));
+  for (int b = 1; b < kBranches; ++b) {
+    WF2_CUDA(cudaStreamCreateWithFlags(&s.side[b], cudaStreamNonBlocking));
+    WF2_CUDA(cudaEventCreateWithFlags(&s.fork_ev[b], cudaEventDisableTiming));
+    WF2_CUDA(cudaEventCreateWithFlags(&s.join_ev[b], cudaEventDisableTiming));
+  }
+  s.branch = 0;
   int rc = ensure_scratch(size_t(8) << 20);
   if (rc) return rc;
   s.inited = true;
@@ -169,6 +183,12 @@ int wf2cu_shutdown(void) {
   if (s.l2flush) cudaFree(s.l2flush);
   s.scratch = nullptr; s.scratch_bytes = 0; s.counters = nullptr; s.l2flush = nullptr; s.l2flush_bytes = 0;
   cudaEventDestroy(s.ev0); cudaEventDestroy(s.ev1);
+  for (int b = 1; b < kBranches; ++b) {
+    if (s.side[b]) { cudaStreamSynchronize(s.side[b]); cudaStreamDestroy(s.side[b]); s.side[b] = nullptr; }
+    if (s.fork_ev[b]) { cudaEventDestroy(s.fork_ev[b]); s.fork_ev[b] = nullptr; }
+    if (s.join_ev[b]) { cudaEventDestroy(s.join_ev[b]); s.join_ev[b] = nullptr; }
+  }
+  s.branch = 0;
   cudaStreamDestroy(s.own_stream);
   s.own_stream = s.stream = nullptr;
   s.inited = false;
@@ -388,6 +408,46 @@ int wf2cu_graph_destroy(void* exec) {
     std::lock_guard<std::mutex> lk(g_mu);
     graph_launches().erase(exec);
   }
+  return 0;
+}
+
+// ---- side branches: independent launches of a compiled step on their own stream ------------------
+// The reference's VM executes a compiled instruction sequence strictly in order (vm/vm.lisp:260-289).  On a
+// GPU, instructions with no data dependence between them (the weight-gradient GEMM and the bias-gradient
+// reduction of a layer vs. the input-gradient GEMM the next backward node waits for) can overlap: each is
+// far too small to fill 148 SMs.  begin(b): launches from now on go to side stream b, ordered after
+// everything issued so far; end(b): back to the main stream; join(b): the main stream waits for branch b.
+// Inside wf2cu_graph_begin/end these become graph edges (fork/join), so the replayed graph runs the branches
+// concurrently.  Each branch has its own quarter of the reduction scratch and tickets.
+int wf2cu_branch_begin(int b) {
+  WF2_REQUIRE_INIT();
+  State& s = S();
+  WF2_CHECK(b >= 1 && b < kBranches, "wf2cu_branch_begin: branch %d not in 1..%d", b, kBranches - 1);
+  WF2_CHECK(s.branch == 0, "wf2cu_branch_begin: branch %d is still open (branches do not nest)", s.branch);
+  s.main_stream = s.stream;
+  WF2_CUDA(cudaEventRecord(s.fork_ev[b], s.main_stream));
+  WF2_CUDA(cudaStreamWaitEvent(s.side[b], s.fork_ev[b], 0));
+  s.stream = s.side[b];
+  s.branch = b;
+  return 0;
+}
+
+int wf2cu_branch_end(int b) {
+  WF2_REQUIRE_INIT();
+  State& s = S();
+  WF2_CHECK(b >= 1 && b < kBranches && s.branch == b, "wf2cu_branch_end: branch %d is not the open branch (%d)", b, s.branch);
+  WF2_CUDA(cudaEventRecord(s.join_ev[b], s.side[b]));
+  s.stream = s.main_stream;
+  s.branch = 0;
+  return 0;
+}
+
+int wf2cu_branch_join(int b) {
+  WF2_REQUIRE_INIT();
+  State& s = S();
+  WF2_CHECK(b >= 1 && b < kBranches, "wf2cu_branch_join: branch %d not in 1..%d", b, kBranches - 1);
+  WF2_CHECK(s.branch == 0, "wf2cu_branch_join: close branch %d first", s.branch);
+  WF2_CUDA(cudaStreamWaitEvent(s.stream, s.join_ev[b], 0));
   return 0;
 }
 

@@ -411,8 +411,8 @@ extern "C" int wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* l
   int rc = ensure_scratch((size_t)grid * sizeof(float));
   if (rc) return rc;
   State& s = S();
-  SceArgs a{(const float*)x + x_off, (const float*)labels + l_off, (float*)z + z_off, (float*)loss + loss_off, (float*)s.scratch,
-            s.counters + 4095, rows, cols, delta};
+  SceArgs a{(const float*)x + x_off, (const float*)labels + l_off, (float*)z + z_off, (float*)loss + loss_off, (float*)scratch_base(),
+            counters_base() + 4095, rows, cols, delta};
   sce_sum_forward_kernel<<<(unsigned)grid, 256, 0, s.stream>>>(a);
   return post_launch("wf2cu_sce_sum_forward");
 }

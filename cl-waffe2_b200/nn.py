@@ -51,6 +51,17 @@ _tape: Optional[Tape] = None
 # `(!sum (softmax-cross-entropy ...))` is one kernel forward and one backward.  FUSE = False issues one
 # launch per node, exactly as the unfused instruction sequence would (both are tested against the oracle).
 FUSE = True
+# Independent backward instructions on side streams (wf2cu_branch_*): a layer's weight-gradient GEMM and
+# bias-gradient reduction run beside the input-gradient GEMM that the next backward node waits for.
+CONCURRENT = True
+_open_branches: List[int] = []
+
+
+def _join_branches() -> None:
+    lib = _lib.load()
+    for b in _open_branches:
+        _lib.check(lib.wf2cu_branch_join(b))
+    _open_branches.clear()
 
 
 def _tracked(t: CUDATensor) -> bool:
@@ -113,15 +124,36 @@ def linear(x: CUDATensor, weight: CUDATensor, bias: Optional[CUDATensor], fuse_r
 
         def bw():
             dout = out.grad
+            lib = _lib.load()
+
             # MatMulNode backward: dA = dout . B^T, dB = A^T . dout with B = (!t W)
-            _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
-            _accumulate(weight, lambda g, acc: _gemm_into(g, acc, ops.t(dout), x))
-            if bias is not None:
-                # the (!flexible bias) broadcast view accumulates dout over the batch axis
-                def bias_grad(g, acc):
-                    gb = view(_as_row(g), [":broadcast", dout.shape[0]], True)
-                    _lib.check(_lib.load().wf2cu_reduce_sum(C.byref(dout.lower()), C.byref(gb.lower()), 1 if acc else 0, 0.0))
-                _accumulate(bias, bias_grad)
+            def param_grads():
+                _accumulate(weight, lambda g, acc: _gemm_into(g, acc, ops.t(dout), x))
+                if bias is not None:
+                    # the (!flexible bias) broadcast view accumulates dout over the batch axis
+                    def bias_grad(g, acc):
+                        gb = view(_as_row(g), [":broadcast", dout.shape[0]], True)
+                        _lib.check(lib.wf2cu_reduce_sum(C.byref(dout.lower()), C.byref(gb.lower()), 1 if acc else 0, 0.0))
+                    _accumulate(bias, bias_grad)
+
+            branch = 0
+            if CONCURRENT and _tracked(x):
+                branch = 1 + len(_open_branches) % 3
+                if branch in _open_branches:          # more than 3 layers in flight: wait for the oldest user
+                    _lib.check(lib.wf2cu_branch_join(branch))
+                    _open_branches.remove(branch)
+            if branch:
+                # nobody but the optimizer waits for dW / db: side stream; dX stays on the main stream
+                _lib.check(lib.wf2cu_branch_begin(branch))
+                try:
+                    param_grads()
+                finally:
+                    _lib.check(lib.wf2cu_branch_end(branch))
+                _open_branches.append(branch)
+                _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
+            else:
+                _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
+                param_grads()
         _tape.nodes.append(bw)
     return out
 
@@ -509,6 +541,7 @@ class CompiledStep:
                 loss._has_grad = True
                 for node in reversed(self.tape.nodes):
                     node()
+                _join_branches()               # every gradient is complete before the exchange / optimizer
                 if self.world > 1 and self.exchange == "p2p":
                     self.opt.step_p2p()         # exchange + 1/world + Adam in one kernel over peer memory
                 else:

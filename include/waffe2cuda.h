@@ -117,6 +117,13 @@ int  wf2cu_graph_begin(void);
 int  wf2cu_graph_end(void** out_exec);
 int  wf2cu_graph_launch(void* exec);
 int  wf2cu_graph_destroy(void* exec);
+/* Side branches of a compiled step (replaces nothing in the reference: its VM runs the instruction
+ * sequence in order, `vm/vm.lisp:260-289`; independent instructions overlap here).  begin(b), b = 1..3:
+ * following launches go to side stream b, ordered after everything issued so far; end(b): back to the main
+ * stream; join(b): the main stream waits for branch b.  Captured as fork/join edges by wf2cu_graph_begin/end. */
+int  wf2cu_branch_begin(int b);
+int  wf2cu_branch_end(int b);
+int  wf2cu_branch_join(int b);
 
 /* ===================== element-wise ===================== */
 /* dst <- dst OP src over views of equal shape.  Axes where dst has stride 0 and extent > 1 are

@@ -42,10 +42,10 @@ def fuse(request, gpu):
     """Both instruction sequences: with the backend's node fusions (GEMM epilogues, one-kernel loss) and
     one launch per node."""
     nn = _nn(gpu)
-    old = nn.FUSE
-    nn.FUSE = request.param
+    old = (nn.FUSE, nn.CONCURRENT)
+    nn.FUSE = nn.CONCURRENT = request.param      # fused + side-stream branches  vs  strictly in-order, one launch per node
     yield request.param
-    nn.FUSE = old
+    nn.FUSE, nn.CONCURRENT = old
 
 
 @pytest.mark.parametrize("use_graph", [True, False])
