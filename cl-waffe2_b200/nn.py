@@ -151,6 +151,24 @@ def linear(x: CUDATensor, weight: CUDATensor, bias: Optional[CUDATensor], fuse_r
                     _lib.check(lib.wf2cu_branch_end(branch))
                 _open_branches.append(branch)
                 _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
+            elif CONCURRENT and bias is not None:
+                # first layer (no dX): the bias-gradient reduction runs beside the weight-gradient GEMM
+                branch = 1 + len(_open_branches) % 3
+                if branch in _open_branches:
+                    _lib.check(lib.wf2cu_branch_join(branch))
+                    _open_branches.remove(branch)
+
+                def bias_grad1(g, acc):
+                    gb = view(_as_row(g), [":broadcast", dout.shape[0]], True)
+                    _lib.check(lib.wf2cu_reduce_sum(C.byref(dout.lower()), C.byref(gb.lower()), 1 if acc else 0, 0.0))
+                _lib.check(lib.wf2cu_branch_begin(branch))
+                try:
+                    _accumulate(bias, bias_grad1)
+                finally:
+                    _lib.check(lib.wf2cu_branch_end(branch))
+                _open_branches.append(branch)
+                _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
+                _accumulate(weight, lambda g, acc: _gemm_into(g, acc, ops.t(dout), x))
             else:
                 _accumulate(x, lambda g, acc: _gemm_into(g, acc, dout, weight, target=x))
                 param_grads()
@@ -535,9 +553,24 @@ class CompiledStep:
         _tape = self.tape
         try:
             with self.pool:
+                seed = None
+                if CONCURRENT:
+                    # the backward seed (dL/dL = 1) does not depend on the forward pass: side stream, joined before backward
+                    seed = make_tensor([1, 1])
+                    _lib.check(lib.wf2cu_branch_begin(3))
+                    try:
+                        ops.fill_(seed, 1.0)
+                    finally:
+                        _lib.check(lib.wf2cu_branch_end(3))
                 loss = self._loss(self.model(self.x))
-                loss.grad = make_tensor(loss.shape)
-                ops.fill_(loss.grad, 1.0)
+                if seed is not None and loss.shape == seed.shape:
+                    _lib.check(lib.wf2cu_branch_join(3))
+                    loss.grad = seed
+                else:
+                    if seed is not None:
+                        _lib.check(lib.wf2cu_branch_join(3))
+                    loss.grad = make_tensor(loss.shape)
+                    ops.fill_(loss.grad, 1.0)
                 loss._has_grad = True
                 for node in reversed(self.tape.nodes):
                     node()
