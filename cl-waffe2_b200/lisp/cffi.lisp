@@ -43,7 +43,17 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 sync ())
 (defwf2 device-name ((buf :pointer) (buflen :size)))
 (defwf2 launch-count ((out :pointer)))
+(defwf2 device-count ((out :pointer)))
+(defwf2 stream ((out :pointer)))
+(defwf2 set-stream ((stream :pointer)))
+(defwf2 timer-start ())
+(defwf2 timer-stop ((out-ms :pointer)))
+(defwf2 l2-flush ())
+(defwf2 mem-in-use ((out :pointer)))
 ;; storage
+(defwf2 free ((dev :pointer)))
+(defwf2 host-alloc ((bytes :size) (out :pointer)))
+(defwf2 host-free ((host :pointer)))
 (defwf2 malloc ((bytes :size) (out :pointer)))
 (defwf2 retain ((dev :pointer)))
 (defwf2 release ((dev :pointer)))
@@ -58,6 +68,10 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 graph-end ((out-exec :pointer)))
 (defwf2 graph-launch ((exec :pointer)))
 (defwf2 graph-destroy ((exec :pointer)))
+;; side branches of a compiled step (fork/join edges inside a captured graph)
+(defwf2 branch-begin ((b :int)))
+(defwf2 branch-end ((b :int)))
+(defwf2 branch-join ((b :int)))
 ;; element-wise
 (defwf2 ew-binary ((op :int) (dst :pointer) (src :pointer)))
 (defwf2 ew-binary3 ((op :int) (out :pointer) (a :pointer) (b :pointer)))
@@ -78,6 +92,19 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 	      (b :pointer) (b-off :int64) (ldb :int64)
 	      (c :pointer) (c-off :int64) (ldc :int64)
 	      (batch :int64) (stride-a :int64) (stride-b :int64) (stride-c :int64)))
+;; MatMulNode + the node after it (bias add, !relu, !relu backward mask) in the epilogue
+(defwf2 gemm-ex ((trans-a :int) (trans-b :int) (m :int64) (n :int64) (k :int64)
+		 (a :pointer) (a-off :int64) (lda :int64)
+		 (b :pointer) (b-off :int64) (ldb :int64)
+		 (c :pointer) (c-off :int64) (ldc :int64)
+		 (bias :pointer) (bias-off :int64) (act :int)
+		 (mask :pointer) (mask-off :int64) (ldmask :int64)))
+;; (!sum (softmax-cross-entropy x labels)) forward / sce-diff-static backward
+(defwf2 sce-sum-forward ((x :pointer) (x-off :int64) (labels :pointer) (l-off :int64) (z :pointer) (z-off :int64)
+			 (loss :pointer) (loss-off :int64) (rows :int64) (cols :int64) (delta :float)))
+(defwf2 sce-backward ((z :pointer) (z-off :int64) (labels :pointer) (l-off :int64) (dy :pointer) (dy-off :int64)
+		      (dx :pointer) (dx-off :int64) (rows :int64) (cols :int64) (accumulate :int)))
+(defwf2 gemm-set-mode ((mode :int)))
 ;; optimizers
 (defwf2 sgd-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64) (n :int64) (lr :float)))
 (defwf2 adam-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64)
@@ -89,6 +116,16 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 comm-init ((rank :int) (world :int) (id128 :pointer)))
 (defwf2 allreduce-sum-f32 ((buf :pointer) (offset :int64) (count :int64)))
 (defwf2 comm-destroy ())
+;; exchange + Adam as one kernel over NVLink peer memory (CUDA IPC, one process per GPU)
+(defwf2 p2p-export ((dev-alloc :pointer) (handle64 :pointer)))
+(defwf2 p2p-signal-export ((handle64 :pointer)))
+(defwf2 p2p-attach ((rank :int) (world :int) (local-grad :pointer) (local-param :pointer)
+		    (grad-handles :pointer) (param-handles :pointer) (signal-handles :pointer)))
+(defwf2 p2p-allreduce-adam-step ((param :pointer) (p-off :int64) (g-off :int64) (m :pointer) (m-off :int64)
+				 (v :pointer) (v-off :int64) (n :int64) (lr-t :float) (lr-t-dev :pointer)
+				 (beta1 :float) (beta2 :float) (eps :float)))
+(defwf2 p2p-status ((timed-out :pointer)))
+(defwf2 p2p-detach ())
 
 ;; enums of waffe2cuda.h
 (defconstant +add+ 0) (defconstant +sub+ 1) (defconstant +mul+ 2) (defconstant +div+ 3) (defconstant +copy+ 4)

@@ -8,6 +8,10 @@
 ;;;;   2. Scalar->MatNode feeding a (:broadcast ..) operand of an arithmetic node
 ;;;;      (`fundamental.lisp:525-533`, `arithmetic.lisp:244-250`) -> wf2cu_ew_scalar with the host number
 ;;;;      as a kernel argument (no 4-byte H2D, SURVEY §7 hard part e).
+;;;;   3. MatMulNode followed by the in-place AddNode of LinearLayer's `(!flexible bias)` operand
+;;;;      (`nn/regression.lisp:14-18`) -> one wf2cu_gemm_ex with the bias in the epilogue (the `!relu` after
+;;;;      it and the `!relu` backward mask take the same entry point: act = 1 / mask; the Python host,
+;;;;      cl-waffe2_b200/nn.py, exercises all three).
 ;;;; Everything else is left as generated; each remaining instruction is already one kernel.
 (in-package :cl-waffe2/backends.cuda)
 
@@ -47,10 +51,68 @@
 		 (push i0 out)))
 	finally (return (nreverse out))))
 
+(defun bias-operand-p (tensor n)
+  "T when TENSOR is a rank-2 view whose row axis is (:broadcast _) over a contiguous N-element vector:
+what `(!flexible bias)` becomes inside `step-linear` (`nn/regression.lisp:14-18`)."
+  (and (typep tensor 'CUDATensor)
+       (= (dims tensor) 2)
+       (subscript-broadcast (first (tensor-view tensor)))
+       (= (observe (second (shape tensor))) n)
+       (eql (observe (second (tensor-stride tensor))) 1)))
+
+(defun fuse-matmul+bias (iseq)
+  "out <- MatMul(a, b, out) ; out <- Add(out, bias*)   ==>   out <- gemm_ex(a, b, out, bias)"
+  (loop with result = nil
+	while iseq
+	do (let* ((i0 (pop iseq))
+		  (i1 (car iseq)))
+	     (if (and i1
+		      (typep (wf/vm:wfop-node i0) 'MatMulNode)
+		      (typep (wf/vm:wfop-node i1) 'AddNode)
+		      (cuda-inst-p i0) (cuda-inst-p i1)
+		      (null (wf/vm:wfop-sv4bw i1))
+		      (= (dims (third (wf/vm:wfop-args i0))) 2)
+		      (eq (first (wf/vm:wfop-out-to i0)) (first (wf/vm:wfop-args i1)))
+		      (bias-operand-p (second (wf/vm:wfop-args i1))
+				      (observe (second (shape (third (wf/vm:wfop-args i0)))))))
+		 (let ((node (wf/vm:wfop-node i0))
+		       (bias (second (wf/vm:wfop-args i1))))
+		   (pop iseq)
+		   (setf (wf/vm:wfop-args i1) (append (wf/vm:wfop-args i0) (list bias))
+			 (wf/vm:wfop-op i1)
+			 #'(lambda (a b out bias)
+			     (let* ((ta (trans-a? node)) (tb (trans-b? node))
+				    (a* (if ta (read-untransposed a) a))
+				    (b* (if tb (read-untransposed b) b))
+				    (m (observe (first (shape out)))) (n (observe (second (shape out))))
+				    (k (observe (car (last (shape a))))))
+			       (with-lowered-views ((av a*) (bv b*) (cv out) (biasv bias))
+				 (flet ((off (v) (foreign-slot-value v '(:struct wf2cu-view) 'offset))
+					(ld  (v) (mem-aref (foreign-slot-pointer v '(:struct wf2cu-view) 'stride) :int64 0)))
+				   (gemm-ex (if ta 1 0) (if tb 1 0) m n k
+					    (device-vec-ptr (tensor-vec a*)) (off av) (ld av)
+					    (device-vec-ptr (tensor-vec b*)) (off bv) (ld bv)
+					    (device-vec-ptr (tensor-vec out)) (off cv) (ld cv)
+					    (device-vec-ptr (tensor-vec bias)) (off biasv) 0
+					    (null-pointer) 0 0))))
+			     out))
+		   (push i1 result))
+		 (push i0 result)))
+	finally (return (nreverse result))))
+
 (defmethod on-finalizing-compiling ((device-name (eql 'CUDATensor)) iseq-fw iseq-bw)
   (if *cuda-available-p*
-      (values (fuse-move+arith iseq-fw) (and iseq-bw (fuse-move+arith iseq-bw)))
+      (flet ((rewrite (iseq) (fuse-matmul+bias (fuse-move+arith iseq))))
+	(values (rewrite iseq-fw) (and iseq-bw (rewrite iseq-bw))))
       (values iseq-fw iseq-bw)))
+
+;; ---- independent instructions on a side stream: (with-cuda-branch (1) <launches>) ... (branch-join 1)
+(defmacro with-cuda-branch ((b) &body body)
+  "BODY's launches go to side stream B (1..3), ordered after everything issued so far; the main stream
+waits for them at `(branch-join B)`.  Inside `with-cuda-graph` these become fork/join edges."
+  `(progn (branch-begin ,b)
+	  (unwind-protect (progn ,@body)
+	    (branch-end ,b))))
 
 ;; ---- CUDA-graph replay (SURVEY §8f rank 1): after `set-adjustable-symbols` the iseq is a fixed
 ;; launch sequence; capture `(forward model)` once and replay it.
@@ -75,3 +137,29 @@
   "Sum the gradient arena over ranks on the library stream; the 1/world factor is applied by the
 optimizer kernel (`grad_scale` of wf2cu_adam_step)."
   (allreduce-sum-f32 (device-vec-ptr (tensor-vec grad-arena)) (tensor-initial-offset grad-arena) n-floats))
+
+;; ---- exchange + Adam as ONE kernel over NVLink peer memory (csrc/p2p.cu): reduce-scatter, Adam on this
+;; rank's shard, parameter all-gather.  HANDLES-EXCHANGE is any host transport that all-gathers 192 bytes per
+;; rank (file, socket, MPI): it receives this rank's (unsigned-byte 8) vector and returns a list of WORLD vectors.
+(defun cuda-p2p-attach (rank world grad-arena param-arena handles-exchange)
+  (with-foreign-objects ((mine :uint8 192) (grads :uint8 (* 64 8)) (params :uint8 (* 64 8)) (sigs :uint8 (* 64 8)))
+    (p2p-export (device-vec-ptr (tensor-vec grad-arena)) mine)
+    (p2p-export (device-vec-ptr (tensor-vec param-arena)) (inc-pointer mine 64))
+    (p2p-signal-export (inc-pointer mine 128))
+    (let* ((blob (make-array 192 :element-type '(unsigned-byte 8)))
+	   (all  (progn (dotimes (i 192) (setf (aref blob i) (mem-aref mine :uint8 i)))
+			(funcall handles-exchange blob))))
+      (loop for r from 0 below world
+	    for h in all
+	    do (dotimes (i 64)
+		 (setf (mem-aref grads  :uint8 (+ (* 64 r) i)) (aref h i)
+		       (mem-aref params :uint8 (+ (* 64 r) i)) (aref h (+ 64 i))
+		       (mem-aref sigs   :uint8 (+ (* 64 r) i)) (aref h (+ 128 i)))))
+      (p2p-attach rank world (device-vec-ptr (tensor-vec grad-arena)) (device-vec-ptr (tensor-vec param-arena))
+		  grads params sigs))))
+
+(defun cuda-p2p-adam-step (param-arena m-arena v-arena n-floats lr-t-device &key (beta1 0.9) (beta2 0.999) (eps 1e-7))
+  "After `backward` on every rank: the whole data-parallel update in one launch."
+  (p2p-allreduce-adam-step (device-vec-ptr (tensor-vec param-arena)) 0 0
+			   (device-vec-ptr (tensor-vec m-arena)) 0 (device-vec-ptr (tensor-vec v-arena)) 0
+			   n-floats 0.0 (device-vec-ptr (tensor-vec lr-t-device)) beta1 beta2 eps))

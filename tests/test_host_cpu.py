@@ -131,6 +131,16 @@ def test_library_exports_every_declared_symbol(wf):
     assert set(wf._lib.PROTOTYPES) | {"wf2cu_last_error"} <= set(names)
 
 
+def test_lisp_host_binds_every_declared_symbol():
+    """cl-waffe2_b200/lisp/cffi.lisp (the CFFI side a cl-waffe2 maintainer loads) has a `defwf2` / `defcfun` for every
+    entry point of the header.  (No Common Lisp in this image: the file is checked by reading it.)"""
+    lisp = open(os.path.join(ROOT, "cl-waffe2_b200", "lisp", "cffi.lisp")).read()
+    bound = {"wf2cu_" + m.replace("-", "_") for m in re.findall(r"\(defwf2 ([a-z0-9-]+)", lisp)}
+    bound |= set(re.findall(r'\(defcfun \("(wf2cu_[a-z0-9_]+)"', lisp))
+    missing = [n for n in declared_symbols() if n not in bound]
+    assert not missing, missing
+
+
 def test_view_struct_layout_matches_header(wf):
     V = wf._lib.View
     assert ctypes.sizeof(V) == 8 + 8 + 4 + 4 + 8 * 8 + 8 * 8
