@@ -70,7 +70,15 @@ __device__ __forceinline__ float unary_dispatch(int fn, float x) {
 
 // powf: CUDA documents powf above 1 ulp; the reference is SLEEF powf u10 (body) / libm pow in
 // double (tail).  Use the double route.
-__device__ __forceinline__ float pow_ref(float x, float n) { return (float)pow((double)x, (double)n); }
+// `waffe2_spow` is SLEEF powf (u10).  The general case goes through double-precision pow (correctly rounded to
+// fp32 in practice).  The exponents the models actually use — 2 in LayerNorm / MSE, 3 in GELU
+// (examples/gpt-2/utils.lisp:114-137) — are exact products in double (x^2: 48 bits, x^3: one double rounding), so
+// they give the same fp32 result as the pow route at a fraction of its cost (58 us -> HBM speed on (8 1024 768)).
+__device__ __forceinline__ float pow_ref(float x, float n) {
+  if (n == 2.0f) return __fmul_rn(x, x);
+  if (n == 3.0f) { const double d = (double)x; return (float)(d * d * d); }
+  return (float)pow((double)x, (double)n);
+}
 
 template <int OP> struct Binary;
 template <> struct Binary<WF2CU_ADD> { __device__ __forceinline__ static float apply(float a, float b) { return __fadd_rn(a, b); } };

@@ -216,6 +216,46 @@ __global__ void __launch_bounds__(256) fused_kernel(const __grid_constant__ Fuse
   }
 }
 
+// ---- compiled form of one well-known program: `!gelu` as cl-waffe2 writes it (nn/activation.lisp:61-66;
+// examples/gpt-2/utils.lisp:129-137): 0.5 x (1 + tanh(c2 (x + c1 x^3))), same operation order and roundings as
+// the interpreted program.  The interpreter keeps its register file in local memory (runtime-indexed) and
+// reached 0.94 TB/s on GPT-2's (8 1024 3072) activation; this kernel is HBM-bound.
+static const int kGeluOps[15][4] = {
+    {WF2CU_P_LOAD, 0, 0, 0},  {WF2CU_P_MUL, 1, 0, 0},  {WF2CU_P_MUL, 1, 1, 0},  {WF2CU_P_IMM, 2, 0, -1}, {WF2CU_P_MUL, 1, 1, 2},
+    {WF2CU_P_ADD, 1, 0, 1},   {WF2CU_P_IMM, 2, 0, -1}, {WF2CU_P_MUL, 1, 2, 1},  {WF2CU_P_UNARY, 1, 1, WF2CU_TANH}, {WF2CU_P_IMM, 2, 0, -1},
+    {WF2CU_P_ADD, 1, 2, 1},   {WF2CU_P_IMM, 2, 0, -1}, {WF2CU_P_MUL, 2, 2, 0},  {WF2CU_P_MUL, 1, 2, 1},  {WF2CU_P_STORE, 1, 1, 0}};
+
+static bool match_gelu(const int32_t* program, int n_instr, float imm[4]) {
+  if (n_instr != 15) return false;
+  int ni = 0;
+  for (int k = 0; k < 15; ++k) {
+    const int32_t* q = program + 4 * k;
+    if (q[0] != kGeluOps[k][0] || q[1] != kGeluOps[k][1] || q[2] != kGeluOps[k][2]) return false;
+    if (kGeluOps[k][0] == WF2CU_P_IMM) { memcpy(&imm[ni++], &q[3], 4); continue; }
+    if (kGeluOps[k][0] == WF2CU_P_LOAD || kGeluOps[k][0] == WF2CU_P_STORE) continue;
+    if (q[3] != kGeluOps[k][3]) return false;
+  }
+  return ni == 4;
+}
+
+__device__ __forceinline__ float gelu_one(float x, float c1, float c2, float one, float half) {
+  float t = __fmul_rn(__fmul_rn(x, x), x);
+  t = __fadd_rn(x, __fmul_rn(t, c1));
+  t = Unary<WF2CU_TANH>::apply(__fmul_rn(c2, t));
+  t = __fadd_rn(one, t);
+  return __fmul_rn(__fmul_rn(half, x), t);
+}
+
+__global__ void __launch_bounds__(256) gelu_vec_kernel(const float4* x, float4* out, int64_t n4,   // may alias (in-place gelu)
+                                                       float c1, float c2, float one, float half) {
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
+    const float4 v = x[i];
+    out[i] = make_float4(gelu_one(v.x, c1, c2, one, half), gelu_one(v.y, c1, c2, one, half),
+                         gelu_one(v.z, c1, c2, one, half), gelu_one(v.w, c1, c2, one, half));
+  }
+}
+
 }  // namespace wf2
 
 using namespace wf2;
@@ -316,6 +356,15 @@ int wf2cu_fused(const int32_t* program, int n_instr, const wf2cu_view* views, in
   int64_t grid = (work + 255) / 256;
   const int64_t cap = (int64_t)S().sm_count * 8;
   if (grid > cap) grid = cap;
+  float imm[4];
+  if (vec && nviews == 2 && p.stride[0][0] == 1 && p.stride[1][0] == 1 && match_gelu(program, n_instr, imm)) {
+    int64_t g = (work + 255) / 256;
+    const int64_t gcap = (int64_t)S().sm_count * 32;
+    if (g > gcap) g = gcap;
+    gelu_vec_kernel<<<(unsigned)g, 256, 0, S().stream>>>(reinterpret_cast<const float4*>(a.base[0]), reinterpret_cast<float4*>(a.base[1]),
+                                                         work, imm[0], imm[1], imm[2], imm[3]);
+    return post_launch("wf2cu_fused(gelu)");
+  }
   fused_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(a);
   return post_launch("wf2cu_fused");
 }

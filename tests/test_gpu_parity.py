@@ -322,6 +322,33 @@ def test_fused_activations(gpu, L):
     x64 = d.astype(np.float64)
     truth = 0.5 * x64 * (1 + np.tanh(np.sqrt(2 / np.pi) * (x64 + 0.044715 * x64 ** 3)))
     np.testing.assert_allclose(g, truth, rtol=1e-5, atol=1e-6)
+    # the compiled gelu path (contiguous, 16-byte aligned) must equal the interpreted program on a strided view bit for bit
+    d2 = RNG.normal(size=(64, 200)).astype(np.float32) * 3
+    g2 = gpu.from_numpy(d2)
+    half = gpu.view(g2, True, [0, 200, 2])                     # every other column: not vectorisable -> interpreter
+    a = gpu.ops.gelu(gpu.from_numpy(np.ascontiguousarray(d2[:, ::2]))).to_numpy()
+    b = gpu.ops.gelu(half).to_numpy()
+    np.testing.assert_array_equal(a, b)
+    # in place, as the GPT-2 example applies it
+    g3 = gpu.from_numpy(d)
+    gpu.ops.gelu(g3, out=g3)
+    np.testing.assert_array_equal(g3.to_numpy(), g)
+
+
+def test_softmax_over_heads_axis_vectorised(gpu, L):
+    """GPT-2's `(!softmax w :avoid-overflow nil)` on a 4-D tensor normalises over axis 1 (examples/gpt-2/utils.lisp:236-242).
+    Large enough for the 4-lanes-per-thread kernel; the scalar lane kernel (a strided view of the same data) is the check."""
+    d = RNG.normal(size=(2, 12, 64, 2048)).astype(np.float32)
+    gx = gpu.from_numpy(d)
+    for avoid in (False, True):
+        r = gpu.ops.softmax(gx, avoid_overflow=avoid, axis=1).to_numpy()
+        x64 = d.astype(np.float64)
+        if avoid:
+            x64 = x64 - x64.mean(axis=1, keepdims=True)
+        e = np.exp(x64)
+        np.testing.assert_allclose(r, e / e.sum(axis=1, keepdims=True), rtol=2e-6, atol=1e-9)
+        small = gpu.from_numpy(np.ascontiguousarray(d[:, :, :8, :64]))          # too small for the vector path
+        np.testing.assert_array_equal(gpu.ops.softmax(small, avoid_overflow=avoid, axis=1).to_numpy(), r[:, :, :8, :64])
 
 
 # ---------------------------------------------------------------- matmul
