@@ -20,7 +20,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
                 int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode);
 // gemm_tc.cu: one-launch tcgen05 kernel for small problems (in-kernel hi/lo split, cluster split-K, fused epilogue)
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
-                      float* C, int64_t ldc, const float* bias, int act, const float* mask, int64_t ldmask);
+                      float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
+                      const float* mask, int64_t ldmask);
 
 constexpr int BM = 128, BN = 128, BK = 16;
 
@@ -333,12 +334,17 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   // mode: 0 auto | 1 fp32 SIMT | 2 tcgen05 3xTF32 (planes + persistent kernel) | 3 tcgen05 1xTF32 | 4 tcgen05 fused small kernel
   {
     const double flops = 2.0 * (double)m * (double)n * (double)k;
-    if (batch == 1 && (mode == 4 || (mode == 0 && flops >= 5.0e7 && flops < 1.0e9))) {
-      const int r = gemm_tc_fused_try(trans_a ? 1 : 0, trans_b ? 1 : 0, m, n, k, a, lda, b, ldb, c, ldc, bias, act, mask, ldmask);
+    // batched with a narrow result (GPT-2's probabilities x V, n = 64 per head): the 128x256 tile of the planes path
+    // wastes 3/4 of every MMA and its split pass rewrites the whole (1024 1024) operand per head twice; the fused
+    // kernel converts in flight (414 us -> see profiles/r01_gpt2_launches.md)
+    const bool narrow_batched = batch > 1 && n <= 128 && m >= 256 && k >= 256;
+    if (mode == 4 || (mode == 0 && ((batch == 1 && flops >= 5.0e7 && flops < 1.0e9) || narrow_batched))) {
+      const int r = gemm_tc_fused_try(trans_a ? 1 : 0, trans_b ? 1 : 0, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b,
+                                      stride_c, bias, act, mask, ldmask);
       if (r < 0) return -r;
       if (r == 1) return 0;
     }
-    if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (batched or out of range)", who);
+    if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (out of range)", who);
   }
   if (mode != 1) {
     const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode);

@@ -528,9 +528,10 @@ static_assert(FM * F_PLD * 4 <= F_STAGE, "partial tile must fit stage 0");
 struct FusedGemmArgs {
   const float* A; const float* B; float* C;
   int64_t lda, ldb, ldc;
+  int64_t sa, sb, sc;        // batch strides (elements); blockIdx.z = batch index * ksplit + K slice
   int m, n, k;
   int ta, tb;
-  int a_vec, b_vec;          // operand rows are 16-byte aligned: 128-bit global loads
+  int a_vec, b_vec, c_vec;   // operand / result rows are 16-byte aligned: 128-bit global accesses
   int ksplit, kchunk;        // cluster size along z, K per slice (multiple of 32)
   const float* bias; const float* mask; int64_t ldmask; int act;
 };
@@ -641,7 +642,8 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_cons
   uint64_t* freed = reinterpret_cast<uint64_t*>(smem + F_STAGES * F_STAGE);   // [2] MMAs that read stage s have retired
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(freed + F_STAGES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ks = (int)blockIdx.z;                       // grid.z == ksplit == cluster size
+  const int ks = (int)(blockIdx.z % g.ksplit);          // cluster = ksplit consecutive z: rank in cluster == K slice
+  const int64_t bz = blockIdx.z / g.ksplit;             // batch index
   const int m0 = blockIdx.y * FM, n0 = blockIdx.x * FN;
   const int kbeg = ks * g.kchunk;
   const int kend = min(g.k, kbeg + g.kchunk);
@@ -666,8 +668,8 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_cons
   constexpr int GB = 4;
   FTile<FM> ta_;
   FTile<FN> tb_;
-  ta_.init(g.A, g.lda, a_kmajor, g.a_vec != 0, m0, g.m, kbeg);
-  tb_.init(g.B, g.ldb, b_kmajor, g.b_vec != 0, n0, g.n, kbeg);
+  ta_.init(g.A + bz * g.sa, g.lda, a_kmajor, g.a_vec != 0, m0, g.m, kbeg);
+  tb_.init(g.B + bz * g.sb, g.ldb, b_kmajor, g.b_vec != 0, n0, g.n, kbeg);
   uint32_t ph0 = 0, ph1 = 0;                            // parity of freed[0] / freed[1]
   for (int kg = 0; kg < nkb; kg += GB) {
     float4 ra[GB][FM / 32], rb[GB][FN / 32];
@@ -768,11 +770,15 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_cons
     }
     const int64_t gm = m0 + r, gn = n0 + c4;
     if (gm < g.m) {
-      float* cp = g.C + gm * g.ldc + gn;
+      float* cp = g.C + bz * g.sc + gm * g.ldc + gn;
       const float v[4] = {t.x, t.y, t.z, t.w};
+      if (g.c_vec && gn + 3 < g.n && !g.bias && !g.act && !g.mask) {
+        *reinterpret_cast<float4*>(cp) = t;
+      } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (gn + j < g.n) cp[j] = f_epilogue(g, v[j], gm, gn + j);
+        for (int j = 0; j < 4; ++j)
+          if (gn + j < g.n) cp[j] = f_epilogue(g, v[j], gm, gn + j);
+      }
     }
   }
   if (ksplit > 1)   // nobody leaves (or frees its shared memory) while a peer may still read its tile
@@ -913,16 +919,17 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
-                      float* C, int64_t ldc, const float* bias, int act, const float* mask, int64_t ldmask) {
-  if (m < 1 || n < 1 || k < 1 || m > (1 << 24) || n > (1 << 24) || k > (1 << 24)) return 0;
+                      float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
+                      const float* mask, int64_t ldmask) {
+  if (m < 1 || n < 1 || k < 1 || m > (1 << 24) || n > (1 << 24) || k > (1 << 24) || batch < 1 || batch > 8000) return 0;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
     if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_tc_fused_kernel)", __FILE__, __LINE__);
     attr_set = true;
   }
-  const int64_t tiles = ((m + FM - 1) / FM) * ((n + FN - 1) / FN);
-  if (tiles > 65535 * 4) return 0;
+  const int64_t tiles = ((m + FM - 1) / FM) * ((n + FN - 1) / FN) * batch;
+  if ((m + FM - 1) / FM > 65535) return 0;
   const int nkb_total = (int)((k + TK - 1) / TK);
   int ksplit = 1;
   // spread K over a cluster while the grid is below ~2 CTAs per SM and every slice keeps >= 2 k-blocks
@@ -932,13 +939,15 @@ int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const flo
   memset(&g, 0, sizeof(g));
   g.A = A; g.B = B; g.C = C; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
   g.m = (int)m; g.n = (int)n; g.k = (int)k; g.ta = ta; g.tb = tb;
-  g.a_vec = ((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (lda & 3) == 0) ? 1 : 0;
-  g.b_vec = ((reinterpret_cast<uintptr_t>(B) & 15) == 0 && (ldb & 3) == 0) ? 1 : 0;
+  g.sa = sa; g.sb = sb; g.sc = sc;
+  g.a_vec = ((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (lda & 3) == 0 && (sa & 3) == 0) ? 1 : 0;
+  g.b_vec = ((reinterpret_cast<uintptr_t>(B) & 15) == 0 && (ldb & 3) == 0 && (sb & 3) == 0) ? 1 : 0;
+  g.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   g.ksplit = ksplit; g.kchunk = kchunk;
   g.bias = bias; g.mask = mask; g.ldmask = ldmask; g.act = act;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3((unsigned)((n + FN - 1) / FN), (unsigned)((m + FM - 1) / FM), (unsigned)ksplit);
+  cfg.gridDim = dim3((unsigned)((n + FN - 1) / FN), (unsigned)((m + FM - 1) / FM), (unsigned)(batch * ksplit));
   cfg.blockDim = dim3(256, 1, 1);
   cfg.dynamicSmemBytes = F_SMEM;
   cfg.stream = S().stream;

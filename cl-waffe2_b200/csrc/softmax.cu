@@ -181,6 +181,7 @@ struct SmLaneArgs {
   int64_t R, sR_x, sR_o;
   int64_t nlanes;
   int avoid_overflow;
+  float pre_div;                   // != 0: every element is divided by it first (the `(!div w n)` node in front, folded in)
 };
 
 template <int RCACHE>
@@ -198,6 +199,10 @@ __global__ void __launch_bounds__(256) softmax_lane_kernel(const __grid_constant
       float v[RCACHE > 0 ? RCACHE : 1];
 #pragma unroll
       for (int k = 0; k < RCACHE; ++k) v[k] = (k < a.R) ? xp[k * a.sR_x] : 0.f;
+      if (a.pre_div != 0.f) {
+#pragma unroll
+        for (int k = 0; k < RCACHE; ++k) v[k] = __fdiv_rn(v[k], a.pre_div);
+      }
       if (a.avoid_overflow) {
         float s = 0.f;
 #pragma unroll
@@ -215,17 +220,19 @@ __global__ void __launch_bounds__(256) softmax_lane_kernel(const __grid_constant
       float mean = 0.f;
       if (a.avoid_overflow) {
         float s = 0.f;
-        for (int64_t k = 0; k < a.R; ++k) s = __fadd_rn(s, xp[k * a.sR_x]);
+        for (int64_t k = 0; k < a.R; ++k) { float t = xp[k * a.sR_x]; if (a.pre_div != 0.f) t = __fdiv_rn(t, a.pre_div); s = __fadd_rn(s, t); }
         mean = __fdiv_rn(s, (float)a.R);
       }
       float z = 0.f;
       for (int64_t k = 0; k < a.R; ++k) {
         float t = xp[k * a.sR_x];
+        if (a.pre_div != 0.f) t = __fdiv_rn(t, a.pre_div);
         if (a.avoid_overflow) t = __fsub_rn(t, mean);
         z = __fadd_rn(z, expf(t));
       }
       for (int64_t k = 0; k < a.R; ++k) {
         float t = xp[k * a.sR_x];
+        if (a.pre_div != 0.f) t = __fdiv_rn(t, a.pre_div);
         if (a.avoid_overflow) t = __fsub_rn(t, mean);
         op[k * a.sR_o] = __fdiv_rn(expf(t), z);
       }
@@ -252,6 +259,13 @@ __global__ void __launch_bounds__(256) softmax_lane_vec_kernel(const __grid_cons
 #pragma unroll
     for (int k = 0; k < RCACHE; ++k)
       v[k] = (k < a.R) ? *reinterpret_cast<const float4*>(xp + k * a.sR_x) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.pre_div != 0.f) {
+#pragma unroll
+      for (int k = 0; k < RCACHE; ++k) {
+        v[k].x = __fdiv_rn(v[k].x, a.pre_div); v[k].y = __fdiv_rn(v[k].y, a.pre_div);
+        v[k].z = __fdiv_rn(v[k].z, a.pre_div); v[k].w = __fdiv_rn(v[k].w, a.pre_div);
+      }
+    }
     if (a.avoid_overflow) {
       float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -361,7 +375,12 @@ __global__ void __launch_bounds__(256) sce_backward_kernel(const float* __restri
 
 using namespace wf2;
 
+extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow, float pre_divisor);
 extern "C" int wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow) {
+  return wf2cu_softmax_ex(x, out, axis, avoid_overflow, 0.f);
+}
+
+extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow, float pre_divisor) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(x && out && x->base && out->base, "wf2cu_softmax: null view");
   WF2_CHECK(x->rank == out->rank && x->rank >= 1 && x->rank <= kMaxRank, "wf2cu_softmax: bad rank");
@@ -381,6 +400,9 @@ extern "C" int wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axi
   // is the softmax axis the innermost non-trivial one?
   bool innermost = true;
   for (int i = axis + 1; i < rank; ++i) if (x->shape[i] != 1) innermost = false;
+  if (innermost && pre_divisor != 0.f)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_softmax_ex: the folded divisor is implemented for a non-innermost softmax axis "
+                     "only; issue the !div node and wf2cu_softmax separately");
   if (innermost) {
     SmRowArgs a;
     memset(&a, 0, sizeof(a));
@@ -432,6 +454,7 @@ extern "C" int wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axi
   memset(&a, 0, sizeof(a));
   a.x = xp; a.out = op; a.R = R; a.sR_x = x->stride[axis]; a.sR_o = out->stride[axis];
   a.avoid_overflow = avoid_overflow;
+  a.pre_div = pre_divisor;
   a.nlanes = 1;
   for (int i = 0; i < rank; ++i) {
     if (i == axis || x->shape[i] == 1) continue;

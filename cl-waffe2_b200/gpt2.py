@@ -100,8 +100,8 @@ def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
     K = split_heads(qkv, "K", n_head)
     V = split_heads(qkv, "V", n_head)
     w = ops.matmul(Q, K)                                    # (B H N N); operands made contiguous (adjust-layout)
-    ops.div_(w, float(w.shape[-1]))                         # (!div w (make-tensor N))
-    ops.softmax(w, avoid_overflow=False, axis=1, out=w)     # default axis=1 -> over heads
+    # (!div w (make-tensor N)) then (!softmax w :avoid-overflow nil), default axis=1 -> over heads; one pass
+    ops.softmax(w, avoid_overflow=False, axis=1, out=w, pre_divisor=float(w.shape[-1]))
     a = ops.matmul(w, V)                                    # (B H N d)
     return merge_heads(a)
 

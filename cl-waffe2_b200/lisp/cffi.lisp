@@ -84,6 +84,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 ;; reductions / composites
 (defwf2 reduce-sum ((x :pointer) (out :pointer) (accumulate :int) (divisor :float)))
 (defwf2 softmax ((x :pointer) (out :pointer) (axis :int) (avoid-overflow :int)))
+(defwf2 softmax-ex ((x :pointer) (out :pointer) (axis :int) (avoid-overflow :int) (pre-divisor :float)))
 (defwf2 reduce-maxmin ((is-min :int) (x :pointer) (out :pointer)))
 (defwf2 argmaxmin ((is-min :int) (x :pointer) (out :pointer)))
 ;; MatmulNode

@@ -191,9 +191,18 @@ def mean(x: CUDATensor, axis=True, keepdims: bool = False, out=None) -> CUDATens
     return sum(x, axis=axis, keepdims=keepdims, out=out, _divisor=float(cnt))
 
 
-def softmax(x: CUDATensor, avoid_overflow: bool = True, axis: int = 1, out=None) -> CUDATensor:
-    """`!softmax` (nn/activation.lisp:126-159) as one kernel.  Mean-shift, as in the reference."""
+def softmax(x: CUDATensor, avoid_overflow: bool = True, axis: int = 1, out=None, pre_divisor: float = 0.0) -> CUDATensor:
+    """`!softmax` (nn/activation.lisp:126-159) as one kernel.  Mean-shift, as in the reference.
+    pre_divisor: fold a `(!div x n)` node in front into the same pass (wf2cu_softmax_ex); when the library does
+    not implement it for this layout the two nodes are issued separately, exactly as written."""
     o = out if out is not None else make_tensor(x.shape)
+    if pre_divisor:
+        rc = _L().wf2cu_softmax_ex(_ref(x.lower()), _ref(o.lower()), int(axis), 1 if avoid_overflow else 0, float(pre_divisor))
+        if rc == 0:
+            return o
+        if rc != 3:                              # WF2CU_ERR_UNSUPPORTED -> the unfused sequence
+            _lib.check(rc)
+        x = div(x, float(pre_divisor))
     _lib.check(_L().wf2cu_softmax(_ref(x.lower()), _ref(o.lower()), int(axis), 1 if avoid_overflow else 0))
     return o
 

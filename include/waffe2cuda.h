@@ -171,6 +171,10 @@ int  wf2cu_fused(const int32_t* program, int n_instr, const wf2cu_view* views, i
 int  wf2cu_reduce_sum(const wf2cu_view* x, const wf2cu_view* out_bcast, int accumulate, float divisor);
 /* `!softmax` (`nn/activation.lisp:126-159`): mean-shift (avoid_overflow) or plain, over `axis`. */
 int  wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow);
+/* `(!softmax (!div x n))`: the scalar divide in front folded into the same pass (GPT-2's attention weights,
+ * `examples/gpt-2/utils.lisp:236-242`).  pre_divisor = 0: plain wf2cu_softmax.  Implemented for a softmax axis that
+ * is not the innermost one; WF2CU_ERR_UNSUPPORTED otherwise (issue the two nodes separately). */
+int  wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow, float pre_divisor);
 /* MaxValue/MinValue/ArgMax/ArgMin over the last axis (`backends/cpu/matrix-ops.lisp:240-369`).
  * out has x's shape with the last axis of extent 1; arg variants write uint32 indices. */
 int  wf2cu_reduce_maxmin(int is_min, const wf2cu_view* x, const wf2cu_view* out);

@@ -349,6 +349,15 @@ def test_softmax_over_heads_axis_vectorised(gpu, L):
         np.testing.assert_allclose(r, e / e.sum(axis=1, keepdims=True), rtol=2e-6, atol=1e-9)
         small = gpu.from_numpy(np.ascontiguousarray(d[:, :, :8, :64]))          # too small for the vector path
         np.testing.assert_array_equal(gpu.ops.softmax(small, avoid_overflow=avoid, axis=1).to_numpy(), r[:, :, :8, :64])
+        # (!softmax (!div x n)) folded into one pass == the two nodes issued separately, bit for bit (both kernels)
+        for t in (gx, small):
+            two = gpu.ops.softmax(gpu.ops.div(t, 1024.0), avoid_overflow=avoid, axis=1).to_numpy()
+            one = gpu.ops.softmax(t, avoid_overflow=avoid, axis=1, pre_divisor=1024.0).to_numpy()
+            np.testing.assert_array_equal(one, two)
+    # innermost axis: the library declines the folded form and the host issues the two nodes
+    m = gpu.from_numpy(d[0, 0])
+    np.testing.assert_array_equal(gpu.ops.softmax(m, axis=1, pre_divisor=7.0).to_numpy(),
+                                  gpu.ops.softmax(gpu.ops.div(m, 7.0), axis=1).to_numpy())
 
 
 # ---------------------------------------------------------------- matmul
