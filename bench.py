@@ -190,6 +190,16 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(key):
+    """dram read + write bytes per launch of `key`, from the committed ncu --set full capture
+    (profiles/ncu_traffic.json; written by hand from profiles/r*_ncu_full_*.md).  None if never captured."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        return json.load(open(p)).get(key)
+    except (OSError, ValueError):
+        return None
+
+
 def dist_env():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 
@@ -232,7 +242,7 @@ def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
             "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::tf32, 3 passes)", "achieved": top["tflops"],
                          "peak": tf32_peak, "unit": "TFLOP/s", "frac": top["frac_of_tf32_peak"], "pipe_frac": top["pipe_frac"],
                          "peak_source": "0.5 x MEASURED_PEAKS.json bf16_tflops (TF32 dense); of measured", "N": top["N"],
-                         "traffic": None}}
+                         "traffic": None, "traffic_at_N4096": ncu_traffic("gemm_tc_kernel_N4096")}}
 
 
 def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3):
@@ -435,7 +445,8 @@ def run_ours(args):
     dom = "add"   # ew_vec_kernel<2, add>: the largest share of the step's bytes (3 cases use it)
     roofline = {"bound": "hbm", "kernel": "ew_vec_kernel<2,FBinary<ADD>> (case add)", "achieved": per_case[dom]["gbps"],
                 "peak": peak, "unit": "GB/s", "frac": per_case[dom]["gbps"] / peak, "peak_source": peak_src,
-                "traffic": None, "algorithmic_bytes_per_launch": per_case[dom]["bytes"]}
+                "traffic": ncu_traffic("ew_vec_kernel<2,FBinary<ADD>>"), "traffic_source": "profiles/ncu_traffic.json (ncu --set full capture, dram read+write per launch)",
+                "algorithmic_bytes_per_launch": per_case[dom]["bytes"]}
 
     # ---- e2e: host buffers in, host results out, copies inside the timed region
     hx = C.c_void_p(); hy = C.c_void_p(); hres = C.c_void_p()
