@@ -521,6 +521,14 @@ def run_ours(args):
         except Exception as e:                       # reported, never silently dropped
             gpt2 = {"error": repr(e)}
 
+    cnn = None
+    if args.cnn and world == 1:
+        stage("cnn")
+        try:
+            cnn = importlib.import_module("cl-waffe2_b200.mlp_bench").run_cnn(wf)
+        except Exception as e:
+            cnn = {"error": repr(e)}
+
     # ---- CPU baseline (rank 0, N=1): the oracle on one host core, bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -550,6 +558,7 @@ def run_ours(args):
                        "parallelism": "replicas only" if world > 1 else "single GPU"},
             "roofline": roofline, "cases": per_case, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(), "mlp": mlp, "gemm": gemm, "gpt2": gpt2,
+            "cnn": cnn,
         }
         print(json.dumps(line))
     if dist is not None:
@@ -571,6 +580,7 @@ def main():
     ap.add_argument("--mlp", type=int, default=1)
     ap.add_argument("--gemm", type=int, default=1)
     ap.add_argument("--gpt2", type=int, default=1)
+    ap.add_argument("--cnn", type=int, default=1)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N>1 gradient exchange: p2p = fused peer-memory allreduce+Adam kernel, nccl = ncclAllReduce + Adam")
     ap.add_argument("--mlp-steps", type=int, default=200)

@@ -30,7 +30,14 @@ class View(C.Structure):
                 ("shape", C.c_int64 * MAX_RANK), ("stride", C.c_int64 * MAX_RANK)]
 
 
+class UnfoldGeom(C.Structure):
+    """struct wf2cu_unfold_geom (include/waffe2cuda.h)."""
+    _fields_ = [(n, C.c_int64) for n in ("N", "C", "H", "W", "Ho", "Wo", "KH", "KW", "pad_h", "pad_w",
+                                         "stride_h", "stride_w", "dilation_h", "dilation_w")]
+
+
 VP = C.POINTER(View)
+GP = C.POINTER(UnfoldGeom)
 i32, i64, f32, vp, sz = C.c_int, C.c_int64, C.c_float, C.c_void_p, C.c_size_t
 
 # name -> argtypes ; every function returns int status except wf2cu_last_error
@@ -59,6 +66,9 @@ PROTOTYPES = {
     "wf2cu_sgd_step": [vp, i64, vp, i64, i64, f32],
     "wf2cu_adam_step": [vp, i64, vp, i64, vp, i64, vp, i64, i64, f32, vp, f32, f32, f32, f32],
     "wf2cu_embedding_gather": [vp, i64, i64, vp, vp, i64, vp],
+    "wf2cu_im2col": [vp, i64, vp, i64, GP], "wf2cu_col2im": [vp, i64, vp, i64, GP],
+    "wf2cu_unfold": [VP, vp, i64, GP], "wf2cu_fold": [vp, i64, VP, GP, i32],
+    "wf2cu_pool2d": [i32, VP, VP, GP], "wf2cu_pool2d_backward": [i32, VP, VP, VP, VP, GP, i32],
     "wf2cu_comm_unique_id": [vp], "wf2cu_comm_init": [i32, i32, vp],
     "wf2cu_allreduce_sum_f32": [vp, i64, i64], "wf2cu_comm_destroy": [],
     "wf2cu_p2p_export": [vp, vp], "wf2cu_p2p_signal_export": [vp], "wf2cu_p2p_attach": [i32, i32, vp, vp, vp, vp, vp],

@@ -299,6 +299,177 @@ static int sgemm_small_try(const GemmArgs& g, int64_t batch) {
   return rc ? -rc : 1;
 }
 
+// ------------------------------------------------------------------ skinny shapes (Conv2D on few channels)
+// Conv2D lowers to (N*Ho*Wo, C*kh*kw) x (C*kh*kw, C_out): on MNIST-CNN that is 67 600 x 9 x 4 and 6 400 x 100 x 16.
+// A 64x64 output tile is then almost empty along n, and the weight-gradient GEMM (4 x 9 outputs over k = 67 600)
+// would run on one tile.  Two exact-fp32 kernels cover the two shapes.
+
+// (a) C[M, n] = A[M, k] . B^T, B stored (n, k), n <= 32, n*k <= 4096: B lives in shared memory, a CTA owns 128
+// rows of A staged through shared memory in k-slices (coalesced global reads), one thread per row, n accumulators.
+constexpr int SK_ROWS = 128;
+constexpr int SK_TK = 32;
+template <int NMAX>
+__global__ void __launch_bounds__(SK_ROWS) sgemm_skinny_nt_kernel(const __grid_constant__ GemmArgs g) {
+  __shared__ float Bs[4096];
+  __shared__ float As[SK_ROWS * (SK_TK + 1)];
+  const int t = threadIdx.x;
+  const int n = (int)g.n, k = (int)g.k;
+  for (int i = t; i < n * k; i += SK_ROWS) Bs[i] = g.B[(int64_t)(i / k) * g.ldb + (i % k)];
+  const int64_t row0 = (int64_t)blockIdx.x * SK_ROWS;
+  const int rows = (int)((g.m - row0) < SK_ROWS ? (g.m - row0) : SK_ROWS);
+  float acc[NMAX];
+#pragma unroll
+  for (int j = 0; j < NMAX; ++j) acc[j] = 0.f;
+  for (int k0 = 0; k0 < k; k0 += SK_TK) {
+    const int tk = (k - k0) < SK_TK ? (k - k0) : SK_TK;
+    __syncthreads();
+    for (int i = t; i < rows * tk; i += SK_ROWS) {
+      const int r = i / tk, c = i - r * tk;
+      As[r * (SK_TK + 1) + c] = g.A[(row0 + r) * g.lda + k0 + c];
+    }
+    __syncthreads();
+    if (t < rows) {
+      for (int c = 0; c < tk; ++c) {
+        const float a = As[t * (SK_TK + 1) + c];
+#pragma unroll
+        for (int j = 0; j < NMAX; ++j)
+          if (j < n) acc[j] = fmaf(a, Bs[j * k + k0 + c], acc[j]);
+      }
+    }
+  }
+  if (t < rows) {
+    float* crow = g.C + (row0 + t) * g.ldc;
+#pragma unroll
+    for (int j = 0; j < NMAX; ++j)
+      if (j < n) crow[j] = epilogue(g, acc[j], row0 + t, j);
+  }
+}
+
+static int sgemm_skinny_nt_try(const GemmArgs& g, int64_t batch) {
+  if (batch != 1 || g.ta || !g.tb) return 0;
+  if (g.n > 32 || g.n * g.k > 4096 || g.m < 2048) return 0;
+  const unsigned grid = (unsigned)((g.m + SK_ROWS - 1) / SK_ROWS);
+  cudaStream_t st = S().stream;
+  if (g.n <= 4) sgemm_skinny_nt_kernel<4><<<grid, SK_ROWS, 0, st>>>(g);
+  else if (g.n <= 8) sgemm_skinny_nt_kernel<8><<<grid, SK_ROWS, 0, st>>>(g);
+  else if (g.n <= 16) sgemm_skinny_nt_kernel<16><<<grid, SK_ROWS, 0, st>>>(g);
+  else sgemm_skinny_nt_kernel<32><<<grid, SK_ROWS, 0, st>>>(g);
+  const int rc = post_launch("wf2cu_gemm(skinny nt)");
+  return rc ? -rc : 1;
+}
+
+// (b) C[m, n] = A^T . B with A stored (K, m), B stored (K, n), m <= 16, n <= 128, K long (a weight gradient):
+// a reduction over K with an m x n accumulator.  CTA c owns a slice of K, warp w its rows w, w+8, ...; the 32
+// lanes form a 4 x 8 grid over the outputs (lane (li, lj) owns i = li + 4a, j = lj + 8b), so one row of A is one
+// broadcast read and one row of B one coalesced read per warp.  Warp partials meet in shared memory in warp
+// order, CTA partials through a last-block ticket in CTA order: deterministic.
+struct SkinnyTnArgs {
+  GemmArgs g;
+  float* partial; unsigned int* counter;
+  int64_t rows_per_cta; int ctas;
+};
+
+template <int TI, int TJ>
+__global__ void __launch_bounds__(256) sgemm_skinny_tn_kernel(const __grid_constant__ SkinnyTnArgs a) {
+  extern __shared__ float red[];          // m * n
+  __shared__ bool is_last;
+  const GemmArgs& g = a.g;
+  const int m = (int)g.m, n = (int)g.n;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int li = lane >> 3, lj = lane & 7;
+  const int64_t k0 = (int64_t)blockIdx.x * a.rows_per_cta;
+  int64_t k1 = k0 + a.rows_per_cta;
+  if (k1 > g.k) k1 = g.k;
+  float acc[TI][TJ];
+#pragma unroll
+  for (int x = 0; x < TI; ++x)
+#pragma unroll
+    for (int y = 0; y < TJ; ++y) acc[x][y] = 0.f;
+  for (int64_t kk = k0 + warp; kk < k1; kk += 8) {
+    const float* ar = g.A + kk * g.lda;
+    const float* br = g.B + kk * g.ldb;
+    float av[TI], bv[TJ];
+#pragma unroll
+    for (int x = 0; x < TI; ++x) { const int i = li + 4 * x; av[x] = i < m ? __ldg(ar + i) : 0.f; }
+#pragma unroll
+    for (int y = 0; y < TJ; ++y) { const int j = lj + 8 * y; bv[y] = j < n ? __ldg(br + j) : 0.f; }
+#pragma unroll
+    for (int x = 0; x < TI; ++x)
+#pragma unroll
+      for (int y = 0; y < TJ; ++y) acc[x][y] = fmaf(av[x], bv[y], acc[x][y]);
+  }
+  for (int w = 0; w < 8; ++w) {
+    if (warp == w) {
+#pragma unroll
+      for (int x = 0; x < TI; ++x)
+#pragma unroll
+        for (int y = 0; y < TJ; ++y) {
+          const int i = li + 4 * x, j = lj + 8 * y;
+          if (i < m && j < n) red[i * n + j] = (w == 0) ? acc[x][y] : red[i * n + j] + acc[x][y];
+        }
+    }
+    __syncthreads();
+  }
+  const int mn = m * n;
+  if (a.ctas == 1) {
+    for (int o = threadIdx.x; o < mn; o += 256) { const int i = o / n, j = o - i * n; g.C[(int64_t)i * g.ldc + j] = epilogue(g, red[o], i, j); }
+    return;
+  }
+  float* mine = a.partial + (int64_t)blockIdx.x * mn;
+  for (int o = threadIdx.x; o < mn; o += 256) mine[o] = red[o];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    is_last = (atomicAdd(a.counter, 1u) == (unsigned)a.ctas - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int o = threadIdx.x; o < mn; o += 256) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int c = 0;
+    for (; c + 3 < a.ctas; c += 4) {
+      s0 += __ldcg(a.partial + (int64_t)c * mn + o); s1 += __ldcg(a.partial + (int64_t)(c + 1) * mn + o);
+      s2 += __ldcg(a.partial + (int64_t)(c + 2) * mn + o); s3 += __ldcg(a.partial + (int64_t)(c + 3) * mn + o);
+    }
+    for (; c < a.ctas; ++c) s0 += __ldcg(a.partial + (int64_t)c * mn + o);
+    const int i = o / n, j = o - i * n;
+    g.C[(int64_t)i * g.ldc + j] = epilogue(g, (s0 + s1) + (s2 + s3), i, j);
+  }
+  if (threadIdx.x == 0) *a.counter = 0;
+}
+
+static int sgemm_skinny_tn_try(const GemmArgs& g, int64_t batch) {
+  if (batch != 1 || !g.ta || g.tb) return 0;
+  if (g.m > 16 || g.n > 128 || g.k < 2048) return 0;
+  SkinnyTnArgs a;
+  a.g = g;
+  const int64_t mn = g.m * g.n;
+  int64_t ctas = g.k / 128;                                    // >= 16 rows per warp
+  const int64_t cap = mn <= 256 ? (int64_t)S().sm_count * 2 : (int64_t)S().sm_count;
+  if (ctas > cap) ctas = cap;
+  if (ctas < 1) ctas = 1;
+  a.rows_per_cta = (g.k + ctas - 1) / ctas;
+  ctas = (g.k + a.rows_per_cta - 1) / a.rows_per_cta;
+  a.ctas = (int)ctas;
+  a.partial = nullptr; a.counter = nullptr;
+  if (ctas > 1) {
+    const int rc = ensure_scratch((size_t)ctas * mn * sizeof(float));
+    if (rc) return -rc;
+    a.partial = (float*)scratch_base();
+    a.counter = counters_base();
+  }
+  const size_t smem = (size_t)mn * sizeof(float);
+  cudaStream_t st = S().stream;
+  const int ti = (int)((g.m + 3) / 4), tj = (int)((g.n + 7) / 8);
+  if (ti <= 1 && tj <= 2) sgemm_skinny_tn_kernel<1, 2><<<(unsigned)ctas, 256, smem, st>>>(a);
+  else if (ti <= 2 && tj <= 4) sgemm_skinny_tn_kernel<2, 4><<<(unsigned)ctas, 256, smem, st>>>(a);
+  else if (ti <= 4 && tj <= 8) sgemm_skinny_tn_kernel<4, 8><<<(unsigned)ctas, 256, smem, st>>>(a);
+  else sgemm_skinny_tn_kernel<4, 16><<<(unsigned)ctas, 256, smem, st>>>(a);
+  const int rc = post_launch("wf2cu_gemm(skinny tn)");
+  return rc ? -rc : 1;
+}
+
 }  // namespace wf2
 
 using namespace wf2;
@@ -360,6 +531,12 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     if (mode >= 2) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: tensor-core path forced but declined this shape/alignment", who);
   }
   WF2_CHECK(batch < 65536, "%s: batch %lld too large for the SIMT path", who, (long long)batch);
+  {
+    int r = sgemm_skinny_nt_try(g, batch);
+    if (r == 0) r = sgemm_skinny_tn_try(g, batch);
+    if (r < 0) return -r;
+    if (r == 1) return 0;
+  }
   {
     const int r = sgemm_small_try(g, batch);
     if (r < 0) return -r;

@@ -532,6 +532,65 @@ __global__ void __launch_bounds__(256) reduce_cols_kernel(const __grid_constant_
   }
 }
 
+// Narrow variant: K <= 64 kept columns, rows dense (sR_src == K), many rows — bias gradients of layers with
+// few outputs (Conv2D's (N*Ho*Wo, C_out) gradient: 67 600 x 4 on MNIST-CNN) — where a column-block grid
+// would give one thread column per CTA.  The tensor is read as ONE flat contiguous run: CTA g owns rows
+// [g*rps, ...), thread t < L*K (L = 256 / K) owns column t % K of rows t / K, t / K + L, ...; consecutive
+// threads read consecutive floats.  Column totals meet in shared memory, CTA partials through the ticket,
+// both in a fixed order.  52 us -> a few us on the shape above.
+template <class M>
+__global__ void __launch_bounds__(256) reduce_cols_narrow_kernel(const __grid_constant__ ColArgs a, const Fin fin) {
+  __shared__ float sm[256];
+  __shared__ bool is_last;
+  const int K = (int)a.K;
+  const int L = 256 / K;                 // rows per step
+  const int t = threadIdx.x;
+  const bool active = t < L * K;
+  const int col = t % K, lr = t / K;
+  const int64_t r0 = (int64_t)blockIdx.x * a.rows_per_split;
+  int64_t r1 = r0 + a.rows_per_split;
+  if (r1 > a.R) r1 = a.R;
+  float acc0 = M::id(), acc1 = M::id(), acc2 = M::id(), acc3 = M::id();
+  if (active) {
+    const float* p = a.src + col;
+    int64_t r = r0 + lr;
+    for (; r + 3 * L < r1; r += 4 * L) {
+      const float x0 = p[r * K], x1 = p[(r + L) * K], x2 = p[(r + 2 * L) * K], x3 = p[(r + 3 * L) * K];
+      acc0 = M::op(acc0, x0); acc1 = M::op(acc1, x1); acc2 = M::op(acc2, x2); acc3 = M::op(acc3, x3);
+    }
+    for (; r < r1; r += L) acc0 = M::op(acc0, p[r * K]);
+  }
+  sm[t] = M::op(M::op(acc0, acc1), M::op(acc2, acc3));
+  __syncthreads();
+  float tot = M::id();
+  if (t < K) {
+    for (int k = 0; k < L; ++k) tot = M::op(tot, sm[k * K + t]);
+    if (a.splits == 1) { fin.store(a.dst + t, tot); }
+    else a.partial[(int64_t)blockIdx.x * K + t] = tot;
+  }
+  if (a.splits == 1) return;
+  __syncthreads();
+  if (t == 0) {
+    __threadfence();
+    is_last = (atomicAdd(&a.counters[0], 1u) == a.splits - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // the last CTA folds the partials: thread t owns column t % K of splits t / K, t / K + L, ...
+  float f = M::id();
+  if (active)
+    for (uint32_t sp = lr; sp < a.splits; sp += L) f = M::op(f, __ldcg(a.partial + (int64_t)sp * K + col));
+  sm[t] = f;
+  __syncthreads();
+  if (t < K) {
+    float r = M::id();
+    for (int k = 0; k < L; ++k) r = M::op(r, sm[k * K + t]);
+    fin.store(a.dst + t, r);
+  }
+  if (t == 0) a.counters[0] = 0;
+}
+
 // Cluster variant (vec only): 8 CTAs along the reduced axis form a thread-block cluster, each sums its
 // eighth of the rows for a 64-column strip (16 lanes x float4, 16 rows per step, 4 loads in flight), and
 // the 8 partial strips meet in DISTRIBUTED SHARED MEMORY: rank 0 reads its peers' strips with
@@ -773,6 +832,23 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
         reduce_cols_cluster_kernel<M><<<grid, 256, 0, s.stream>>>(a, fin);
         return post_launch(who);
       }
+    }
+    if (a.B == 1 && a.K <= 64 && a.sR_src == a.K && a.R >= 256) {
+      // narrow and tall: one flat contiguous run
+      const int64_t L = 256 / a.K;
+      int64_t splits = (a.R + 4 * L * 8 - 1) / (4 * L * 8);          // >= 8 unrolled steps per CTA
+      if (splits > (int64_t)s.sm_count * 2) splits = (int64_t)s.sm_count * 2;
+      int64_t rps = (a.R + splits - 1) / splits;
+      splits = (a.R + rps - 1) / rps;
+      a.splits = (uint32_t)splits; a.rows_per_split = rps;
+      if (splits > 1) {
+        rc = ensure_scratch((size_t)splits * a.K * sizeof(float));
+        if (rc) return rc;
+        a.partial = (float*)scratch_base();
+        a.counters = counters_base();
+      }
+      reduce_cols_narrow_kernel<M><<<(unsigned)splits, 256, 0, s.stream>>>(a, fin);
+      return post_launch(who);
     }
     const int64_t colblocks = (a.K + 127) / 128;
     const int64_t target_ctas = (int64_t)s.sm_count * 8;

@@ -112,6 +112,18 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 		   (m :pointer) (m-off :int64) (v :pointer) (v-off :int64) (n :int64)
 		   (lr-t :float) (lr-t-dev :pointer) (beta1 :float) (beta2 :float) (eps :float) (grad-scale :float)))
 (defwf2 embedding-gather ((ctx :pointer) (batch :int64) (seq :int64) (wte :pointer) (wpe :pointer) (dim :int64) (out :pointer)))
+;; unfold / Conv2D / pooling (csrc/conv.cu)
+(defcstruct wf2cu-unfold-geom
+  (n :int64) (c :int64) (h :int64) (w :int64)
+  (h-out :int64) (w-out :int64) (k-h :int64) (k-w :int64)
+  (pad-h :int64) (pad-w :int64) (stride-h :int64) (stride-w :int64) (dilation-h :int64) (dilation-w :int64))
+(defwf2 im2col ((col :pointer) (col-off :int64) (im :pointer) (im-off :int64) (geom :pointer)))
+(defwf2 col2im ((col :pointer) (col-off :int64) (im :pointer) (im-off :int64) (geom :pointer)))
+(defwf2 unfold ((x :pointer) (rows :pointer) (rows-off :int64) (geom :pointer)))
+(defwf2 fold ((drows :pointer) (drows-off :int64) (dx :pointer) (geom :pointer) (accumulate :int)))
+(defwf2 pool2d ((mode :int) (x :pointer) (out :pointer) (geom :pointer)))
+(defwf2 pool2d-backward ((mode :int) (x :pointer) (out :pointer) (dout :pointer) (dx :pointer) (geom :pointer)
+			 (accumulate :int)))
 ;; multi-GPU
 (defwf2 comm-unique-id ((out128 :pointer)))
 (defwf2 comm-init ((rank :int) (world :int) (id128 :pointer)))
@@ -129,6 +141,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 p2p-detach ())
 
 ;; enums of waffe2cuda.h
+(defconstant +pool-max+ 0) (defconstant +pool-avg+ 1)
 (defconstant +add+ 0) (defconstant +sub+ 1) (defconstant +mul+ 2) (defconstant +div+ 3) (defconstant +copy+ 4)
 (defparameter *unary-codes*
   '(:sin 0 :cos 1 :tan 2 :asin 3 :acos 4 :atan 5 :sinh 6 :cosh 7 :tanh 8 :abs 9 :exp 10 :loge 11

@@ -100,9 +100,48 @@ what `(!flexible bias)` becomes inside `step-linear` (`nn/regression.lisp:14-18`
 		 (push i0 result)))
 	finally (return (nreverse result))))
 
+;; ---- unfold: Im2ColNode ; Permute-Node ; MoveTensor(->contiguous)  ==>  one wf2cu_unfold
+;; `!im2col` (`nn/im2col.lisp:15-54`) always emits  col <- Im2Col(x, col) ; p <- Permute(col) ;
+;; dense <- MoveTensor(dense, p)  (the `->contiguous` inside `!reshape`).  With padding (0 0) — MNIST-CNN,
+;; the pooling layers — the three instructions become one launch that reads the image through its view
+;; and writes the (N*Ho*Wo, C*kh*kw) rows directly.  With padding the chain is left as it is (the padded
+;; image is produced by a Move into a window, and the node then skips trailing rows: three launches).
+(defun unpadded-unfold-p (node)
+  (with-slots (padding-h padding-w dilation-h dilation-w) node
+    (and (eql padding-h 0) (eql padding-w 0) (eql dilation-h 1) (eql dilation-w 1))))
+
+(defun fuse-unfold-chain (iseq)
+  (loop with out = nil
+	while iseq
+	do (let* ((i0 (pop iseq))
+		  (i1 (first iseq))
+		  (i2 (second iseq)))
+	     (if (and i1 i2
+		      (typep (wf/vm:wfop-node i0) 'Im2ColNode)
+		      (unpadded-unfold-p (wf/vm:wfop-node i0))
+		      (typep (wf/vm:wfop-node i1) 'cl-waffe2/base-impl::Permute-Node)
+		      (typep (wf/vm:wfop-node i2) 'MoveTensorNode)
+		      (cuda-inst-p i0) (cuda-inst-p i2)
+		      (null (wf/vm:wfop-sv4bw i0))
+		      (eq (first (wf/vm:wfop-out-to i0)) (first (wf/vm:wfop-args i1)))
+		      (eq (first (wf/vm:wfop-out-to i1)) (second (wf/vm:wfop-args i2))))
+		 (let ((node (wf/vm:wfop-node i0))
+		       (x    (first (wf/vm:wfop-args i0))))
+		   (pop iseq) (pop iseq)
+		   (setf (wf/vm:wfop-args i2) (list (first (wf/vm:wfop-args i2)) x)
+			 (wf/vm:wfop-op i2)
+			 #'(lambda (dense image)
+			     (with-unfold-geom (g node (shape image))
+			       (with-lowered-views ((xv image))
+				 (unfold xv (device-vec-ptr (tensor-vec dense)) (tensor-initial-offset dense) g)))
+			     dense))
+		   (push i2 out))
+		 (push i0 out)))
+	finally (return (nreverse out))))
+
 (defmethod on-finalizing-compiling ((device-name (eql 'CUDATensor)) iseq-fw iseq-bw)
   (if *cuda-available-p*
-      (flet ((rewrite (iseq) (fuse-matmul+bias (fuse-move+arith iseq))))
+      (flet ((rewrite (iseq) (fuse-matmul+bias (fuse-move+arith (fuse-unfold-chain iseq)))))
 	(values (rewrite iseq-fw) (and iseq-bw (rewrite iseq-bw))))
       (values iseq-fw iseq-bw)))
 

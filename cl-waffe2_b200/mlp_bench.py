@@ -42,14 +42,19 @@ def _all_gather_bytes(dist, world):
     return f
 
 
-def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0, exchange="nccl"):
+def _run_one(dist, rank, world, per_gpu_batch, steps, warmup, seed=0, exchange="nccl", workload="mlp"):
     lib = _lib.load()
-    _stage(f"run_one batch={per_gpu_batch}")
+    _stage(f"run_one {workload} batch={per_gpu_batch}")
     chk = _lib.check
     rng = np.random.default_rng(seed + 17 * rank)          # each rank owns a different shard
-    X = rng.uniform(0, 1, size=(per_gpu_batch, DIMS[0])).astype(np.float32)
+    if workload == "cnn":
+        from . import conv
+        X = rng.uniform(0, 1, size=(per_gpu_batch, 1, 28, 28)).astype(np.float32)
+        model = conv.MNISTCNN(seed=1234)
+    else:
+        X = rng.uniform(0, 1, size=(per_gpu_batch, DIMS[0])).astype(np.float32)
+        model = nn.MLPSequence(DIMS, "relu", seed=1234)    # same seed everywhere: replicas start identical
     Y = np.eye(DIMS[-1], dtype=np.float32)[rng.integers(DIMS[-1], size=per_gpu_batch)]
-    model = nn.MLPSequence(DIMS, "relu", seed=1234)        # same seed everywhere: replicas start identical
     step = nn.CompiledStep(model, "softmax-cross-entropy-sum", nn.Adam(model.arena, lr=1e-3), X.shape, Y.shape, world=world,
                            exchange=exchange)
     if world > 1 and exchange == "p2p":
@@ -170,4 +175,16 @@ def run(wf, dist, rank: int, world: int, steps: int = 200, warmup: int = 20, exc
         res["weak_nccl"] = _run_one(dist, rank, world, 1024, steps, warmup, exchange="nccl")          # the library baseline
     if world > 1:
         _lib.check(_lib.load().wf2cu_comm_destroy())
+    return res
+
+
+def run_cnn(wf, steps: int = 100, warmup: int = 10) -> dict:
+    """§8 f-3: the MNIST-CNN training step (examples/mnist/cnn.lisp:5-26; Conv2D 1->4 3x3, relu, MaxPool 2,
+    Conv2D 4->16 5x5, relu, MaxPool 2, LinearLayer 256->10, softmax-cross-entropy (!sum), Adam) on one GPU, at
+    the example's batch of 100 and at 1024."""
+    res = {"model": "MNIST-CNN (examples/mnist/cnn.lisp): Conv2D(1,4,3x3) relu MaxPool2D(2) Conv2D(4,16,5x5) relu "
+                    "MaxPool2D(2) LinearLayer(256,10), softmax-cross-entropy (!sum), Adam lr 1e-3, fp32",
+           "data": "synthetic U(0,1) images (N 1 28 28), one-hot labels"}
+    for b in (100, 1024):
+        res[f"batch{b}"] = _run_one(None, 0, 1, b, steps, warmup, workload="cnn")
     return res

@@ -82,7 +82,8 @@ def _accumulate(t: CUDATensor, compute: Callable[[CUDATensor, bool], None]) -> N
     if not _tracked(t):
         return
     if t.grad is None:
-        t.grad = make_tensor(t.shape)
+        like = getattr(t, "_grad_like", None)       # e.g. Conv2D's channels-last result: same layout for its gradient
+        t.grad = like(t) if like is not None else make_tensor(t.shape)
     acc = bool(getattr(t, "_has_grad", False))
     masked = getattr(t, "_relu_out", False)
     t._mask_done = False

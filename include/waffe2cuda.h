@@ -229,6 +229,48 @@ int  wf2cu_adam_step(void* param, int64_t p_off, const void* grad, int64_t g_off
 int  wf2cu_embedding_gather(const void* ctx, int64_t batch, int64_t seq, const void* wte,
                             const void* wpe, int64_t dim, void* out);
 
+/* ===================== unfold / Conv2D / pooling ===================== */
+/* Geometry of one unfold, the argument list of `waffe2_im2col_s_column` / `waffe2_col2im_s_column`
+ * (`cl-waffe2-simd/kernels/im2col.c:63-80`; CFFI `cl-waffe2-simd/api.lisp:27-61`; slots of
+ * `Im2ColNode`, `source/base-impl/unfold.lisp:9-23`).  For wf2cu_im2col / wf2cu_col2im H, W are the
+ * extents of the already padded image the node receives; for the fused entry points below they are
+ * the extents of the unpadded input. */
+typedef struct wf2cu_unfold_geom {
+  int64_t N, C, H, W;
+  int64_t Ho, Wo, KH, KW;
+  int64_t pad_h, pad_w, stride_h, stride_w, dilation_h, dilation_w;
+} wf2cu_unfold_geom;
+
+/* Im2ColNode forward (`source/backends/cpu/im2col.lisp:4-25`): col (N C KH KW Ho Wo) <- im (N C H W),
+ * both dense C-order buffers (`:order :column`; the reference's `_row` variants index `col` out of
+ * bounds and are not offered).  As in the reference, output rows j with j*stride_h + pad_h >=
+ * stride_h*Ho (and columns likewise) are left untouched.  dilation != 1 -> WF2CU_ERR_UNSUPPORTED. */
+int  wf2cu_im2col(void* col, int64_t col_off, const void* im, int64_t im_off, const wf2cu_unfold_geom* g);
+/* Col2ImNode forward (`source/backends/cpu/im2col.lisp:27-50`): im <- 0 ; im += col over the same walk;
+ * per image element the contributions are added in (kh, kw) ascending order, as the C loop does. */
+int  wf2cu_col2im(const void* col, int64_t col_off, void* im, int64_t im_off, const wf2cu_unfold_geom* g);
+
+/* `unfold` (`source/nn/im2col.lisp:56-98`) as one pass: zero padding ((pad, pad + Ho mod stride) per
+ * axis), Im2ColNode, `(!permute (torch-order 0 4 5 1 2 3))`, `->contiguous`, reshape.
+ * x: rank-4 view (N C H W) of the UNPADDED input, any strides; rows: dense (N*Ho*Wo, C*KH*KW).
+ * Positions the node leaves untouched are written as 0. */
+int  wf2cu_unfold(const wf2cu_view* x, void* rows, int64_t rows_off, const wf2cu_unfold_geom* g);
+/* Backward of that chain as one pass (reshape, Permute-Node backward, Col2ImNode, the window of the
+ * padded gradient, and the gradient adder `vm/utils.lisp:109-142`): dx (N C H W view) <- or += fold(drows). */
+int  wf2cu_fold(const void* drows, int64_t drows_off, const wf2cu_view* dx, const wf2cu_unfold_geom* g, int accumulate);
+
+/* MaxPool2D / AvgPool2D (`source/nn/pool.lisp:73-105`): unfold -> windows (.., KH*KW) -> `!max` / `!mean`
+ * over axis 1 -> (N Ho Wo C) -> permute, as one pass.  x: (N C H W) view, out: (N C Ho Wo) view (the
+ * reference's result is a permuted view over (N Ho Wo C) storage; any strides are accepted).
+ * avg: sequential fp32 sum in window order, then / (KH*KW), as `!mean` does. */
+enum wf2cu_pool_mode { WF2CU_POOL_MAX = 0, WF2CU_POOL_AVG = 1 };
+int  wf2cu_pool2d(int mode, const wf2cu_view* x, const wf2cu_view* out, const wf2cu_unfold_geom* g);
+/* Backward: max = MaxValue-Node backward (`base-impl/matrix-ops.lisp:311-334`: (a == max a) * dout, every
+ * tie gets the gradient) followed by the unfold backward; avg = dout / (KH*KW) spread over the window.
+ * x and out are read for max only (may be NULL for avg).  dx <- or += . */
+int  wf2cu_pool2d_backward(int mode, const wf2cu_view* x, const wf2cu_view* out, const wf2cu_view* dout,
+                           const wf2cu_view* dx, const wf2cu_unfold_geom* g, int accumulate);
+
 /* ===================== multi-GPU (batch-sharded MLP step) ===================== */
 int  wf2cu_comm_unique_id(void* out128);                       /* rank 0: 128-byte NCCL id   */
 int  wf2cu_comm_init(int rank, int world, const void* id128);  /* one process per GPU        */

@@ -72,6 +72,12 @@ class Kernels:
             fn.restype = None
             fn.argtypes = [_c_long, _vp, _c_long, _vp, _c_long, _c_float, _c_float, _c_float]
 
+        u64 = ctypes.c_uint64
+        for name in ("im2col", "col2im"):
+            fn = getattr(L, f"waffe2_{name}_s_column")      # the _row variants write out of bounds (port.c note)
+            fn.restype = None
+            fn.argtypes = [_vp] + [u64] * 14 + [_vp]
+
     # vec is a 1-D float32 numpy array (the tensor's storage); off is an element offset
     @staticmethod
     def _p(vec: np.ndarray, off: int) -> int:
@@ -118,6 +124,14 @@ class Kernels:
     def cmp_scal(self, name, n, x, xoff, incx, out, ooff, inco, scal, then_v, else_v):
         getattr(self.lib, "waffe2_s" + name + "_scal")(int(n), self._p(x, xoff), int(incx), self._p(out, ooff),
                                                         int(inco), float(scal), float(then_v), float(else_v))
+
+
+    def unfold(self, name, col, N, C, H, W, Ho, Wo, KH, KW, pad_h, pad_w, sh, sw, dh, dw, im):
+        """`waffe2_{im2col,col2im}_s_column` (cl-waffe2-simd/kernels/im2col.c:63-115,395-448; bound in
+        cl-waffe2-simd/api.lisp:27-61,298-310): col is (N C KH KW Ho Wo), im the already padded (N C H W)
+        image, both whole contiguous storages."""
+        getattr(self.lib, f"waffe2_{name}_s_column")(self._p(col, 0), N, C, H, W, Ho, Wo, KH, KW, pad_h, pad_w, sh, sw, dh, dw,
+                                                      self._p(im, 0))
 
 
 _cache: dict = {}

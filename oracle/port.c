@@ -139,3 +139,45 @@ void wf2port_sgemm(int ta, int tb, long m, long n, long k, const float* A, long 
       C[i * ldc + j] = acc;
     }
 }
+
+/* Unfold leaves (`cl-waffe2-simd/kernels/im2col.c:63-115,395-448`), restated for `:order :column`
+ * (C order, the default).  The image handed in is already padded (`nn/im2col.lisp:88-98`); for kernel
+ * offset (kh, kw) the reference visits image rows y = kh, kh+stride_h, ... while
+ * y < dilation_h*kh - pad_h + stride_h*H_out (unsigned arithmetic, so "- pad_h" wraps and comes back),
+ * and likewise for columns.  Elements of `col` outside that range are left untouched.
+ * The `_row` variants (`im2col.c:227-279,562-615`) index `col` with strides that are not a bijection
+ * (the W_out index is multiplied by C*K_H*K_W*H_out*W_out) and write out of bounds for W_out > N:
+ * they are not restated and the CUDA backend declines `:order :row` for these two nodes. */
+#include <stdint.h>
+#define WF2PORT_UNFOLD_ARGS                                                                           \
+  const uint64_t N, const uint64_t C, const uint64_t H, const uint64_t W, const uint64_t Ho,           \
+  const uint64_t Wo, const uint64_t KH, const uint64_t KW, const uint64_t pad_h, const uint64_t pad_w, \
+  const uint64_t sh, const uint64_t sw, const uint64_t dh, const uint64_t dw
+
+static void unfold_walk(int scatter, float* col, WF2PORT_UNFOLD_ARGS, float* im) {
+  if (scatter) for (uint64_t i = 0; i < N * C * H * W; ++i) im[i] = 0.0f;
+  for (uint64_t n = 0; n < N; ++n)
+    for (uint64_t kh = 0; kh < KH; ++kh) {
+      const uint64_t y_end = dh * kh - pad_h + sh * Ho;
+      for (uint64_t kw = 0; kw < KW; ++kw) {
+        const uint64_t x_end = dw * kw - pad_w + sw * Wo;
+        uint64_t j = 0;
+        for (uint64_t y = kh; y < y_end; y += sh, ++j) {
+          uint64_t i = 0;
+          for (uint64_t x = kw; x < x_end; x += sw, ++i)
+            for (uint64_t c = 0; c < C; ++c) {
+              float* pc = col + ((((n * C + c) * KH + kh) * KW + kw) * Ho + j) * Wo + i;
+              float* pi = im + ((n * C + c) * H + y) * W + x;
+              if (scatter) *pi += *pc; else *pc = *pi;
+            }
+        }
+      }
+    }
+}
+
+void waffe2_im2col_s_column(float* col, WF2PORT_UNFOLD_ARGS, const float* im) {
+  unfold_walk(0, col, N, C, H, W, Ho, Wo, KH, KW, pad_h, pad_w, sh, sw, dh, dw, (float*)im);
+}
+void waffe2_col2im_s_column(const float* col, WF2PORT_UNFOLD_ARGS, float* im) {
+  unfold_walk(1, (float*)col, N, C, H, W, Ho, Wo, KH, KW, pad_h, pad_w, sh, sw, dh, dw, im);
+}
