@@ -68,7 +68,7 @@ PROTOTYPES = {
     "wf2cu_embedding_gather": [vp, i64, i64, vp, vp, i64, vp],
     "wf2cu_im2col": [vp, i64, vp, i64, GP], "wf2cu_col2im": [vp, i64, vp, i64, GP],
     "wf2cu_unfold": [VP, vp, i64, GP], "wf2cu_fold": [vp, i64, VP, GP, i32],
-    "wf2cu_pool2d": [i32, VP, VP, GP], "wf2cu_pool2d_backward": [i32, VP, VP, VP, VP, GP, i32],
+    "wf2cu_pool2d": [i32, VP, VP, GP], "wf2cu_pool2d_backward": [i32, VP, VP, VP, VP, GP, i32, i32],
     "wf2cu_comm_unique_id": [vp], "wf2cu_comm_init": [i32, i32, vp],
     "wf2cu_allreduce_sum_f32": [vp, i64, i64], "wf2cu_comm_destroy": [],
     "wf2cu_p2p_export": [vp, vp], "wf2cu_p2p_signal_export": [vp], "wf2cu_p2p_attach": [i32, i32, vp, vp, vp, vp, vp],

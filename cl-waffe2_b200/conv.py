@@ -292,8 +292,11 @@ def _pool2d(mode: int, x: CUDATensor, kernel_size, stride, padding_) -> CUDATens
             def f(gx, acc):
                 if nn.FUSE:
                     gs = geom.struct(False)
+                    masked = bool(getattr(x, "_relu_out", False))      # x = relu(...) folded into its producer: mask here
                     _lib.check(lib.wf2cu_pool2d_backward(mode, C.byref(x.lower()), C.byref(res.lower()), C.byref(res.grad.lower()),
-                                                         C.byref(gx.lower()), C.byref(gs), 1 if acc else 0))
+                                                         C.byref(gx.lower()), C.byref(gs), 1 if acc else 0, 1 if masked else 0))
+                    if masked:
+                        x._mask_done = True
                     return
                 kk = ks[0] * ks[1]
                 d4 = permute(res.grad, *torch_order(res.grad, 0, 2, 3, 1))

@@ -103,16 +103,23 @@ __device__ __forceinline__ float sample(const View4& x, const Geom& g, int n, in
 }
 
 __global__ void __launch_bounds__(256) unfold_rows_kernel(float* __restrict__ rows, const View4 x, const Geom g, int64_t total) {
+  // one thread per (n, j, i, c, kh): the index arithmetic is paid once per KW outputs
   for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
     int64_t r = t;
-    const int kw = (int)(r % g.KW); r /= g.KW;
     const int kh = (int)(r % g.KH); r /= g.KH;
     const int c = (int)(r % g.C); r /= g.C;
     const int i = (int)(r % g.Wo); r /= g.Wo;
     const int j = (int)(r % g.Ho); r /= g.Ho;
-    float v = 0.0f;
-    if (j < g.jmax && i < g.imax) v = sample(x, g, (int)r, c, kh + j * g.sh, kw + i * g.sw);
-    rows[t] = v;
+    const int n = (int)r;
+    float* o = rows + t * g.KW;
+    const int y = kh + j * g.sh - g.pad_h;
+    const bool row_ok = j < g.jmax && i < g.imax && y >= 0 && y < g.H;
+    const float* src = x.p + n * x.s[0] + c * x.s[1] + (int64_t)y * x.s[2];
+    const int x0 = i * g.sw - g.pad_w;
+    for (int kw = 0; kw < g.KW; ++kw) {
+      const int xx = x0 + kw;
+      o[kw] = (row_ok && xx >= 0 && xx < g.W) ? src[xx * x.s[3]] : 0.0f;
+    }
   }
 }
 
@@ -181,7 +188,7 @@ __global__ void __launch_bounds__(256) pool2d_kernel(const View4 x, const View4W
 // the window, then the unfold backward.  Thread per input element, windows in (kh, kw) order.
 template <bool AVG, bool C_FAST>
 __global__ void __launch_bounds__(256) pool2d_backward_kernel(const View4 x, const View4 out, const View4 dout, const View4W dx,
-                                                              const Geom g, int64_t total, int accumulate) {
+                                                              const Geom g, int64_t total, int accumulate, int relu_input) {
   const float cnt = (float)(g.KH * g.KW);
   for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (int64_t)gridDim.x * 256) {
     int64_t r = t;
@@ -189,7 +196,7 @@ __global__ void __launch_bounds__(256) pool2d_backward_kernel(const View4 x, con
     if (C_FAST) { c = (int)(r % g.C); r /= g.C; xi = (int)(r % g.W); r /= g.W; yi = (int)(r % g.H); r /= g.H; n = (int)r; }
     else        { xi = (int)(r % g.W); r /= g.W; yi = (int)(r % g.H); r /= g.H; c = (int)(r % g.C); r /= g.C; n = (int)r; }
     const int y = yi + g.pad_h, xx = xi + g.pad_w;
-    const float v = AVG ? 0.0f : x.p[n * x.s[0] + c * x.s[1] + yi * x.s[2] + xi * x.s[3]];
+    const float v = (AVG && !relu_input) ? 0.0f : x.p[n * x.s[0] + c * x.s[1] + yi * x.s[2] + xi * x.s[3]];
     float acc = 0.0f;
     for (int kh = 0; kh < g.KH && kh <= y; ++kh) {
       const int dy = y - kh;
@@ -211,6 +218,9 @@ __global__ void __launch_bounds__(256) pool2d_backward_kernel(const View4 x, con
         acc = __fadd_rn(acc, gcontrib);
       }
     }
+    // x is the output of a fused `... + !relu` node: its incoming gradient passes the MulNode backward of
+    // `!relu`, dout * (x > 0 ? 1 : 0) (x > 0 <=> pre-activation > 0)
+    if (relu_input) acc = __fmul_rn(acc, v > 0.f ? 1.f : 0.f);
     float* q = dx.p + n * dx.s[0] + c * dx.s[1] + yi * dx.s[2] + xi * dx.s[3];
     *q = accumulate ? __fadd_rn(*q, acc) : acc;
   }
@@ -277,7 +287,7 @@ extern "C" int wf2cu_unfold(const wf2cu_view* x, void* rows, int64_t rows_off, c
   View4 xv;
   rc = view4(x, "wf2cu_unfold", g.N, g.C, g.H, g.W, &xv.p, xv.s);
   if (rc) return rc;
-  const int64_t total = (int64_t)g.N * g.Ho * g.Wo * g.C * g.KH * g.KW;
+  const int64_t total = (int64_t)g.N * g.Ho * g.Wo * g.C * g.KH;
   if (total == 0) return 0;
   unfold_rows_kernel<<<grid_for(total), 256, 0, S().stream>>>((float*)rows + rows_off, xv, g, total);
   return post_launch("wf2cu_unfold");
@@ -334,7 +344,7 @@ extern "C" int wf2cu_pool2d(int mode, const wf2cu_view* x, const wf2cu_view* out
 }
 
 extern "C" int wf2cu_pool2d_backward(int mode, const wf2cu_view* x, const wf2cu_view* out, const wf2cu_view* dout,
-                                     const wf2cu_view* dx, const wf2cu_unfold_geom* geom, int accumulate) {
+                                     const wf2cu_view* dx, const wf2cu_unfold_geom* geom, int accumulate, int relu_input) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(mode == WF2CU_POOL_MAX || mode == WF2CU_POOL_AVG, "wf2cu_pool2d_backward: bad mode %d", mode);
   Geom g;
@@ -343,9 +353,11 @@ extern "C" int wf2cu_pool2d_backward(int mode, const wf2cu_view* x, const wf2cu_
   View4 xv{nullptr, {0, 0, 0, 0}}, ov{nullptr, {0, 0, 0, 0}}, dv;
   View4W gx;
   const float* p;
-  if (mode == WF2CU_POOL_MAX) {
+  if (mode == WF2CU_POOL_MAX || relu_input) {
     rc = view4(x, "wf2cu_pool2d_backward(x)", g.N, g.C, g.H, g.W, &xv.p, xv.s);
     if (rc) return rc;
+  }
+  if (mode == WF2CU_POOL_MAX) {
     rc = view4(out, "wf2cu_pool2d_backward(out)", g.N, g.C, g.Ho, g.Wo, &ov.p, ov.s);
     if (rc) return rc;
   }
@@ -362,11 +374,11 @@ extern "C" int wf2cu_pool2d_backward(int mode, const wf2cu_view* x, const wf2cu_
   const unsigned grid = grid_for(total);
   cudaStream_t st = S().stream;
   if (mode == WF2CU_POOL_AVG) {
-    if (cfast) pool2d_backward_kernel<true, true><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate);
-    else pool2d_backward_kernel<true, false><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate);
+    if (cfast) pool2d_backward_kernel<true, true><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate, relu_input);
+    else pool2d_backward_kernel<true, false><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate, relu_input);
   } else {
-    if (cfast) pool2d_backward_kernel<false, true><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate);
-    else pool2d_backward_kernel<false, false><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate);
+    if (cfast) pool2d_backward_kernel<false, true><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate, relu_input);
+    else pool2d_backward_kernel<false, false><<<grid, 256, 0, st>>>(xv, ov, dv, gx, g, total, accumulate, relu_input);
   }
   return post_launch("wf2cu_pool2d_backward");
 }

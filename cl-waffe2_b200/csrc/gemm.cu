@@ -300,153 +300,234 @@ static int sgemm_small_try(const GemmArgs& g, int64_t batch) {
 }
 
 // ------------------------------------------------------------------ skinny shapes (Conv2D on few channels)
-// Conv2D lowers to (N*Ho*Wo, C*kh*kw) x (C*kh*kw, C_out): on MNIST-CNN that is 67 600 x 9 x 4 and 6 400 x 100 x 16.
+// Conv2D lowers to (N*Ho*Wo, C*kh*kw) x (C*kh*kw, C_out): on MNIST-CNN that is 67 600 x 9 x 4 and 8 100 x 100 x 16.
 // A 64x64 output tile is then almost empty along n, and the weight-gradient GEMM (4 x 9 outputs over k = 67 600)
-// would run on one tile.  Two exact-fp32 kernels cover the two shapes.
+// would run on one tile.  Two exact-fp32 kernels cover the two shapes.  Both are latency-bound, not
+// bandwidth-bound (a few MB, L2-resident): what matters is enough threads and independent loads in flight —
+// a first version with one thread per row (8 K threads on the GPU) ran at IPC 0.28 and took 83 us on 8 100 x 100 x 16
+// (profiles/r01c_ncu_cnn_skinny.md).
 
-// (a) C[M, n] = A[M, k] . B^T, B stored (n, k), n <= 32, n*k <= 4096: B lives in shared memory, a CTA owns 128
-// rows of A staged through shared memory in k-slices (coalesced global reads), one thread per row, n accumulators.
-constexpr int SK_ROWS = 128;
-constexpr int SK_TK = 32;
-template <int NMAX>
-__global__ void __launch_bounds__(SK_ROWS) sgemm_skinny_nt_kernel(const __grid_constant__ GemmArgs g) {
-  __shared__ float Bs[4096];
-  __shared__ float As[SK_ROWS * (SK_TK + 1)];
+// (a) C[M, n] = A[M, k] . B^T, B stored (n, k), n <= 32, n*k <= 4096: one thread per OUTPUT element, 256 / NP rows
+// per CTA (NP = n rounded up to a power of two).  B sits in shared memory with an odd row stride (the NP threads of
+// a row read NP different banks), A is staged in k-slices through shared memory with coalesced global reads and is
+// read back as a broadcast.
+constexpr int SKN_TK = 64;
+template <int NP>
+__global__ void __launch_bounds__(256) sgemm_skinny_nt_kernel(const __grid_constant__ GemmArgs g) {
+  constexpr int R = 256 / NP;
+  __shared__ float Bs[4096 + 64];
+  __shared__ float As[R * (SKN_TK + 1)];
   const int t = threadIdx.x;
   const int n = (int)g.n, k = (int)g.k;
-  for (int i = t; i < n * k; i += SK_ROWS) Bs[i] = g.B[(int64_t)(i / k) * g.ldb + (i % k)];
-  const int64_t row0 = (int64_t)blockIdx.x * SK_ROWS;
-  const int rows = (int)((g.m - row0) < SK_ROWS ? (g.m - row0) : SK_ROWS);
-  float acc[NMAX];
-#pragma unroll
-  for (int j = 0; j < NMAX; ++j) acc[j] = 0.f;
-  for (int k0 = 0; k0 < k; k0 += SK_TK) {
-    const int tk = (k - k0) < SK_TK ? (k - k0) : SK_TK;
+  const int kp = k | 1;
+  for (int i = t; i < n * k; i += 256) { const int jj = i / k, cc = i - jj * k; Bs[jj * kp + cc] = __ldg(g.B + (int64_t)jj * g.ldb + cc); }
+  const int64_t row0 = (int64_t)blockIdx.x * R;
+  const int rows = (int)((g.m - row0) < R ? (g.m - row0) : R);
+  const int r = t / NP, j = t % NP;
+  const bool mine = r < rows && j < n;
+  float acc0 = 0.f, acc1 = 0.f;
+  for (int k0 = 0; k0 < k; k0 += SKN_TK) {
+    const int tk = (k - k0) < SKN_TK ? (k - k0) : SKN_TK;
     __syncthreads();
-    for (int i = t; i < rows * tk; i += SK_ROWS) {
-      const int r = i / tk, c = i - r * tk;
-      As[r * (SK_TK + 1) + c] = g.A[(row0 + r) * g.lda + k0 + c];
-    }
-    __syncthreads();
-    if (t < rows) {
-      for (int c = 0; c < tk; ++c) {
-        const float a = As[t * (SK_TK + 1) + c];
+    const int total = rows * tk;
+    for (int i0 = t; i0 < total; i0 += 256 * 4) {
+      float v[4];
 #pragma unroll
-        for (int j = 0; j < NMAX; ++j)
-          if (j < n) acc[j] = fmaf(a, Bs[j * k + k0 + c], acc[j]);
+      for (int u = 0; u < 4; ++u) {
+        // unconditional (clamped) loads: a guarded load is not hoisted above the previous store and the
+        // four round trips would run one after the other
+        const int i = min(i0 + u * 256, total - 1);
+        const int rr = i / tk, cc = i - rr * tk;
+        v[u] = __ldg(g.A + (row0 + rr) * g.lda + k0 + cc);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * 256;
+        const int rr = i / tk, cc = i - rr * tk;
+        if (i < total) As[rr * (SKN_TK + 1) + cc] = v[u];
       }
     }
+    __syncthreads();
+    if (mine) {
+      const float* ap = As + r * (SKN_TK + 1);
+      const float* bp = Bs + j * kp + k0;
+      int c = 0;
+      for (; c + 1 < tk; c += 2) { acc0 = fmaf(ap[c], bp[c], acc0); acc1 = fmaf(ap[c + 1], bp[c + 1], acc1); }
+      if (c < tk) acc0 = fmaf(ap[c], bp[c], acc0);
+    }
   }
-  if (t < rows) {
-    float* crow = g.C + (row0 + t) * g.ldc;
-#pragma unroll
-    for (int j = 0; j < NMAX; ++j)
-      if (j < n) crow[j] = epilogue(g, acc[j], row0 + t, j);
-  }
+  if (mine) g.C[(row0 + r) * g.ldc + j] = epilogue(g, acc0 + acc1, row0 + r, j);
 }
 
 static int sgemm_skinny_nt_try(const GemmArgs& g, int64_t batch) {
   if (batch != 1 || g.ta || !g.tb) return 0;
   if (g.n > 32 || g.n * g.k > 4096 || g.m < 2048) return 0;
-  const unsigned grid = (unsigned)((g.m + SK_ROWS - 1) / SK_ROWS);
   cudaStream_t st = S().stream;
-  if (g.n <= 4) sgemm_skinny_nt_kernel<4><<<grid, SK_ROWS, 0, st>>>(g);
-  else if (g.n <= 8) sgemm_skinny_nt_kernel<8><<<grid, SK_ROWS, 0, st>>>(g);
-  else if (g.n <= 16) sgemm_skinny_nt_kernel<16><<<grid, SK_ROWS, 0, st>>>(g);
-  else sgemm_skinny_nt_kernel<32><<<grid, SK_ROWS, 0, st>>>(g);
+  if (g.n <= 4) sgemm_skinny_nt_kernel<4><<<(unsigned)((g.m + 63) / 64), 256, 0, st>>>(g);
+  else if (g.n <= 8) sgemm_skinny_nt_kernel<8><<<(unsigned)((g.m + 31) / 32), 256, 0, st>>>(g);
+  else if (g.n <= 16) sgemm_skinny_nt_kernel<16><<<(unsigned)((g.m + 15) / 16), 256, 0, st>>>(g);
+  else sgemm_skinny_nt_kernel<32><<<(unsigned)((g.m + 7) / 8), 256, 0, st>>>(g);
   const int rc = post_launch("wf2cu_gemm(skinny nt)");
   return rc ? -rc : 1;
 }
 
-// (b) C[m, n] = A^T . B with A stored (K, m), B stored (K, n), m <= 16, n <= 128, K long (a weight gradient):
-// a reduction over K with an m x n accumulator.  CTA c owns a slice of K, warp w its rows w, w+8, ...; the 32
-// lanes form a 4 x 8 grid over the outputs (lane (li, lj) owns i = li + 4a, j = lj + 8b), so one row of A is one
-// broadcast read and one row of B one coalesced read per warp.  Warp partials meet in shared memory in warp
-// order, CTA partials through a last-block ticket in CTA order: deterministic.
+// (b) C[m, n] = A^T . B with A stored (K, m), B stored (K, n), m*n <= 2048, K long (a weight gradient): a reduction
+// over K with an m x n accumulator.  CTA c owns a slice of K and walks it in chunks of 64 rows staged through shared
+// memory (coalesced reads, 4 per thread in flight).  m*n > 256: thread t owns outputs t, t+256, ... (Q of them);
+// m*n <= 256: 256 / (m*n) thread groups share the chunk's rows and meet in shared memory.  CTA partials meet through
+// a last-block ticket; every load of the fold is independent of the others.  All orders are fixed: deterministic.
 struct SkinnyTnArgs {
   GemmArgs g;
   float* partial; unsigned int* counter;
   int64_t rows_per_cta; int ctas;
+  int ks;                 // rows per staged chunk: as many as fit 32 KiB (64 .. 512)
 };
 
-template <int TI, int TJ>
+template <int Q>
 __global__ void __launch_bounds__(256) sgemm_skinny_tn_kernel(const __grid_constant__ SkinnyTnArgs a) {
-  extern __shared__ float red[];          // m * n
+  extern __shared__ float smem[];         // As[KS][m] | Bs[KS][n] | red[256]
   __shared__ bool is_last;
   const GemmArgs& g = a.g;
-  const int m = (int)g.m, n = (int)g.n;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int li = lane >> 3, lj = lane & 7;
+  const int m = (int)g.m, n = (int)g.n, mn = m * n;
+  const int SKT_KS = a.ks;
+  float* As = smem;
+  float* Bs = smem + SKT_KS * m;
+  float* red = Bs + SKT_KS * n;
+  const int t = threadIdx.x;
+  const int G = (Q == 1 && mn <= 256) ? 256 / mn : 1;       // thread groups sharing the rows
+  const int grp = (G > 1) ? t / mn : 0;
+  const int o0 = (G > 1) ? t % mn : t;
+  int ai[Q], bj[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { const int o = o0 + 256 * q; ai[q] = o < mn ? o / n : 0; bj[q] = o < mn ? o % n : 0; }
+  const bool active = (G > 1) ? grp < G : true;
+  float acc[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) acc[q] = 0.f;
   const int64_t k0 = (int64_t)blockIdx.x * a.rows_per_cta;
   int64_t k1 = k0 + a.rows_per_cta;
   if (k1 > g.k) k1 = g.k;
-  float acc[TI][TJ];
+  for (int64_t kc = k0; kc < k1; kc += SKT_KS) {
+    const int rows = (int)((k1 - kc) < SKT_KS ? (k1 - kc) : SKT_KS);
+    __syncthreads();
+    {
+      // A rows then B rows of the chunk, 8 unconditional (clamped) loads per thread in flight
+      const int ta = rows * m, tb = rows * n;
+      for (int i0 = t; i0 < ta; i0 += 256 * 8) {
+        float v[8];
 #pragma unroll
-  for (int x = 0; x < TI; ++x)
-#pragma unroll
-    for (int y = 0; y < TJ; ++y) acc[x][y] = 0.f;
-  for (int64_t kk = k0 + warp; kk < k1; kk += 8) {
-    const float* ar = g.A + kk * g.lda;
-    const float* br = g.B + kk * g.ldb;
-    float av[TI], bv[TJ];
-#pragma unroll
-    for (int x = 0; x < TI; ++x) { const int i = li + 4 * x; av[x] = i < m ? __ldg(ar + i) : 0.f; }
-#pragma unroll
-    for (int y = 0; y < TJ; ++y) { const int j = lj + 8 * y; bv[y] = j < n ? __ldg(br + j) : 0.f; }
-#pragma unroll
-    for (int x = 0; x < TI; ++x)
-#pragma unroll
-      for (int y = 0; y < TJ; ++y) acc[x][y] = fmaf(av[x], bv[y], acc[x][y]);
-  }
-  for (int w = 0; w < 8; ++w) {
-    if (warp == w) {
-#pragma unroll
-      for (int x = 0; x < TI; ++x)
-#pragma unroll
-        for (int y = 0; y < TJ; ++y) {
-          const int i = li + 4 * x, j = lj + 8 * y;
-          if (i < m && j < n) red[i * n + j] = (w == 0) ? acc[x][y] : red[i * n + j] + acc[x][y];
+        for (int u = 0; u < 8; ++u) {
+          const int i = min(i0 + u * 256, ta - 1);
+          const int rr = i / m, cc = i - rr * m;
+          v[u] = __ldg(g.A + (kc + rr) * g.lda + cc);
         }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { const int i = i0 + u * 256; if (i < ta) As[i] = v[u]; }
+      }
+      for (int i0 = t; i0 < tb; i0 += 256 * 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = min(i0 + u * 256, tb - 1);
+          const int rr = i / n, cc = i - rr * n;
+          v[u] = __ldg(g.B + (kc + rr) * g.ldb + cc);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { const int i = i0 + u * 256; if (i < tb) Bs[i] = v[u]; }
+      }
     }
     __syncthreads();
+    if (active) {
+      for (int rr = grp; rr < rows; rr += G) {
+        const float* ap = As + rr * m;
+        const float* bp = Bs + rr * n;
+#pragma unroll
+        for (int q = 0; q < Q; ++q) acc[q] = fmaf(ap[ai[q]], bp[bj[q]], acc[q]);
+      }
+    }
   }
-  const int mn = m * n;
+  // groups meet (fixed order), then the CTA's partial goes out
+  if (G > 1) {
+    __syncthreads();
+    red[t] = active ? acc[0] : 0.f;
+    __syncthreads();
+    if (t < mn) { float r = 0.f; for (int q = 0; q < G; ++q) r += red[q * mn + t]; acc[0] = r; }
+  }
+  const bool owner = (G > 1) ? t < mn : true;
   if (a.ctas == 1) {
-    for (int o = threadIdx.x; o < mn; o += 256) { const int i = o / n, j = o - i * n; g.C[(int64_t)i * g.ldc + j] = epilogue(g, red[o], i, j); }
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int o = o0 + 256 * q;
+      if (owner && o < mn) g.C[(int64_t)ai[q] * g.ldc + bj[q]] = epilogue(g, acc[q], ai[q], bj[q]);
+    }
     return;
   }
   float* mine = a.partial + (int64_t)blockIdx.x * mn;
-  for (int o = threadIdx.x; o < mn; o += 256) mine[o] = red[o];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { const int o = o0 + 256 * q; if (owner && o < mn) mine[o] = acc[q]; }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (t == 0) {
     __threadfence();
     is_last = (atomicAdd(a.counter, 1u) == (unsigned)a.ctas - 1);
   }
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  for (int o = threadIdx.x; o < mn; o += 256) {
+  if (G > 1) {
+    // thread (grp, o) sums partials grp, grp+G, ...; 4 in flight; groups meet in shared memory
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int c = 0;
-    for (; c + 3 < a.ctas; c += 4) {
-      s0 += __ldcg(a.partial + (int64_t)c * mn + o); s1 += __ldcg(a.partial + (int64_t)(c + 1) * mn + o);
-      s2 += __ldcg(a.partial + (int64_t)(c + 2) * mn + o); s3 += __ldcg(a.partial + (int64_t)(c + 3) * mn + o);
+    if (active) {
+      int c = grp;
+      for (; c + 3 * G < a.ctas; c += 4 * G) {
+        s0 += __ldcg(a.partial + (int64_t)c * mn + o0); s1 += __ldcg(a.partial + (int64_t)(c + G) * mn + o0);
+        s2 += __ldcg(a.partial + (int64_t)(c + 2 * G) * mn + o0); s3 += __ldcg(a.partial + (int64_t)(c + 3 * G) * mn + o0);
+      }
+      for (; c < a.ctas; c += G) s0 += __ldcg(a.partial + (int64_t)c * mn + o0);
     }
-    for (; c < a.ctas; ++c) s0 += __ldcg(a.partial + (int64_t)c * mn + o);
-    const int i = o / n, j = o - i * n;
-    g.C[(int64_t)i * g.ldc + j] = epilogue(g, (s0 + s1) + (s2 + s3), i, j);
+    __syncthreads();
+    red[t] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (t < mn) {
+      float r = 0.f;
+      for (int q = 0; q < G; ++q) r += red[q * mn + t];
+      g.C[(int64_t)ai[0] * g.ldc + bj[0]] = epilogue(g, r, ai[0], bj[0]);
+    }
+  } else {
+    // Q outputs x 4 partials per step, every load unconditional (clamped) so that all of them are in flight
+    float s[Q][4];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) { s[q][0] = s[q][1] = s[q][2] = s[q][3] = 0.f; }
+    for (int c = 0; c < a.ctas; c += 4) {
+      float v[Q][4];
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const int o = min(o0 + 256 * q, mn - 1);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[q][u] = __ldcg(a.partial + (int64_t)min(c + u, a.ctas - 1) * mn + o);
+      }
+#pragma unroll
+      for (int q = 0; q < Q; ++q)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) s[q][u] += (c + u < a.ctas) ? v[q][u] : 0.f;
+    }
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const int o = o0 + 256 * q;
+      if (o < mn) g.C[(int64_t)ai[q] * g.ldc + bj[q]] = epilogue(g, (s[q][0] + s[q][1]) + (s[q][2] + s[q][3]), ai[q], bj[q]);
+    }
   }
-  if (threadIdx.x == 0) *a.counter = 0;
+  if (t == 0) *a.counter = 0;
 }
 
 static int sgemm_skinny_tn_try(const GemmArgs& g, int64_t batch) {
   if (batch != 1 || !g.ta || g.tb) return 0;
-  if (g.m > 16 || g.n > 128 || g.k < 2048) return 0;
+  const int64_t mn = g.m * g.n;
+  if (mn > 2048 || g.m + g.n > 176 || g.k < 2048) return 0;        // chunk of A and B rows <= 45 KiB of shared memory
   SkinnyTnArgs a;
   a.g = g;
-  const int64_t mn = g.m * g.n;
-  int64_t ctas = g.k / 128;                                    // >= 16 rows per warp
-  const int64_t cap = mn <= 256 ? (int64_t)S().sm_count * 2 : (int64_t)S().sm_count;
+  // slices: at least 64 rows each; the fold reads ctas x mn floats in one CTA, so fewer slices for bigger results
+  int64_t ctas = g.k / 64;
+  const int64_t cap = mn <= 256 ? (int64_t)S().sm_count : (mn <= 1024 ? 96 : 64);
   if (ctas > cap) ctas = cap;
   if (ctas < 1) ctas = 1;
   a.rows_per_cta = (g.k + ctas - 1) / ctas;
@@ -459,13 +540,17 @@ static int sgemm_skinny_tn_try(const GemmArgs& g, int64_t batch) {
     a.partial = (float*)scratch_base();
     a.counter = counters_base();
   }
-  const size_t smem = (size_t)mn * sizeof(float);
+  int ks = (int)(8192 / (g.m + g.n)) & ~7;
+  if (ks > 512) ks = 512;
+  if (ks < 64) ks = 64;
+  a.ks = ks;
+  const size_t smem = (size_t)(ks * (g.m + g.n) + 256) * sizeof(float);
   cudaStream_t st = S().stream;
-  const int ti = (int)((g.m + 3) / 4), tj = (int)((g.n + 7) / 8);
-  if (ti <= 1 && tj <= 2) sgemm_skinny_tn_kernel<1, 2><<<(unsigned)ctas, 256, smem, st>>>(a);
-  else if (ti <= 2 && tj <= 4) sgemm_skinny_tn_kernel<2, 4><<<(unsigned)ctas, 256, smem, st>>>(a);
-  else if (ti <= 4 && tj <= 8) sgemm_skinny_tn_kernel<4, 8><<<(unsigned)ctas, 256, smem, st>>>(a);
-  else sgemm_skinny_tn_kernel<4, 16><<<(unsigned)ctas, 256, smem, st>>>(a);
+  const int q = (int)((mn + 255) / 256);
+  if (q <= 1) sgemm_skinny_tn_kernel<1><<<(unsigned)ctas, 256, smem, st>>>(a);
+  else if (q <= 2) sgemm_skinny_tn_kernel<2><<<(unsigned)ctas, 256, smem, st>>>(a);
+  else if (q <= 4) sgemm_skinny_tn_kernel<4><<<(unsigned)ctas, 256, smem, st>>>(a);
+  else sgemm_skinny_tn_kernel<8><<<(unsigned)ctas, 256, smem, st>>>(a);
   const int rc = post_launch("wf2cu_gemm(skinny tn)");
   return rc ? -rc : 1;
 }

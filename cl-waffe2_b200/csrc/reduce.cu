@@ -836,7 +836,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
     if (a.B == 1 && a.K <= 64 && a.sR_src == a.K && a.R >= 256) {
       // narrow and tall: one flat contiguous run
       const int64_t L = 256 / a.K;
-      int64_t splits = (a.R + 4 * L * 8 - 1) / (4 * L * 8);          // >= 8 unrolled steps per CTA
+      int64_t splits = (a.R + 4 * L * 2 - 1) / (4 * L * 2);          // two unrolled steps (8 loads) per thread: latency-bound otherwise
       if (splits > (int64_t)s.sm_count * 2) splits = (int64_t)s.sm_count * 2;
       int64_t rps = (a.R + splits - 1) / splits;
       splits = (a.R + rps - 1) / rps;

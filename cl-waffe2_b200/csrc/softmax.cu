@@ -182,6 +182,8 @@ struct SmLaneArgs {
   int64_t nlanes;
   int avoid_overflow;
   float pre_div;                   // != 0: every element is divided by it first (the `(!div w n)` node in front, folded in)
+  float pre_mul;                   // != 0: pre_div is a power of two; x * pre_mul is then the same real number as
+                                   // x / pre_div, so the correctly rounded product IS the quotient (1 instruction, not ~10)
 };
 
 template <int RCACHE>
@@ -259,7 +261,13 @@ __global__ void __launch_bounds__(256) softmax_lane_vec_kernel(const __grid_cons
 #pragma unroll
     for (int k = 0; k < RCACHE; ++k)
       v[k] = (k < a.R) ? *reinterpret_cast<const float4*>(xp + k * a.sR_x) : make_float4(0.f, 0.f, 0.f, 0.f);
-    if (a.pre_div != 0.f) {
+    if (a.pre_mul != 0.f) {
+#pragma unroll
+      for (int k = 0; k < RCACHE; ++k) {
+        v[k].x = __fmul_rn(v[k].x, a.pre_mul); v[k].y = __fmul_rn(v[k].y, a.pre_mul);
+        v[k].z = __fmul_rn(v[k].z, a.pre_mul); v[k].w = __fmul_rn(v[k].w, a.pre_mul);
+      }
+    } else if (a.pre_div != 0.f) {
 #pragma unroll
       for (int k = 0; k < RCACHE; ++k) {
         v[k].x = __fdiv_rn(v[k].x, a.pre_div); v[k].y = __fdiv_rn(v[k].y, a.pre_div);
@@ -455,6 +463,12 @@ extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int 
   a.x = xp; a.out = op; a.R = R; a.sR_x = x->stride[axis]; a.sR_o = out->stride[axis];
   a.avoid_overflow = avoid_overflow;
   a.pre_div = pre_divisor;
+  {
+    int e = 0;
+    const float mant = frexpf(fabsf(pre_divisor), &e);
+    // power of two with a representable, normal reciprocal
+    if (pre_divisor != 0.f && mant == 0.5f && e > -120 && e < 120) a.pre_mul = 1.0f / pre_divisor;
+  }
   a.nlanes = 1;
   for (int i = 0; i < rank; ++i) {
     if (i == axis || x->shape[i] == 1) continue;

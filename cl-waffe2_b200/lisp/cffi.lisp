@@ -123,7 +123,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 fold ((drows :pointer) (drows-off :int64) (dx :pointer) (geom :pointer) (accumulate :int)))
 (defwf2 pool2d ((mode :int) (x :pointer) (out :pointer) (geom :pointer)))
 (defwf2 pool2d-backward ((mode :int) (x :pointer) (out :pointer) (dout :pointer) (dx :pointer) (geom :pointer)
-			 (accumulate :int)))
+			 (accumulate :int) (relu-input :int)))
 ;; multi-GPU
 (defwf2 comm-unique-id ((out128 :pointer)))
 (defwf2 comm-init ((rank :int) (world :int) (id128 :pointer)))

@@ -267,9 +267,12 @@ enum wf2cu_pool_mode { WF2CU_POOL_MAX = 0, WF2CU_POOL_AVG = 1 };
 int  wf2cu_pool2d(int mode, const wf2cu_view* x, const wf2cu_view* out, const wf2cu_unfold_geom* g);
 /* Backward: max = MaxValue-Node backward (`base-impl/matrix-ops.lisp:311-334`: (a == max a) * dout, every
  * tie gets the gradient) followed by the unfold backward; avg = dout / (KH*KW) spread over the window.
- * x and out are read for max only (may be NULL for avg).  dx <- or += . */
+ * x and out are read for max only (may be NULL for avg).  dx <- or += .
+ * relu_input != 0: x is the result of a fused `... + !relu` node (wf2cu_gemm_ex act 1); the `!relu` backward
+ * `dout * (x > 0 ? 1 : 0)` (`nn/activation.lisp:11-26`) is applied to the contribution here (x is then read
+ * for avg too). */
 int  wf2cu_pool2d_backward(int mode, const wf2cu_view* x, const wf2cu_view* out, const wf2cu_view* dout,
-                           const wf2cu_view* dx, const wf2cu_unfold_geom* g, int accumulate);
+                           const wf2cu_view* dx, const wf2cu_unfold_geom* g, int accumulate, int relu_input);
 
 /* ===================== multi-GPU (batch-sharded MLP step) ===================== */
 int  wf2cu_comm_unique_id(void* out128);                       /* rank 0: 128-byte NCCL id   */

@@ -246,7 +246,7 @@ def test_unfold_declines_dilation(gpu):
     assert lib.wf2cu_unfold(C.byref(x.lower()), rows.vec.ptr, 0, C.byref(g)) == 3      # WF2CU_ERR_UNSUPPORTED
 
 
-@pytest.mark.parametrize("shape", [(67600, 4, 9), (6400, 16, 100), (4096, 32, 128), (2048, 1, 7), (3001, 5, 33)])
+@pytest.mark.parametrize("shape", [(67600, 4, 9), (8100, 16, 100), (4096, 32, 128), (2048, 1, 7), (3001, 5, 33), (2500, 3, 1000), (5000, 20, 200)])
 def test_skinny_forward_gemm(gpu, shape):
     # Conv2D's forward product (N*Ho*Wo, C*kh*kw) x (!t (C_out, C*kh*kw)) with bias + relu in the epilogue
     ops = importlib.import_module("cl-waffe2_b200.ops")
@@ -263,7 +263,7 @@ def test_skinny_forward_gemm(gpu, shape):
     np.testing.assert_allclose(out.to_numpy(), ref2, rtol=1e-4, atol=1e-4 * np.abs(ref).max())
 
 
-@pytest.mark.parametrize("shape", [(4, 9, 67600), (16, 100, 6400), (16, 128, 2048), (1, 1, 5000), (3, 17, 2049), (13, 77, 40000)])
+@pytest.mark.parametrize("shape", [(4, 9, 67600), (16, 100, 8100), (16, 128, 2048), (1, 1, 5000), (3, 17, 2049), (13, 77, 40000), (40, 50, 3000), (2, 170, 2500), (7, 36, 100000)])
 def test_skinny_weight_gradient_gemm(gpu, shape):
     # Conv2D's weight gradient: (!t dout (K, m)) x rows (K, n), a long reduction with a small result
     ops = importlib.import_module("cl-waffe2_b200.ops")
@@ -295,3 +295,23 @@ def test_narrow_column_sum(gpu, shape):
     gb = gpu.view(acc, [":broadcast", rows], True)
     gpu._lib.check(lib.wf2cu_reduce_sum(C.byref(x.lower()), C.byref(gb.lower()), 1, 0.0))
     np.testing.assert_allclose(acc.to_numpy().ravel(), truth + 1.0, rtol=0, atol=1e-5 * np.abs(X).astype(np.float64).sum(axis=0).max())
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_pool2d_backward_applies_relu_mask(gpu, mode):
+    # the `!relu` backward folded into the pooling backward: dx = fold(...) * (x > 0)
+    _, cv = _mods(gpu)
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(11)
+    X = rng.standard_normal((3, 4, 10, 10)).astype(np.float32)
+    g = cv.Geometry(X.shape, (2, 2), (2, 2), (0, 0))
+    x = gpu.from_numpy(X)
+    out = cv._channels_last(3, 4, 5, 5)
+    gs = g.struct(False)
+    gpu._lib.check(lib.wf2cu_pool2d(mode, C.byref(x.lower()), C.byref(out.lower()), C.byref(gs)))
+    dout = gpu.from_numpy(rng.standard_normal((3, 4, 5, 5)).astype(np.float32))
+    plain = gpu.make_tensor(X.shape)
+    masked = gpu.from_numpy(np.ones(X.shape, np.float32))
+    gpu._lib.check(lib.wf2cu_pool2d_backward(mode, C.byref(x.lower()), C.byref(out.lower()), C.byref(dout.lower()), C.byref(plain.lower()), C.byref(gs), 0, 0))
+    gpu._lib.check(lib.wf2cu_pool2d_backward(mode, C.byref(x.lower()), C.byref(out.lower()), C.byref(dout.lower()), C.byref(masked.lower()), C.byref(gs), 1, 1))
+    np.testing.assert_array_equal(masked.to_numpy(), np.float32(1.0) + plain.to_numpy() * (X > 0))
