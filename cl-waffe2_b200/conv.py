@@ -385,6 +385,12 @@ class MNISTCNN:
     def parameters(self) -> List[CUDATensor]:
         return self.arena.params
 
+    def named_parameters(self):
+        """Conv2D's slots are `weight` and `bias` (nn/conv.lisp:52-58), LinearLayer's `weights` and `bias`."""
+        p = self.arena.params
+        return [("Conv2D", "weight", p[0]), ("Conv2D", "bias", p[1]), ("Conv2D", "weight", p[2]), ("Conv2D", "bias", p[3]),
+                ("LinearLayer", "weights", p[4]), ("LinearLayer", "bias", p[5])]
+
     def __call__(self, x: CUDATensor) -> CUDATensor:
         W1, b1, W2, b2, W3, b3 = self.arena.params
         h = conv2d(x, W1, b1, fuse_relu=nn.FUSE)

@@ -415,6 +415,14 @@ class MLPSequence:
     def parameters(self) -> List[CUDATensor]:
         return self.arena.params
 
+    def named_parameters(self):
+        """(composite, slot, tensor) in parameter order: LinearLayer's slots are `weights` and `bias`
+        (nn/regression.lisp:20-55), which gives the state-dict keys `param:linearlayer.<nth>.weights`."""
+        out = []
+        for i in range(len(self.dims) - 1):
+            out += [("LinearLayer", "weights", self.arena.params[2 * i]), ("LinearLayer", "bias", self.arena.params[2 * i + 1])]
+        return out
+
     def __call__(self, x: CUDATensor) -> CUDATensor:
         p = self.arena.params
         n = len(self.dims) - 1
@@ -471,6 +479,29 @@ class Adam:
         a = self.arena
         _lib.check(_lib.load().wf2cu_adam_step(a.param_store.ptr, 0, a.grad_store.ptr, 0, self.m.ptr, 0, self.v.ptr, 0,
                                                a.total, 0.0, self.lr_t.ptr, self.b1, self.b2, self.eps, grad_scale))
+
+    # ---- state-dict slots (`find-params` on the optimizer, state-dicts.lisp:204-222): per parameter idx
+    def _slice(self, store: Storage, idx: int) -> CUDATensor:
+        a = self.arena
+        return tensor_at(store, a.offsets[idx], a.params[idx].shape)
+
+    def state_for(self, idx: int):
+        """[(slot, lisp-type-name, value)] as `(type-of value)` prints them in SBCL, lower case."""
+        int_type = "bit" if self.n <= 1 else "(integer 0 4611686018427387903)"
+        return [("lr", "single-float", self.lr), ("eps", "single-float", self.eps), ("beta1", "single-float", self.b1),
+                ("beta2", "single-float", self.b2), ("n", int_type, int(self.n)),
+                ("m", "cudatensor", self._slice(self.m, idx)), ("v", "cudatensor", self._slice(self.v, idx))]
+
+    def restore(self, idx: int, slot: str, value) -> None:
+        """Scalars are shared by every parameter's optimizer instance in the reference; here they are one."""
+        if slot == "n":
+            self.n = int(value)
+        elif slot in ("lr", "eps"):
+            setattr(self, slot, float(np.float32(value)))
+        elif slot in ("beta1", "beta2"):
+            setattr(self, "b1" if slot == "beta1" else "b2", float(np.float32(value)))
+        else:
+            raise KeyError(f"Adam: no slot {slot!r}")
 
     def step_p2p(self):
         """Data-parallel step as ONE kernel: sum of all ranks' gradient arenas over NVLink peer memory,

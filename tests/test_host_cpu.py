@@ -175,3 +175,27 @@ def test_product_does_not_import_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
                 assert "oracle/" not in src and "libwaffe2_port" not in src and "libwaffe2simd_ref" not in src, f
+
+
+def test_state_dict_key_convention(wf):
+    """`{prefix}:{composite}.{nth}.{slot}` (vm/generic-tensor/state-dicts.lisp:71-96,152-235): nth counts
+    duplicates from 0; keys parse back with parse-state-dict-key."""
+    import importlib
+    sd = importlib.import_module("cl-waffe2_b200.state_dict")
+
+    class Opt:
+        def state_for(self, idx):
+            return [("lr", "single-float", 0.5), ("n", "bit", 0)]
+    Opt.__name__ = "Adam"
+    named = [("LinearLayer", "weights", "W0"), ("LinearLayer", "bias", "b0"), ("Conv2D", "weight", "C0"),
+             ("LinearLayer", "weights", "W1"), ("LinearLayer", "bias", "b1")]
+    d = sd.make_state_dict(named, Opt(), optimizers=True)
+    assert d["param:linearlayer.0.weights"] == "W0" and d["param:linearlayer.1.weights"] == "W1"
+    assert d["param:conv2d.0.weight"] == "C0" and d["param:linearlayer.1.bias"] == "b1"
+    assert d["optimizer:linearlayer.0.bias.adam.single-float.lr"] == 0.5
+    assert d["optimizer:linearlayer.1.weights.adam.bit.n"] == 0
+    assert sd.parse_state_dict_key("param:linearlayer.0.bias") == ("param", ["linearlayer", "0", "bias"])
+    assert sd.parse_state_dict_key("optimizer:linearlayer.0.bias.adam.single-float.lr")[0] == "optimizer"
+    with pytest.raises(ValueError):
+        sd.parse_state_dict_key("weights:linearlayer.0.bias")
+    assert len(sd.make_state_dict(named, Opt(), weights=False, optimizers=True)) == 10
