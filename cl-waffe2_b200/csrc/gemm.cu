@@ -381,6 +381,7 @@ struct SkinnyTnArgs {
   float* partial; unsigned int* counter;
   int64_t rows_per_cta; int ctas;
   int ks;                 // rows per staged chunk: as many as fit 32 KiB (64 .. 512)
+  int dense4;             // lda == m, ldb == n, 16-byte aligned, every chunk a whole number of float4
 };
 
 template <int Q>
@@ -413,6 +414,29 @@ __global__ void __launch_bounds__(256) sgemm_skinny_tn_kernel(const __grid_const
     {
       // A rows then B rows of the chunk, 8 unconditional (clamped) loads per thread in flight
       const int ta = rows * m, tb = rows * n;
+      if (a.dense4) {
+        // both operands dense (lda == m, ldb == n) and 16-byte aligned: the chunk is two contiguous runs,
+        // copied as float4 (32 KiB per round trip per CTA instead of 8)
+        const float4* ga = reinterpret_cast<const float4*>(g.A + kc * g.lda);
+        const float4* gb = reinterpret_cast<const float4*>(g.B + kc * g.ldb);
+        float4* sa4 = reinterpret_cast<float4*>(As);
+        float4* sb4 = reinterpret_cast<float4*>(Bs);
+        const int na = ta >> 2, nb = tb >> 2;
+        for (int i0 = t; i0 < na; i0 += 256 * 4) {
+          float4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) v[u] = __ldg(ga + min(i0 + u * 256, na - 1));
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const int i = i0 + u * 256; if (i < na) sa4[i] = v[u]; }
+        }
+        for (int i0 = t; i0 < nb; i0 += 256 * 8) {
+          float4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = __ldg(gb + min(i0 + u * 256, nb - 1));
+#pragma unroll
+          for (int u = 0; u < 8; ++u) { const int i = i0 + u * 256; if (i < nb) sb4[i] = v[u]; }
+        }
+      } else {
       for (int i0 = t; i0 < ta; i0 += 256 * 8) {
         float v[8];
 #pragma unroll
@@ -434,6 +458,7 @@ __global__ void __launch_bounds__(256) sgemm_skinny_tn_kernel(const __grid_const
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) { const int i = i0 + u * 256; if (i < tb) Bs[i] = v[u]; }
+      }
       }
     }
     __syncthreads();
@@ -527,7 +552,8 @@ static int sgemm_skinny_tn_try(const GemmArgs& g, int64_t batch) {
   a.g = g;
   // slices: at least 64 rows each; the fold reads ctas x mn floats in one CTA, so fewer slices for bigger results
   int64_t ctas = g.k / 64;
-  const int64_t cap = mn <= 256 ? (int64_t)S().sm_count : (mn <= 1024 ? 96 : 64);
+  const bool longk = g.k >= 32768;
+  const int64_t cap = mn <= 256 ? (int64_t)S().sm_count * (longk ? 2 : 1) : (mn <= 1024 ? (longk ? 148 : 96) : (longk ? 128 : 64));
   if (ctas > cap) ctas = cap;
   if (ctas < 1) ctas = 1;
   a.rows_per_cta = (g.k + ctas - 1) / ctas;
@@ -544,6 +570,15 @@ static int sgemm_skinny_tn_try(const GemmArgs& g, int64_t batch) {
   if (ks > 512) ks = 512;
   if (ks < 64) ks = 64;
   a.ks = ks;
+  // float4 staging needs dense operands with 16-byte aligned bases and every chunk to start and end on a multiple
+  // of 4 rows (ks is a multiple of 8; slices are rounded up to 4 rows; k itself a multiple of 4)
+  a.dense4 = 0;
+  if (g.lda == g.m && g.ldb == g.n && ((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0 && g.k % 4 == 0) {
+    a.rows_per_cta = (a.rows_per_cta + 3) & ~int64_t(3);
+    ctas = (g.k + a.rows_per_cta - 1) / a.rows_per_cta;        // never more than the scratch was sized for
+    a.ctas = (int)ctas;
+    a.dense4 = 1;
+  }
   const size_t smem = (size_t)(ks * (g.m + g.n) + 256) * sizeof(float);
   cudaStream_t st = S().stream;
   const int q = (int)((mn + 255) / 256);
@@ -588,6 +623,13 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   // auto: 50 MFLOP..1 GFLOP -> fused tcgen05 kernel (14.6 vs 22.3 us on 1024x256x784, 8.6 vs 10.2 us on 1024x256x256;
   // below 50 MFLOP its ~5 us floor loses to the SIMT split-K kernel: 7.9 vs 6.9 us on 1024x10x256; gpurun_out/gemm_small5.log)
   // mode: 0 auto | 1 fp32 SIMT | 2 tcgen05 3xTF32 (planes + persistent kernel) | 3 tcgen05 1xTF32 | 4 tcgen05 fused small kernel
+  if (mode == 0 || mode == 1) {
+    // a long reduction with a small result (Conv2D's weight gradient: 16 x 100 over k = 82 944 at batch 1024) goes to
+    // the K-sliced kernel whatever its flop count: on a tile-per-CTA kernel it is two tiles (604 us on 16 CTAs)
+    const int r = sgemm_skinny_tn_try(g, batch);
+    if (r < 0) return -r;
+    if (r == 1) return 0;
+  }
   {
     const double flops = 2.0 * (double)m * (double)n * (double)k;
     // batched with a narrow result (GPT-2's probabilities x V, n = 64 per head): the 128x256 tile of the planes path

@@ -103,8 +103,9 @@ def test_unfold_fold_bit_exact(gpu, fuse, geo, layout):
 
 @pytest.mark.parametrize("mode", ["max", "avg"])
 @pytest.mark.parametrize("geo", [(1, 3, 16, 16, 4, 4, 0, 0, 4, 4), (4, 4, 26, 26, 2, 2, 0, 0, 2, 2), (2, 3, 9, 9, 3, 3, 0, 0, 2, 2),
-                                 (2, 5, 8, 8, 2, 2, 1, 1, 2, 2), (3, 2, 7, 10, 3, 2, 0, 0, 1, 1)])
-def test_pool2d_forward_backward_bit_exact(gpu, fuse, mode, geo):
+                                 (2, 5, 8, 8, 2, 2, 1, 1, 2, 2), (3, 2, 7, 10, 3, 2, 0, 0, 1, 1), (2, 3, 12, 12, 5, 5, 0, 0, 1, 1)])
+@pytest.mark.parametrize("layout", ["nchw", "channels-last"])
+def test_pool2d_forward_backward_bit_exact(gpu, fuse, mode, geo, layout):
     nn, cv = _mods(gpu)
     from oracle import loopnest as L, conv as OC
     N, Cc, Hin, Win, kh, kw, ph, pw, sh, sw = geo
@@ -114,7 +115,13 @@ def test_pool2d_forward_backward_bit_exact(gpu, fuse, mode, geo):
     ox = L.make_tensor(list(X.shape), data=X)
     ofw, obw = (OC.maxpool2d_fw, OC.maxpool2d_bw) if mode == "max" else (OC.avgpool2d_fw, OC.avgpool2d_bw)
     oout, octx = ofw(ox, (kh, kw), (sh, sw), (ph, pw))
-    x = gpu.from_numpy(X)
+    if layout == "nchw":
+        x = gpu.from_numpy(X)
+    else:                                              # what Conv2D hands over; its gradient has the same layout
+        x = cv._channels_last(N, Cc, Hin, Win)
+        importlib.import_module("cl-waffe2_b200.ops").move_(x, gpu.from_numpy(X))
+        x._channels_last = True
+        x._grad_like = cv._grad_like
     x.requires_grad = True
     tape = nn.Tape()
     nn._tape = tape
