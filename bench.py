@@ -238,8 +238,8 @@ def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
                       "pipe_frac": 3 * tf / tf32_peak})
         del A, B, o
     top = cases[-1]
-    return {"workload": "c3_matmul_NxN_f32 (split planes + tcgen05 3xTF32, both launches timed)", "cases": cases,
-            "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::tf32, 3 passes)", "achieved": top["tflops"],
+    return {"workload": "c3_matmul_NxN_f32 (split planes + tcgen05 3xTF32, all launches timed; N <= 1024 the one-launch fused kernel, N = 2048 128x256 tiles, N >= 4096 256x256 tiles)", "cases": cases,
+            "roofline": {"bound": "tensor", "kernel": "gemm_tc256_kernel (tcgen05.mma kind::tf32, 3 passes, 256x256 tiles)", "achieved": top["tflops"],
                          "peak": tf32_peak, "unit": "TFLOP/s", "frac": top["frac_of_tf32_peak"], "pipe_frac": top["pipe_frac"],
                          "peak_source": "0.5 x MEASURED_PEAKS.json bf16_tflops (TF32 dense); of measured", "N": top["N"],
                          "traffic": None, "traffic_at_N4096": ncu_traffic("gemm_tc_kernel_N4096")}}

@@ -823,6 +823,8 @@ static int ensure_ws(size_t bytes) {
   return 0;
 }
 
+static bool g_t256_auto = true;       // auto mode may take the 256x256-tile kernel (rule in gemm_tc_try)
+
 static int make_map(CUtensorMap* map, float* base, int rows, int Kp, int nbatch, int box_rows) {
   cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)rows, (cuuint64_t)nbatch};
   cuuint64_t strides[2] = {(cuuint64_t)Kp * 4, (cuuint64_t)rows * Kp * 4};
@@ -831,6 +833,17 @@ static int make_map(CUtensorMap* map, float* base, int rows, int Kp, int nbatch,
   CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return -set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rows=%d Kp=%d batch=%d", (int)r, rows, Kp, nbatch);
+  return 0;
+}
+
+static int make_map256(CUtensorMap* map, float* base, int rows, int Kp, int nbatch) {
+  cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)rows, (cuuint64_t)nbatch};
+  cuuint64_t strides[2] = {(cuuint64_t)Kp * 4, (cuuint64_t)rows * Kp * 4};
+  cuuint32_t box[3] = {(cuuint32_t)T2K, 256, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return -set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(256x16, SWIZZLE_64B) failed (%d) rows=%d Kp=%d batch=%d", (int)r, rows, Kp, nbatch);
   return 0;
 }
 
@@ -879,7 +892,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     g_attr_set = true;
   }
   const int Kp = (int)((k + TK - 1) / TK) * TK;
-  const int passes = mode == 3 ? 1 : 3;
+  const int passes = mode == 3 ? 1 : 3;      // mode 5 = 3xTF32 on the 256x256-tile kernel
   const int a_nb = (sa == 0 || batch == 1) ? 1 : (int)batch;
   const int b_nb = (sb == 0 || batch == 1) ? 1 : (int)batch;
   auto plane = [&](int64_t rows, int nb) { return (((size_t)nb * rows * Kp * 4) + 255) & ~(size_t)255; };
@@ -898,6 +911,36 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   if (rc) return rc;
 
   CUtensorMap mah, mal, mbh, mbl;
+  // auto: the 256x256 kernel cannot overlap its epilogue with the next tile (its two accumulators fill TMEM), so it
+  // wants a long K, and it has half as many tiles, so it wants enough of them: measured on B200 (scripts/gemm_t256.py)
+  // 4096^3 234 vs 203 TFLOP/s, 8192^3 275 vs 250, 8192x768x3072 151 vs 133; but 2048^3 109 vs 163 (64 tiles) and
+  // 8192x2304x768 185 vs 193 (short K).  Results are bit-identical to the 128x256 kernel (same k order per output).
+  const int64_t tiles256 = ((m + T2M - 1) / T2M) * ((n + T2N - 1) / T2N) * batch;
+  if (mode == 5 || (mode == 0 && g_t256_auto && k >= 2048 && tiles256 >= 96)) {
+    // 256 x 256 tiles: two M = 128 MMAs share every B slice (42.7 instead of 62.5 B/clk of L2 -> SM traffic per SM)
+    static bool attr256 = false;
+    if (!attr256) {
+      cudaError_t e = cudaFuncSetAttribute(gemm_tc256_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES);
+      if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_tc256_kernel)", __FILE__, __LINE__);
+      attr256 = true;
+    }
+    if ((rc = make_map256(&mah, ah, (int)m, Kp, a_nb))) return rc;
+    if ((rc = make_map256(&mal, al, (int)m, Kp, a_nb))) return rc;
+    if ((rc = make_map256(&mbh, bh, (int)n, Kp, b_nb))) return rc;
+    if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb))) return rc;
+    TcArgs t;
+    t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = Kp / T2K;
+    t.tiles_m = (int)((m + T2M - 1) / T2M); t.tiles_n = (int)((n + T2N - 1) / T2N); t.batch = (int)batch;
+    t.passes = passes;
+    t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
+    t.a_bcast = a_nb == 1 ? 1 : 0;
+    t.b_bcast = b_nb == 1 ? 1 : 0;
+    const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
+    const int grid = (int)(total < S().sm_count ? total : S().sm_count);
+    gemm_tc256_kernel<<<grid, GEMM_THREADS, T2_SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, t);
+    rc = post_launch("wf2cu_gemm(tcgen05 256x256)");
+    return rc ? -rc : 1;
+  }
   if ((rc = make_map(&mah, ah, (int)m, Kp, a_nb, TM))) return rc;
   if ((rc = make_map(&mal, al, (int)m, Kp, a_nb, TM))) return rc;
   if ((rc = make_map(&mbh, bh, (int)n, Kp, b_nb, TN))) return rc;
