@@ -17,7 +17,7 @@ namespace wf2 {
 
 // implemented in gemm_tc.cu; returns 1 when it handled the problem, 0 when it declines, <0 error
 int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B,
-                int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode);
+                int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act);
 // gemm_tc.cu: one-launch tcgen05 kernel for small problems (in-kernel hi/lo split, cluster split-K, fused epilogue)
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                       float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
@@ -646,10 +646,12 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (out of range)", who);
   }
   if (mode != 1) {
-    const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode);
+    // bias and relu ride in the persistent kernel's epilogue; only the relu-backward mask needs its own pass
+    const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode, bias, act);
     if (r < 0) return -r;
     if (r == 1) {
-      if (!epi) return 0;
+      if (!mask) return 0;
+      g.bias = nullptr; g.act = 0;
       int64_t grid = (m * n + 255) / 256;
       const int64_t cap = (int64_t)S().sm_count * 8;
       if (grid > cap) grid = cap;

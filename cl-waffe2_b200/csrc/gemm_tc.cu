@@ -192,7 +192,25 @@ struct TcArgs {
   int passes;            // 3 = 3xTF32 (parity grade), 1 = single TF32 pass (hi planes only)
   int c_vec;             // C rows are 16-byte aligned -> 128-bit stores
   int a_bcast, b_bcast;  // operand shared by every batch index (batch stride 0): one plane set
+  const float* bias;     // != NULL: C[r, c] = acc + bias[c]  (LinearLayer's bias add folded into the epilogue)
+  int act;               // 1: then C = C * (C > 0 ? 1 : 0)  (`!relu`)
 };
+
+// epilogue of the persistent kernels: 32 consecutive columns of one row per lane; same arithmetic as the separate
+// nodes.  Called by the whole warp (col0 is warp-uniform): lane j fetches bias[col0 + j] with one coalesced load
+// and the 32 values travel by shuffle — 32 dependent loads per lane made the epilogue longer than a K = 768 mainloop.
+__device__ __forceinline__ void tc_epilogue32(const TcArgs& a, uint32_t (&v)[32], int col0, int lane) {
+  if (a.bias) {
+    const float mine = (col0 + lane < a.n) ? __ldg(a.bias + col0 + lane) : 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      v[j] = __float_as_uint(__fadd_rn(__uint_as_float(v[j]), __shfl_sync(0xffffffffu, mine, j)));
+  }
+  if (a.act == 1) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) { const float x = __uint_as_float(v[j]); v[j] = __float_as_uint(__fmul_rn(x, x > 0.f ? 1.f : 0.f)); }
+  }
+}
 
 constexpr int kGroupM = 16;   // raster: 16 m-tiles x all n-tiles per group, m fastest (L2 reuse of B panels)
 
@@ -314,6 +332,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
         tc_ld32(tbase + c * 32, v);
         tc_ld_wait();
         const int col0 = nt * TN + c * 32;
+        if (col0 < a.n) tc_epilogue32(a, v, col0, lane);
         if (row < a.m && col0 < a.n) {
           if (a.c_vec && col0 + 32 <= a.n) {
 #pragma unroll
@@ -472,6 +491,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           tc_ld32(tbase + c * 32, v);
           tc_ld_wait();
           const int col0 = nt * T2N + c * 32;
+          if (col0 < a.n) tc_epilogue32(a, v, col0, lane);
           if (row < a.m && col0 < a.n) {
             if (a.c_vec && col0 + 32 <= a.n) {
 #pragma unroll
@@ -865,8 +885,8 @@ static int launch_split(const float* src, float* hi, float* lo, int64_t ld, int6
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
 int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
-                float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode) {
-  // mode: 0 auto, 2 force 3xTF32, 3 force 1xTF32
+                float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act) {
+  // mode: 0 auto, 2 force 3xTF32, 3 force 1xTF32; bias / act: folded into the epilogue (the caller still runs the mask pass)
   if (k < 1 || m > (1 << 30) || n > (1 << 30) || k > (1 << 30) || batch > 65535) return 0;
   // the hi/lo plane workspace is one buffer: only the main stream may use it (a side branch of a compiled
   // step takes the SIMT / fused kernels instead)
@@ -935,6 +955,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
     t.a_bcast = a_nb == 1 ? 1 : 0;
     t.b_bcast = b_nb == 1 ? 1 : 0;
+    t.bias = bias; t.act = act;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     const int grid = (int)(total < S().sm_count ? total : S().sm_count);
     gemm_tc256_kernel<<<grid, GEMM_THREADS, T2_SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, t);
@@ -953,6 +974,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   t.a_bcast = a_nb == 1 ? 1 : 0;
   t.b_bcast = b_nb == 1 ? 1 : 0;
+  t.bias = bias; t.act = act;
   const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
   const int grid = (int)(total < S().sm_count ? total : S().sm_count);
   gemm_tc_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, t);

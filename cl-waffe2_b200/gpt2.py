@@ -108,6 +108,12 @@ def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
 
 def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor) -> CUDATensor:
     """`(!matmul x w)` + `(!add (%transform b[i] -> [~ i]))` (model.lisp:118-120)."""
+    if x.dims() == 3 and x.is_contiguous() and not x.permuted_p():
+        # W is shared by the batch, so (B N in) . (in out) is one (B*N in) . (in out) product; the bias add rides in the
+        # GEMM epilogue (wf2cu_gemm_ex — the MatMul + Add fusion of lisp/fusion.lisp), same arithmetic, one pass less
+        B_, N_, _ = x.shape
+        y = ops.matmul(reshape_contiguous(x, [B_ * N_, x.shape[2]]), w, bias=b)
+        return reshape_contiguous(y, [B_, N_, y.shape[1]])
     y = ops.matmul(x, w)                                    # (B N in) . (in out): W shared by the batch
     ops.add_(y, _bcast_last(b, y))
     return y

@@ -551,3 +551,29 @@ def test_matmul_tcgen05_256_tile_kernel_batched(gpu):
     finally:
         gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
     np.testing.assert_allclose(r, A.astype(np.float64) @ W.T.astype(np.float64), rtol=0, atol=2e-4)
+
+
+@pytest.mark.parametrize("mode", [0, 2, 5])
+def test_matmul_tcgen05_persistent_kernels_fold_bias_and_relu(gpu, mode):
+    """wf2cu_gemm_ex on the planes path: `+ bias` and `!relu` ride in the persistent kernels' TMEM -> global epilogue
+    (the relu-backward mask stays a separate pass); equal to the unfused nodes bit for bit."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(21)
+    m, n, k = 1536, 1000, 1024                                  # 3.1 GFLOP: auto takes planes + persistent kernel
+    A = rng.uniform(-1, 1, size=(m, k)).astype(np.float32)
+    B = rng.uniform(-1, 1, size=(k, n)).astype(np.float32)
+    bias = rng.uniform(-1, 1, size=(n,)).astype(np.float32)
+    mask = rng.uniform(-1, 1, size=(m, n)).astype(np.float32)
+    ga, gb, gbias, gmask = (gpu.from_numpy(x) for x in (A, B, bias, mask))
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
+    try:
+        plain = gpu.ops.matmul(ga, gb).to_numpy()
+        fused = gpu.ops.matmul(ga, gb, bias=gbias, relu=True).to_numpy()
+        masked = gpu.ops.matmul(ga, gb, bias=gbias, relu_mask=gmask).to_numpy()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    truth = A.astype(np.float64) @ B.astype(np.float64)
+    assert np.abs(plain - truth).max() <= 2e-5 * np.abs(truth).max()
+    want = plain + bias[None, :]
+    np.testing.assert_array_equal(fused, want * (want > 0))
+    np.testing.assert_array_equal(masked, want * (mask > 0))
