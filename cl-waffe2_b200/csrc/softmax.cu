@@ -503,6 +503,78 @@ extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int 
   return post_launch("wf2cu_softmax(lane)");
 }
 
+// ------------------------------------------------------------------ LayerNorm (GPT-2 example)
+// `LayerNorm-Revisit` (examples/gpt-2/utils.lisp:114-127) is ten nodes: !mean, !sub, !expt 2, !mean, !add eps,
+// !sqrt, !div, !mul g, !add b (+ the broadcast views) — ten passes over a (B N E) tensor, 225 launches of the 562 of
+// a GPT-2 small forward.  One kernel, a warp per row with the row in registers; every element goes through the
+// same operations in the same order as the node chain (mean = sum / count with a correctly rounded divide, square
+// as a product, IEEE sqrt and divide), the two row sums are shuffle trees (the 1e-5 reduction bar).
+struct LnArgs { const float* x; const float* g; const float* b; float* out; int64_t rows; int cols; float eps; };
+
+template <int V>   // float4 per lane: cols <= 128 * V
+__global__ void __launch_bounds__(256) layernorm_kernel(const __grid_constant__ LnArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= a.rows) return;
+  const int nv = a.cols >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(a.x + row * a.cols);
+  float4 v[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) { const int i = lane + 32 * k; v[k] = i < nv ? xr[i] : make_float4(0.f, 0.f, 0.f, 0.f); }
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < V; ++k) s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float cnt = (float)a.cols;
+  const float u = __fdiv_rn(s, cnt);
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const int i = lane + 32 * k;
+    v[k].x = __fsub_rn(v[k].x, u); v[k].y = __fsub_rn(v[k].y, u); v[k].z = __fsub_rn(v[k].z, u); v[k].w = __fsub_rn(v[k].w, u);
+    if (i < nv) q += (__fmul_rn(v[k].x, v[k].x) + __fmul_rn(v[k].y, v[k].y)) + (__fmul_rn(v[k].z, v[k].z) + __fmul_rn(v[k].w, v[k].w));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float r = __fsqrt_rn(__fadd_rn(__fdiv_rn(q, cnt), a.eps));
+  const float4* gr = reinterpret_cast<const float4*>(a.g);
+  const float4* br = reinterpret_cast<const float4*>(a.b);
+  float4* orow = reinterpret_cast<float4*>(a.out + row * a.cols);
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const int i = lane + 32 * k;
+    if (i < nv) {
+      const float4 g4 = __ldg(gr + i), b4 = __ldg(br + i);
+      float4 y;
+      y.x = __fadd_rn(__fmul_rn(__fdiv_rn(v[k].x, r), g4.x), b4.x);
+      y.y = __fadd_rn(__fmul_rn(__fdiv_rn(v[k].y, r), g4.y), b4.y);
+      y.z = __fadd_rn(__fmul_rn(__fdiv_rn(v[k].z, r), g4.z), b4.z);
+      y.w = __fadd_rn(__fmul_rn(__fdiv_rn(v[k].w, r), g4.w), b4.w);
+      orow[i] = y;
+    }
+  }
+}
+
+extern "C" int wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int64_t g_off, const void* b, int64_t b_off,
+                               void* out, int64_t out_off, int64_t rows, int64_t cols, float eps) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(x && g && b && out && rows >= 0 && cols >= 1, "wf2cu_layernorm: bad arguments");
+  LnArgs a{(const float*)x + x_off, (const float*)g + g_off, (const float*)b + b_off, (float*)out + out_off, rows, (int)cols, eps};
+  const bool ok = cols % 4 == 0 && cols <= 1024 && al16s(a.x) && al16s(a.g) && al16s(a.b) && al16s(a.out);
+  if (!ok)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_layernorm: rows of %lld floats (need a multiple of 4, <= 1024, 16-byte aligned): "
+                     "issue the node chain instead", (long long)cols);
+  if (rows == 0) return 0;
+  const int64_t grid = (rows + 7) / 8;
+  WF2_CHECK(grid < (int64_t(1) << 31), "wf2cu_layernorm: too many rows");
+  cudaStream_t st = S().stream;
+  if (cols <= 256) layernorm_kernel<2><<<(unsigned)grid, 256, 0, st>>>(a);
+  else if (cols <= 512) layernorm_kernel<4><<<(unsigned)grid, 256, 0, st>>>(a);
+  else layernorm_kernel<8><<<(unsigned)grid, 256, 0, st>>>(a);
+  return post_launch("wf2cu_layernorm");
+}
+
 extern "C" int wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
                                      void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta) {
   WF2_REQUIRE_INIT();

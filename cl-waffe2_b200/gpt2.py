@@ -46,6 +46,9 @@ def init_weights(cfg: Dict[str, int], seed: int = 0, std: float = 0.02) -> Dict[
     return w
 
 
+FUSE_LAYERNORM = True
+
+
 def _bcast_last(vec1d: CUDATensor, like: CUDATensor) -> CUDATensor:
     """`(%transform b[i] -> [~ i])`: a (E) vector broadcast over every leading axis of `like`."""
     r = like.dims()
@@ -59,8 +62,15 @@ def _bcast_keep(stat: CUDATensor, like: CUDATensor) -> CUDATensor:
 
 
 def layer_norm(x: CUDATensor, g: CUDATensor, b: CUDATensor, eps: float = 1e-5) -> CUDATensor:
-    """LayerNorm-Revisit (examples/gpt-2/utils.lisp:114-127), node by node."""
+    """LayerNorm-Revisit (examples/gpt-2/utils.lisp:114-127): one kernel when FUSE_LAYERNORM (the ten-node chain
+    with the same per-element operations, wf2cu_layernorm), node by node otherwise."""
     shape = x.shape
+    if FUSE_LAYERNORM and x.is_contiguous() and not x.permuted_p() and shape[-1] % 4 == 0 and shape[-1] <= 1024:
+        out = make_tensor(shape)
+        rows = x.numel() // shape[-1]
+        _lib.check(_lib.load().wf2cu_layernorm(x.vec.ptr, x.lower().offset, g.vec.ptr, g.lower().offset, b.vec.ptr, b.lower().offset,
+                                               out.vec.ptr, out.lower().offset, rows, shape[-1], float(eps)))
+        return out
     u = make_tensor(shape[:-1] + [1])
     ops.mean(x, axis=-1, out=u)
     d = ops.sub(x, _bcast_keep(u, x))                       # x - u

@@ -112,6 +112,8 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 		   (m :pointer) (m-off :int64) (v :pointer) (v-off :int64) (n :int64)
 		   (lr-t :float) (lr-t-dev :pointer) (beta1 :float) (beta2 :float) (eps :float) (grad-scale :float)))
 (defwf2 embedding-gather ((ctx :pointer) (batch :int64) (seq :int64) (wte :pointer) (wpe :pointer) (dim :int64) (out :pointer)))
+(defwf2 layernorm ((x :pointer) (x-off :int64) (g :pointer) (g-off :int64) (b :pointer) (b-off :int64)
+		   (out :pointer) (out-off :int64) (rows :int64) (cols :int64) (eps :float)))
 ;; unfold / Conv2D / pooling (csrc/conv.cu)
 (defcstruct wf2cu-unfold-geom
   (n :int64) (c :int64) (h :int64) (w :int64)

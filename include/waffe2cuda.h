@@ -227,6 +227,13 @@ int  wf2cu_adam_step(void* param, int64_t p_off, const void* grad, int64_t g_off
                      void* m, int64_t m_off, void* v, int64_t v_off, int64_t n,
                      float lr_t, const void* lr_t_dev, float beta1, float beta2, float eps, float grad_scale);
 
+/* `LayerNorm-Revisit` (`examples/gpt-2/utils.lisp:114-127`) over the last axis of dense rows, the ten-node chain
+ * (!mean, !sub, !expt 2, !mean, !add eps, !sqrt, !div, !mul g, !add b) as one pass with the same per-element
+ * operations in the same order.  cols must be a multiple of 4, <= 1024, buffers 16-byte aligned; otherwise
+ * WF2CU_ERR_UNSUPPORTED (issue the nodes). */
+int  wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int64_t g_off, const void* b, int64_t b_off,
+                     void* out, int64_t out_off, int64_t rows, int64_t cols, float eps);
+
 /* `GPT2PositionalEmbedding` (`examples/gpt-2/utils.lisp:19-112`):
  * out[b,p,:] = wte[round(ctx[b,p]),:] + wpe[p,:] ; token ids are floats. */
 int  wf2cu_embedding_gather(const void* ctx, int64_t batch, int64_t seq, const void* wte,

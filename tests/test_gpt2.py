@@ -59,8 +59,52 @@ def test_oracle_fp32_tracks_fp64():
 
 # ------------------------------------------------------------------ device parity
 @pytest.mark.gpu
+@pytest.mark.parametrize("cols", [768, 64, 1024, 260, 12])
+def test_layernorm_one_kernel_equals_node_chain(gpu, cols):
+    """wf2cu_layernorm vs the ten-node LayerNorm-Revisit chain (examples/gpt-2/utils.lisp:114-127): the element-wise
+    operations are the same in the same order, only the two row sums use another (shuffle) tree -> a few ulp; both
+    within 1e-5 of fp64."""
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    rng = np.random.default_rng(cols)
+    X = (rng.normal(size=(3, 37, cols)) * 3 + 1.5).astype(np.float32)
+    G = rng.normal(size=(cols,)).astype(np.float32)
+    Bv = rng.normal(size=(cols,)).astype(np.float32)
+    x, gg, bb = gpu.from_numpy(X), gpu.from_numpy(G), gpu.from_numpy(Bv)
+    old = g.FUSE_LAYERNORM
+    try:
+        g.FUSE_LAYERNORM = True
+        fused = g.layer_norm(x, gg, bb).to_numpy()
+        g.FUSE_LAYERNORM = False
+        chain = g.layer_norm(x, gg, bb).to_numpy()
+    finally:
+        g.FUSE_LAYERNORM = old
+    truth = O.layer_norm(X.astype(np.float64), G.astype(np.float64), Bv.astype(np.float64))
+    scale = np.abs(truth).max()
+    assert np.abs(fused - truth).max() <= 1e-5 * scale
+    assert np.abs(chain - truth).max() <= 1e-5 * scale
+    np.testing.assert_allclose(fused, chain, rtol=0, atol=4e-6 * scale)
+
+
+@pytest.mark.gpu
+def test_layernorm_declines_unsupported_rows(gpu):
+    lib = gpu._lib.load()
+    x = gpu.make_tensor([4, 2050])
+    v = gpu.make_tensor([2050])
+    assert lib.wf2cu_layernorm(x.vec.ptr, 0, v.vec.ptr, 0, v.vec.ptr, 0, x.vec.ptr, 0, 4, 2050, 1e-5) == 3   # UNSUPPORTED
+
+
+@pytest.fixture(params=[True, False], ids=["fused-layernorm", "node-chain"])
+def ln_mode(request):
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    old = g.FUSE_LAYERNORM
+    g.FUSE_LAYERNORM = request.param
+    yield request.param
+    g.FUSE_LAYERNORM = old
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("lm_head", [False, True])
-def test_gpt2_forward_matches_oracle(gpu, lm_head):
+def test_gpt2_forward_matches_oracle(gpu, lm_head, ln_mode):
     g = importlib.import_module("cl-waffe2_b200.gpt2")
     W = _weights(CFG, seed=5)
     ctx = np.random.default_rng(4).integers(0, CFG["n_vocab"], size=(3, 24)).astype(np.float32)
