@@ -145,6 +145,33 @@ what `(!flexible bias)` becomes inside `step-linear` (`nn/regression.lisp:14-18`
 	(values (rewrite iseq-fw) (and iseq-bw (rewrite iseq-bw))))
       (values iseq-fw iseq-bw)))
 
+;; ---- LayerNorm over the last axis as ONE launch (csrc/softmax.cu `layernorm_kernel`).  The GPT-2 example
+;; spells it as eleven nodes (`LayerNorm-Revisit`, examples/gpt-2/utils.lisp:114-127: two !mean, !sub, !expt,
+;; !add eps, !sqrt, !div, !mul g, !add b); the kernel evaluates the same operations in the same order with
+;; correctly rounded div/sqrt, so the result agrees with the node chain to the last few ulp.  Inference only
+;; (the example never differentiates it): the backward is left to the node chain.
+(define-op (CUDALayerNormNode (self eps)
+	    :slots ((eps :initarg :eps :initform 1.0e-5 :reader eps-of))
+	    :where (X[~ n] G[n] B[n] Out[~ n] -> Out[~ n])
+	    :forward ((self x g b out)
+		      (let* ((cols (car (last (shape x))))
+			     (rows (/ (apply #'* (shape x)) cols)))
+			(layernorm (device-vec-ptr (tensor-vec x)) (tensor-initial-offset x)
+				   (device-vec-ptr (tensor-vec g)) (tensor-initial-offset g)
+				   (device-vec-ptr (tensor-vec b)) (tensor-initial-offset b)
+				   (device-vec-ptr (tensor-vec out)) (tensor-initial-offset out)
+				   rows cols (coerce (eps-of self) 'single-float))
+			out))
+	    :backward ((self dout)
+		       (declare (ignore dout))
+		       (error "CUDALayerNormNode: forward only; differentiate LayerNorm-Revisit instead")))
+  (setf (slot-value self 'eps) eps))
+
+(defun cuda-layer-norm (x g b &key (eps 1.0e-5))
+  "Drop-in for `LayerNorm-Revisit` on dense CUDATensors whose last axis is a multiple of 4 and <= 1024
+(the library answers UNSUPPORTED otherwise, which `defwf2` signals as `cuda-backend-error`)."
+  (call (CUDALayerNormNode eps) (->contiguous x) g b (make-input (shape x) nil :dtype (dtype x) :order (order x))))
+
 ;; ---- independent instructions on a side stream: (with-cuda-branch (1) <launches>) ... (branch-join 1)
 (defmacro with-cuda-branch ((b) &body body)
   "BODY's launches go to side stream B (1..3), ordered after everything issued so far; the main stream

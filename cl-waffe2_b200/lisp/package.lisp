@@ -21,7 +21,8 @@
    #:with-cuda
    #:cuda-sync
    #:cuda-comm-init
-   #:cuda-allreduce-gradients))
+   #:cuda-allreduce-gradients
+   #:cuda-layer-norm))
 (in-package :cl-waffe2/backends.cuda)
 
 (defparameter *cuda-available-p* nil
