@@ -597,7 +597,7 @@ using namespace wf2;
 extern "C" {
 
 int wf2cu_gemm_set_mode(int mode) {
-  WF2_CHECK(mode >= 0 && mode <= 5, "wf2cu_gemm_set_mode: mode %d not in 0..5", mode);
+  WF2_CHECK(mode >= 0 && mode <= 6, "wf2cu_gemm_set_mode: mode %d not in 0..6", mode);
   S().gemm_mode = mode;
   return 0;
 }
@@ -623,7 +623,7 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   // auto: 50 MFLOP..2.5 GFLOP -> fused tcgen05 kernel (38.5 vs 44.1 us on 1024^3, 89.5 vs 55.6 us on 1280^3; 14.6 vs 22.3 us on 1024x256x784, 8.6 vs 10.2 us on 1024x256x256;
   // below 50 MFLOP its ~5 us floor loses to the SIMT split-K kernel: 7.9 vs 6.9 us on 1024x10x256; gpurun_out/gemm_small5.log)
   // mode: 0 auto | 1 fp32 SIMT | 2 tcgen05 3xTF32 (planes + persistent kernel) | 3 tcgen05 1xTF32 | 4 tcgen05 fused small kernel
-  //       | 5 tcgen05 3xTF32 planes + the 256x256-tile persistent kernel
+  //       | 5 / 6 tcgen05 3xTF32 planes + the 256x256 / 256x192-tile persistent kernel
   if (mode == 0 || mode == 1) {
     // a long reduction with a small result (Conv2D's weight gradient: 16 x 100 over k = 82 944 at batch 1024) goes to
     // the K-sliced kernel whatever its flop count: on a tile-per-CTA kernel it is two tiles (604 us on 16 CTAs)

@@ -30,7 +30,9 @@ constexpr int STAGES = 2;
 constexpr int A_PLANE_BYTES = TM * TK * 4;   // 16 KiB
 constexpr int B_PLANE_BYTES = TN * TK * 4;   // 32 KiB
 constexpr int STAGE_BYTES = 2 * A_PLANE_BYTES + 2 * B_PLANE_BYTES;   // 96 KiB
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int EPI_LD = 36;                               // floats per staged output row (32 + 4: float4 rows stay conflict-free)
+constexpr int EPI_BYTES = 4 * 32 * EPI_LD * 4;           // one 32 x 32 block per epilogue warp
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + EPI_BYTES;
 constexpr int GEMM_THREADS = 192;
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -212,6 +214,36 @@ __device__ __forceinline__ void tc_epilogue32(const TcArgs& a, uint32_t (&v)[32]
   }
 }
 
+// 32 consecutive columns of row (row0 + lane), held one row per lane -> C.  A lane-per-row float4 store touches 32
+// lines with 16 bytes each (32 LSU wavefronts per instruction: ~16K for a 256x256 tile, which is what made the
+// K = 64 products of attention and the non-overlapped epilogue of the 256-row tiles slow).  The block is transposed
+// through shared memory so that every store instruction writes four whole 128-byte lines.
+__device__ __forceinline__ void tc_store32(const TcArgs& a, float* cbase, float* stage, const uint32_t (&v)[32], int row0,
+                                           int col0, int lane) {
+  if (col0 >= a.n) return;                                  // warp-uniform
+  if (a.c_vec && col0 + 32 <= a.n) {
+    float* mine = stage + lane * EPI_LD;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(mine + 4 * j) =
+          make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+    __syncwarp();
+    const int seg = lane & 7, sub = lane >> 3;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + sub;
+      const float4 x = *reinterpret_cast<const float4*>(stage + r * EPI_LD + 4 * seg);
+      if (row0 + r < a.m) *reinterpret_cast<float4*>(cbase + (int64_t)(row0 + r) * a.ldc + col0 + 4 * seg) = x;
+    }
+    __syncwarp();
+  } else if (row0 + lane < a.m) {
+    float* crow = cbase + (int64_t)(row0 + lane) * a.ldc;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (col0 + j < a.n) crow[col0 + j] = __uint_as_float(v[j]);
+  }
+}
+
 constexpr int kGroupM = 16;   // raster: 16 m-tiles x all n-tiles per group, m fastest (L2 reuse of B panels)
 
 __device__ __forceinline__ void tile_coords(int t, const TcArgs& a, int& b, int& mt, int& nt) {
@@ -317,34 +349,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
   } else {
     // ===================== epilogue: TMEM -> registers -> global =====================
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
+    float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256) + (warp - 2) * (32 * EPI_LD);
     int as = 0; uint32_t aph = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int b, mt, nt;
       tile_coords(t, a, b, mt, nt);
       mbar_wait(&acc_full[as], aph);
       tc_fence_after();
-      const int row = mt * TM + q * 32 + lane;
-      float* crow = a.C + (int64_t)b * a.sc + (int64_t)row * a.ldc;
+      float* cbase = a.C + (int64_t)b * a.sc;
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TN);
+      // two register buffers: the TMEM read of the next 32 columns is in flight while this one is stored
+      uint32_t v0[32], v1[32];
+      tc_ld32(tbase, v0);
 #pragma unroll 1
-      for (int c = 0; c < TN / 32; ++c) {
-        uint32_t v[32];
-        tc_ld32(tbase + c * 32, v);
+      for (int c = 0; c < TN / 32; c += 2) {
         tc_ld_wait();
-        const int col0 = nt * TN + c * 32;
-        if (col0 < a.n) tc_epilogue32(a, v, col0, lane);
-        if (row < a.m && col0 < a.n) {
-          if (a.c_vec && col0 + 32 <= a.n) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              *reinterpret_cast<float4*>(crow + col0 + 4 * j) =
-                  make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < a.n) crow[col0 + j] = __uint_as_float(v[j]);
-          }
-        }
+        tc_ld32(tbase + (c + 1) * 32, v1);
+        int col0 = nt * TN + c * 32;
+        if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
+        tc_store32(a, cbase, stage, v0, mt * TM + q * 32, col0, lane);
+        tc_ld_wait();
+        if (c + 2 < TN / 32) tc_ld32(tbase + (c + 2) * 32, v0);
+        col0 += 32;
+        if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
+        tc_store32(a, cbase, stage, v1, mt * TM + q * 32, col0, lane);
       }
       tc_fence_before();
       __syncwarp();
@@ -368,10 +396,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
 // 64 KiB per 1536 cycles = 42.7 B/clk.  k-block = 16 floats (64-byte rows, SWIZZLE_64B) so that
 // 3 stages x 64 KiB fit; the two 128x256 accumulators fill TMEM (512 columns), so the epilogue is
 // not overlapped with the next tile's MMAs (<= 2 % at K = 4096).
-constexpr int T2M = 256, T2N = 256, T2K = 16, T2_STAGES = 3;
-constexpr int T2_PLANE = 256 * T2K * 4;                 // 16 KiB: 256 rows x 64 B
-constexpr int T2_STAGE_BYTES = 4 * T2_PLANE;            // A_hi A_lo B_hi B_lo = 64 KiB
-constexpr int T2_SMEM_BYTES = T2_STAGES * T2_STAGE_BYTES + 1024 + 256;
+//
+// NB = 192 is the same kernel with 256 x 192 tiles (48.6 B/clk): for N = 768 (GPT-2's projections) 8192 rows make
+// 128 tiles instead of 96 on 148 SMs.
+constexpr int T2M = 256, T2K = 16;
+constexpr int T2_PLANE = 256 * T2K * 4;                 // A plane, 16 KiB: 256 rows x 64 B
+__host__ __device__ constexpr int t2_bplane(int nb) { return nb * T2K * 4; }
+__host__ __device__ constexpr int t2_stage_bytes(int nb) { return 2 * T2_PLANE + 2 * t2_bplane(nb); }   // A_hi A_lo B_hi B_lo
+__host__ __device__ constexpr int t2_smem_bytes(int nb, int nst) { return nst * t2_stage_bytes(nb) + 1024 + 256 + EPI_BYTES; }
+__host__ __device__ constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24); }
 
 // K-major SWIZZLE_64B descriptor: SBO = 8 rows x 64 B = 512, layout_type = 4
 __device__ __forceinline__ uint64_t make_desc_sw64(uint32_t smem_addr) {
@@ -384,10 +417,13 @@ __device__ __forceinline__ uint64_t make_desc_sw64(uint32_t smem_addr) {
   return d;
 }
 
+template <int NB, int NST>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
                   const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
                   const __grid_constant__ TcArgs a) {
+  constexpr int T2N = NB, T2_STAGES = NST, B_PLANE = t2_bplane(NB), T2_STAGE_BYTES = t2_stage_bytes(NB);
+  constexpr uint32_t kIdesc = idesc_tf32(NB);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_STAGES * T2_STAGE_BYTES);
@@ -417,7 +453,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
 
   if (warp == 0) {
     if (lane == 0) {
-      const uint32_t tx_bytes = a.passes == 3 ? T2_STAGE_BYTES : 2 * T2_PLANE;
+      const uint32_t tx_bytes = a.passes == 3 ? T2_STAGE_BYTES : T2_PLANE + B_PLANE;
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int b, mt, nt;
@@ -431,7 +467,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           tma_load_3d(&map_bh, &full[s], st + 2 * T2_PLANE, kb * T2K, nt * T2N, bb);
           if (a.passes == 3) {
             tma_load_3d(&map_al, &full[s], st + T2_PLANE, kb * T2K, mt * T2M, ba);
-            tma_load_3d(&map_bl, &full[s], st + 3 * T2_PLANE, kb * T2K, nt * T2N, bb);
+            tma_load_3d(&map_bl, &full[s], st + 2 * T2_PLANE + B_PLANE, kb * T2K, nt * T2N, bb);
           }
           if (++s == T2_STAGES) { s = 0; ph ^= 1; }
         }
@@ -448,7 +484,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           mbar_wait(&full[s], ph);
           tc_fence_after();
           const uint32_t st = smem_u32(smem + s * T2_STAGE_BYTES);
-          const uint64_t dbh = make_desc_sw64(st + 2 * T2_PLANE), dbl = make_desc_sw64(st + 3 * T2_PLANE);
+          const uint64_t dbh = make_desc_sw64(st + 2 * T2_PLANE), dbl = make_desc_sw64(st + 2 * T2_PLANE + B_PLANE);
 #pragma unroll
           for (int h = 0; h < 2; ++h) {         // rows [0,128) and [128,256) of the A tile: + 128 rows x 64 B
             const uint64_t dah = make_desc_sw64(st + h * (128 * 64)), dal = make_desc_sw64(st + T2_PLANE + h * (128 * 64));
@@ -457,11 +493,11 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
             for (int k = 0; k < T2K / UK; ++k) {
               const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
               if (a.passes == 3) {
-                tc_mma_tf32(d, dal + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
-                tc_mma_tf32(d, dah + adv, dbl + adv, kIdescTf32, 1);
-                tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, 1);
+                tc_mma_tf32(d, dal + adv, dbh + adv, kIdesc, (kb | k) != 0);
+                tc_mma_tf32(d, dah + adv, dbl + adv, kIdesc, 1);
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdesc, 1);
               } else {
-                tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdesc, (kb | k) != 0);
               }
             }
           }
@@ -474,36 +510,31 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
     }
   } else {
     const int q = warp & 3;
+    float* stage = reinterpret_cast<float*>(smem + T2_STAGES * T2_STAGE_BYTES + 256) + (warp - 2) * (32 * EPI_LD);
     uint32_t aph = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int b, mt, nt;
       tile_coords(t, a, b, mt, nt);
       mbar_wait(acc_full, aph);
       tc_fence_after();
+      float* cbase = a.C + (int64_t)b * a.sc;
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
-        const int row = mt * T2M + h * 128 + q * 32 + lane;
-        float* crow = a.C + (int64_t)b * a.sc + (int64_t)row * a.ldc;
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256);
+        uint32_t v0[32], v1[32];
+        tc_ld32(tbase, v0);
 #pragma unroll 1
-        for (int c = 0; c < T2N / 32; ++c) {
-          uint32_t v[32];
-          tc_ld32(tbase + c * 32, v);
+        for (int c = 0; c < T2N / 32; c += 2) {
           tc_ld_wait();
-          const int col0 = nt * T2N + c * 32;
-          if (col0 < a.n) tc_epilogue32(a, v, col0, lane);
-          if (row < a.m && col0 < a.n) {
-            if (a.c_vec && col0 + 32 <= a.n) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j)
-                *reinterpret_cast<float4*>(crow + col0 + 4 * j) =
-                    make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (col0 + j < a.n) crow[col0 + j] = __uint_as_float(v[j]);
-            }
-          }
+          tc_ld32(tbase + (c + 1) * 32, v1);
+          int col0 = nt * T2N + c * 32;
+          if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
+          tc_store32(a, cbase, stage, v0, mt * T2M + h * 128 + q * 32, col0, lane);
+          tc_ld_wait();
+          if (c + 2 < T2N / 32) tc_ld32(tbase + (c + 2) * 32, v0);
+          col0 += 32;
+          if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
+          tc_store32(a, cbase, stage, v1, mt * T2M + h * 128 + q * 32, col0, lane);
         }
       }
       tc_fence_before();
@@ -856,10 +887,10 @@ static int make_map(CUtensorMap* map, float* base, int rows, int Kp, int nbatch,
   return 0;
 }
 
-static int make_map256(CUtensorMap* map, float* base, int rows, int Kp, int nbatch) {
+static int make_map256(CUtensorMap* map, float* base, int rows, int Kp, int nbatch, int box_rows) {
   cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)rows, (cuuint64_t)nbatch};
   cuuint64_t strides[2] = {(cuuint64_t)Kp * 4, (cuuint64_t)rows * Kp * 4};
-  cuuint32_t box[3] = {(cuuint32_t)T2K, 256, 1};
+  cuuint32_t box[3] = {(cuuint32_t)T2K, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                         CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -881,6 +912,22 @@ static int launch_split(const float* src, float* hi, float* lo, int64_t ld, int6
   }
   const int rc = post_launch("wf2cu_gemm(split)");
   return rc ? -rc : 0;
+}
+
+// auto rule for the 256-row tile kernels (0 = stay on the 128x256 kernel): they cannot overlap the epilogue with the
+// next tile, so they want a long K, and they have fewer tiles, so they want enough of them.
+// Cost model fitted on B200 (scripts/gemm_t256.py, gpurun_out/gemm_t256.log), in units of one 128x256 MMA column of
+// depth 1: waves x (MMA time of a tile / its efficiency + the exposed epilogue).  The 128x256 kernel is L2-port bound
+// (x1.3) but hides its epilogue; 256x256 runs at the tensor rate; 256x192 pays x1.12 for its smaller B slices.
+//   8192x768x3072: 286 / 242 / 212 us (128x256 / 256x256 / 256x192)   8192x768x768: 82 / 78 / 68
+//   8192x1536x1536: 207 / 230 / 196     8192x2304x768: 139 / 136 / 156     2048^3: 103 / 154 / 131     4096^3: 679 / 577 / 680
+static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t tiles192, int sms) {
+  auto waves = [&](int64_t t) { return (double)((t + sms - 1) / sms); };
+  const double c128 = waves(tiles128) * 1.30 * (double)kp;
+  const double c256 = waves(tiles256) * (2.00 * (double)kp + 450.0);
+  const double c192 = waves(tiles192) * (1.68 * (double)kp + 337.0);
+  if (c128 <= c256 * 1.02 && c128 <= c192 * 1.02) return 0;
+  return c256 <= c192 ? 256 : 192;
 }
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
@@ -912,7 +959,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     g_attr_set = true;
   }
   const int Kp = (int)((k + TK - 1) / TK) * TK;
-  const int passes = mode == 3 ? 1 : 3;      // mode 5 = 3xTF32 on the 256x256-tile kernel
+  const int passes = mode == 3 ? 1 : 3;      // modes 5 / 6 = 3xTF32 on the 256x256 / 256x192-tile kernel
   const int a_nb = (sa == 0 || batch == 1) ? 1 : (int)batch;
   const int b_nb = (sb == 0 || batch == 1) ? 1 : (int)batch;
   auto plane = [&](int64_t rows, int nb) { return (((size_t)nb * rows * Kp * 4) + 255) & ~(size_t)255; };
@@ -931,26 +978,32 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   if (rc) return rc;
 
   CUtensorMap mah, mal, mbh, mbl;
-  // auto: the 256x256 kernel cannot overlap its epilogue with the next tile (its two accumulators fill TMEM), so it
-  // wants a long K, and it has half as many tiles, so it wants enough of them: measured on B200 (scripts/gemm_t256.py)
-  // 4096^3 234 vs 203 TFLOP/s, 8192^3 275 vs 250, 8192x768x3072 151 vs 133; but 2048^3 109 vs 163 (64 tiles) and
-  // 8192x2304x768 185 vs 193 (short K).  Results are bit-identical to the 128x256 kernel (same k order per output).
-  const int64_t tiles256 = ((m + T2M - 1) / T2M) * ((n + T2N - 1) / T2N) * batch;
-  if (mode == 5 || (mode == 0 && g_t256_auto && k >= 2048 && tiles256 >= 96)) {
-    // 256 x 256 tiles: two M = 128 MMAs share every B slice (42.7 instead of 62.5 B/clk of L2 -> SM traffic per SM)
+  // 128x256, 256x256 or 256x192 tiles: results are bit-identical (same k order per output), pick_tile256 chooses
+  const int64_t tiles_m256 = (m + T2M - 1) / T2M;
+  const int64_t tiles256 = tiles_m256 * ((n + 255) / 256) * batch;
+  const int64_t tiles192 = tiles_m256 * ((n + 191) / 192) * batch;
+  int nb = 0;                                              // 0: the 128x256 kernel below
+  if (mode == 5) nb = 256;
+  else if (mode == 6) nb = 192;
+  else if (mode == 0 && g_t256_auto)
+    nb = pick_tile256(Kp, ((m + TM - 1) / TM) * ((n + TN - 1) / TN) * batch, tiles256, tiles192, S().sm_count);
+  if (nb) {
+    // 256-row tiles: two M = 128 MMAs share every B slice (42.7 instead of 62.5 B/clk of L2 -> SM traffic per SM)
     static bool attr256 = false;
     if (!attr256) {
-      cudaError_t e = cudaFuncSetAttribute(gemm_tc256_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES);
+      cudaError_t e = cudaFuncSetAttribute(gemm_tc256_kernel<256, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, t2_smem_bytes(256, 3));
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(gemm_tc256_kernel<192, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, t2_smem_bytes(192, 3));
       if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_tc256_kernel)", __FILE__, __LINE__);
       attr256 = true;
     }
-    if ((rc = make_map256(&mah, ah, (int)m, Kp, a_nb))) return rc;
-    if ((rc = make_map256(&mal, al, (int)m, Kp, a_nb))) return rc;
-    if ((rc = make_map256(&mbh, bh, (int)n, Kp, b_nb))) return rc;
-    if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb))) return rc;
+    if ((rc = make_map256(&mah, ah, (int)m, Kp, a_nb, 256))) return rc;
+    if ((rc = make_map256(&mal, al, (int)m, Kp, a_nb, 256))) return rc;
+    if ((rc = make_map256(&mbh, bh, (int)n, Kp, b_nb, nb))) return rc;
+    if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb, nb))) return rc;
     TcArgs t;
     t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = Kp / T2K;
-    t.tiles_m = (int)((m + T2M - 1) / T2M); t.tiles_n = (int)((n + T2N - 1) / T2N); t.batch = (int)batch;
+    t.tiles_m = (int)tiles_m256; t.tiles_n = (int)((n + nb - 1) / nb); t.batch = (int)batch;
     t.passes = passes;
     t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
     t.a_bcast = a_nb == 1 ? 1 : 0;
@@ -958,8 +1011,9 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.bias = bias; t.act = act;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     const int grid = (int)(total < S().sm_count ? total : S().sm_count);
-    gemm_tc256_kernel<<<grid, GEMM_THREADS, T2_SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, t);
-    rc = post_launch("wf2cu_gemm(tcgen05 256x256)");
+    if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, GEMM_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, t);
+    else           gemm_tc256_kernel<192, 3><<<grid, GEMM_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, t);
+    rc = post_launch(nb == 256 ? "wf2cu_gemm(tcgen05 256x256)" : "wf2cu_gemm(tcgen05 256x192)");
     return rc ? -rc : 1;
   }
   if ((rc = make_map(&mah, ah, (int)m, Kp, a_nb, TM))) return rc;

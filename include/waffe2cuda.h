@@ -194,7 +194,7 @@ int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
                 int64_t batch, int64_t stride_a, int64_t stride_b, int64_t stride_c);
 /* 0 = auto, 1 = force fp32 SIMT path, 2 = force tcgen05 3xTF32 (planes + persistent 128x256-tile kernel),
  * 3 = tcgen05 1xTF32 (not parity-grade), 4 = force the one-launch fused tcgen05 kernel (small problems),
- * 5 = force tcgen05 3xTF32 on the persistent 256x256-tile kernel.  Forced modes return WF2CU_ERR_UNSUPPORTED
+ * 5 / 6 = force tcgen05 3xTF32 on the persistent 256x256 / 256x192-tile kernel.  Forced modes return WF2CU_ERR_UNSUPPORTED
  * for shapes their kernel does not take. */
 int  wf2cu_gemm_set_mode(int mode);
 /* MatmulNode with the node that follows it folded into the epilogue (what the backend's

@@ -520,9 +520,9 @@ def test_errors_are_loud(gpu):
 
 @pytest.mark.parametrize("ta,tb,m,n,k", [(0, 0, 512, 512, 256), (1, 0, 300, 700, 100), (0, 1, 1000, 517, 333), (1, 1, 257, 255, 48), (0, 0, 64, 64, 32)])
 def test_matmul_tcgen05_256_tile_kernel(gpu, ta, tb, m, n, k):
-    """mode 5: planes + the persistent 256x256-tile tcgen05 kernel (two M = 128 MMAs share each B slice, SWIZZLE_64B
-    k-blocks of 16) on ragged and transposed shapes; bar 1e-4, and bit-identical to the 128x256-tile kernel (mode 2):
-    both add the same products in the same k order."""
+    """modes 5 / 6: planes + the persistent 256x256 / 256x192-tile tcgen05 kernel (two M = 128 MMAs share each B slice,
+    SWIZZLE_64B k-blocks of 16) on ragged and transposed shapes; bar 1e-4, and bit-identical to the 128x256-tile kernel
+    (mode 2): all three add the same products in the same k order."""
     lib = gpu._lib.load()
     rng = np.random.default_rng(m + 3 * n + 5 * k)
     A = rng.uniform(-1, 1, size=((k, m) if ta else (m, k))).astype(np.float32)
@@ -531,21 +531,23 @@ def test_matmul_tcgen05_256_tile_kernel(gpu, ta, tb, m, n, k):
     truth = (A.T if ta else A).astype(np.float64) @ (B.T if tb else B).astype(np.float64)
     outs = {}
     try:
-        for mode in (5, 2):
+        for mode in (5, 6, 2):
             gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
             outs[mode] = gpu.ops.matmul(gpu.ops.t(ga) if ta else ga, gpu.ops.t(gb) if tb else gb).to_numpy()
     finally:
         gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
     assert np.abs(outs[5] - truth).max() <= 2e-5 * np.abs(truth).max()
     np.testing.assert_array_equal(outs[5], outs[2])
+    np.testing.assert_array_equal(outs[6], outs[2])
 
 
-def test_matmul_tcgen05_256_tile_kernel_batched(gpu):
+@pytest.mark.parametrize("mode", [5, 6])
+def test_matmul_tcgen05_256_tile_kernel_batched(gpu, mode):
     lib = gpu._lib.load()
     rng = np.random.default_rng(12)
     A = rng.uniform(-1, 1, size=(3, 300, 80)).astype(np.float32)
     W = rng.uniform(-1, 1, size=(520, 80)).astype(np.float32)        # shared by the batch, transposed
-    gpu._lib.check(lib.wf2cu_gemm_set_mode(5))
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
     try:
         r = gpu.ops.matmul(gpu.from_numpy(A), gpu.ops.t(gpu.from_numpy(W))).to_numpy()
     finally:
@@ -553,7 +555,7 @@ def test_matmul_tcgen05_256_tile_kernel_batched(gpu):
     np.testing.assert_allclose(r, A.astype(np.float64) @ W.T.astype(np.float64), rtol=0, atol=2e-4)
 
 
-@pytest.mark.parametrize("mode", [0, 2, 5])
+@pytest.mark.parametrize("mode", [0, 2, 5, 6])
 def test_matmul_tcgen05_persistent_kernels_fold_bias_and_relu(gpu, mode):
     """wf2cu_gemm_ex on the planes path: `+ bias` and `!relu` ride in the persistent kernels' TMEM -> global epilogue
     (the relu-backward mask stays a separate pass); equal to the unfused nodes bit for bit."""
