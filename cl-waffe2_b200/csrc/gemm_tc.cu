@@ -650,6 +650,11 @@ struct FTile {
       reg[it] = v;
     }
   }
+  // interior tile, aligned operands, whole k-blocks (uniform over the CTA): one 128-bit load per chunk, no tests
+  __device__ __forceinline__ void load_fast(float4 (&reg)[ROWS / 32], int blk) const {
+#pragma unroll
+    for (int it = 0; it < ROWS / 32; ++it) reg[it] = *reinterpret_cast<const float4*>(p[it] + blk * step);
+  }
   // hi = x with the 13 low mantissa bits cleared (a TF32 number), lo = x - hi (exact).  lo is stored as is: the
   // tensor core reads 19 bits of it, an error of 2^-10 |lo| <= 2^-20 |x|, the same order as the split itself.
   __device__ __forceinline__ static void split(float x, float& hi, float& lo) {
@@ -687,6 +692,61 @@ __device__ __forceinline__ float f_epilogue(const FusedGemmArgs& g, float v, int
   return v;
 }
 
+// Main loop of the fused kernel.  A ring of GB = 4 k-blocks lives in registers: as soon as a block has been converted
+// and stored, the load of the block GB steps ahead is issued into the same registers, so three blocks of global
+// latency are always in flight (with the loads of a whole group issued together and then drained, GPT-2's P.V —
+// K = 1024 per CTA — spent its time in long-scoreboard stalls: 260 us for 402 MB, profiles/r01d_attention_ncu.md).
+template <bool FAST>
+__device__ __forceinline__ void fused_mainloop(const FTile<FM>& ta_, const FTile<FN>& tb_, uint8_t* smem, uint64_t* freed,
+                                               uint32_t tmem_base, int nkb, int kbeg, int kend, uint32_t& ph0, uint32_t& ph1) {
+  constexpr int GB = 4;
+  float4 ra[GB][FM / 32], rb[GB][FN / 32];
+#pragma unroll
+  for (int u = 0; u < GB; ++u)
+    if (u < nkb) {
+      if (FAST) { ta_.load_fast(ra[u], u); tb_.load_fast(rb[u], u); }
+      else { const int krem = kend - (kbeg + u * TK); ta_.load(ra[u], u, krem); tb_.load(rb[u], u, krem); }
+    }
+#pragma unroll 1
+  for (int kg = 0; kg < nkb; kg += GB) {
+#pragma unroll
+    for (int u = 0; u < GB; ++u) {
+      const int kb = kg + u;
+      if (kb < nkb) {                                   // uniform across the CTA
+        const int s = kb & 1;
+        uint8_t* st = smem + s * F_STAGE;
+        if (kb >= F_STAGES) {                           // the MMAs of block kb-2 must be done reading this stage
+          if (s == 0) { mbar_wait(&freed[0], ph0); ph0 ^= 1; } else { mbar_wait(&freed[1], ph1); ph1 ^= 1; }
+          tc_fence_after();
+        }
+        ta_.store(ra[u], st, st + F_A_PLANE);
+        tb_.store(rb[u], st + 2 * F_A_PLANE, st + 2 * F_A_PLANE + F_B_PLANE);
+        if (kb + GB < nkb) {                            // refill this ring slot
+          if (FAST) { ta_.load_fast(ra[u], kb + GB); tb_.load_fast(rb[u], kb + GB); }
+          else { const int krem = kend - (kbeg + (kb + GB) * TK); ta_.load(ra[u], kb + GB, krem); tb_.load(rb[u], kb + GB, krem); }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          tc_fence_after();
+          const uint32_t sa = smem_u32(st);
+          const uint64_t dah = make_desc_sw128(sa), dal = make_desc_sw128(sa + F_A_PLANE);
+          const uint64_t dbh = make_desc_sw128(sa + 2 * F_A_PLANE), dbl = make_desc_sw128(sa + 2 * F_A_PLANE + F_B_PLANE);
+#pragma unroll
+          for (int k = 0; k < TK / UK; ++k) {
+            const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
+            tc_mma_tf32(tmem_base, dal + adv, dbh + adv, kIdescTf32F, (kb | k) != 0);
+            tc_mma_tf32(tmem_base, dah + adv, dbl + adv, kIdescTf32F, 1);
+            tc_mma_tf32(tmem_base, dah + adv, dbh + adv, kIdescTf32F, 1);
+          }
+          tc_commit(&freed[s]);
+        }
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_constant__ FusedGemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -714,55 +774,15 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_cons
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // K blocks are taken in groups of 4: the global loads of a group are issued before its first conversion, so
-  // the global-memory latency is paid once per 128 k (with the usual K slice of <= 128 per CTA: once).
-  constexpr int GB = 4;
+  // interior tiles of aligned operands (every tile of GPT-2's P.V, most of the MLP's) skip the per-chunk tests
   FTile<FM> ta_;
   FTile<FN> tb_;
   ta_.init(g.A + bz * g.sa, g.lda, a_kmajor, g.a_vec != 0, m0, g.m, kbeg);
   tb_.init(g.B + bz * g.sb, g.ldb, b_kmajor, g.b_vec != 0, n0, g.n, kbeg);
   uint32_t ph0 = 0, ph1 = 0;                            // parity of freed[0] / freed[1]
-  for (int kg = 0; kg < nkb; kg += GB) {
-    float4 ra[GB][FM / 32], rb[GB][FN / 32];
-#pragma unroll
-    for (int u = 0; u < GB; ++u)
-      if (kg + u < nkb) {
-        const int krem = kend - (kbeg + (kg + u) * TK);
-        ta_.load(ra[u], kg + u, krem);
-        tb_.load(rb[u], kg + u, krem);
-      }
-#pragma unroll
-    for (int u = 0; u < GB; ++u) {
-      const int kb = kg + u;
-      if (kb < nkb) {                                   // uniform across the CTA
-        const int s = kb & 1;
-        uint8_t* st = smem + s * F_STAGE;
-        if (kb >= F_STAGES) {                           // the MMAs of block kb-2 must be done reading this stage
-          if (s == 0) { mbar_wait(&freed[0], ph0); ph0 ^= 1; } else { mbar_wait(&freed[1], ph1); ph1 ^= 1; }
-          tc_fence_after();
-        }
-        ta_.store(ra[u], st, st + F_A_PLANE);
-        tb_.store(rb[u], st + 2 * F_A_PLANE, st + 2 * F_A_PLANE + F_B_PLANE);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
-        tc_fence_before();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          tc_fence_after();
-          const uint32_t sa = smem_u32(st);
-          const uint64_t dah = make_desc_sw128(sa), dal = make_desc_sw128(sa + F_A_PLANE);
-          const uint64_t dbh = make_desc_sw128(sa + 2 * F_A_PLANE), dbl = make_desc_sw128(sa + 2 * F_A_PLANE + F_B_PLANE);
-#pragma unroll
-          for (int k = 0; k < TK / UK; ++k) {
-            const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
-            tc_mma_tf32(tmem_base, dal + adv, dbh + adv, kIdescTf32F, (kb | k) != 0);
-            tc_mma_tf32(tmem_base, dah + adv, dbl + adv, kIdescTf32F, 1);
-            tc_mma_tf32(tmem_base, dah + adv, dbh + adv, kIdescTf32F, 1);
-          }
-          tc_commit(&freed[s]);
-        }
-      }
-    }
-  }
+  const bool fast = g.a_vec && g.b_vec && m0 + FM <= g.m && n0 + FN <= g.n && nkb > 0 && ((kend - kbeg) % TK) == 0;
+  if (fast) fused_mainloop<true>(ta_, tb_, smem, freed, tmem_base, nkb, kbeg, kend, ph0, ph1);
+  else      fused_mainloop<false>(ta_, tb_, smem, freed, tmem_base, nkb, kbeg, kend, ph0, ph1);
   // ---- all MMAs retired?  (the last commit covers every earlier one)
   if (nkb > 0) {
     // commits retire in order, so waiting for the last block's commit covers every MMA; the other
