@@ -31,8 +31,11 @@ constexpr int A_PLANE_BYTES = TM * TK * 4;   // 16 KiB
 constexpr int B_PLANE_BYTES = TN * TK * 4;   // 32 KiB
 constexpr int STAGE_BYTES = 2 * A_PLANE_BYTES + 2 * B_PLANE_BYTES;   // 96 KiB
 constexpr int EPI_LD = 36;                               // floats per staged output row (32 + 4: float4 rows stay conflict-free)
-constexpr int EPI_BYTES = 4 * 32 * EPI_LD * 4;           // one 32 x 32 block per epilogue warp
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + EPI_BYTES;
+constexpr int EPI_SLOT = 8192;                           // per epilogue warp, 1024-byte aligned: two 4 KiB 32 x 32 blocks in the
+                                                         // SWIZZLE_128B layout of the bulk tensor store (or one padded block, 4608 B)
+constexpr int EPI_BYTES = 4 * EPI_SLOT;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + EPI_BYTES + 256 /*barriers*/;
+static_assert(32 * EPI_LD * 4 <= EPI_SLOT && SMEM_BYTES <= 232448, "shared-memory budget");
 constexpr int GEMM_THREADS = 192;
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -67,6 +70,13 @@ __device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint64_t* ba
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
       ::"r"(smem_u32(dst)), "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
+}
+// one box of shared memory -> C through the tensor map (the bulk engine writes whole lines and clips at the edges)
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"((uint64_t)map), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -196,6 +206,7 @@ struct TcArgs {
   int a_bcast, b_bcast;  // operand shared by every batch index (batch stride 0): one plane set
   const float* bias;     // != NULL: C[r, c] = acc + bias[c]  (LinearLayer's bias add folded into the epilogue)
   int act;               // 1: then C = C * (C > 0 ? 1 : 0)  (`!relu`)
+  int c_tma;             // C goes out through map_c (bulk tensor stores) instead of per-lane global stores
 };
 
 // epilogue of the persistent kernels: 32 consecutive columns of one row per lane; same arithmetic as the separate
@@ -244,6 +255,28 @@ __device__ __forceinline__ void tc_store32(const TcArgs& a, float* cbase, float*
   }
 }
 
+// The same block through the bulk-copy engine: each lane writes its row into a 4 KiB staging block in the SWIZZLE_128B
+// layout (16-byte chunk j of row r at chunk j ^ (r & 7): conflict-free for the quarter-warps of a 128-bit store), one
+// lane hands the block to cp.async.bulk.tensor, which writes whole lines and clips rows >= m / columns >= n.  Per block
+// the warp issues 8 shared stores instead of 8 shared stores + 8 shared loads + 8 global stores, and never waits for
+// the global stores: two staging blocks alternate, a block is reused once the engine has read it (wait_group.read 1).
+__device__ __forceinline__ void tc_store32_tma(const TcArgs& a, const CUtensorMap* map_c, uint8_t* slot, uint32_t& which,
+                                               const uint32_t (&v)[32], int row0, int col0, int b, int lane) {
+  if (col0 >= a.n || row0 >= a.m) return;                   // warp-uniform
+  uint8_t* blk = slot + which * 4096;
+  which ^= 1;
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+  __syncwarp();
+  uint8_t* mine = blk + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    *reinterpret_cast<float4*>(mine + ((j ^ (lane & 7)) << 4)) =
+        make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  if (lane == 0) tma_store_3d(map_c, blk, col0, row0, b);
+}
+
 constexpr int kGroupM = 16;   // raster: 16 m-tiles x all n-tiles per group, m fastest (L2 reuse of B panels)
 
 __device__ __forceinline__ void tile_coords(int t, const TcArgs& a, int& b, int& mt, int& nt) {
@@ -262,11 +295,11 @@ __device__ __forceinline__ void tile_coords(int t, const TcArgs& a, int& b, int&
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
                const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
-               const __grid_constant__ TcArgs a) {
+               const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte aligned tiles
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + EPI_BYTES);
   uint64_t* full = bars;                    // [STAGES]  TMA -> MMA
   uint64_t* empty = bars + STAGES;          // [STAGES]  MMA -> TMA
   uint64_t* acc_full = bars + 2 * STAGES;   // [2]       MMA -> epilogue
@@ -349,7 +382,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
   } else {
     // ===================== epilogue: TMEM -> registers -> global =====================
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
-    float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256) + (warp - 2) * (32 * EPI_LD);
+    uint8_t* slot = smem + STAGES * STAGE_BYTES + (warp - 2) * EPI_SLOT;
+    float* stage = reinterpret_cast<float*>(slot);
+    uint32_t which = 0;
     int as = 0; uint32_t aph = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int b, mt, nt;
@@ -367,18 +402,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
         tc_ld32(tbase + (c + 1) * 32, v1);
         int col0 = nt * TN + c * 32;
         if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
-        tc_store32(a, cbase, stage, v0, mt * TM + q * 32, col0, lane);
+        if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, mt * TM + q * 32, col0, b, lane);
+        else tc_store32(a, cbase, stage, v0, mt * TM + q * 32, col0, lane);
         tc_ld_wait();
         if (c + 2 < TN / 32) tc_ld32(tbase + (c + 2) * 32, v0);
         col0 += 32;
         if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
-        tc_store32(a, cbase, stage, v1, mt * TM + q * 32, col0, lane);
+        if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, mt * TM + q * 32, col0, b, lane);
+        else tc_store32(a, cbase, stage, v1, mt * TM + q * 32, col0, lane);
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);
       if (++as == 2) { as = 0; aph ^= 1; }
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // every bulk store of this warp has landed
   }
 
   tc_fence_before();
@@ -403,7 +441,8 @@ constexpr int T2M = 256, T2K = 16;
 constexpr int T2_PLANE = 256 * T2K * 4;                 // A plane, 16 KiB: 256 rows x 64 B
 __host__ __device__ constexpr int t2_bplane(int nb) { return nb * T2K * 4; }
 __host__ __device__ constexpr int t2_stage_bytes(int nb) { return 2 * T2_PLANE + 2 * t2_bplane(nb); }   // A_hi A_lo B_hi B_lo
-__host__ __device__ constexpr int t2_smem_bytes(int nb, int nst) { return nst * t2_stage_bytes(nb) + 1024 + 256 + EPI_BYTES; }
+__host__ __device__ constexpr int t2_smem_bytes(int nb, int nst) { return nst * t2_stage_bytes(nb) + 1024 + EPI_BYTES + 256; }
+static_assert(t2_smem_bytes(256, 3) <= 232448 && t2_stage_bytes(192) % 1024 == 0 && t2_stage_bytes(256) % 1024 == 0, "shared-memory budget");
 __host__ __device__ constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24); }
 
 // K-major SWIZZLE_64B descriptor: SBO = 8 rows x 64 B = 512, layout_type = 4
@@ -421,12 +460,12 @@ template <int NB, int NST>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
                   const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
-                  const __grid_constant__ TcArgs a) {
+                  const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
   constexpr int T2N = NB, T2_STAGES = NST, B_PLANE = t2_bplane(NB), T2_STAGE_BYTES = t2_stage_bytes(NB);
   constexpr uint32_t kIdesc = idesc_tf32(NB);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_STAGES * T2_STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_STAGES * T2_STAGE_BYTES + EPI_BYTES);
   uint64_t* full = bars;                       // [T2_STAGES]
   uint64_t* empty = bars + T2_STAGES;          // [T2_STAGES]
   uint64_t* acc_full = bars + 2 * T2_STAGES;   // [1]
@@ -510,7 +549,9 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
     }
   } else {
     const int q = warp & 3;
-    float* stage = reinterpret_cast<float*>(smem + T2_STAGES * T2_STAGE_BYTES + 256) + (warp - 2) * (32 * EPI_LD);
+    uint8_t* slot = smem + T2_STAGES * T2_STAGE_BYTES + (warp - 2) * EPI_SLOT;
+    float* stage = reinterpret_cast<float*>(slot);
+    uint32_t which = 0;
     uint32_t aph = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int b, mt, nt;
@@ -529,12 +570,14 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           tc_ld32(tbase + (c + 1) * 32, v1);
           int col0 = nt * T2N + c * 32;
           if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
-          tc_store32(a, cbase, stage, v0, mt * T2M + h * 128 + q * 32, col0, lane);
+          if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, mt * T2M + h * 128 + q * 32, col0, b, lane);
+          else tc_store32(a, cbase, stage, v0, mt * T2M + h * 128 + q * 32, col0, lane);
           tc_ld_wait();
           if (c + 2 < T2N / 32) tc_ld32(tbase + (c + 2) * 32, v0);
           col0 += 32;
           if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
-          tc_store32(a, cbase, stage, v1, mt * T2M + h * 128 + q * 32, col0, lane);
+          if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, mt * T2M + h * 128 + q * 32, col0, b, lane);
+          else tc_store32(a, cbase, stage, v1, mt * T2M + h * 128 + q * 32, col0, lane);
         }
       }
       tc_fence_before();
@@ -542,6 +585,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       if (lane == 0) mbar_arrive(acc_empty);
       aph ^= 1;
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
 
   tc_fence_before();
@@ -585,6 +629,7 @@ struct FusedGemmArgs {
   int a_vec, b_vec, c_vec;   // operand / result rows are 16-byte aligned: 128-bit global accesses
   int ksplit, kchunk;        // cluster size along z, K per slice (multiple of 32)
   const float* bias; const float* mask; int64_t ldmask; int act;
+  int a_hint;                // cache hint for the streamed K-major A rows (0 none, 1 L2::256B, 2 + L1::no_allocate, 3 L1::no_allocate)
 };
 
 // byte offset of element (r, k) inside a K-major SWIZZLE_128B plane (128-byte rows, 16-byte chunks XOR r%8)
@@ -651,9 +696,19 @@ struct FTile {
     }
   }
   // interior tile, aligned operands, whole k-blocks (uniform over the CTA): one 128-bit load per chunk, no tests
-  __device__ __forceinline__ void load_fast(float4 (&reg)[ROWS / 32], int blk) const {
+  __device__ __forceinline__ void load_fast(float4 (&reg)[ROWS / 32], int blk, int hint = 0) const {
 #pragma unroll
-    for (int it = 0; it < ROWS / 32; ++it) reg[it] = *reinterpret_cast<const float4*>(p[it] + blk * step);
+    for (int it = 0; it < ROWS / 32; ++it) {
+      const float* q = p[it] + blk * step;
+      if (hint == 1)
+        asm volatile("ld.global.L2::256B.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(reg[it].x), "=f"(reg[it].y), "=f"(reg[it].z), "=f"(reg[it].w) : "l"(q));
+      else if (hint == 2)
+        asm volatile("ld.global.L1::no_allocate.L2::256B.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(reg[it].x), "=f"(reg[it].y), "=f"(reg[it].z), "=f"(reg[it].w) : "l"(q));
+      else if (hint == 3)
+        asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(reg[it].x), "=f"(reg[it].y), "=f"(reg[it].z), "=f"(reg[it].w) : "l"(q));
+      else
+        reg[it] = *reinterpret_cast<const float4*>(q);
+    }
   }
   // hi = x with the 13 low mantissa bits cleared (a TF32 number), lo = x - hi (exact).  lo is stored as is: the
   // tensor core reads 19 bits of it, an error of 2^-10 |lo| <= 2^-20 |x|, the same order as the split itself.
@@ -698,13 +753,13 @@ __device__ __forceinline__ float f_epilogue(const FusedGemmArgs& g, float v, int
 // K = 1024 per CTA — spent its time in long-scoreboard stalls: 260 us for 402 MB, profiles/r01d_attention_ncu.md).
 template <bool FAST>
 __device__ __forceinline__ void fused_mainloop(const FTile<FM>& ta_, const FTile<FN>& tb_, uint8_t* smem, uint64_t* freed,
-                                               uint32_t tmem_base, int nkb, int kbeg, int kend, uint32_t& ph0, uint32_t& ph1) {
+                                               uint32_t tmem_base, int nkb, int kbeg, int kend, uint32_t& ph0, uint32_t& ph1, int hint) {
   constexpr int GB = 4;
   float4 ra[GB][FM / 32], rb[GB][FN / 32];
 #pragma unroll
   for (int u = 0; u < GB; ++u)
     if (u < nkb) {
-      if (FAST) { ta_.load_fast(ra[u], u); tb_.load_fast(rb[u], u); }
+      if (FAST) { ta_.load_fast(ra[u], u, hint); tb_.load_fast(rb[u], u); }
       else { const int krem = kend - (kbeg + u * TK); ta_.load(ra[u], u, krem); tb_.load(rb[u], u, krem); }
     }
 #pragma unroll 1
@@ -722,7 +777,7 @@ __device__ __forceinline__ void fused_mainloop(const FTile<FM>& ta_, const FTile
         ta_.store(ra[u], st, st + F_A_PLANE);
         tb_.store(rb[u], st + 2 * F_A_PLANE, st + 2 * F_A_PLANE + F_B_PLANE);
         if (kb + GB < nkb) {                            // refill this ring slot
-          if (FAST) { ta_.load_fast(ra[u], kb + GB); tb_.load_fast(rb[u], kb + GB); }
+          if (FAST) { ta_.load_fast(ra[u], kb + GB, hint); tb_.load_fast(rb[u], kb + GB); }
           else { const int krem = kend - (kbeg + (kb + GB) * TK); ta_.load(ra[u], kb + GB, krem); tb_.load(rb[u], kb + GB, krem); }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
@@ -781,8 +836,8 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_cons
   tb_.init(g.B + bz * g.sb, g.ldb, b_kmajor, g.b_vec != 0, n0, g.n, kbeg);
   uint32_t ph0 = 0, ph1 = 0;                            // parity of freed[0] / freed[1]
   const bool fast = g.a_vec && g.b_vec && m0 + FM <= g.m && n0 + FN <= g.n && nkb > 0 && ((kend - kbeg) % TK) == 0;
-  if (fast) fused_mainloop<true>(ta_, tb_, smem, freed, tmem_base, nkb, kbeg, kend, ph0, ph1);
-  else      fused_mainloop<false>(ta_, tb_, smem, freed, tmem_base, nkb, kbeg, kend, ph0, ph1);
+  if (fast) fused_mainloop<true>(ta_, tb_, smem, freed, tmem_base, nkb, kbeg, kend, ph0, ph1, g.a_hint);
+  else      fused_mainloop<false>(ta_, tb_, smem, freed, tmem_base, nkb, kbeg, kend, ph0, ph1, 0);
   // ---- all MMAs retired?  (the last commit covers every earlier one)
   if (nkb > 0) {
     // commits retire in order, so waiting for the last block's commit covers every MMA; the other
@@ -918,6 +973,26 @@ static int make_map256(CUtensorMap* map, float* base, int rows, int Kp, int nbat
   return 0;
 }
 
+// C as (n, m, batch) for the epilogue's bulk tensor stores: 32 x 32 boxes, SWIZZLE_128B.  Returns 1 when the map was
+// built, 0 when C's layout does not fit a tensor map (the epilogue then stores from registers).
+static int g_c_tma = -1;              // WF2CU_GEMM_CTMA=0 turns the bulk-store epilogue off
+static int make_map_c(CUtensorMap* map, float* C, int64_t m, int64_t n, int64_t ldc, int64_t sc, int64_t batch) {
+  memset(map, 0, sizeof(*map));
+  if (g_c_tma < 0) { const char* e = getenv("WF2CU_GEMM_CTMA"); g_c_tma = (e && e[0] == '0') ? 0 : 1; }
+  if (!g_c_tma) return 0;
+  if ((reinterpret_cast<uintptr_t>(C) & 15) != 0 || (ldc & 3) != 0 || ldc < n) return 0;
+  int64_t bstride = sc;
+  if (batch == 1) bstride = m * ldc;
+  else if (sc < m * ldc || (sc % ldc) != 0) return 0;       // overlapping or oddly pitched batches: keep the plain path
+  cuuint64_t dims[3] = {(cuuint64_t)n, (cuuint64_t)m, (cuuint64_t)batch};
+  cuuint64_t strides[2] = {(cuuint64_t)ldc * 4, (cuuint64_t)bstride * 4};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, C, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 1 : 0;
+}
+
 static int launch_split(const float* src, float* hi, float* lo, int64_t ld, int64_t sx, int R, int K, int Kp, int nbatch,
                         bool r_contiguous) {
   SplitArgs sa{src, hi, lo, ld, sx, R, K, Kp, 0};
@@ -997,7 +1072,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0);
   if (rc) return rc;
 
-  CUtensorMap mah, mal, mbh, mbl;
+  CUtensorMap mah, mal, mbh, mbl, mc;
+  const int c_tma = make_map_c(&mc, C, m, n, ldc, sc, batch);
   // 128x256, 256x256 or 256x192 tiles: results are bit-identical (same k order per output), pick_tile256 chooses
   const int64_t tiles_m256 = (m + T2M - 1) / T2M;
   const int64_t tiles256 = tiles_m256 * ((n + 255) / 256) * batch;
@@ -1028,11 +1104,11 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
     t.a_bcast = a_nb == 1 ? 1 : 0;
     t.b_bcast = b_nb == 1 ? 1 : 0;
-    t.bias = bias; t.act = act;
+    t.bias = bias; t.act = act; t.c_tma = c_tma;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     const int grid = (int)(total < S().sm_count ? total : S().sm_count);
-    if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, GEMM_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, t);
-    else           gemm_tc256_kernel<192, 3><<<grid, GEMM_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, t);
+    if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, GEMM_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
+    else           gemm_tc256_kernel<192, 3><<<grid, GEMM_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
     rc = post_launch(nb == 256 ? "wf2cu_gemm(tcgen05 256x256)" : "wf2cu_gemm(tcgen05 256x192)");
     return rc ? -rc : 1;
   }
@@ -1048,10 +1124,10 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   t.a_bcast = a_nb == 1 ? 1 : 0;
   t.b_bcast = b_nb == 1 ? 1 : 0;
-  t.bias = bias; t.act = act;
+  t.bias = bias; t.act = act; t.c_tma = c_tma;
   const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
   const int grid = (int)(total < S().sm_count ? total : S().sm_count);
-  gemm_tc_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, t);
+  gemm_tc_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, mc, t);
   rc = post_launch("wf2cu_gemm(tcgen05)");
   return rc ? -rc : 1;
 }
@@ -1084,6 +1160,12 @@ int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const flo
   g.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   g.ksplit = ksplit; g.kchunk = kchunk;
   g.bias = bias; g.mask = mask; g.ldmask = ldmask; g.act = act;
+  {
+    static int hint = -1;
+    // measured on GPT-2's P.V (B200): 221 / 212 / 207 / 213 us for hints 0 / 1 / 2 / 3 (profiles/r01d_attention_ncu.md)
+    if (hint < 0) { const char* e = getenv("WF2CU_FUSED_AHINT"); hint = e ? atoi(e) : 2; if (hint < 0 || hint > 3) hint = 2; }
+    if (!ta && kchunk / TK >= 16) g.a_hint = hint;
+  }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)((n + FN - 1) / FN), (unsigned)((m + FM - 1) / FM), (unsigned)(batch * ksplit));
