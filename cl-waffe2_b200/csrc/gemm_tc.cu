@@ -14,7 +14,9 @@
 //        warp 0    TMA producer   cp.async.bulk.tensor.3d, SWIZZLE_128B, 4 planes per stage
 //        warp 1    MMA issuer     tcgen05.mma.cta_group::1.kind::tf32, 128x256x8, 3 per k-slice,
 //                                 accumulator double-buffered in TMEM (2 x 256 columns)
-//        warps 2-5 epilogue       tcgen05.ld 32x32b.x32 -> registers -> global (bounds-checked)
+//        warps 2-5 epilogue       tcgen05.ld 32x32b.x32 -> registers -> SWIZZLE_128B staging block in shared memory ->
+//                                 cp.async.bulk.tensor store through a tensor map of C (clipped at the edges by the map);
+//                                 C layouts a tensor map cannot describe are stored from registers, bounds-checked
 //      smem full/empty mbarriers between warp 0 and warp 1, TMEM full/empty between 1 and 2-5.
 #include <cuda.h>
 #include <vector>

@@ -199,3 +199,85 @@ def test_state_dict_key_convention(wf):
     with pytest.raises(ValueError):
         sd.parse_state_dict_key("weights:linearlayer.0.bias")
     assert len(sd.make_state_dict(named, Opt(), weights=False, optimizers=True)) == 10
+
+
+# ------------------------------------------------------------------ the Lisp host files (no Common Lisp here: lint by reading)
+LISP_DIR = os.path.join(ROOT, "cl-waffe2_b200", "lisp")
+
+
+def _strip_lisp(src):
+    """Source with comments, strings and character literals blanked out."""
+    out, i, n = [], 0, len(src)
+    while i < n:
+        c = src[i]
+        if c == ";":
+            while i < n and src[i] != "\n":
+                i += 1
+        elif c == "#" and src[i + 1:i + 2] == "|":
+            j = src.index("|#", i)
+            out.append("\n" * src[i:j].count("\n"))
+            i = j + 2
+        elif c == '"':
+            i += 1
+            while src[i] != '"':
+                if src[i] == "\\":
+                    i += 1
+                if src[i] == "\n":
+                    out.append("\n")
+                i += 1
+            i += 1
+            out.append('""')
+        elif c == "#" and src[i + 1:i + 2] == "\\":
+            i += 3
+            out.append("x")
+        else:
+            out.append(c)
+            i += 1
+    return "".join(out)
+
+
+def test_lisp_host_forms_are_balanced():
+    files = sorted(f for f in os.listdir(LISP_DIR) if f.endswith(".lisp"))
+    assert {"package.lisp", "cffi.lisp", "tensor.lisp", "lowering.lisp", "arithmetic.lisp", "mathematics.lisp", "logical.lisp",
+            "matrix-ops.lisp", "fusion.lisp", "im2col.lisp"} <= set(files)
+    for f in files:
+        depth, line = 0, 1
+        for ch in _strip_lisp(open(os.path.join(LISP_DIR, f)).read()):
+            if ch == "\n":
+                line += 1
+            elif ch == "(":
+                depth += 1
+            elif ch == ")":
+                depth -= 1
+                assert depth >= 0, f"{f}:{line}: unmatched ')'"
+        assert depth == 0, f"{f}: {depth} unclosed '('"
+
+
+def test_lisp_host_names_exist_in_reference():
+    """Every node class the backend implements and every package-qualified symbol it uses is defined by the reference
+    (a typo here would only show up when a maintainer loads the files).  Needs /root/reference, which exists in the
+    authoring container only."""
+    ref = "/root/reference/source"
+    if not os.path.isdir(ref):
+        pytest.skip("reference sources are not on this machine")
+    corpus = []
+    for dirpath, _, fs in os.walk("/root/reference"):
+        if "/third_party" in dirpath or "/.git" in dirpath:
+            continue
+        corpus += [open(os.path.join(dirpath, f), errors="replace").read().lower() for f in fs if f.endswith((".lisp", ".asd"))]
+    corpus = "\n".join(corpus)
+    own = "\n".join(_strip_lisp(open(os.path.join(LISP_DIR, f)).read()) for f in sorted(os.listdir(LISP_DIR)) if f.endswith(".lisp"))
+    nodes = set(re.findall(r"\(define-(?:arith-impl|math-impl|rowred)\s+([A-Za-z0-9>\-]+)", own))
+    nodes |= set(re.findall(r"\(define-impl(?:-op)?\s+\(([A-Za-z0-9>\-]+)\s+:device", own))
+    defined_here = set(re.findall(r"\(defnode\s+\(([A-Za-z0-9>\-]+)", own))
+    assert len(nodes) >= 30, sorted(nodes)
+    for nd in sorted(nodes - defined_here):
+        assert re.search(r"\((?:defnode|define-op)\s+\(" + re.escape(nd.lower()) + r"[\s)]", corpus) or \
+            re.search(r"\(define-(?:arith|math|scalar-mat|logical)[a-z-]*\s.*" + re.escape(nd.lower()), corpus) or \
+            nd.lower() in corpus, f"node {nd} is not defined by the reference"
+    qualified = set(re.findall(r"\b((?:cl-waffe2/[a-z.\-]+|wf/[a-z]+)::?[a-zA-Z0-9*+<>=/!?\-]+)", own))
+    assert qualified, "expected package-qualified symbols"
+    for q in sorted(qualified):
+        pkg, sym = re.split(r"::?", q, maxsplit=1)
+        assert pkg.lower() in corpus, f"package {pkg} ({q}) not found in the reference"
+        assert re.search(r"[\s(:'#]" + re.escape(sym.lower()) + r"[\s)]", corpus), f"{q}: {sym} not found in the reference"
