@@ -1,0 +1,192 @@
+"""`:backward` compositions of the hot-path nodes (cl-waffe2_b200/backward.py).
+
+CPU part: the compositions, run over the oracle's nodes (the reference's own C kernels), against the gradient goldens of
+the reference's tests — `base-impl/t/arithmetic.lisp:25-51` (a = 10, b = 1: grads (1 1) (1 -1) (1 10) (1 -10)),
+`base-impl/t/mathematical.lisp:36-141` (x = 1, dout = 1: abs' = signum, sign' = 0, sqrt' = 1/x, square' = x, sin' = cos,
+cos' = -sin, tan' = 1/cos^2, sinh' = cosh, cosh' = -sinh [as the reference defines it], tanh' = 1/cosh^2, exp' = exp,
+log2' = 1/(x ln 2), log10' = 1/(x ln 10), loge' = 1/x) — and against fp64 derivatives on random points.
+
+GPU part (`-m gpu`): the same compositions on CUDATensor, every step one libwaffe2cuda.so kernel, against the oracle run:
+bit-exact for the arithmetic nodes, within a few ulp for the chains that contain transcendentals.
+(The file sorts last on purpose: it was added after the round's last GPU session.)
+"""
+import importlib
+import math
+
+import numpy as np
+import pytest
+
+RNG = np.random.default_rng(5)
+
+
+class OracleBackend:
+    """cl-waffe2_b200.backward's backend protocol over oracle/loopnest.py."""
+
+    def __init__(self, L):
+        self.L = L
+
+    def copy(self, x):
+        return self.L.copy(x)
+
+    def ones_like(self, x):
+        return self.L.make_tensor(x.shape, data=np.ones(x.shape, np.float32))
+
+    def arith_(self, op, x, y):
+        if isinstance(y, (int, float)):
+            return self.L.scalar_op_(op, x, float(y))
+        return self.L.arith_(op, x, y)
+
+    def unary(self, fn, x):
+        # SignNode / SquareNode have LispTensor impls only (`backends/lisp/mathematics.lisp:49,53`: `signum`, `(* x x)`);
+        # the C kernels name the natural logarithm `log`
+        if fn == "sign":
+            return self.L.make_tensor(x.shape, data=np.sign(x.to_numpy()).astype(np.float32))
+        if fn == "square":
+            v = x.to_numpy().astype(np.float32)
+            return self.L.make_tensor(x.shape, data=v * v)
+        return self.L.unary({"loge": "log"}.get(fn, fn), x)
+
+    def expt(self, x, n):
+        return self.L.expt(x, float(n))
+
+
+@pytest.fixture(scope="module")
+def bw(wf):
+    return importlib.import_module("cl-waffe2_b200.backward")
+
+
+def const(L, shape, v):
+    return L.make_tensor(shape, data=np.full(shape, v, np.float32))
+
+
+# ------------------------------------------------------------------ CPU: the reference's gradient goldens
+@pytest.mark.parametrize("op,g1,g2", [("add", 1, 1), ("sub", 1, -1), ("mul", 1, 10), ("div", 1, -10)])
+def test_arith_backward_goldens(bw, L, op, g1, g2):
+    # define-arith-tester: a = 10, b = 1, dout = 1 => (grad a, grad b); note: mul's tester swaps because grad a = dout * b
+    B = OracleBackend(L)
+    a, b, dout = const(L, (100, 100), 10), const(L, (100, 100), 1), const(L, (100, 100), 1)
+    ga, gb = bw.arith_backward(B, op, dout, a, b)
+    assert (ga.to_numpy() == g1).all() and (gb.to_numpy() == g2).all()
+    # inputs are untouched (every builder copies first, like !mul etc.)
+    assert (a.to_numpy() == 10).all() and (b.to_numpy() == 1).all() and (dout.to_numpy() == 1).all()
+
+
+GOLDEN_AT_ONE = {
+    "abs": 1.0, "sign": 0.0, "sqrt": 1.0, "square": 1.0, "sin": math.cos(1), "cos": -math.sin(1),
+    "tan": 1 / math.cos(1) ** 2, "sinh": math.cosh(1), "cosh": -math.sinh(1), "tanh": 1 / math.cosh(1) ** 2,
+    "exp": math.exp(1), "log2": 1 / math.log(2), "log10": 1 / math.log(10), "loge": 1.0,
+}
+
+
+@pytest.mark.parametrize("fn", sorted(GOLDEN_AT_ONE))
+def test_unary_backward_goldens_at_one(bw, L, fn):
+    # define-mathematical-kernel-tester: (30 30) of ones, `~=` is a 1e-6-ish float comparison in the reference
+    B = OracleBackend(L)
+    x, dout = const(L, (30, 30), 1), const(L, (30, 30), 1)
+    g = bw.unary_backward(B, fn, dout, x).to_numpy()
+    assert g.shape == (30, 30)
+    np.testing.assert_allclose(g, GOLDEN_AT_ONE[fn], rtol=2e-6, atol=1e-7)
+    assert (x.to_numpy() == 1).all() and (dout.to_numpy() == 1).all()
+
+
+TRUE_DERIVATIVE = {          # fp64; the four nodes whose reference formula is not the calculus one are excluded
+    "abs": np.sign, "sin": np.cos, "cos": lambda x: -np.sin(x), "tan": lambda x: 1 / np.cos(x) ** 2,
+    "sinh": np.cosh, "tanh": lambda x: 1 / np.cosh(x) ** 2, "asin": lambda x: 1 / np.sqrt(1 - x * x),
+    "acos": lambda x: -1 / np.sqrt(1 - x * x), "atan": lambda x: 1 / (1 + x * x), "exp": np.exp,
+    "log2": lambda x: 1 / (x * np.log(2)), "log10": lambda x: 1 / (x * np.log(10)), "loge": lambda x: 1 / x,
+    "log1p": lambda x: 1 / (1 + x),
+}
+
+
+def _domain(fn, shape):
+    if fn in ("log2", "log10", "loge", "sqrt"):
+        return RNG.uniform(0.5, 3.0, size=shape).astype(np.float32)
+    if fn == "log1p":
+        return RNG.uniform(-0.5, 3.0, size=shape).astype(np.float32)
+    if fn in ("asin", "acos"):
+        return RNG.uniform(-0.9, 0.9, size=shape).astype(np.float32)
+    return RNG.uniform(-1.0, 1.0, size=shape).astype(np.float32)
+
+
+@pytest.mark.parametrize("fn", sorted(TRUE_DERIVATIVE))
+def test_unary_backward_matches_fp64_derivative(bw, L, fn):
+    B = OracleBackend(L)
+    xs, ds = _domain(fn, (17, 33)), RNG.uniform(-2, 2, size=(17, 33)).astype(np.float32)
+    g = bw.unary_backward(B, fn, L.make_tensor(xs.shape, data=ds), L.make_tensor(xs.shape, data=xs)).to_numpy()
+    want = ds.astype(np.float64) * TRUE_DERIVATIVE[fn](xs.astype(np.float64))
+    np.testing.assert_allclose(g, want, rtol=5e-6, atol=1e-6)
+
+
+def test_reference_quirks_are_kept(bw, L):
+    """cosh' = -sinh, sqrt' = 1/x, square' = x, sign' = x*0 (mathematics.lisp:131-147,184-188): reproduced as written."""
+    B = OracleBackend(L)
+    xs = RNG.uniform(0.5, 2.0, size=(8, 8)).astype(np.float32)
+    x, one = L.make_tensor(xs.shape, data=xs), const(L, (8, 8), 1)
+    np.testing.assert_allclose(bw.unary_backward(B, "cosh", one, x).to_numpy(), -np.sinh(xs.astype(np.float64)), rtol=2e-6)
+    np.testing.assert_allclose(bw.unary_backward(B, "sqrt", one, x).to_numpy(), 1 / xs.astype(np.float64), rtol=2e-6)
+    np.testing.assert_array_equal(bw.unary_backward(B, "square", one, x).to_numpy(), xs)
+    assert (bw.unary_backward(B, "sign", one, x).to_numpy() == 0).all()
+
+
+def test_expt_backward(bw, L):
+    B = OracleBackend(L)
+    xs = RNG.uniform(0.5, 2.0, size=(9, 11)).astype(np.float32)
+    ds = RNG.uniform(-1, 1, size=(9, 11)).astype(np.float32)
+    gx, gn = bw.expt_backward(B, L.make_tensor(xs.shape, data=ds), L.make_tensor(xs.shape, data=xs), 3.0, want_dn=True)
+    x64, d64 = xs.astype(np.float64), ds.astype(np.float64)
+    np.testing.assert_allclose(gx.to_numpy(), d64 * 3 * x64 ** 2, rtol=5e-6, atol=1e-6)
+    np.testing.assert_allclose(gn.to_numpy(), d64 * x64 ** 3 * np.log(x64), rtol=5e-6, atol=1e-6)
+
+
+def test_scalar_first_dispatch(bw, L):
+    """(!sub 1 x) = (x * -1) + 1 and (!div 1 x) = (ones / x) * 1 (arithmetic.lisp:398-434, 179-208): same roundings as the
+    reference's rewrite, not a fused 1 - x."""
+    B = OracleBackend(L)
+    xs = RNG.uniform(0.5, 2.0, size=(7, 5)).astype(np.float32)
+    x = L.make_tensor(xs.shape, data=xs)
+    np.testing.assert_array_equal(bw.sub(B, 1, x).to_numpy(), (xs * np.float32(-1)) + np.float32(1))
+    np.testing.assert_array_equal(bw.div(B, 1, x).to_numpy(), (np.float32(1) / xs) * np.float32(1))
+    np.testing.assert_array_equal(bw.add(B, 2, x).to_numpy(), xs + np.float32(2))
+    np.testing.assert_array_equal(x.to_numpy(), xs)
+
+
+# ------------------------------------------------------------------ GPU: the same compositions on CUDATensor
+@pytest.mark.gpu
+@pytest.mark.parametrize("op", ["add", "sub", "mul", "div"])
+def test_gpu_arith_backward_exact(gpu, bw, L, op):
+    shape = (33, 130)
+    a = RNG.uniform(-1, 1, size=shape).astype(np.float32)
+    b = RNG.uniform(0.5, 2, size=shape).astype(np.float32)
+    d = RNG.uniform(-1, 1, size=shape).astype(np.float32)
+    mk_o = lambda v: L.make_tensor(shape, data=v)
+    mk_g = lambda v: gpu.make_tensor(shape, data=v)
+    oa, ob = bw.arith_backward(OracleBackend(L), op, mk_o(d), mk_o(a), mk_o(b))
+    ga, gb = bw.arith_backward(bw.DeviceBackend(), op, mk_g(d), mk_g(a), mk_g(b))
+    np.testing.assert_array_equal(ga.to_numpy(), oa.to_numpy())
+    np.testing.assert_array_equal(gb.to_numpy(), ob.to_numpy())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fn", ["abs", "sign", "sqrt", "square", "sin", "cos", "tan", "sinh", "cosh", "tanh", "asin", "acos", "atan",
+                                "exp", "log2", "log10", "loge", "log1p"])
+def test_gpu_unary_backward_matches_oracle(gpu, bw, L, fn):
+    shape = (19, 67)
+    xs, ds = _domain(fn, shape), RNG.uniform(-2, 2, size=shape).astype(np.float32)
+    o = bw.unary_backward(OracleBackend(L), fn, L.make_tensor(shape, data=ds), L.make_tensor(shape, data=xs)).to_numpy()
+    gx, gd = gpu.make_tensor(shape, data=xs), gpu.make_tensor(shape, data=ds)
+    g = bw.unary_backward(bw.DeviceBackend(), fn, gd, gx).to_numpy()
+    # each transcendental is within 2 ulp of the reference's; a chain of at most three of them plus exact arithmetic
+    np.testing.assert_allclose(g, o, rtol=2e-6, atol=1e-7)
+    np.testing.assert_array_equal(gx.to_numpy(), xs)        # saved inputs are not modified
+    np.testing.assert_array_equal(gd.to_numpy(), ds)
+
+
+@pytest.mark.gpu
+def test_gpu_expt_backward_matches_oracle(gpu, bw, L):
+    shape = (12, 40)
+    xs = RNG.uniform(0.5, 2.0, size=shape).astype(np.float32)
+    ds = RNG.uniform(-1, 1, size=shape).astype(np.float32)
+    ox, on = bw.expt_backward(OracleBackend(L), L.make_tensor(shape, data=ds), L.make_tensor(shape, data=xs), 2.5, want_dn=True)
+    gx, gn = bw.expt_backward(bw.DeviceBackend(), gpu.make_tensor(shape, data=ds), gpu.make_tensor(shape, data=xs), 2.5, want_dn=True)
+    np.testing.assert_allclose(gx.to_numpy(), ox.to_numpy(), rtol=5e-6, atol=1e-7)
+    np.testing.assert_allclose(gn.to_numpy(), on.to_numpy(), rtol=5e-6, atol=1e-7)
