@@ -8,7 +8,7 @@ log2' = 1/(x ln 2), log10' = 1/(x ln 10), loge' = 1/x) — and against fp64 deri
 
 GPU part (`-m gpu`): the same compositions on CUDATensor, every step one libwaffe2cuda.so kernel, against the oracle run:
 bit-exact for the arithmetic nodes, within a few ulp for the chains that contain transcendentals.
-(The file sorts last on purpose: it was added after the round's last GPU session.)
+(Run on a B200: profiles/r01d_pytest_gpu_backward_rules.log, 23 passed.)
 """
 import importlib
 import math
