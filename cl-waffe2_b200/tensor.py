@@ -228,6 +228,14 @@ class CUDATensor:
                 first = range_nth(v.rng, 0)
                 off += st * first
                 stride.append(st * (range_nth(v.rng, 1) - first))
+        # a kernel trusts the descriptor: refuse one that addresses elements outside the storage (possible through
+        # `permute*` of a sliced view, which re-applies the slice: tensor.lisp:880-896, 929-991) instead of faulting
+        if all(ext > 0 for ext in shape):
+            lo = off + sum((ext - 1) * sd for ext, sd in zip(shape, stride) if sd < 0)
+            hi = off + sum((ext - 1) * sd for ext, sd in zip(shape, stride) if sd > 0)
+            if lo < 0 or hi * 4 >= self.vec.nbytes:
+                raise ValueError(f"view of shape {shape} addresses elements [{lo}, {hi}] outside its storage of "
+                                 f"{self.vec.nbytes // 4} elements")
         return _lib.make_view(self.vec.ptr, off, shape, stride)
 
     def is_contiguous(self) -> bool:

@@ -281,3 +281,73 @@ def test_lisp_host_names_exist_in_reference():
         pkg, sym = re.split(r"::?", q, maxsplit=1)
         assert pkg.lower() in corpus, f"package {pkg} ({q}) not found in the reference"
         assert re.search(r"[\s(:'#]" + re.escape(sym.lower()) + r"[\s)]", corpus), f"{q}: {sym} not found in the reference"
+
+
+# ------------------------------------------------------------------ property test: random view / permute chains
+def _random_subscript(draw, st, size):
+    """One subscript the reference's parse-view accepts for an axis of SIZE elements (view.lisp:138-206)."""
+    kind = draw(st.sampled_from(["t", "index", "slice", "step", "neg"] if size > 1 else ["t", "index", "bcast"]))
+    if kind == "t":
+        return True
+    if kind == "index":
+        return draw(st.integers(0, size - 1))
+    if kind == "bcast":
+        return [":broadcast", draw(st.integers(1, 4))]
+    a = draw(st.integers(0, size - 1))
+    b = draw(st.integers(a + 1, size))
+    if kind == "slice":
+        return [a, b]
+    step = draw(st.integers(1, 3))
+    return [a, b, step] if kind == "step" else [b, a, -step] if a > 0 or b < size else [a, b, step]
+
+
+def test_random_view_chains_match_oracle(wf):
+    """Shapes of rank 1-4, up to three views stacked on each other (index / slice / stepped / reversed / broadcast),
+    with a permute in between: the lowered (offset, shape, stride) of the product addresses exactly the elements the
+    oracle's restatement of `mref` + `range-nth` does; where the reference's algebra leaves the storage (an index into a
+    broadcast axis; `permute*` re-applying a slice that does not start at 0: detach-and-clone1, tensor.lisp:880-896) the
+    product refuses to lower the view instead of handing a kernel an out-of-range descriptor."""
+    hyp = pytest.importorskip("hypothesis")
+    st = hyp.strategies
+
+    def same(g, o, msg):
+        """True when both address the same elements; False when both leave the storage."""
+        assert g.shape == o.shape, msg
+        try:
+            want = oracle_offsets(o)
+        except IndexError:
+            with pytest.raises(ValueError, match="outside its storage"):
+                g.lower()
+            return False
+        np.testing.assert_array_equal(lowered_offsets(g), want, err_msg=msg)
+        return True
+
+    @hyp.settings(max_examples=300, deadline=None, suppress_health_check=list(hyp.HealthCheck))
+    @hyp.given(st.data())
+    def run(data):
+        draw = data.draw
+        shape = draw(st.lists(st.integers(1, 6), min_size=1, max_size=4))
+        order = draw(st.sampled_from(["column", "row"]))
+        g, o = fake_tensor(wf, tuple(shape), order), L.make_tensor(list(shape), order=order)
+        for depth in range(draw(st.integers(1, 3))):
+            subs = [_random_subscript(draw, st, n) for n in g.shape]
+            try:
+                o2 = L.view(o, *subs)
+            except (AssertionError, ValueError, IndexError, ZeroDivisionError):
+                # a chain the reference's view algebra rejects must be rejected by the product as well
+                with pytest.raises((AssertionError, ValueError, IndexError, ZeroDivisionError)):
+                    wf.view(g, *subs)
+                return
+            g, o = wf.view(g, *subs), o2
+            if 0 in o.shape:            # a stepped range can come out empty (range-size floors): nothing left to view
+                assert g.shape == o.shape
+                return
+            if not same(g, o, f"{shape} {order} {subs}"):
+                return
+            if depth == 0 and len(g.shape) > 1 and draw(st.booleans()):
+                perm = draw(st.permutations(list(range(len(g.shape)))))
+                g, o = wf.permute(g, *perm), L.permute(o, *perm)
+                if not same(g, o, f"{shape} {order} perm {perm}"):
+                    return
+
+    run()
