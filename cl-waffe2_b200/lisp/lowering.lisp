@@ -42,6 +42,25 @@
 		   (incf offset (* stride first))
 		   (setf (mem-aref stride-ptr :int64 k) (* stride step)))))
     (setf (foreign-slot-value view-ptr '(:struct wf2cu-view) 'offset) offset)
+    ;; A kernel trusts the descriptor: refuse one that addresses elements outside the storage (possible through
+    ;; `permute*` of a sliced view, which re-applies the slice: `tensor.lisp:880-896,929-991`) instead of faulting.
+    (let ((shape-ptr  (foreign-slot-pointer view-ptr '(:struct wf2cu-view) 'shape))
+	  (stride-ptr (foreign-slot-pointer view-ptr '(:struct wf2cu-view) 'stride))
+	  (lo offset)
+	  (hi offset)
+	  (empty-p nil))
+      (dotimes (k rank)
+	(let ((ext (mem-aref shape-ptr :int64 k))
+	      (sd  (mem-aref stride-ptr :int64 k)))
+	  (cond
+	    ((<= ext 0) (setq empty-p t))
+	    ((< sd 0)   (incf lo (* (1- ext) sd)))
+	    (t          (incf hi (* (1- ext) sd))))))
+      (when (and (not empty-p)
+		 (or (< lo 0)
+		     (>= (* 4 hi) (device-vec-bytes (tensor-vec tensor)))))
+	(error "CUDATensor: a view of shape ~a addresses elements [~a, ~a] outside its storage of ~a elements"
+	       (shape tensor) lo hi (floor (device-vec-bytes (tensor-vec tensor)) 4))))
     view-ptr))
 
 (defmacro with-lowered-views ((&rest bindings) &body body)
