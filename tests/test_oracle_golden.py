@@ -1,6 +1,7 @@
 """Pins the oracle (oracle/loopnest.py + the reference's own C kernels in oracle/_ref) against the
 golden vectors of the reference's test-suite.  CPU only.  Each test cites the reference test it
 replays (paths under /root/reference/source)."""
+import os
 import numpy as np
 import pytest
 
@@ -186,3 +187,75 @@ def test_port_matches_reference_build():
         d = np.abs(o1.view(np.int32).astype(np.int64) - o2.view(np.int32).astype(np.int64))
         assert d.max() <= 1, (name, d.max())      # SLEEF u10 body vs double-libm tail arithmetic
         assert np.array_equal(o1[-(n % 8):], o2[-(n % 8):])   # the reference's own tail IS the port's arithmetic
+
+
+# ---- committed fixtures: outputs of the reference's own compiled kernels (tests/golden/make_golden.py) ------------------
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_kernels_v1.npz")
+
+
+def _ulps(a, b):
+    ia = a.view(np.int32).astype(np.int64)
+    ib = b.view(np.int32).astype(np.int64)
+    ia = np.where(ia < 0, -(ia & 0x7FFFFFFF), ia)
+    ib = np.where(ib < 0, -(ib & 0x7FFFFFFF), ib)
+    return np.abs(ia - ib)
+
+
+@pytest.mark.parametrize("which", ["port", "reference"])
+def test_kernels_reproduce_committed_golden_outputs(which):
+    """`port`: oracle/port.c against what the reference's C kernels + SLEEF produced (bit-exact for everything except the
+    transcendentals' SIMD body, where SLEEF's polynomial and the port's double-libm differ by <= 1 ulp).
+    `reference`: the compiled reference itself must reproduce the fixture bit for bit (a stale fixture fails here)."""
+    if which == "reference" and not kernels.have_reference():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    K = kernels.load(which)
+    assert K.kind == which
+    G = np.load(GOLDEN)
+    exact = which == "reference"
+    for fn in ["sin", "cos", "tan", "asin", "acos", "atan", "sinh", "cosh", "tanh", "exp", "log", "log2", "log10", "log1p",
+               "sqrt", "abs"]:
+        x, want = G[f"unary/{fn}/x"].copy(), G[f"unary/{fn}/y"]
+        got = np.zeros_like(want)
+        K.unary(fn, len(x), x, 0, 1, got, 0, 1)
+        assert _ulps(got, want).max() <= (0 if exact else 1), (fn, _ulps(got, want).max())
+    x, y = G["arith/x"], G["arith/y"].copy()
+    for op in kernels.ARITH:
+        acc = x.copy()
+        K.arith(op, len(acc), acc, 0, 1, y, 0, 1)
+        assert np.array_equal(acc, G[f"arith/{op}"]), op
+    px = G["pow/x"].copy()
+    for p in (2.0, 3.0, 0.5, -1.5):
+        got = np.zeros_like(px)
+        K.pow(len(px), px, 0, 1, p, got, 0, 1)
+        assert _ulps(got, G[f"pow/{p}"]).max() <= (0 if exact else 1), p
+    cx, cy = G["cmp/x"].copy(), G["cmp/y"].copy()
+    for op in kernels.CMP:
+        got = np.zeros_like(cx)
+        K.cmp(op, len(cx), cx, 0, 1, cy, 0, 1, got, 0, 1, 2.0, -1.0)
+        assert np.array_equal(got, G[f"cmp/{op}"]), op
+        got = np.zeros_like(cx)
+        K.cmp_scal(op, len(cx), cx, 0, 1, got, 0, 1, 0.25, 1.0, 0.0)
+        assert np.array_equal(got, G[f"cmp/{op}_scal"]), op
+    mx = G["maxmin/x"].copy()
+    for name in ("max", "min"):
+        got = np.zeros(1, np.float32)
+        K.maxmin(name, len(mx), mx, 0, 1, got, 0)
+        assert got[0] == G[f"maxmin/{name}"][0]
+    sx = G["seqsum/x"].copy()
+    acc = np.zeros(1, np.float32)
+    K.arith("add", len(sx), acc, 0, 0, sx, 0, 1)
+    assert acc[0] == G["seqsum/sum"][0]                       # the sequential fp32 order of `!sum`
+    seq = np.float32(0)
+    for v in sx:
+        seq = np.float32(seq + v)
+    assert seq == G["seqsum/sum"][0]
+    bx = G["bcast/x"].copy()
+    K.arith("mul", len(bx), bx, 0, 1, G["bcast/y"].copy(), 0, 0)
+    assert np.array_equal(bx, G["bcast/mul"])
+    geo = [int(v) for v in G["unfold/geometry"]]
+    col = np.zeros_like(G["unfold/col"])
+    K.unfold("im2col", col, *geo, G["unfold/img"].copy())
+    assert np.array_equal(col, G["unfold/col"])
+    back = np.zeros_like(G["unfold/back"])
+    K.unfold("col2im", G["unfold/col"].copy(), *geo, back)
+    assert np.array_equal(back, G["unfold/back"])

@@ -190,3 +190,58 @@ def test_gpu_expt_backward_matches_oracle(gpu, bw, L):
     gx, gn = bw.expt_backward(bw.DeviceBackend(), gpu.make_tensor(shape, data=ds), gpu.make_tensor(shape, data=xs), 2.5, want_dn=True)
     np.testing.assert_allclose(gx.to_numpy(), ox.to_numpy(), rtol=5e-6, atol=1e-7)
     np.testing.assert_allclose(gn.to_numpy(), on.to_numpy(), rtol=5e-6, atol=1e-7)
+
+
+# ------------------------------------------------------------------ GPU vs the committed reference outputs
+# tests/golden/ref_kernels_v1.npz holds what the reference's own compiled C kernels + SLEEF produced for fixed inputs
+# (tests/golden/make_golden.py); these checks need neither /root/reference nor the compiled reference library.
+import os
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_kernels_v1.npz")
+
+
+def _ulps(a, b):
+    ia = np.asarray(a, np.float32).ravel().view(np.int32).astype(np.int64)
+    ib = np.asarray(b, np.float32).ravel().view(np.int32).astype(np.int64)
+    ia = np.where(ia < 0, -(ia & 0x7FFFFFFF), ia)
+    ib = np.where(ib < 0, -(ib & 0x7FFFFFFF), ib)
+    return np.abs(ia - ib)
+
+
+@pytest.mark.gpu
+def test_gpu_matches_committed_reference_outputs(gpu):
+    G = np.load(GOLDEN)
+    two_d = lambda v: np.ascontiguousarray(v).reshape(5, -1)           # 525 = 5 x 105
+    name_map = {"log": "loge"}
+    for fn in ["sin", "cos", "tan", "asin", "acos", "atan", "sinh", "cosh", "tanh", "exp", "log", "log2", "log10", "log1p",
+               "sqrt", "abs"]:
+        x, want = two_d(G[f"unary/{fn}/x"]), G[f"unary/{fn}/y"]
+        got = gpu.ops.unary(name_map.get(fn, fn), gpu.from_numpy(x)).to_numpy()
+        worst = int(_ulps(got, want).max())
+        assert worst <= 2, f"{fn}: {worst} ulp from the reference's output"
+    for op in ["add", "sub", "mul", "div"]:                               # bit-exact
+        gx = gpu.from_numpy(two_d(G["arith/x"]))
+        getattr(gpu.ops, op + "_")(gx, gpu.from_numpy(two_d(G["arith/y"])))
+        np.testing.assert_array_equal(gx.to_numpy().ravel(), G[f"arith/{op}"], err_msg=op)
+    gx = gpu.from_numpy(two_d(G["pow/x"]))
+    for p in (2.0, 3.0, 0.5, -1.5):
+        worst = int(_ulps(gpu.ops.expt(gx, p).to_numpy(), G[f"pow/{p}"]).max())
+        assert worst <= 2, f"pow {p}: {worst} ulp"
+    cx, cy = gpu.from_numpy(two_d(G["cmp/x"])), gpu.from_numpy(two_d(G["cmp/y"]))
+    for cmp in ["eq", "lt", "le", "gt", "ge"]:
+        np.testing.assert_array_equal(gpu.ops.compare(cx, cmp, cy, 2.0, -1.0).to_numpy().ravel(), G[f"cmp/{cmp}"], err_msg=cmp)
+        np.testing.assert_array_equal(gpu.ops.where(cx, cmp, 0.25, 1.0, 0.0).to_numpy().ravel(), G[f"cmp/{cmp}_scal"], err_msg=cmp)
+    mx = gpu.from_numpy(G["maxmin/x"].reshape(1, -1))
+    assert gpu.ops.max(mx).to_numpy().ravel()[0] == G["maxmin/max"][0]
+    assert gpu.ops.min(mx).to_numpy().ravel()[0] == G["maxmin/min"][0]
+    bx = gpu.from_numpy(two_d(G["bcast/x"]))
+    gpu.ops.mul_(bx, float(G["bcast/y"][0]))
+    np.testing.assert_array_equal(bx.to_numpy().ravel(), G["bcast/mul"])
+    # `!sum`: the reference adds sequentially in fp32 (its result is the fixture); ours is a fixed tree.  Bar:
+    # ours within 1e-5 * sum|x| of the fp64 truth, and the reference's own distance shown beside it.
+    sx = G["seqsum/x"]
+    truth, sumabs = float(sx.astype(np.float64).sum()), float(np.abs(sx.astype(np.float64)).sum())
+    got = float(gpu.ops.sum(gpu.from_numpy(sx.reshape(1, -1)), axis=1).to_numpy().ravel()[0])
+    ref = float(G["seqsum/sum"][0])
+    assert abs(got - truth) <= 1e-5 * sumabs, (got, truth, ref)
+    assert abs(got - truth) <= max(abs(ref - truth), 2e-7 * sumabs) * 4 + 1e-7 * sumabs, (got, truth, ref)
