@@ -31,6 +31,9 @@
 		    (ew-binary +copy+ xv yv))
 		  x))))
 
-;; Scalar operands: `scalar (x) matrix` reaches the backend as Scalar->MatNode + a (:broadcast ...) view
-;; (`base-impl/arithmetic.lisp:244-250`, `fundamental.lisp:525-533`), i.e. a 4-byte H2D per use.  The
-;; fusion pass (fusion.lisp) rewrites that pattern to wf2cu_ew_scalar; nothing to define here.
+;; Scalar operands: `scalar (x) matrix` reaches the backend as an ordinary arithmetic node whose second operand is a
+;; one-element tensor viewed with (:broadcast n) on every axis (`base-impl/arithmetic.lisp:28-51,244-250`): for a number
+;; that tensor is made once at build time (`fill` in tensor.lisp), for a ScalarTensor it is refreshed by Scalar->MatNode's
+;; `(setf vref)` (`fundamental.lisp:525-533`, a 4-byte transfer).  wf2cu_ew_binary hoists stride-0 operands into
+;; registers, so nothing needs to be defined here; wf2cu_ew_scalar (scalar as a kernel argument) is bound in cffi.lisp
+;; for hosts that know the number.

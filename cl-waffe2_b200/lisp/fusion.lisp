@@ -2,16 +2,21 @@
 ;;;;
 ;;;; `on-finalizing-compiling` is called once per `build` per device with the forward / backward
 ;;;; InstructionSeq (`source/vm/nodes/defnode.lisp:26-57`, `vm/compile.lisp:237-238`; working
-;;;; precedent: `source/backends/aten/tensor.lisp:105-141`).  Two rewrites are installed:
+;;;; precedent: `source/backends/aten/tensor.lisp:105-141`).  Three rewrites are installed:
 ;;;;   1. MoveTensorNode immediately followed by an in-place {Add,Sub,Mul,Div}Node on the copy
 ;;;;      (`!add` = `!copy` + `A+=B`, `base-impl/arithmetic.lisp:150-152`) -> one wf2cu_ew_binary3 launch.
-;;;;   2. Scalar->MatNode feeding a (:broadcast ..) operand of an arithmetic node
-;;;;      (`fundamental.lisp:525-533`, `arithmetic.lisp:244-250`) -> wf2cu_ew_scalar with the host number
-;;;;      as a kernel argument (no 4-byte H2D, SURVEY §7 hard part e).
-;;;;   3. MatMulNode followed by the in-place AddNode of LinearLayer's `(!flexible bias)` operand
-;;;;      (`nn/regression.lisp:14-18`) -> one wf2cu_gemm_ex with the bias in the epilogue (the `!relu` after
-;;;;      it and the `!relu` backward mask take the same entry point: act = 1 / mask; the Python host,
-;;;;      cl-waffe2_b200/nn.py, exercises all three).
+;;;;   2. MatMulNode followed by the in-place AddNode of LinearLayer's `(!flexible bias)` operand
+;;;;      (`nn/regression.lisp:14-18`) -> one wf2cu_gemm_ex with the bias in the epilogue.
+;;;;   3. Im2ColNode + Permute-Node + the `->contiguous` MoveTensorNode of an unpadded `unfold`
+;;;;      (`nn/im2col.lisp:15-54`) -> one wf2cu_unfold.
+;;;; Two composites are offered as drop-in functions instead of pattern matches (they are plain functions in the
+;;;; reference, not nodes): `cuda-layer-norm` (the GPT-2 example's LayerNorm-Revisit) and `cuda-softmax` (`!softmax`,
+;;;; optionally with the `(!div w n)` in front of it), forward only.
+;;;; NOT rewritten here yet — bound in cffi.lisp and driven through the same C ABI by the Python host
+;;;; (cl-waffe2_b200/nn.py, conv.py), where they are tested: the `!relu` / relu-backward-mask forms of wf2cu_gemm_ex,
+;;;; wf2cu_sce_sum_forward/backward, wf2cu_fold, wf2cu_pool2d(_backward), wf2cu_ew_scalar for non-constant scalars
+;;;; (a constant scalar operand is a one-element CUDATensor made at build time and viewed with (:broadcast n): no
+;;;; per-step transfer; a ScalarTensor goes through Scalar->MatNode's 4-byte `(setf vref)`).
 ;;;; Everything else is left as generated; each remaining instruction is already one kernel.
 (in-package :cl-waffe2/backends.cuda)
 
@@ -171,6 +176,30 @@ what `(!flexible bias)` becomes inside `step-linear` (`nn/regression.lisp:14-18`
   "Drop-in for `LayerNorm-Revisit` on dense CUDATensors whose last axis is a multiple of 4 and <= 1024
 (the library answers UNSUPPORTED otherwise, which `defwf2` signals as `cuda-backend-error`)."
   (call (CUDALayerNormNode eps) (->contiguous x) g b (make-input (shape x) nil :dtype (dtype x) :order (order x))))
+
+;; ---- `!softmax` (`nn/activation.lisp:126-159`: five nodes and two disguised reductions) as ONE launch, optionally with the
+;; `(!div w n)` that precedes it in the GPT-2 example folded in (`examples/gpt-2/utils.lisp:236-242`: PRE-DIVISOR = n; 0 =
+;; none).  AXIS counts from the front like `!softmax :axis`.  Forward only, like CUDALayerNormNode.
+(define-op (CUDASoftmaxNode (self axis avoid-overflow pre-divisor)
+	    :slots ((axis :initform 1 :reader axis-of)
+		    (avoid-overflow :initform t :reader avoid-overflow-of)
+		    (pre-divisor :initform 0.0 :reader pre-divisor-of))
+	    :where (X[~] Out[~] -> Out[~])
+	    :forward ((self x out)
+		      (with-lowered-views ((xv x) (ov out))
+			(softmax-ex xv ov (axis-of self) (if (avoid-overflow-of self) 1 0)
+				    (coerce (pre-divisor-of self) 'single-float)))
+		      out)
+	    :backward ((self dout)
+		       (declare (ignore dout))
+		       (error "CUDASoftmaxNode: forward only; differentiate !softmax instead")))
+  (setf (slot-value self 'axis) axis
+	(slot-value self 'avoid-overflow) avoid-overflow
+	(slot-value self 'pre-divisor) pre-divisor))
+
+(defun cuda-softmax (x &key (axis 1) (avoid-overflow t) (pre-divisor 0.0))
+  "Drop-in for `(!softmax x :axis axis :avoid-overflow avoid-overflow)`; with PRE-DIVISOR n for `(!softmax (!div x n) ...)`."
+  (call (CUDASoftmaxNode axis avoid-overflow pre-divisor) x (make-input (shape x) nil :dtype (dtype x) :order (order x))))
 
 ;; ---- independent instructions on a side stream: (with-cuda-branch (1) <launches>) ... (branch-join 1)
 (defmacro with-cuda-branch ((b) &body body)

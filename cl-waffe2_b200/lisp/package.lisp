@@ -22,7 +22,8 @@
    #:cuda-sync
    #:cuda-comm-init
    #:cuda-allreduce-gradients
-   #:cuda-layer-norm))
+   #:cuda-layer-norm
+   #:cuda-softmax))
 (in-package :cl-waffe2/backends.cuda)
 
 (defparameter *cuda-available-p* nil
