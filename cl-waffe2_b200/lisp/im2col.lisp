@@ -42,7 +42,7 @@ with strides that leave the buffer (`cl-waffe2-simd/kernels/im2col.c:245-256`)."
 	    (unless (eql (order col) :column)
 	      (error "CUDATensor Col2ImNode: only :order :column is supported"))
 	    ;; the incoming gradient is a permuted view (Permute-Node backward); the kernel wants it dense
-	    (let ((col* (if (tensor-permuted-p col) (cuda-contiguous-copy col) col)))
+	    (let ((col* (if (cl-waffe2/base-impl::tensor-permuted-p col) (cuda-contiguous-copy col) col)))
 	      (with-unfold-geom (g self (shape output-to))
 		(col2im (device-vec-ptr (tensor-vec col*)) (tensor-initial-offset col*)
 			(device-vec-ptr (tensor-vec output-to)) (tensor-initial-offset output-to) g)))

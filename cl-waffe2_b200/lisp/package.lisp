@@ -15,6 +15,9 @@
 (defpackage :cl-waffe2/backends.cuda
   (:documentation "B200 (sm_100a) device backend: CUDATensor -> CFFI -> libwaffe2cuda.so")
   (:use :cl :cl-waffe2/vm.generic-tensor :cl-waffe2/vm.nodes :cl-waffe2/base-impl :cffi)
+  ;; cffi.lisp names each binding after its C entry point (wf2cu_fill -> `fill`, wf2cu_stream -> `stream`): these two
+  ;; would otherwise redefine symbols of the locked COMMON-LISP package
+  (:shadow #:fill #:stream)
   (:export
    #:CUDATensor
    #:*cuda-available-p*
