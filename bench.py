@@ -245,6 +245,47 @@ def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
                          "traffic": None, "traffic_at_N4096": ncu_traffic("gemm_tc_kernel_N4096")}}
 
 
+def cpu_sgemm_baseline(n=2048, reps=3):
+    """the reference's MatmulNode leaf is BLAS `sgemm_` (`source/backends/cpu/matrix-ops.lisp:58-79`); the stand-in
+    here is the OpenBLAS behind numpy (the reference pins no BLAS version).  Timed with all host threads and with one."""
+    rng = np.random.default_rng(5)
+    a = rng.uniform(-1, 1, size=(n, n)).astype(np.float32)
+    b = rng.uniform(-1, 1, size=(n, n)).astype(np.float32)
+
+    def timed():
+        a @ b
+        best = None
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            a @ b
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        return 2.0 * n ** 3 / best / 1e9
+    out = {"N": n, "kind": "OpenBLAS sgemm through numpy (stand-in for the reference's unpinned system BLAS)", "host_cores": os.cpu_count()}
+    out["gflops_all_threads"] = timed()
+    try:
+        from threadpoolctl import threadpool_limits
+        with threadpool_limits(limits=1):
+            out["gflops_1_thread"] = timed()
+    except Exception as e:                                  # threadpoolctl missing: report only the all-thread figure
+        out["gflops_1_thread"] = None
+        out["note"] = repr(e)
+    return out
+
+
+def gemm_numerics(wf, n=1024):
+    """max|C - C64| / max|C64| at N = n for the device path and for OpenBLAS fp32 beside it."""
+    rng = np.random.default_rng(9)
+    a = rng.uniform(-1, 1, size=(n, n)).astype(np.float32)
+    b = rng.uniform(-1, 1, size=(n, n)).astype(np.float32)
+    c64 = a.astype(np.float64) @ b.astype(np.float64)
+    ours = wf.ops.matmul(wf.from_numpy(a), wf.from_numpy(b)).to_numpy().astype(np.float64)
+    blas = (a @ b).astype(np.float64)
+    den = float(np.abs(c64).max())
+    return {"N": n, "ours_max_rel_err": float(np.abs(ours - c64).max()) / den,
+            "openblas_fp32_max_rel_err": float(np.abs(blas - c64).max()) / den, "tolerance": 1e-4}
+
+
 def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3):
     """C5: examples/gpt-2 GPT-2 small forward (hidden states, as `(call model prev)` returns them),
     random-init weights, fp32, B=8, N=1024, semantics as the example writes them.  The launch sequence
@@ -512,6 +553,13 @@ def run_ours(args):
     gemm = None
     if args.gemm and world == 1:
         gemm = gemm_sweep(wf)
+        for key, fn in (("numerics", lambda: gemm_numerics(wf)), ("cpu_baseline", cpu_sgemm_baseline)):
+            if key == "cpu_baseline" and (rank != 0 or args.no_cpu):
+                continue
+            try:                                             # side information: may never break the bench line
+                gemm[key] = fn()
+            except Exception as e:
+                gemm[key] = {"error": repr(e)}
 
     gpt2 = None
     if args.gpt2 and world == 1:
