@@ -322,7 +322,8 @@ def test_random_view_chains_match_oracle(wf):
         np.testing.assert_array_equal(lowered_offsets(g), want, err_msg=msg)
         return True
 
-    @hyp.settings(max_examples=300, deadline=None, suppress_health_check=list(hyp.HealthCheck))
+    @hyp.settings(max_examples=int(os.environ.get("WF2_HYP_EXAMPLES", "300")), deadline=None, derandomize="WF2_HYP_EXAMPLES" not in os.environ,
+                  suppress_health_check=list(hyp.HealthCheck), database=None)
     @hyp.given(st.data())
     def run(data):
         draw = data.draw
