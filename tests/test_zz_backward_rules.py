@@ -150,6 +150,49 @@ def test_scalar_first_dispatch(bw, L):
     np.testing.assert_array_equal(x.to_numpy(), xs)
 
 
+# ------------------------------------------------------------------ CPU: the reference's chain-rule tests
+def _sum_backward(B, dout_value, x):
+    """`!sum` is `out*[:broadcast] += x` (reduction.lisp:60-79), so its gradient is dout broadcast over x's shape."""
+    return B.arith_("mul", B.ones_like(x), float(dout_value))
+
+
+def test_chain_rule_goldens(bw, L):
+    """vm/generic-tensor/t/backward.lisp: chain-test3, 6, 7, 8, 9 and backward-being-not-destructed, replayed by applying the
+    node :backward compositions by hand in reverse order (the VM does the same walk)."""
+    B = OracleBackend(L)
+    ones = const(L, (15, 15), 1)
+    # chain-test3: (!div (!sum a) 2.0) -> grad a = 0.5 everywhere
+    s = L.sum_(ones, axis=True)
+    gs, _ = bw.arith_backward(B, "div", const(L, s.shape, 1), s, const(L, s.shape, 2))
+    assert (_sum_backward(B, gs.to_numpy().ravel()[0], ones).to_numpy() == 0.5).all()
+    # chain-test6: (!sum (!add (!sin a) b)) -> cos 1
+    a = const(L, (15, 15), 1)
+    g_add, _ = bw.arith_backward(B, "add", _sum_backward(B, 1.0, a), None, None)
+    np.testing.assert_allclose(bw.unary_backward(B, "sin", g_add, a).to_numpy(), math.cos(1), rtol=2e-6)
+    # chain-test7: (!sin (!sin a)) -> cos(sin 1) * cos 1
+    x1 = B.unary("sin", a)
+    g = bw.unary_backward(B, "sin", bw.unary_backward(B, "sin", const(L, (15, 15), 1), x1), a)
+    np.testing.assert_allclose(g.to_numpy(), math.cos(math.sin(1)) * math.cos(1), rtol=2e-6)
+    # chain-test8: (!sum (!add (!mul a b) c)), a = 3, b = 2, c = 1 -> 2, 3, 1
+    a3, b2, c1 = const(L, (3, 3), 3), const(L, (3, 3), 2), const(L, (3, 3), 1)
+    ab = bw.mul(B, a3, b2)
+    d_ab, d_c = bw.arith_backward(B, "add", _sum_backward(B, 1.0, ab), ab, c1)
+    d_a, d_b = bw.arith_backward(B, "mul", d_ab, a3, b2)
+    assert (d_a.to_numpy() == 2).all() and (d_b.to_numpy() == 3).all() and (d_c.to_numpy() == 1).all()
+    # chain-test9: prev = a*b + c ; (!sum (!add (!mul a1 prev) c1)), a1 = 2 -> a 4, b 6, c 2, a1 7, c1 1
+    a1, c11 = const(L, (3, 3), 2), const(L, (3, 3), 1)
+    prev = bw.add(B, ab, c1)
+    top = bw.mul(B, a1, prev)
+    d_top, d_c11 = bw.arith_backward(B, "add", _sum_backward(B, 1.0, top), top, c11)
+    d_a1, d_prev = bw.arith_backward(B, "mul", d_top, a1, prev)
+    d_ab2, d_c2 = bw.arith_backward(B, "add", d_prev, ab, c1)
+    d_a2, d_b2 = bw.arith_backward(B, "mul", d_ab2, a3, b2)
+    for got, want in [(d_a2, 4), (d_b2, 6), (d_c2, 2), (d_a1, 7), (d_c11, 1)]:
+        assert (got.to_numpy() == want).all(), want
+    # backward-being-not-destructed: parameters keep their values
+    assert (a3.to_numpy() == 3).all() and (b2.to_numpy() == 2).all() and (c1.to_numpy() == 1).all() and (a1.to_numpy() == 2).all()
+
+
 # ------------------------------------------------------------------ GPU: the same compositions on CUDATensor
 @pytest.mark.gpu
 @pytest.mark.parametrize("op", ["add", "sub", "mul", "div"])
