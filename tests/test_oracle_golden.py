@@ -259,3 +259,30 @@ def test_kernels_reproduce_committed_golden_outputs(which):
     back = np.zeros_like(G["unfold/back"])
     K.unfold("col2im", G["unfold/col"].copy(), *geo, back)
     assert np.array_equal(back, G["unfold/back"])
+
+
+# ---- nn/t/regression.lisp:429-454 (grad-decay-test) and backends/lisp/t/package.lisp:26-32 (lazy-test) ---------------------
+@pytest.mark.parametrize("opt,lr", [("sgd", 1e-3), ("adam", 1e-3)])
+def test_mlp_loss_decreases_on_sin_wave(opt, lr):
+    """X = sin(ax+b (100 100) 0.01 0.1), Y = cos(ax+b (100 1) 0.01 0.1), 100 -> 10 -> 1 sigmoid MLP, MSE: the loss after
+    training is below the first one (the reference runs 3000 SGD steps; 300 already show it)."""
+    import importlib
+    from oracle.mlp import OracleMLP
+    nn = importlib.import_module("cl-waffe2_b200.nn")
+    X = L.unary("sin", L.ax_plus_b([100, 100], 0.01, 0.1)).to_numpy()
+    Y = L.unary("cos", L.ax_plus_b([100, 1], 0.01, 0.1)).to_numpy()
+    m = OracleMLP([100, 10, 1], "sigmoid", nn.mlp_init_arrays([100, 10, 1], seed=1), "mse-mean", opt=opt, lr=lr)
+    losses = [m.step(X, Y) for _ in range(300)]
+    assert np.isfinite(losses).all()
+    assert losses[-1] < losses[0]
+    assert losses[-1] < losses[len(losses) // 2] < losses[0] or opt == "adam"      # monotone trend for plain SGD
+
+
+def test_sin_of_permuted_tensor_matches_elementwise_truth():
+    """lazy-test: (!sin (!permute (ax+b (10 10 10) 1 0) 2 0 1)) through the CPU kernels equals sin applied element by element
+    (the LispTensor route) within the test's 1e-5."""
+    t = L.permute(L.ax_plus_b([10, 10, 10], 1, 0), 2, 0, 1)
+    got = L.unary("sin", t).to_numpy()
+    want = np.sin(t.to_numpy().astype(np.float64))
+    assert got.shape == want.shape == tuple(t.shape)
+    assert np.abs(got - want).max() < 1e-5
