@@ -36,6 +36,16 @@ sys.path.insert(0, ROOT)
 METRIC = "fused_elementwise_reduce_hbm_gbps"
 UNIT = "GB/s"
 NSETS = 4
+NOMINAL_HBM_GBS = 8000.0          # north_star's "~8 TB/s" denominator, reported beside the measured one
+
+
+def workload_config(n: int, cases):
+    """`config` of the JSON line — byte-identical in both arms (the driver compares them)."""
+    nb = n * n * 4
+    return {"workload": f"c2_elementwise_reduce_sweep_{n}x{n}_f32", "cases": [c for c, _ in cases],
+            "bytes_per_step": sum(b for _, b in cases),
+            "l2": f"inputs larger than L2: every case streams 64 MiB tensors and the GPU arm rotates through {NSETS} buffer sets "
+                  f"({NSETS * 3 * nb >> 20} MiB > 2x the 126 MB L2); no flush kernel in the timed region"}
 
 
 # ------------------------------------------------------------------------------- sweep definition
@@ -205,11 +215,26 @@ def dist_env():
 
 
 
-def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
-    """C3: `!matmul` (N N)x(N N) fp32 through wf2cu_gemm (auto mode -> tcgen05 3xTF32).  flops = 2N^3
-    (algorithmic); the tensor pipe executes 3 TF32 passes, so pipe-level = 3x.  Peak: TF32 dense =
-    1/2 x the measured bf16 figure of MEASURED_PEAKS.json (no TF32 figure is driver-measured);
-    cuBLAS TF32 on this pool measured 715 TFLOP/s (profiles/r01_cublas_gemm_peaks.log)."""
+GEMM_PATHS = {0: "none", 1: "simt", 2: "simt_splitk", 3: "simt_skinny", 4: "tc_fused", 5: "tc_128x256", 6: "tc_256x256", 7: "tc_256x192", 8: "tc_raw"}
+
+
+def _gemm_rows_check(rng, A, B, got, ta, tb, nrows=64):
+    """max|C - C64| / max|C64| over `nrows` sampled rows of the output of the TIMED launches, and OpenBLAS fp32's own figure."""
+    N = A.shape[0]
+    rows = np.unique(np.concatenate([[0, N // 2, N - 1], rng.integers(0, N, size=nrows)]))
+    opA = (A.T if ta else A)[rows]
+    opB = B.T if tb else B
+    truth = opA.astype(np.float64) @ opB.astype(np.float64)
+    blas = (np.ascontiguousarray(opA) @ np.ascontiguousarray(opB)).astype(np.float64)
+    den = float(np.abs(truth).max())
+    return float(np.abs(got[rows].astype(np.float64) - truth).max()) / den, float(np.abs(blas - truth).max()) / den
+
+
+def gemm_sweep(wf, sizes=(256, 512, 1024, 2048, 4096, 8192), check=True):
+    """C3: `!matmul` (N N)x(N N) fp32 through wf2cu_gemm under AUTO dispatch (N = 256..8192 and all four `trans`
+    combos at N = 4096).  flops = 2N^3 (algorithmic); the tensor pipe executes 3 TF32 passes, so pipe-level = 3x.  Peak: TF32
+    dense = 1/2 x the measured bf16 figure of MEASURED_PEAKS.json (no TF32 figure is driver-measured); cuBLAS TF32 is measured
+    in the same run (`cublas_tf32_tflops`).  `err` is computed on the output buffer of the timed launches."""
     import ctypes as C
     lib = wf._lib.load()
     chk = wf._lib.check
@@ -218,31 +243,66 @@ def gemm_sweep(wf, sizes=(1024, 2048, 4096, 8192)):
     tf32_peak = bf16 / 2
     rng = np.random.default_rng(3)
     cases = []
-    for N in sizes:
-        A = wf.from_numpy(rng.uniform(-1, 1, size=(N, N)).astype(np.float32))
-        B = wf.from_numpy(rng.uniform(-1, 1, size=(N, N)).astype(np.float32))
+    plan = [(N, False, False) for N in sizes] + [(4096, True, False), (4096, False, True), (4096, True, True)]
+    for N, ta, tb in plan:
+        hA = rng.uniform(-1, 1, size=(N, N)).astype(np.float32)
+        hB = rng.uniform(-1, 1, size=(N, N)).astype(np.float32)
+        A, B = wf.from_numpy(hA), wf.from_numpy(hB)
         o = wf.make_tensor((N, N))
+        a_op = wf.ops.t(A) if ta else A
+        b_op = wf.ops.t(B) if tb else B
         for _ in range(3):
-            wf.ops.matmul(A, B, out=o)
-        reps = 10 if N <= 4096 else 5
+            wf.ops.matmul(a_op, b_op, out=o)
+        path = C.c_int(0)
+        chk(lib.wf2cu_gemm_last_path(C.byref(path)))
+        reps = 20 if N <= 2048 else (10 if N <= 4096 else 5)
         best = None
         for _ in range(2):
             chk(lib.wf2cu_timer_start())
             for _ in range(reps):
-                wf.ops.matmul(A, B, out=o)
+                wf.ops.matmul(a_op, b_op, out=o)
             ms = C.c_float()
             chk(lib.wf2cu_timer_stop(C.byref(ms)))
             best = ms.value / reps if best is None else min(best, ms.value / reps)
         tf = 2.0 * N ** 3 / (best * 1e-3) / 1e12
-        cases.append({"N": N, "ms": best, "tflops": tf, "frac_of_tf32_peak": tf / tf32_peak, "pipe_tflops": 3 * tf,
-                      "pipe_frac": 3 * tf / tf32_peak})
+        c = {"N": N, "trans": f"{'T' if ta else 'N'}{'T' if tb else 'N'}", "path": GEMM_PATHS.get(path.value, str(path.value)), "ms": best,
+             "tflops": tf, "frac_of_tf32_peak": tf / tf32_peak, "pipe_tflops": 3 * tf, "pipe_frac": 3 * tf / tf32_peak}
+        if check:
+            try:
+                c["err"], c["openblas_fp32_err"] = _gemm_rows_check(rng, hA, hB, o.to_numpy(), ta, tb)
+                c["err_ok"] = bool(c["err"] <= 1e-4)
+            except Exception as e:                              # side information: may never break the bench line
+                c["err"] = repr(e)
+        cases.append(c)
         del A, B, o
-    top = cases[-1]
-    return {"workload": "c3_matmul_NxN_f32 (split planes + tcgen05 3xTF32, all launches timed; N <= 1024 the one-launch fused kernel, N = 2048 128x256 tiles, N >= 4096 256x256 tiles)", "cases": cases,
-            "roofline": {"bound": "tensor", "kernel": "gemm_tc256_kernel (tcgen05.mma kind::tf32, 3 passes, 256x256 tiles)", "achieved": top["tflops"],
+    top = max((c for c in cases if c["trans"] == "NN"), key=lambda c: c["N"])
+    return {"workload": "c3_matmul_NxN_f32, auto dispatch, every launch of a MatmulNode timed (operand pre-passes included)", "cases": cases,
+            "tolerance": 1e-4,
+            "roofline": {"bound": "tensor", "kernel": top["path"], "achieved": top["tflops"],
                          "peak": tf32_peak, "unit": "TFLOP/s", "frac": top["frac_of_tf32_peak"], "pipe_frac": top["pipe_frac"],
                          "peak_source": "0.5 x MEASURED_PEAKS.json bf16_tflops (TF32 dense); of measured", "N": top["N"],
-                         "traffic": None, "traffic_at_N4096": ncu_traffic("gemm_tc_kernel_N4096")}}
+                         "traffic": ncu_traffic(f"gemm_N{top['N']}"), "traffic_at_N4096": ncu_traffic("gemm_N4096")}}
+
+
+def cublas_tf32_peak(n=8192, reps=5):
+    """cuBLAS TF32 at n^3 through torch (a library GEMM as the second denominator); measured after
+    every number of this repo's own kernels has been taken."""
+    import torch
+    torch.backends.cuda.matmul.allow_tf32 = True
+    a = torch.randn(n, n, device="cuda"); b = torch.randn(n, n, device="cuda")
+    for _ in range(2):
+        a @ b
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = None
+    for _ in range(3):
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record(); torch.cuda.synchronize()
+        t = e0.elapsed_time(e1) / reps
+        best = t if best is None else min(best, t)
+    return {"N": n, "ms": best, "tflops": 2.0 * n ** 3 / (best * 1e-3) / 1e12, "how": "torch.matmul fp32, allow_tf32=True (cuBLAS), best of 3 x 5"}
 
 
 def cpu_sgemm_baseline(n=2048, reps=3):
@@ -273,20 +333,7 @@ def cpu_sgemm_baseline(n=2048, reps=3):
     return out
 
 
-def gemm_numerics(wf, n=1024):
-    """max|C - C64| / max|C64| at N = n for the device path and for OpenBLAS fp32 beside it."""
-    rng = np.random.default_rng(9)
-    a = rng.uniform(-1, 1, size=(n, n)).astype(np.float32)
-    b = rng.uniform(-1, 1, size=(n, n)).astype(np.float32)
-    c64 = a.astype(np.float64) @ b.astype(np.float64)
-    ours = wf.ops.matmul(wf.from_numpy(a), wf.from_numpy(b)).to_numpy().astype(np.float64)
-    blas = (a @ b).astype(np.float64)
-    den = float(np.abs(c64).max())
-    return {"N": n, "ours_max_rel_err": float(np.abs(ours - c64).max()) / den,
-            "openblas_fp32_max_rel_err": float(np.abs(blas - c64).max()) / den, "tolerance": 1e-4}
-
-
-def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3):
+def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3, oracle_check=True):
     """C5: examples/gpt-2 GPT-2 small forward (hidden states, as `(call model prev)` returns them),
     random-init weights, fp32, B=8, N=1024, semantics as the example writes them.  The launch sequence
     runs under a StaticPool (the reference's static allocation) and is replayed as one CUDA graph."""
@@ -325,6 +372,19 @@ def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3):
         best = ms.value if best is None else min(best, ms.value)
     h = out.to_numpy()
     chk(lib.wf2cu_graph_destroy(ex))
+    check = None
+    if oracle_check:
+        # rows of the batch are independent (the heads-axis softmax couples heads, not rows): batch row 0 of the timed
+        # B = 8 forward against the numpy restatement of the example in fp64 on the host
+        try:
+            from oracle import gpt2 as O
+            t0 = time.perf_counter()
+            h64 = O.forward(np.asarray(ctx.to_numpy()[:1]), g.init_weights(cfg, 0), cfg, np.float64)
+            check = {"max_rel_err": float(np.abs(h[:1].astype(np.float64) - h64).max() / np.abs(h64).max()), "tolerance": 1e-3,
+                     "against": "oracle/gpt2.py fp64, batch row 0 of the timed forward", "host_seconds": time.perf_counter() - t0}
+            check["ok"] = bool(check["max_rel_err"] <= 1e-3)
+        except Exception as e:
+            check = {"error": repr(e)}
     # matmul flops of one forward: per layer qkv + attn-proj + fc + fc-proj, plus QK^T and PV
     E, L, H = cfg["n_emb"], cfg["n_layer"], cfg["n_head"]
     T = batch * seq
@@ -332,7 +392,8 @@ def gpt2_forward_bench(wf, batch=8, seq=1024, reps=3):
     return {"workload": f"gpt2_small_forward_b{batch}_n{seq}_f32 (hidden states, random-init weights)", "ms_per_forward": best,
             "tokens_per_s": T / (best * 1e-3), "launches_per_forward": int(l1.value - l0.value),
             "matmul_tflops": flops / (best * 1e-3) / 1e12, "pool_bytes": pool.nbytes(),
-            "finite": bool(np.isfinite(h).all()), "hidden_absmax": float(np.abs(h).max())}
+            "finite": bool(np.isfinite(h).all()), "hidden_absmax": float(np.abs(h).max()), "check": check,
+            "max_rel_err": check.get("max_rel_err") if check else None}
 
 # ------------------------------------------------------------------------------- reference arm
 def run_reference(args):
@@ -356,8 +417,8 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"c2_elementwise_reduce_sweep_{n}x{n}_f32", "cases": [c for c, _ in sw.cases],
-                   "bytes_per_step": sw.bytes_per_step()},
+        "config": workload_config(n, sw.cases),
+        "method": {"launch": "host threads, one reference kernel call per row / per flattened tensor", "parallelism": f"{threads} host threads"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": sw.kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -371,6 +432,133 @@ def stage(msg: str):
     """Progress marker on stderr (WF2_BENCH_TRACE=1): tells where a multi-rank run stopped."""
     if os.environ.get("WF2_BENCH_TRACE"):
         print(f"[bench rank {os.environ.get('RANK', '0')} t={time.time() % 1000:.1f}] {msg}", file=sys.stderr, flush=True)
+
+
+def fused_chain_cases(wf, n: int, peak: float, capture, reps: int = 20):
+    """`fused_chains`: the element-wise composites of SURVEY 8 a16 on (n n) fp32 — each ONE launch of a compiled chain kernel
+    (csrc/fused.cu) or of the fused optimizer kernel — with their algorithmic bytes, GB/s and fraction of the HBM peak.
+    sigmoid `nn/activation.lisp:43`; relu backward mask `:11-26`; MSE difference chain `nn/criterion.lisp:73-79`;
+    sin(sin(sin x)) `benchmarks/compose.lisp:21-26`; gelu `nn/activation.lisp:61-66`; SGD on views `optimizers/impls/sgd.lisp:20-26`;
+    Adam over a 16 Mi-element arena `optimizers/impls/adam.lisp:45-116`."""
+    import ctypes as C
+    lib = wf._lib.load()
+    chk = wf._lib.check
+    P = wf._lib
+    imm = wf.ops._imm
+    gt = P.P_CMPSEL | (P.CMP["gt"] << 8)
+    t = n * n * 4
+    rng = np.random.default_rng(21)
+    sets = []
+    for _ in range(NSETS):                                  # rotate: every launch reads HBM-cold data
+        sets.append([wf.from_numpy(rng.uniform(-1, 1, size=(n, n)).astype(np.float32)) for _ in range(3)])
+    progs = {
+        "sigmoid": (2 * t, lambda v: wf.ops.sigmoid(v[0], out=v[2])),
+        "gelu": (2 * t, lambda v: wf.ops.gelu(v[0], out=v[2])),
+        "sin_sin_sin": (2 * t, lambda v: wf.ops.fused([(P.P_LOAD, 0, 0, 0), (P.P_UNARY, 0, 0, P.UNARY["sin"]), (P.P_UNARY, 0, 0, P.UNARY["sin"]),
+                                                       (P.P_UNARY, 0, 0, P.UNARY["sin"]), (P.P_STORE, 0, 1, 0)], [v[0], v[2]])),
+        "relu_backward_mask": (3 * t, lambda v: wf.ops.fused([(P.P_LOAD, 0, 0, 0), (P.P_IMM, 1, 0, imm(0.0)), (gt, 1, 0, 1), (P.P_LOAD, 2, 1, 0),
+                                                              (P.P_MUL, 1, 2, 1), (P.P_STORE, 1, 2, 0)], [v[0], v[1], v[2]])),
+        "mse_diff": (3 * t, lambda v: wf.ops.fused([(P.P_LOAD, 0, 0, 0), (P.P_LOAD, 1, 1, 0), (P.P_SUB, 0, 0, 1), (P.P_MUL, 0, 0, 0),
+                                                    (P.P_STORE, 0, 2, 0)], [v[0], v[1], v[2]])),
+        "sgd_on_views": (3 * t, lambda v: wf.ops.fused([(P.P_LOAD, 0, 0, 0), (P.P_LOAD, 1, 1, 0), (P.P_IMM, 2, 0, imm(1e-3)), (P.P_MUL, 1, 1, 2),
+                                                        (P.P_SUB, 0, 0, 1), (P.P_STORE, 0, 0, 0)], [v[2], v[1]])),
+    }
+    out = {}
+    cursor = [0]
+    path = C.c_int(0)
+    for name, (nbytes, fn) in progs.items():
+        def many(fn=fn):
+            for _ in range(reps):
+                cursor[0] = (cursor[0] + 1) % NSETS
+                fn(sets[cursor[0]])
+        many()
+        chk(lib.wf2cu_fused_last_path(C.byref(path)))
+        g = capture(many)
+        chk(lib.wf2cu_graph_launch(g))
+        best = None
+        for _ in range(3):
+            chk(lib.wf2cu_timer_start())
+            chk(lib.wf2cu_graph_launch(g))
+            tm = C.c_float()
+            chk(lib.wf2cu_timer_stop(C.byref(tm)))
+            best = tm.value if best is None else min(best, tm.value)
+        chk(lib.wf2cu_graph_destroy(g))
+        gbps = nbytes / (best / reps * 1e-3) / 1e9
+        out[name] = {"ms": best / reps, "bytes": nbytes, "gbps": gbps, "frac": gbps / peak,
+                     "executor": {1: "interpreter", 2: "compiled"}.get(path.value, str(path.value))}
+    # Adam over a flat 16 Mi-element arena: reads p, g, m, v and writes p, m, v = 7 x 64 MiB
+    cnt = 16 * 1024 * 1024
+    arenas = []
+    for _ in range(2):
+        arenas.append([wf.from_numpy(rng.uniform(-1, 1, size=(cnt,)).astype(np.float32)) for _ in range(4)])
+    for ar in arenas:
+        ar[3] = wf.from_numpy(rng.uniform(0.1, 1, size=(cnt,)).astype(np.float32))     # v >= 0
+    k = [0]
+
+    def adam_many():
+        for _ in range(reps):
+            k[0] ^= 1
+            p_, g_, m_, v_ = arenas[k[0]]
+            chk(lib.wf2cu_adam_step(p_.vec.ptr, 0, g_.vec.ptr, 0, m_.vec.ptr, 0, v_.vec.ptr, 0, cnt, 1e-3, None, 0.9, 0.999, 1e-7, 1.0))
+    adam_many()
+    g = capture(adam_many)
+    chk(lib.wf2cu_graph_launch(g))
+    best = None
+    for _ in range(3):
+        chk(lib.wf2cu_timer_start())
+        chk(lib.wf2cu_graph_launch(g))
+        tm = C.c_float()
+        chk(lib.wf2cu_timer_stop(C.byref(tm)))
+        best = tm.value if best is None else min(best, tm.value)
+    chk(lib.wf2cu_graph_destroy(g))
+    nbytes = 7 * cnt * 4
+    gbps = nbytes / (best / reps * 1e-3) / 1e9
+    out["adam_16Mi_arena"] = {"ms": best / reps, "bytes": nbytes, "gbps": gbps, "frac": gbps / peak, "executor": "adam_kernel"}
+    return out
+
+
+def mlp_host_losses(world: int, per_gpu_batch: int, steps: int, seed: int = 0):
+    """CPU checker for the sharded step (bench.py alone may use oracle/): every shard's forward/backward with shared
+    parameters, gradients summed over shards x 1/world, one Adam step; the loss is the sum of the shards' `!sum` losses."""
+    import importlib as il
+    from oracle.mlp import OracleMLP
+    nn = il.import_module("cl-waffe2_b200.nn")
+    mb = il.import_module("cl-waffe2_b200.mlp_bench")
+    ref = OracleMLP(mb.DIMS, "relu", nn.mlp_init_arrays(mb.DIMS, seed=1234), "softmax-cross-entropy-sum", opt="adam", lr=1e-3)
+    shards = [mb.shard_data(r, per_gpu_batch, seed) for r in range(world)]
+    out = []
+    for _ in range(steps):
+        total, gW, gb = 0.0, None, None
+        for X, Y in shards:
+            loss, w, b = ref.forward_backward(X, Y)
+            total += loss
+            if gW is None:
+                gW, gb = w, b
+            else:
+                for a, c in zip(gW + gb, w + b):
+                    a.vec[:] = a.vec + c.vec
+        ref.apply(gW, gb, grad_scale=1.0 / world)
+        out.append(total)
+    return out
+
+
+def mlp_cpu_baseline(steps: int = 4) -> dict:
+    """The reference's own CPU path for the C4 step on the host cores: oracle/mlp.py (its C kernels driven by the restated loop
+    nest + OpenBLAS sgemm), batch 1024, a bounded sample.  Context: the reference publishes 3.111 s per epoch of MNIST for
+    this model (60 000 samples: 19.3 K samples/s), `Readme.md:140-148`."""
+    import importlib as il
+    from oracle.mlp import OracleMLP
+    nn = il.import_module("cl-waffe2_b200.nn")
+    mb = il.import_module("cl-waffe2_b200.mlp_bench")
+    X, Y = mb.shard_data(0, 1024, 0)
+    ref = OracleMLP(mb.DIMS, "relu", nn.mlp_init_arrays(mb.DIMS, seed=1234), "softmax-cross-entropy-sum", opt="adam", lr=1e-3)
+    ref.step(X, Y)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ref.step(X, Y)
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": 1024 / dt, "unit": "samples/s", "ms_per_step": dt * 1e3, "cores": os.cpu_count(), "kind": "reference",
+            "sample": f"{steps} Adam steps at batch 1024 after 1 warm-up: reference C kernels (1 thread) + OpenBLAS sgemm (all host threads)"}
 
 
 def run_ours(args):
@@ -411,6 +599,7 @@ def run_ours(args):
     sw = GpuSweep(wf, n)
     stage("sweep buffers uploaded")
     launches0 = C.c_int64()
+    warm = max(args.warmup, 3)                               # the timing rules ask for >= 3; what ran is printed as `warmup`
 
     def capture(fn):
         """Record fn()'s launches into a CUDA graph (the static iseq of a compiled model)."""
@@ -422,11 +611,11 @@ def run_ours(args):
 
     # ---- timed region: K steps, device time on the library stream.  One step (12 C-ABI calls) is
     # captured once into a CUDA graph and replayed, so the GPU is not waiting on the Python host.
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warm):
         sw.step()
     sw.cursor = 0
     step_graph = capture(sw.step)
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warm):
         chk(lib.wf2cu_graph_launch(step_graph))
     barrier()
     with ClockSampler(local_rank) as clocks:
@@ -483,28 +672,57 @@ def run_ours(args):
     peak, peak_src = measured_peaks()
     for c in per_case.values():
         c["frac"] = c["gbps"] / peak
-    dom = "add"   # ew_vec_kernel<2, add>: the largest share of the step's bytes (3 cases use it)
+    # the dominant kernel = the one with the largest share of the step's time: ew_vec_kernel<2, add> runs 2 of the 12
+    # launches (add, add_inplace); the limiting one and the whole-step aggregate are reported beside it
+    dom = "add"
+    lim = min(per_case, key=lambda k: per_case[k]["frac"])
+    agg = bytes_step / (ms_per_step * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "ew_vec_kernel<2,FBinary<ADD>> (case add)", "achieved": per_case[dom]["gbps"],
                 "peak": peak, "unit": "GB/s", "frac": per_case[dom]["gbps"] / peak, "peak_source": peak_src,
-                "traffic": ncu_traffic("ew_vec_kernel<2,FBinary<ADD>>"), "traffic_source": "profiles/ncu_traffic.json (ncu --set full capture, dram read+write per launch)",
-                "algorithmic_bytes_per_launch": per_case[dom]["bytes"]}
+                "traffic": ncu_traffic("ew_vec_kernel<2,FBinary<ADD>>"),
+                "traffic_source": "profiles/ncu_traffic.json (generated by scripts/ncu_traffic.py from the ncu --set full capture: dram read+write per launch)",
+                "algorithmic_bytes_per_launch": per_case[dom]["bytes"],
+                "aggregate_frac": agg / world / peak if world > 1 else agg / peak, "aggregate_gbps_per_gpu": agg,
+                "min_frac": per_case[lim]["frac"], "limiting_kernel": lim,
+                "frac_of_nominal_8tbs": per_case[dom]["gbps"] / NOMINAL_HBM_GBS, "aggregate_frac_of_nominal_8tbs": agg / NOMINAL_HBM_GBS,
+                "min_frac_of_nominal_8tbs": per_case[lim]["gbps"] / NOMINAL_HBM_GBS}
 
-    # ---- e2e: host buffers in, host results out, copies inside the timed region
-    hx = C.c_void_p(); hy = C.c_void_p(); hres = C.c_void_p()
+    fused_chains = None
+    if args.fused and world == 1:
+        stage("fused chains")
+        try:
+            fused_chains = fused_chain_cases(wf, n, peak, capture)
+        except Exception as e:
+            fused_chains = {"error": repr(e)}
+
+    # ---- e2e: host buffers in, EVERY result back in host memory, copies inside the timed region.
+    # Per step: x and y (2 x 64 MiB) up; the nine (n n) outputs (9 x 64 MiB) and the three reductions down.  Each case
+    # writes its own device buffer; its download is queued on side branch 2 as soon as the kernel is issued, the next step's
+    # upload runs on side branch 1 (PCIe is full duplex), and the step ends when both branches have joined.
     nb = n * n * 4
+    big = [c for c, _ in sw.cases if not c.startswith("sum_")]
+    hx = C.c_void_p(); hy = C.c_void_p(); hres = C.c_void_p(); hout = C.c_void_p()
     chk(lib.wf2cu_host_alloc(nb, C.byref(hx))); chk(lib.wf2cu_host_alloc(nb, C.byref(hy)))
-    d2h_bytes = 2 * n * 4 + 4
-    chk(lib.wf2cu_host_alloc(d2h_bytes, C.byref(hres)))
+    red_bytes = 2 * n * 4 + 4
+    chk(lib.wf2cu_host_alloc(red_bytes, C.byref(hres)))
+    chk(lib.wf2cu_host_alloc(len(big) * nb, C.byref(hout)))
     C.memmove(hx.value, sw.hx.ctypes.data, nb); C.memmove(hy.value, sw.hy.ctypes.data, nb)
+    e2e_out = {c: wf.make_tensor((n, n)) for c in big}
+    d2h_bytes = len(big) * nb + red_bytes
 
     def upload(s):
         chk(lib.wf2cu_h2d(s["x"].vec.ptr, 0, hx, nb))
         chk(lib.wf2cu_h2d(s["y"].vec.ptr, 0, hy, nb))
 
+    def download(dev, host_off, nbytes):
+        chk(lib.wf2cu_branch_begin(2))
+        try:
+            chk(lib.wf2cu_d2h_async(dev.vec.ptr, 0, hout.value + host_off if host_off >= 0 else hres.value - host_off - 1, nbytes))
+        finally:
+            chk(lib.wf2cu_branch_end(2))
+
     def e2e_run(steps):
-        """`steps` sweeps, each on inputs copied from pinned host memory inside the timed region.  The copy for
-        step i+1 goes to a side stream (wf2cu_branch_*) into the next buffer set while step i computes; step
-        0's copy is exposed.  Exactly `steps` uploads, `steps` sweeps and `steps` result read-backs."""
+        """`steps` sweeps; exactly `steps` uploads, `steps` sweeps and `steps` read-backs of every result."""
         cur = sw.sets[sw.cursor]
         upload(cur)
         for i in range(steps):
@@ -515,57 +733,60 @@ def run_ours(args):
                     upload(nxt)
                 finally:
                     chk(lib.wf2cu_branch_end(1))
-            for name, _ in sw.cases:
+            for j, name in enumerate(big):
+                s2 = dict(cur)
+                s2["out"] = e2e_out[name]                      # (add_inplace accumulates into its own buffer from step to step)
+                sw.run_case(name, s2)
+                download(e2e_out[name], j * nb, nb)
+            for name, key, off, nbytes in (("sum_axis1", "s1", 0, n * 4), ("sum_axis0", "s0", n * 4, n * 4), ("sum_all", "sa", 2 * n * 4, 4)):
                 sw.run_case(name, cur)
-            chk(lib.wf2cu_d2h(cur["s1"].vec.ptr, 0, hres.value, n * 4))
-            chk(lib.wf2cu_d2h(cur["s0"].vec.ptr, 0, hres.value + n * 4, n * 4))
-            chk(lib.wf2cu_d2h(cur["sa"].vec.ptr, 0, hres.value + 2 * n * 4, 4))
+                download(cur[key], -(off + 1), nbytes)
+            chk(lib.wf2cu_branch_join(2))
             if i + 1 < steps:
                 chk(lib.wf2cu_branch_join(1))
             sw.cursor = (sw.cursor + 1) % NSETS
             cur = nxt
 
-    e2e_run(3)
+    e2e_run(2)
     barrier()
-    e2e_steps = max(3, min(args.steps, 20))
+    e2e_steps = max(3, min(args.steps, 10))
     chk(lib.wf2cu_timer_start())
     e2e_run(e2e_steps)
     t = C.c_float()
     chk(lib.wf2cu_timer_stop(C.byref(t)))
     e2e_ms = max_over_ranks(float(t.value)) / e2e_steps
+    # what came back is what the device computed: the add result and the full sum, checked on the host copy
+    host_add = np.ctypeslib.as_array(C.cast(hout.value, C.POINTER(C.c_float)), shape=(n * n,))[:4096].copy()
+    host_sum = float(np.ctypeslib.as_array(C.cast(hres.value + 2 * n * 4, C.POINTER(C.c_float)), shape=(1,))[0])
+    e2e_ok = bool(np.array_equal(host_add, (sw.hx + sw.hy).ravel()[:4096]) and
+                  abs(host_sum - float(sw.hx.astype(np.float64).sum())) <= 1e-5 * float(np.abs(sw.hx).astype(np.float64).sum()))
     e2e = {"value": world * bytes_step / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_ms,
-           "h2d_bytes_per_step": 2 * nb, "d2h_bytes_per_step": d2h_bytes,
-           "api": "cl-waffe2_b200.ops (one libwaffe2cuda C-ABI call per node) + wf2cu_h2d/wf2cu_d2h from pinned host memory; "
-                  "the upload of step i+1 runs on a side stream (wf2cu_branch_*) under step i's kernels"}
+           "h2d_bytes_per_step": 2 * nb, "d2h_bytes_per_step": d2h_bytes, "steps": e2e_steps, "results_checked_on_host": e2e_ok,
+           "pcie_gbps_down": d2h_bytes / (e2e_ms * 1e-3) / 1e9,
+           "api": "cl-waffe2_b200.ops (one libwaffe2cuda C-ABI call per node) + wf2cu_h2d / wf2cu_d2h_async with pinned host memory: every "
+                  "result of the 12 cases is copied back (9 x 64 MiB + the three reductions); downloads queue on side branch 2 behind the "
+                  "kernel that produced them, the upload of step i+1 runs on side branch 1 (full duplex); PCIe-bound"}
+    for h in (hx, hy, hres, hout):
+        chk(lib.wf2cu_host_free(h))
+    e2e_out.clear()
 
     stage("e2e timed")
-    # ---- MLP training step (the sharded path)
-    mlp = None
-    if args.mlp:
-        try:
-            mlp_mod = importlib.import_module("cl-waffe2_b200.mlp_bench")
-            mlp = mlp_mod.run(wf, dist, rank, world, steps=args.mlp_steps, warmup=args.mlp_warmup, exchange=args.exchange)
-        except ModuleNotFoundError:
-            mlp = {"unavailable": "MLP training step not built yet"}
-
-    stage("mlp done")
     # ---- MatmulNode sweep (C3), single GPU only
     gemm = None
     if args.gemm and world == 1:
-        gemm = gemm_sweep(wf)
-        for key, fn in (("numerics", lambda: gemm_numerics(wf)), ("cpu_baseline", cpu_sgemm_baseline)):
-            if key == "cpu_baseline" and (rank != 0 or args.no_cpu):
-                continue
+        stage("gemm")
+        gemm = gemm_sweep(wf, check=not args.no_cpu)
+        if rank == 0 and not args.no_cpu:
             try:                                             # side information: may never break the bench line
-                gemm[key] = fn()
+                gemm["cpu_baseline"] = cpu_sgemm_baseline()
             except Exception as e:
-                gemm[key] = {"error": repr(e)}
+                gemm["cpu_baseline"] = {"error": repr(e)}
 
     gpt2 = None
     if args.gpt2 and world == 1:
         stage("gpt2")
         try:
-            gpt2 = gpt2_forward_bench(wf)
+            gpt2 = gpt2_forward_bench(wf, oracle_check=not args.no_cpu)
         except Exception as e:                       # reported, never silently dropped
             gpt2 = {"error": repr(e)}
 
@@ -576,6 +797,19 @@ def run_ours(args):
             cnn = importlib.import_module("cl-waffe2_b200.mlp_bench").run_cnn(wf)
         except Exception as e:
             cnn = {"error": repr(e)}
+
+    # ---- MLP training step (the sharded path)
+    mlp = mlp_detail = None
+    if args.mlp:
+        stage("mlp")
+        mlp_mod = importlib.import_module("cl-waffe2_b200.mlp_bench")
+        mlp, mlp_detail = mlp_mod.run(wf, dist, rank, world, steps=args.mlp_steps, warmup=args.mlp_warmup, exchange=args.exchange,
+                                      host_losses=None if args.no_cpu else mlp_host_losses,
+                                      cpu_fn=None if args.no_cpu else mlp_cpu_baseline)
+        for k in ("weak", "strong", "weak_nccl", "n1_same_run"):
+            if mlp_detail.get(k):
+                mlp_detail[k].pop("loss_first20", None)
+    stage("mlp done")
 
     # ---- CPU baseline (rank 0, N=1): the oracle on one host core, bounded sample
     cpu = None
@@ -594,19 +828,29 @@ def run_ours(args):
                          f"(reference default *num-cores*=1); host has {os.cpu_count()} cores",
                "ms_per_step": dt * 1e3}
 
+    # a library GEMM as the second tensor denominator: after every number of this repo's own kernels has been taken
+    if gemm is not None and args.cublas:
+        stage("cublas tf32")
+        try:
+            gemm["cublas_tf32"] = cublas_tf32_peak()
+            top = gemm["roofline"]
+            gemm["roofline"]["pipe_frac_of_cublas_tf32"] = top["achieved"] * 3 / gemm["cublas_tf32"]["tflops"]
+        except Exception as e:
+            gemm["cublas_tf32"] = {"error": repr(e)}
+
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
+            "warmup_requested": args.warmup,
             "ms_per_step": ms_per_step, "eager_ms_per_step": eager_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"c2_elementwise_reduce_sweep_{n}x{n}_f32", "cases": [c for c, _ in sw.cases],
-                       "bytes_per_step": bytes_step, "l2": f"inputs rotate through {NSETS} buffer sets "
-                       f"({NSETS * 3 * nb >> 20} MiB > 2x L2), no flush kernel in the timed region",
-                       "launch": "one step captured into a CUDA graph and replayed",
-                       "parallelism": "replicas only" if world > 1 else "single GPU"},
-            "roofline": roofline, "cases": per_case, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(), "mlp": mlp, "gemm": gemm, "gpt2": gpt2,
-            "cnn": cnn,
+            "config": workload_config(n, sw.cases),
+            "method": {"launch": "one step captured into a CUDA graph and replayed",
+                       "parallelism": "replicas only (the sharded path is the `mlp` object)" if world > 1 else "single GPU"},
+            "roofline": roofline, "cases": per_case, "fused_chains": fused_chains, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(launches1.value - launches0.value), "clocks": clocks.summary(),
+            "gemm": gemm, "gpt2": gpt2, "cnn": cnn, "mlp_detail": mlp_detail,
+            "mlp": mlp,                                       # compact and LAST: survives the driver's tail at every N
         }
         print(json.dumps(line))
     if dist is not None:
@@ -629,6 +873,8 @@ def main():
     ap.add_argument("--gemm", type=int, default=1)
     ap.add_argument("--gpt2", type=int, default=1)
     ap.add_argument("--cnn", type=int, default=1)
+    ap.add_argument("--fused", type=int, default=1, help="fused_chains block (compiled element-wise chains + Adam arena)")
+    ap.add_argument("--cublas", type=int, default=1, help="measure cuBLAS TF32 at 8192^3 through torch as a second GEMM denominator")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N>1 gradient exchange: p2p = fused peer-memory allreduce+Adam kernel, nccl = ncclAllReduce + Adam")
     ap.add_argument("--mlp-steps", type=int, default=200)

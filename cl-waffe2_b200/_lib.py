@@ -47,7 +47,7 @@ PROTOTYPES = {
     "wf2cu_set_stream": [vp], "wf2cu_launch_count": [C.POINTER(i64)],
     "wf2cu_malloc": [sz, C.POINTER(vp)], "wf2cu_retain": [vp], "wf2cu_release": [vp], "wf2cu_free": [vp],
     "wf2cu_memset0": [vp, sz, sz], "wf2cu_h2d": [vp, sz, vp, sz], "wf2cu_d2h": [vp, sz, vp, sz],
-    "wf2cu_d2d": [vp, sz, vp, sz, sz], "wf2cu_get_f32": [vp, i64, C.POINTER(f32)], "wf2cu_set_f32": [vp, i64, f32],
+    "wf2cu_d2h_async": [vp, sz, vp, sz], "wf2cu_d2d": [vp, sz, vp, sz, sz], "wf2cu_get_f32": [vp, i64, C.POINTER(f32)], "wf2cu_set_f32": [vp, i64, f32],
     "wf2cu_host_alloc": [sz, C.POINTER(vp)], "wf2cu_host_free": [vp], "wf2cu_mem_in_use": [C.POINTER(sz)],
     "wf2cu_timer_start": [], "wf2cu_timer_stop": [C.POINTER(f32)], "wf2cu_l2_flush": [],
     "wf2cu_graph_begin": [], "wf2cu_graph_end": [C.POINTER(vp)], "wf2cu_graph_launch": [vp],
@@ -56,10 +56,11 @@ PROTOTYPES = {
     "wf2cu_ew_binary": [i32, VP, VP], "wf2cu_ew_binary3": [i32, VP, VP, VP], "wf2cu_ew_scalar": [i32, VP, f32],
     "wf2cu_fill": [VP, f32], "wf2cu_ew_unary": [i32, VP, VP], "wf2cu_pow": [VP, VP, f32],
     "wf2cu_cmp": [i32, VP, VP, f32, VP, f32, f32], "wf2cu_fused": [C.POINTER(C.c_int32), i32, VP, i32],
+    "wf2cu_fused_set_mode": [i32], "wf2cu_fused_last_path": [C.POINTER(i32)], "wf2cu_fused_catalogue_size": [C.POINTER(i32)],
     "wf2cu_reduce_sum": [VP, VP, i32, f32], "wf2cu_softmax": [VP, VP, i32, i32], "wf2cu_softmax_ex": [VP, VP, i32, i32, f32],
     "wf2cu_reduce_maxmin": [i32, VP, VP], "wf2cu_argmaxmin": [i32, VP, VP],
     "wf2cu_gemm": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i64, i64, i64],
-    "wf2cu_gemm_set_mode": [i32],
+    "wf2cu_gemm_set_mode": [i32], "wf2cu_gemm_last_path": [C.POINTER(i32)],
     "wf2cu_gemm_ex": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i32, vp, i64, i64],
     "wf2cu_sce_sum_forward": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, f32],
     "wf2cu_sce_backward": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32],

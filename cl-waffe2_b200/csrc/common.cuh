@@ -29,6 +29,7 @@ struct State {
   std::atomic<int64_t> launches{0};
   std::atomic<size_t> bytes_in_use{0};
   int gemm_mode = 0;
+  int gemm_last_path = 0;        // WF2CU_GEMM_PATH_* of the last wf2cu_gemm / wf2cu_gemm_ex call (wf2cu_gemm_last_path)
   // side branches (wf2cu_branch_begin/end/join): independent work of a compiled step on its own stream
   cudaStream_t main_stream = nullptr;             // where launches return to after wf2cu_branch_end
   cudaStream_t side[kBranches] = {};

@@ -596,6 +596,12 @@ using namespace wf2;
 
 extern "C" {
 
+int wf2cu_gemm_last_path(int* out) {
+  WF2_CHECK(out, "wf2cu_gemm_last_path: null out");
+  *out = S().gemm_last_path;
+  return 0;
+}
+
 int wf2cu_gemm_set_mode(int mode) {
   WF2_CHECK(mode >= 0 && mode <= 6, "wf2cu_gemm_set_mode: mode %d not in 0..6", mode);
   S().gemm_mode = mode;
@@ -629,7 +635,7 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     // the K-sliced kernel whatever its flop count: on a tile-per-CTA kernel it is two tiles (604 us on 16 CTAs)
     const int r = sgemm_skinny_tn_try(g, batch);
     if (r < 0) return -r;
-    if (r == 1) return 0;
+    if (r == 1) { S().gemm_last_path = WF2CU_GEMM_PATH_SIMT_SKINNY; return 0; }
   }
   {
     const double flops = 2.0 * (double)m * (double)n * (double)k;
@@ -665,15 +671,16 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     int r = sgemm_skinny_nt_try(g, batch);
     if (r == 0) r = sgemm_skinny_tn_try(g, batch);
     if (r < 0) return -r;
-    if (r == 1) return 0;
+    if (r == 1) { S().gemm_last_path = WF2CU_GEMM_PATH_SIMT_SKINNY; return 0; }
   }
   {
     const int r = sgemm_small_try(g, batch);
     if (r < 0) return -r;
-    if (r == 1) return 0;
+    if (r == 1) { S().gemm_last_path = WF2CU_GEMM_PATH_SIMT_SPLITK; return 0; }
   }
   dim3 grid((unsigned)((n + BN - 1) / BN), (unsigned)((m + BM - 1) / BM), (unsigned)batch);
   sgemm_simt_kernel<<<grid, 256, 0, S().stream>>>(g);
+  S().gemm_last_path = WF2CU_GEMM_PATH_SIMT;
   return post_launch("wf2cu_gemm(simt)");
 }
 

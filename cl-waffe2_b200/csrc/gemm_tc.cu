@@ -1112,6 +1112,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, GEMM_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
     else           gemm_tc256_kernel<192, 3><<<grid, GEMM_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
     rc = post_launch(nb == 256 ? "wf2cu_gemm(tcgen05 256x256)" : "wf2cu_gemm(tcgen05 256x192)");
+    S().gemm_last_path = nb == 256 ? WF2CU_GEMM_PATH_TC_256X256 : WF2CU_GEMM_PATH_TC_256X192;
     return rc ? -rc : 1;
   }
   if ((rc = make_map(&mah, ah, (int)m, Kp, a_nb, TM))) return rc;
@@ -1131,6 +1132,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   const int grid = (int)(total < S().sm_count ? total : S().sm_count);
   gemm_tc_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, mc, t);
   rc = post_launch("wf2cu_gemm(tcgen05)");
+  S().gemm_last_path = WF2CU_GEMM_PATH_TC_128X256;
   return rc ? -rc : 1;
 }
 
@@ -1181,6 +1183,7 @@ int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const flo
   cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_fused_kernel, g);
   if (e != cudaSuccess) return -cuda_fail(e, "cudaLaunchKernelEx(gemm_tc_fused_kernel)", __FILE__, __LINE__);
   const int rc = post_launch("wf2cu_gemm(tcgen05 fused)");
+  S().gemm_last_path = WF2CU_GEMM_PATH_TC_FUSED;
   return rc ? -rc : 1;
 }
 

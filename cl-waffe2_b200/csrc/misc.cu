@@ -1,5 +1,5 @@
-// misc.cu — max/min/argmax rows, fused optimizer steps, the GPT-2 embedding gather and the
-// fused element-wise program interpreter.
+// misc.cu — max/min/argmax rows, fused optimizer steps and the GPT-2 embedding gather
+// (the fused element-wise chains live in fused.cu).
 #include "common.cuh"
 #include "math.cuh"
 
@@ -138,124 +138,6 @@ __global__ void __launch_bounds__(256) embedding_kernel(const float* __restrict_
   for (int64_t d = threadIdx.x; d < dim; d += 256) o[d] = __fadd_rn(e[d], w[d]);
 }
 
-// ------------------------------------------------------------------ fused program interpreter
-constexpr int kMaxInstr = 64;
-constexpr int kMaxRegs = 16;
-struct FusedArgs {
-  int n_instr;
-  int nviews;
-  int4 prog[kMaxInstr];
-  float* base[kMaxOperands];
-  int rank;
-  int64_t shape[kMaxRank];
-  int64_t stride[kMaxOperands][kMaxRank];
-  int64_t numel;
-  int vec;  // all views contiguous (stride 1 or 0 over a rank-1 plan) and 16-byte aligned
-};
-
-__device__ __forceinline__ float fused_eval(const int4 ins, const float* r) {
-  const int opc = ins.x & 0xff;
-  switch (opc) {
-    case WF2CU_P_IMM: return __int_as_float(ins.w);
-    case WF2CU_P_ADD: return __fadd_rn(r[ins.z], r[ins.w]);
-    case WF2CU_P_SUB: return __fsub_rn(r[ins.z], r[ins.w]);
-    case WF2CU_P_MUL: return __fmul_rn(r[ins.z], r[ins.w]);
-    case WF2CU_P_DIV: return __fdiv_rn(r[ins.z], r[ins.w]);
-    case WF2CU_P_UNARY: return unary_dispatch(ins.w, r[ins.z]);
-    case WF2CU_P_POW: return pow_ref(r[ins.z], r[ins.w]);
-    case WF2CU_P_CMPSEL: return cmp_dispatch(ins.x >> 8, r[ins.z], r[ins.w]) ? 1.0f : 0.0f;
-    case WF2CU_P_MOV: return r[ins.z];
-    default: return 0.f;
-  }
-}
-
-__global__ void __launch_bounds__(256) fused_kernel(const __grid_constant__ FusedArgs a) {
-  const int64_t gstride = (int64_t)gridDim.x * 256;
-  if (a.vec) {
-    const int64_t n4 = a.numel >> 2;
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += gstride) {
-      float r[4][kMaxRegs];
-      for (int k = 0; k < a.n_instr; ++k) {
-        const int4 ins = a.prog[k];
-        const int opc = ins.x & 0xff;
-        if (opc == WF2CU_P_LOAD) {
-          if (a.stride[ins.z][0] == 0) {
-            const float s = a.base[ins.z][0];
-            r[0][ins.y] = s; r[1][ins.y] = s; r[2][ins.y] = s; r[3][ins.y] = s;
-          } else {
-            const float4 v = reinterpret_cast<const float4*>(a.base[ins.z])[i];
-            r[0][ins.y] = v.x; r[1][ins.y] = v.y; r[2][ins.y] = v.z; r[3][ins.y] = v.w;
-          }
-        } else if (opc == WF2CU_P_STORE) {
-          reinterpret_cast<float4*>(a.base[ins.z])[i] = make_float4(r[0][ins.y], r[1][ins.y], r[2][ins.y], r[3][ins.y]);
-        } else {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) r[e][ins.y] = fused_eval(ins, r[e]);
-        }
-      }
-    }
-    return;
-  }
-  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < a.numel; idx += gstride) {
-    int64_t off[kMaxOperands];
-    for (int j = 0; j < a.nviews; ++j) off[j] = 0;
-    int64_t rem = idx;
-    for (int d = a.rank - 1; d >= 0; --d) {
-      const int64_t q = rem / a.shape[d], rr = rem - q * a.shape[d];
-      rem = q;
-      for (int j = 0; j < a.nviews; ++j) off[j] += rr * a.stride[j][d];
-    }
-    float r[kMaxRegs];
-    for (int k = 0; k < a.n_instr; ++k) {
-      const int4 ins = a.prog[k];
-      const int opc = ins.x & 0xff;
-      if (opc == WF2CU_P_LOAD) r[ins.y] = a.base[ins.z][off[ins.z]];
-      else if (opc == WF2CU_P_STORE) a.base[ins.z][off[ins.z]] = r[ins.y];
-      else r[ins.y] = fused_eval(ins, r);
-    }
-  }
-}
-
-// ---- compiled form of one well-known program: `!gelu` as cl-waffe2 writes it (nn/activation.lisp:61-66;
-// examples/gpt-2/utils.lisp:129-137): 0.5 x (1 + tanh(c2 (x + c1 x^3))), same operation order and roundings as
-// the interpreted program.  The interpreter keeps its register file in local memory (runtime-indexed) and
-// reached 0.94 TB/s on GPT-2's (8 1024 3072) activation; this kernel is HBM-bound.
-static const int kGeluOps[15][4] = {
-    {WF2CU_P_LOAD, 0, 0, 0},  {WF2CU_P_MUL, 1, 0, 0},  {WF2CU_P_MUL, 1, 1, 0},  {WF2CU_P_IMM, 2, 0, -1}, {WF2CU_P_MUL, 1, 1, 2},
-    {WF2CU_P_ADD, 1, 0, 1},   {WF2CU_P_IMM, 2, 0, -1}, {WF2CU_P_MUL, 1, 2, 1},  {WF2CU_P_UNARY, 1, 1, WF2CU_TANH}, {WF2CU_P_IMM, 2, 0, -1},
-    {WF2CU_P_ADD, 1, 2, 1},   {WF2CU_P_IMM, 2, 0, -1}, {WF2CU_P_MUL, 2, 2, 0},  {WF2CU_P_MUL, 1, 2, 1},  {WF2CU_P_STORE, 1, 1, 0}};
-
-static bool match_gelu(const int32_t* program, int n_instr, float imm[4]) {
-  if (n_instr != 15) return false;
-  int ni = 0;
-  for (int k = 0; k < 15; ++k) {
-    const int32_t* q = program + 4 * k;
-    if (q[0] != kGeluOps[k][0] || q[1] != kGeluOps[k][1] || q[2] != kGeluOps[k][2]) return false;
-    if (kGeluOps[k][0] == WF2CU_P_IMM) { memcpy(&imm[ni++], &q[3], 4); continue; }
-    if (kGeluOps[k][0] == WF2CU_P_LOAD || kGeluOps[k][0] == WF2CU_P_STORE) continue;
-    if (q[3] != kGeluOps[k][3]) return false;
-  }
-  return ni == 4;
-}
-
-__device__ __forceinline__ float gelu_one(float x, float c1, float c2, float one, float half) {
-  float t = __fmul_rn(__fmul_rn(x, x), x);
-  t = __fadd_rn(x, __fmul_rn(t, c1));
-  t = Unary<WF2CU_TANH>::apply(__fmul_rn(c2, t));
-  t = __fadd_rn(one, t);
-  return __fmul_rn(__fmul_rn(half, x), t);
-}
-
-__global__ void __launch_bounds__(256) gelu_vec_kernel(const float4* x, float4* out, int64_t n4,   // may alias (in-place gelu)
-                                                       float c1, float c2, float one, float half) {
-  const int64_t stride = (int64_t)gridDim.x * 256;
-  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
-    const float4 v = x[i];
-    out[i] = make_float4(gelu_one(v.x, c1, c2, one, half), gelu_one(v.y, c1, c2, one, half),
-                         gelu_one(v.z, c1, c2, one, half), gelu_one(v.w, c1, c2, one, half));
-  }
-}
-
 }  // namespace wf2
 
 using namespace wf2;
@@ -304,69 +186,6 @@ int wf2cu_embedding_gather(const void* ctx, int64_t batch, int64_t seq, const vo
   embedding_kernel<<<(unsigned)(batch * seq), 256, 0, S().stream>>>((const float*)ctx, seq, (const float*)wte,
                                                                    (const float*)wpe, dim, (float*)out);
   return post_launch("wf2cu_embedding_gather");
-}
-
-int wf2cu_fused(const int32_t* program, int n_instr, const wf2cu_view* views, int nviews) {
-  WF2_REQUIRE_INIT();
-  WF2_CHECK(program && views, "wf2cu_fused: null argument");
-  WF2_CHECK(n_instr >= 1 && n_instr <= kMaxInstr, "wf2cu_fused: %d instructions (max %d)", n_instr, kMaxInstr);
-  WF2_CHECK(nviews >= 1 && nviews <= kMaxOperands, "wf2cu_fused: %d views (max %d)", nviews, kMaxOperands);
-  const wf2cu_view* vp[kMaxOperands];
-  for (int j = 0; j < nviews; ++j) vp[j] = &views[j];
-  Plan p;
-  int rc = build_plan(vp, nviews, &p, "wf2cu_fused");
-  if (rc) return rc;
-  if (p.numel == 0) return 0;
-  FusedArgs a;
-  memset(&a, 0, sizeof(a));
-  a.n_instr = n_instr; a.nviews = nviews;
-  bool stored[kMaxOperands] = {false};
-  for (int k = 0; k < n_instr; ++k) {
-    const int32_t* q = program + 4 * k;
-    const int opc = q[0] & 0xff;
-    WF2_CHECK(opc >= WF2CU_P_LOAD && opc <= WF2CU_P_MOV, "wf2cu_fused: bad opcode %d at %d", opc, k);
-    WF2_CHECK(q[1] >= 0 && q[1] < kMaxRegs, "wf2cu_fused: bad dst register at %d", k);
-    if (opc == WF2CU_P_LOAD || opc == WF2CU_P_STORE) {
-      WF2_CHECK(q[2] >= 0 && q[2] < nviews, "wf2cu_fused: bad view index at %d", k);
-      if (opc == WF2CU_P_STORE) stored[q[2]] = true;
-    } else if (opc != WF2CU_P_IMM) {
-      WF2_CHECK(q[2] >= 0 && q[2] < kMaxRegs, "wf2cu_fused: bad source register at %d", k);
-      if (opc != WF2CU_P_UNARY && opc != WF2CU_P_MOV)
-        WF2_CHECK(q[3] >= 0 && q[3] < kMaxRegs, "wf2cu_fused: bad source register at %d", k);
-    }
-    a.prog[k] = make_int4(q[0], q[1], q[2], q[3]);
-  }
-  bool vec = (p.rank == 1) && (p.numel % 4 == 0);
-  for (int j = 0; j < nviews; ++j) {
-    a.base[j] = fptr(&views[j]);
-    for (int d = 0; d < p.rank; ++d) {
-      a.stride[j][d] = p.stride[j][d];
-      if (stored[j] && p.stride[j][d] == 0 && p.shape[d] > 1)
-        return set_error(WF2CU_ERR_INVALID, "wf2cu_fused: stored view %d has a broadcast axis", j);
-    }
-    const int64_t s0 = p.stride[j][0];
-    if (!(s0 == 1 || s0 == 0)) vec = false;
-    if (s0 == 1 && (reinterpret_cast<uintptr_t>(a.base[j]) & 15)) vec = false;
-  }
-  a.rank = p.rank;
-  for (int d = 0; d < p.rank; ++d) a.shape[d] = p.shape[d];
-  a.numel = p.numel;
-  a.vec = vec ? 1 : 0;
-  int64_t work = vec ? p.numel / 4 : p.numel;
-  int64_t grid = (work + 255) / 256;
-  const int64_t cap = (int64_t)S().sm_count * 8;
-  if (grid > cap) grid = cap;
-  float imm[4];
-  if (vec && nviews == 2 && p.stride[0][0] == 1 && p.stride[1][0] == 1 && match_gelu(program, n_instr, imm)) {
-    int64_t g = (work + 255) / 256;
-    const int64_t gcap = (int64_t)S().sm_count * 32;
-    if (g > gcap) g = gcap;
-    gelu_vec_kernel<<<(unsigned)g, 256, 0, S().stream>>>(reinterpret_cast<const float4*>(a.base[0]), reinterpret_cast<float4*>(a.base[1]),
-                                                         work, imm[0], imm[1], imm[2], imm[3]);
-    return post_launch("wf2cu_fused(gelu)");
-  }
-  fused_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(a);
-  return post_launch("wf2cu_fused");
 }
 
 }  // extern "C"

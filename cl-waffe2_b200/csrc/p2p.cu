@@ -22,11 +22,17 @@
 namespace wf2 {
 
 constexpr int kMaxPeers = 8;
-constexpr unsigned long long kSpinLimitNs = 2000000000ull;   // 2 s: a lost peer must not hang the GPU
+constexpr unsigned long long kSpinLimitNs = 10000000000ull;  // 10 s: a lost peer must not hang the GPU, ordinary host skew must not trip it
 
+// A timeout is STICKY and FATAL for the attachment: the rank that gives up sets its own flag (device word local[2] and a
+// mapped pinned host word the host polls without a sync) and writes `abort` into every peer's signal page; a rank that
+// sees `abort` (while spinning or at kernel entry) does the same.  From then on every rank's kernel returns at entry without
+// touching flags, gradients or parameters, so no replica is updated from a half-arrived exchange and no peer reads an
+// arena its owner has moved on from; the host raises on the next step (nn.CompiledStep.step polls wf2cu_p2p_status).
 struct SignalPage {                 // lives in each rank's device memory, written by its peers
   uint32_t ready[16];               // ready[r] = epoch for which rank r's gradients are complete
   uint32_t done[16];                // done[r]  = epoch for which rank r has finished reading my arena
+  uint32_t abort;                   // != 0: some rank timed out; the attachment is dead
 };
 
 struct P2PState {
@@ -37,7 +43,9 @@ struct P2PState {
   SignalPage* peer_signal[kMaxPeers] = {};
   bool opened_grad[kMaxPeers] = {}, opened_signal[kMaxPeers] = {};
   SignalPage* my_signal = nullptr;
-  uint32_t* local = nullptr;                // [0] epoch, [1] ticket, [2] timeout flag
+  uint32_t* local = nullptr;                // [0] epoch, [1] ticket, [2] timeout flag (sticky)
+  uint32_t* host_flag = nullptr;            // mapped pinned host word, written by the kernel on a timeout (host polls it, no sync)
+  uint32_t* host_flag_dev = nullptr;        // its device address
 };
 static P2PState g_p2p;
 
@@ -51,6 +59,7 @@ struct P2PArgs {
   float* params[kMaxPeers];                 // every replica's parameter arena (params[rank] == param)
   SignalPage* signals[kMaxPeers];
   uint32_t* local;
+  uint32_t* host_flag;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -66,14 +75,22 @@ __device__ __forceinline__ unsigned long long now_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-// wait until *p has reached epoch e (wrap-safe); false on timeout
-__device__ __forceinline__ bool wait_epoch(const uint32_t* p, uint32_t e) {
+// wait until *p has reached epoch e (wrap-safe); false on timeout or when a peer has declared the attachment dead
+__device__ __forceinline__ bool wait_epoch(const uint32_t* p, uint32_t e, const uint32_t* abort_word) {
   const unsigned long long t0 = now_ns();
+  uint32_t spins = 0;
   while ((int32_t)(ld_acquire_sys(p) - e) < 0) {
+    if ((++spins & 63u) == 0 && ld_acquire_sys(abort_word) != 0) return false;
     if (now_ns() - t0 > kSpinLimitNs) return false;
     __nanosleep(64);
   }
   return true;
+}
+// this rank gives up: sticky local flag, the host's word, and `abort` in every peer's page (and its own)
+__device__ __forceinline__ void declare_dead(const P2PArgs& a) {
+  a.local[2] = 1;
+  st_release_sys(a.host_flag, 1u);
+  for (int r = 0; r < a.world; ++r) st_release_sys(&a.signals[r]->abort, 1u);
 }
 __device__ __forceinline__ float4 ld_peer(const float4* p) {
   float4 v;   // L1 no-allocate: every line is read once, and a stale line must never be served next step
@@ -91,18 +108,28 @@ __device__ __forceinline__ float adam_one(float gi, float& m, float& v, float p,
 
 __global__ void __launch_bounds__(256) allreduce_adam_kernel(const __grid_constant__ P2PArgs a) {
   __shared__ uint32_t epoch_s;
-  __shared__ int ok_s;
+  __shared__ int alive_s, ready_s;
   __shared__ bool last_s;
-  if (threadIdx.x == 0) { epoch_s = a.local[0] + 1; ok_s = 1; }
+  if (threadIdx.x == 0) {
+    epoch_s = a.local[0] + 1;
+    // a dead attachment stays dead: no flags, no loads from peers, no parameter stores
+    alive_s = (a.local[2] == 0 && ld_acquire_sys(&a.signals[a.rank]->abort) == 0) ? 1 : 0;
+    ready_s = 1;
+  }
   __syncthreads();
+  if (!alive_s) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) declare_dead(a);
+    return;
+  }
   const uint32_t e = epoch_s;
   // ---- 1. gradients complete everywhere?  (the kernel follows this rank's backward in stream order)
   if (blockIdx.x == 0 && threadIdx.x < a.world) st_release_sys(&a.signals[threadIdx.x]->ready[a.rank], e);
   if (threadIdx.x < a.world)
-    if (!wait_epoch(&a.signals[a.rank]->ready[threadIdx.x], e)) { ok_s = 0; a.local[2] = 1; }
+    if (!wait_epoch(&a.signals[a.rank]->ready[threadIdx.x], e, &a.signals[a.rank]->abort)) { ready_s = 0; declare_dead(a); }
   __syncthreads();
+  if (!ready_s) return;              // no update, no ticket, no done flag, the epoch does not advance: every later launch returns at entry
   // ---- 2. my shard: sum over ranks in rank order, x 1/world, Adam, parameters out to every replica
-  if (ok_s) {
+  {
     const float lr_t = a.lr_dev ? *a.lr_dev : a.lr_t;
     const float omb1 = __fsub_rn(1.0f, a.b1), omb2 = __fsub_rn(1.0f, a.b2);
     const int64_t n4 = (a.n + 3) >> 2;
@@ -148,10 +175,13 @@ __global__ void __launch_bounds__(256) allreduce_adam_kernel(const __grid_consta
   if (!last_s) return;
   __threadfence_system();            // ... and all CTAs' stores before the done flags below
   if (threadIdx.x < a.world) st_release_sys(&a.signals[threadIdx.x]->done[a.rank], e);
-  if (threadIdx.x < a.world)
-    if (!wait_epoch(&a.signals[a.rank]->done[threadIdx.x], e)) a.local[2] = 1;
+  __shared__ int done_ok_s;
+  if (threadIdx.x == 0) done_ok_s = 1;
   __syncthreads();
-  if (threadIdx.x == 0) { a.local[1] = 0; a.local[0] = e; }
+  if (threadIdx.x < a.world)
+    if (!wait_epoch(&a.signals[a.rank]->done[threadIdx.x], e, &a.signals[a.rank]->abort)) { done_ok_s = 0; declare_dead(a); }
+  __syncthreads();
+  if (threadIdx.x == 0) { a.local[1] = 0; if (done_ok_s) a.local[0] = e; }
 }
 
 static void p2p_close() {
@@ -191,6 +221,9 @@ int wf2cu_p2p_signal_export(void* handle64) {
     WF2_CUDA(cudaMemset(p.my_signal, 0, 4096));
     WF2_CUDA(cudaMalloc(&p.local, 256));
     WF2_CUDA(cudaMemset(p.local, 0, 256));
+    WF2_CUDA(cudaHostAlloc((void**)&p.host_flag, 64, cudaHostAllocMapped));
+    *p.host_flag = 0;
+    WF2_CUDA(cudaHostGetDevicePointer((void**)&p.host_flag_dev, p.host_flag, 0));
   }
   cudaIpcMemHandle_t h;
   WF2_CUDA(cudaIpcGetMemHandle(&h, p.my_signal));
@@ -206,9 +239,9 @@ int wf2cu_p2p_attach(int rank, int world, void* local_grad_alloc, void* local_pa
   P2PState& p = g_p2p;
   if (p.world) return set_error(WF2CU_ERR_COMM, "wf2cu_p2p_attach: already attached (call wf2cu_p2p_detach)");
   if (!p.my_signal) return set_error(WF2CU_ERR_COMM, "wf2cu_p2p_attach: call wf2cu_p2p_signal_export first");
-  // a fresh attachment starts at epoch 0 on every rank
-  WF2_CUDA(cudaMemset(p.my_signal, 0, 4096));
-  WF2_CUDA(cudaMemset(p.local, 0, 256));
+  // The signal page and the epoch were zeroed when the page was created and by wf2cu_p2p_detach — NOT here: a faster peer
+  // that has finished its own attach may already have posted ready[peer] = 1 into this page, and a memset now would erase it
+  // (the first step would then end in a timeout).  Contract: a host barrier across ranks before wf2cu_p2p_detach.
   for (int r = 0; r < world; ++r) {
     if (r == rank) { p.peer_grad_base[r] = local_grad_alloc; p.peer_param_base[r] = local_param_alloc; p.peer_signal[r] = p.my_signal; continue; }
     cudaIpcMemHandle_t h;
@@ -252,6 +285,7 @@ int wf2cu_p2p_allreduce_adam_step(void* param, int64_t p_off, int64_t g_off, voi
   }
   if (a.params[p.rank] != a.param) return set_error(WF2CU_ERR_INVALID, "wf2cu_p2p_allreduce_adam_step: param is not the arena given to wf2cu_p2p_attach");
   a.local = p.local;
+  a.host_flag = p.host_flag_dev;
   const int64_t n4 = (n + 3) >> 2;
   const int64_t per = (n4 + p.world - 1) / p.world;
   int64_t grid = (per + 255) / 256;
@@ -265,11 +299,9 @@ int wf2cu_p2p_status(int* timed_out) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(timed_out, "wf2cu_p2p_status: null out");
   *timed_out = 0;
-  if (!g_p2p.local) return 0;
-  uint32_t flag = 0;
-  WF2_CUDA(cudaStreamSynchronize(S().stream));
-  WF2_CUDA(cudaMemcpy(&flag, g_p2p.local + 2, 4, cudaMemcpyDeviceToHost));
-  *timed_out = (int)flag;
+  if (!g_p2p.host_flag) return 0;
+  // no sync: the kernel writes this mapped pinned word with a system-scope release store when it gives up
+  *timed_out = (int)*(volatile uint32_t*)g_p2p.host_flag;
   return 0;
 }
 
@@ -277,6 +309,10 @@ int wf2cu_p2p_detach(void) {
   if (g_p2p.world) {
     cudaStreamSynchronize(S().stream);
     p2p_close();
+    // every rank's kernels have finished (the caller's barrier): a fresh attachment starts at epoch 0 with clean flags
+    if (g_p2p.my_signal) cudaMemset(g_p2p.my_signal, 0, 4096);
+    if (g_p2p.local) cudaMemset(g_p2p.local, 0, 256);
+    if (g_p2p.host_flag) *g_p2p.host_flag = 0;
   }
   return 0;
 }

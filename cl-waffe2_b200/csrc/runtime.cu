@@ -5,6 +5,7 @@
 #include <stdarg.h>
 #include <mutex>
 #include <unordered_map>
+#include <vector>
 #include "common.cuh"
 
 namespace wf2 {
@@ -29,12 +30,25 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
   return WF2CU_ERR_CUDA;
 }
 
+static std::vector<void*>& retired_scratch() {
+  static std::vector<void*> v;
+  return v;
+}
+
 int ensure_scratch(size_t bytes) {
   State& s = S();
   bytes = (bytes + 255) & ~size_t(255);
   if (s.scratch_bytes / kBranches >= bytes) return 0;
-  // Growing while a graph is being captured is not allowed; callers size for the worst case up front.
-  if (s.scratch) WF2_CUDA(cudaFree(s.scratch));
+  // A captured CUDA graph has scratch_base() pointers baked into its reduce / split-K / SCE kernel arguments: the old
+  // buffer is retired (kept alive until shutdown), never freed, and growing inside a capture is refused — run the same
+  // shapes once before wf2cu_graph_begin (every host path here does: the first step of a CompiledStep is eager).
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (s.stream) cudaStreamIsCapturing(s.stream, &cs);
+  if (cs != cudaStreamCaptureStatusNone)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "reduction scratch must grow to %zu bytes per branch while a CUDA graph is being captured; "
+                     "run the same shapes once before wf2cu_graph_begin", bytes);
+  if (s.scratch) retired_scratch().push_back(s.scratch);
+  s.scratch = nullptr; s.scratch_bytes = 0;
   size_t want = bytes * kBranches < (size_t(8) << 20) ? (size_t(8) << 20) : bytes * kBranches;
   WF2_CUDA(cudaMalloc(&s.scratch, want));
   s.scratch_bytes = want;
@@ -179,6 +193,8 @@ int wf2cu_shutdown(void) {
   }
   gemm_tc_release();
   if (s.scratch) cudaFree(s.scratch);
+  for (void* p : retired_scratch()) cudaFree(p);
+  retired_scratch().clear();
   if (s.counters) cudaFree(s.counters);
   if (s.l2flush) cudaFree(s.l2flush);
   s.scratch = nullptr; s.scratch_bytes = 0; s.counters = nullptr; s.l2flush = nullptr; s.l2flush_bytes = 0;
@@ -298,6 +314,13 @@ int wf2cu_d2h(const void* dev, size_t off, void* host, size_t bytes) {
   WF2_CHECK(dev && (host || bytes == 0), "wf2cu_d2h: null pointer");
   if (bytes) WF2_CUDA(cudaMemcpyAsync(host, (const char*)dev + off, bytes, cudaMemcpyDeviceToHost, S().stream));
   WF2_CUDA(cudaStreamSynchronize(S().stream));
+  return 0;
+}
+
+int wf2cu_d2h_async(const void* dev, size_t off, void* host, size_t bytes) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(dev && (host || bytes == 0), "wf2cu_d2h_async: null pointer");
+  if (bytes) WF2_CUDA(cudaMemcpyAsync(host, (const char*)dev + off, bytes, cudaMemcpyDeviceToHost, S().stream));
   return 0;
 }
 

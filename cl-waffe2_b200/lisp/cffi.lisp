@@ -60,6 +60,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 memset0 ((dev :pointer) (offset-bytes :size) (bytes :size)))
 (defwf2 h2d ((dev :pointer) (offset-bytes :size) (host :pointer) (bytes :size)))
 (defwf2 d2h ((dev :pointer) (offset-bytes :size) (host :pointer) (bytes :size)))
+(defwf2 d2h-async ((dev :pointer) (offset-bytes :size) (host :pointer) (bytes :size)))
 (defwf2 d2d ((dst :pointer) (dst-off :size) (src :pointer) (src-off :size) (bytes :size)))
 (defwf2 get-f32 ((dev :pointer) (index :int64) (out :pointer)))
 (defwf2 set-f32 ((dev :pointer) (index :int64) (value :float)))
@@ -81,6 +82,9 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 pow ((src :pointer) (dst :pointer) (n :float)))
 (defwf2 cmp ((op :int) (x :pointer) (y :pointer) (scal :float) (dst :pointer) (then :float) (else :float)))
 (defwf2 fused ((program :pointer) (n-instr :int) (views :pointer) (nviews :int)))
+(defwf2 fused-set-mode ((mode :int)))
+(defwf2 fused-last-path ((out :pointer)))
+(defwf2 fused-catalogue-size ((out :pointer)))
 ;; reductions / composites
 (defwf2 reduce-sum ((x :pointer) (out :pointer) (accumulate :int) (divisor :float)))
 (defwf2 softmax ((x :pointer) (out :pointer) (axis :int) (avoid-overflow :int)))
@@ -106,6 +110,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 sce-backward ((z :pointer) (z-off :int64) (labels :pointer) (l-off :int64) (dy :pointer) (dy-off :int64)
 		      (dx :pointer) (dx-off :int64) (rows :int64) (cols :int64) (accumulate :int)))
 (defwf2 gemm-set-mode ((mode :int)))
+(defwf2 gemm-last-path ((out :pointer)))
 ;; optimizers
 (defwf2 sgd-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64) (n :int64) (lr :float)))
 (defwf2 adam-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64)

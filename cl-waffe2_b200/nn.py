@@ -538,6 +538,7 @@ def p2p_detach() -> None:
 
 
 def p2p_timed_out() -> bool:
+    """The exchange kernel's sticky give-up flag: a mapped pinned host word, read without a device sync."""
     f = C.c_int(0)
     _lib.check(_lib.load().wf2cu_p2p_status(C.byref(f)))
     return bool(f.value)
@@ -641,6 +642,10 @@ class CompiledStep:
                 self.graph = ex
             _lib.check(lib.wf2cu_graph_launch(self.graph))
         self._runs += 1
+        if self.world > 1 and self.exchange == "p2p" and p2p_timed_out():
+            # sticky and fatal (csrc/p2p.cu): a peer never arrived, every rank's exchange kernel now returns at entry
+            raise RuntimeError("CompiledStep: the peer-memory gradient exchange timed out waiting for a rank; the replicas were "
+                               "not updated from that step on — rebuild the process group and restore from a checkpoint")
 
     def close(self):
         """Destroy the captured graph (must happen before the communicator it references goes away)."""

@@ -100,6 +100,10 @@ int  wf2cu_free(void* dev);                  /* == release           */
 int  wf2cu_memset0(void* dev, size_t offset_bytes, size_t bytes);
 int  wf2cu_h2d(void* dev, size_t offset_bytes, const void* host, size_t bytes);
 int  wf2cu_d2h(const void* dev, size_t offset_bytes, void* host, size_t bytes);   /* syncs */
+/* enqueue only, on the current (branch) stream: `host` must be pinned (wf2cu_host_alloc) and may be read after wf2cu_sync,
+ * wf2cu_timer_stop or a wf2cu_d2h on a stream that has joined the copy's branch.  Bulk results of a step leave the device this
+ * way while the next step's kernels run (the reference's results are already in host memory, `array-converter.lisp:154-218`). */
+int  wf2cu_d2h_async(const void* dev, size_t offset_bytes, void* host, size_t bytes);
 int  wf2cu_d2d(void* dst, size_t dst_off, const void* src, size_t src_off, size_t bytes);
 int  wf2cu_get_f32(const void* dev, int64_t index, float* out);                    /* vref, syncs */
 int  wf2cu_set_f32(void* dev, int64_t index, float value);                         /* (setf vref) */
@@ -162,6 +166,14 @@ enum {
   WF2CU_P_MOV         /* r[dst] = r[a]                             */
 };
 int  wf2cu_fused(const int32_t* program, int n_instr, const wf2cu_view* views, int nviews);
+/* Executors of wf2cu_fused.  The programs the host fusion passes emit (sigmoid, relu and its backward, gelu, the MSE and
+ * softmax-cross-entropy chains, SGD on views, sin(sin(sin x)) of `benchmarks/compose.lisp:21-26`) are compiled kernels
+ * (path 2: straight-line code, HBM-bound); anything else, and strided or misaligned views, runs on the per-element
+ * interpreter (path 1).  Both apply the same operations in the same order: results are bit-identical.
+ * set_mode(1) forces the interpreter (used by the parity tests); last_path: 0 none yet, 1 interpreter, 2 compiled. */
+int  wf2cu_fused_set_mode(int mode);
+int  wf2cu_fused_last_path(int* out);
+int  wf2cu_fused_catalogue_size(int* out);
 
 /* ===================== reductions / composites ===================== */
 /* out <- [out +] sum(x) over the axes where out has stride 0 or extent 1 vs x; the fused form of
@@ -197,6 +209,20 @@ int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
  * 5 / 6 = force tcgen05 3xTF32 on the persistent 256x256 / 256x192-tile kernel.  Forced modes return WF2CU_ERR_UNSUPPORTED
  * for shapes their kernel does not take. */
 int  wf2cu_gemm_set_mode(int mode);
+/* Which kernel the last wf2cu_gemm / wf2cu_gemm_ex call launched (the parity tests assert that the benchmarked shapes
+ * really run on the kernel whose throughput is quoted). */
+enum {
+  WF2CU_GEMM_PATH_NONE = 0,
+  WF2CU_GEMM_PATH_SIMT = 1,          /* fp32 FMA tile kernel                                   */
+  WF2CU_GEMM_PATH_SIMT_SPLITK = 2,   /* fp32 FMA, K over a cluster                             */
+  WF2CU_GEMM_PATH_SIMT_SKINNY = 3,   /* fp32 FMA, Conv2D's tall / long-K shapes                */
+  WF2CU_GEMM_PATH_TC_FUSED = 4,      /* tcgen05 3xTF32, one launch, split in registers         */
+  WF2CU_GEMM_PATH_TC_128X256 = 5,    /* tcgen05 3xTF32, hi/lo planes + persistent 128x256 tiles */
+  WF2CU_GEMM_PATH_TC_256X256 = 6,    /* ... 256x256 tiles                                       */
+  WF2CU_GEMM_PATH_TC_256X192 = 7,    /* ... 256x192 tiles                                       */
+  WF2CU_GEMM_PATH_TC_RAW = 8         /* tcgen05 3xTF32, raw fp32 tiles by TMA, lo planes made on the SM (no pre-pass) */
+};
+int  wf2cu_gemm_last_path(int* out);
 /* MatmulNode with the node that follows it folded into the epilogue (what the backend's
  * `on-finalizing-compiling` pass emits for LinearLayer, `nn/regression.lisp:14-18`, and for the
  * `!relu` that follows / precedes it, `nn/activation.lisp:11-26`):
@@ -301,8 +327,12 @@ int  wf2cu_comm_destroy(void);
  *      1/world, applies Adam (same formula as wf2cu_adam_step) with its m/v shard and stores the new
  *      parameters into every replica; then waits until every rank has written its shard, so replicas
  *      stay bit-identical and the gradient arena can be reused by the next backward.
- * A peer that never arrives makes the kernel give up after 2 s and raises the flag wf2cu_p2p_status
- * reports (the GPU is never left spinning).  g_off, p_off, m_off, v_off: element offsets, multiples of 4. */
+ * A peer that never arrives makes the kernel give up after 10 s (the GPU is never left spinning).  Giving up is sticky and
+ * fatal for the attachment: the rank raises its flag (wf2cu_p2p_status: a mapped pinned host word, read without a sync),
+ * tells every peer, and from then on every rank's step kernel returns at entry without touching gradients or parameters.
+ * wf2cu_p2p_detach resets flags and epochs: the host must pass a barrier across ranks before calling it (every rank's
+ * kernels finished), and need not synchronise before the first step of a new attachment.
+ * g_off, p_off, m_off, v_off: element offsets, multiples of 4. */
 int  wf2cu_p2p_export(void* dev_alloc, void* handle64);
 int  wf2cu_p2p_signal_export(void* handle64);
 int  wf2cu_p2p_attach(int rank, int world, void* local_grad_alloc, void* local_param_alloc,
