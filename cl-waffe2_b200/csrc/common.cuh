@@ -72,6 +72,33 @@ void* scratch_base();                        // the current branch's region (val
 unsigned int* counters_base();               // the current branch's kCountersPerBranch tickets
 void gemm_tc_release();   // gemm_tc.cu: frees the hi/lo plane workspaces
 
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------------
+// Back-to-back kernels of a compiled instruction sequence are serialised by the stream (or by the edges of the captured
+// graph): kernel N+1 is launched only when the last CTA of kernel N has retired, so every boundary costs a launch
+// latency plus the ramp of the new grid — 1-2 us against 12-30 us kernels.  A kernel launched through launch_pdl may
+// start its CTAs while its predecessor drains; it calls pdl_prologue() before its first global memory access, which
+// (1) lets ITS successor do the same and (2) blocks until the predecessor grid has completed and its writes are
+// visible.  Without the launch attribute both instructions are no-ops, so the same kernel works either way.
+// WF2CU_PDL=0 turns the attribute off (A/B measurements).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+#endif
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 inline float* fptr(const wf2cu_view* v) { return reinterpret_cast<float*>(v->base) + v->offset; }
 
 // ---- iteration-space plan shared by all strided kernels -------------------------------

@@ -79,6 +79,7 @@ template <int NIN> struct GenArgs {
 // ---------------------------------------------------------------- vec kernel
 template <int NIN, class F>
 __global__ void __launch_bounds__(kThreads) ew_vec_kernel(const F f, const __grid_constant__ VecArgs<NIN> a) {
+  pdl_prologue();
   // n4 < 2^31 is guaranteed by the dispatcher: all index math below is 32-bit
   const uint32_t base = blockIdx.x * (uint32_t)(kThreads * kUnroll) + threadIdx.x;
   const uint32_t n4 = (uint32_t)a.n4;
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(kThreads) ew_vec_kernel(const F f, const __gri
 // ---------------------------------------------------------------- generic strided kernel
 template <int NIN, class F>
 __global__ void __launch_bounds__(kThreads) ew_gen_kernel(const F f, const __grid_constant__ GenArgs<NIN> a) {
+  pdl_prologue();
   const int64_t gstride = (int64_t)gridDim.x * kThreads;
   for (int64_t idx = (int64_t)blockIdx.x * kThreads + threadIdx.x; idx < a.numel; idx += gstride) {
     int64_t rem = idx, o_out = 0;
@@ -181,6 +183,7 @@ template <int NIN> struct TrArgs {
 template <int NIN, class F>
 __global__ void __launch_bounds__(256) ew_tr_kernel(const F f, const __grid_constant__ TrArgs<NIN> a) {
   __shared__ float tile[NIN > 0 ? NIN : 1][32][33];
+  pdl_prologue();
   uint32_t bid = blockIdx.x;
   const uint32_t ti = bid % a.tilesI; bid /= a.tilesI;
   const uint32_t tj = bid % a.tilesJ; bid /= a.tilesJ;
@@ -233,6 +236,7 @@ __global__ void __launch_bounds__(256) ew_tr_kernel(const F f, const __grid_cons
 template <int NIN, class F>
 __global__ void __launch_bounds__(256) ew_tr4_kernel(const F f, const __grid_constant__ TrArgs<NIN> a) {
   __shared__ float tile[NIN > 0 ? NIN : 1][64][65];   // [i][j], pitch 65: conflict-light both ways
+  pdl_prologue();
   uint32_t bid = blockIdx.x;
   const uint32_t ti = bid % a.tilesI; bid /= a.tilesI;
   const uint32_t tj = bid % a.tilesJ; bid /= a.tilesJ;
@@ -366,7 +370,7 @@ int launch_ew(const F& f, const wf2cu_view* out, const wf2cu_view* const* ins, c
     a.n4 = p.numel / 4;
     const int64_t per_block = kThreads * kUnroll;
     const int64_t grid = (a.n4 + per_block - 1) / per_block;
-    ew_vec_kernel<NIN, F><<<(unsigned)grid, kThreads, 0, s.stream>>>(f, a);
+    WF2_CUDA(launch_pdl(ew_vec_kernel<NIN, F>, dim3((unsigned)grid), dim3(kThreads), 0, s.stream, f, a));
     return post_launch(who);
   }
   // ---- transposed-operand path?
@@ -415,8 +419,8 @@ int launch_ew(const F& f, const wf2cu_view* out, const wf2cu_view* const* ins, c
       a.tilesJ = (uint32_t)((a.J + tile - 1) / tile);
       const int64_t grid = (int64_t)a.tilesI * a.tilesJ * nbatch_total;
       if (nb <= 3 && grid < (int64_t(1) << 31)) {
-        if (v4) ew_tr4_kernel<NIN, F><<<(unsigned)grid, 256, 0, s.stream>>>(f, a);
-        else ew_tr_kernel<NIN, F><<<(unsigned)grid, 256, 0, s.stream>>>(f, a);
+        if (v4) WF2_CUDA(launch_pdl(ew_tr4_kernel<NIN, F>, dim3((unsigned)grid), dim3(256), 0, s.stream, f, a));
+        else WF2_CUDA(launch_pdl(ew_tr_kernel<NIN, F>, dim3((unsigned)grid), dim3(256), 0, s.stream, f, a));
         return post_launch(who);
       }
     }
@@ -436,7 +440,7 @@ int launch_ew(const F& f, const wf2cu_view* out, const wf2cu_view* const* ins, c
   int64_t grid = (p.numel + kThreads - 1) / kThreads;
   const int64_t cap = (int64_t)s.sm_count * 32;
   if (grid > cap) grid = cap;
-  ew_gen_kernel<NIN, F><<<(unsigned)grid, kThreads, 0, s.stream>>>(f, a);
+  WF2_CUDA(launch_pdl(ew_gen_kernel<NIN, F>, dim3((unsigned)grid), dim3(kThreads), 0, s.stream, f, a));
   return post_launch(who);
 }
 

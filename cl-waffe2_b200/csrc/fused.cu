@@ -56,6 +56,7 @@ __device__ __forceinline__ float fused_eval(const int4 ins, const float* r) {
 }
 
 __global__ void __launch_bounds__(256) fused_kernel(const __grid_constant__ FusedArgs a) {
+  pdl_prologue();
   const int64_t gstride = (int64_t)gridDim.x * 256;
   if (a.vec) {
     const int64_t n4 = a.numel >> 2;
@@ -225,6 +226,7 @@ struct CatStep {
 // Views may alias (in-place programs): every element is read before it is written, by the same thread.
 template <class P, int V>
 __global__ void __launch_bounds__(256) fused_cat_kernel(const __grid_constant__ CatArgs a) {
+  pdl_prologue();
   const uint32_t first = blockIdx.x * (uint32_t)(256 * V) + threadIdx.x;
   uint32_t idx[V];
   bool ok[V];
@@ -259,7 +261,7 @@ static int cat_launch(const CatArgs& a) {
   constexpr int V = P::nviews >= 4 ? 2 : 4;      // <= 12 128-bit loads in flight per thread
   const uint32_t per = 256 * V;
   const uint32_t grid = (a.n4 + per - 1) / per;
-  fused_cat_kernel<P, V><<<grid, 256, 0, S().stream>>>(a);
+  WF2_CUDA(launch_pdl(fused_cat_kernel<P, V>, dim3(grid), dim3(256), 0, S().stream, a));
   return post_launch(P::name());
 }
 
@@ -367,7 +369,7 @@ int wf2cu_fused(const int32_t* program, int n_instr, const wf2cu_view* views, in
   int64_t grid = (work + 255) / 256;
   const int64_t cap = (int64_t)S().sm_count * 8;
   if (grid > cap) grid = cap;
-  fused_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(a);
+  WF2_CUDA(launch_pdl(fused_kernel, dim3((unsigned)grid), dim3(256), 0, S().stream, a));
   g_fused_last_path = 1;
   return post_launch("wf2cu_fused");
 }

@@ -239,6 +239,7 @@ __global__ void __launch_bounds__(256) reduce_rows_tile_kernel(const __grid_cons
   constexpr int TPR = 256 / RPC;
   constexpr int WPR = TPR / 32;                 // warps per row
   __shared__ float smem[8];
+  pdl_prologue();
   const int sub = threadIdx.x / TPR;            // row slot inside the CTA
   const int t = threadIdx.x % TPR;
   const uint32_t row_id = blockIdx.x * RPC + sub;
@@ -315,6 +316,7 @@ __global__ void __launch_bounds__(kFlatThreads) reduce_flat_bulk_kernel(const __
   __shared__ float red[kFlatThreads / 32];
   __shared__ bool is_last;
   constexpr int T = kFlatThreads;
+  pdl_prologue();
   const int64_t nchunks = (a.n * 4) / kFlatChunk;
   const char* base = reinterpret_cast<const char*>(a.src);
   if (threadIdx.x == 0) {
@@ -603,6 +605,7 @@ reduce_cols_cluster_kernel(const __grid_constant__ ColArgs a, const Fin fin) {
   constexpr int LX = 16, LY = 16, U = 4;
   __shared__ float4 sm[LY][LX];
   __shared__ float4 res[LX];
+  pdl_prologue();
   cg::cluster_group cluster = cg::this_cluster();
   const int tx = threadIdx.x % LX, ty = threadIdx.x / LX;
   const int64_t b = blockIdx.z;
@@ -762,7 +765,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
       rc = ensure_scratch((size_t)grid * sizeof(float));
       if (rc) return rc;
       FlatArgs f{sptr, dptr, (float*)scratch_base(), counters_base(), a.cols};
-      kfn<<<(unsigned)grid, kFlatThreads, kFlatStages * kFlatChunk, s.stream>>>(f, fin);
+      WF2_CUDA(launch_pdl(kfn, dim3((unsigned)grid), dim3(kFlatThreads), kFlatStages * kFlatChunk, s.stream, f, fin));
       return post_launch(who);
     }
     if (rows < (int64_t(1) << 31)) {
@@ -771,13 +774,13 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
         const int64_t v1 = a.cols >> 2;
         a.chunks = 1; a.chunk_len = a.cols;
         if (v1 <= 256) {
-          reduce_rows_tile_kernel<M, 8><<<(unsigned)((rows + 7) / 8), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+          WF2_CUDA(launch_pdl(reduce_rows_tile_kernel<M, 8>, dim3((unsigned)((rows + 7) / 8)), dim3(256), 0, s.stream, a, fin, (uint32_t)rows));
         } else if (v1 <= 512) {
-          reduce_rows_tile_kernel<M, 4><<<(unsigned)((rows + 3) / 4), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+          WF2_CUDA(launch_pdl(reduce_rows_tile_kernel<M, 4>, dim3((unsigned)((rows + 3) / 4)), dim3(256), 0, s.stream, a, fin, (uint32_t)rows));
         } else if (v1 <= 1024) {
-          reduce_rows_tile_kernel<M, 2><<<(unsigned)((rows + 1) / 2), 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+          WF2_CUDA(launch_pdl(reduce_rows_tile_kernel<M, 2>, dim3((unsigned)((rows + 1) / 2)), dim3(256), 0, s.stream, a, fin, (uint32_t)rows));
         } else {
-          reduce_rows_tile_kernel<M, 1><<<(unsigned)rows, 256, 0, s.stream>>>(a, fin, (uint32_t)rows);
+          WF2_CUDA(launch_pdl(reduce_rows_tile_kernel<M, 1>, dim3((unsigned)rows), dim3(256), 0, s.stream, a, fin, (uint32_t)rows));
         }
         return post_launch(who);
       }
@@ -829,7 +832,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
         a.splits = kColsClusterSize;
         a.rows_per_split = (a.R + kColsClusterSize - 1) / kColsClusterSize;
         dim3 grid((unsigned)strips, kColsClusterSize, (unsigned)a.B);
-        reduce_cols_cluster_kernel<M><<<grid, 256, 0, s.stream>>>(a, fin);
+        WF2_CUDA(launch_pdl(reduce_cols_cluster_kernel<M>, grid, dim3(256), 0, s.stream, a, fin));
         return post_launch(who);
       }
     }

@@ -3,6 +3,7 @@
 // (`source/backends/lisp/tensor.lisp:12-28`, `source/vm/allocation.lisp:71-171`): storage is
 // zero-initialised, shared by aliasing, and released through `tensor-finalizer`.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -13,6 +14,12 @@ namespace wf2 {
 State& S() {
   static State s;
   return s;
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("WF2CU_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on != 0;
 }
 
 static thread_local char g_err[1024] = "";

@@ -59,6 +59,7 @@ __device__ __forceinline__ void decode_row(const SmRowArgs& a, uint32_t row, int
 template <int THREADS, int VPT>
 __global__ void __launch_bounds__(THREADS) softmax_row_block_kernel(const __grid_constant__ SmRowArgs a) {
   __shared__ float smem[THREADS / 32];
+  pdl_prologue();
   int64_t xo, oo;
   decode_row(a, blockIdx.x, xo, oo);
   const float4* xp = reinterpret_cast<const float4*>(a.x + xo);
@@ -248,6 +249,7 @@ __global__ void __launch_bounds__(256) softmax_lane_kernel(const __grid_constant
 // kernel above = 2.1 TB/s).  The host passes the lane decode with the innermost extent / 4 and stride 4.
 template <int RCACHE>
 __global__ void __launch_bounds__(256) softmax_lane_vec_kernel(const __grid_constant__ SmLaneArgs a) {
+  pdl_prologue();
   const int64_t gstride = (int64_t)gridDim.x * 256;
   for (int64_t l = (int64_t)blockIdx.x * 256 + threadIdx.x; l < a.nlanes; l += gstride) {
     int64_t rem = l, xo = 0, oo = 0;
@@ -442,15 +444,15 @@ extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int 
         return post_launch("wf2cu_softmax(row,warp)");
       }
       if (vec && R <= 1024) {
-        softmax_row_block_kernel<128, 2><<<(unsigned)rows, 128, 0, s.stream>>>(a);
+        WF2_CUDA(launch_pdl(softmax_row_block_kernel<128, 2>, dim3((unsigned)rows), dim3(128), 0, s.stream, a));
         return post_launch("wf2cu_softmax(row,block128)");
       }
       if (vec && R <= 4096) {
-        softmax_row_block_kernel<128, 8><<<(unsigned)rows, 128, 0, s.stream>>>(a);
+        WF2_CUDA(launch_pdl(softmax_row_block_kernel<128, 8>, dim3((unsigned)rows), dim3(128), 0, s.stream, a));
         return post_launch("wf2cu_softmax(row,block128x8)");
       }
       if (vec && R <= 16384) {
-        softmax_row_block_kernel<512, 8><<<(unsigned)rows, 512, 0, s.stream>>>(a);
+        WF2_CUDA(launch_pdl(softmax_row_block_kernel<512, 8>, dim3((unsigned)rows), dim3(512), 0, s.stream, a));
         return post_launch("wf2cu_softmax(row,block512)");
       }
       softmax_row_stream_kernel<<<(unsigned)rows, 512, 0, s.stream>>>(a, e);
@@ -487,9 +489,9 @@ extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int 
       int64_t g4 = (v.nlanes + 255) / 256;
       const int64_t cap4 = (int64_t)s.sm_count * 16;
       if (g4 > cap4) g4 = cap4;
-      if (R <= 8) softmax_lane_vec_kernel<8><<<(unsigned)g4, 256, 0, s.stream>>>(v);
-      else if (R <= 12) softmax_lane_vec_kernel<12><<<(unsigned)g4, 256, 0, s.stream>>>(v);
-      else softmax_lane_vec_kernel<16><<<(unsigned)g4, 256, 0, s.stream>>>(v);
+      if (R <= 8) WF2_CUDA(launch_pdl(softmax_lane_vec_kernel<8>, dim3((unsigned)g4), dim3(256), 0, s.stream, v));
+      else if (R <= 12) WF2_CUDA(launch_pdl(softmax_lane_vec_kernel<12>, dim3((unsigned)g4), dim3(256), 0, s.stream, v));
+      else WF2_CUDA(launch_pdl(softmax_lane_vec_kernel<16>, dim3((unsigned)g4), dim3(256), 0, s.stream, v));
       return post_launch("wf2cu_softmax(lane,vec4)");
     }
   }
@@ -513,6 +515,7 @@ struct LnArgs { const float* x; const float* g; const float* b; float* out; int6
 
 template <int V>   // float4 per lane: cols <= 128 * V
 __global__ void __launch_bounds__(256) layernorm_kernel(const __grid_constant__ LnArgs a) {
+  pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= a.rows) return;
@@ -569,9 +572,9 @@ extern "C" int wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int6
   const int64_t grid = (rows + 7) / 8;
   WF2_CHECK(grid < (int64_t(1) << 31), "wf2cu_layernorm: too many rows");
   cudaStream_t st = S().stream;
-  if (cols <= 256) layernorm_kernel<2><<<(unsigned)grid, 256, 0, st>>>(a);
-  else if (cols <= 512) layernorm_kernel<4><<<(unsigned)grid, 256, 0, st>>>(a);
-  else layernorm_kernel<8><<<(unsigned)grid, 256, 0, st>>>(a);
+  if (cols <= 256) WF2_CUDA(launch_pdl(layernorm_kernel<2>, dim3((unsigned)grid), dim3(256), 0, st, a));
+  else if (cols <= 512) WF2_CUDA(launch_pdl(layernorm_kernel<4>, dim3((unsigned)grid), dim3(256), 0, st, a));
+  else WF2_CUDA(launch_pdl(layernorm_kernel<8>, dim3((unsigned)grid), dim3(256), 0, st, a));
   return post_launch("wf2cu_layernorm");
 }
 

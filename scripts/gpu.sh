@@ -5,6 +5,7 @@
 #         newtests         only tests/test_gpu_bench_shapes.py (prints kept)
 #         bench            python bench.py            -> gpurun_out/<tag>_bench.json / .err
 #         benchref         python bench.py --impl reference
+#         benchnopdl       the sweep / fused chains / MLP with WF2CU_PDL=0 (A/B of programmatic dependent launch)
 #         launches         ncu launch list of `bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --fused 1 --no-cpu`
 #         ncu:<regex>:<script.py>   ncu --set full on kernels matching <regex> while running python <script.py>
 #         py:<script.py>   run a python script, log -> gpurun_out/<tag>_<script>.log
@@ -16,6 +17,7 @@ for task in "$@"; do
     tests)    timeout 1500 python -m pytest tests -m gpu -q -rf 2>&1 | tail -60 > gpurun_out/${tag}_pytest.log; tail -5 gpurun_out/${tag}_pytest.log ;;
     newtests) timeout 900 python -m pytest tests/test_gpu_bench_shapes.py -m gpu -q -rf -s 2>&1 | tail -80 > gpurun_out/${tag}_newtests.log; tail -40 gpurun_out/${tag}_newtests.log ;;
     bench)    timeout 900 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"; tail -c 1500 gpurun_out/${tag}_bench.json; tail -5 gpurun_out/${tag}_bench.err ;;
+    benchnopdl) WF2CU_PDL=0 timeout 900 python bench.py --gemm 0 --gpt2 0 --cnn 0 --no-cpu > gpurun_out/${tag}_bench_nopdl.json 2> gpurun_out/${tag}_bench_nopdl.err; echo "bench (WF2CU_PDL=0) rc=$?" ;;
     benchref) timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "benchref rc=$?" ;;
     launches) cmd="python bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --no-cpu"
               timeout 300 $cmd > gpurun_out/${tag}_launches_plain.log 2>&1 &&
