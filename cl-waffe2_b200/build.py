@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libwaffe2cuda.so")
-SOURCES = ["runtime", "elementwise", "reduce", "softmax", "misc", "fused", "comm", "p2p", "conv", "gemm", "gemm_tc"]
+SOURCES = ["runtime", "elementwise", "reduce", "softmax", "misc", "fused", "comm", "p2p", "conv", "gemm", "gemm_tc", "attention"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

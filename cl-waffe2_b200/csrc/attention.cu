@@ -1,0 +1,320 @@
+// attention.cu — the GPT-2 example's SelfAttention as two tcgen05 kernels (second half).
+//
+// The reference composes it from nodes (`examples/gpt-2/utils.lisp:204-244`): split-heads (view + permute +
+// ->contiguous copies), `(!matmul Q K)` into a materialised (B H N N) tensor, `(!div w N)` with N = the LAST axis of w
+// (the sequence length, not sqrt(d)), `(!softmax w :avoid-overflow nil)` with !softmax's default axis 1 = the HEADS axis
+// of the 4-D tensor, no causal mask, `(!matmul w V)`, merge-heads (permute + reshape copy).  All of it is reproduced as
+// written; what changes is the number of passes over the 402 MB (B H N N) tensor at B = 8, N = 1024:
+//
+//   wf2cu_attn_heads_softmax : P[b,h,i,j] = e[b,h,i,j] / sum_h' e[b,h',i,j],  e = exp((Q_h[i,:] . K_h[j,:]) / N)
+//       reads Q and K straight from the dense (B N 3E) activation of the QKV projection (both are K-major there: no
+//       head-split copies, no transposes, no hi / lo planes in global memory) and writes P ONCE.  It runs on the raw-operand
+//       3xTF32 main loop of MatmulNode (gemm_raw.cuh: 128 queries x 256 keys per tile, 128x256x8 MMAs) with two epilogues:
+//         pass 1  den[b,i,j] = sum over the 12 heads (in head order, like `!sum`) of exp(s / N), accumulated in registers across
+//                 the 12 head sub-tiles of a position and stored once (33 MB at B = 8, N = 1024, L2 resident)
+//         pass 2  the product again (Q.K is 13 GFLOP per layer: cheap next to a second trip of the 402 MB tensor through HBM),
+//                 p = exp(s / N) / den, 32 x 8 blocks through the bulk-copy engine into P
+//       How it got there (all measured on B200, B = 8, N = 1024, per layer):  the heads-axis softmax couples the 12 heads of
+//       one (i, j), so the first design kept all 12 score tiles of a (128 x 32) tile in TMEM: 144 us with ONE truncated TF32
+//       pass (error 3e-4 on P for N(0, 2) inputs: not acceptable for a library kernel), 271 us with the compensated three —
+//       whether the lo planes came from global memory, from converter warps, or the Q operand lived in tensor memory (294 us).
+//       scripts/micro/mma_rate_test.cu explains it: a kind::tf32 MMA with M = 128 costs the same whatever N is, so 288 MMAs of
+//       N = 32 per tile were the bound.  With N = 256 per MMA the products of BOTH passes cost less than one pass of that.
+//   wf2cu_attn_pv : out[b,i,h*64:(h+1)*64] = sum_j P[b,h,i,j] V_h[j,:], error-compensated 3xTF32 (as MatmulNode), written
+//       in the merged-heads layout (B N E) that merge-heads produces (no permute copies).  P tiles arrive by TMA as RAW
+//       fp32; converter warps move each tile into tensor memory as the A operand (raw bits = the TF32 hi plane, lo = x -
+//       trunc(x)); V's hi / lo planes are split and transposed once per call (25 MB against 402 MB of P).  warp 0 TMA,
+//       warp 1 MMA (12 x 128x64x8 per k-block into one of two 64-column accumulators), warps 2-5 converters, warps 6-9 epilogue.
+// Both kernels are specialised for 12 heads of 64 features (GPT-2 small); other shapes return WF2CU_ERR_UNSUPPORTED and the
+// host issues the nodes one by one, exactly as before.
+#include <cuda.h>
+#include "common.cuh"
+#include "math.cuh"
+#include "tc.cuh"
+
+namespace wf2 {
+
+constexpr int AH = 12, AD = 64, AE = AH * AD;
+constexpr int UK = 8;
+
+// ------------------------------------------------------------------ helpers
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+               "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+                 "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]),
+                 "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]),
+                 "r"(v[30]), "r"(v[31]) : "memory");
+}
+// D[tmem] (+)= A[tmem] . B[smem desc], kind::tf32: row r of the 128-row A tile is TMEM lane r, element k of it column a + k
+// (scripts/micro/ts_mma_test.cu checks exactly this layout on hardware)
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}\n"
+               ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ float tf32_lo(float x) {   // x - trunc_tf32(x), exact; inf / nan live in the hi part only
+  return (fabsf(x) <= 3.0e38f) ? x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u) : 0.f;
+}
+
+// ------------------------------------------------------------------ P . V
+constexpr int P_M = 128, P_N = 64, P_K = 32;
+constexpr int P_ATILE = P_M * P_K * 4;               // 16 KiB
+constexpr int P_BTILE = P_N * P_K * 4;               // 8 KiB
+constexpr int P_STAGE = P_ATILE + 2 * P_BTILE;       // raw P | V_hi | V_lo = 32 KiB
+constexpr int P_NS = 6;
+constexpr int P_ACOL = 2 * P_N;                      // TMEM: columns [0, 128) two accumulators, [128, 256) two P operand buffers
+constexpr int P_THREADS = 320;
+constexpr int P_SMEM = P_NS * P_STAGE + 1024 + 256;
+constexpr uint32_t P_IDESC = idesc_tf32_mn(P_M, P_N);
+
+// V_h (N x 64 per (b, h), rows 3E apart inside the QKV activation) -> hi / lo planes [b*H + h][64][N], K-major
+__global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restrict__ qkv, float* __restrict__ hi, float* __restrict__ lo, int N) {
+  __shared__ float t[32][65];
+  pdl_prologue();
+  const int bh = blockIdx.y, b = bh / AH, h = bh % AH, k0 = blockIdx.x * 32;
+  const float* src = qkv + ((size_t)b * N + k0) * (3 * AE) + 2 * AE + h * AD;
+  for (int e = threadIdx.x; e < 32 * 64; e += 256) t[e >> 6][e & 63] = src[(size_t)(e >> 6) * (3 * AE) + (e & 63)];   // rows of 64
+  __syncthreads();
+  for (int e = threadIdx.x; e < 64 * 32; e += 256) {
+    const int n = e >> 5, k = e & 31;
+    const float x = t[k][n];
+    const float hv = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+    const size_t o = ((size_t)bh * 64 + n) * N + k0 + k;
+    hi[o] = hv;
+    lo[o] = (fabsf(x) <= 3.0e38f) ? x - hv : 0.f;        // inf / nan live in hi only
+  }
+}
+
+struct PvArgs { float* out; int N, tiles_m, batch_heads; };
+
+__global__ void __launch_bounds__(P_THREADS, 1)
+attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant__ CUtensorMap map_vh,
+               const __grid_constant__ CUtensorMap map_vl, const __grid_constant__ PvArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P_NS * P_STAGE);
+  uint64_t* full = bars;                   // [P_NS] TMA -> converters / MMA
+  uint64_t* conv = bars + P_NS;            // [P_NS] converters -> MMA (4 arrivals, one per warp)
+  uint64_t* empty = bars + 2 * P_NS;       // [P_NS] MMA -> TMA
+  uint64_t* acc_full = bars + 3 * P_NS;    // [2]
+  uint64_t* acc_empty = acc_full + 2;      // [2] (4 arrivals)
+  uint64_t* afree = acc_empty + 2;         // [2] MMA -> converters: the P operand buffer in TMEM may be overwritten
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(afree + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = a.tiles_m * a.batch_heads;
+  const int nkb = a.N / P_K;
+  pdl_prologue();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P_NS; ++s) { mbar_init(&full[s], 1); mbar_init(&conv[s], 4); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4); mbar_init(&afree[s], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int bh = t / a.tiles_m, mt = t % a.tiles_m;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* st = smem + s * P_STAGE;
+          mbar_expect_tx(&full[s], P_ATILE + 2 * P_BTILE);
+          tma_load_3d(&map_p, &full[s], st, kb * P_K, mt * P_M, bh);
+          tma_load_3d(&map_vh, &full[s], st + P_ATILE, kb * P_K, 0, bh);
+          tma_load_3d(&map_vl, &full[s], st + P_ATILE + P_BTILE, kb * P_K, 0, bh);
+          if (++s == P_NS) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      int as = 0; uint32_t aph = 0, n = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        mbar_wait(&acc_empty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + (uint32_t)(as * P_N);
+        for (int kb = 0; kb < nkb; ++kb, ++n) {
+          mbar_wait(&full[s], ph);          // the V planes (async proxy) ...
+          mbar_wait(&conv[s], ph);          // ... and P's hi / lo planes in TMEM (tcgen05.st) are in place
+          tc_fence_after();
+          const uint32_t st = smem_u32(smem + s * P_STAGE);
+          const uint64_t dbh = make_desc_sw128(st + P_ATILE), dbl = make_desc_sw128(st + P_ATILE + P_BTILE);
+          const uint32_t ah = tmem_base + (uint32_t)(P_ACOL + (n & 1u) * 64u), al = ah + 32u;
+#pragma unroll
+          for (int k = 0; k < P_K / UK; ++k) {
+            const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
+            tc_mma_tf32_ts(d, al + k * UK, dbh + adv, P_IDESC, (kb | k) != 0);   // small terms first, then the main product
+            tc_mma_tf32_ts(d, ah + k * UK, dbl + adv, P_IDESC, 1);
+            tc_mma_tf32_ts(d, ah + k * UK, dbh + adv, P_IDESC, 1);
+          }
+          tc_commit(&empty[s]);
+          tc_commit(&afree[n & 1u]);
+          if (++s == P_NS) { s = 0; ph ^= 1; }
+        }
+        tc_commit(&acc_full[as]);
+        if (++as == 2) { as = 0; aph ^= 1; }
+      }
+    }
+  } else if (warp < 6) {
+    // ---- converters: the P tile goes to TENSOR MEMORY as the A operand (row = lane, k = column): raw bits = hi plane,
+    // lo = x - trunc(x); the MMAs then fetch only the V planes from shared memory
+    const int q = warp & 3, row = q * 32 + lane;
+    int s = 0; uint32_t ph = 0, n = 0, apar = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      for (int kb = 0; kb < nkb; ++kb, ++n) {
+        const uint32_t u = n & 1u;
+        mbar_wait(&full[s], ph);
+        const uint8_t* st = smem + s * P_STAGE;
+        uint32_t hi[32], lo[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {                                // this lane's row: 8 chunks of 16 bytes, SWIZZLE_128B
+          const float4 x = *reinterpret_cast<const float4*>(st + row * 128 + ((j ^ (row & 7)) << 4));
+          hi[4 * j] = __float_as_uint(x.x); hi[4 * j + 1] = __float_as_uint(x.y); hi[4 * j + 2] = __float_as_uint(x.z); hi[4 * j + 3] = __float_as_uint(x.w);
+          lo[4 * j] = __float_as_uint(tf32_lo(x.x)); lo[4 * j + 1] = __float_as_uint(tf32_lo(x.y));
+          lo[4 * j + 2] = __float_as_uint(tf32_lo(x.z)); lo[4 * j + 3] = __float_as_uint(tf32_lo(x.w));
+        }
+        mbar_wait(&afree[u], ((apar >> u) & 1u) ^ 1u);               // the MMAs that read this buffer two k-blocks ago have retired
+        apar ^= 1u << u;
+        tc_fence_after();
+        const uint32_t aa = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(P_ACOL + u * 64u);
+        tc_st32(aa, hi);
+        tc_st32(aa + 32, lo);
+        tc_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&conv[s]);
+        if (++s == P_NS) { s = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    // ---- epilogue: accumulator -> out[b, row, h*64 .. h*64+63] (merged heads)
+    const int q = warp & 3;
+    int as = 0; uint32_t aph = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int bh = t / a.tiles_m, mt = t % a.tiles_m, b = bh / AH, h = bh % AH;
+      mbar_wait(&acc_full[as], aph);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * P_N);
+      uint32_t v0[32], v1[32];
+      tc_ld32(tbase, v0);
+      tc_ld32(tbase + 32, v1);
+      tc_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);          // the accumulator is in registers now
+      const int row = mt * P_M + q * 32 + lane;
+      if (row < a.N) {
+        float4* crow = reinterpret_cast<float4*>(a.out + ((size_t)b * a.N + row) * AE + h * AD);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          crow[j] = make_float4(__uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          crow[8 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+      }
+      if (++as == 2) { as = 0; aph ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(256) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host side
+static int encode(CUtensorMap* map, int rank, void* base, const cuuint64_t* dims, const cuuint64_t* strides, const cuuint32_t* box,
+                  CUtensorMapSwizzle sw, CUtensorMapL2promotion l2, const char* what) {
+  EncodeTiledFn enc = tensor_map_encoder();
+  if (!enc) return WF2CU_ERR_CUDA;
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, l2,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed (%d)", what, (int)r);
+  return 0;
+}
+
+static bool attn_shape_ok(int64_t batch, int64_t seq, int64_t n_head, int64_t head_dim) {
+  return n_head == AH && head_dim == AD && batch >= 1 && batch <= 4096 && seq >= 128 && seq % 128 == 0 && seq <= (1 << 20);
+}
+
+}  // namespace wf2
+
+using namespace wf2;
+
+extern "C" {
+
+int wf2cu_attn_heads_softmax(const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head, int64_t head_dim,
+                             float divisor, void* p, int64_t p_off) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(qkv && p, "wf2cu_attn_heads_softmax: null pointer");
+  if (!attn_shape_ok(batch, seq, n_head, head_dim) || !(divisor > 0.f))
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_heads_softmax: implemented for 12 heads of 64 features and seq a multiple of 128 "
+                     "(got heads=%lld dim=%lld seq=%lld); issue the nodes separately", (long long)n_head, (long long)head_dim, (long long)seq);
+  float* x = (float*)qkv + qkv_off;
+  float* P = (float*)p + p_off;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(P) & 15))
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_heads_softmax: operands must be 16-byte aligned");
+  const int rc = attn_scores_raw(x, batch, seq, divisor, P);
+  return rc;
+}
+
+int wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head,
+                  int64_t head_dim, void* out, int64_t out_off) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(qkv && p && out, "wf2cu_attn_pv: null pointer");
+  if (!attn_shape_ok(batch, seq, n_head, head_dim) || S().branch != 0)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_pv: implemented for 12 heads of 64 features and seq a multiple of 128 on the main "
+                     "stream (got heads=%lld dim=%lld seq=%lld); issue the nodes separately", (long long)n_head, (long long)head_dim, (long long)seq);
+  float* P = (float*)p + p_off;
+  const float* x = (const float*)qkv + qkv_off;
+  float* O = (float*)out + out_off;
+  if ((reinterpret_cast<uintptr_t>(P) & 15) || (reinterpret_cast<uintptr_t>(O) & 15))
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_pv: operands must be 16-byte aligned");
+  const int N = (int)seq, BH = (int)(batch * AH);
+  const size_t plane = (size_t)BH * AD * N * 4;
+  float* vh = tc_workspace(2 * plane);
+  if (!vh) return WF2CU_ERR_CUDA;
+  float* vl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(vh) + plane);
+  WF2_CUDA(launch_pdl(attn_split_v_kernel, dim3((unsigned)(N / 32), (unsigned)BH), dim3(256), 0, S().stream, x, vh, vl, N));
+  int rc = post_launch("wf2cu_attn_pv(split V)");
+  if (rc) return rc;
+  CUtensorMap mp, mvh, mvl;
+  {
+    const cuuint64_t pd[3] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)BH};
+    const cuuint64_t ps[2] = {(cuuint64_t)N * 4, (cuuint64_t)N * N * 4};
+    const cuuint32_t pb[3] = {P_K, P_M, 1};
+    rc = encode(&mp, 3, P, pd, ps, pb, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, "P");
+    if (rc) return rc;
+    const cuuint64_t vd[3] = {(cuuint64_t)N, (cuuint64_t)AD, (cuuint64_t)BH};
+    const cuuint64_t vs[2] = {(cuuint64_t)N * 4, (cuuint64_t)AD * N * 4};
+    const cuuint32_t vb[3] = {P_K, P_N, 1};
+    rc = encode(&mvh, 3, vh, vd, vs, vb, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, "V hi");
+    if (rc) return rc;
+    rc = encode(&mvl, 3, vl, vd, vs, vb, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, "V lo");
+    if (rc) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    attr_set = true;
+  }
+  PvArgs args{O, N, N / P_M, BH};
+  const int total = args.tiles_m * BH;
+  const int grid = total < S().sm_count ? total : S().sm_count;
+  WF2_CUDA(launch_pdl(attn_pv_kernel, dim3(grid), dim3(P_THREADS), P_SMEM, S().stream, mp, mvh, mvl, args));
+  return post_launch("wf2cu_attn_pv");
+}
+
+}  // extern "C"

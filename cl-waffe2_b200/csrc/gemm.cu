@@ -9,6 +9,7 @@
 //   * this file  : register-tiled fp32 FMA kernel (128x128x16 tile, 8x8 per thread) for everything
 //                  the tensor path does not take (tiny / unaligned shapes such as the 10-wide
 //                  classifier head).
+#include <stdlib.h>
 #include "common.cuh"
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
@@ -19,6 +20,8 @@ namespace wf2 {
 int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B,
                 int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act);
 // gemm_tc.cu: one-launch tcgen05 kernel for small problems (in-kernel hi/lo split, cluster split-K, fused epilogue)
+int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
+                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act);
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                       float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
                       const float* mask, int64_t ldmask);
@@ -594,6 +597,12 @@ static int sgemm_skinny_tn_try(const GemmArgs& g, int64_t batch) {
 
 using namespace wf2;
 
+static bool raw_auto() {   // WF2CU_GEMM_RAW=0: auto dispatch keeps the planes kernels (A/B measurements)
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("WF2CU_GEMM_RAW"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on != 0;
+}
+
 extern "C" {
 
 int wf2cu_gemm_last_path(int* out) {
@@ -603,7 +612,7 @@ int wf2cu_gemm_last_path(int* out) {
 }
 
 int wf2cu_gemm_set_mode(int mode) {
-  WF2_CHECK(mode >= 0 && mode <= 6, "wf2cu_gemm_set_mode: mode %d not in 0..6", mode);
+  WF2_CHECK(mode >= 0 && mode <= 7, "wf2cu_gemm_set_mode: mode %d not in 0..7", mode);
   S().gemm_mode = mode;
   return 0;
 }
@@ -650,6 +659,22 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
       if (r == 1) return 0;
     }
     if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (out of range)", who);
+  }
+  if (mode == 7 || (mode == 0 && raw_auto() && !trans_a && 2.0 * (double)m * (double)n * (double)k * (double)batch >= 1.0e9 && m >= 64 && n >= 64 &&
+                    k >= 32)) {
+    // A is K-major: raw fp32 tiles by TMA, lo planes made on the SM — no operand pre-pass (gemm_raw.cuh)
+    const int r = gemm_raw_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, bias, act);
+    if (r < 0) return -r;
+    if (r == 1) {
+      if (!mask) return 0;
+      g.bias = nullptr; g.act = 0;
+      int64_t grid = (m * n + 255) / 256;
+      const int64_t cap = (int64_t)S().sm_count * 8;
+      if (grid > cap) grid = cap;
+      gemm_epilogue_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(g);
+      return post_launch("wf2cu_gemm_ex(epilogue)");
+    }
+    if (mode == 7) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: raw-operand tensor-core kernel forced but declined (A transposed or misaligned)", who);
   }
   if (mode != 1) {
     // bias and relu ride in the persistent kernel's epilogue; only the relu-backward mask needs its own pass

@@ -19,8 +19,11 @@
 //                                 C layouts a tensor map cannot describe are stored from registers, bounds-checked
 //      smem full/empty mbarriers between warp 0 and warp 1, TMEM full/empty between 1 and 2-5.
 #include <cuda.h>
+#include <stdlib.h>
+#include <type_traits>
 #include <vector>
 #include "common.cuh"
+#include "math.cuh"
 #include "tc.cuh"
 
 namespace wf2 {
@@ -509,6 +512,10 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   }
 }
 
+}  // namespace wf2
+#include "gemm_raw.cuh"   // step 2c: the same main loop on RAW fp32 tiles (no operand pre-pass) + the attention-score epilogues
+namespace wf2 {
+
 // ------------------------------------------------------------------ step 3: fused small-problem kernel
 // The MLP training step's GEMMs (C4: 1024x256x784 ... 10x256x1024) are 0.005-0.4 GFLOP each: too small for
 // two extra launches that write hi/lo planes, and too few 128x256 tiles to fill 148 SMs.  Here ONE launch
@@ -873,6 +880,12 @@ static int ensure_ws(size_t bytes) {
   return 0;
 }
 
+// the planes workspace, for the other tcgen05 kernels of the library (attention.cu): nullptr + error set on failure
+float* tc_workspace(size_t bytes) {
+  if (ensure_ws(bytes)) return nullptr;
+  return g_ws;
+}
+
 static bool g_t256_auto = true;       // auto mode may take the 256x256-tile kernel (rule in gemm_tc_try)
 
 static int make_map(CUtensorMap* map, float* base, int rows, int Kp, int nbatch, int box_rows) {
@@ -1049,6 +1062,155 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   rc = post_launch("wf2cu_gemm(tcgen05)");
   S().gemm_last_path = WF2CU_GEMM_PATH_TC_128X256;
   return rc ? -rc : 1;
+}
+
+// ---- raw-operand kernel (gemm_raw.cuh): A must be K-major (not transposed); B raw when K-major (trans_b), else planes
+static int make_map_raw(CUtensorMap* map, const float* base, int64_t k, int64_t rows, int64_t ld, int64_t nbatch, int64_t bstride, int box_rows) {
+  cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)(nbatch < 1 ? 1 : nbatch)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 4, (cuuint64_t)(nbatch > 1 ? bstride : rows * ld) * 4};
+  cuuint32_t box[3] = {(cuuint32_t)RK, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return -set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(raw operand) failed (%d) k=%lld rows=%lld ld=%lld", (int)r,
+                                           (long long)k, (long long)rows, (long long)ld);
+  return 0;
+}
+
+static bool raw_operand_ok(const float* p, int64_t ld, int64_t bstride, int64_t nbatch) {
+  return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld & 3) == 0 && (nbatch <= 1 || ((bstride & 3) == 0 && bstride > 0));
+}
+
+// returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
+int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
+                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act) {
+  if (ta || k < 1 || m > (1 << 30) || n > (1 << 30) || k > (1 << 30) || batch > 65535 || S().branch != 0) return 0;
+  const int a_nb = (sa == 0 || batch == 1) ? 1 : (int)batch;
+  const int b_nb = (sb == 0 || batch == 1) ? 1 : (int)batch;
+  if (!raw_operand_ok(A, lda, sa, a_nb)) return 0;
+  const bool b_raw = tb != 0 && raw_operand_ok(B, ldb, sb, b_nb);
+  if (!tensor_map_encoder()) return -WF2CU_ERR_CUDA;
+  static bool attr_set = false;
+  if (!attr_set) {
+    const int bytes = raw_smem(RawGemmJob::kEpiWarps, RawGemmJob::kEpiBytes);
+    cudaError_t e = cudaFuncSetAttribute(gemm_raw_kernel<RawGemmJob, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_raw_kernel<RawGemmJob, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_raw_kernel)", __FILE__, __LINE__);
+    attr_set = true;
+  }
+  CUtensorMap ma, mb, mbl, mc;
+  memset(&mbl, 0, sizeof(mbl));
+  int rc;
+  if ((rc = make_map_raw(&ma, A, k, m, lda, a_nb, sa, RM))) return rc;
+  if (b_raw) {
+    if ((rc = make_map_raw(&mb, B, k, n, ldb, b_nb, sb, RN))) return rc;
+    mbl = mb;
+  } else {
+    // B is MN-major for the product (or misaligned): transposing split into K-major hi / lo planes, as before
+    const int Kp = (int)((k + TK - 1) / TK) * TK;
+    const size_t pb = ((((size_t)b_nb * n * Kp * 4) + 255) & ~(size_t)255);
+    if ((rc = ensure_ws(2 * pb))) return rc;
+    float* bh = g_ws;
+    float* bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
+    if ((rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0))) return rc;
+    if ((rc = make_map256(&mb, bh, (int)n, Kp, b_nb, RN))) return rc;
+    if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb, RN))) return rc;
+  }
+  RawGemmJob job;
+  TcArgs& t = job.t;
+  t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = (int)((k + RK - 1) / RK);
+  t.tiles_m = (int)((m + RM - 1) / RM); t.tiles_n = (int)((n + RN - 1) / RN); t.batch = (int)batch;
+  t.passes = 3;
+  t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
+  t.a_bcast = a_nb == 1 ? 1 : 0;
+  t.b_bcast = b_nb == 1 ? 1 : 0;
+  t.bias = bias; t.act = act;
+  t.c_tma = make_map_c(&mc, C, m, n, ldc, sc, batch);
+  const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
+  const int grid = (int)(total < S().sm_count ? total : S().sm_count);
+  const int threads = raw_threads(RawGemmJob::kEpiWarps, true), bytes = raw_smem(RawGemmJob::kEpiWarps, RawGemmJob::kEpiBytes);
+  cudaError_t e = b_raw ? launch_pdl(gemm_raw_kernel<RawGemmJob, true, true, true>, dim3(grid), dim3(threads), bytes, S().stream, ma, ma, mb, mbl, mc, job)
+                        : launch_pdl(gemm_raw_kernel<RawGemmJob, true, false, true>, dim3(grid), dim3(threads), bytes, S().stream, ma, ma, mb, mbl, mc, job);
+  if (e != cudaSuccess) return -cuda_fail(e, "launch(gemm_raw_kernel)", __FILE__, __LINE__);
+  rc = post_launch("wf2cu_gemm(tcgen05 raw operands)");
+  S().gemm_last_path = WF2CU_GEMM_PATH_TC_RAW;
+  return rc ? -rc : 1;
+}
+
+// lo planes of Q and K: lo[b, n, c] = x - trunc_tf32(x) for the first 2E features of every (b, n) row of the QKV activation
+__global__ void __launch_bounds__(256) attn_split_qk_kernel(const float* __restrict__ qkv, float* __restrict__ lo, int64_t rows) {
+  pdl_prologue();
+  constexpr int V4 = 2 * RA_E / 4;                                   // float4 per row
+  const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= rows * V4) return;
+  const int64_t r = idx / V4;
+  const int c4 = (int)(idx - r * V4);
+  const float4 x = reinterpret_cast<const float4*>(qkv + r * (3 * RA_E))[c4];
+  reinterpret_cast<float4*>(lo + r * (2 * RA_E))[c4] = make_float4(raw_lo(x.x), raw_lo(x.y), raw_lo(x.z), raw_lo(x.w));
+}
+
+// The GPT-2 example's attention weights through the raw main loop: P[b,h,i,j] = exp(s_h / divisor) / sum_h' exp(s_h' / divisor).
+// qkv: dense (B N 3E), 16-byte aligned; P: dense (B H N N); N a multiple of 128.  Returns 0 or a wf2cu status.
+int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor, float* P) {
+  if (!tensor_map_encoder()) return WF2CU_ERR_CUDA;
+  if (S().branch != 0) return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_heads_softmax: main stream only (the workspace is not per branch)");
+  const int B = (int)batch, N = (int)seq;
+  // WF2CU_ATTN_PLANES=1: lo planes of Q and K pre-split into the workspace and loaded by TMA instead of made by converter warps
+  // (twice the L2 -> SM bytes: the kernel is then bound by the ~7.4 TB/s the L2 delivers to the SMs; kept for A/B measurements)
+  static int planes = -1;
+  if (planes < 0) { const char* e = getenv("WF2CU_ATTN_PLANES"); planes = (e && e[0] == '1') ? 1 : 0; }
+  float* qk_lo = nullptr;
+  if (planes) {
+    if (ensure_ws((size_t)B * N * 2 * RA_E * 4)) return WF2CU_ERR_CUDA;
+    qk_lo = g_ws;
+    const int64_t rows = batch * seq, work = rows * (2 * RA_E / 4);
+    WF2_CUDA(launch_pdl(attn_split_qk_kernel, dim3((unsigned)((work + 255) / 256)), dim3(256), 0, S().stream, qkv, qk_lo, rows));
+    const int rc0 = post_launch("wf2cu_attn_heads_softmax(split Q K)");
+    if (rc0) return rc0;
+  }
+  static bool attr_set = false;
+  const int bytes = raw_smem(RawAttnJob::kEpiWarps, RawAttnJob::kEpiBytes);
+  if (!attr_set) {
+    WF2_CUDA(cudaFuncSetAttribute(gemm_raw_kernel<RawAttnJob, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    WF2_CUDA(cudaFuncSetAttribute(gemm_raw_kernel<RawAttnJob, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    attr_set = true;
+  }
+  CUtensorMap mq, mql, mk, mkl, mp;
+  {
+    cuuint32_t boxq[3] = {RK, RM, 1}, boxk[3] = {RK, RN, 1}, estr[4] = {1, 1, 1, 1};
+    cuuint64_t dims[3] = {(cuuint64_t)(3 * RA_E), (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)(3 * RA_E) * 4, (cuuint64_t)N * 3 * RA_E * 4};
+    cuuint64_t ldims[3] = {(cuuint64_t)(2 * RA_E), (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t lstrides[2] = {(cuuint64_t)(2 * RA_E) * 4, (cuuint64_t)N * 2 * RA_E * 4};
+    cuuint64_t pd[4] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)RA_H, (cuuint64_t)B};
+    cuuint64_t ps[3] = {(cuuint64_t)N * 4, (cuuint64_t)N * N * 4, (cuuint64_t)RA_H * N * N * 4};
+    cuuint32_t pb[4] = {16, 32, 1, 1};
+    CUresult r[5];
+    r[0] = g_encode(&mq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qkv, dims, strides, boxq, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    r[1] = g_encode(&mk, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qkv, dims, strides, boxk, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    r[2] = r[3] = CUDA_SUCCESS;
+    mql = mq; mkl = mk;
+    if (planes) {
+      r[2] = g_encode(&mql, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qk_lo, ldims, lstrides, boxq, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      r[3] = g_encode(&mkl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qk_lo, ldims, lstrides, boxk, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    r[4] = g_encode(&mp, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)P, pd, ps, pb, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    for (int i = 0; i < 5; ++i)
+      if (r[i] != CUDA_SUCCESS) return set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(attention scores, map %d) failed (%d)", i, (int)r[i]);
+  }
+  RawAttnJob job{RawAttnArgs{B, N, (N + RM - 1) / RM, (N + RN - 1) / RN, (float)(1.4426950408889634 / (double)divisor)}};
+  const int items = job.a.B * job.a.tiles_i * job.a.tiles_j, sms = S().sm_count;
+  const int grid = items < sms ? items : sms;
+  if (planes) WF2_CUDA(launch_pdl(gemm_raw_kernel<RawAttnJob, false, false, true>, dim3(grid), dim3(raw_threads(RawAttnJob::kEpiWarps, false)), bytes,
+                                  S().stream, mq, mql, mk, mkl, mp, job));
+  else        WF2_CUDA(launch_pdl(gemm_raw_kernel<RawAttnJob, true, true, true>, dim3(grid), dim3(raw_threads(RawAttnJob::kEpiWarps, true)), bytes,
+                                  S().stream, mq, mql, mk, mkl, mp, job));
+  return post_launch("wf2cu_attn_heads_softmax");
 }
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)

@@ -104,8 +104,27 @@ def merge_heads(x: CUDATensor) -> CUDATensor:
     return reshape_contiguous(ops.copy(p), [B, N, H * d])
 
 
+FUSE_ATTENTION = True
+
+
 def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
-    """SelfAttention (utils.lisp:222-244) without a past: as written in the example."""
+    """SelfAttention (utils.lisp:222-244) without a past: as written in the example.
+    FUSE_ATTENTION: two launches (wf2cu_attn_heads_softmax, wf2cu_attn_pv: csrc/attention.cu) read Q, K and V straight from
+    the QKV activation, write the (B H N N) weights once and leave the result in merged-heads layout; shapes the
+    library does not take (WF2CU_ERR_UNSUPPORTED) run node by node below, exactly as the example composes them."""
+    if FUSE_ATTENTION and qkv.dims() == 3 and qkv.is_contiguous() and not qkv.permuted_p():
+        lib = _lib.load()
+        B, N, E3 = qkv.shape
+        E = E3 // 3
+        w = make_tensor([B, n_head, N, N])
+        off = qkv.lower().offset
+        rc = lib.wf2cu_attn_heads_softmax(qkv.vec.ptr, off, B, N, n_head, E // n_head, float(N), w.vec.ptr, w.lower().offset)
+        if rc == 0:
+            out = make_tensor([B, N, E])
+            _lib.check(lib.wf2cu_attn_pv(w.vec.ptr, w.lower().offset, qkv.vec.ptr, off, B, N, n_head, E // n_head, out.vec.ptr, out.lower().offset))
+            return out
+        if rc != 3:                              # anything but WF2CU_ERR_UNSUPPORTED is an error
+            _lib.check(rc)
     Q = split_heads(qkv, "Q", n_head)
     K = split_heads(qkv, "K", n_head)
     V = split_heads(qkv, "V", n_head)

@@ -117,6 +117,11 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 		   (m :pointer) (m-off :int64) (v :pointer) (v-off :int64) (n :int64)
 		   (lr-t :float) (lr-t-dev :pointer) (beta1 :float) (beta2 :float) (eps :float) (grad-scale :float)))
 (defwf2 embedding-gather ((ctx :pointer) (batch :int64) (seq :int64) (wte :pointer) (wpe :pointer) (dim :int64) (out :pointer)))
+;; the GPT-2 example's SelfAttention as two launches (examples/gpt-2/utils.lisp:204-244)
+(defwf2 attn-heads-softmax ((qkv :pointer) (qkv-off :int64) (batch :int64) (seq :int64) (n-head :int64) (head-dim :int64)
+			    (divisor :float) (p :pointer) (p-off :int64)))
+(defwf2 attn-pv ((p :pointer) (p-off :int64) (qkv :pointer) (qkv-off :int64) (batch :int64) (seq :int64) (n-head :int64)
+		 (head-dim :int64) (out :pointer) (out-off :int64)))
 (defwf2 layernorm ((x :pointer) (x-off :int64) (g :pointer) (g-off :int64) (b :pointer) (b-off :int64)
 		   (out :pointer) (out-off :int64) (rows :int64) (cols :int64) (eps :float)))
 ;; unfold / Conv2D / pooling (csrc/conv.cu)

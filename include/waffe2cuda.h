@@ -206,8 +206,9 @@ int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
                 int64_t batch, int64_t stride_a, int64_t stride_b, int64_t stride_c);
 /* 0 = auto, 1 = force fp32 SIMT path, 2 = force tcgen05 3xTF32 (planes + persistent 128x256-tile kernel),
  * 3 = tcgen05 1xTF32 (not parity-grade), 4 = force the one-launch fused tcgen05 kernel (small problems),
- * 5 / 6 = force tcgen05 3xTF32 on the persistent 256x256 / 256x192-tile kernel.  Forced modes return WF2CU_ERR_UNSUPPORTED
- * for shapes their kernel does not take. */
+ * 5 / 6 = force tcgen05 3xTF32 on the persistent 256x256 / 256x192-tile kernel, 7 = force the raw-operand kernel (A not
+ * transposed: fp32 tiles straight from the operand by TMA, lo planes made on the SM, no pre-pass).  Forced modes return
+ * WF2CU_ERR_UNSUPPORTED for shapes their kernel does not take. */
 int  wf2cu_gemm_set_mode(int mode);
 /* Which kernel the last wf2cu_gemm / wf2cu_gemm_ex call launched (the parity tests assert that the benchmarked shapes
  * really run on the kernel whose throughput is quoted). */
@@ -264,6 +265,22 @@ int  wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int64_t g_off,
  * out[b,p,:] = wte[round(ctx[b,p]),:] + wpe[p,:] ; token ids are floats. */
 int  wf2cu_embedding_gather(const void* ctx, int64_t batch, int64_t seq, const void* wte,
                             const void* wpe, int64_t dim, void* out);
+
+/* ===================== the GPT-2 example's SelfAttention ===================== */
+/* `SelfAttention` of `examples/gpt-2/utils.lisp:204-244`, as written there (scale 1 / N with N = the last axis of the score
+ * tensor, `!softmax :avoid-overflow nil` over its default axis 1 = the HEADS axis of the 4-D tensor, no causal mask), in two
+ * launches instead of split-heads copies + `!matmul` + `!div` + `!softmax` + `!matmul` + merge-heads copies:
+ *   wf2cu_attn_heads_softmax : p[b,h,i,j] = e / sum_h' e[b,h',i,j],  e = exp((Q_h[i,:] . K_h[j,:]) / divisor)
+ *   wf2cu_attn_pv            : out[b,i,h*dim:(h+1)*dim] = sum_j p[b,h,i,j] V_h[j,:]        (merged heads, as merge-heads leaves them)
+ * qkv: the dense (batch seq 3*n_head*head_dim) activation of the fused QKV projection (Q | K | V along the last axis, heads
+ * consecutive inside each); p: dense (batch n_head seq seq); out: dense (batch seq n_head*head_dim).
+ * Numerics: both products are the error-compensated 3xTF32 of MatmulNode (raw fp32 tiles are the hi planes, lo = x - trunc(x)).
+ * Implemented for n_head = 12, head_dim = 64, seq a multiple of 128, 16-byte aligned operands; WF2CU_ERR_UNSUPPORTED otherwise
+ * (issue the nodes separately, exactly as the example does). */
+int  wf2cu_attn_heads_softmax(const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head, int64_t head_dim,
+                              float divisor, void* p, int64_t p_off);
+int  wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head,
+                   int64_t head_dim, void* out, int64_t out_off);
 
 /* ===================== unfold / Conv2D / pooling ===================== */
 /* Geometry of one unfold, the argument list of `waffe2_im2col_s_column` / `waffe2_col2im_s_column`

@@ -3,11 +3,13 @@
 #   gpurun --timeout 900 -- 'bash scripts/gpu.sh <tag> <task> [task ...]'
 # tasks:  tests            pytest -m gpu (all), log -> gpurun_out/<tag>_pytest.log
 #         newtests         only tests/test_gpu_bench_shapes.py (prints kept)
+#         pytest:<file>    one test file, prints kept
 #         bench            python bench.py            -> gpurun_out/<tag>_bench.json / .err
 #         benchref         python bench.py --impl reference
 #         benchnopdl       the sweep / fused chains / MLP with WF2CU_PDL=0 (A/B of programmatic dependent launch)
 #         launches         ncu launch list of `bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --fused 1 --no-cpu`
 #         ncu:<regex>:<script.py>   ncu --set full on kernels matching <regex> while running python <script.py>
+#         ncutime:<script.py>  per-kernel device times of a script (ncu gpu__time_duration, cold-cache, serialised)
 #         py:<script.py>   run a python script, log -> gpurun_out/<tag>_<script>.log
 # Every task runs under its own timeout so that a protocol bug cannot hold the box.
 tag=$1; shift
@@ -15,6 +17,8 @@ mkdir -p gpurun_out
 for task in "$@"; do
   case "$task" in
     tests)    timeout 1500 python -m pytest tests -m gpu -q -rf 2>&1 | tail -60 > gpurun_out/${tag}_pytest.log; tail -5 gpurun_out/${tag}_pytest.log ;;
+    pytest:*) f=${task#pytest:}; base=$(basename "$f" .py)
+              timeout 900 python -m pytest "$f" -m gpu -q -rf -s 2>&1 | tail -60 > gpurun_out/${tag}_${base}.log; tail -25 gpurun_out/${tag}_${base}.log ;;
     newtests) timeout 900 python -m pytest tests/test_gpu_bench_shapes.py -m gpu -q -rf -s 2>&1 | tail -80 > gpurun_out/${tag}_newtests.log; tail -40 gpurun_out/${tag}_newtests.log ;;
     bench)    timeout 900 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"; tail -c 1500 gpurun_out/${tag}_bench.json; tail -5 gpurun_out/${tag}_bench.err ;;
     benchnopdl) WF2CU_PDL=0 timeout 900 python bench.py --gemm 0 --gpt2 0 --cnn 0 --no-cpu > gpurun_out/${tag}_bench_nopdl.json 2> gpurun_out/${tag}_bench_nopdl.err; echo "bench (WF2CU_PDL=0) rc=$?" ;;
@@ -27,6 +31,22 @@ for task in "$@"; do
               timeout 300 python "$script" > gpurun_out/${tag}_${base}_plain.log 2>&1 &&
               timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$regex" -c 3 -f -o gpurun_out/${tag}_${base} python "$script" > gpurun_out/${tag}_${base}_ncu.log 2>&1
               echo "ncu $regex rc=$?"; tail -3 gpurun_out/${tag}_${base}_plain.log ;;
+    ncutime:*) script=${task#ncutime:}; base=$(basename "$script" .py)
+              timeout 300 python $script > gpurun_out/${tag}_${base}_plain.log 2>&1 &&
+              timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_${base}_launches.csv python $script > gpurun_out/${tag}_${base}_ncu.log 2>&1
+              echo "ncutime $script rc=$?"
+              python - <<PYEOF
+import csv, collections
+rows = [l for l in open("gpurun_out/${tag}_${base}_launches.csv") if not l.startswith("==")]
+agg = collections.OrderedDict()
+for r in csv.DictReader(rows):
+    if r.get("Metric Name") == "gpu__time_duration.sum":
+        t = float(r["Metric Value"]); t = t / 1000 if r["Metric Unit"] in ("ns", "nsecond") else t
+        a = agg.setdefault(r["Kernel Name"][:90], [0, 0.0]); a[0] += 1; a[1] += t
+for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:14]:
+    print(f"{t / c:9.1f} us x {c:4d}  {k}")
+PYEOF
+              ;;
     py:*)     script=${task#py:}; base=$(basename "$script" .py)
               timeout 900 python $script > gpurun_out/${tag}_${base}.log 2>&1; echo "$script rc=$?"; tail -30 gpurun_out/${tag}_${base}.log ;;
     *) echo "unknown task $task" ;;

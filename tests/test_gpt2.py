@@ -133,3 +133,73 @@ def test_gpt2_blocks_on_tensor_cores(gpu):
         gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
     truth = O.forward(ctx, W, cfg, np.float64)
     assert np.abs(out - truth).max() / np.abs(truth).max() <= 1e-3
+
+
+# ------------------------------------------------------------------ the two attention kernels (csrc/attention.cu)
+def _attention_truth(qkv, n_head):
+    """examples/gpt-2/utils.lisp:222-244 in fp64: scores / N, exp, normalised over the HEADS axis, times V, merged heads."""
+    x = qkv.astype(np.float64)
+    Q, K, V = (O.split_heads(x, w, n_head) for w in "QKV")
+    w = (Q @ K) / x.shape[1]
+    p = O.softmax_no_shift(w, axis=1)
+    return p, O.merge_heads(p @ V)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,N", [(1, 128), (2, 256), (1, 384), (3, 640)])
+def test_attention_kernels_match_fp64_and_the_node_sequence(gpu, B, N):
+    """wf2cu_attn_heads_softmax + wf2cu_attn_pv at 12 heads x 64 features (GPT-2 small) against fp64 and against the node-by-node
+    sequence the example composes (the unfused path of gpt2.self_attention).  Bars: weights 1e-4 relative (one truncated TF32
+    pass on the scores, divided by N before exp), output 1e-4 relative to max|out| (3xTF32 product)."""
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    H, D = 12, 64
+    rng = np.random.default_rng(B * 1000 + N)
+    qkv = (rng.normal(size=(B, N, 3 * H * D)) * 2).astype(np.float32)
+    x = gpu.from_numpy(qkv)
+    lib = gpu._lib.load()
+    p_dev = gpu.make_tensor([B, H, N, N])
+    gpu._lib.check(lib.wf2cu_attn_heads_softmax(x.vec.ptr, 0, B, N, H, D, float(N), p_dev.vec.ptr, 0))
+    o_dev = gpu.make_tensor([B, N, H * D])
+    gpu._lib.check(lib.wf2cu_attn_pv(p_dev.vec.ptr, 0, x.vec.ptr, 0, B, N, H, D, o_dev.vec.ptr, 0))
+    p, out = p_dev.to_numpy(), o_dev.to_numpy()
+    p64, out64 = _attention_truth(qkv, H)
+    np.testing.assert_allclose(p.sum(axis=1), 1.0, rtol=0, atol=1e-6)            # normalised over the heads axis
+    rel_p = np.abs(p - p64).max() / np.abs(p64).max()
+    rel_o = np.abs(out - out64).max() / np.abs(out64).max()
+    assert rel_p <= 1e-4, rel_p
+    assert rel_o <= 1e-4, rel_o
+    # the product alone, on the device's own weights: 3xTF32 grade
+    pv64 = O.merge_heads(p.astype(np.float64) @ O.split_heads(qkv.astype(np.float64), "V", H))
+    assert np.abs(out - pv64).max() / np.abs(pv64).max() <= 2e-5
+    # and the whole block against the node sequence
+    old = g.FUSE_ATTENTION
+    try:
+        g.FUSE_ATTENTION = False
+        nodes = g.self_attention(x, H).to_numpy()
+        g.FUSE_ATTENTION = True
+        fused = g.self_attention(x, H).to_numpy()
+    finally:
+        g.FUSE_ATTENTION = old
+    np.testing.assert_array_equal(fused, out)
+    assert np.abs(nodes - out64).max() / np.abs(out64).max() <= 1e-4
+    assert np.abs(fused - nodes).max() / np.abs(out64).max() <= 1e-4
+
+
+@pytest.mark.gpu
+def test_attention_divisor_not_a_power_of_two_and_unsupported_shapes(gpu):
+    """divisor = 384 takes the true-division path (`!div` is a divide, x * (1/384) would differ in the last bit); shapes the
+    kernels do not take are declined with WF2CU_ERR_UNSUPPORTED so the host issues the nodes."""
+    H, D, B, N = 12, 64, 1, 384
+    rng = np.random.default_rng(9)
+    qkv = (rng.normal(size=(B, N, 3 * H * D)) * 2).astype(np.float32)
+    x = gpu.from_numpy(qkv)
+    lib = gpu._lib.load()
+    p_dev = gpu.make_tensor([B, H, N, N])
+    gpu._lib.check(lib.wf2cu_attn_heads_softmax(x.vec.ptr, 0, B, N, H, D, 384.0, p_dev.vec.ptr, 0))
+    p64, _ = _attention_truth(qkv, H)
+    assert np.abs(p_dev.to_numpy() - p64).max() / np.abs(p64).max() <= 1e-4
+    y = gpu.make_tensor([1, 100, 3 * 64])
+    q = gpu.make_tensor([1, 4, 100, 100])
+    assert lib.wf2cu_attn_heads_softmax(y.vec.ptr, 0, 1, 100, 4, 16, 100.0, q.vec.ptr, 0) == 3
+    assert lib.wf2cu_attn_pv(q.vec.ptr, 0, y.vec.ptr, 0, 1, 100, 4, 16, y.vec.ptr, 0) == 3
+    assert lib.wf2cu_attn_heads_softmax(x.vec.ptr, 0, B, 200, H, D, 200.0, p_dev.vec.ptr, 0) == 3     # seq not a multiple of 128

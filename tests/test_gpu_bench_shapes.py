@@ -279,3 +279,52 @@ def test_fused_compiled_ragged_tail_broadcast_scalar_and_fallback(gpu, L):
     a = gpu.ops.sigmoid(half).to_numpy()
     assert _fused_path(gpu) == 1
     np.testing.assert_array_equal(a, s[:, ::2])
+
+
+# ------------------------------------------------------------------ the raw-operand tcgen05 kernel (csrc/gemm_raw.cuh), forced
+@pytest.mark.parametrize("tb", [False, True])
+@pytest.mark.parametrize("m,n,k", [(128, 256, 16), (130, 70, 33), (300, 700, 100), (1000, 517, 333), (257, 255, 48), (1024, 256, 784),
+                                   (64, 64, 32), (2048, 768, 768)])
+def test_matmul_raw_operand_kernel(gpu, tb, m, n, k):
+    """mode 7: A (K-major) arrives as raw fp32 tiles by TMA, its lo plane is made on the SM; B likewise when it is K-major
+    (`(!t b)`), through the transposing split otherwise.  Ragged m / n / k (TMA zero-fills past the edges), against fp64."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(m + 3 * n + 5 * k + int(tb))
+    A = rng.uniform(-1, 1, size=(m, k)).astype(np.float32)
+    B = rng.uniform(-1, 1, size=((n, k) if tb else (k, n))).astype(np.float32)
+    ga, gb = gpu.from_numpy(A), gpu.from_numpy(B)
+    truth = A.astype(np.float64) @ (B.T if tb else B).astype(np.float64)
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(7))
+    try:
+        if k % 4:                                   # rows not 16-byte aligned: the kernel declines, loudly
+            with pytest.raises(gpu.Wf2CudaError):
+                gpu.ops.matmul(ga, gpu.ops.t(gb) if tb else gb)
+            return
+        out = gpu.ops.matmul(ga, gpu.ops.t(gb) if tb else gb).to_numpy()
+        assert _last_path(gpu) == 8
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    assert np.abs(out - truth).max() <= 2e-5 * np.abs(truth).max()
+
+
+def test_matmul_raw_operand_kernel_batched_bias_relu(gpu):
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(77)
+    A = rng.uniform(-1, 1, size=(3, 300, 80)).astype(np.float32)
+    W = rng.uniform(-1, 1, size=(520, 80)).astype(np.float32)        # shared by the batch, K-major: raw on both sides
+    A2 = rng.uniform(-1, 1, size=(1536, 1024)).astype(np.float32)
+    B2 = rng.uniform(-1, 1, size=(1024, 1000)).astype(np.float32)
+    bias = rng.uniform(-1, 1, size=(1000,)).astype(np.float32)
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(7))
+    try:
+        r = gpu.ops.matmul(gpu.from_numpy(A), gpu.ops.t(gpu.from_numpy(W))).to_numpy()
+        ga, gb, gbias = gpu.from_numpy(A2), gpu.from_numpy(B2), gpu.from_numpy(bias)
+        plain = gpu.ops.matmul(ga, gb).to_numpy()
+        fused = gpu.ops.matmul(ga, gb, bias=gbias, relu=True).to_numpy()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    np.testing.assert_allclose(r, A.astype(np.float64) @ W.T.astype(np.float64), rtol=0, atol=2e-4)
+    truth = A2.astype(np.float64) @ B2.astype(np.float64)
+    assert np.abs(plain - truth).max() <= 2e-5 * np.abs(truth).max()
+    want = plain + bias[None, :]
+    np.testing.assert_array_equal(fused, want * (want > 0))
