@@ -22,6 +22,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
 // gemm_tc.cu: one-launch tcgen05 kernel for small problems (in-kernel hi/lo split, cluster split-K, fused epilogue)
 int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                  float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act);
+bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch);
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                       float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
                       const float* mask, int64_t ldmask);
@@ -661,7 +662,7 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (out of range)", who);
   }
   if (mode == 7 || (mode == 0 && raw_auto() && !trans_a && 2.0 * (double)m * (double)n * (double)k * (double)batch >= 1.0e9 && m >= 64 && n >= 64 &&
-                    k >= 32)) {
+                    k >= 32 && gemm_raw_preferred(trans_b ? 1 : 0, m, n, k, batch))) {
     // A is K-major: raw fp32 tiles by TMA, lo planes made on the SM — no operand pre-pass (gemm_raw.cuh)
     const int r = gemm_raw_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, bias, act);
     if (r < 0) return -r;

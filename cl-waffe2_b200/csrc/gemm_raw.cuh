@@ -67,9 +67,10 @@ constexpr int RA_H = 12, RA_D = 64, RA_E = RA_H * RA_D;
 struct RawAttnArgs {
   int B, N, tiles_i, tiles_j;  // tiles of 128 queries x 256 keys
   float scale;                 // log2(e) / divisor
+  int dbg;                     // measurement switches (WF2CU_ATTN_DBG): 1 no P stores, 2 no pass-2 arithmetic, 4 no pass-1 arithmetic
 };
 struct RawAttnJob {
-  static constexpr int kEpiWarps = 16, kEpiBytes = 2 * 2048, kSubTiles = 2 * RA_H;
+  static constexpr int kEpiWarps = 16, kEpiBytes = 2 * 1024, kSubTiles = 2 * RA_H;
   RawAttnArgs a;
   __device__ __forceinline__ int items() const { return a.B * a.tiles_i * a.tiles_j; }
   __device__ __forceinline__ void where(int w, int& jt, int& it, int& b) const {
@@ -273,7 +274,9 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
               tc_ld16(tbase + c0, v);
               tc_ld_wait();
 #pragma unroll
-              for (int c = 0; c < 16; ++c) den[c0 + c] = __fadd_rn(den[c0 + c], raw_attn_exp<POW2>(__uint_as_float(v[c]), a.scale));
+              if (!(a.dbg & 4))
+#pragma unroll
+                for (int c = 0; c < 16; ++c) den[c0 + c] = __fadd_rn(den[c0 + c], raw_attn_exp<POW2>(__uint_as_float(v[c]), a.scale));
             }
             tc_fence_before();
             __syncwarp();
@@ -286,33 +289,30 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           } else {
             const int h = sub - RA_H;
 #pragma unroll
-            for (int c0 = 0; c0 < COLS; c0 += 16) {
-              uint32_t v[16];
-              tc_ld16(tbase + c0, v);
-              uint8_t* blk = slot + which * 2048;
+            for (int c0 = 0; c0 < COLS; c0 += 8) {
+              uint32_t v[8];
+              tc_ld8(tbase + c0, v);
+              uint8_t* blk = slot + which * 1024;
               which ^= 1;
               if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
               tc_ld_wait();
-              if (c0 + 16 >= COLS) {                                  // the accumulator is in registers now
+              if (c0 + 8 >= COLS) {                                   // the accumulator is in registers now
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&acc_empty[as]);
               } else {
                 __syncwarp();
               }
-              uint8_t* mine = blk + lane * 64;                       // SWIZZLE_64B: 16-byte chunk j of row r at j ^ ((r >> 1) & 3)
+              if (a.dbg & 2) continue;
+              float p[8];
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                float4 p;
-                p.x = __fmul_rn(raw_attn_exp<POW2>(__uint_as_float(v[4 * j]), a.scale), den[c0 + 4 * j]);
-                p.y = __fmul_rn(raw_attn_exp<POW2>(__uint_as_float(v[4 * j + 1]), a.scale), den[c0 + 4 * j + 1]);
-                p.z = __fmul_rn(raw_attn_exp<POW2>(__uint_as_float(v[4 * j + 2]), a.scale), den[c0 + 4 * j + 2]);
-                p.w = __fmul_rn(raw_attn_exp<POW2>(__uint_as_float(v[4 * j + 3]), a.scale), den[c0 + 4 * j + 3]);
-                *reinterpret_cast<float4*>(mine + ((j ^ ((lane >> 1) & 3)) << 4)) = p;
-              }
+              for (int c = 0; c < 8; ++c) p[c] = __fmul_rn(raw_attn_exp<POW2>(__uint_as_float(v[c]), a.scale), den[c0 + c]);
+              uint8_t* mine = blk + lane * 32;                       // SWIZZLE_32B: 16-byte chunk j of row r at j ^ ((r >> 2) & 1)
+              *reinterpret_cast<float4*>(mine + ((0 ^ ((lane >> 2) & 1)) << 4)) = make_float4(p[0], p[1], p[2], p[3]);
+              *reinterpret_cast<float4*>(mine + ((1 ^ ((lane >> 2) & 1)) << 4)) = make_float4(p[4], p[5], p[6], p[7]);
               asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
               __syncwarp();
-              if (lane == 0) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
+              if (lane == 0 && !(a.dbg & 1)) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
             }
           }
           if (++as == 2) { as = 0; aph ^= 1; }

@@ -1081,6 +1081,26 @@ static bool raw_operand_ok(const float* p, int64_t ld, int64_t bstride, int64_t 
   return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld & 3) == 0 && (nbatch <= 1 || ((bstride & 3) == 0 && bstride > 0));
 }
 
+// Auto rule: raw-operand kernel or planes kernels?  Cycle model fitted on B200 (scripts/gemm_raw_bench.py, profiles/r02_gemm_raw.md):
+// per k-block of 16 a tile costs 1180 cycles on the raw kernel (shared-memory bound: TMA writes + converter traffic + operand reads
+// of six 128x256x8 MMAs), 1110 / 1850 / 1500 on the 128x256 / 256x256 / 256x192 planes kernels; the 256-row tiles expose their
+// epilogue; an operand pre-pass moves 12 bytes per element at ~4.5 TB/s plus a launch.  The raw kernel skips A's pre-pass always
+// and B's when B is K-major.  2048^3: raw 88 us vs 101; 4096^3: 654 vs 571; 8192x2304x768: 124 vs 132; 8192x768x3072: 236 vs 210.
+bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch) {
+  const double sms = (double)S().sm_count;
+  auto waves = [&](int64_t tiles) { return (double)((tiles * batch + (int64_t)sms - 1) / (int64_t)sms); };
+  auto presplit = [&](int64_t rows) { return (double)rows * (double)k * (double)batch * 12.0 / 4.5e12 * 1.9e9 + 6000.0; };
+  const double nkb = (double)((k + 15) / 16);
+  const int64_t t128 = ((m + 127) / 128) * ((n + 255) / 256), t256 = ((m + 255) / 256) * ((n + 255) / 256), t192 = ((m + 255) / 256) * ((n + 191) / 192);
+  const double raw = waves(t128) * nkb * 1180.0 + 8000.0 + (tb ? 0.0 : presplit(n));
+  double planes = waves(t128) * nkb * 1110.0;
+  const double p256 = waves(t256) * (nkb * 1850.0 + 10000.0), p192 = waves(t192) * (nkb * 1500.0 + 8000.0);
+  if (p256 < planes) planes = p256;
+  if (p192 < planes) planes = p192;
+  planes += presplit(m) + presplit(n);
+  return raw <= planes;
+}
+
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
 int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                  float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act) {
@@ -1184,7 +1204,7 @@ int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor,
     cuuint64_t lstrides[2] = {(cuuint64_t)(2 * RA_E) * 4, (cuuint64_t)N * 2 * RA_E * 4};
     cuuint64_t pd[4] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)RA_H, (cuuint64_t)B};
     cuuint64_t ps[3] = {(cuuint64_t)N * 4, (cuuint64_t)N * N * 4, (cuuint64_t)RA_H * N * N * 4};
-    cuuint32_t pb[4] = {16, 32, 1, 1};
+    cuuint32_t pb[4] = {8, 32, 1, 1};
     CUresult r[5];
     r[0] = g_encode(&mq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qkv, dims, strides, boxq, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1199,11 +1219,13 @@ int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor,
                       CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     }
     r[4] = g_encode(&mp, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)P, pd, ps, pb, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     for (int i = 0; i < 5; ++i)
       if (r[i] != CUDA_SUCCESS) return set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(attention scores, map %d) failed (%d)", i, (int)r[i]);
   }
-  RawAttnJob job{RawAttnArgs{B, N, (N + RM - 1) / RM, (N + RN - 1) / RN, (float)(1.4426950408889634 / (double)divisor)}};
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("WF2CU_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
+  RawAttnJob job{RawAttnArgs{B, N, (N + RM - 1) / RM, (N + RN - 1) / RN, (float)(1.4426950408889634 / (double)divisor), dbg}};
   const int items = job.a.B * job.a.tiles_i * job.a.tiles_j, sms = S().sm_count;
   const int grid = items < sms ? items : sms;
   if (planes) WF2_CUDA(launch_pdl(gemm_raw_kernel<RawAttnJob, false, false, true>, dim3(grid), dim3(raw_threads(RawAttnJob::kEpiWarps, false)), bytes,

@@ -5,6 +5,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstdlib>
 #include "tc.cuh"
 using namespace wf2;
 namespace wf2 { int set_error(int, const char*, ...) { return 1; } EncodeTiledFn tensor_map_encoder() { return nullptr; } float* tc_workspace(size_t) { return nullptr; } }
@@ -14,8 +15,11 @@ __device__ __forceinline__ void mma_ts(uint32_t d, uint32_t a_tmem, uint64_t db,
                ::"r"(d), "r"(a_tmem), "l"(db), "r"(idesc), "r"(acc) : "memory");
 }
 
-// n: MMA N; nacc: accumulators rotated through (each n columns wide); ts: A from TMEM; iters MMAs in total
-__global__ void __launch_bounds__(128) rate_kernel(int n, int nacc, int ts, int iters, long long* out) {
+// N: MMA N; NACC: accumulators rotated through (each N columns wide); TS: A from TMEM; iters MMAs in total.
+// The issue loop is unrolled 16 x with compile-time operands: the first version of this test computed `i % nacc` per MMA and
+// measured its own integer division (188 cycles per iteration whatever N was).
+template <int N, int NACC, int TS>
+__global__ void __launch_bounds__(128) rate_kernel(int iters, long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];      // A tile 128 x 32 (16 KiB) | B tile 256 x 32 (32 KiB)
   __shared__ uint64_t bar;
   __shared__ uint32_t tslot;
@@ -31,14 +35,17 @@ __global__ void __launch_bounds__(128) rate_kernel(int n, int nacc, int ts, int 
   const uint32_t tb = tslot;
   if (threadIdx.x == 0) {
     const uint64_t da = make_desc_sw128(smem_u32(smem)), db = make_desc_sw128(smem_u32(smem + 16384));
-    const uint32_t idesc = idesc_tf32_mn(128, n);
-    const uint32_t acol = 448;                            // A operand columns when ts (accumulators use < 448)
+    constexpr uint32_t idesc = idesc_tf32_mn(128, N);
+    constexpr uint32_t acol = 448;                        // A operand columns when TS (accumulators use < 448)
     long long t0 = clock64();
-    for (int i = 0; i < iters; ++i) {
-      const uint32_t d = tb + (uint32_t)((i % nacc) * n);
-      const uint64_t adv = (uint64_t)(((i & 3) * 32) >> 4);
-      if (ts) mma_ts(d, tb + acol + (i & 3) * 8, db + adv, idesc, 1);
-      else tc_mma_tf32(d, da + adv, db + adv, idesc, 1);
+    for (int i = 0; i < iters; i += 16) {
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        const uint32_t d = tb + (uint32_t)((u % NACC) * N);
+        const uint64_t adv = (uint64_t)(((u & 3) * 32) >> 4);
+        if (TS) mma_ts(d, tb + acol + (u & 3) * 8, db + adv, idesc, 1);
+        else tc_mma_tf32(d, da + adv, db + adv, idesc, 1);
+      }
     }
     tc_commit(&bar);
     mbar_wait(&bar, 0);
@@ -49,25 +56,30 @@ __global__ void __launch_bounds__(128) rate_kernel(int n, int nacc, int ts, int 
   if (warp == 0) { tc_fence_after(); asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tb), "n"(512) : "memory"); }
 }
 
+template <int N, int NACC>
+static void run(long long* d, int iters) {
+  double c[2];
+  for (int ts = 0; ts < 2; ++ts) {
+    for (int rep = 0; rep < 2; ++rep) {
+      if (ts) rate_kernel<N, NACC, 1><<<1, 128, 49152 + 1024>>>(iters, d);
+      else    rate_kernel<N, NACC, 0><<<1, 128, 49152 + 1024>>>(iters, d);
+    }
+    long long h; cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { printf("CUDA error %s\n", cudaGetErrorString(e)); exit(1); }
+    c[ts] = (double)h / iters;
+  }
+  printf("%6d %6d %10.1f %10.1f   (%d)\n", N, NACC, c[0], c[1], 128 * N / 256);
+}
+
 int main() {
   long long* d; cudaMalloc(&d, 8);
-  cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 + 1024);
+#define ATTR(N, A) cudaFuncSetAttribute(rate_kernel<N, A, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 + 1024); \
+                   cudaFuncSetAttribute(rate_kernel<N, A, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 + 1024);
+  ATTR(16, 1) ATTR(16, 4) ATTR(32, 1) ATTR(32, 4) ATTR(64, 1) ATTR(64, 4) ATTR(128, 1) ATTR(128, 2) ATTR(256, 1)
   const int iters = 4096;
-  printf("cycles per tcgen05.mma.kind::tf32 128 x N x 8 (one issuing thread, %d MMAs, back to back)\n", iters);
-  printf("%6s %6s %10s %10s   (floor 128 N / 256)\n", "N", "nacc", "A in smem", "A in tmem");
-  for (int n : {16, 32, 64, 128, 256}) {
-    for (int nacc : {1, 2, 4}) {
-      if (n * nacc > 448) continue;
-      double c[2];
-      for (int ts = 0; ts < 2; ++ts) {
-        rate_kernel<<<1, 128, 49152 + 1024>>>(n, nacc, ts, iters, d);
-        rate_kernel<<<1, 128, 49152 + 1024>>>(n, nacc, ts, iters, d);
-        long long h; cudaError_t e = cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) { printf("CUDA error %s\n", cudaGetErrorString(e)); return 1; }
-        c[ts] = (double)h / iters;
-      }
-      printf("%6d %6d %10.1f %10.1f   (%d)\n", n, nacc, c[0], c[1], 128 * n / 256);
-    }
-  }
+  printf("cycles per tcgen05.mma.kind::tf32 128 x N x 8 (one issuing thread, %d MMAs back to back, unrolled issue)\n", iters);
+  printf("%6s %6s %10s %10s   (128 N / 256)\n", "N", "nacc", "A in smem", "A in tmem");
+  run<16, 1>(d, iters); run<16, 4>(d, iters); run<32, 1>(d, iters); run<32, 4>(d, iters); run<64, 1>(d, iters); run<64, 4>(d, iters);
+  run<128, 1>(d, iters); run<128, 2>(d, iters); run<256, 1>(d, iters);
   return 0;
 }
