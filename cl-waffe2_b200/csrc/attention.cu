@@ -10,16 +10,17 @@
 //       reads Q and K straight from the dense (B N 3E) activation of the QKV projection (both are K-major there: no
 //       head-split copies, no transposes, no hi / lo planes in global memory) and writes P ONCE.  It runs on the raw-operand
 //       3xTF32 main loop of MatmulNode (gemm_raw.cuh: 128 queries x 256 keys per tile, 128x256x8 MMAs) with two epilogues:
-//         pass 1  den[b,i,j] = sum over the 12 heads (in head order, like `!sum`) of exp(s / N), accumulated in registers across
-//                 the 12 head sub-tiles of a position and stored once (33 MB at B = 8, N = 1024, L2 resident)
+//         pass 1  den[i,j] = sum over the 12 heads (in head order, like `!sum`) of exp(s / N), accumulated in registers across
+//                 the 12 head sub-tiles of a (128 queries x 256 keys) position — it never leaves the SM
 //         pass 2  the product again (Q.K is 13 GFLOP per layer: cheap next to a second trip of the 402 MB tensor through HBM),
-//                 p = exp(s / N) / den, 32 x 8 blocks through the bulk-copy engine into P
+//                 p = exp(s / N) * RN(1 / den), 32 x 8 blocks through the bulk-copy engine into P
 //       How it got there (all measured on B200, B = 8, N = 1024, per layer):  the heads-axis softmax couples the 12 heads of
 //       one (i, j), so the first design kept all 12 score tiles of a (128 x 32) tile in TMEM: 144 us with ONE truncated TF32
 //       pass (error 3e-4 on P for N(0, 2) inputs: not acceptable for a library kernel), 271 us with the compensated three —
 //       whether the lo planes came from global memory, from converter warps, or the Q operand lived in tensor memory (294 us).
-//       scripts/micro/mma_rate_test.cu explains it: a kind::tf32 MMA with M = 128 costs the same whatever N is, so 288 MMAs of
-//       N = 32 per tile were the bound.  With N = 256 per MMA the products of BOTH passes cost less than one pass of that.
+//       scripts/micro/mma_rate_test.cu: a kind::tf32 MMA with M = 128 costs max(45, N / 2) cycles, so the 288 N = 32 MMAs of a
+//       tile ran at a third of the tensor rate and the 16-warp exp/divide epilogue could not hide behind them.  With N = 256
+//       per MMA the products of BOTH passes together take 147 us of main loop; the whole kernel runs in 194 us.
 //   wf2cu_attn_pv : out[b,i,h*64:(h+1)*64] = sum_j P[b,h,i,j] V_h[j,:], error-compensated 3xTF32 (as MatmulNode), written
 //       in the merged-heads layout (B N E) that merge-heads produces (no permute copies).  P tiles arrive by TMA as RAW
 //       fp32; converter warps move each tile into tensor memory as the A operand (raw bits = the TF32 hi plane, lo = x -

@@ -11,6 +11,7 @@
 //                  classifier head).
 #include <stdlib.h>
 #include "common.cuh"
+#include "math.cuh"
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
@@ -18,10 +19,12 @@ namespace wf2 {
 
 // implemented in gemm_tc.cu; returns 1 when it handled the problem, 0 when it declines, <0 error
 int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B,
-                int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act);
+                int64_t ldb, float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act,
+                const float* res, int64_t ldres);
 // gemm_tc.cu: one-launch tcgen05 kernel for small problems (in-kernel hi/lo split, cluster split-K, fused epilogue)
 int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
-                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act);
+                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act, const float* res,
+                 int64_t ldres);
 bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch);
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                       float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
@@ -35,6 +38,7 @@ struct GemmArgs {
   int ta, tb;
   // fused epilogue (wf2cu_gemm_ex): v = acc [+ bias[col]] ; [v = v * (v > 0)] ; [v = v * (mask[row, col] > 0)]
   const float* bias; const float* mask; int64_t ldmask; int act;
+  const float* res = nullptr; int64_t ldres = 0;     // [v = v + res[row, col]]  (a residual connection riding on the projection)
 };
 
 // `!relu` is x * (where x > 0 then 1 else 0) (nn/activation.lisp:11-26): a true multiply, so a negative
@@ -42,6 +46,8 @@ struct GemmArgs {
 __device__ __forceinline__ float epilogue(const GemmArgs& g, float v, int64_t gm, int64_t gn) {
   if (g.bias) v = __fadd_rn(v, g.bias[gn]);
   if (g.act == 1) v = __fmul_rn(v, v > 0.f ? 1.f : 0.f);
+  else if (g.act == 2) v = gelu_tanh_ref(v);
+  if (g.res) v = __fadd_rn(g.res[gm * g.ldres + gn], v);
   if (g.mask) v = __fmul_rn(v, g.mask[gm * g.ldmask + gn] > 0.f ? 1.f : 0.f);
   return v;
 }
@@ -621,7 +627,7 @@ int wf2cu_gemm_set_mode(int mode) {
 static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
                      const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc, int64_t batch,
                      int64_t stride_a, int64_t stride_b, int64_t stride_c, const float* bias, int act, const float* mask,
-                     int64_t ldmask, const char* who) {
+                     int64_t ldmask, const char* who, const float* res = nullptr, int64_t ldres = 0) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(A && B && C, "%s: null operand", who);
   WF2_CHECK(m >= 0 && n >= 0 && k >= 0 && batch >= 0, "%s: negative extent", who);
@@ -635,7 +641,20 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   const bool epi = bias || act || mask;
   WF2_CHECK(!epi || batch == 1, "%s: the fused epilogue takes unbatched operands (batch=%lld)", who, (long long)batch);
   GemmArgs g{a, b, c, m, n, k, lda, ldb, ldc, stride_a, stride_b, stride_c, trans_a ? 1 : 0, trans_b ? 1 : 0, bias, mask, ldmask, act};
+  g.res = res; g.ldres = ldres;
   const int mode = S().gemm_mode;
+  // gelu / residual epilogues ride in the persistent tensor-core kernels (planes and raw); every other path computes
+  // C = A.B + bias first and applies the rest in one element-wise pass (same operations, same order)
+  const bool ext = res != nullptr || act == 2;
+  auto tail_pass = [&]() -> int {
+    GemmArgs e = g;
+    e.bias = nullptr;
+    int64_t grid = (m * n + 255) / 256;
+    const int64_t cap = (int64_t)S().sm_count * 8;
+    if (grid > cap) grid = cap;
+    gemm_epilogue_kernel<<<(unsigned)grid, 256, 0, S().stream>>>(e);
+    return post_launch("wf2cu_gemm_ex2(epilogue)");
+  };
   // auto: 50 MFLOP..2.5 GFLOP -> fused tcgen05 kernel (38.5 vs 44.1 us on 1024^3, 89.5 vs 55.6 us on 1280^3; 14.6 vs 22.3 us on 1024x256x784, 8.6 vs 10.2 us on 1024x256x256;
   // below 50 MFLOP its ~5 us floor loses to the SIMT split-K kernel: 7.9 vs 6.9 us on 1024x10x256; gpurun_out/gemm_small5.log)
   // mode: 0 auto | 1 fp32 SIMT | 2 tcgen05 3xTF32 (planes + persistent kernel) | 3 tcgen05 1xTF32 | 4 tcgen05 fused small kernel
@@ -646,6 +665,14 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     const int r = sgemm_skinny_tn_try(g, batch);
     if (r < 0) return -r;
     if (r == 1) { S().gemm_last_path = WF2CU_GEMM_PATH_SIMT_SKINNY; return 0; }
+  }
+  if (ext && mode != 7 && mode != 2 && mode != 5 && mode != 6 &&
+      !(mode == 0 && 2.0 * (double)m * (double)n * (double)k * (double)batch >= 2.5e9 && m >= 64 && n >= 64 && k >= 32)) {
+    // small problems: the plain product (+ bias) on whatever kernel auto picks, then the rest of the epilogue as one pass
+    const int rc = gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, batch, stride_a, stride_b, stride_c, bias, 0,
+                             nullptr, 0, who);
+    if (rc) return rc;
+    return tail_pass();
   }
   {
     const double flops = 2.0 * (double)m * (double)n * (double)k;
@@ -664,11 +691,11 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   if (mode == 7 || (mode == 0 && raw_auto() && !trans_a && 2.0 * (double)m * (double)n * (double)k * (double)batch >= 1.0e9 && m >= 64 && n >= 64 &&
                     k >= 32 && gemm_raw_preferred(trans_b ? 1 : 0, m, n, k, batch))) {
     // A is K-major: raw fp32 tiles by TMA, lo planes made on the SM — no operand pre-pass (gemm_raw.cuh)
-    const int r = gemm_raw_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, bias, act);
+    const int r = gemm_raw_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, bias, act, res, ldres);
     if (r < 0) return -r;
     if (r == 1) {
       if (!mask) return 0;
-      g.bias = nullptr; g.act = 0;
+      g.bias = nullptr; g.act = 0; g.res = nullptr;
       int64_t grid = (m * n + 255) / 256;
       const int64_t cap = (int64_t)S().sm_count * 8;
       if (grid > cap) grid = cap;
@@ -679,11 +706,11 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   }
   if (mode != 1) {
     // bias and relu ride in the persistent kernel's epilogue; only the relu-backward mask needs its own pass
-    const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode, bias, act);
+    const int r = gemm_tc_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, mode, bias, act, res, ldres);
     if (r < 0) return -r;
     if (r == 1) {
       if (!mask) return 0;
-      g.bias = nullptr; g.act = 0;
+      g.bias = nullptr; g.act = 0; g.res = nullptr;
       int64_t grid = (m * n + 255) / 256;
       const int64_t cap = (int64_t)S().sm_count * 8;
       if (grid > cap) grid = cap;
@@ -691,6 +718,12 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
       return post_launch("wf2cu_gemm_ex(epilogue)");
     }
     if (mode >= 2) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: tensor-core path forced but declined this shape/alignment", who);
+  }
+  if (ext) {
+    const int rc = gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, batch, stride_a, stride_b, stride_c, bias, 0,
+                             nullptr, 0, who);
+    if (rc) return rc;
+    return tail_pass();
   }
   WF2_CHECK(batch < 65536, "%s: batch %lld too large for the SIMT path", who, (long long)batch);
   {
@@ -725,6 +758,16 @@ int wf2cu_gemm_ex(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, con
   return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
                    bias ? (const float*)bias + bias_off : nullptr, act, mask ? (const float*)mask + mask_off : nullptr, ldmask,
                    "wf2cu_gemm_ex");
+}
+
+int wf2cu_gemm_ex2(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
+                   const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc,
+                   const void* bias, int64_t bias_off, int act, const void* residual, int64_t res_off, int64_t ldres) {
+  WF2_CHECK(act >= 0 && act <= 2, "wf2cu_gemm_ex2: act %d not in {0 none, 1 relu, 2 gelu}", act);
+  WF2_CHECK(!residual || ldres >= n, "wf2cu_gemm_ex2: ldres %lld < n %lld", (long long)ldres, (long long)n);
+  return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
+                   bias ? (const float*)bias + bias_off : nullptr, act, nullptr, 0, "wf2cu_gemm_ex2",
+                   residual ? (const float*)residual + res_off : nullptr, ldres);
 }
 
 }  // extern "C"

@@ -14,17 +14,18 @@
 // two 256-column accumulators in TMEM so the epilogue of a tile overlaps the main loop of the next:
 //   warp 0      TMA producer       warp 1      MMA issuer (6 x tcgen05.mma 128x256x8 per k-block)
 //   warps 2-5   converters         warps 6-..  epilogue (4 x CG warps: TMEM lane quarter x column group)
-// Measured on B200 (scripts/micro/mma_rate_test.cu): a kind::tf32 MMA with M = 128 takes the same ~130-190 cycles for any
-// N <= 256, so tiles are as wide as the instruction allows — which is also why the GPT-2 example's attention scores run
-// through this main loop (N = 256 keys per MMA) instead of keeping all 12 heads of a narrow tile in TMEM (N = 32 per MMA:
-// 271 us per layer, MMA-count bound).
+// Measured on B200 (scripts/micro/mma_rate_test.cu): a kind::tf32 MMA with M = 128 costs max(45, N / 2) cycles — N = 256 runs
+// at the nominal rate (128 cycles), anything below N = 96 pays the 45-cycle floor — so tiles are as wide as the instruction
+// allows.  That is also why the GPT-2 example's attention scores run through this main loop (N = 256 keys per MMA) instead of
+// keeping all 12 heads of a narrow tile in TMEM (N = 32 per MMA, 288 MMAs per 128 x 32 tile: 271 us per layer).
 //
 // The work list and the epilogue are template parameters:
 //   RawGemmJob      MatmulNode: C = op(A) . op(B) (+ bias, relu), C through bulk tensor stores
 //   RawAttnJob      the GPT-2 example's attention weights: per (batch, 128 queries, 256 keys) 24 sub-tiles — the 12 heads once
 //                   to accumulate den = sum_h exp((Q_h . K_h) / N) in registers (head order), then the 12 heads again to write
-//                   P = exp(...) / den.  Both operands arrive as planes (raw = hi, lo pre-split once per call: 50 MB) — with 16
-//                   exp-bound epilogue warps on the SM, converter warps were starved of issue slots (measured: 328 us).
+//                   P = exp(...) / den.  Raw operands + converter warps by default (194 us per layer at B = 8, N = 1024);
+//                   WF2CU_ATTN_PLANES=1 pre-splits the lo planes instead (184 us + a 16 us split launch).  Ablation
+//                   (WF2CU_ATTN_DBG, profiles/r02_attention.md): main loop alone 147 us, pass-2 arithmetic + staging +26, P stores +22.
 #pragma once
 
 namespace wf2 {
@@ -238,13 +239,13 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
           tc_ld_wait();
           tc_ld32(tbase + (c + 1) * 32, v1);
           int col0 = nt * RN + c * 32;
-          if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
+          if (col0 < a.n) tc_epilogue32(a, v0, mt * RM + q * 32, col0, lane);
           if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, mt * RM + q * 32, col0, b, lane);
           else tc_store32(a, cbase, stage, v0, mt * RM + q * 32, col0, lane);
           tc_ld_wait();
           if (c + 2 < RN / 32) tc_ld32(tbase + (c + 2) * 32, v0);
           col0 += 32;
-          if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
+          if (col0 < a.n) tc_epilogue32(a, v1, mt * RM + q * 32, col0, lane);
           if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, mt * RM + q * 32, col0, b, lane);
           else tc_store32(a, cbase, stage, v1, mt * RM + q * 32, col0, lane);
         }

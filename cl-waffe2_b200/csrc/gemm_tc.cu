@@ -132,14 +132,16 @@ struct TcArgs {
   int c_vec;             // C rows are 16-byte aligned -> 128-bit stores
   int a_bcast, b_bcast;  // operand shared by every batch index (batch stride 0): one plane set
   const float* bias;     // != NULL: C[r, c] = acc + bias[c]  (LinearLayer's bias add folded into the epilogue)
-  int act;               // 1: then C = C * (C > 0 ? 1 : 0)  (`!relu`)
+  int act;               // 1: then C = C * (C > 0 ? 1 : 0)  (`!relu`) ; 2: C = gelu(C) (`!gelu`, tanh form)
+  const float* res;      // != NULL: then C = res[r, c] + C  (a residual connection riding on the projection)
+  int64_t ldres;
   int c_tma;             // C goes out through map_c (bulk tensor stores) instead of per-lane global stores
 };
 
 // epilogue of the persistent kernels: 32 consecutive columns of one row per lane; same arithmetic as the separate
 // nodes.  Called by the whole warp (col0 is warp-uniform): lane j fetches bias[col0 + j] with one coalesced load
 // and the 32 values travel by shuffle — 32 dependent loads per lane made the epilogue longer than a K = 768 mainloop.
-__device__ __forceinline__ void tc_epilogue32(const TcArgs& a, uint32_t (&v)[32], int col0, int lane) {
+__device__ __forceinline__ void tc_epilogue32(const TcArgs& a, uint32_t (&v)[32], int row0, int col0, int lane) {
   if (a.bias) {
     const float mine = (col0 + lane < a.n) ? __ldg(a.bias + col0 + lane) : 0.f;
 #pragma unroll
@@ -149,6 +151,26 @@ __device__ __forceinline__ void tc_epilogue32(const TcArgs& a, uint32_t (&v)[32]
   if (a.act == 1) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) { const float x = __uint_as_float(v[j]); v[j] = __float_as_uint(__fmul_rn(x, x > 0.f ? 1.f : 0.f)); }
+  } else if (a.act == 2) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(gelu_tanh_ref(__uint_as_float(v[j])));
+  }
+  if (a.res && row0 + lane < a.m) {          // lane = row: 32 consecutive floats of the residual's row (whole 128-byte lines)
+    const float* r = a.res + (int64_t)(row0 + lane) * a.ldres + col0;
+    if (col0 + 32 <= a.n && (a.ldres & 3) == 0 && (reinterpret_cast<uintptr_t>(a.res) & 15) == 0 && (col0 & 3) == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 x = __ldg(reinterpret_cast<const float4*>(r) + j);
+        v[4 * j] = __float_as_uint(__fadd_rn(x.x, __uint_as_float(v[4 * j])));
+        v[4 * j + 1] = __float_as_uint(__fadd_rn(x.y, __uint_as_float(v[4 * j + 1])));
+        v[4 * j + 2] = __float_as_uint(__fadd_rn(x.z, __uint_as_float(v[4 * j + 2])));
+        v[4 * j + 3] = __float_as_uint(__fadd_rn(x.w, __uint_as_float(v[4 * j + 3])));
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < a.n) v[j] = __float_as_uint(__fadd_rn(__ldg(r + j), __uint_as_float(v[j])));
+    }
   }
 }
 
@@ -328,13 +350,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
         tc_ld_wait();
         tc_ld32(tbase + (c + 1) * 32, v1);
         int col0 = nt * TN + c * 32;
-        if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
+        if (col0 < a.n) tc_epilogue32(a, v0, mt * TM + q * 32, col0, lane);
         if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, mt * TM + q * 32, col0, b, lane);
         else tc_store32(a, cbase, stage, v0, mt * TM + q * 32, col0, lane);
         tc_ld_wait();
         if (c + 2 < TN / 32) tc_ld32(tbase + (c + 2) * 32, v0);
         col0 += 32;
-        if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
+        if (col0 < a.n) tc_epilogue32(a, v1, mt * TM + q * 32, col0, lane);
         if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, mt * TM + q * 32, col0, b, lane);
         else tc_store32(a, cbase, stage, v1, mt * TM + q * 32, col0, lane);
       }
@@ -485,13 +507,13 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           tc_ld_wait();
           tc_ld32(tbase + (c + 1) * 32, v1);
           int col0 = nt * T2N + c * 32;
-          if (col0 < a.n) tc_epilogue32(a, v0, col0, lane);
+          if (col0 < a.n) tc_epilogue32(a, v0, mt * T2M + h * 128 + q * 32, col0, lane);
           if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, mt * T2M + h * 128 + q * 32, col0, b, lane);
           else tc_store32(a, cbase, stage, v0, mt * T2M + h * 128 + q * 32, col0, lane);
           tc_ld_wait();
           if (c + 2 < T2N / 32) tc_ld32(tbase + (c + 2) * 32, v0);
           col0 += 32;
-          if (col0 < a.n) tc_epilogue32(a, v1, col0, lane);
+          if (col0 < a.n) tc_epilogue32(a, v1, mt * T2M + h * 128 + q * 32, col0, lane);
           if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, mt * T2M + h * 128 + q * 32, col0, b, lane);
           else tc_store32(a, cbase, stage, v1, mt * T2M + h * 128 + q * 32, col0, lane);
         }
@@ -964,7 +986,8 @@ static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t 
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
 int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
-                float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act) {
+                float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, int mode, const float* bias, int act,
+                const float* res, int64_t ldres) {
   // mode: 0 auto, 2 force 3xTF32, 3 force 1xTF32; bias / act: folded into the epilogue (the caller still runs the mask pass)
   if (k < 1 || m > (1 << 30) || n > (1 << 30) || k > (1 << 30) || batch > 65535) return 0;
   // the hi/lo plane workspace is one buffer: only the main stream may use it (a side branch of a compiled
@@ -1034,7 +1057,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
     t.a_bcast = a_nb == 1 ? 1 : 0;
     t.b_bcast = b_nb == 1 ? 1 : 0;
-    t.bias = bias; t.act = act; t.c_tma = c_tma;
+    t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     const int grid = (int)(total < S().sm_count ? total : S().sm_count);
     if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, GEMM_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
@@ -1055,7 +1078,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   t.a_bcast = a_nb == 1 ? 1 : 0;
   t.b_bcast = b_nb == 1 ? 1 : 0;
-  t.bias = bias; t.act = act; t.c_tma = c_tma;
+  t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
   const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
   const int grid = (int)(total < S().sm_count ? total : S().sm_count);
   gemm_tc_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, S().stream>>>(mah, mal, mbh, mbl, mc, t);
@@ -1103,7 +1126,8 @@ bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch) 
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
 int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
-                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act) {
+                 float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act, const float* res,
+                 int64_t ldres) {
   if (ta || k < 1 || m > (1 << 30) || n > (1 << 30) || k > (1 << 30) || batch > 65535 || S().branch != 0) return 0;
   const int a_nb = (sa == 0 || batch == 1) ? 1 : (int)batch;
   const int b_nb = (sb == 0 || batch == 1) ? 1 : (int)batch;
@@ -1144,7 +1168,7 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
   t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   t.a_bcast = a_nb == 1 ? 1 : 0;
   t.b_bcast = b_nb == 1 ? 1 : 0;
-  t.bias = bias; t.act = act;
+  t.bias = bias; t.act = act; t.res = res; t.ldres = ldres;
   t.c_tma = make_map_c(&mc, C, m, n, ldc, sc, batch);
   const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
   const int grid = (int)(total < S().sm_count ? total : S().sm_count);

@@ -80,6 +80,17 @@ __device__ __forceinline__ float pow_ref(float x, float n) {
   return (float)pow((double)x, (double)n);
 }
 
+// `!gelu` as cl-waffe2 writes it (nn/activation.lisp:61-66; examples/gpt-2/utils.lisp:129-137): 0.5 x (1 + tanh(c2 (x + c1 x^3))),
+// with exactly the operations and order of the fused program PGelu (fused.cu) / ops.gelu, so a GEMM epilogue that applies it
+// gives the same bits as the separate node.  c1 = 0.044715, c2 = (coerce (sqrt (/ 2.0 pi)) 'single-float).
+__device__ __forceinline__ float gelu_tanh_ref(float x) {
+  float t = __fmul_rn(__fmul_rn(x, x), x);
+  t = __fadd_rn(x, __fmul_rn(t, 0.044715f));
+  t = Unary<WF2CU_TANH>::apply(__fmul_rn(0.7978845608028654f, t));
+  t = __fadd_rn(1.0f, t);
+  return __fmul_rn(__fmul_rn(0.5f, x), t);
+}
+
 template <int OP> struct Binary;
 template <> struct Binary<WF2CU_ADD> { __device__ __forceinline__ static float apply(float a, float b) { return __fadd_rn(a, b); } };
 template <> struct Binary<WF2CU_SUB> { __device__ __forceinline__ static float apply(float a, float b) { return __fsub_rn(a, b); } };

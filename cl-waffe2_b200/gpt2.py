@@ -135,16 +135,31 @@ def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
     return merge_heads(a)
 
 
-def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor) -> CUDATensor:
-    """`(!matmul x w)` + `(!add (%transform b[i] -> [~ i]))` (model.lisp:118-120)."""
+FUSE_EPILOGUES = True
+
+
+def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor, gelu: bool = False, residual: Optional[CUDATensor] = None) -> CUDATensor:
+    """`(!matmul x w)` + `(!add (%transform b[i] -> [~ i]))` (model.lisp:118-120), optionally followed by the node the block
+    puts next: `!gelu` (after the first MLP projection) or the residual `(!add x ...)` (after both output projections)."""
     if x.dims() == 3 and x.is_contiguous() and not x.permuted_p():
         # W is shared by the batch, so (B N in) . (in out) is one (B*N in) . (in out) product; the bias add rides in the
-        # GEMM epilogue (wf2cu_gemm_ex — the MatMul + Add fusion of lisp/fusion.lisp), same arithmetic, one pass less
+        # GEMM epilogue (wf2cu_gemm_ex — the MatMul + Add fusion of lisp/fusion.lisp), same arithmetic, one pass less;
+        # FUSE_EPILOGUES: the gelu / residual node too (wf2cu_gemm_ex2), bit-identical to the separate nodes
         B_, N_, _ = x.shape
-        y = ops.matmul(reshape_contiguous(x, [B_ * N_, x.shape[2]]), w, bias=b)
-        return reshape_contiguous(y, [B_, N_, y.shape[1]])
-    y = ops.matmul(x, w)                                    # (B N in) . (in out): W shared by the batch
-    ops.add_(y, _bcast_last(b, y))
+        x2 = reshape_contiguous(x, [B_ * N_, x.shape[2]])
+        fuse = FUSE_EPILOGUES and (gelu or residual is not None) and (residual is None or (residual.is_contiguous() and not residual.permuted_p()))
+        if fuse:
+            r2 = reshape_contiguous(residual, [B_ * N_, residual.shape[2]]) if residual is not None else None
+            y = ops.matmul(x2, w, bias=b, gelu=gelu, residual=r2)
+            return reshape_contiguous(y, [B_, N_, y.shape[1]])
+        y = reshape_contiguous(ops.matmul(x2, w, bias=b), [B_, N_, w.shape[1]])
+    else:
+        y = ops.matmul(x, w)                                # (B N in) . (in out): W shared by the batch
+        ops.add_(y, _bcast_last(b, y))
+    if gelu:
+        ops.gelu(y, out=y)
+    if residual is not None:
+        y = ops.add(residual, y)
     return y
 
 
@@ -165,13 +180,10 @@ class GPT2Layer:
         h = layer_norm(x, self.ln_1_g, self.ln_1_b)
         qkv = _linear(h, self.attn_w, self.attn_b)
         a = self_attention(qkv, self.n_head)
-        a = _linear(a, self.proj_w, self.proj_b)
-        x = ops.add(x, a)                                   # residual
+        x = _linear(a, self.proj_w, self.proj_b, residual=x)            # (!add x (proj a)): residual
         h = layer_norm(x, self.ln_2_g, self.ln_2_b)
-        m = _linear(h, self.fc_w, self.fc_b)
-        ops.gelu(m, out=m)
-        m = _linear(m, self.fc_proj_w, self.fc_proj_b)
-        return ops.add(x, m)                                # residual
+        m = _linear(h, self.fc_w, self.fc_b, gelu=True)                 # (!gelu (fc h))
+        return _linear(m, self.fc_proj_w, self.fc_proj_b, residual=x)   # (!add x (fc-proj m)): residual
 
 
 class GPT2:

@@ -104,6 +104,10 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 		 (c :pointer) (c-off :int64) (ldc :int64)
 		 (bias :pointer) (bias-off :int64) (act :int)
 		 (mask :pointer) (mask-off :int64) (ldmask :int64)))
+(defwf2 gemm-ex2 ((trans-a :int) (trans-b :int) (m :int64) (n :int64) (k :int64)
+		  (a :pointer) (a-off :int64) (lda :int64) (b :pointer) (b-off :int64) (ldb :int64)
+		  (c :pointer) (c-off :int64) (ldc :int64) (bias :pointer) (bias-off :int64) (act :int)
+		  (residual :pointer) (res-off :int64) (ldres :int64)))
 ;; (!sum (softmax-cross-entropy x labels)) forward / sce-diff-static backward
 (defwf2 sce-sum-forward ((x :pointer) (x-off :int64) (labels :pointer) (l-off :int64) (z :pointer) (z-off :int64)
 			 (loss :pointer) (loss-off :int64) (rows :int64) (cols :int64) (delta :float)))

@@ -269,11 +269,12 @@ def _mat_operand(x: CUDATensor):
 
 
 def matmul(a, b, out: Optional[CUDATensor] = None, bias: Optional[CUDATensor] = None, relu: bool = False,
-           relu_mask: Optional[CUDATensor] = None) -> CUDATensor:
+           relu_mask: Optional[CUDATensor] = None, gelu: bool = False, residual: Optional[CUDATensor] = None) -> CUDATensor:
     """`(!matmul a b)` with `(!t ·)` operands (base-impl/matrix-ops.lisp:6-173):
     C[~ i k] <- A[~ i j] . B[~ j k], alpha=1, beta=0.
     bias / relu / relu_mask fold the node that follows into the epilogue (wf2cu_gemm_ex): `+ bias` per column
-    (LinearLayer, nn/regression.lisp:14-18), `!relu` of the result, or `* (mask > 0)` (the `!relu` backward)."""
+    (LinearLayer, nn/regression.lisp:14-18), `!relu` of the result, or `* (mask > 0)` (the `!relu` backward).
+    gelu / residual (wf2cu_gemm_ex2): `!gelu` of the result, `(!add residual result)` — the GPT-2 block's two patterns."""
     ta = isinstance(a, LazyT)
     tb = isinstance(b, LazyT)
     A = a.x if ta else a
@@ -300,6 +301,23 @@ def matmul(a, b, out: Optional[CUDATensor] = None, bias: Optional[CUDATensor] = 
     if o.shape != bshape + [m, n] or not o.is_contiguous():
         raise ValueError(f"!matmul: out must be a contiguous {bshape + [m, n]} tensor, got {o.shape}")
     lo = o.lower()
+    if gelu or residual is not None:
+        if batch != 1 or relu_mask is not None or (gelu and relu):
+            raise ValueError("!matmul: the gelu / residual epilogue takes unbatched operands and excludes relu / relu_mask")
+        bp, boff = (None, 0)
+        if bias is not None:
+            if bias.numel() != n or not bias.is_contiguous():
+                raise ValueError(f"!matmul: bias must be a contiguous {n}-element tensor, got {bias.shape}")
+            bp, boff = bias.vec.ptr, bias.lower().offset
+        rp, roff, ldr = (None, 0, 0)
+        if residual is not None:
+            if residual.numel() != m * n or not residual.is_contiguous():
+                raise ValueError(f"!matmul: residual must be a contiguous {[m, n]} tensor, got {residual.shape}")
+            rp, roff, ldr = residual.vec.ptr, residual.lower().offset, n
+        _lib.check(_L().wf2cu_gemm_ex2(1 if ta else 0, 1 if tb else 0, m, n, k, A.vec.ptr, la.offset, lda,
+                                       B.vec.ptr, lb.offset, ldb, o.vec.ptr, lo.offset, n, bp, boff, 2 if gelu else (1 if relu else 0),
+                                       rp, roff, ldr))
+        return o
     if bias is not None or relu or relu_mask is not None:
         if batch != 1:
             raise ValueError("!matmul: the fused epilogue takes unbatched operands")

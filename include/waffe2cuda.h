@@ -233,6 +233,15 @@ int  wf2cu_gemm_ex(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
                    const void* A, int64_t a_off, int64_t lda, const void* B, int64_t b_off, int64_t ldb,
                    void* C, int64_t c_off, int64_t ldc, const void* bias, int64_t bias_off, int act,
                    const void* mask, int64_t mask_off, int64_t ldmask);
+/* The GPT-2 example's block (`examples/gpt-2/model.lisp:93-137`) follows two of its projections with one more node: `!gelu`
+ * after the first MLP projection (`utils.lisp:129-137`) and the residual `(!add x ...)` after the attention and MLP output
+ * projections.  Both ride in the epilogue here:  C = op(A) op(B) [+ bias[col]] ; act = 1: relu, act = 2: gelu (tanh form, the
+ * operations and order of the node) ; residual != NULL: C = residual[row, col] + C.  Bit-identical to the separate nodes.
+ * Unbatched. */
+int  wf2cu_gemm_ex2(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
+                    const void* A, int64_t a_off, int64_t lda, const void* B, int64_t b_off, int64_t ldb,
+                    void* C, int64_t c_off, int64_t ldc, const void* bias, int64_t bias_off, int act,
+                    const void* residual, int64_t res_off, int64_t ldres);
 /* `(!sum (softmax-cross-entropy x labels))` (`nn/criterion.lisp:89-117,164-188`; the MNIST example's
  * loss, `examples/mnist/mlp.lisp:24-28`) in one kernel: z = softmax(x) row-wise (avoid-overflow nil),
  * loss[0] = sum(-1 * labels * log(z + delta)); x, labels, z contiguous (rows cols), cols <= 1024.

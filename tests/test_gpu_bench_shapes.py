@@ -328,3 +328,35 @@ def test_matmul_raw_operand_kernel_batched_bias_relu(gpu):
     assert np.abs(plain - truth).max() <= 2e-5 * np.abs(truth).max()
     want = plain + bias[None, :]
     np.testing.assert_array_equal(fused, want * (want > 0))
+
+
+@pytest.mark.parametrize("mode", [0, 2, 5, 7])
+@pytest.mark.parametrize("m,n,k", [(1536, 1000, 1024), (200, 96, 64)])
+def test_matmul_gelu_and_residual_epilogues_equal_the_separate_nodes(gpu, mode, m, n, k):
+    """wf2cu_gemm_ex2: the GPT-2 block's `!gelu` after a projection and its residual `(!add x ...)` ride in the epilogue of the
+    persistent tensor-core kernels (planes and raw; small problems take the product + one element-wise pass) — the same
+    operations in the same order as the separate nodes, so bit for bit."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(31 + m)
+    A = rng.uniform(-1, 1, size=(m, k)).astype(np.float32)
+    B = rng.uniform(-1, 1, size=(k, n)).astype(np.float32)
+    bias = rng.uniform(-1, 1, size=(n,)).astype(np.float32)
+    R = rng.uniform(-1, 1, size=(m, n)).astype(np.float32)
+    ga, gb, gbias, gr = (gpu.from_numpy(x) for x in (A, B, bias, R))
+    if mode != 0 and m < 1000:
+        pytest.skip("forced tensor modes are exercised on the large shape")
+    gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
+    try:
+        plain = gpu.ops.matmul(ga, gb, bias=gbias)
+        want_gelu = gpu.ops.gelu(plain).to_numpy()
+        want_res = gpu.ops.add(gr, plain).to_numpy()
+        got_gelu = gpu.ops.matmul(ga, gb, bias=gbias, gelu=True).to_numpy()
+        got_res = gpu.ops.matmul(ga, gb, bias=gbias, residual=gr).to_numpy()
+        got_both = gpu.ops.matmul(ga, gb, bias=gbias, gelu=True, residual=gr).to_numpy()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    np.testing.assert_array_equal(got_gelu, want_gelu)
+    np.testing.assert_array_equal(got_res, want_res)
+    np.testing.assert_array_equal(got_both, (want_gelu + R).astype(np.float32))
+    truth = A.astype(np.float64) @ B.astype(np.float64) + bias
+    assert np.abs(plain.to_numpy() - truth).max() <= 2e-5 * np.abs(truth).max()
