@@ -80,3 +80,8 @@ so dispatch falls to the next backend (`source/vm/nodes/defnode.lisp:215-232`)."
   (or (not *cuda-available-p*)
       (let ((dtype (find-if #'keywordp constructor-args)))
 	(and dtype (not (eql dtype :float))))))
+
+(defun cuda-only-reject-p (&rest constructor-args)
+  ":reject-p for nodes whose constructor takes no dtype (`cuda-reject-p` would read a keyword argument as one)."
+  (declare (ignore constructor-args))
+  (not *cuda-available-p*))

@@ -26,7 +26,8 @@
    #:cuda-comm-init
    #:cuda-allreduce-gradients
    #:cuda-layer-norm
-   #:cuda-softmax))
+   #:cuda-softmax
+   #:cuda-self-attention))
 (in-package :cl-waffe2/backends.cuda)
 
 (defparameter *cuda-available-p* nil

@@ -6,6 +6,7 @@
 #         pytest:<file>    one test file, prints kept
 #         bench            python bench.py            -> gpurun_out/<tag>_bench.json / .err
 #         benchref         python bench.py --impl reference
+#         benchN:<n>       torchrun bench.py on n GPUs (call gpurun with --gpus n)
 #         benchnopdl       the sweep / fused chains / MLP with WF2CU_PDL=0 (A/B of programmatic dependent launch)
 #         launches         ncu launch list of `bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --fused 1 --no-cpu`
 #         ncu:<regex>:<script.py>   ncu --set full on kernels matching <regex> while running python <script.py>
@@ -22,6 +23,9 @@ for task in "$@"; do
     newtests) timeout 900 python -m pytest tests/test_gpu_bench_shapes.py -m gpu -q -rf -s 2>&1 | tail -80 > gpurun_out/${tag}_newtests.log; tail -40 gpurun_out/${tag}_newtests.log ;;
     bench)    timeout 900 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"; tail -c 1500 gpurun_out/${tag}_bench.json; tail -5 gpurun_out/${tag}_bench.err ;;
     benchnopdl) WF2CU_PDL=0 timeout 900 python bench.py --gemm 0 --gpt2 0 --cnn 0 --no-cpu > gpurun_out/${tag}_bench_nopdl.json 2> gpurun_out/${tag}_bench_nopdl.err; echo "bench (WF2CU_PDL=0) rc=$?" ;;
+    benchN:*) n=${task#benchN:}
+              timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $n --steps 10 --warmup 3 \
+                > gpurun_out/${tag}_bench_n${n}.json 2> gpurun_out/${tag}_bench_n${n}.err; echo "bench N=$n rc=$?"; tail -c 1400 gpurun_out/${tag}_bench_n${n}.json; grep -v "^W\|^\*\*\*" gpurun_out/${tag}_bench_n${n}.err | tail -8 ;;
     benchref) timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "benchref rc=$?" ;;
     launches) cmd="python bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --no-cpu"
               timeout 300 $cmd > gpurun_out/${tag}_launches_plain.log 2>&1 &&
