@@ -9,7 +9,7 @@
 #         benchN:<n>       torchrun bench.py on n GPUs (call gpurun with --gpus n)
 #         benchnopdl       the sweep / fused chains / MLP with WF2CU_PDL=0 (A/B of programmatic dependent launch)
 #         launches         ncu launch list of `bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --fused 1 --no-cpu`
-#         ncu:<regex>:<script.py>   ncu --set full on kernels matching <regex> while running python <script.py>
+#         ncu:<regex>:<script.py>[+arg...]   ncu --set full on kernels matching <regex> while running python <script.py> [args]
 #         ncutime:<script.py>  per-kernel device times of a script (ncu gpu__time_duration, cold-cache, serialised)
 #         py:<script.py>   run a python script, log -> gpurun_out/<tag>_<script>.log
 # Every task runs under its own timeout so that a protocol bug cannot hold the box.
@@ -31,9 +31,10 @@ for task in "$@"; do
               timeout 300 $cmd > gpurun_out/${tag}_launches_plain.log 2>&1 &&
               timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${tag}_launches.csv $cmd > gpurun_out/${tag}_launches_ncu.log 2>&1
               echo "launches rc=$?" ;;
-    ncu:*)    IFS=: read -r _ regex script <<< "$task"; base=$(basename "$script" .py)
-              timeout 300 python "$script" > gpurun_out/${tag}_${base}_plain.log 2>&1 &&
-              timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$regex" -c 3 -f -o gpurun_out/${tag}_${base} python "$script" > gpurun_out/${tag}_${base}_ncu.log 2>&1
+    ncu:*)    IFS=: read -r _ regex script <<< "$task"; base=$(basename "${script%%+*}" .py)$(echo "${script#*.py}" | tr -d '+')
+              cmd="python ${script//+/ }"          # scripts/x.py+8192 -> python scripts/x.py 8192
+              timeout 300 $cmd > gpurun_out/${tag}_${base}_plain.log 2>&1 &&
+              timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$regex" -c ${NCU_COUNT:-3} -f -o gpurun_out/${tag}_${base} $cmd > gpurun_out/${tag}_${base}_ncu.log 2>&1
               echo "ncu $regex rc=$?"; tail -3 gpurun_out/${tag}_${base}_plain.log ;;
     ncutime:*) script=${task#ncutime:}; base=$(basename "$script" .py)
               timeout 300 python $script > gpurun_out/${tag}_${base}_plain.log 2>&1 &&
