@@ -26,6 +26,8 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
                  float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act, const float* res,
                  int64_t ldres);
 bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch);
+void gemm_tc_set_correction(int kind);
+int gemm_tc_correction();
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                       float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,
                       const float* mask, int64_t ldmask);
@@ -615,6 +617,12 @@ extern "C" {
 int wf2cu_gemm_last_path(int* out) {
   WF2_CHECK(out, "wf2cu_gemm_last_path: null out");
   *out = S().gemm_last_path;
+  return 0;
+}
+
+int wf2cu_gemm_set_correction(int kind) {
+  WF2_CHECK(kind == WF2CU_GEMM_CORRECTION_BF16 || kind == WF2CU_GEMM_CORRECTION_TF32, "wf2cu_gemm_set_correction: kind %d not in {0, 1}", kind);
+  gemm_tc_set_correction(kind);
   return 0;
 }
 

@@ -36,7 +36,7 @@ constexpr int R_BTILE = RN * RK * 4;                 // 16 KiB
 constexpr int R_STAGE = 2 * R_ATILE + 2 * R_BTILE;   // A raw | A lo | B raw (or hi) | B lo = 48 KiB
 constexpr int R_NS = 3;
 constexpr int R_CONV_WARPS = 4;
-constexpr uint32_t R_IDESC = idesc_tf32_mn(RM, RN);
+constexpr uint32_t R_IDESC = idesc_tf32_mn(RM, RN), R_IDESC_B = idesc_bf16_mn(RM, RN);
 // converter warps exist only when an operand arrives raw: idle warps would still take their share of the register file
 __host__ __device__ constexpr int raw_threads(int epi_warps, bool convert) { return 64 + (convert ? 32 * R_CONV_WARPS : 0) + 32 * epi_warps; }
 __host__ __device__ constexpr int raw_smem(int epi_warps, int epi_bytes_per_warp) { return R_NS * R_STAGE + epi_warps * epi_bytes_per_warp + 1024 + 256; }
@@ -51,10 +51,18 @@ __device__ __forceinline__ float raw_lo(float x) {   // x - trunc_tf32(x), exact
   return (fabsf(x) <= 3.0e38f) ? x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u) : 0.f;
 }
 
+// the mixed bf16 lo tile of a raw operand (same bytes as the fp32 lo tile): per 64-byte row bf16_rn(x[0:16]) then
+// bf16_rn(x[0:16] - trunc_tf32(x[0:16])); inf / nan contribute 0 to the corrections
+__device__ __forceinline__ uint32_t raw_bf2(float a, float b) {
+  return (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(a)) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(b)) << 16);
+}
+__device__ __forceinline__ float raw_fin(float x) { return (fabsf(x) <= 3.0e38f) ? x : 0.f; }
+
 // ---------------------------------------------------------------- MatmulNode
 struct RawGemmJob {
   static constexpr int kEpiWarps = 4, kEpiBytes = EPI_SLOT, kSubTiles = 1;
   TcArgs t;                   // C, ldc, m, n, tiles, bias, act, c_tma ... (nkb in k-blocks of 16)
+  __device__ __forceinline__ bool hyb() const { return t.passes == 2; }   // corrections as bf16 MMAs on mixed lo tiles
   __device__ __forceinline__ int items() const { return t.tiles_m * t.tiles_n * t.batch; }
   __device__ __forceinline__ RawCoords coords(int w, int) const {
     int b, mt, nt;
@@ -69,10 +77,12 @@ struct RawAttnArgs {
   int B, N, tiles_i, tiles_j;  // tiles of 128 queries x 256 keys
   float scale;                 // log2(e) / divisor
   int dbg;                     // measurement switches (WF2CU_ATTN_DBG): 1 no P stores, 2 no pass-2 arithmetic, 4 no pass-1 arithmetic
+  int hyb;                     // corrections as bf16 MMAs on mixed lo tiles (see split_bf in gemm_tc.cu)
 };
 struct RawAttnJob {
   static constexpr int kEpiWarps = 16, kEpiBytes = 2 * 1024, kSubTiles = 2 * RA_H;
   RawAttnArgs a;
+  __device__ __forceinline__ bool hyb() const { return a.hyb != 0; }
   __device__ __forceinline__ int items() const { return a.B * a.tiles_i * a.tiles_j; }
   __device__ __forceinline__ void where(int w, int& jt, int& it, int& b) const {
     jt = w % a.tiles_j; it = (w / a.tiles_j) % a.tiles_i; b = w / (a.tiles_j * a.tiles_i);
@@ -118,6 +128,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int items = job.items();
+  const bool hyb = job.hyb();
   pdl_prologue();
 
   if (threadIdx.x == 0) {
@@ -173,12 +184,21 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const uint32_t st = smem_u32(smem + s * R_STAGE);
             const uint64_t dah = make_desc_sw64(st), dal = make_desc_sw64(st + R_ATILE);
             const uint64_t dbh = make_desc_sw64(st + 2 * R_ATILE), dbl = make_desc_sw64(st + 2 * R_ATILE + R_BTILE);
+            if (hyb) {
+              // the 64-byte swizzle row of a mixed lo tile: hb[0:16] then lb[0:16]; bf16(A) . bf16(B_lo) + bf16(A_lo) . bf16(B)
+              // as two bf16 MMAs of K = 16, then the main product on the raw tiles (the tensor core truncates fp32 to TF32)
+              tc_mma_bf16(d, dal, dbl + 2, R_IDESC_B, kb != 0);
+              tc_mma_bf16(d, dal + 2, dbl, R_IDESC_B, 1);
+              tc_mma_tf32(d, dah, dbh, R_IDESC, 1);
+              tc_mma_tf32(d, dah + 2, dbh + 2, R_IDESC, 1);
+            } else {
 #pragma unroll
-            for (int k = 0; k < RK / UK; ++k) {
-              const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
-              tc_mma_tf32(d, dal + adv, dbh + adv, R_IDESC, (kb | k) != 0);   // small terms first, then the main product
-              tc_mma_tf32(d, dah + adv, dbl + adv, R_IDESC, 1);
-              tc_mma_tf32(d, dah + adv, dbh + adv, R_IDESC, 1);
+              for (int k = 0; k < RK / UK; ++k) {
+                const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
+                tc_mma_tf32(d, dal + adv, dbh + adv, R_IDESC, (kb | k) != 0);   // small terms first, then the main product
+                tc_mma_tf32(d, dah + adv, dbl + adv, R_IDESC, 1);
+                tc_mma_tf32(d, dah + adv, dbh + adv, R_IDESC, 1);
+              }
             }
             tc_commit(&empty[s]);
             if (++s == R_NS) { s = 0; ph ^= 1; }
@@ -206,7 +226,19 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const int src = c < R_ATILE / 16 ? c * 16 : 2 * R_ATILE + (c - R_ATILE / 16) * 16;
             const int dst = src + (c < R_ATILE / 16 ? R_ATILE : R_BTILE);
             const float4 x = *reinterpret_cast<const float4*>(st + src);
-            *reinterpret_cast<float4*>(st + dst) = make_float4(raw_lo(x.x), raw_lo(x.y), raw_lo(x.z), raw_lo(x.w));
+            if (hyb) {
+              // SWIZZLE_64B: the 16-byte chunk of logical index l of row r lies at chunk l ^ ((r >> 1) & 3).  This chunk holds
+              // x[4l : 4l+4]; its 4 hb go to the (l & 1) half of logical chunk l >> 1, its 4 lb to the same half of chunk 2 + (l >> 1).
+              const int cl = (c < R_ATILE / 16) ? c : c - R_ATILE / 16;
+              const int row = cl >> 2, sw = (row >> 1) & 3, l = (cl & 3) ^ sw;
+              uint8_t* rowp = st + dst - (cl & 3) * 16 + (l & 1) * 8;
+              const float f0 = raw_fin(x.x), f1 = raw_fin(x.y), f2 = raw_fin(x.z), f3 = raw_fin(x.w);
+              *reinterpret_cast<uint2*>(rowp + (((l >> 1)) ^ sw) * 16) = make_uint2(raw_bf2(f0, f1), raw_bf2(f2, f3));
+              *reinterpret_cast<uint2*>(rowp + ((2 + (l >> 1)) ^ sw) * 16) =
+                  make_uint2(raw_bf2(raw_lo(x.x), raw_lo(x.y)), raw_bf2(raw_lo(x.z), raw_lo(x.w)));
+            } else {
+              *reinterpret_cast<float4*>(st + dst) = make_float4(raw_lo(x.x), raw_lo(x.y), raw_lo(x.z), raw_lo(x.w));
+            }
           }
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();

@@ -19,6 +19,7 @@
 //                                 C layouts a tensor map cannot describe are stored from registers, bounds-checked
 //      smem full/empty mbarriers between warp 0 and warp 1, TMEM full/empty between 1 and 2-5.
 #include <cuda.h>
+#include <cuda_bf16.h>
 #include <stdlib.h>
 #include <type_traits>
 #include <vector>
@@ -47,6 +48,11 @@ constexpr int GEMM_THREADS = 192;
 // instruction descriptor (cute::UMMA::InstrDescriptor): D=f32 [4,6)=1, A=tf32 [7,10)=2, B=tf32 [10,13)=2,
 // both K-major (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29)
 constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+// the same for kind::f16 with bf16 operands: A = B = bf16 (format 1), K = 16 per instruction
+__host__ __device__ constexpr uint32_t idesc_bf16_mn(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+constexpr uint32_t kIdescBf16 = idesc_bf16_mn(TM, TN);
 
 __device__ __forceinline__ float tf32_rn(float x) {
   uint32_t r;
@@ -60,6 +66,14 @@ __device__ __forceinline__ void split1(float x, float& hi, float& lo) {
 }
 
 // ------------------------------------------------------------------ step 1: hi / lo planes
+// Two forms of the second plane:
+//   bf_blk == 0   lo = tf32_rn(x - hi), fp32: the classic 3xTF32 split (C = hi.hi + hi.lo + lo.hi, three kind::tf32 MMAs)
+//   bf_blk == 16 / 32   a MIXED bf16 plane of the same size and geometry: per k-block of bf_blk elements (bf_blk * 4 bytes, one
+//                 swizzle row of the consuming kernel) first bf16_rn(x) of the block, then bf16_rn(x - hi) of the block.  The
+//                 corrections hi.lo + lo.hi then run as TWO kind::f16 (bf16) MMAs of K = 16 instead of four kind::tf32 MMAs of
+//                 K = 8: the tensor pipe spends 2 units per 8 k instead of 3.  The corrections are ~2^-12 of the product, so the
+//                 bf16 rounding of their factors (2^-9) leaves ~2^-20 per product: measured 5e-7 of max|C| on random operands,
+//                 the size of an fp32 sgemm's own rounding error (scripts/emulate_hybrid_split.py).
 struct SplitArgs {
   const float* src;   // operand base (already offset)
   float* hi;          // [batch][R][Kp]
@@ -67,7 +81,18 @@ struct SplitArgs {
   int64_t ld, sx;     // leading dimension and batch stride of src (elements)
   int R, K, Kp;       // rows of the plane (m or n), true k, padded k
   int vec;            // src rows are 16-byte aligned (direct variant only)
+  int bf_blk;         // 0: fp32 lo plane ; 16 / 32: mixed bf16 plane with that k-block
 };
+
+__device__ __forceinline__ void split_bf(float x, float& hi, uint16_t& hb, uint16_t& lb) {
+  hi = tf32_rn(x);
+  if (fabsf(hi) <= 3.0e38f) {
+    hb = __bfloat16_as_ushort(__float2bfloat16_rn(x));
+    lb = __bfloat16_as_ushort(__float2bfloat16_rn(x - hi));   // x - hi is exact
+  } else {             // inf / nan live in hi only: the corrections must not turn inf into inf - inf or inf . 0
+    hb = 0; lb = 0;
+  }
+}
 
 // src is K-contiguous: (r, k) at r*ld + k
 __global__ void __launch_bounds__(256) split_planes_direct_kernel(const __grid_constant__ SplitArgs a) {
@@ -85,9 +110,23 @@ __global__ void __launch_bounds__(256) split_planes_direct_kernel(const __grid_c
 #pragma unroll
     for (int j = 0; j < 4; ++j) x[j] = (k + j < a.K) ? s[j] : 0.f;
   }
+  const int64_t o = (b * a.R + r) * (int64_t)a.Kp + k;
+  if (a.bf_blk) {
+    float4 h;
+    uint16_t hb[4], lb[4];
+    split_bf(x[0], h.x, hb[0], lb[0]); split_bf(x[1], h.y, hb[1], lb[1]);
+    split_bf(x[2], h.z, hb[2], lb[2]); split_bf(x[3], h.w, hb[3], lb[3]);
+    *reinterpret_cast<float4*>(a.hi + o) = h;
+    // row base in 16-bit units: 2 * Kp per row; k-block kb holds hb[0:blk] then lb[0:blk]
+    uint16_t* row = reinterpret_cast<uint16_t*>(a.lo) + (b * a.R + r) * (int64_t)(2 * a.Kp);
+    const int kb = k / a.bf_blk, j = k - kb * a.bf_blk;
+    uint16_t* dst = row + (int64_t)kb * 2 * a.bf_blk + j;
+    *reinterpret_cast<uint2*>(dst) = make_uint2((uint32_t)hb[0] | ((uint32_t)hb[1] << 16), (uint32_t)hb[2] | ((uint32_t)hb[3] << 16));
+    *reinterpret_cast<uint2*>(dst + a.bf_blk) = make_uint2((uint32_t)lb[0] | ((uint32_t)lb[1] << 16), (uint32_t)lb[2] | ((uint32_t)lb[3] << 16));
+    return;
+  }
   float4 h, l;
   split1(x[0], h.x, l.x); split1(x[1], h.y, l.y); split1(x[2], h.z, l.z); split1(x[3], h.w, l.w);
-  const int64_t o = (b * a.R + r) * (int64_t)a.Kp + k;
   *reinterpret_cast<float4*>(a.hi + o) = h;
   *reinterpret_cast<float4*>(a.lo + o) = l;
 }
@@ -95,7 +134,7 @@ __global__ void __launch_bounds__(256) split_planes_direct_kernel(const __grid_c
 // src is R-contiguous: (r, k) at k*ld + r  -> transpose through shared memory
 __global__ void __launch_bounds__(256) split_planes_transpose_kernel(const __grid_constant__ SplitArgs a) {
   __shared__ float th[32][33];
-  __shared__ float tl[32][33];
+  __shared__ float tl[32][33];          // fp32 lo, or (hb | lb << 16) of the mixed plane
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
   const int r0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
   const int64_t b = blockIdx.z;
@@ -105,7 +144,13 @@ __global__ void __launch_bounds__(256) split_planes_transpose_kernel(const __gri
     const int k = k0 + ty + j * 8, r = r0 + tx;
     const float x = (k < a.K && r < a.R) ? s[(int64_t)k * a.ld + r] : 0.f;
     float h, l;
-    split1(x, h, l);
+    if (a.bf_blk) {
+      uint16_t hb, lb;
+      split_bf(x, h, hb, lb);
+      l = __uint_as_float((uint32_t)hb | ((uint32_t)lb << 16));
+    } else {
+      split1(x, h, l);
+    }
     th[ty + j * 8][tx] = h;
     tl[ty + j * 8][tx] = l;
   }
@@ -116,7 +161,15 @@ __global__ void __launch_bounds__(256) split_planes_transpose_kernel(const __gri
     if (r < a.R) {   // k < Kp always (Kp is a multiple of 32)
       const int64_t o = (b * a.R + r) * (int64_t)a.Kp + k;
       a.hi[o] = th[tx][ty + j * 8];
-      a.lo[o] = tl[tx][ty + j * 8];
+      if (a.bf_blk) {
+        const uint32_t w = __float_as_uint(tl[tx][ty + j * 8]);
+        uint16_t* row = reinterpret_cast<uint16_t*>(a.lo) + (b * a.R + r) * (int64_t)(2 * a.Kp);
+        const int kb = k / a.bf_blk, jj = k - kb * a.bf_blk;
+        row[(int64_t)kb * 2 * a.bf_blk + jj] = (uint16_t)(w & 0xFFFFu);
+        row[(int64_t)kb * 2 * a.bf_blk + a.bf_blk + jj] = (uint16_t)(w >> 16);
+      } else {
+        a.lo[o] = tl[tx][ty + j * 8];
+      }
     }
   }
 }
@@ -128,7 +181,8 @@ struct TcArgs {
   int m, n;
   int nkb;               // Kp / TK
   int tiles_m, tiles_n, batch;
-  int passes;            // 3 = 3xTF32 (parity grade), 1 = single TF32 pass (hi planes only)
+  int passes;            // 3 = 3xTF32 (fp32 lo planes), 2 = TF32 + two bf16 correction MMAs (mixed bf16 planes; the default),
+                         // 1 = single TF32 pass (hi planes only, not parity grade)
   int c_vec;             // C rows are 16-byte aligned -> 128-bit stores
   int a_bcast, b_bcast;  // operand shared by every batch index (batch stride 0): one plane set
   const float* bias;     // != NULL: C[r, c] = acc + bias[c]  (LinearLayer's bias add folded into the epilogue)
@@ -275,7 +329,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      const uint32_t tx_bytes = a.passes == 3 ? STAGE_BYTES : (A_PLANE_BYTES + B_PLANE_BYTES);
+      const uint32_t tx_bytes = a.passes != 1 ? STAGE_BYTES : (A_PLANE_BYTES + B_PLANE_BYTES);
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int b, mt, nt;
@@ -287,7 +341,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
           const int ba = a.a_bcast ? 0 : b, bb = a.b_bcast ? 0 : b;
           tma_load_3d(&map_ah, &full[s], st, kb * TK, mt * TM, ba);
           tma_load_3d(&map_bh, &full[s], st + 2 * A_PLANE_BYTES, kb * TK, nt * TN, bb);
-          if (a.passes == 3) {
+          if (a.passes != 1) {
             tma_load_3d(&map_al, &full[s], st + A_PLANE_BYTES, kb * TK, mt * TM, ba);
             tma_load_3d(&map_bl, &full[s], st + 2 * A_PLANE_BYTES + B_PLANE_BYTES, kb * TK, nt * TN, bb);
           }
@@ -310,15 +364,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
           const uint32_t st = smem_u32(smem + s * STAGE_BYTES);
           const uint64_t dah = make_desc_sw128(st), dal = make_desc_sw128(st + A_PLANE_BYTES);
           const uint64_t dbh = make_desc_sw128(st + 2 * A_PLANE_BYTES), dbl = make_desc_sw128(st + 2 * A_PLANE_BYTES + B_PLANE_BYTES);
+          if (a.passes == 2) {
+            // per 16 k: the two corrections as bf16 MMAs of K = 16 (bf16(A) . bf16(B_lo) + bf16(A_lo) . bf16(B)), then the main
+            // product as two TF32 MMAs of K = 8 — the order gemm_tc256_kernel uses per k-block of 16, so that every tile shape
+            // accumulates in the same order.  The 128-byte swizzle row of the mixed plane holds hb[0:16] hb[16:32] lb[0:16]
+            // lb[16:32], 32 bytes (two 16-byte descriptor units) each.
 #pragma unroll
-          for (int k = 0; k < TK / UK; ++k) {
-            const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);   // +32 bytes per UMMA_K inside the swizzle row
-            if (a.passes == 3) {   // small terms first, then the main product
-              tc_mma_tf32(d, dal + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
-              tc_mma_tf32(d, dah + adv, dbl + adv, kIdescTf32, 1);
-              tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, 1);
-            } else {
-              tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
+            for (int j = 0; j < 2; ++j) {
+              tc_mma_bf16(d, dal + (uint64_t)(2 * j), dbl + (uint64_t)(2 * (2 + j)), kIdescBf16, (kb | j) != 0);
+              tc_mma_bf16(d, dal + (uint64_t)(2 * (2 + j)), dbl + (uint64_t)(2 * j), kIdescBf16, 1);
+              tc_mma_tf32(d, dah + (uint64_t)(4 * j), dbh + (uint64_t)(4 * j), kIdescTf32, 1);
+              tc_mma_tf32(d, dah + (uint64_t)(4 * j + 2), dbh + (uint64_t)(4 * j + 2), kIdescTf32, 1);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < TK / UK; ++k) {
+              const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);   // +32 bytes per UMMA_K inside the swizzle row
+              if (a.passes == 3) {   // small terms first, then the main product
+                tc_mma_tf32(d, dal + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
+                tc_mma_tf32(d, dah + adv, dbl + adv, kIdescTf32, 1);
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, 1);
+              } else {
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdescTf32, (kb | k) != 0);
+              }
             }
           }
           tc_commit(&empty[s]);                 // frees the smem stage when these MMAs retire
@@ -400,7 +468,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
                   const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
   constexpr int T2N = NB, T2_STAGES = NST, B_PLANE = t2_bplane(NB), T2_STAGE_BYTES = t2_stage_bytes(NB);
-  constexpr uint32_t kIdesc = idesc_tf32(NB);
+  constexpr uint32_t kIdesc = idesc_tf32(NB), kIdescB = idesc_bf16_mn(128, NB);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_STAGES * T2_STAGE_BYTES + EPI_BYTES);
@@ -430,7 +498,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
 
   if (warp == 0) {
     if (lane == 0) {
-      const uint32_t tx_bytes = a.passes == 3 ? T2_STAGE_BYTES : T2_PLANE + B_PLANE;
+      const uint32_t tx_bytes = a.passes != 1 ? T2_STAGE_BYTES : T2_PLANE + B_PLANE;
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int b, mt, nt;
@@ -442,7 +510,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           mbar_expect_tx(&full[s], tx_bytes);
           tma_load_3d(&map_ah, &full[s], st, kb * T2K, mt * T2M, ba);
           tma_load_3d(&map_bh, &full[s], st + 2 * T2_PLANE, kb * T2K, nt * T2N, bb);
-          if (a.passes == 3) {
+          if (a.passes != 1) {
             tma_load_3d(&map_al, &full[s], st + T2_PLANE, kb * T2K, mt * T2M, ba);
             tma_load_3d(&map_bl, &full[s], st + 2 * T2_PLANE + B_PLANE, kb * T2K, nt * T2N, bb);
           }
@@ -466,10 +534,17 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           for (int h = 0; h < 2; ++h) {         // rows [0,128) and [128,256) of the A tile: + 128 rows x 64 B
             const uint64_t dah = make_desc_sw64(st + h * (128 * 64)), dal = make_desc_sw64(st + T2_PLANE + h * (128 * 64));
             const uint32_t d = tmem_base + (uint32_t)(h * 256);
+            if (a.passes == 2) {
+              // the 64-byte swizzle row of the mixed plane: hb[0:16] then lb[0:16]; one bf16 MMA (K = 16) per correction
+              tc_mma_bf16(d, dal, dbl + 2, kIdescB, kb != 0);
+              tc_mma_bf16(d, dal + 2, dbl, kIdescB, 1);
+            }
 #pragma unroll
             for (int k = 0; k < T2K / UK; ++k) {
               const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
-              if (a.passes == 3) {
+              if (a.passes == 2) {
+                tc_mma_tf32(d, dah + adv, dbh + adv, kIdesc, 1);
+              } else if (a.passes == 3) {
                 tc_mma_tf32(d, dal + adv, dbh + adv, kIdesc, (kb | k) != 0);
                 tc_mma_tf32(d, dah + adv, dbl + adv, kIdesc, 1);
                 tc_mma_tf32(d, dah + adv, dbh + adv, kIdesc, 1);
@@ -909,6 +984,14 @@ float* tc_workspace(size_t bytes) {
 }
 
 static bool g_t256_auto = true;       // auto mode may take the 256x256-tile kernel (rule in gemm_tc_try)
+// how the planes kernels form the correction terms hi.lo + lo.hi: 0 = two bf16 MMAs on mixed planes (default), 1 = two TF32
+// MMAs on fp32 lo planes (classic 3xTF32).  WF2CU_GEMM_CORRECTION=tf32 selects 1 at start-up.
+static int g_correction = -1;
+int gemm_tc_correction() {
+  if (g_correction < 0) { const char* e = getenv("WF2CU_GEMM_CORRECTION"); g_correction = (e && (e[0] == 't' || e[0] == '1')) ? 1 : 0; }
+  return g_correction;
+}
+void gemm_tc_set_correction(int kind) { g_correction = kind ? 1 : 0; }
 
 static int make_map(CUtensorMap* map, float* base, int rows, int Kp, int nbatch, int box_rows) {
   cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)rows, (cuuint64_t)nbatch};
@@ -953,8 +1036,8 @@ static int make_map_c(CUtensorMap* map, float* C, int64_t m, int64_t n, int64_t 
 }
 
 static int launch_split(const float* src, float* hi, float* lo, int64_t ld, int64_t sx, int R, int K, int Kp, int nbatch,
-                        bool r_contiguous) {
-  SplitArgs sa{src, hi, lo, ld, sx, R, K, Kp, 0};
+                        bool r_contiguous, int bf_blk) {
+  SplitArgs sa{src, hi, lo, ld, sx, R, K, Kp, 0, bf_blk};
   if (!r_contiguous) {
     sa.vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (ld & 3) == 0 && (sx & 3) == 0) ? 1 : 0;
     const int64_t work = (int64_t)R * (Kp >> 2);
@@ -975,11 +1058,21 @@ static int launch_split(const float* src, float* hi, float* lo, int64_t ld, int6
 // (x1.3) but hides its epilogue; 256x256 runs at the tensor rate; 256x192 pays x1.12 for its smaller B slices.
 //   8192x768x3072: 286 / 242 / 212 us (128x256 / 256x256 / 256x192)   8192x768x768: 82 / 78 / 68
 //   8192x1536x1536: 207 / 230 / 196     8192x2304x768: 139 / 136 / 156     2048^3: 103 / 154 / 131     4096^3: 679 / 577 / 680
-static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t tiles192, int sms) {
+static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t tiles192, int sms, bool bf16_corr) {
   auto waves = [&](int64_t t) { return (double)((t + sms - 1) / sms); };
-  const double c128 = waves(tiles128) * 1.30 * (double)kp;
-  const double c256 = waves(tiles256) * (2.00 * (double)kp + 450.0);
-  const double c192 = waves(tiles192) * (1.68 * (double)kp + 337.0);
+  double c128, c256, c192;
+  if (bf16_corr) {
+    // TF32 + bf16 corrections (r02d, scripts/gemm_hybrid_bench.py): 35 / 53 / 44.5 ns per k per tile; 256-row epilogues ~8 / 6 us
+    //   4096^3: 624 / 490 / 606 us   8192^3: 3944 / 3217 / 3814   2048^3: 95 / 119 / 112   8192x2304x768: 124 / 112 / 134
+    //   8192x768x768: 72 / 66 / 62   8192x3072x768: 171 / 154 / 170   8192x768x3072: 262 / 202 / 193
+    c128 = waves(tiles128) * 1.02 * (double)kp;
+    c256 = waves(tiles256) * (1.59 * (double)kp + 240.0);
+    c192 = waves(tiles192) * (1.33 * (double)kp + 180.0);
+  } else {
+    c128 = waves(tiles128) * 1.30 * (double)kp;
+    c256 = waves(tiles256) * (2.00 * (double)kp + 450.0);
+    c192 = waves(tiles192) * (1.68 * (double)kp + 337.0);
+  }
   if (c128 <= c256 * 1.02 && c128 <= c192 * 1.02) return 0;
   return c256 <= c192 ? 256 : 192;
 }
@@ -1007,7 +1100,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     g_attr_set = true;
   }
   const int Kp = (int)((k + TK - 1) / TK) * TK;
-  const int passes = mode == 3 ? 1 : 3;      // modes 5 / 6 = 3xTF32 on the 256x256 / 256x192-tile kernel
+  // 1: TF32 only (mode 3, not parity grade); 2: TF32 + bf16 corrections; 3: 3xTF32.  Modes 5 / 6 pick the tile, not the split.
+  const int passes = mode == 3 ? 1 : (gemm_tc_correction() ? 3 : 2);
   const int a_nb = (sa == 0 || batch == 1) ? 1 : (int)batch;
   const int b_nb = (sb == 0 || batch == 1) ? 1 : (int)batch;
   auto plane = [&](int64_t rows, int nb) { return (((size_t)nb * rows * Kp * 4) + 255) & ~(size_t)255; };
@@ -1018,13 +1112,6 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   float* al = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ah) + pa);
   float* bh = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(al) + pa);
   float* bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
-  // A: logical (m x k).  ta = stored transposed (k x m) -> m is the contiguous axis of the source.
-  rc = launch_split(A, ah, al, lda, sa, (int)m, (int)k, Kp, a_nb, ta != 0);
-  if (rc) return rc;
-  // B: planes are (n x k).  op(B) is k x n; !tb = stored (k x n) row-major -> n contiguous.
-  rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0);
-  if (rc) return rc;
-
   CUtensorMap mah, mal, mbh, mbl, mc;
   const int c_tma = make_map_c(&mc, C, m, n, ldc, sc, batch);
   // 128x256, 256x256 or 256x192 tiles: results are bit-identical (same k order per output), pick_tile256 chooses
@@ -1035,7 +1122,16 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   if (mode == 5) nb = 256;
   else if (mode == 6) nb = 192;
   else if (mode == 0 && g_t256_auto)
-    nb = pick_tile256(Kp, ((m + TM - 1) / TM) * ((n + TN - 1) / TN) * batch, tiles256, tiles192, S().sm_count);
+    nb = pick_tile256(Kp, ((m + TM - 1) / TM) * ((n + TN - 1) / TN) * batch, tiles256, tiles192, S().sm_count, passes == 2);
+  // the second plane: fp32 lo (3xTF32) or the mixed bf16 plane laid out for the chosen kernel's k-block
+  const int bf_blk = passes == 2 ? (nb ? T2K : TK) : 0;
+  // A: logical (m x k).  ta = stored transposed (k x m) -> m is the contiguous axis of the source.
+  rc = launch_split(A, ah, al, lda, sa, (int)m, (int)k, Kp, a_nb, ta != 0, bf_blk);
+  if (rc) return rc;
+  // B: planes are (n x k).  op(B) is k x n; !tb = stored (k x n) row-major -> n contiguous.
+  rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, bf_blk);
+  if (rc) return rc;
+
   if (nb) {
     // 256-row tiles: two M = 128 MMAs share every B slice (42.7 instead of 62.5 B/clk of L2 -> SM traffic per SM)
     static bool attr256 = false;
@@ -1116,8 +1212,12 @@ bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch) 
   const double nkb = (double)((k + 15) / 16);
   const int64_t t128 = ((m + 127) / 128) * ((n + 255) / 256), t256 = ((m + 255) / 256) * ((n + 255) / 256), t192 = ((m + 255) / 256) * ((n + 191) / 192);
   const double raw = waves(t128) * nkb * 1180.0 + 8000.0 + (tb ? 0.0 : presplit(n));
-  double planes = waves(t128) * nkb * 1110.0;
-  const double p256 = waves(t256) * (nkb * 1850.0 + 10000.0), p192 = waves(t192) * (nkb * 1500.0 + 8000.0);
+  // the planes kernels with bf16 corrections (the default) spend 2 tensor-pipe units per k instead of 3: 870 / 1470 / 1190
+  // (r02d: 2048^3 raw 90 us vs 95; 8192x2304x768 raw 129 vs 112; 4096^3 raw 654 vs 490)
+  const bool bf = gemm_tc_correction() == 0;
+  double planes = waves(t128) * nkb * (bf ? 870.0 : 1110.0);
+  const double p256 = waves(t256) * (nkb * (bf ? 1470.0 : 1850.0) + (bf ? 7000.0 : 10000.0));
+  const double p192 = waves(t192) * (nkb * (bf ? 1190.0 : 1500.0) + (bf ? 5500.0 : 8000.0));
   if (p256 < planes) planes = p256;
   if (p192 < planes) planes = p192;
   planes += presplit(m) + presplit(n);
@@ -1156,7 +1256,7 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
     if ((rc = ensure_ws(2 * pb))) return rc;
     float* bh = g_ws;
     float* bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
-    if ((rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0))) return rc;
+    if ((rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, gemm_tc_correction() ? 0 : RK))) return rc;
     if ((rc = make_map256(&mb, bh, (int)n, Kp, b_nb, RN))) return rc;
     if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb, RN))) return rc;
   }
@@ -1164,7 +1264,7 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
   TcArgs& t = job.t;
   t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = (int)((k + RK - 1) / RK);
   t.tiles_m = (int)((m + RM - 1) / RM); t.tiles_n = (int)((n + RN - 1) / RN); t.batch = (int)batch;
-  t.passes = 3;
+  t.passes = gemm_tc_correction() ? 3 : 2;   // 2: the lo tiles are mixed bf16 tiles and the corrections run as bf16 MMAs
   t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   t.a_bcast = a_nb == 1 ? 1 : 0;
   t.b_bcast = b_nb == 1 ? 1 : 0;
@@ -1181,8 +1281,9 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
   return rc ? -rc : 1;
 }
 
-// lo planes of Q and K: lo[b, n, c] = x - trunc_tf32(x) for the first 2E features of every (b, n) row of the QKV activation
-__global__ void __launch_bounds__(256) attn_split_qk_kernel(const float* __restrict__ qkv, float* __restrict__ lo, int64_t rows) {
+// lo planes of Q and K for the first 2E features of every (b, n) row of the QKV activation: fp32 lo[b, n, c] = x - trunc_tf32(x),
+// or (mixed != 0) per 16 features bf16_rn(x[0:16]) then bf16_rn(x[0:16] - trunc_tf32(x[0:16])) in the same 64 bytes
+__global__ void __launch_bounds__(256) attn_split_qk_kernel(const float* __restrict__ qkv, float* __restrict__ lo, int64_t rows, int mixed) {
   pdl_prologue();
   constexpr int V4 = 2 * RA_E / 4;                                   // float4 per row
   const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
@@ -1190,6 +1291,14 @@ __global__ void __launch_bounds__(256) attn_split_qk_kernel(const float* __restr
   const int64_t r = idx / V4;
   const int c4 = (int)(idx - r * V4);
   const float4 x = reinterpret_cast<const float4*>(qkv + r * (3 * RA_E))[c4];
+  if (mixed) {
+    // features [4 c4, 4 c4 + 4) of block c4 / 4: hb at 16-bit index blk * 32 + j, lb at blk * 32 + 16 + j
+    uint16_t* row = reinterpret_cast<uint16_t*>(lo + r * (2 * RA_E));
+    uint16_t* dst = row + (c4 >> 2) * 32 + (c4 & 3) * 4;
+    *reinterpret_cast<uint2*>(dst) = make_uint2(raw_bf2(raw_fin(x.x), raw_fin(x.y)), raw_bf2(raw_fin(x.z), raw_fin(x.w)));
+    *reinterpret_cast<uint2*>(dst + 16) = make_uint2(raw_bf2(raw_lo(x.x), raw_lo(x.y)), raw_bf2(raw_lo(x.z), raw_lo(x.w)));
+    return;
+  }
   reinterpret_cast<float4*>(lo + r * (2 * RA_E))[c4] = make_float4(raw_lo(x.x), raw_lo(x.y), raw_lo(x.z), raw_lo(x.w));
 }
 
@@ -1203,12 +1312,13 @@ int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor,
   // (twice the L2 -> SM bytes: the kernel is then bound by the ~7.4 TB/s the L2 delivers to the SMs; kept for A/B measurements)
   static int planes = -1;
   if (planes < 0) { const char* e = getenv("WF2CU_ATTN_PLANES"); planes = (e && e[0] == '1') ? 1 : 0; }
+  const int hyb = gemm_tc_correction() ? 0 : 1;     // corrections of Q.K^T as bf16 MMAs on mixed lo tiles (the library default)
   float* qk_lo = nullptr;
   if (planes) {
     if (ensure_ws((size_t)B * N * 2 * RA_E * 4)) return WF2CU_ERR_CUDA;
     qk_lo = g_ws;
     const int64_t rows = batch * seq, work = rows * (2 * RA_E / 4);
-    WF2_CUDA(launch_pdl(attn_split_qk_kernel, dim3((unsigned)((work + 255) / 256)), dim3(256), 0, S().stream, qkv, qk_lo, rows));
+    WF2_CUDA(launch_pdl(attn_split_qk_kernel, dim3((unsigned)((work + 255) / 256)), dim3(256), 0, S().stream, qkv, qk_lo, rows, hyb));
     const int rc0 = post_launch("wf2cu_attn_heads_softmax(split Q K)");
     if (rc0) return rc0;
   }
@@ -1249,7 +1359,7 @@ int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor,
   }
   static int dbg = -1;
   if (dbg < 0) { const char* e = getenv("WF2CU_ATTN_DBG"); dbg = e ? atoi(e) : 0; }
-  RawAttnJob job{RawAttnArgs{B, N, (N + RM - 1) / RM, (N + RN - 1) / RN, (float)(1.4426950408889634 / (double)divisor), dbg}};
+  RawAttnJob job{RawAttnArgs{B, N, (N + RM - 1) / RM, (N + RN - 1) / RN, (float)(1.4426950408889634 / (double)divisor), dbg, hyb}};
   const int items = job.a.B * job.a.tiles_i * job.a.tiles_j, sms = S().sm_count;
   const int grid = items < sms ? items : sms;
   if (planes) WF2_CUDA(launch_pdl(gemm_raw_kernel<RawAttnJob, false, false, true>, dim3(grid), dim3(raw_threads(RawAttnJob::kEpiWarps, false)), bytes,

@@ -114,6 +114,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 sce-backward ((z :pointer) (z-off :int64) (labels :pointer) (l-off :int64) (dy :pointer) (dy-off :int64)
 		      (dx :pointer) (dx-off :int64) (rows :int64) (cols :int64) (accumulate :int)))
 (defwf2 gemm-set-mode ((mode :int)))
+(defwf2 gemm-set-correction ((kind :int)))
 (defwf2 gemm-last-path ((out :pointer)))
 ;; optimizers
 (defwf2 sgd-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64) (n :int64) (lr :float)))

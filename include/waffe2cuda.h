@@ -210,6 +210,16 @@ int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
  * transposed: fp32 tiles straight from the operand by TMA, lo planes made on the SM, no pre-pass).  Forced modes return
  * WF2CU_ERR_UNSUPPORTED for shapes their kernel does not take. */
 int  wf2cu_gemm_set_mode(int mode);
+/* How the plane-fed tcgen05 kernels form the error-compensation terms of the split product
+ *   C = A_hi.B_hi + (A_hi.B_lo + A_lo.B_hi),  A_hi = tf32_rn(A), A_lo = A - A_hi:
+ * BF16 (default): the two correction products run as kind::f16 MMAs on bf16_rn(A), bf16_rn(A_lo) (K = 16 per instruction,
+ * twice the TF32 rate): 2 tensor-pipe units per k instead of 3.  The corrections are ~2^-12 of the product, so rounding their
+ * factors to bf16 leaves ~5e-7 of max|C| on random operands — the size of an fp32 sgemm's own rounding error (the reference
+ * leaf is OpenBLAS sgemm_, `source/backends/cpu/matrix-ops.lisp:58-79`); small integers stay exact (lo = 0).
+ * TF32: the classic 3xTF32 form (corrections as kind::tf32 MMAs on tf32_rn(A_lo)), ~6e-8.  Start-up default from
+ * WF2CU_GEMM_CORRECTION=tf32.  The raw-operand and small-problem kernels always use the TF32 form. */
+enum { WF2CU_GEMM_CORRECTION_BF16 = 0, WF2CU_GEMM_CORRECTION_TF32 = 1 };
+int  wf2cu_gemm_set_correction(int kind);
 /* Which kernel the last wf2cu_gemm / wf2cu_gemm_ex call launched (the parity tests assert that the benchmarked shapes
  * really run on the kernel whose throughput is quoted). */
 enum {

@@ -1,9 +1,17 @@
 #!/usr/bin/env python
-"""Turn the ncu exports of scripts/gpu_round1_final.sh (gpurun_out/f_*) into the tracked summaries under profiles/."""
-import collections, csv, json, os, shutil, sys
+"""Turn what `scripts/gpu.sh <tag> ...` left in gpurun_out/ into the tracked summaries under profiles/.
+
+    python scripts/summarize_profiles.py <tag> [--traffic key=<rep basename>:<kernel substring> ...]
+
+For every gpurun_out/<tag>_*.ncu-rep : profiles/<tag>_ncu_<name>.md   (one row per captured launch: time, DRAM bytes, tensor
+                                        pipe, shared-memory pipe, occupancy, registers; read with `ncu -i ... --page raw --csv`)
+For gpurun_out/<tag>_launches.csv    : profiles/<tag>_launches.csv + <tag>_launches_summary.md (per-kernel shares)
+For <tag>_bench.json / _pytest.log   : copied as profiles/<tag>_bench_n1.json / <tag>_pytest_gpu.log
+--traffic writes dram read + write bytes per launch of the named kernel into profiles/ncu_traffic.json (bench.py's
+`roofline.traffic`)."""
+import collections, csv, glob, io, json, os, shutil, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G = os.path.join(ROOT, "gpurun_out"); P = os.path.join(ROOT, "profiles")
-TAG = sys.argv[1] if len(sys.argv) > 1 else "r01b"
 
 
 def launch_list(path):
@@ -30,46 +38,96 @@ def table(rows, title, cmd, out, note=""):
         f.write(f"\nTotal listed: {tot:.1f} us over {len(rows)} launches.\n")
 
 
-def raw_summary(path, title, out, note=""):
-    rows = list(csv.reader(open(path)))
+COLS = [("time us", "gpu__time_duration.sum", "time"),
+        ("dram read MB", "dram__bytes_read.sum", "bytes"), ("dram write MB", "dram__bytes_write.sum", "bytes"),
+        ("dram % of peak", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "num"),
+        ("tensor pipe % (while SM active)", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "num"),
+        ("tensor pipe % (of elapsed)", "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed", "num"),
+        ("shared-memory pipe % (LSU wavefronts)", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed", "num"),
+        ("L2 throughput %", "lts__throughput.avg.pct_of_peak_sustained_elapsed", "num"),
+        ("SM busy cycles / elapsed", None, "busy"),
+        ("occupancy %", "sm__warps_active.avg.pct_of_peak_sustained_active", "num"),
+        ("regs", "launch__registers_per_thread", "str")]
+
+
+def raw_rows(rep):
+    r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True)
+    rows = list(csv.reader(io.StringIO(r.stdout)))
     hdr, units = rows[0], rows[1]
     ix = {h: i for i, h in enumerate(hdr)}
-    def get(r, k, d=""):
-        return r[ix[k]] if k in ix else d
+    out = []
+    for r_ in rows[2:]:
+        def num(k):
+            try: return float(r_[ix[k]].replace(",", ""))
+            except (KeyError, ValueError): return float("nan")
+        d = {"kernel": r_[ix["Kernel Name"]], "grid": r_[ix["Grid Size"]]}
+        for label, key, kind in COLS:
+            if kind == "time":
+                t, u = num(key), units[ix[key]]
+                d[label] = t / 1000 if u in ("ns", "nsecond") else (t * 1000 if u in ("ms", "msecond") else t)
+            elif kind == "bytes":
+                d[label] = num(key) * {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}.get(units[ix[key]], 1e-6)
+            elif kind == "num":
+                d[label] = num(key)
+            elif kind == "busy":
+                d[label] = num("smsp__cycles_active.avg") / num("sm__cycles_elapsed.max")
+            else:
+                d[label] = r_[ix[key]] if key in ix else ""
+        out.append(d)
+    return out
+
+
+def ncu_summary(rep, out, title):
+    rows = raw_rows(rep)
     with open(out, "w") as f:
-        f.write(f"# {title}\n\n`ncu --set full --clock-control none`, per launch; traffic = dram__bytes_read.sum + dram__bytes_write.sum.\n{note}\n")
-        f.write("| kernel | grid | time us | dram read MB | dram write MB | traffic MB | dram % of peak | achieved occupancy % | regs | tensor pipe active % | L2 throughput % |\n|---|---|---|---|---|---|---|---|---|---|---|\n")
-        for r in rows[2:]:
-            def num(k):
-                try: return float(get(r, k, "nan").replace(",", ""))
-                except ValueError: return float("nan")
-            def scaled(k):      # bytes metrics come with a unit column
-                v = num(k); u = units[ix[k]] if k in ix else ""
-                return v * {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}.get(u, 1e-6)
-            t = num("gpu__time_duration.sum"); tu = units[ix["gpu__time_duration.sum"]]
-            t = t / 1000 if tu in ("ns", "nsecond") else (t * 1000 if tu in ("ms", "msecond") else t)
-            rd, wr = scaled("dram__bytes_read.sum"), scaled("dram__bytes_write.sum")
-            f.write(f"| `{get(r, 'Kernel Name')[:90]}` | {get(r, 'Grid Size')} | {t:.2f} | {rd:.1f} | {wr:.1f} | {rd + wr:.1f} | "
-                    f"{num('gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'):.1f} | {num('sm__warps_active.avg.pct_of_peak_sustained_active'):.1f} | "
-                    f"{get(r, 'launch__registers_per_thread')} | {num('TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed'):.1f} | {num('lts__throughput.avg.pct_of_peak_sustained_elapsed'):.1f} |\n")
+        f.write(f"# {title}\n\n`ncu --set full --clock-control none --import-source on`, one row per captured launch (cold-cache, serialised; "
+                f"the report itself is `gpurun_out/{os.path.basename(rep)}`, not tracked).  Traffic = dram__bytes_read.sum + dram__bytes_write.sum.\n\n")
+        f.write("| kernel | grid | " + " | ".join(c[0] for c in COLS) + " |\n|---|---|" + "---:|" * len(COLS) + "\n")
+        for d in rows:
+            cells = []
+            for label, _, kind in COLS:
+                v = d[label]
+                cells.append(v if kind == "str" else (f"{v:.2f}" if kind in ("time", "busy") else f"{v:.1f}"))
+            f.write(f"| `{d['kernel'][:90]}` | {d['grid']} | " + " | ".join(cells) + " |\n")
+    return rows
 
 
-os.makedirs(P, exist_ok=True)
-sweep = launch_list(os.path.join(G, "f_launches.csv"))
-table(sweep, "Round 1 (final) — ncu launch list of the C2 sweep",
-      "ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv python bench.py --steps 3 --warmup 3 --no-cpu --mlp 0 --gemm 0 --gpt2 0",
-      os.path.join(P, f"{TAG}_launches_summary.md"), f"Raw CSV: `profiles/{TAG}_launches.csv`.\n")
-shutil.copy(os.path.join(G, "f_launches.csv"), os.path.join(P, f"{TAG}_launches.csv"))
-mlp = launch_list(os.path.join(G, "f_mlp_launches.csv"))
-table(mlp[-15:], "Round 1 (final) — ncu launch list of ONE compiled MNIST-MLP training step (C4, batch 1024)",
-      "ncu --metrics gpu__time_duration.sum --clock-control none --csv python scripts/mlp_profile.py",
-      os.path.join(P, f"{TAG}_mlp_launches_summary.md"),
-      f"Last step of the run (15 launches, in issue order in `profiles/{TAG}_mlp_launches.csv`).  Inside the replayed graph the "
-      "weight-gradient / bias-gradient kernels run on side branches beside the input-gradient GEMMs, so the step takes less than this sum.\n")
-shutil.copy(os.path.join(G, "f_mlp_launches.csv"), os.path.join(P, f"{TAG}_mlp_launches.csv"))
-raw_summary(os.path.join(G, "f_prof_raw.csv"), "Round 1 (final) — full capture of one C2 sweep step (12 launches)", os.path.join(P, f"{TAG}_ncu_full_sweep.md"))
-raw_summary(os.path.join(G, "f_mlp_prof_raw.csv"), "Round 1 (final) — full capture of one MLP training step (15 launches)", os.path.join(P, f"{TAG}_ncu_full_mlp.md"))
-raw_summary(os.path.join(G, "f_gemm_prof_raw.csv"), "Round 1 (final) — full capture of MatmulNode N=4096 (split planes x2 + tcgen05 kernel)", os.path.join(P, f"{TAG}_ncu_full_gemm.md"))
-for src, dst in [("f_bench.json", f"{TAG}_bench_n1.json"), ("f_bench_ref.json", f"{TAG}_bench_reference_arm.json"), ("f_pytest.log", f"{TAG}_pytest_gpu.log")]:
-    shutil.copy(os.path.join(G, src), os.path.join(P, dst))
-print("ok")
+def main():
+    tag = sys.argv[1]
+    traffic = [a.split("=", 1) for a in sys.argv[3:]] if len(sys.argv) > 2 and sys.argv[2] == "--traffic" else []
+    os.makedirs(P, exist_ok=True)
+    captured = {}
+    for rep in sorted(glob.glob(os.path.join(G, f"{tag}_*.ncu-rep"))):
+        name = os.path.basename(rep)[len(tag) + 1:-len(".ncu-rep")]
+        captured[name] = ncu_summary(rep, os.path.join(P, f"{tag}_ncu_{name}.md"), f"{tag}: ncu --set full capture while running `{name}`")
+        print("wrote", f"profiles/{tag}_ncu_{name}.md", len(captured[name]), "launches")
+    ll = os.path.join(G, f"{tag}_launches.csv")
+    if os.path.exists(ll):
+        shutil.copy(ll, os.path.join(P, f"{tag}_launches.csv"))
+        table(launch_list(ll), f"{tag}: ncu launch list of the element-wise / reduction sweep and the fused chains",
+              "ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv python bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --no-cpu",
+              os.path.join(P, f"{tag}_launches_summary.md"), f"Raw CSV: `profiles/{tag}_launches.csv`.\n")
+        print("wrote", f"profiles/{tag}_launches_summary.md")
+    for src, dst in [(f"{tag}_bench.json", f"{tag}_bench_n1.json"), (f"{tag}_bench_ref.json", f"{tag}_bench_reference_arm.json"),
+                     (f"{tag}_pytest.log", f"{tag}_pytest_gpu.log")]:
+        if os.path.exists(os.path.join(G, src)):
+            shutil.copy(os.path.join(G, src), os.path.join(P, dst))
+    if traffic:
+        path = os.path.join(P, "ncu_traffic.json")
+        try:
+            tj = json.load(open(path))
+        except (OSError, ValueError):
+            tj = {}
+        for key, spec in traffic:
+            name, sub = spec.split(":", 1)
+            hits = [d for d in captured.get(name, []) if sub in d["kernel"]]
+            if hits:
+                tj[key] = int(1e6 * sum(d["dram read MB"] + d["dram write MB"] for d in hits) / len(hits))
+        tj["_source"] = (f"scripts/summarize_profiles.py {tag} --traffic ...: dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes), "
+                         f"mean over the captured launches; tables in profiles/{tag}_ncu_*.md")
+        json.dump(tj, open(path, "w"), indent=2)
+        print("wrote profiles/ncu_traffic.json", {k: v for k, v in tj.items() if not k.startswith("_")})
+
+
+if __name__ == "__main__":
+    main()

@@ -360,3 +360,50 @@ def test_matmul_gelu_and_residual_epilogues_equal_the_separate_nodes(gpu, mode, 
     np.testing.assert_array_equal(got_both, (want_gelu + R).astype(np.float32))
     truth = A.astype(np.float64) @ B.astype(np.float64) + bias
     assert np.abs(plain.to_numpy() - truth).max() <= 2e-5 * np.abs(truth).max()
+
+
+@pytest.mark.gpu
+def test_matmul_correction_kinds(gpu):
+    """The plane-fed tcgen05 kernels form the compensation terms A_hi.B_lo + A_lo.B_hi either as two bf16 MMAs (default:
+    2 tensor-pipe units per k) or as two TF32 MMAs (classic 3xTF32), `wf2cu_gemm_set_correction`.  Both against fp64 on a
+    ragged, transposed shape: the bf16 form within 4x of numpy's own fp32 error or 2e-6 (the split itself costs ~5e-7,
+    scripts/emulate_hybrid_split.py), every tile shape bit-identical within a kind, small integers exact in both, and an
+    infinity in A comes out as the infinity sgemm gives (the correction planes carry 0 for it)."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(11)
+    m, n, k = 700, 517, 1000
+    A = rng.normal(size=(m, k)).astype(np.float32)
+    B = rng.normal(size=(n, k)).astype(np.float32)           # used as (!t B)
+    truth = A.astype(np.float64) @ B.T.astype(np.float64)
+    den = np.abs(truth).max()
+    f32_err = np.abs((A @ B.T) - truth).max() / den
+    ints_a = rng.integers(-8, 9, size=(300, 260)).astype(np.float32)
+    ints_b = rng.integers(-8, 9, size=(260, 280)).astype(np.float32)
+    errs = {}
+    try:
+        for kind in (0, 1):
+            gpu._lib.check(lib.wf2cu_gemm_set_correction(kind))
+            outs = []
+            for mode in (2, 5, 6):
+                gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
+                outs.append(gpu.ops.matmul(gpu.from_numpy(A), gpu.ops.t(gpu.from_numpy(B))).to_numpy())
+                assert _last_path(gpu) == {2: 5, 5: 6, 6: 7}[mode]
+                exact = gpu.ops.matmul(gpu.from_numpy(ints_a), gpu.from_numpy(ints_b)).to_numpy()
+                np.testing.assert_array_equal(exact, ints_a @ ints_b)
+            np.testing.assert_array_equal(outs[0], outs[1])
+            np.testing.assert_array_equal(outs[0], outs[2])
+            errs[kind] = float(np.abs(outs[0] - truth).max() / den)
+        gpu._lib.check(lib.wf2cu_gemm_set_correction(0))
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(5))
+        Ainf = A.copy()
+        Ainf[3, 17] = np.inf
+        got = gpu.ops.matmul(gpu.from_numpy(Ainf), gpu.ops.t(gpu.from_numpy(B))).to_numpy()
+        want = np.where(B[:, 17] > 0, np.inf, -np.inf)
+        np.testing.assert_array_equal(got[3], want)
+        assert np.isfinite(got[[0, 1, 2, 4, 5]]).all()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+        gpu._lib.check(lib.wf2cu_gemm_set_correction(0))
+    print(f"\ncorrection kinds on ({m} {k}) x ({n} {k})^T: bf16 {errs[0]:.2e}  tf32 {errs[1]:.2e}  numpy fp32 {f32_err:.2e}")
+    assert errs[1] <= 2e-5 and errs[0] <= 2e-5
+    assert errs[0] <= max(4 * f32_err, 2e-6) + 1.0e-8 * k, (errs, f32_err)
