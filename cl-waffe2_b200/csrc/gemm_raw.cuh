@@ -128,7 +128,9 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int items = job.items();
-  const bool hyb = job.hyb();
+  // bf16 corrections only on pre-split (mixed) lo planes: the converter warps are the raw variants' bottleneck, and mixed
+  // tiles cost them two scattered 8-byte stores per chunk instead of one 16-byte store (r02f: 194 -> 336 us on attention)
+  const bool hyb = (A_RAW || B_RAW) ? false : job.hyb();
   pdl_prologue();
 
   if (threadIdx.x == 0) {
@@ -226,19 +228,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const int src = c < R_ATILE / 16 ? c * 16 : 2 * R_ATILE + (c - R_ATILE / 16) * 16;
             const int dst = src + (c < R_ATILE / 16 ? R_ATILE : R_BTILE);
             const float4 x = *reinterpret_cast<const float4*>(st + src);
-            if (hyb) {
-              // SWIZZLE_64B: the 16-byte chunk of logical index l of row r lies at chunk l ^ ((r >> 1) & 3).  This chunk holds
-              // x[4l : 4l+4]; its 4 hb go to the (l & 1) half of logical chunk l >> 1, its 4 lb to the same half of chunk 2 + (l >> 1).
-              const int cl = (c < R_ATILE / 16) ? c : c - R_ATILE / 16;
-              const int row = cl >> 2, sw = (row >> 1) & 3, l = (cl & 3) ^ sw;
-              uint8_t* rowp = st + dst - (cl & 3) * 16 + (l & 1) * 8;
-              const float f0 = raw_fin(x.x), f1 = raw_fin(x.y), f2 = raw_fin(x.z), f3 = raw_fin(x.w);
-              *reinterpret_cast<uint2*>(rowp + (((l >> 1)) ^ sw) * 16) = make_uint2(raw_bf2(f0, f1), raw_bf2(f2, f3));
-              *reinterpret_cast<uint2*>(rowp + ((2 + (l >> 1)) ^ sw) * 16) =
-                  make_uint2(raw_bf2(raw_lo(x.x), raw_lo(x.y)), raw_bf2(raw_lo(x.z), raw_lo(x.w)));
-            } else {
-              *reinterpret_cast<float4*>(st + dst) = make_float4(raw_lo(x.x), raw_lo(x.y), raw_lo(x.z), raw_lo(x.w));
-            }
+            *reinterpret_cast<float4*>(st + dst) = make_float4(raw_lo(x.x), raw_lo(x.y), raw_lo(x.z), raw_lo(x.w));
           }
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();

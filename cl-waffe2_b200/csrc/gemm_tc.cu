@@ -1256,7 +1256,7 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
     if ((rc = ensure_ws(2 * pb))) return rc;
     float* bh = g_ws;
     float* bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
-    if ((rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, gemm_tc_correction() ? 0 : RK))) return rc;
+    if ((rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, 0))) return rc;
     if ((rc = make_map256(&mb, bh, (int)n, Kp, b_nb, RN))) return rc;
     if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb, RN))) return rc;
   }
@@ -1264,7 +1264,9 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
   TcArgs& t = job.t;
   t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = (int)((k + RK - 1) / RK);
   t.tiles_m = (int)((m + RM - 1) / RM); t.tiles_n = (int)((n + RN - 1) / RN); t.batch = (int)batch;
-  t.passes = gemm_tc_correction() ? 3 : 2;   // 2: the lo tiles are mixed bf16 tiles and the corrections run as bf16 MMAs
+  // 3xTF32: the converter warps are this kernel's bottleneck, and making mixed bf16 tiles (two scattered 8-byte stores per chunk
+  // instead of one 16-byte store) costs them more than the two saved MMAs give back (r02f: 4096^3 654 -> 748 us)
+  t.passes = 3;
   t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
   t.a_bcast = a_nb == 1 ? 1 : 0;
   t.b_bcast = b_nb == 1 ? 1 : 0;
@@ -1312,7 +1314,9 @@ int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor,
   // (twice the L2 -> SM bytes: the kernel is then bound by the ~7.4 TB/s the L2 delivers to the SMs; kept for A/B measurements)
   static int planes = -1;
   if (planes < 0) { const char* e = getenv("WF2CU_ATTN_PLANES"); planes = (e && e[0] == '1') ? 1 : 0; }
-  const int hyb = gemm_tc_correction() ? 0 : 1;     // corrections of Q.K^T as bf16 MMAs on mixed lo tiles (the library default)
+  // corrections of Q.K^T as bf16 MMAs on mixed lo planes: only when the planes are pre-split (the converter warps of the raw
+  // variant are its bottleneck; mixed tiles cost them more than the saved MMAs return: 194 -> 336 us, r02f)
+  const int hyb = (planes && gemm_tc_correction() == 0) ? 1 : 0;
   float* qk_lo = nullptr;
   if (planes) {
     if (ensure_ws((size_t)B * N * 2 * RA_E * 4)) return WF2CU_ERR_CUDA;
