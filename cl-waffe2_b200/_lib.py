@@ -57,7 +57,7 @@ PROTOTYPES = {
     "wf2cu_fill": [VP, f32], "wf2cu_ew_unary": [i32, VP, VP], "wf2cu_pow": [VP, VP, f32],
     "wf2cu_cmp": [i32, VP, VP, f32, VP, f32, f32], "wf2cu_fused": [C.POINTER(C.c_int32), i32, VP, i32],
     "wf2cu_fused_set_mode": [i32], "wf2cu_fused_last_path": [C.POINTER(i32)], "wf2cu_fused_catalogue_size": [C.POINTER(i32)],
-    "wf2cu_reduce_sum": [VP, VP, i32, f32], "wf2cu_softmax": [VP, VP, i32, i32], "wf2cu_softmax_ex": [VP, VP, i32, i32, f32],
+    "wf2cu_reduce_sum": [VP, VP, i32, f32], "wf2cu_sum_all_noalloc": [vp, i64, i64, vp, i64, i32, f32], "wf2cu_softmax": [VP, VP, i32, i32], "wf2cu_softmax_ex": [VP, VP, i32, i32, f32],
     "wf2cu_reduce_maxmin": [i32, VP, VP], "wf2cu_argmaxmin": [i32, VP, VP],
     "wf2cu_gemm": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i64, i64, i64],
     "wf2cu_gemm_set_mode": [i32], "wf2cu_gemm_set_correction": [i32], "wf2cu_gemm_last_path": [C.POINTER(i32)],

@@ -951,3 +951,71 @@ int wf2cu_reduce_sum(const wf2cu_view* x, const wf2cu_view* out_bcast, int accum
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ allocation-free `sum :axis t`
+// wf2cu_sum_all_noalloc: reduce_flat_bulk_kernel<MSum> fed from a file-scope device array instead of the cudaMalloc'ed
+// scratch of runtime.cu, for callers that may not allocate (graph capture, serving loops).  Layout of the array:
+// [0, kNoAllocSlots) one fp32 partial per CTA, then one 256-byte line whose first word is the last-block ticket.
+// Every GPU that loads the library holds these kNoAllocBytes until exit.  All calls share the array: calls that
+// overlap on the GPU (two streams, two host threads) race on the partials and on the ticket.
+namespace wf2 {
+constexpr int kNoAllocSlots = 1024;                                   // CTAs a launch may use
+constexpr size_t kNoAllocBytes = kNoAllocSlots * sizeof(float) + 256;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// In host code `g_noalloc_scratch` is the host-side stand-in of the symbol, not a device address: the address the
+// kernel gets is looked up once per device (with that device current) and kept here.
+static unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+static int noalloc_setup(int dev, unsigned char** out) {
+  if (dev < 0 || dev >= kNoAllocMaxDevices)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_sum_all_noalloc: device ordinal %d outside 0..%d", dev, kNoAllocMaxDevices - 1);
+  if (!g_noalloc_ptr[dev]) {
+    unsigned char* p = nullptr;
+    WF2_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    WF2_CUDA(cudaFuncSetAttribute(reduce_flat_bulk_kernel<MSum>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFlatStages * kFlatChunk));
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace wf2
+
+extern "C" {
+
+int wf2cu_sum_all_noalloc(const void* x, int64_t x_off, int64_t n, void* out, int64_t out_off, int accumulate, float divisor) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(x && out, "wf2cu_sum_all_noalloc: null pointer");
+  WF2_CHECK(n >= 1, "wf2cu_sum_all_noalloc: n = %lld (need at least one element)", (long long)n);
+  if (n > (int64_t)WF2CU_NOALLOC_MAX_ELEMS)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_sum_all_noalloc: n = %lld exceeds the maximum of %lld elements this entry point "
+                     "accepts (its scratch is a fixed %zu-byte device array); use wf2cu_reduce_sum",
+                     (long long)n, (long long)WF2CU_NOALLOC_MAX_ELEMS, kNoAllocBytes);
+  const float* sptr = reinterpret_cast<const float*>(x) + x_off;
+  float* dptr = reinterpret_cast<float*>(out) + out_off;
+  WF2_CHECK(al16(sptr), "wf2cu_sum_all_noalloc: x + x_off must be 16-byte aligned");
+  State& s = S();
+  int dev = -1;
+  WF2_CUDA(cudaGetDevice(&dev));
+  unsigned char* scratch = nullptr;
+  int rc = noalloc_setup(dev, &scratch);
+  if (rc) return rc;
+  float* partial = reinterpret_cast<float*>(scratch);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + kNoAllocSlots * sizeof(float));
+  // same grid rule as wf2cu_reduce_sum's flat path (2 persistent CTAs per SM), so both give the same bits
+  const int64_t nchunks = (n * 4) / kFlatChunk;
+  int64_t grid = (int64_t)s.sm_count * 2;
+  if (grid > nchunks) grid = nchunks;
+  if (grid < 1) grid = 1;               // shorter than one chunk: CTA 0's ragged-tail loop does all of it
+  if (grid > kNoAllocSlots) grid = kNoAllocSlots;
+  // the ticket must start at zero whatever an earlier (possibly aborted) call left behind; the partials are
+  // overwritten before they are read
+  WF2_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s.stream));
+  FlatArgs f{sptr, dptr, partial, ticket, n};
+  Fin fin{accumulate ? FIN_ADD : FIN_SET, divisor};
+  reduce_flat_bulk_kernel<MSum><<<(unsigned)grid, kFlatThreads, kFlatStages * kFlatChunk, s.stream>>>(f, fin);
+  return post_launch("wf2cu_sum_all_noalloc");
+}
+
+}  // extern "C"

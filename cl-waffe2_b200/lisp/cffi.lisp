@@ -87,6 +87,8 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 fused-catalogue-size ((out :pointer)))
 ;; reductions / composites
 (defwf2 reduce-sum ((x :pointer) (out :pointer) (accumulate :int) (divisor :float)))
+;; no counterpart in the reference: allocation-free `sum :axis t` (fixed device-array scratch), see include/waffe2cuda.h
+(defwf2 sum-all-noalloc ((x :pointer) (x-off :int64) (n :int64) (out :pointer) (out-off :int64) (accumulate :int) (divisor :float)))
 (defwf2 softmax ((x :pointer) (out :pointer) (axis :int) (avoid-overflow :int)))
 (defwf2 softmax-ex ((x :pointer) (out :pointer) (axis :int) (avoid-overflow :int) (pre-divisor :float)))
 (defwf2 reduce-maxmin ((is-min :int) (x :pointer) (out :pointer)))

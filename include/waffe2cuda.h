@@ -181,6 +181,17 @@ int  wf2cu_fused_catalogue_size(int* out);
  * result (1/count gives `!mean`, `reduction.lisp:81-136`; division is done as a true divide by
  * `divisor` when divisor != 0 to match `!div`). */
 int  wf2cu_reduce_sum(const wf2cu_view* x, const wf2cu_view* out_bcast, int accumulate, float divisor);
+/* Allocation-free `sum :axis t`.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * out[out_off] <- [out[out_off] +] sum(x[x_off .. x_off + n)) [/ divisor]  (fp32 element offsets, device pointers,
+ * x + x_off 16-byte aligned), on the library's stream — the flat-sum kernel of wf2cu_reduce_sum with its per-CTA
+ * partials and last-block ticket in a file-scope `static __device__` array of 4352 bytes (1024 partials + one 256-byte
+ * ticket line) that every GPU loading the library holds until exit.  It calls no cudaMalloc / cudaFree / allocating
+ * routine.  n > WF2CU_NOALLOC_MAX_ELEMS is refused with WF2CU_ERR_UNSUPPORTED (use wf2cu_reduce_sum).  Every call
+ * shares the one array (the ticket is cleared on the stream before each launch, the partials are overwritten before
+ * they are read): calls that overlap on the GPU — other streams, other host threads — race; serialise them. */
+#define WF2CU_NOALLOC_MAX_ELEMS (1ll << 28)   /* 1 GiB of fp32 */
+int  wf2cu_sum_all_noalloc(const void* x, int64_t x_off, int64_t n, void* out, int64_t out_off, int accumulate, float divisor);
 /* `!softmax` (`nn/activation.lisp:126-159`): mean-shift (avoid_overflow) or plain, over `axis`. */
 int  wf2cu_softmax(const wf2cu_view* x, const wf2cu_view* out, int axis, int avoid_overflow);
 /* `(!softmax (!div x n))`: the scalar divide in front folded into the same pass (GPT-2's attention weights,
