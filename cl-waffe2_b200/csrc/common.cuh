@@ -71,6 +71,9 @@ int ensure_scratch(size_t bytes);           // per branch: the buffer holds kBra
 void* scratch_base();                        // the current branch's region (valid after ensure_scratch)
 unsigned int* counters_base();               // the current branch's kCountersPerBranch tickets
 void gemm_tc_release();   // gemm_tc.cu: frees the hi/lo plane workspaces
+// gemm_tc.cu: storage [ptr, ptr + bytes) was overwritten by a transfer (released = false: planes kept for a constant operand
+// there are split again on the next product) or freed (released = true: planes and the constant declaration are dropped)
+void gemm_tc_const_touch(const void* ptr, size_t bytes, bool released);
 
 // ---- programmatic dependent launch (PDL) -------------------------------------------------------------
 // Back-to-back kernels of a compiled instruction sequence are serialised by the stream (or by the edges of the captured

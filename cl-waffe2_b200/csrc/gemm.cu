@@ -25,7 +25,10 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
 int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                  float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act, const float* res,
                  int64_t ldres);
-bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch);
+bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch, double a_share, double b_share);
+double gemm_tc_prepass_share(const float* p, int64_t ld, int64_t bstride, int64_t nbatch, bool kmajor);
+int gemm_tc_const_declare(const void* ptr, size_t bytes, int on);
+void gemm_tc_const_stats(int64_t* entries, int64_t* bytes);
 void gemm_tc_set_correction(int kind);
 int gemm_tc_correction();
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
@@ -697,7 +700,9 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     if (mode == 4) return set_error(WF2CU_ERR_UNSUPPORTED, "%s: fused tensor-core kernel forced but declined (out of range)", who);
   }
   if (mode == 7 || (mode == 0 && raw_auto() && !trans_a && 2.0 * (double)m * (double)n * (double)k * (double)batch >= 1.0e9 && m >= 64 && n >= 64 &&
-                    k >= 32 && gemm_raw_preferred(trans_b ? 1 : 0, m, n, k, batch))) {
+                    k >= 32 && gemm_raw_preferred(trans_b ? 1 : 0, m, n, k, batch,
+                                                  gemm_tc_prepass_share(a, lda, stride_a, (stride_a == 0 || batch == 1) ? 1 : batch, true),
+                                                  gemm_tc_prepass_share(b, ldb, stride_b, (stride_b == 0 || batch == 1) ? 1 : batch, trans_b != 0)))) {
     // A is K-major: raw fp32 tiles by TMA, lo planes made on the SM — no operand pre-pass (gemm_raw.cuh)
     const int r = gemm_raw_try(trans_a, trans_b, m, n, k, a, lda, b, ldb, c, ldc, batch, stride_a, stride_b, stride_c, bias, act, res, ldres);
     if (r < 0) return -r;
@@ -749,6 +754,18 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
   sgemm_simt_kernel<<<grid, 256, 0, S().stream>>>(g);
   S().gemm_last_path = WF2CU_GEMM_PATH_SIMT;
   return post_launch("wf2cu_gemm(simt)");
+}
+
+int wf2cu_gemm_const_operand(const void* base, int64_t offset, int64_t count, int constant) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(base && offset >= 0 && count > 0, "wf2cu_gemm_const_operand: bad range (offset %lld, count %lld)", (long long)offset, (long long)count);
+  return gemm_tc_const_declare((const float*)base + offset, (size_t)count * 4, constant);
+}
+
+int wf2cu_gemm_const_stats(int64_t* entries, int64_t* bytes) {
+  WF2_CHECK(entries && bytes, "wf2cu_gemm_const_stats: null output");
+  gemm_tc_const_stats(entries, bytes);
+  return 0;
 }
 
 int wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,

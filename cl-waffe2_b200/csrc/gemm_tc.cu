@@ -21,6 +21,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdlib.h>
+#include <map>
+#include <tuple>
 #include <type_traits>
 #include <vector>
 #include "common.cuh"
@@ -82,10 +84,15 @@ struct SplitArgs {
   int R, K, Kp;       // rows of the plane (m or n), true k, padded k
   int vec;            // src rows are 16-byte aligned (direct variant only)
   int bf_blk;         // 0: fp32 lo plane ; 16 / 32: mixed bf16 plane with that k-block
+  int raw_hi;         // the kernel reads the SOURCE itself as its hi plane (TMA map over the operand; kind::tf32 uses the upper
+                      // 19 bits of the container, i.e. hi = trunc_tf32(x)): no hi plane is written and lo = x - trunc_tf32(x)
 };
 
+__device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
+template <bool RAW_HI>
 __device__ __forceinline__ void split_bf(float x, float& hi, uint16_t& hb, uint16_t& lb) {
-  hi = tf32_rn(x);
+  hi = RAW_HI ? trunc_tf32(x) : tf32_rn(x);
   if (fabsf(hi) <= 3.0e38f) {
     hb = __bfloat16_as_ushort(__float2bfloat16_rn(x));
     lb = __bfloat16_as_ushort(__float2bfloat16_rn(x - hi));   // x - hi is exact
@@ -93,8 +100,15 @@ __device__ __forceinline__ void split_bf(float x, float& hi, uint16_t& hb, uint1
     hb = 0; lb = 0;
   }
 }
+template <bool RAW_HI>
+__device__ __forceinline__ void split1v(float x, float& hi, float& lo) {
+  if (!RAW_HI) { split1(x, hi, lo); return; }
+  hi = trunc_tf32(x);
+  lo = (fabsf(x) <= 3.0e38f) ? tf32_rn(x - hi) : 0.f;
+}
 
 // src is K-contiguous: (r, k) at r*ld + k
+template <bool RAW_HI>
 __global__ void __launch_bounds__(256) split_planes_direct_kernel(const __grid_constant__ SplitArgs a) {
   const int kq = a.Kp >> 2;
   const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
@@ -114,9 +128,9 @@ __global__ void __launch_bounds__(256) split_planes_direct_kernel(const __grid_c
   if (a.bf_blk) {
     float4 h;
     uint16_t hb[4], lb[4];
-    split_bf(x[0], h.x, hb[0], lb[0]); split_bf(x[1], h.y, hb[1], lb[1]);
-    split_bf(x[2], h.z, hb[2], lb[2]); split_bf(x[3], h.w, hb[3], lb[3]);
-    *reinterpret_cast<float4*>(a.hi + o) = h;
+    split_bf<RAW_HI>(x[0], h.x, hb[0], lb[0]); split_bf<RAW_HI>(x[1], h.y, hb[1], lb[1]);
+    split_bf<RAW_HI>(x[2], h.z, hb[2], lb[2]); split_bf<RAW_HI>(x[3], h.w, hb[3], lb[3]);
+    if (!RAW_HI) *reinterpret_cast<float4*>(a.hi + o) = h;
     // row base in 16-bit units: 2 * Kp per row; k-block kb holds hb[0:blk] then lb[0:blk]
     uint16_t* row = reinterpret_cast<uint16_t*>(a.lo) + (b * a.R + r) * (int64_t)(2 * a.Kp);
     const int kb = k / a.bf_blk, j = k - kb * a.bf_blk;
@@ -126,8 +140,8 @@ __global__ void __launch_bounds__(256) split_planes_direct_kernel(const __grid_c
     return;
   }
   float4 h, l;
-  split1(x[0], h.x, l.x); split1(x[1], h.y, l.y); split1(x[2], h.z, l.z); split1(x[3], h.w, l.w);
-  *reinterpret_cast<float4*>(a.hi + o) = h;
+  split1v<RAW_HI>(x[0], h.x, l.x); split1v<RAW_HI>(x[1], h.y, l.y); split1v<RAW_HI>(x[2], h.z, l.z); split1v<RAW_HI>(x[3], h.w, l.w);
+  if (!RAW_HI) *reinterpret_cast<float4*>(a.hi + o) = h;
   *reinterpret_cast<float4*>(a.lo + o) = l;
 }
 
@@ -146,7 +160,7 @@ __global__ void __launch_bounds__(256) split_planes_transpose_kernel(const __gri
     float h, l;
     if (a.bf_blk) {
       uint16_t hb, lb;
-      split_bf(x, h, hb, lb);
+      split_bf<false>(x, h, hb, lb);
       l = __uint_as_float((uint32_t)hb | ((uint32_t)lb << 16));
     } else {
       split1(x, h, l);
@@ -954,11 +968,13 @@ static size_t g_ws_bytes = 0;
 static std::vector<void*> g_retired;     // older workspaces a captured graph may still reference
 static bool g_attr_set = false;
 
+void gemm_tc_const_release();
 void gemm_tc_release() {
   if (g_ws) cudaFree(g_ws);
   for (void* p : g_retired) cudaFree(p);
   g_retired.clear();
   g_ws = nullptr; g_ws_bytes = 0; g_attr_set = false;
+  gemm_tc_const_release();
 }
 
 static int ensure_ws(size_t bytes) {
@@ -993,17 +1009,6 @@ int gemm_tc_correction() {
 }
 void gemm_tc_set_correction(int kind) { g_correction = kind ? 1 : 0; }
 
-static int make_map(CUtensorMap* map, float* base, int rows, int Kp, int nbatch, int box_rows) {
-  cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)rows, (cuuint64_t)nbatch};
-  cuuint64_t strides[2] = {(cuuint64_t)Kp * 4, (cuuint64_t)rows * Kp * 4};
-  cuuint32_t box[3] = {(cuuint32_t)TK, (cuuint32_t)box_rows, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return -set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rows=%d Kp=%d batch=%d", (int)r, rows, Kp, nbatch);
-  return 0;
-}
-
 static int make_map256(CUtensorMap* map, float* base, int rows, int Kp, int nbatch, int box_rows) {
   cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)rows, (cuuint64_t)nbatch};
   cuuint64_t strides[2] = {(cuuint64_t)Kp * 4, (cuuint64_t)rows * Kp * 4};
@@ -1036,19 +1041,134 @@ static int make_map_c(CUtensorMap* map, float* C, int64_t m, int64_t n, int64_t 
 }
 
 static int launch_split(const float* src, float* hi, float* lo, int64_t ld, int64_t sx, int R, int K, int Kp, int nbatch,
-                        bool r_contiguous, int bf_blk) {
-  SplitArgs sa{src, hi, lo, ld, sx, R, K, Kp, 0, bf_blk};
+                        bool r_contiguous, int bf_blk, bool raw_hi = false) {
+  SplitArgs sa{src, hi, lo, ld, sx, R, K, Kp, 0, bf_blk, raw_hi ? 1 : 0};
   if (!r_contiguous) {
     sa.vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (ld & 3) == 0 && (sx & 3) == 0) ? 1 : 0;
     const int64_t work = (int64_t)R * (Kp >> 2);
     dim3 grid((unsigned)((work + 255) / 256), (unsigned)nbatch);
-    split_planes_direct_kernel<<<grid, 256, 0, S().stream>>>(sa);
+    if (raw_hi) split_planes_direct_kernel<true><<<grid, 256, 0, S().stream>>>(sa);
+    else        split_planes_direct_kernel<false><<<grid, 256, 0, S().stream>>>(sa);
   } else {
     dim3 grid((unsigned)((R + 31) / 32), (unsigned)(Kp / 32), (unsigned)nbatch);
     split_planes_transpose_kernel<<<grid, 256, 0, S().stream>>>(sa);
   }
   const int rc = post_launch("wf2cu_gemm(split)");
   return rc ? -rc : 0;
+}
+
+// A K-major operand plane or the operand ITSELF as (k, rows, batch) with a row pitch of `ld` floats; k beyond the true extent is
+// zero-filled by the TMA unit (OOB fill), so a raw source needs no padded copy.
+static int make_map_k(CUtensorMap* map, const float* base, int64_t kdim, int64_t rows, int64_t ld, int64_t nbatch, int64_t bstride,
+                      int box_k, int box_rows) {
+  cuuint64_t dims[3] = {(cuuint64_t)kdim, (cuuint64_t)rows, (cuuint64_t)(nbatch < 1 ? 1 : nbatch)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 4, (cuuint64_t)(nbatch > 1 ? bstride : rows * ld) * 4};
+  cuuint32_t box[3] = {(cuuint32_t)box_k, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        box_k == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return -set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(operand, box %dx%d) failed (%d) k=%lld rows=%lld ld=%lld batch=%lld",
+                                           box_k, box_rows, (int)r, (long long)kdim, (long long)rows, (long long)ld, (long long)nbatch);
+  return 0;
+}
+
+static bool raw_operand_ok(const float* p, int64_t ld, int64_t bstride, int64_t nbatch);
+
+// WF2CU_GEMM_RAWHI=0: always write RN hi planes (A/B measurements; the round-1 behaviour)
+static bool rawhi_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("WF2CU_GEMM_RAWHI"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on != 0;
+}
+
+// ---- prepared (constant) operands ------------------------------------------------------------------------------
+// BLAS libraries offer packed-operand entry points (sgemm_pack / sgemm_compute) for a matrix that is multiplied many times; here
+// the host declares a storage range constant (wf2cu_gemm_const_operand: the parameters of a model in inference) and the planes
+// of an operand that starts inside such a range are split ONCE into buffers of their own and found again by
+// (pointer, pitch, shape, layout).  An upload / memset / free that touches the range marks the planes stale (re-split on the
+// next product) or drops them.  GPT-2 small: 48 weight matrices, 680 MB of planes, 48 transposing split launches per forward saved.
+struct ConstRange { uintptr_t lo, hi; };
+struct PlaneKey {
+  const float* p; int64_t ld, sx; int R, K, Kp, nb, rcontig, bf_blk, raw_hi;
+  bool operator<(const PlaneKey& o) const {
+    return std::tie(p, ld, sx, R, K, Kp, nb, rcontig, bf_blk, raw_hi) < std::tie(o.p, o.ld, o.sx, o.R, o.K, o.Kp, o.nb, o.rcontig, o.bf_blk, o.raw_hi);
+  }
+};
+struct PlaneVal { float* hi; float* lo; size_t bytes; uintptr_t src_lo, src_hi; bool stale; };
+static std::vector<ConstRange> g_const;
+static std::map<PlaneKey, PlaneVal> g_planes;
+static size_t g_planes_bytes = 0;
+
+static bool in_const_range(const float* p) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  for (const ConstRange& r : g_const)
+    if (a >= r.lo && a < r.hi) return true;
+  return false;
+}
+
+static void drop_plane(PlaneVal& v) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(S().stream, &cs);
+  if (cs != cudaStreamCaptureStatusNone) { if (v.hi) g_retired.push_back(v.hi); if (v.lo) g_retired.push_back(v.lo); }
+  else { if (v.hi) cudaFree(v.hi); if (v.lo) cudaFree(v.lo); }
+  g_planes_bytes -= v.bytes;
+}
+
+// the storage [ptr, ptr + bytes) was written (stale = true: keep the buffers, split again) or released (drop them)
+void gemm_tc_const_touch(const void* ptr, size_t bytes, bool released) {
+  if (g_planes.empty() && (!released || g_const.empty())) return;
+  const uintptr_t lo = reinterpret_cast<uintptr_t>(ptr), hi = lo + bytes;
+  for (auto it = g_planes.begin(); it != g_planes.end();) {
+    if (it->second.src_lo < hi && lo < it->second.src_hi) {
+      if (released) { drop_plane(it->second); it = g_planes.erase(it); continue; }
+      it->second.stale = true;
+    }
+    ++it;
+  }
+  if (released)
+    for (size_t i = 0; i < g_const.size();)
+      if (g_const[i].lo < hi && lo < g_const[i].hi) g_const.erase(g_const.begin() + i); else ++i;
+}
+
+int gemm_tc_const_declare(const void* ptr, size_t bytes, int on) {
+  const uintptr_t lo = reinterpret_cast<uintptr_t>(ptr), hi = lo + bytes;
+  if (on) {
+    for (const ConstRange& r : g_const)
+      if (r.lo <= lo && hi <= r.hi) return 0;
+    g_const.push_back(ConstRange{lo, hi});
+    return 0;
+  }
+  gemm_tc_const_touch(ptr, bytes, true);
+  return 0;
+}
+
+void gemm_tc_const_release() {
+  for (auto& kv : g_planes) { if (kv.second.hi) cudaFree(kv.second.hi); if (kv.second.lo) cudaFree(kv.second.lo); }
+  g_planes.clear(); g_const.clear(); g_planes_bytes = 0;
+}
+
+void gemm_tc_const_stats(int64_t* entries, int64_t* bytes) { *entries = (int64_t)g_planes.size(); *bytes = (int64_t)g_planes_bytes; }
+
+// the planes of a constant operand: found, or allocated here (fresh = they still have to be filled).  <0 = -(error code)
+static int const_planes(const PlaneKey& key, size_t plane_bytes, size_t src_floats, PlaneVal** out, bool* fresh) {
+  auto it = g_planes.find(key);
+  if (it != g_planes.end()) { *out = &it->second; *fresh = it->second.stale; it->second.stale = false; return 0; }
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(S().stream, &cs);
+  if (cs != cudaStreamCaptureStatusNone)
+    return -set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_gemm: the planes of a constant operand must be allocated (%zu bytes) while a CUDA graph is "
+                      "being captured; run the same product once before wf2cu_graph_begin", plane_bytes);
+  PlaneVal v{nullptr, nullptr, 0, reinterpret_cast<uintptr_t>(key.p), reinterpret_cast<uintptr_t>(key.p) + src_floats * 4, false};
+  cudaError_t e = cudaSuccess;
+  if (!key.raw_hi) e = cudaMalloc(&v.hi, plane_bytes);
+  if (e == cudaSuccess) e = cudaMalloc(&v.lo, plane_bytes);
+  if (e != cudaSuccess) { if (v.hi) cudaFree(v.hi); return -cuda_fail(e, "cudaMalloc(constant operand planes)", __FILE__, __LINE__); }
+  v.bytes = (key.raw_hi ? 1 : 2) * plane_bytes;
+  g_planes_bytes += v.bytes;
+  *out = &g_planes.emplace(key, v).first->second;
+  *fresh = true;
+  return 0;
 }
 
 // auto rule for the 256-row tile kernels (0 = stay on the 128x256 kernel): they cannot overlap the epilogue with the
@@ -1106,12 +1226,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   const int b_nb = (sb == 0 || batch == 1) ? 1 : (int)batch;
   auto plane = [&](int64_t rows, int nb) { return (((size_t)nb * rows * Kp * 4) + 255) & ~(size_t)255; };
   const size_t pa = plane(m, a_nb), pb = plane(n, b_nb);
-  int rc = ensure_ws(2 * pa + 2 * pb);
-  if (rc) return rc;
-  float* ah = g_ws;
-  float* al = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ah) + pa);
-  float* bh = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(al) + pa);
-  float* bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
+  int rc = 0;
   CUtensorMap mah, mal, mbh, mbl, mc;
   const int c_tma = make_map_c(&mc, C, m, n, ldc, sc, batch);
   // 128x256, 256x256 or 256x192 tiles: results are bit-identical (same k order per output), pick_tile256 chooses
@@ -1125,12 +1240,47 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     nb = pick_tile256(Kp, ((m + TM - 1) / TM) * ((n + TN - 1) / TN) * batch, tiles256, tiles192, S().sm_count, passes == 2);
   // the second plane: fp32 lo (3xTF32) or the mixed bf16 plane laid out for the chosen kernel's k-block
   const int bf_blk = passes == 2 ? (nb ? T2K : TK) : 0;
-  // A: logical (m x k).  ta = stored transposed (k x m) -> m is the contiguous axis of the source.
-  rc = launch_split(A, ah, al, lda, sa, (int)m, (int)k, Kp, a_nb, ta != 0, bf_blk);
-  if (rc) return rc;
-  // B: planes are (n x k).  op(B) is k x n; !tb = stored (k x n) row-major -> n contiguous.
-  rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, bf_blk);
-  if (rc) return rc;
+  // Operand planes.  A: logical (m x k); ta = stored transposed (k x m) -> m is the contiguous axis of the source.
+  // B: planes are (n x k); op(B) is k x n; !tb = stored (k x n) row-major -> n contiguous.
+  //   raw_hi   a K-major, 16-byte aligned operand is its own hi plane (TMA map over the source, hi = trunc_tf32(x)): its pre-pass
+  //            writes the second plane only (4 instead of 8 bytes per element)
+  //   constant an operand inside a range declared with wf2cu_gemm_const_operand keeps its planes between calls (no pre-pass)
+  struct Prep { const float* src; int64_t ld, sx; int rows, nb; bool rcontig, raw, konst; float* hi; float* lo; size_t pbytes; };
+  Prep pr[2] = {{A, lda, sa, (int)m, a_nb, ta != 0, false, false, nullptr, nullptr, pa},
+                {B, ldb, sb, (int)n, b_nb, tb == 0, false, false, nullptr, nullptr, pb}};
+  size_t ws_need = 0;
+  bool fresh[2] = {true, true};
+  for (Prep& q : pr) {
+    q.raw = passes >= 2 && !q.rcontig && rawhi_enabled() && raw_operand_ok(q.src, q.ld, q.sx, q.nb);
+    q.konst = in_const_range(q.src);
+    if (!q.konst) ws_need += (q.raw ? 1 : 2) * q.pbytes;
+  }
+  if (ws_need && (rc = ensure_ws(ws_need))) return rc;
+  {
+    uint8_t* w = reinterpret_cast<uint8_t*>(g_ws);
+    for (int i = 0; i < 2; ++i) {
+      Prep& q = pr[i];
+      if (q.konst) {
+        const PlaneKey key{q.src, q.ld, q.sx, q.rows, (int)k, Kp, q.nb, q.rcontig ? 1 : 0, bf_blk, q.raw ? 1 : 0};
+        const int64_t inner = q.rcontig ? q.rows : k, outer = q.rcontig ? k : q.rows;
+        const size_t src_floats = (size_t)((q.nb - 1) * q.sx + (outer - 1) * q.ld + inner);
+        PlaneVal* v = nullptr;
+        if ((rc = const_planes(key, q.pbytes, src_floats, &v, &fresh[i]))) return rc;
+        q.hi = v->hi; q.lo = v->lo;
+      } else {
+        if (!q.raw) { q.hi = reinterpret_cast<float*>(w); w += q.pbytes; }
+        q.lo = reinterpret_cast<float*>(w); w += q.pbytes;
+      }
+      if (fresh[i] && (rc = launch_split(q.src, q.hi, q.lo, q.ld, q.sx, q.rows, (int)k, Kp, q.nb, q.rcontig, bf_blk, q.raw))) return rc;
+    }
+  }
+  // hi maps: the source itself (raw) or the hi plane; lo maps: the second plane
+  auto maps = [&](const Prep& q, CUtensorMap* mh, CUtensorMap* ml, int box_k, int box_rows) -> int {
+    int r = q.raw ? make_map_k(mh, q.src, k, q.rows, q.ld, q.nb, q.sx, box_k, box_rows)
+                  : make_map_k(mh, q.hi, Kp, q.rows, Kp, q.nb, (int64_t)q.rows * Kp, box_k, box_rows);
+    if (r) return r;
+    return make_map_k(ml, q.lo, Kp, q.rows, Kp, q.nb, (int64_t)q.rows * Kp, box_k, box_rows);
+  };
 
   if (nb) {
     // 256-row tiles: two M = 128 MMAs share every B slice (42.7 instead of 62.5 B/clk of L2 -> SM traffic per SM)
@@ -1142,10 +1292,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
       if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_tc256_kernel)", __FILE__, __LINE__);
       attr256 = true;
     }
-    if ((rc = make_map256(&mah, ah, (int)m, Kp, a_nb, 256))) return rc;
-    if ((rc = make_map256(&mal, al, (int)m, Kp, a_nb, 256))) return rc;
-    if ((rc = make_map256(&mbh, bh, (int)n, Kp, b_nb, nb))) return rc;
-    if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb, nb))) return rc;
+    if ((rc = maps(pr[0], &mah, &mal, T2K, 256))) return rc;
+    if ((rc = maps(pr[1], &mbh, &mbl, T2K, nb))) return rc;
     TcArgs t;
     t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = Kp / T2K;
     t.tiles_m = (int)tiles_m256; t.tiles_n = (int)((n + nb - 1) / nb); t.batch = (int)batch;
@@ -1162,10 +1310,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     S().gemm_last_path = nb == 256 ? WF2CU_GEMM_PATH_TC_256X256 : WF2CU_GEMM_PATH_TC_256X192;
     return rc ? -rc : 1;
   }
-  if ((rc = make_map(&mah, ah, (int)m, Kp, a_nb, TM))) return rc;
-  if ((rc = make_map(&mal, al, (int)m, Kp, a_nb, TM))) return rc;
-  if ((rc = make_map(&mbh, bh, (int)n, Kp, b_nb, TN))) return rc;
-  if ((rc = make_map(&mbl, bl, (int)n, Kp, b_nb, TN))) return rc;
+  if ((rc = maps(pr[0], &mah, &mal, TK, TM))) return rc;
+  if ((rc = maps(pr[1], &mbh, &mbl, TK, TN))) return rc;
 
   TcArgs t;
   t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = Kp / TK;
@@ -1205,13 +1351,21 @@ static bool raw_operand_ok(const float* p, int64_t ld, int64_t bstride, int64_t 
 // of six 128x256x8 MMAs), 1110 / 1850 / 1500 on the 128x256 / 256x256 / 256x192 planes kernels; the 256-row tiles expose their
 // epilogue; an operand pre-pass moves 12 bytes per element at ~4.5 TB/s plus a launch.  The raw kernel skips A's pre-pass always
 // and B's when B is K-major.  2048^3: raw 88 us vs 101; 4096^3: 654 vs 571; 8192x2304x768: 124 vs 132; 8192x768x3072: 236 vs 210.
-bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch) {
+// share of a full pre-pass (read 4 + write 8 bytes per element, one launch) an operand of the planes kernels costs: 0 when its
+// planes are kept (constant operand), 2/3 when the source is its own hi plane, 1 otherwise
+double gemm_tc_prepass_share(const float* p, int64_t ld, int64_t bstride, int64_t nbatch, bool kmajor) {
+  if (in_const_range(p)) return 0.0;
+  if (kmajor && rawhi_enabled() && gemm_tc_correction() == 0 && raw_operand_ok(p, ld, bstride, nbatch)) return 2.0 / 3.0;
+  return 1.0;
+}
+
+bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch, double a_share, double b_share) {
   const double sms = (double)S().sm_count;
   auto waves = [&](int64_t tiles) { return (double)((tiles * batch + (int64_t)sms - 1) / (int64_t)sms); };
   auto presplit = [&](int64_t rows) { return (double)rows * (double)k * (double)batch * 12.0 / 4.5e12 * 1.9e9 + 6000.0; };
   const double nkb = (double)((k + 15) / 16);
   const int64_t t128 = ((m + 127) / 128) * ((n + 255) / 256), t256 = ((m + 255) / 256) * ((n + 255) / 256), t192 = ((m + 255) / 256) * ((n + 191) / 192);
-  const double raw = waves(t128) * nkb * 1180.0 + 8000.0 + (tb ? 0.0 : presplit(n));
+  const double raw = waves(t128) * nkb * 1180.0 + 8000.0 + (tb ? 0.0 : (b_share > 0.0 ? presplit(n) : 0.0));
   // the planes kernels with bf16 corrections (the default) spend 2 tensor-pipe units per k instead of 3: 870 / 1470 / 1190
   // (r02d: 2048^3 raw 90 us vs 95; 8192x2304x768 raw 129 vs 112; 4096^3 raw 654 vs 490)
   const bool bf = gemm_tc_correction() == 0;
@@ -1220,7 +1374,7 @@ bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch) 
   const double p192 = waves(t192) * (nkb * (bf ? 1190.0 : 1500.0) + (bf ? 5500.0 : 8000.0));
   if (p256 < planes) planes = p256;
   if (p192 < planes) planes = p192;
-  planes += presplit(m) + presplit(n);
+  planes += (a_share > 0.0 ? a_share * presplit(m) : 0.0) + (b_share > 0.0 ? b_share * presplit(n) : 0.0);
   return raw <= planes;
 }
 
@@ -1253,10 +1407,21 @@ int gemm_raw_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A
     // B is MN-major for the product (or misaligned): transposing split into K-major hi / lo planes, as before
     const int Kp = (int)((k + TK - 1) / TK) * TK;
     const size_t pb = ((((size_t)b_nb * n * Kp * 4) + 255) & ~(size_t)255);
-    if ((rc = ensure_ws(2 * pb))) return rc;
-    float* bh = g_ws;
-    float* bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
-    if ((rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, 0))) return rc;
+    float *bh, *bl;
+    bool fresh = true;
+    if (in_const_range(B)) {              // a constant operand keeps its planes between calls
+      const bool rc_b = tb == 0;
+      const PlaneKey key{B, ldb, sb, (int)n, (int)k, Kp, b_nb, rc_b ? 1 : 0, 0, 0};
+      const int64_t inner = rc_b ? n : k, outer = rc_b ? k : n;
+      PlaneVal* v = nullptr;
+      if ((rc = const_planes(key, pb, (size_t)((b_nb - 1) * sb + (outer - 1) * ldb + inner), &v, &fresh))) return rc;
+      bh = v->hi; bl = v->lo;
+    } else {
+      if ((rc = ensure_ws(2 * pb))) return rc;
+      bh = g_ws;
+      bl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bh) + pb);
+    }
+    if (fresh && (rc = launch_split(B, bh, bl, ldb, sb, (int)n, (int)k, Kp, b_nb, tb == 0, 0))) return rc;
     if ((rc = make_map256(&mb, bh, (int)n, Kp, b_nb, RN))) return rc;
     if ((rc = make_map256(&mbl, bl, (int)n, Kp, b_nb, RN))) return rc;
   }

@@ -290,6 +290,7 @@ int wf2cu_release(void* dev) {
   }
   // stream-ordered: work already queued on the buffer finishes first
   WF2_CUDA(cudaStreamSynchronize(S().stream));
+  gemm_tc_const_touch(dev, bytes, true);       // planes kept for constant operands in this storage go with it
   WF2_CUDA(cudaFree(dev));
   S().bytes_in_use -= bytes;
   return 0;
@@ -305,6 +306,7 @@ int wf2cu_mem_in_use(size_t* bytes) {
 int wf2cu_memset0(void* dev, size_t off, size_t bytes) {
   WF2_REQUIRE_INIT();
   WF2_CUDA(cudaMemsetAsync((char*)dev + off, 0, bytes, S().stream));
+  gemm_tc_const_touch((char*)dev + off, bytes, false);
   return 0;
 }
 
@@ -313,6 +315,7 @@ int wf2cu_h2d(void* dev, size_t off, const void* host, size_t bytes) {
   WF2_CHECK(dev && (host || bytes == 0), "wf2cu_h2d: null pointer");
   if (bytes == 0) return 0;
   WF2_CUDA(cudaMemcpyAsync((char*)dev + off, host, bytes, cudaMemcpyHostToDevice, S().stream));
+  gemm_tc_const_touch((char*)dev + off, bytes, false);   // a new value for a constant operand: its planes are split again
   return 0;
 }
 
@@ -334,6 +337,7 @@ int wf2cu_d2h_async(const void* dev, size_t off, void* host, size_t bytes) {
 int wf2cu_d2d(void* dst, size_t doff, const void* src, size_t soff, size_t bytes) {
   WF2_REQUIRE_INIT();
   if (bytes) WF2_CUDA(cudaMemcpyAsync((char*)dst + doff, (const char*)src + soff, bytes, cudaMemcpyDeviceToDevice, S().stream));
+  if (bytes) gemm_tc_const_touch((char*)dst + doff, bytes, false);
   return 0;
 }
 

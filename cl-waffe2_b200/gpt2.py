@@ -189,12 +189,24 @@ class GPT2Layer:
 class GPT2:
     """model.lisp:139-192: embedding -> n_layer blocks -> LayerNorm [-> lm-head]."""
 
-    def __init__(self, cfg: Dict[str, int] = None, weights: Optional[Dict[str, np.ndarray]] = None, seed: int = 0):
+    def __init__(self, cfg: Dict[str, int] = None, weights: Optional[Dict[str, np.ndarray]] = None, seed: int = 0,
+                 constant_weights: bool = True):
         self.cfg = dict(CONFIG_SMALL if cfg is None else cfg)
         w = weights if weights is not None else init_weights(self.cfg, seed)
         self.wte, self.wpe = from_numpy(w["wte"]), from_numpy(w["wpe"])
         self.ln_g, self.ln_b = from_numpy(w["ln_f.g"]), from_numpy(w["ln_f.b"])
         self.layers: List[GPT2Layer] = [GPT2Layer(w, i, self.cfg["n_head"]) for i in range(self.cfg["n_layer"])]
+        if constant_weights:
+            self.declare_constant(True)
+
+    def declare_constant(self, on: bool = True) -> None:
+        """The example only runs the model forward (gpt2-model.lisp loads the weights once): the weight matrices are declared
+        constant operands (wf2cu_gemm_const_operand), so MatmulNode keeps their tensor-core operand planes between calls
+        instead of re-splitting 48 matrices per forward."""
+        lib = _lib.load()
+        mats = [self.wte] + [m for l in self.layers for m in (l.attn_w, l.proj_w, l.fc_w, l.fc_proj_w)]
+        for t in mats:
+            _lib.check(lib.wf2cu_gemm_const_operand(t.vec.ptr, 0, int(np.prod(t.shape)), 1 if on else 0))
 
     def embed(self, ctx: CUDATensor) -> CUDATensor:
         """GPT2PositionalEmbedding (utils.lisp:19-112); ctx: (B N) float token ids."""

@@ -118,6 +118,8 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 (defwf2 gemm-set-mode ((mode :int)))
 (defwf2 gemm-set-correction ((kind :int)))
 (defwf2 gemm-last-path ((out :pointer)))
+(defwf2 gemm-const-operand ((base :pointer) (offset :int64) (count :int64) (constant :int)))
+(defwf2 gemm-const-stats ((entries :pointer) (bytes :pointer)))
 ;; optimizers
 (defwf2 sgd-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64) (n :int64) (lr :float)))
 (defwf2 adam-step ((param :pointer) (p-off :int64) (grad :pointer) (g-off :int64)

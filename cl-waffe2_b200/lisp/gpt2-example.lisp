@@ -26,3 +26,21 @@
 	       (cl-waffe2/vm:maybe-observe-axis (second (shape wte)))
 	       (ptr ctx-out)))
 	    ctx-out))
+
+;; The example only runs the model forward (`gpt2-inference`, model.lisp:216-239) and its weights are loaded once by the
+;; model constructors (model.lisp:46-160): declaring the weight matrices constant lets MatmulNode keep their tensor-core
+;; operand planes between calls (wf2cu_gemm_const_operand) instead of re-splitting 48 matrices per forward.
+;; Call once after `(GPT2)` when the tensors live on CUDATensor; a later upload into a weight re-splits it.
+(defun declare-constant-weights (model &key (constant t))
+  (flet ((declare-one (tensor)
+	   (when (typep tensor 'cl-waffe2/backends.cuda:CUDATensor)
+	     (cl-waffe2/backends.cuda::gemm-const-operand
+	      (cl-waffe2/backends.cuda::device-vec-ptr (tensor-vec tensor))
+	      (tensor-initial-offset tensor)
+	      (apply #'* (shape tensor))
+	      (if constant 1 0)))))
+    (declare-one (slot-value model 'wte))
+    (dolist (layer (slot-value model 'layers))
+      (dolist (slot '(attn-attn-w attn-proj-w mlp-fc-w mlp-proj-w))
+	(declare-one (slot-value layer slot))))
+    model))

@@ -245,6 +245,17 @@ enum {
   WF2CU_GEMM_PATH_TC_RAW = 8         /* tcgen05 3xTF32, raw fp32 tiles by TMA, lo planes made on the SM (no pre-pass) */
 };
 int  wf2cu_gemm_last_path(int* out);
+/* Prepared operands — the packed-operand idea of BLAS libraries (sgemm_pack / sgemm_compute) for the leaf the reference calls
+ * (`sgemm_`, `source/backends/cpu/matrix-ops.lisp:58-79`, which re-reads its operands every call).  The host declares
+ * count fp32 elements from base + offset constant (constant != 0): the parameters of a model that is only run forward
+ * (`examples/gpt-2/gpt2-model.lisp`).  A MatmulNode operand that STARTS inside such a range keeps its tensor-core operand
+ * planes between calls (found again by pointer, pitch, shape and layout), so its pre-pass runs once.  wf2cu_h2d / wf2cu_d2d /
+ * wf2cu_memset0 into the range mark the planes stale (split again by the next product); wf2cu_free of the storage, or
+ * constant == 0, drops them.  Kernels of this library that write into a declared range are the caller's contract
+ * violation.  Planes are allocated on first use: not inside wf2cu_graph_begin/end (run the product once first).
+ * stats: number of kept plane sets and their bytes. */
+int  wf2cu_gemm_const_operand(const void* base, int64_t offset, int64_t count, int constant);
+int  wf2cu_gemm_const_stats(int64_t* entries, int64_t* bytes);
 /* MatmulNode with the node that follows it folded into the epilogue (what the backend's
  * `on-finalizing-compiling` pass emits for LinearLayer, `nn/regression.lisp:14-18`, and for the
  * `!relu` that follows / precedes it, `nn/activation.lisp:11-26`):

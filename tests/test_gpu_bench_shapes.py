@@ -407,3 +407,68 @@ def test_matmul_correction_kinds(gpu):
     print(f"\ncorrection kinds on ({m} {k}) x ({n} {k})^T: bf16 {errs[0]:.2e}  tf32 {errs[1]:.2e}  numpy fp32 {f32_err:.2e}")
     assert errs[1] <= 2e-5 and errs[0] <= 2e-5
     assert errs[0] <= max(4 * f32_err, 2e-6) + 1.0e-8 * k, (errs, f32_err)
+
+
+def _const_stats(gpu):
+    e, b = C.c_int64(0), C.c_int64(0)
+    gpu._lib.check(gpu._lib.load().wf2cu_gemm_const_stats(C.byref(e), C.byref(b)))
+    return e.value, b.value
+
+
+@pytest.mark.parametrize("tb", [False, True])
+def test_matmul_constant_operand_keeps_its_planes(gpu, tb):
+    """wf2cu_gemm_const_operand: a weight declared constant is split once (one kept plane set, found again on the next call),
+    gives the bits of the undeclared product, follows an upload of new values (planes split again), and lets go of its
+    planes when the declaration is withdrawn or the storage is freed."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(21)
+    m, n, k = 1024, 768, 1000
+    A = rng.normal(size=(m, k)).astype(np.float32)
+    W = rng.normal(size=(n, k) if tb else (k, n)).astype(np.float32)
+    W2 = rng.normal(size=W.shape).astype(np.float32)
+    ga, gw = gpu.from_numpy(A), gpu.from_numpy(W)
+    op = lambda: gpu.ops.matmul(ga, gpu.ops.t(gw) if tb else gw).to_numpy()
+    base_entries, _ = _const_stats(gpu)
+    try:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(5))
+        plain = op()
+        gpu._lib.check(lib.wf2cu_gemm_const_operand(gw.vec.ptr, 0, W.size, 1))
+        first, second = op(), op()
+        entries, nbytes = _const_stats(gpu)
+        assert entries == base_entries + 1, entries
+        assert nbytes >= (1 if tb else 2) * n * k * 4                        # K-major: the weight is its own hi plane
+        np.testing.assert_array_equal(first, plain)
+        np.testing.assert_array_equal(second, plain)
+        # new values through the host API: the planes follow
+        gpu._lib.check(lib.wf2cu_h2d(gw.vec.ptr, 0, W2.ctypes.data, W2.nbytes))
+        third = op()
+        truth = A.astype(np.float64) @ (W2.T if tb else W2).astype(np.float64)
+        assert float(np.abs(third - truth).max() / np.abs(truth).max()) <= 2e-5
+        assert _const_stats(gpu)[0] == base_entries + 1
+        # withdrawn: planes dropped, same bits from the workspace path
+        gpu._lib.check(lib.wf2cu_gemm_const_operand(gw.vec.ptr, 0, W.size, 0))
+        assert _const_stats(gpu)[0] == base_entries
+        np.testing.assert_array_equal(op(), third)
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+        gpu._lib.check(lib.wf2cu_gemm_const_operand(gw.vec.ptr, 0, W.size, 0))
+
+
+def test_gpt2_constant_weights_equal_plain_forward(gpu):
+    """GPT2(constant_weights=True) (the default) against the same model with the declaration withdrawn: same bits, and the
+    kept planes are released with the declaration."""
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    cfg = dict(n_vocab=211, n_ctx=256, n_emb=768, n_head=12, n_layer=2)
+    model = g.GPT2(cfg, seed=3)
+    ctx = gpu.from_numpy(np.random.default_rng(5).integers(0, cfg["n_vocab"], size=(8, 256)).astype(np.float32))
+    base = _const_stats(gpu)[0]
+    kept = model(ctx).to_numpy()
+    kept2 = model(ctx).to_numpy()
+    entries = _const_stats(gpu)[0]
+    model.declare_constant(False)
+    assert _const_stats(gpu)[0] <= base
+    plain = model(ctx).to_numpy()
+    np.testing.assert_array_equal(kept, kept2)
+    np.testing.assert_array_equal(kept, plain)
+    print(f"\nGPT-2 (2 layers) kept plane sets: {entries - base}")
+    assert entries > base
