@@ -25,7 +25,7 @@
 //                   to accumulate den = sum_h exp((Q_h . K_h) / N) in registers (head order), then the 12 heads again to write
 //                   P = exp(...) / den.  Raw operands + converter warps by default (194 us per layer at B = 8, N = 1024);
 //                   WF2CU_ATTN_PLANES=1 pre-splits the lo planes instead (184 us + a 16 us split launch).  Ablation
-//                   (WF2CU_ATTN_DBG, profiles/r02_attention.md): main loop alone 147 us, pass-2 arithmetic + staging +26, P stores +22.
+//                   (WF2CU_ATTN_DBG): main loop alone 147 us, pass-2 arithmetic + staging +26, P stores +22.
 #pragma once
 
 namespace wf2 {

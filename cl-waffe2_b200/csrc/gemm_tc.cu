@@ -1346,7 +1346,7 @@ static bool raw_operand_ok(const float* p, int64_t ld, int64_t bstride, int64_t 
   return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld & 3) == 0 && (nbatch <= 1 || ((bstride & 3) == 0 && bstride > 0));
 }
 
-// Auto rule: raw-operand kernel or planes kernels?  Cycle model fitted on B200 (scripts/gemm_raw_bench.py, profiles/r02_gemm_raw.md):
+// Auto rule: raw-operand kernel or planes kernels?  Cycle model fitted on B200 (scripts/gemm_raw_bench.py):
 // per k-block of 16 a tile costs 1180 cycles on the raw kernel (shared-memory bound: TMA writes + converter traffic + operand reads
 // of six 128x256x8 MMAs), 1110 / 1850 / 1500 on the 128x256 / 256x256 / 256x192 planes kernels; the 256-row tiles expose their
 // epilogue; an operand pre-pass moves 12 bytes per element at ~4.5 TB/s plus a launch.  The raw kernel skips A's pre-pass always
