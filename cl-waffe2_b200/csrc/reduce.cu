@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "math.cuh"
 #include <cooperative_groups.h>
+#include <stdlib.h>
 namespace cg = cooperative_groups;
 
 namespace wf2 {
@@ -295,8 +296,8 @@ __global__ void __launch_bounds__(256) reduce_rows_tile_kernel(const __grid_cons
 // One long contiguous run, no kept axes.  ptxas keeps only two 128-bit register loads in flight per
 // thread in the looped row kernel above however the source is written (the SASS re-uses two register
 // quads), so here the loads do not go through registers at all: a persistent CTA (2 per SM) streams
-// 16 KiB chunks into a 4-stage shared-memory ring with the bulk async-copy engine
-// (cp.async.bulk.shared.global + mbarrier complete_tx), i.e. 64 KiB in flight per CTA by construction.
+// 16 KiB chunks into a 3-stage shared-memory ring with the bulk async-copy engine
+// (cp.async.bulk.shared.global + mbarrier complete_tx), i.e. 48 KiB in flight per CTA by construction.
 // Partials meet through a ticket (st.relaxed + atom.acq_rel); the last CTA folds them in a fixed order.
 constexpr int kFlatThreads = 256, kFlatStages = 4, kFlatChunk = 16384;   // bytes per stage
 struct FlatArgs {
@@ -305,6 +306,8 @@ struct FlatArgs {
   float* partial;       // [gridDim.x]
   unsigned int* counter;
   int64_t n;            // elements
+  int stages;           // ring depth actually used (<= kFlatStages; the launch passes stages * kFlatChunk bytes)
+  int late_trigger;     // 1: let the dependent grid in only when this CTA has finished streaming
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -316,17 +319,20 @@ __global__ void __launch_bounds__(kFlatThreads) reduce_flat_bulk_kernel(const __
   __shared__ float red[kFlatThreads / 32];
   __shared__ bool is_last;
   constexpr int T = kFlatThreads;
-  pdl_prologue();
+  const int S = a.stages;
   const int64_t nchunks = (a.n * 4) / kFlatChunk;
   const char* base = reinterpret_cast<const char*>(a.src);
+  // shared-memory set-up first: under programmatic dependent launch it overlaps the predecessor's tail
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kFlatStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&bar[s])));
+    for (int s = 0; s < S; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&bar[s])));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  if (!a.late_trigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   if (threadIdx.x == 0) {
     int64_t c = blockIdx.x;
-    for (int s = 0; s < kFlatStages && c < nchunks; ++s, c += gridDim.x) {
+    for (int s = 0; s < S && c < nchunks; ++s, c += gridDim.x) {
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar[s])), "r"(kFlatChunk) : "memory");
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                    ::"r"(smem_addr(ring + s * kFlatChunk)), "l"(base + c * kFlatChunk), "r"(kFlatChunk), "r"(smem_addr(&bar[s])) : "memory");
@@ -349,15 +355,16 @@ __global__ void __launch_bounds__(kFlatThreads) reduce_flat_bulk_kernel(const __
     acc3 = M::op(acc3, M::op(M::op(x3.x, x3.y), M::op(x3.z, x3.w)));
     __syncthreads();   // every thread is done with stage s
     if (threadIdx.x == 0) {
-      const int64_t nc = c + (int64_t)kFlatStages * gridDim.x;
+      const int64_t nc = c + (int64_t)S * gridDim.x;
       if (nc < nchunks) {
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar[s])), "r"(kFlatChunk) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(smem_addr(ring + s * kFlatChunk)), "l"(base + nc * kFlatChunk), "r"(kFlatChunk), "r"(smem_addr(&bar[s])) : "memory");
       }
     }
-    if (++s == kFlatStages) { s = 0; ph ^= 1; }
+    if (++s == S) { s = 0; ph ^= 1; }
   }
+  if (a.late_trigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // ragged tail (< one chunk): CTA 0, plain loads
   if (blockIdx.x == 0)
     for (int64_t i = nchunks * (kFlatChunk / 4) + threadIdx.x; i < a.n; i += T) acc0 = M::op(acc0, a.src[i]);
@@ -717,6 +724,24 @@ bool has_reduction_axes(const wf2cu_view* dst) {
   return false;
 }
 
+// Launch shape of the flat kernel (defaults measured on B200, scripts/flat_variants.py -> profiles/r02j_flat_variants.log;
+// WF2CU_FLAT_* for A/B runs).  (4096 4096): 4 stages 14.2 us, 3 stages 12.9 us (a 48 KiB ring lets FOUR CTAs share an SM, so
+// under programmatic dependent launch the whole next grid is resident and past its barrier set-up when this one drains),
+// 2 stages 13.4; 3 or 4 CTAs per SM, an ordinary launch, or letting the dependents in late are all slower.
+//   stages x 16 KiB of ring per CTA, CTAs per SM, pdl: 0 = ordinary launch, 1 = programmatic dependent launch with the
+//   dependents let in at once, 2 = ... let in when this CTA has finished streaming
+struct FlatTune { int stages, ctas_per_sm, pdl; };
+static const FlatTune& flat_tune() {
+  static FlatTune t = {0, 0, 0};
+  if (!t.stages) {
+    auto env = [](const char* k, int d, int lo, int hi) { const char* e = getenv(k); int v = e ? atoi(e) : d; return v < lo ? lo : (v > hi ? hi : v); };
+    t.ctas_per_sm = env("WF2CU_FLAT_CTAS", 2, 1, 4);
+    t.pdl = env("WF2CU_FLAT_PDL", 1, 0, 2);
+    t.stages = env("WF2CU_FLAT_STAGES", 3, 2, kFlatStages);
+  }
+  return t;
+}
+
 template <class M>
 static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, const char* who) {
   const wf2cu_view* views[2] = {dst, src};
@@ -759,13 +784,15 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
         WF2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, kFlatStages * kFlatChunk));
         attr_set[which] = true;
       }
+      const FlatTune& ft = flat_tune();
       const int64_t nchunks = (a.cols * 4) / kFlatChunk;
-      int64_t grid = (int64_t)s.sm_count * 2;
+      int64_t grid = (int64_t)s.sm_count * ft.ctas_per_sm;
       if (grid > nchunks) grid = nchunks;
       rc = ensure_scratch((size_t)grid * sizeof(float));
       if (rc) return rc;
-      FlatArgs f{sptr, dptr, (float*)scratch_base(), counters_base(), a.cols};
-      WF2_CUDA(launch_pdl(kfn, dim3((unsigned)grid), dim3(kFlatThreads), kFlatStages * kFlatChunk, s.stream, f, fin));
+      FlatArgs f{sptr, dptr, (float*)scratch_base(), counters_base(), a.cols, ft.stages, ft.pdl == 2 ? 1 : 0};
+      if (ft.pdl) WF2_CUDA(launch_pdl(kfn, dim3((unsigned)grid), dim3(kFlatThreads), ft.stages * kFlatChunk, s.stream, f, fin));
+      else { kfn<<<(unsigned)grid, kFlatThreads, ft.stages * kFlatChunk, s.stream>>>(f, fin); }
       return post_launch(who);
     }
     if (rows < (int64_t(1) << 31)) {
@@ -1005,16 +1032,17 @@ int wf2cu_sum_all_noalloc(const void* x, int64_t x_off, int64_t n, void* out, in
   unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + kNoAllocSlots * sizeof(float));
   // same grid rule as wf2cu_reduce_sum's flat path (2 persistent CTAs per SM), so both give the same bits
   const int64_t nchunks = (n * 4) / kFlatChunk;
-  int64_t grid = (int64_t)s.sm_count * 2;
+  const FlatTune& ft = flat_tune();
+  int64_t grid = (int64_t)s.sm_count * ft.ctas_per_sm;
   if (grid > nchunks) grid = nchunks;
   if (grid < 1) grid = 1;               // shorter than one chunk: CTA 0's ragged-tail loop does all of it
   if (grid > kNoAllocSlots) grid = kNoAllocSlots;
   // the ticket must start at zero whatever an earlier (possibly aborted) call left behind; the partials are
   // overwritten before they are read
   WF2_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s.stream));
-  FlatArgs f{sptr, dptr, partial, ticket, n};
+  FlatArgs f{sptr, dptr, partial, ticket, n, ft.stages, 0};
   Fin fin{accumulate ? FIN_ADD : FIN_SET, divisor};
-  reduce_flat_bulk_kernel<MSum><<<(unsigned)grid, kFlatThreads, kFlatStages * kFlatChunk, s.stream>>>(f, fin);
+  reduce_flat_bulk_kernel<MSum><<<(unsigned)grid, kFlatThreads, ft.stages * kFlatChunk, s.stream>>>(f, fin);
   return post_launch("wf2cu_sum_all_noalloc");
 }
 

@@ -568,6 +568,9 @@ class CompiledStep:
         self.graph = None
         self.use_graph = use_graph
         self._runs = 0
+        # measurement aid: run the peer-memory exchange kernel on a world of ONE attached rank (what the kernel itself costs
+        # against the plain Adam launch, with nothing on the wire; scripts/p2p_world1.py)
+        self.p2p_single = False
 
     def _loss(self, out: CUDATensor) -> CUDATensor:
         if self.loss_kind == "softmax-cross-entropy-sum":      # examples/mnist/mlp.lisp:24-28
@@ -608,7 +611,7 @@ class CompiledStep:
                 for node in reversed(self.tape.nodes):
                     node()
                 _join_branches()               # every gradient is complete before the exchange / optimizer
-                if self.world > 1 and self.exchange == "p2p":
+                if self.exchange == "p2p" and (self.world > 1 or self.p2p_single):
                     self.opt.step_p2p()         # exchange + 1/world + Adam in one kernel over peer memory
                 else:
                     if self.world > 1:

@@ -385,6 +385,10 @@ int  wf2cu_comm_destroy(void);
  *      1/world, applies Adam (same formula as wf2cu_adam_step) with its m/v shard and stores the new
  *      parameters into every replica; then waits until every rank has written its shard, so replicas
  *      stay bit-identical and the gradient arena can be reused by the next backward.
+ * Buckets of at most 2^20 floats take the LL (push) form of the same step: every 16-byte store over NVLink carries
+ * {value, epoch, value, epoch}, receivers poll their own staging area (part of the window wf2cu_p2p_signal_export exports), so
+ * there are no fences, flags or "done" exchange on the path; same summation order and arithmetic, bit-identical results
+ * (WF2CU_P2P_LL=0 forces the pull form above; the bucket size must not change within one attachment).
  * A peer that never arrives makes the kernel give up after 10 s (the GPU is never left spinning).  Giving up is sticky and
  * fatal for the attachment: the rank raises its flag (wf2cu_p2p_status: a mapped pinned host word, read without a sync),
  * tells every peer, and from then on every rank's step kernel returns at entry without touching gradients or parameters.

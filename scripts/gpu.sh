@@ -7,6 +7,7 @@
 #         bench            python bench.py            -> gpurun_out/<tag>_bench.json / .err
 #         benchref         python bench.py --impl reference
 #         benchN:<n>       torchrun bench.py on n GPUs (call gpurun with --gpus n)
+#         mlpN:<n>         the sharded MLP step only on n GPUs: LL (push) exchange, then WF2CU_P2P_LL=0 (pull), + scripts/p2p_check.py
 #         benchnopdl       the sweep / fused chains / MLP with WF2CU_PDL=0 (A/B of programmatic dependent launch)
 #         launches         ncu launch list of `bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --fused 1 --no-cpu`
 #         ncu:<regex>:<script.py>[+arg...]   ncu --set full on kernels matching <regex> while running python <script.py> [args]
@@ -26,6 +27,15 @@ for task in "$@"; do
     benchN:*) n=${task#benchN:}
               timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $n --steps 10 --warmup 3 \
                 > gpurun_out/${tag}_bench_n${n}.json 2> gpurun_out/${tag}_bench_n${n}.err; echo "bench N=$n rc=$?"; tail -c 1400 gpurun_out/${tag}_bench_n${n}.json; grep -v "^W\|^\*\*\*" gpurun_out/${tag}_bench_n${n}.err | tail -8 ;;
+    mlpN:*)   n=${task#mlpN:}
+              for ll in 1 0; do
+                WF2CU_P2P_TRACE=1 WF2CU_P2P_LL=$ll timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2951$ll bench.py --gpus $n --steps 5 --warmup 3 \
+                  --gemm 0 --gpt2 0 --cnn 0 --fused 0 --cublas 0 > gpurun_out/${tag}_mlp_n${n}_ll${ll}.json 2> gpurun_out/${tag}_mlp_n${n}_ll${ll}.err
+                echo "mlp N=$n LL=$ll rc=$?"; python -c "import json,sys; d=json.loads(open('gpurun_out/${tag}_mlp_n${n}_ll${ll}.json').read().strip().splitlines()[-1]); print(json.dumps(d['mlp']))"
+                grep "p2p trace rank 0" gpurun_out/${tag}_mlp_n${n}_ll${ll}.err | tail -6
+              done
+              timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29533 scripts/p2p_check.py 2>&1 | grep -v "^W\|^\*\*\*" | tail -$((n + 2)) | tee gpurun_out/${tag}_p2p_check_n${n}.log ;;
+    flat)     for v in "" "WF2CU_FLAT_STAGES=3" "WF2CU_FLAT_STAGES=3 WF2CU_FLAT_PDL=2" "WF2CU_FLAT_STAGES=2" "WF2CU_FLAT_STAGES=2 WF2CU_FLAT_PDL=2" "WF2CU_FLAT_STAGES=3 WF2CU_FLAT_PDL=0" "WF2CU_FLAT_STAGES=2 WF2CU_FLAT_CTAS=3" "WF2CU_FLAT_STAGES=3"; do env $v timeout 120 python scripts/flat_variants.py 2>&1 | tail -1; done | tee gpurun_out/${tag}_flat_variants.log ;;
     benchref) timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "benchref rc=$?" ;;
     launches) cmd="python bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --no-cpu"
               timeout 300 $cmd > gpurun_out/${tag}_launches_plain.log 2>&1 &&
