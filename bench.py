@@ -215,7 +215,7 @@ def dist_env():
 
 
 
-GEMM_PATHS = {0: "none", 1: "simt", 2: "simt_splitk", 3: "simt_skinny", 4: "tc_fused", 5: "tc_128x256", 6: "tc_256x256", 7: "tc_256x192", 8: "tc_raw"}
+GEMM_PATHS = {0: "none", 1: "simt", 2: "simt_splitk", 3: "simt_skinny", 4: "tc_fused", 5: "tc_128x256", 6: "tc_256x256", 7: "tc_256x192", 8: "tc_raw", 9: "tc_2sm"}
 
 
 def _gemm_rows_check(rng, A, B, got, ta, tb, nrows=64):

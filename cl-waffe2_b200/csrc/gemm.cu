@@ -630,7 +630,7 @@ int wf2cu_gemm_set_correction(int kind) {
 }
 
 int wf2cu_gemm_set_mode(int mode) {
-  WF2_CHECK(mode >= 0 && mode <= 7, "wf2cu_gemm_set_mode: mode %d not in 0..7", mode);
+  WF2_CHECK(mode >= 0 && mode <= 8, "wf2cu_gemm_set_mode: mode %d not in 0..8", mode);
   S().gemm_mode = mode;
   return 0;
 }
@@ -677,7 +677,7 @@ static int gemm_impl(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, 
     if (r < 0) return -r;
     if (r == 1) { S().gemm_last_path = WF2CU_GEMM_PATH_SIMT_SKINNY; return 0; }
   }
-  if (ext && mode != 7 && mode != 2 && mode != 5 && mode != 6 &&
+  if (ext && mode != 7 && mode != 2 && mode != 5 && mode != 6 && mode != 8 &&
       !(mode == 0 && 2.0 * (double)m * (double)n * (double)k * (double)batch >= 2.5e9 && m >= 64 && n >= 64 && k >= 32)) {
     // small problems: the plain product (+ bias) on whatever kernel auto picks, then the rest of the epilogue as one pass
     const int rc = gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, batch, stride_a, stride_b, stride_c, bias, 0,

@@ -624,6 +624,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
 }
 
 }  // namespace wf2
+#include "gemm_tc2sm.cuh"   // step 2b': the same plane-fed loop on a CTA pair (cta_group::2), half of B per CTA
 #include "gemm_raw.cuh"   // step 2c: the same main loop on RAW fp32 tiles (no operand pre-pass) + the attention-score epilogues
 namespace wf2 {
 
@@ -1178,23 +1179,37 @@ static int const_planes(const PlaneKey& key, size_t plane_bytes, size_t src_floa
 // (x1.3) but hides its epilogue; 256x256 runs at the tensor rate; 256x192 pays x1.12 for its smaller B slices.
 //   8192x768x3072: 286 / 242 / 212 us (128x256 / 256x256 / 256x192)   8192x768x768: 82 / 78 / 68
 //   8192x1536x1536: 207 / 230 / 196     8192x2304x768: 139 / 136 / 156     2048^3: 103 / 154 / 131     4096^3: 679 / 577 / 680
-static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t tiles192, int sms, bool bf16_corr) {
+static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t tiles192, int64_t tiles_pair, int sms, bool bf16_corr) {
   auto waves = [&](int64_t t) { return (double)((t + sms - 1) / sms); };
-  double c128, c256, c192;
+  auto pair_waves = [&](int64_t t) { const int64_t pairs = sms / 2; return (double)((t + pairs - 1) / pairs); };
+  double c128, c256, c192, cpair;
   if (bf16_corr) {
     // TF32 + bf16 corrections (r02d, scripts/gemm_hybrid_bench.py): 35 / 53 / 44.5 ns per k per tile; 256-row epilogues ~8 / 6 us
     //   4096^3: 624 / 490 / 606 us   8192^3: 3944 / 3217 / 3814   2048^3: 95 / 119 / 112   8192x2304x768: 124 / 112 / 134
     //   8192x768x768: 72 / 66 / 62   8192x3072x768: 171 / 154 / 170   8192x768x3072: 262 / 202 / 193
+    // CTA-pair kernel (512 x 256 pair tiles on sms / 2 pairs, r02r, scripts/gemm_pair_bench.py): 4096^3 446 (NT 420), 8192^3 3125,
+    //   8192x2304x768 107, 8192x768x768 64, 8192x3072x768 144, 8192x768x3072 179, 2048^3 117
     c128 = waves(tiles128) * 1.02 * (double)kp;
     c256 = waves(tiles256) * (1.59 * (double)kp + 240.0);
     c192 = waves(tiles192) * (1.33 * (double)kp + 180.0);
+    cpair = pair_waves(tiles_pair) * (1.50 * (double)kp + 240.0);
   } else {
     c128 = waves(tiles128) * 1.30 * (double)kp;
     c256 = waves(tiles256) * (2.00 * (double)kp + 450.0);
     c192 = waves(tiles192) * (1.68 * (double)kp + 337.0);
+    cpair = pair_waves(tiles_pair) * (1.90 * (double)kp + 450.0);
   }
-  if (c128 <= c256 * 1.02 && c128 <= c192 * 1.02) return 0;
+  if (tiles_pair <= 0) cpair = 1e300;
+  if (c128 <= c256 * 1.02 && c128 <= c192 * 1.02 && c128 <= cpair * 1.02) return 0;
+  if (cpair <= c256 && cpair <= c192) return 512;
   return c256 <= c192 ? 256 : 192;
+}
+
+// WF2CU_GEMM_PAIR=0: auto never takes the CTA-pair kernel; =1: always when the shape allows (A/B measurements)
+static int pair_override() {
+  static int force = -2;
+  if (force == -2) { const char* e = getenv("WF2CU_GEMM_PAIR"); force = e ? atoi(e) : -1; }
+  return force;
 }
 
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
@@ -1234,10 +1249,16 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   const int64_t tiles256 = tiles_m256 * ((n + 255) / 256) * batch;
   const int64_t tiles192 = tiles_m256 * ((n + 191) / 192) * batch;
   int nb = 0;                                              // 0: the 128x256 kernel below
+  bool pair2 = mode == 8;
   if (mode == 5) nb = 256;
   else if (mode == 6) nb = 192;
-  else if (mode == 0 && g_t256_auto)
-    nb = pick_tile256(Kp, ((m + TM - 1) / TM) * ((n + TN - 1) / TN) * batch, tiles256, tiles192, S().sm_count, passes == 2);
+  else if (mode == 0 && g_t256_auto) {
+    const int64_t tiles_pair = pair_override() == 0 ? 0 : ((m + 511) / 512) * ((n + 255) / 256) * batch;
+    nb = pick_tile256(Kp, ((m + TM - 1) / TM) * ((n + TN - 1) / TN) * batch, tiles256, tiles192, tiles_pair, S().sm_count, passes == 2);
+    if (pair_override() == 1 && m >= 512 && n >= 256) nb = 512;
+  }
+  if (nb == 512) pair2 = true;
+  if (pair2) nb = 256;                                     // (the pair kernel shares the 256-row kernels' k-block and plane layout)
   // the second plane: fp32 lo (3xTF32) or the mixed bf16 plane laid out for the chosen kernel's k-block
   const int bf_blk = passes == 2 ? (nb ? T2K : TK) : 0;
   // Operand planes.  A: logical (m x k); ta = stored transposed (k x m) -> m is the contiguous axis of the source.
@@ -1282,6 +1303,32 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     return make_map_k(ml, q.lo, Kp, q.rows, Kp, q.nb, (int64_t)q.rows * Kp, box_k, box_rows);
   };
 
+  if (pair2) {
+    // CTA pair, 512 x 256 pair tiles: each CTA loads its 256 rows of A and HALF of the B tile (gemm_tc2sm.cuh)
+    static bool attr2 = false;
+    if (!attr2) {
+      cudaError_t e = cudaFuncSetAttribute(gemm_tc2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P2_SMEM);
+      if (e != cudaSuccess) return -cuda_fail(e, "cudaFuncSetAttribute(gemm_tc2sm_kernel)", __FILE__, __LINE__);
+      attr2 = true;
+    }
+    if ((rc = maps(pr[0], &mah, &mal, T2K, 256))) return rc;
+    if ((rc = maps(pr[1], &mbh, &mbl, T2K, 128))) return rc;
+    TcArgs t;
+    t.C = C; t.ldc = ldc; t.sc = sc; t.m = (int)m; t.n = (int)n; t.nkb = Kp / T2K;
+    t.tiles_m = (int)((m + 511) / 512); t.tiles_n = (int)((n + 255) / 256); t.batch = (int)batch;
+    t.passes = passes;
+    t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
+    t.a_bcast = a_nb == 1 ? 1 : 0;
+    t.b_bcast = b_nb == 1 ? 1 : 0;
+    t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
+    const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
+    const int64_t pairs_max = S().sm_count / 2;
+    const int grid = 2 * (int)(total < pairs_max ? total : pairs_max);
+    gemm_tc2sm_kernel<<<grid, GEMM_THREADS, P2_SMEM, S().stream>>>(mah, mal, mbh, mbl, mc, t);
+    rc = post_launch("wf2cu_gemm(tcgen05 CTA pair)");
+    S().gemm_last_path = WF2CU_GEMM_PATH_TC_2SM;
+    return rc ? -rc : 1;
+  }
   if (nb) {
     // 256-row tiles: two M = 128 MMAs share every B slice (42.7 instead of 62.5 B/clk of L2 -> SM traffic per SM)
     static bool attr256 = false;
@@ -1374,6 +1421,11 @@ bool gemm_raw_preferred(int tb, int64_t m, int64_t n, int64_t k, int64_t batch, 
   const double p192 = waves(t192) * (nkb * (bf ? 1190.0 : 1500.0) + (bf ? 5500.0 : 8000.0));
   if (p256 < planes) planes = p256;
   if (p192 < planes) planes = p192;
+  if (pair_override() != 0) {          // CTA-pair kernel: ~6 % fewer cycles per k-block than the 256x256 tiles, on sms / 2 pairs
+    const int64_t tp = ((m + 511) / 512) * ((n + 255) / 256) * batch, pairs = (int64_t)sms / 2;
+    const double ppair = (double)((tp + pairs - 1) / pairs) * (nkb * (bf ? 1385.0 : 1755.0) + (bf ? 7000.0 : 10000.0));
+    if (ppair < planes) planes = ppair;
+  }
   planes += (a_share > 0.0 ? a_share * presplit(m) : 0.0) + (b_share > 0.0 ? b_share * presplit(n) : 0.0);
   return raw <= planes;
 }

@@ -8,8 +8,9 @@
 // MMAs per k-step, accumulators 2 x 256 columns = all of TMEM as in gemm_tc256_kernel):
 //     per CTA and k-block of 16:  A 256 x 64 B x 2 planes = 32 KiB  +  B 128 x 64 B x 2 planes = 16 KiB  = 48 KiB (was 64)
 // Protocol (cluster of 2 along x; rank 0 = leader):
-//   warp 0 of BOTH CTAs   TMA producer: waits for its own empty[s] (multicast commit of the leader), then arrive.expect_tx and
-//                          cp.async.bulk.tensor ... .cta_group::2 signalling the LEADER's full[s] (count 2: one arrival per CTA)
+//   warp 0 of BOTH CTAs   TMA producer: waits for its own empty[s] (multicast commit of the leader), then cp.async.bulk.tensor
+//                          ... .cta_group::2 whose bytes complete on the LEADER's full[s]; the leader alone arrives (expect_tx of
+//                          both CTAs' bytes)
 //   warp 1 of the leader  MMA issuer: tcgen05.mma.cta_group::2 (M = 256, N = 256), tcgen05.commit ... multicast::cluster to
 //                          empty[s] / acc_full of both CTAs
 //   warps 2-5 of both     epilogue of the CTA's own 256 rows; acc_empty lives in the leader (8 arrivals, the peer's are remote)
@@ -64,7 +65,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P2_STAGES * P2_STAGE + EPI_BYTES);
-  uint64_t* full = bars;                       // [P2_STAGES]  the leader's are used: 2 arrivals + both CTAs' bytes
+  uint64_t* full = bars;                       // [P2_STAGES]  the leader's are used: its arrival + both CTAs' bytes
   uint64_t* empty = bars + P2_STAGES;          // [P2_STAGES]  per CTA, multicast commit
   uint64_t* acc_full = bars + 2 * P2_STAGES;   // [1]          per CTA, multicast commit
   uint64_t* acc_empty = acc_full + 1;          // [1]          the leader's is used: 8 arrivals
@@ -76,7 +77,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   const int total_tiles = a.tiles_m * a.tiles_n * a.batch;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < P2_STAGES; ++s) { mbar_init(&full[s], 2); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < P2_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
     mbar_init(acc_empty, 8);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -105,7 +106,10 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           mbar_wait(&empty[s], ph ^ 1);
           uint8_t* st = smem + s * P2_STAGE;
           const uint32_t fb = full0 + (uint32_t)s * 8u;
-          mbar_expect_tx_cluster(fb, tx_bytes);
+          // ONE arrival per phase, by the leader, for the bytes of both CTAs; the peer only sends bytes.  (Its bytes may land
+          // before the leader's expect_tx: the count goes negative inside the same phase, which the pending arrival keeps open.
+          // A remote arrive.expect_tx per stage from the peer cost the pipeline half its rate: 674 vs 484 us at 4096^3.)
+          if (rank == 0) mbar_expect_tx(&full[s], 2 * tx_bytes);
           tma_load_3d_2sm(&map_ah, fb, st, kb * T2K, row_a, ba);
           tma_load_3d_2sm(&map_bh, fb, st + 2 * P2_APLANE, kb * T2K, row_b, bb);
           if (a.passes != 1) {

@@ -218,7 +218,8 @@ int  wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k,
 /* 0 = auto, 1 = force fp32 SIMT path, 2 = force tcgen05 3xTF32 (planes + persistent 128x256-tile kernel),
  * 3 = tcgen05 1xTF32 (not parity-grade), 4 = force the one-launch fused tcgen05 kernel (small problems),
  * 5 / 6 = force tcgen05 3xTF32 on the persistent 256x256 / 256x192-tile kernel, 7 = force the raw-operand kernel (A not
- * transposed: fp32 tiles straight from the operand by TMA, lo planes made on the SM, no pre-pass).  Forced modes return
+ * transposed: fp32 tiles straight from the operand by TMA, lo planes made on the SM, no pre-pass), 8 = force the CTA-pair kernel
+ * (tcgen05.mma.cta_group::2 on 512x256 pair tiles: each CTA of a pair loads half of the B tile).  Forced modes return
  * WF2CU_ERR_UNSUPPORTED for shapes their kernel does not take. */
 int  wf2cu_gemm_set_mode(int mode);
 /* How the plane-fed tcgen05 kernels form the error-compensation terms of the split product
@@ -242,7 +243,8 @@ enum {
   WF2CU_GEMM_PATH_TC_128X256 = 5,    /* tcgen05 3xTF32, hi/lo planes + persistent 128x256 tiles */
   WF2CU_GEMM_PATH_TC_256X256 = 6,    /* ... 256x256 tiles                                       */
   WF2CU_GEMM_PATH_TC_256X192 = 7,    /* ... 256x192 tiles                                       */
-  WF2CU_GEMM_PATH_TC_RAW = 8         /* tcgen05 3xTF32, raw fp32 tiles by TMA, lo planes made on the SM (no pre-pass) */
+  WF2CU_GEMM_PATH_TC_RAW = 8,        /* tcgen05 3xTF32, raw fp32 tiles by TMA, lo planes made on the SM (no pre-pass) */
+  WF2CU_GEMM_PATH_TC_2SM = 9         /* hi/lo planes + persistent 512x256 pair tiles on CTA pairs (cta_group::2)       */
 };
 int  wf2cu_gemm_last_path(int* out);
 /* Prepared operands — the packed-operand idea of BLAS libraries (sgemm_pack / sgemm_compute) for the leaf the reference calls

@@ -19,8 +19,8 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 PATH = {0: "none", 1: "simt", 2: "simt_splitk", 3: "simt_skinny", 4: "tc_fused", 5: "tc_128x256", 6: "tc_256x256", 7: "tc_256x192",
-        8: "tc_raw"}
-TENSOR_PATHS = {4, 5, 6, 7, 8}
+        8: "tc_raw", 9: "tc_2sm"}
+TENSOR_PATHS = {4, 5, 6, 7, 8, 9}
 
 
 def _last_path(gpu) -> int:
@@ -64,7 +64,7 @@ def test_c3_matmul_benchmarked_sizes_auto_dispatch(gpu, N):
     if N >= 512:
         assert path in TENSOR_PATHS, f"N={N} ran on {PATH[path]}: the bench quotes a tcgen05 kernel for it"
     if N >= 2048:
-        assert path in (5, 6, 7, 8), f"N={N} ran on {PATH[path]}"
+        assert path in (5, 6, 7, 8, 9), f"N={N} ran on {PATH[path]}"
 
 
 @pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
@@ -72,7 +72,7 @@ def test_c3_matmul_n4096_all_transposes(gpu, ta, tb):
     err, blas_err, path = _matmul_case(gpu, 4096, ta, tb, seed=7 + 2 * ta + tb)
     print(f"\nC3 N=4096 ta={int(ta)} tb={int(tb)}: path={PATH[path]} err={err:.3e} openblas_fp32_err={blas_err:.3e}")
     assert err <= 1e-4 and err <= 3e-7 + 1.0e-8 * 4096, err
-    assert path in (5, 6, 7, 8)
+    assert path in (5, 6, 7, 8, 9)
 
 
 def test_c5_gpt2_small_full_width_matches_oracle(gpu):
@@ -330,7 +330,59 @@ def test_matmul_raw_operand_kernel_batched_bias_relu(gpu):
     np.testing.assert_array_equal(fused, want * (want > 0))
 
 
-@pytest.mark.parametrize("mode", [0, 2, 5, 7])
+@pytest.mark.parametrize("ta,tb,m,n,k,batch", [
+    (False, False, 1536, 1000, 1024, 1), (False, True, 700, 517, 333, 1), (True, False, 512, 256, 64, 1),
+    (True, True, 2050, 770, 100, 1), (False, False, 520, 300, 200, 3), (False, True, 129, 7, 40, 2)])
+def test_matmul_cta_pair_kernel(gpu, ta, tb, m, n, k, batch):
+    """Mode 8 / path 9: the plane-fed kernel on CTA pairs (`tcgen05.mma.cta_group::2`, 512 x 256 pair tiles, each CTA loads half of
+    the B tile; csrc/gemm_tc2sm.cuh).  Ragged edges in m (pair tile, CTA half, MMA half), n and k, every transpose flag, batched
+    operands with a shared B: every element against fp64, and bit for bit against the single-CTA 256 x 256 kernel (mode 5: same
+    planes, same k order per output)."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(1000 * m + n)
+    A = rng.uniform(-1, 1, size=((batch, k, m) if ta else (batch, m, k))).astype(np.float32)
+    B = rng.uniform(-1, 1, size=((n, k) if tb else (k, n))).astype(np.float32)      # shared by every batch index
+    if batch == 1:
+        A = A[0]
+    ga, gb = gpu.from_numpy(A), gpu.from_numpy(B)
+    outs = {}
+    try:
+        for mode in (8, 5):
+            gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
+            outs[mode] = gpu.ops.matmul(gpu.ops.t(ga) if ta else ga, gpu.ops.t(gb) if tb else gb).to_numpy()
+            assert _last_path(gpu) == {8: 9, 5: 6}[mode]
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    opA = np.swapaxes(A, -1, -2) if ta else A
+    truth = opA.astype(np.float64) @ (B.T if tb else B).astype(np.float64)
+    assert outs[8].shape == truth.shape
+    assert np.abs(outs[8] - truth).max() <= 2e-5 * np.abs(truth).max()
+    np.testing.assert_array_equal(outs[8], outs[5])
+
+
+def test_matmul_cta_pair_kernel_bias_relu(gpu):
+    """LinearLayer's bias add and the `!relu` after it in the pair kernel's epilogue: bit for bit the single-CTA kernel's."""
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(77)
+    m, n, k = 1100, 600, 300
+    A = rng.uniform(-1, 1, size=(m, k)).astype(np.float32)
+    W = rng.uniform(-1, 1, size=(n, k)).astype(np.float32)
+    bias = rng.uniform(-1, 1, size=(n,)).astype(np.float32)
+    ga, gw, gbias = gpu.from_numpy(A), gpu.from_numpy(W), gpu.from_numpy(bias)
+    outs = {}
+    try:
+        for mode in (8, 5):
+            gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
+            outs[mode] = gpu.ops.matmul(ga, gpu.ops.t(gw), bias=gbias, relu=True).to_numpy()
+    finally:
+        gpu._lib.check(lib.wf2cu_gemm_set_mode(0))
+    want = A.astype(np.float64) @ W.T.astype(np.float64) + bias
+    want = want * (want > 0)
+    assert np.abs(outs[8] - want).max() <= 2e-5 * np.abs(want).max()
+    np.testing.assert_array_equal(outs[8], outs[5])
+
+
+@pytest.mark.parametrize("mode", [0, 2, 5, 7, 8])
 @pytest.mark.parametrize("m,n,k", [(1536, 1000, 1024), (200, 96, 64)])
 def test_matmul_gelu_and_residual_epilogues_equal_the_separate_nodes(gpu, mode, m, n, k):
     """wf2cu_gemm_ex2: the GPT-2 block's `!gelu` after a projection and its residual `(!add x ...)` ride in the epilogue of the
@@ -384,14 +436,15 @@ def test_matmul_correction_kinds(gpu):
         for kind in (0, 1):
             gpu._lib.check(lib.wf2cu_gemm_set_correction(kind))
             outs = []
-            for mode in (2, 5, 6):
+            for mode in (2, 5, 6, 8):
                 gpu._lib.check(lib.wf2cu_gemm_set_mode(mode))
                 outs.append(gpu.ops.matmul(gpu.from_numpy(A), gpu.ops.t(gpu.from_numpy(B))).to_numpy())
-                assert _last_path(gpu) == {2: 5, 5: 6, 6: 7}[mode]
+                assert _last_path(gpu) == {2: 5, 5: 6, 6: 7, 8: 9}[mode]
                 exact = gpu.ops.matmul(gpu.from_numpy(ints_a), gpu.from_numpy(ints_b)).to_numpy()
                 np.testing.assert_array_equal(exact, ints_a @ ints_b)
             np.testing.assert_array_equal(outs[0], outs[1])
             np.testing.assert_array_equal(outs[0], outs[2])
+            np.testing.assert_array_equal(outs[0], outs[3])
             errs[kind] = float(np.abs(outs[0] - truth).max() / den)
         gpu._lib.check(lib.wf2cu_gemm_set_correction(0))
         gpu._lib.check(lib.wf2cu_gemm_set_mode(5))
