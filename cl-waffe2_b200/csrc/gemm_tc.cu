@@ -204,6 +204,7 @@ struct TcArgs {
   const float* res;      // != NULL: then C = res[r, c] + C  (a residual connection riding on the projection)
   int64_t ldres;
   int c_tma;             // C goes out through map_c (bulk tensor stores) instead of per-lane global stores
+  int group_m = 0;       // m-tiles per raster group (0 = kGroupM)
 };
 
 // epilogue of the persistent kernels: 32 consecutive columns of one row per lane; same arithmetic as the separate
@@ -300,10 +301,11 @@ __device__ __forceinline__ void tile_coords(int t, const TcArgs& a, int& b, int&
   const int per_batch = a.tiles_m * a.tiles_n;
   b = t / per_batch;
   int r = t - b * per_batch;
-  const int group_sz = kGroupM * a.tiles_n;
+  const int G = a.group_m > 0 ? a.group_m : kGroupM;
+  const int group_sz = G * a.tiles_n;
   const int g = r / group_sz;
-  const int first_m = g * kGroupM;
-  const int gm = min(kGroupM, a.tiles_m - first_m);
+  const int first_m = g * G;
+  const int gm = min(G, a.tiles_m - first_m);
   r -= g * group_sz;
   mt = first_m + r % gm;
   nt = r / gm;
@@ -1322,6 +1324,13 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.b_bcast = b_nb == 1 ? 1 : 0;
     t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
+    {
+      // raster: 8 m-tiles of 512 rows per group — with 74 pairs in flight that is ~8 x 9 pair tiles sharing A blocks 9-fold and B
+      // blocks 8-fold (16 per group left 4.6-fold A reuse: 5.9 GB from DRAM at 8192^3 against 3.3 GB for the single-CTA kernel)
+      static int grp = -1;
+      if (grp < 0) { const char* e = getenv("WF2CU_PAIR_GROUP"); grp = e ? atoi(e) : 8; if (grp < 1) grp = 8; }
+      t.group_m = grp;
+    }
     const int64_t pairs_max = S().sm_count / 2;
     const int grid = 2 * (int)(total < pairs_max ? total : pairs_max);
     gemm_tc2sm_kernel<<<grid, GEMM_THREADS, P2_SMEM, S().stream>>>(mah, mal, mbh, mbl, mc, t);
