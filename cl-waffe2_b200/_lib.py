@@ -60,7 +60,7 @@ PROTOTYPES = {
     "wf2cu_reduce_sum": [VP, VP, i32, f32], "wf2cu_sum_all_noalloc": [vp, i64, i64, vp, i64, i32, f32], "wf2cu_softmax": [VP, VP, i32, i32], "wf2cu_softmax_ex": [VP, VP, i32, i32, f32],
     "wf2cu_reduce_maxmin": [i32, VP, VP], "wf2cu_argmaxmin": [i32, VP, VP],
     "wf2cu_gemm": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i64, i64, i64],
-    "wf2cu_gemm_set_mode": [i32], "wf2cu_gemm_set_correction": [i32], "wf2cu_gemm_last_path": [C.POINTER(i32)],
+    "wf2cu_gemm_set_mode": [i32], "wf2cu_gemm_set_correction": [i32], "wf2cu_emit_operand_planes": [i32], "wf2cu_gemm_last_path": [C.POINTER(i32)],
     "wf2cu_gemm_const_operand": [vp, i64, i64, i32], "wf2cu_gemm_const_stats": [C.POINTER(i64), C.POINTER(i64)],
     "wf2cu_gemm_ex": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i32, vp, i64, i64],
     "wf2cu_gemm_ex2": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i32, vp, i64, i64],

@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restri
   }
 }
 
-struct PvArgs { float* out; int N, tiles_m, batch_heads; };
+struct PvArgs { float* out; int N, tiles_m, batch_heads; float* plane; };   // plane: mixed bf16 operand plane of out (or NULL)
 
 __global__ void __launch_bounds__(P_THREADS, 1)
 attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant__ CUtensorMap map_vh,
@@ -222,6 +222,14 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           crow[8 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+        if (a.plane) {                       // the projection that follows reads this row as its K-major A operand
+          float* prow = a.plane + ((size_t)b * a.N + row) * AE;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            plane_store4(prow, h * AD + 4 * j, __uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
+            plane_store4(prow, h * AD + 32 + 4 * j, __uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+          }
+        }
       }
       if (++as == 2) { as = 0; aph ^= 1; }
     }
@@ -311,11 +319,14 @@ int wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off
     WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
     attr_set = true;
   }
-  PvArgs args{O, N, N / P_M, BH};
+  PvArgs args{O, N, N / P_M, BH, nullptr};
+  if (S().emit_next) args.plane = planes_emit_begin(batch * seq, AE);     // wf2cu_emit_operand_planes: one-shot, may decline
   const int total = args.tiles_m * BH;
   const int grid = total < S().sm_count ? total : S().sm_count;
   WF2_CUDA(launch_pdl(attn_pv_kernel, dim3(grid), dim3(P_THREADS), P_SMEM, S().stream, mp, mvh, mvl, args));
-  return post_launch("wf2cu_attn_pv");
+  rc = post_launch("wf2cu_attn_pv");
+  if (!rc && args.plane) planes_emit_publish(O, batch * seq, AE, AE, args.plane);
+  return rc;
 }
 
 }  // extern "C"

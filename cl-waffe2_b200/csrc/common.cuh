@@ -35,6 +35,10 @@ struct State {
   cudaStream_t side[kBranches] = {};
   cudaEvent_t fork_ev[kBranches] = {}, join_ev[kBranches] = {};
   int branch = 0;                                 // 0 = main, 1..kBranches-1 = side
+  // operand planes written by a PRODUCER for the MatmulNode that follows it (wf2cu_emit_operand_planes; gemm_tc.cu):
+  // valid from the producer's launch until the next launch of any kind (post_launch clears it; the consuming product looks first)
+  struct FreshPlanes { const float* ptr = nullptr; int64_t rows = 0, k = 0, ld = 0; float* lo = nullptr; } fresh;
+  int emit_next = 0;                              // one-shot: the next producer call also writes its result's planes
 };
 State& S();
 
@@ -62,6 +66,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 // call after every kernel launch
 inline int post_launch(const char* name) {
   S().launches.fetch_add(1, std::memory_order_relaxed);
+  S().fresh.ptr = nullptr;                         // whatever was launched may have written the tensor the planes belong to
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(e, name, __FILE__, __LINE__);
   return 0;
@@ -74,6 +79,30 @@ void gemm_tc_release();   // gemm_tc.cu: frees the hi/lo plane workspaces
 // gemm_tc.cu: storage [ptr, ptr + bytes) was overwritten by a transfer (released = false: planes kept for a constant operand
 // there are split again on the next product) or freed (released = true: planes and the constant declaration are dropped)
 void gemm_tc_const_touch(const void* ptr, size_t bytes, bool released);
+// gemm_tc.cu: a producer that was asked to (S().emit_next, cleared here) gets the buffer for the mixed bf16 operand plane of its
+// (rows x k) fp32 result — layout of split_planes_direct_kernel with k-blocks of 16 — or nullptr when the request cannot be
+// met (k not a multiple of 32, allocation needed inside a graph capture, side branch).  After its launch it publishes them.
+float* planes_emit_begin(int64_t rows, int64_t k);
+void planes_emit_publish(const float* result, int64_t rows, int64_t k, int64_t ld, float* lo);
+#ifdef __CUDACC__
+// the two 16-bit halves a producer stores for element x: bf16_rn(x) and bf16_rn(x - trunc_tf32(x)); 0 / 0 for inf and nan
+// (exactly split_bf<true> of gemm_tc.cu, so a produced plane equals the pre-pass's bit for bit)
+__device__ __forceinline__ void plane_bits(float x, uint32_t& hb, uint32_t& lb) {
+  const float hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+  if (fabsf(hi) <= 3.0e38f) {
+    asm("{\n\t.reg .b16 t;\n\tcvt.rn.bf16.f32 t, %1;\n\tcvt.u32.u16 %0, t;\n\t}" : "=r"(hb) : "f"(x));
+    asm("{\n\t.reg .b16 t;\n\tcvt.rn.bf16.f32 t, %1;\n\tcvt.u32.u16 %0, t;\n\t}" : "=r"(lb) : "f"(__fsub_rn(x, hi)));
+  } else { hb = 0; lb = 0; }
+}
+// four consecutive elements (columns c .. c + 3, c a multiple of 4) of a row of the plane: two 8-byte stores
+__device__ __forceinline__ void plane_store4(float* plane_row, int c, float x0, float x1, float x2, float x3) {
+  uint32_t h0, h1, h2, h3, l0, l1, l2, l3;
+  plane_bits(x0, h0, l0); plane_bits(x1, h1, l1); plane_bits(x2, h2, l2); plane_bits(x3, h3, l3);
+  uint16_t* dst = reinterpret_cast<uint16_t*>(plane_row) + (c >> 4) * 32 + (c & 15);
+  *reinterpret_cast<uint2*>(dst) = make_uint2(h0 | (h1 << 16), h2 | (h3 << 16));
+  *reinterpret_cast<uint2*>(dst + 16) = make_uint2(l0 | (l1 << 16), l2 | (l3 << 16));
+}
+#endif
 
 // ---- programmatic dependent launch (PDL) -------------------------------------------------------------
 // Back-to-back kernels of a compiled instruction sequence are serialised by the stream (or by the edges of the captured

@@ -629,6 +629,12 @@ int wf2cu_gemm_set_correction(int kind) {
   return 0;
 }
 
+int wf2cu_emit_operand_planes(int on) {
+  WF2_REQUIRE_INIT();
+  S().emit_next = on ? 1 : 0;
+  return 0;
+}
+
 int wf2cu_gemm_set_mode(int mode) {
   WF2_CHECK(mode >= 0 && mode <= 8, "wf2cu_gemm_set_mode: mode %d not in 0..8", mode);
   S().gemm_mode = mode;

@@ -383,12 +383,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
           if (a.passes == 2) {
             // per 16 k: the two corrections as bf16 MMAs of K = 16 (bf16(A) . bf16(B_lo) + bf16(A_lo) . bf16(B)), then the main
             // product as two TF32 MMAs of K = 8 — the order gemm_tc256_kernel uses per k-block of 16, so that every tile shape
-            // accumulates in the same order.  The 128-byte swizzle row of the mixed plane holds hb[0:16] hb[16:32] lb[0:16]
-            // lb[16:32], 32 bytes (two 16-byte descriptor units) each.
+            // accumulates in the same order.  The mixed plane is laid out per k-block of 16 for every kernel (hb[0:16] lb[0:16]
+            // hb[16:32] lb[16:32] in this kernel's 128-byte swizzle row, 32 bytes = two 16-byte descriptor units each), so one
+            // plane set serves whichever tile shape consumes it (and a producer can write it without knowing the consumer).
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
-              tc_mma_bf16(d, dal + (uint64_t)(2 * j), dbl + (uint64_t)(2 * (2 + j)), kIdescBf16, (kb | j) != 0);
-              tc_mma_bf16(d, dal + (uint64_t)(2 * (2 + j)), dbl + (uint64_t)(2 * j), kIdescBf16, 1);
+              tc_mma_bf16(d, dal + (uint64_t)(4 * j), dbl + (uint64_t)(4 * j + 2), kIdescBf16, (kb | j) != 0);
+              tc_mma_bf16(d, dal + (uint64_t)(4 * j + 2), dbl + (uint64_t)(4 * j), kIdescBf16, 1);
               tc_mma_tf32(d, dah + (uint64_t)(4 * j), dbh + (uint64_t)(4 * j), kIdescTf32, 1);
               tc_mma_tf32(d, dah + (uint64_t)(4 * j + 2), dbh + (uint64_t)(4 * j + 2), kIdescTf32, 1);
             }
@@ -972,7 +973,9 @@ static std::vector<void*> g_retired;     // older workspaces a captured graph ma
 static bool g_attr_set = false;
 
 void gemm_tc_const_release();
+void planes_emit_release();
 void gemm_tc_release() {
+  planes_emit_release();
   if (g_ws) cudaFree(g_ws);
   for (void* p : g_retired) cudaFree(p);
   g_retired.clear();
@@ -1000,6 +1003,42 @@ static int ensure_ws(size_t bytes) {
 float* tc_workspace(size_t bytes) {
   if (ensure_ws(bytes)) return nullptr;
   return g_ws;
+}
+
+// ---- operand planes written by producers (wf2cu_emit_operand_planes) ---------------------------------------------
+// The activations of a layer chain are the K-major A operand of the next MatmulNode: its pre-pass (read 4 + write 4 bytes per
+// element, one launch) only restates what the producing kernel had in registers.  A producer that is asked to writes the mixed
+// bf16 plane itself (GPT-2 small: LayerNorm -> QKV / fc, P.V -> proj, gelu(fc) -> proj: 4 pre-passes per block, 8 % of the
+// forward).  One grow-only buffer, stream ordered like the workspace; retired buffers stay alive for captured graphs.
+static float* g_emit = nullptr;
+static size_t g_emit_bytes = 0;
+int gemm_tc_correction();
+
+float* planes_emit_begin(int64_t rows, int64_t k) {
+  S().emit_next = 0;
+  if (rows < 1 || k < 32 || (k & 31) || S().branch != 0 || gemm_tc_correction() != 0) return nullptr;
+  const size_t need = (size_t)rows * (size_t)k * 4;
+  if (need > g_emit_bytes) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(S().stream, &cs);
+    if (cs != cudaStreamCaptureStatusNone) return nullptr;      // no allocation inside a capture: the consumer runs its pre-pass
+    float* p = nullptr;
+    if (cudaMalloc(&p, need) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (g_emit) g_retired.push_back(g_emit);
+    g_emit = p; g_emit_bytes = need;
+  }
+  return g_emit;
+}
+
+void planes_emit_release() {
+  if (g_emit) cudaFree(g_emit);
+  g_emit = nullptr; g_emit_bytes = 0;
+  S().fresh.ptr = nullptr; S().emit_next = 0;
+}
+
+void planes_emit_publish(const float* result, int64_t rows, int64_t k, int64_t ld, float* lo) {
+  State::FreshPlanes& f = S().fresh;
+  f.ptr = result; f.rows = rows; f.k = k; f.ld = ld; f.lo = lo;
 }
 
 static bool g_t256_auto = true;       // auto mode may take the 256x256-tile kernel (rule in gemm_tc_try)
@@ -1120,6 +1159,15 @@ static void drop_plane(PlaneVal& v) {
 
 // the storage [ptr, ptr + bytes) was written (stale = true: keep the buffers, split again) or released (drop them)
 void gemm_tc_const_touch(const void* ptr, size_t bytes, bool released) {
+  {
+    // a transfer into (or the release of) the tensor a producer wrote planes for: the planes no longer describe it
+    const State::FreshPlanes& f = S().fresh;
+    if (f.ptr) {
+      const uintptr_t a0 = reinterpret_cast<uintptr_t>(ptr), a1 = a0 + bytes;
+      const uintptr_t f0 = reinterpret_cast<uintptr_t>(f.ptr), f1 = f0 + (size_t)f.rows * (size_t)f.ld * 4;
+      if (a0 < f1 && f0 < a1) S().fresh.ptr = nullptr;
+    }
+  }
   if (g_planes.empty() && (!released || g_const.empty())) return;
   const uintptr_t lo = reinterpret_cast<uintptr_t>(ptr), hi = lo + bytes;
   for (auto it = g_planes.begin(); it != g_planes.end();) {
@@ -1223,6 +1271,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   // the hi/lo plane workspace is one buffer: only the main stream may use it (a side branch of a compiled
   // step takes the SIMT / fused kernels instead)
   if (S().branch != 0) return 0;
+  const State::FreshPlanes fp = S().fresh;                 // planes the producer of A wrote (valid until the next launch)
+  S().fresh.ptr = nullptr;
   if (mode == 0) {
     // the tensor path pays two extra passes over the operands and wants >= 1 wave of 128x256 tiles
     if (m < 64 || n < 64 || k < 32) return 0;
@@ -1262,7 +1312,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   if (nb == 512) pair2 = true;
   if (pair2) nb = 256;                                     // (the pair kernel shares the 256-row kernels' k-block and plane layout)
   // the second plane: fp32 lo (3xTF32) or the mixed bf16 plane laid out for the chosen kernel's k-block
-  const int bf_blk = passes == 2 ? (nb ? T2K : TK) : 0;
+  const int bf_blk = passes == 2 ? T2K : 0;                // one mixed-plane layout (k-blocks of 16) for every tile shape
   // Operand planes.  A: logical (m x k); ta = stored transposed (k x m) -> m is the contiguous axis of the source.
   // B: planes are (n x k); op(B) is k x n; !tb = stored (k x n) row-major -> n contiguous.
   //   raw_hi   a K-major, 16-byte aligned operand is its own hi plane (TMA map over the source, hi = trunc_tf32(x)): its pre-pass
@@ -1278,6 +1328,10 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     q.konst = in_const_range(q.src);
     if (!q.konst) ws_need += (q.raw ? 1 : 2) * q.pbytes;
   }
+  // A's second plane already written by its producer: same bits as the pre-pass would write (plane_bits == split_bf<true>)
+  const bool a_fresh = fp.ptr == A && fp.lo && !ta && passes == 2 && pr[0].raw && !pr[0].konst && a_nb == 1 && fp.rows == m && fp.k == k &&
+                       fp.ld == lda && Kp == k;
+  if (a_fresh) ws_need -= pr[0].pbytes;
   if (ws_need && (rc = ensure_ws(ws_need))) return rc;
   {
     uint8_t* w = reinterpret_cast<uint8_t*>(g_ws);
@@ -1290,6 +1344,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
         PlaneVal* v = nullptr;
         if ((rc = const_planes(key, q.pbytes, src_floats, &v, &fresh[i]))) return rc;
         q.hi = v->hi; q.lo = v->lo;
+      } else if (i == 0 && a_fresh) {
+        q.lo = fp.lo; fresh[0] = false;
       } else {
         if (!q.raw) { q.hi = reinterpret_cast<float*>(w); w += q.pbytes; }
         q.lo = reinterpret_cast<float*>(w); w += q.pbytes;
@@ -1411,6 +1467,7 @@ static bool raw_operand_ok(const float* p, int64_t ld, int64_t bstride, int64_t 
 // planes are kept (constant operand), 2/3 when the source is its own hi plane, 1 otherwise
 double gemm_tc_prepass_share(const float* p, int64_t ld, int64_t bstride, int64_t nbatch, bool kmajor) {
   if (in_const_range(p)) return 0.0;
+  if (kmajor && S().fresh.ptr == p && S().fresh.lo && S().fresh.ld == ld) return 0.0;   // its producer wrote the plane
   if (kmajor && rawhi_enabled() && gemm_tc_correction() == 0 && raw_operand_ok(p, ld, bstride, nbatch)) return 2.0 / 3.0;
   return 1.0;
 }

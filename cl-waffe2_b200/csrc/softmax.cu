@@ -511,7 +511,8 @@ extern "C" int wf2cu_softmax_ex(const wf2cu_view* x, const wf2cu_view* out, int 
 // a GPT-2 small forward.  One kernel, a warp per row with the row in registers; every element goes through the
 // same operations in the same order as the node chain (mean = sum / count with a correctly rounded divide, square
 // as a product, IEEE sqrt and divide), the two row sums are shuffle trees (the 1e-5 reduction bar).
-struct LnArgs { const float* x; const float* g; const float* b; float* out; int64_t rows; int cols; float eps; };
+struct LnArgs { const float* x; const float* g; const float* b; float* out; int64_t rows; int cols; float eps;
+                float* plane; };   // != NULL: also the mixed bf16 operand plane of the result (planes_emit_begin)
 
 template <int V>   // float4 per lane: cols <= 128 * V
 __global__ void __launch_bounds__(256) layernorm_kernel(const __grid_constant__ LnArgs a) {
@@ -555,6 +556,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const __grid_constant__ 
       y.z = __fadd_rn(__fmul_rn(__fdiv_rn(v[k].z, r), g4.z), b4.z);
       y.w = __fadd_rn(__fmul_rn(__fdiv_rn(v[k].w, r), g4.w), b4.w);
       orow[i] = y;
+      if (a.plane) plane_store4(a.plane + row * a.cols, 4 * i, y.x, y.y, y.z, y.w);
     }
   }
 }
@@ -563,7 +565,7 @@ extern "C" int wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int6
                                void* out, int64_t out_off, int64_t rows, int64_t cols, float eps) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(x && g && b && out && rows >= 0 && cols >= 1, "wf2cu_layernorm: bad arguments");
-  LnArgs a{(const float*)x + x_off, (const float*)g + g_off, (const float*)b + b_off, (float*)out + out_off, rows, (int)cols, eps};
+  LnArgs a{(const float*)x + x_off, (const float*)g + g_off, (const float*)b + b_off, (float*)out + out_off, rows, (int)cols, eps, nullptr};
   const bool ok = cols % 4 == 0 && cols <= 1024 && al16s(a.x) && al16s(a.g) && al16s(a.b) && al16s(a.out);
   if (!ok)
     return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_layernorm: rows of %lld floats (need a multiple of 4, <= 1024, 16-byte aligned): "
@@ -571,11 +573,14 @@ extern "C" int wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int6
   if (rows == 0) return 0;
   const int64_t grid = (rows + 7) / 8;
   WF2_CHECK(grid < (int64_t(1) << 31), "wf2cu_layernorm: too many rows");
+  if (S().emit_next) a.plane = planes_emit_begin(rows, cols);      // wf2cu_emit_operand_planes: one-shot, may decline
   cudaStream_t st = S().stream;
   if (cols <= 256) WF2_CUDA(launch_pdl(layernorm_kernel<2>, dim3((unsigned)grid), dim3(256), 0, st, a));
   else if (cols <= 512) WF2_CUDA(launch_pdl(layernorm_kernel<4>, dim3((unsigned)grid), dim3(256), 0, st, a));
   else WF2_CUDA(launch_pdl(layernorm_kernel<8>, dim3((unsigned)grid), dim3(256), 0, st, a));
-  return post_launch("wf2cu_layernorm");
+  const int rc = post_launch("wf2cu_layernorm");
+  if (!rc && a.plane) planes_emit_publish(a.out, rows, cols, cols, a.plane);
+  return rc;
 }
 
 extern "C" int wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,

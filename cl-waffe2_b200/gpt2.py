@@ -61,13 +61,19 @@ def _bcast_keep(stat: CUDATensor, like: CUDATensor) -> CUDATensor:
     return view(stat, *([T] * (like.dims() - 1) + [[":broadcast", like.shape[-1]]]))
 
 
-def layer_norm(x: CUDATensor, g: CUDATensor, b: CUDATensor, eps: float = 1e-5) -> CUDATensor:
+EMIT_PLANES = True      # producers write the operand plane of the MatmulNode that follows (wf2cu_emit_operand_planes)
+
+
+def layer_norm(x: CUDATensor, g: CUDATensor, b: CUDATensor, eps: float = 1e-5, feeds_matmul: bool = False) -> CUDATensor:
     """LayerNorm-Revisit (examples/gpt-2/utils.lisp:114-127): one kernel when FUSE_LAYERNORM (the ten-node chain
-    with the same per-element operations, wf2cu_layernorm), node by node otherwise."""
+    with the same per-element operations, wf2cu_layernorm), node by node otherwise.  feeds_matmul: the result is the A operand
+    of the projection issued next, so the kernel also writes its tensor-core operand plane (same bits as the product's pre-pass)."""
     shape = x.shape
     if FUSE_LAYERNORM and x.is_contiguous() and not x.permuted_p() and shape[-1] % 4 == 0 and shape[-1] <= 1024:
         out = make_tensor(shape)
         rows = x.numel() // shape[-1]
+        if feeds_matmul and EMIT_PLANES:
+            _lib.check(_lib.load().wf2cu_emit_operand_planes(1))
         _lib.check(_lib.load().wf2cu_layernorm(x.vec.ptr, x.lower().offset, g.vec.ptr, g.lower().offset, b.vec.ptr, b.lower().offset,
                                                out.vec.ptr, out.lower().offset, rows, shape[-1], float(eps)))
         return out
@@ -121,6 +127,8 @@ def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
         rc = lib.wf2cu_attn_heads_softmax(qkv.vec.ptr, off, B, N, n_head, E // n_head, float(N), w.vec.ptr, w.lower().offset)
         if rc == 0:
             out = make_tensor([B, N, E])
+            if EMIT_PLANES:                                  # the output projection is issued next
+                _lib.check(lib.wf2cu_emit_operand_planes(1))
             _lib.check(lib.wf2cu_attn_pv(w.vec.ptr, w.lower().offset, qkv.vec.ptr, off, B, N, n_head, E // n_head, out.vec.ptr, out.lower().offset))
             return out
         if rc != 3:                              # anything but WF2CU_ERR_UNSUPPORTED is an error
@@ -177,11 +185,11 @@ class GPT2Layer:
         self.fc_proj_w, self.fc_proj_b = g("mlp.c_proj.w"), g("mlp.c_proj.b")
 
     def __call__(self, x: CUDATensor) -> CUDATensor:
-        h = layer_norm(x, self.ln_1_g, self.ln_1_b)
+        h = layer_norm(x, self.ln_1_g, self.ln_1_b, feeds_matmul=True)
         qkv = _linear(h, self.attn_w, self.attn_b)
         a = self_attention(qkv, self.n_head)
         x = _linear(a, self.proj_w, self.proj_b, residual=x)            # (!add x (proj a)): residual
-        h = layer_norm(x, self.ln_2_g, self.ln_2_b)
+        h = layer_norm(x, self.ln_2_g, self.ln_2_b, feeds_matmul=True)
         m = _linear(h, self.fc_w, self.fc_b, gelu=True)                 # (!gelu (fc h))
         return _linear(m, self.fc_proj_w, self.fc_proj_b, residual=x)   # (!add x (fc-proj m)): residual
 

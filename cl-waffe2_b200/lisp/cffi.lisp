@@ -117,6 +117,7 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 		      (dx :pointer) (dx-off :int64) (rows :int64) (cols :int64) (accumulate :int)))
 (defwf2 gemm-set-mode ((mode :int)))
 (defwf2 gemm-set-correction ((kind :int)))
+(defwf2 emit-operand-planes ((on :int)))
 (defwf2 gemm-last-path ((out :pointer)))
 (defwf2 gemm-const-operand ((base :pointer) (offset :int64) (count :int64) (constant :int)))
 (defwf2 gemm-const-stats ((entries :pointer) (bytes :pointer)))

@@ -525,3 +525,72 @@ def test_gpt2_constant_weights_equal_plain_forward(gpu):
     np.testing.assert_array_equal(kept, plain)
     print(f"\nGPT-2 (2 layers) kept plane sets: {entries - base}")
     assert entries > base
+
+
+def _launches(gpu) -> int:
+    n = C.c_int64(0)
+    gpu._lib.check(gpu._lib.load().wf2cu_launch_count(C.byref(n)))
+    return n.value
+
+
+def test_producer_written_operand_planes_equal_the_prepass(gpu):
+    """wf2cu_emit_operand_planes: LayerNorm / P.V / a gelu projection also write the tensor-core operand plane of their result, and
+    the MatmulNode issued next skips its pre-pass.  Same bits as the pre-pass writes (csrc/common.cuh plane_bits == split_bf), so the
+    product — and a whole GPT-2 forward — is bit-identical with and without; the launch count shows the pre-passes are gone; a
+    launch between producer and consumer, a different operand, or a transposed use must fall back to the pre-pass silently."""
+    g = importlib.import_module("cl-waffe2_b200.gpt2")
+    lib = gpu._lib.load()
+    rng = np.random.default_rng(9)
+    rows, E, n = 2048, 768, 2304
+    x = gpu.from_numpy(rng.normal(size=(rows, E)).astype(np.float32))
+    gam = gpu.from_numpy((1 + 0.02 * rng.normal(size=(E,))).astype(np.float32))
+    bet = gpu.from_numpy((0.02 * rng.normal(size=(E,))).astype(np.float32))
+    W = gpu.from_numpy((0.02 * rng.normal(size=(E, n))).astype(np.float32))
+    gpu._lib.check(lib.wf2cu_gemm_const_operand(W.vec.ptr, 0, E * n, 1))
+    try:
+        g.EMIT_PLANES = False
+        h0 = g.layer_norm(x, gam, bet, feeds_matmul=True)
+        want = gpu.ops.matmul(h0, W).to_numpy()
+        l0 = _launches(gpu)
+        h0 = g.layer_norm(x, gam, bet, feeds_matmul=True)
+        gpu.ops.matmul(h0, W)
+        plain_launches = _launches(gpu) - l0
+        g.EMIT_PLANES = True
+        l0 = _launches(gpu)
+        h1 = g.layer_norm(x, gam, bet, feeds_matmul=True)
+        got = gpu.ops.matmul(h1, W)
+        emit_launches = _launches(gpu) - l0
+        np.testing.assert_array_equal(h1.to_numpy(), h0.to_numpy())
+        np.testing.assert_array_equal(got.to_numpy(), want)
+        assert emit_launches == plain_launches - 1, (emit_launches, plain_launches)
+        # a launch in between invalidates the planes: the product runs its pre-pass again, same result
+        h2 = g.layer_norm(x, gam, bet, feeds_matmul=True)
+        gpu.ops.add_(h2, 0.0)
+        l0 = _launches(gpu)
+        got2 = gpu.ops.matmul(h2, W)
+        assert _launches(gpu) - l0 == plain_launches - 1          # (the LayerNorm launch is not in this window)
+        np.testing.assert_array_equal(got2.to_numpy(), want)
+        # planes published for h3 must not be used for a product that reads another tensor
+        h3 = g.layer_norm(x, gam, bet, feeds_matmul=True)
+        other = gpu.ops.matmul(x, W).to_numpy()
+        truth = x.to_numpy().astype(np.float64) @ W.to_numpy().astype(np.float64)
+        assert np.abs(other - truth).max() <= 2e-5 * np.abs(truth).max()
+        del h3
+    finally:
+        g.EMIT_PLANES = True
+        gpu._lib.check(lib.wf2cu_gemm_const_operand(W.vec.ptr, 0, E * n, 0))
+    # the whole block chain: GPT-2 (2 layers, full width) with and without producer-written planes
+    cfg = dict(n_vocab=211, n_ctx=256, n_emb=768, n_head=12, n_layer=2)
+    model = g.GPT2(cfg, seed=3)
+    ctx = gpu.from_numpy(np.random.default_rng(5).integers(0, cfg["n_vocab"], size=(8, 256)).astype(np.float32))
+    try:
+        g.EMIT_PLANES = True
+        model(ctx)
+        l0 = _launches(gpu); a = model(ctx).to_numpy(); la = _launches(gpu) - l0
+        g.EMIT_PLANES = False
+        l0 = _launches(gpu); b = model(ctx).to_numpy(); lb = _launches(gpu) - l0
+    finally:
+        g.EMIT_PLANES = True
+    np.testing.assert_array_equal(a, b)
+    print(f"\nGPT-2 (2 layers): {la} launches with producer-written planes, {lb} without")
+    assert la < lb
