@@ -593,9 +593,13 @@ with the final argument lists."
 		       (error "CUDALayerNormNode: forward only; differentiate LayerNorm-Revisit instead")))
   (setf (slot-value self 'eps) eps))
 
-(defun cuda-layer-norm (x g b &key (eps 1.0e-5))
+(defun cuda-layer-norm (x g b &key (eps 1.0e-5) feeds-matmul)
   "Drop-in for `LayerNorm-Revisit` on dense CUDATensors whose last axis is a multiple of 4 and <= 1024
-(the library answers UNSUPPORTED otherwise, which `defwf2` signals as `cuda-backend-error`)."
+(the library answers UNSUPPORTED otherwise, which `defwf2` signals as `cuda-backend-error`).
+FEEDS-MATMUL: the result is the untransposed left operand of the `!matmul` issued next (LinearLayer after the norm): the kernel
+also writes that product's tensor-core operand plane (wf2cu_emit_operand_planes, one shot; same bits as the product's own
+pre-pass; ignored when the very next launch is not that product)."
+  (when feeds-matmul (emit-operand-planes 1))
   (call (CUDALayerNormNode eps) (->contiguous x) g b (make-input (shape x) nil :dtype (dtype x) :order (order x))))
 
 ;; ---- `!softmax` (`nn/activation.lisp:126-159`: five nodes and two disguised reductions) as ONE launch, optionally with the
@@ -655,8 +659,11 @@ with the final argument lists."
 		       (error "CUDASelfAttentionNode: forward only; differentiate SelfAttention instead")))
   (setf (slot-value self 'n-head) n-head))
 
-(defun cuda-self-attention (x &key (n-head 12))
-  "Drop-in for the first value of `(SelfAttention x nil)` on a dense (batch N 3E) CUDATensor."
+(defun cuda-self-attention (x &key (n-head 12) feeds-matmul)
+  "Drop-in for the first value of `(SelfAttention x nil)` on a dense (batch N 3E) CUDATensor.
+FEEDS-MATMUL: as in `cuda-layer-norm` (the output projection follows; the request reaches the second of the two launches
+because the first one is not a producer and leaves the one-shot flag alone)."
+  (when feeds-matmul (emit-operand-planes 1))
   (let ((e (/ (car (last (shape x))) 3)))
     (call (CUDASelfAttentionNode n-head)
 	  (->contiguous x)
