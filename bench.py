@@ -267,7 +267,7 @@ def gemm_sweep(wf, sizes=(256, 512, 1024, 2048, 4096, 8192), check=True):
             chk(lib.wf2cu_timer_stop(C.byref(ms)))
             best = ms.value / reps if best is None else min(best, ms.value / reps)
         tf = 2.0 * N ** 3 / (best * 1e-3) / 1e12
-        units = 2 if path.value in (5, 6, 7) else 3          # planes kernels: TF32 + 2 x bf16 corrections; others: 3 x TF32
+        units = 2 if path.value in (5, 6, 7, 9) else 3       # planes kernels (single CTA and CTA pair): TF32 + 2 x bf16 corrections; others: 3 x TF32
         c = {"N": N, "trans": f"{'T' if ta else 'N'}{'T' if tb else 'N'}", "path": GEMM_PATHS.get(path.value, str(path.value)), "ms": best,
              "tflops": tf, "frac_of_tf32_peak": tf / tf32_peak, "pipe_units": units, "pipe_tflops": units * tf,
              "pipe_frac": units * tf / tf32_peak}

@@ -119,8 +119,10 @@ __device__ __forceinline__ void pdl_prologue() {
 }
 #endif
 bool pdl_enabled();
+void carveout_hint(const void* kernel);
 template <class... KArgs, class... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  carveout_hint(reinterpret_cast<const void*>(kernel));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;

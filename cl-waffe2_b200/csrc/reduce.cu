@@ -730,6 +730,14 @@ bool has_reduction_axes(const wf2cu_view* dst) {
 // 2 stages 13.4; 3 or 4 CTAs per SM, an ordinary launch, or letting the dependents in late are all slower.
 //   stages x 16 KiB of ring per CTA, CTAs per SM, pdl: 0 = ordinary launch, 1 = programmatic dependent launch with the
 //   dependents let in at once, 2 = ... let in when this CTA has finished streaming
+// The carve-out matters for the kernels AROUND this one: left to the driver, a 48 KiB ring asks for the 196 KB configuration (four
+// CTAs would fit), its neighbours in a compiled sequence use almost no shared memory, and the SMs reconfigure at both boundaries —
+// the 12-kernel sweep step took 0.2875 ms instead of 0.2808 although this kernel alone got 1 us faster.  44 % (the 100 KB
+// configuration: the two resident CTAs' rings) keeps both: step 0.2806 ms, this kernel 13.2 us (profiles/r02z_flat_carveout.log).
+static int flat_carveout() {
+  const char* e = getenv("WF2CU_FLAT_CARVEOUT");
+  return e ? atoi(e) : 44;
+}
 struct FlatTune { int stages, ctas_per_sm, pdl; };
 static const FlatTune& flat_tune() {
   static FlatTune t = {0, 0, 0};
@@ -782,6 +790,7 @@ static int reduce_impl(const wf2cu_view* dst, const wf2cu_view* src, Fin fin, co
       constexpr int which = std::is_same<M, MSum>::value ? 0 : 1;
       if (!attr_set[which]) {
         WF2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, kFlatStages * kFlatChunk));
+        WF2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, flat_carveout()));
         attr_set[which] = true;
       }
       const FlatTune& ft = flat_tune();
@@ -1002,6 +1011,7 @@ static int noalloc_setup(int dev, unsigned char** out) {
     unsigned char* p = nullptr;
     WF2_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
     WF2_CUDA(cudaFuncSetAttribute(reduce_flat_bulk_kernel<MSum>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFlatStages * kFlatChunk));
+    WF2_CUDA(cudaFuncSetAttribute(reduce_flat_bulk_kernel<MSum>, cudaFuncAttributePreferredSharedMemoryCarveout, flat_carveout()));
     g_noalloc_ptr[dev] = p;
   }
   *out = g_noalloc_ptr[dev];

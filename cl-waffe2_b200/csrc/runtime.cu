@@ -22,6 +22,18 @@ bool pdl_enabled() {
   return on != 0;
 }
 
+// WF2CU_CARVEOUT=<percent>: every kernel launched through launch_pdl asks for that shared-memory carve-out (experiment: a kernel
+// whose carve-out differs from its neighbours' makes the SMs reconfigure at both boundaries)
+void carveout_hint(const void* kernel) {
+  static int pct = -2;
+  if (pct == -2) { const char* e = getenv("WF2CU_CARVEOUT"); pct = e ? atoi(e) : -1; }
+  if (pct < 0) return;
+  static std::vector<const void*> seen;
+  for (const void* k : seen) if (k == kernel) return;
+  seen.push_back(kernel);
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+}
+
 static thread_local char g_err[1024] = "";
 
 int set_error(int code, const char* fmt, ...) {
