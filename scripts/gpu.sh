@@ -41,7 +41,7 @@ for task in "$@"; do
               timeout 300 $cmd > gpurun_out/${tag}_launches_plain.log 2>&1 &&
               timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${tag}_launches.csv $cmd > gpurun_out/${tag}_launches_ncu.log 2>&1
               echo "launches rc=$?" ;;
-    ncu:*)    IFS=: read -r _ regex script <<< "$task"; base=$(basename "${script%%+*}" .py)$(echo "${script#*.py}" | tr -d '+')
+    ncu:*)    IFS=: read -r _ regex script <<< "$task"; base=$(basename "${script%%+*}" .py)$(echo "${script#*.py}" | tr -d '+')_$(echo "$regex" | tr -cd 'A-Za-z0-9_')
               cmd="python ${script//+/ }"          # scripts/x.py+8192 -> python scripts/x.py 8192
               timeout 300 $cmd > gpurun_out/${tag}_${base}_plain.log 2>&1 &&
               timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$regex" -c ${NCU_COUNT:-3} -f -o gpurun_out/${tag}_${base} $cmd > gpurun_out/${tag}_${base}_ncu.log 2>&1
