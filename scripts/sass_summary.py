@@ -4,7 +4,8 @@ the sm_100a machine code contains, with registers and spills from ptxas.
     python scripts/sass_summary.py [out.md]        (run by __graft_entry__.build(); default profiles/r02_sass_summary.md)
 
 Sources: `cuobjdump -sass cl-waffe2_b200/lib/libwaffe2cuda.so` (mnemonics per `Function :` block) and the `-Xptxas -v`
-logs build.py keeps in cl-waffe2_b200/_obj/*.log.  Mnemonics (B200_PROFILING.md): UTCHMMA = tcgen05.mma kind::tf32/f16,
+logs build.py keeps in cl-waffe2_b200/_obj/*.log.  Mnemonics (B200_PROFILING.md): UTCHMMA = tcgen05.mma kind::tf32/f16, 2CTA = any instruction in its
+cta_group::2 form (UTCHMMA.2CTA, UTMALDG...2CTA, UTCBAR.2CTA: the CTA-pair kernel),
 LDTM / STTM = tcgen05.ld / st (tensor memory), UTMALDG / UTMASTG = cp.async.bulk.tensor load / store (TMA),
 UBLKCP = cp.async.bulk (1-D bulk copy), UTCBAR = tcgen05.commit, SYNCS = mbarrier ops, LDG.E.128 / STG.E.128 = 16-byte
 global accesses, HMMA/IMMA would be legacy mma.sync (none expected)."""
@@ -17,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "cl-waffe2_b200", "lib", "libwaffe2cuda.so")
 OBJ = os.path.join(ROOT, "cl-waffe2_b200", "_obj")
 CUDA_BIN = os.path.dirname(os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc"))
-COLUMNS = ["UTCHMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTCBAR", "SYNCS", "LDG.E.128", "STG.E.128", "HMMA"]
+COLUMNS = ["UTCHMMA", "2CTA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTCBAR", "SYNCS", "LDG.E.128", "STG.E.128", "HMMA"]
 
 
 def demangle(names):
@@ -84,6 +85,8 @@ def sass_counts():
             continue
         op = m.group(1)
         counts[cur]["n"] += 1
+        if ".2CTA" in op:                                   # cta_group::2 forms (UTCHMMA.2CTA, UTMALDG...2CTA, UTCBAR.2CTA...)
+            counts[cur]["2CTA"] += 1
         for col in COLUMNS:
             if op == col or op.startswith(col + ".") or (col in ("LDG.E.128", "STG.E.128") and op.startswith(col.split(".")[0] + ".E.") and ".128" in op):
                 counts[cur][col] += 1
