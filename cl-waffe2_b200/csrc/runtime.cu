@@ -361,6 +361,7 @@ int wf2cu_set_f32(void* dev, int64_t index, float value) {
   WF2_REQUIRE_INIT();
   // value is copied by the runtime before returning for pageable sources
   WF2_CUDA(cudaMemcpyAsync((char*)dev + index * 4, &value, 4, cudaMemcpyHostToDevice, S().stream));
+  gemm_tc_const_touch((char*)dev + index * 4, 4, false);   // (setf vref) into a constant operand / a tensor with producer-written planes
   return 0;
 }
 
