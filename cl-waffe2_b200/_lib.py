@@ -72,6 +72,7 @@ PROTOTYPES = {
     "wf2cu_layernorm": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, f32],
     "wf2cu_attn_heads_softmax": [vp, i64, i64, i64, i64, i64, f32, vp, i64],
     "wf2cu_attn_pv": [vp, i64, vp, i64, i64, i64, i64, i64, vp, i64],
+    "wf2cu_attn_fused": [vp, i64, i64, i64, i64, i64, f32, vp, i64],
     "wf2cu_im2col": [vp, i64, vp, i64, GP], "wf2cu_col2im": [vp, i64, vp, i64, GP],
     "wf2cu_unfold": [VP, vp, i64, GP], "wf2cu_fold": [vp, i64, VP, GP, i32],
     "wf2cu_pool2d": [i32, VP, VP, GP], "wf2cu_pool2d_backward": [i32, VP, VP, VP, VP, GP, i32, i32],

@@ -63,6 +63,11 @@ constexpr int P_ATILE = P_M * P_K * 4;               // 16 KiB
 constexpr int P_BTILE = P_N * P_K * 4;               // 8 KiB
 constexpr int P_STAGE = P_ATILE + 2 * P_BTILE;       // raw P | V_hi | V_lo = 32 KiB
 constexpr int P_NS = 6;
+// NORM variant (wf2cu_attn_fused): the P tile holds the UN-normalised exponentials and a fourth tile of the stage the reciprocal
+// denominators r[i, j] of the same positions (shared by the 12 heads): stage = E | V_hi | V_lo | R = 48 KiB, 4 stages
+__host__ __device__ constexpr int p_stage(bool norm) { return P_STAGE + (norm ? P_ATILE : 0); }
+__host__ __device__ constexpr int p_ns(bool norm) { return norm ? 4 : P_NS; }
+__host__ __device__ constexpr int p_smem(bool norm) { return p_ns(norm) * p_stage(norm) + 1024 + 256; }
 constexpr int P_ACOL = 2 * P_N;                      // TMEM: columns [0, 128) two accumulators, [128, 256) two P operand buffers
 constexpr int P_THREADS = 320;
 constexpr int P_SMEM = P_NS * P_STAGE + 1024 + 256;
@@ -88,9 +93,11 @@ __global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restri
 
 struct PvArgs { float* out; int N, tiles_m, batch_heads; float* plane; };   // plane: mixed bf16 operand plane of out (or NULL)
 
+template <bool NORM>
 __global__ void __launch_bounds__(P_THREADS, 1)
 attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant__ CUtensorMap map_vh,
-               const __grid_constant__ CUtensorMap map_vl, const __grid_constant__ PvArgs a) {
+               const __grid_constant__ CUtensorMap map_vl, const __grid_constant__ CUtensorMap map_r, const __grid_constant__ PvArgs a) {
+  constexpr int P_NS = p_ns(NORM), P_STAGE = p_stage(NORM);          // shadow the two-launch path's constants
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P_NS * P_STAGE);
@@ -128,10 +135,11 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
           uint8_t* st = smem + s * P_STAGE;
-          mbar_expect_tx(&full[s], P_ATILE + 2 * P_BTILE);
+          mbar_expect_tx(&full[s], P_STAGE);
           tma_load_3d(&map_p, &full[s], st, kb * P_K, mt * P_M, bh);
           tma_load_3d(&map_vh, &full[s], st + P_ATILE, kb * P_K, 0, bh);
           tma_load_3d(&map_vl, &full[s], st + P_ATILE + P_BTILE, kb * P_K, 0, bh);
+          if (NORM) tma_load_3d(&map_r, &full[s], st + P_ATILE + 2 * P_BTILE, kb * P_K, mt * P_M, bh / AH);
           if (++s == P_NS) { s = 0; ph ^= 1; }
         }
       }
@@ -179,7 +187,11 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
         uint32_t hi[32], lo[32];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {                                // this lane's row: 8 chunks of 16 bytes, SWIZZLE_128B
-          const float4 x = *reinterpret_cast<const float4*>(st + row * 128 + ((j ^ (row & 7)) << 4));
+          float4 x = *reinterpret_cast<const float4*>(st + row * 128 + ((j ^ (row & 7)) << 4));
+          if (NORM) {      // p = RN(e r): the product the two-launch path forms in the score kernel's second pass
+            const float4 r = *reinterpret_cast<const float4*>(st + P_ATILE + 2 * P_BTILE + row * 128 + ((j ^ (row & 7)) << 4));
+            x.x = __fmul_rn(x.x, r.x); x.y = __fmul_rn(x.y, r.y); x.z = __fmul_rn(x.z, r.z); x.w = __fmul_rn(x.w, r.w);
+          }
           hi[4 * j] = __float_as_uint(x.x); hi[4 * j + 1] = __float_as_uint(x.y); hi[4 * j + 2] = __float_as_uint(x.z); hi[4 * j + 3] = __float_as_uint(x.w);
           lo[4 * j] = __float_as_uint(tf32_lo(x.x)); lo[4 * j + 1] = __float_as_uint(tf32_lo(x.y));
           lo[4 * j + 2] = __float_as_uint(tf32_lo(x.z)); lo[4 * j + 3] = __float_as_uint(tf32_lo(x.w));
@@ -279,27 +291,13 @@ int wf2cu_attn_heads_softmax(const void* qkv, int64_t qkv_off, int64_t batch, in
   return rc;
 }
 
-int wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head,
-                  int64_t head_dim, void* out, int64_t out_off) {
-  WF2_REQUIRE_INIT();
-  WF2_CHECK(qkv && p && out, "wf2cu_attn_pv: null pointer");
-  if (!attn_shape_ok(batch, seq, n_head, head_dim) || S().branch != 0)
-    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_pv: implemented for 12 heads of 64 features and seq a multiple of 128 on the main "
-                     "stream (got heads=%lld dim=%lld seq=%lld); issue the nodes separately", (long long)n_head, (long long)head_dim, (long long)seq);
-  float* P = (float*)p + p_off;
-  const float* x = (const float*)qkv + qkv_off;
-  float* O = (float*)out + out_off;
-  if ((reinterpret_cast<uintptr_t>(P) & 15) || (reinterpret_cast<uintptr_t>(O) & 15))
-    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_pv: operands must be 16-byte aligned");
+// P . V for both entry points.  norm_r != NULL: P holds un-normalised exponentials and norm_r the (B N N) reciprocal denominators.
+static int launch_pv(float* P, const float* norm_r, const float* x, float* vh, float* vl, int64_t batch, int64_t seq, float* O, const char* who) {
   const int N = (int)seq, BH = (int)(batch * AH);
-  const size_t plane = (size_t)BH * AD * N * 4;
-  float* vh = tc_workspace(2 * plane);
-  if (!vh) return WF2CU_ERR_CUDA;
-  float* vl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(vh) + plane);
   WF2_CUDA(launch_pdl(attn_split_v_kernel, dim3((unsigned)(N / 32), (unsigned)BH), dim3(256), 0, S().stream, x, vh, vl, N));
   int rc = post_launch("wf2cu_attn_pv(split V)");
   if (rc) return rc;
-  CUtensorMap mp, mvh, mvl;
+  CUtensorMap mp, mvh, mvl, mr;
   {
     const cuuint64_t pd[3] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)BH};
     const cuuint64_t ps[2] = {(cuuint64_t)N * 4, (cuuint64_t)N * N * 4};
@@ -313,20 +311,74 @@ int wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off
     if (rc) return rc;
     rc = encode(&mvl, 3, vl, vd, vs, vb, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, "V lo");
     if (rc) return rc;
+    mr = mp;
+    if (norm_r) {
+      const cuuint64_t rd[3] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)batch};
+      rc = encode(&mr, 3, (void*)norm_r, rd, ps, pb, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, "R");
+      if (rc) return rc;
+    }
   }
   static bool attr_set = false;
   if (!attr_set) {
-    WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+    WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(false)));
+    WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(true)));
     attr_set = true;
   }
   PvArgs args{O, N, N / P_M, BH, nullptr};
   if (S().emit_next) args.plane = planes_emit_begin(batch * seq, AE);     // wf2cu_emit_operand_planes: one-shot, may decline
   const int total = args.tiles_m * BH;
   const int grid = total < S().sm_count ? total : S().sm_count;
-  WF2_CUDA(launch_pdl(attn_pv_kernel, dim3(grid), dim3(P_THREADS), P_SMEM, S().stream, mp, mvh, mvl, args));
-  rc = post_launch("wf2cu_attn_pv");
+  if (norm_r) WF2_CUDA(launch_pdl(attn_pv_kernel<true>, dim3(grid), dim3(P_THREADS), p_smem(true), S().stream, mp, mvh, mvl, mr, args));
+  else        WF2_CUDA(launch_pdl(attn_pv_kernel<false>, dim3(grid), dim3(P_THREADS), p_smem(false), S().stream, mp, mvh, mvl, mr, args));
+  rc = post_launch(who);
   if (!rc && args.plane) planes_emit_publish(O, batch * seq, AE, AE, args.plane);
   return rc;
+}
+
+int wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head,
+                  int64_t head_dim, void* out, int64_t out_off) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(qkv && p && out, "wf2cu_attn_pv: null pointer");
+  if (!attn_shape_ok(batch, seq, n_head, head_dim) || S().branch != 0)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_pv: implemented for 12 heads of 64 features and seq a multiple of 128 on the main "
+                     "stream (got heads=%lld dim=%lld seq=%lld); issue the nodes separately", (long long)n_head, (long long)head_dim, (long long)seq);
+  float* P = (float*)p + p_off;
+  const float* x = (const float*)qkv + qkv_off;
+  float* O = (float*)out + out_off;
+  if ((reinterpret_cast<uintptr_t>(P) & 15) || (reinterpret_cast<uintptr_t>(O) & 15))
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_pv: operands must be 16-byte aligned");
+  const size_t plane = (size_t)(batch * AH) * AD * seq * 4;
+  float* vh = tc_workspace(2 * plane);
+  if (!vh) return WF2CU_ERR_CUDA;
+  float* vl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(vh) + plane);
+  return launch_pv(P, nullptr, x, vh, vl, batch, seq, O, "wf2cu_attn_pv");
+}
+
+int wf2cu_attn_fused(const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head, int64_t head_dim, float divisor,
+                     void* out, int64_t out_off) {
+  WF2_REQUIRE_INIT();
+  WF2_CHECK(qkv && out, "wf2cu_attn_fused: null pointer");
+  if (!attn_shape_ok(batch, seq, n_head, head_dim) || !(divisor > 0.f) || S().branch != 0)
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_fused: implemented for 12 heads of 64 features and seq a multiple of 128 on the main "
+                     "stream (got heads=%lld dim=%lld seq=%lld); issue the nodes separately", (long long)n_head, (long long)head_dim, (long long)seq);
+  const float* x = (const float*)qkv + qkv_off;
+  float* O = (float*)out + out_off;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(O) & 15))
+    return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_attn_fused: operands must be 16-byte aligned");
+  // workspace: E (B H N N) | R (B N N) | V_hi | V_lo
+  const size_t ebytes = (size_t)batch * AH * seq * seq * 4, rbytes = (size_t)batch * seq * seq * 4, plane = (size_t)(batch * AH) * AD * seq * 4;
+  float* ws = tc_workspace(ebytes + rbytes + 2 * plane);
+  if (!ws) return WF2CU_ERR_CUDA;
+  float* E = ws;
+  float* R = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws) + ebytes);
+  float* vh = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(R) + rbytes);
+  float* vl = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(vh) + plane);
+  const int emit = S().emit_next;            // the request is for the P.V launch: keep it across the score kernel
+  S().emit_next = 0;
+  int rc = attn_scores_onepass(x, batch, seq, divisor, E, R);
+  if (rc) return rc;
+  S().emit_next = emit;
+  return launch_pv(E, R, x, vh, vl, batch, seq, O, "wf2cu_attn_fused");
 }
 
 }  // extern "C"

@@ -95,6 +95,25 @@ struct RawAttnJob {
   }
 };
 
+// One-pass form (wf2cu_attn_fused): the 12 heads ONCE — E[b,h,i,j] = exp(s_h / N) leaves un-normalised, den accumulates in registers as
+// above, and after the twelfth head R[b,i,j] = RN(1 / den) goes out as a (B N N) tensor; the P.V kernel multiplies E by R on its way
+// into tensor memory (p = RN(e r), the very product the second pass forms).  Half the Q.K^T work, one exp per element instead of two.
+// R leaves through the tensor map in the `map_al` slot (unused when both operands arrive raw).
+struct RawAttnJob1 {
+  static constexpr int kEpiWarps = 16, kEpiBytes = 2 * 1024, kSubTiles = RA_H;
+  RawAttnArgs a;
+  __device__ __forceinline__ bool hyb() const { return false; }
+  __device__ __forceinline__ int items() const { return a.B * a.tiles_i * a.tiles_j; }
+  __device__ __forceinline__ void where(int w, int& jt, int& it, int& b) const {
+    jt = w % a.tiles_j; it = (w / a.tiles_j) % a.tiles_i; b = w / (a.tiles_j * a.tiles_i);
+  }
+  __device__ __forceinline__ RawCoords coords(int w, int sub) const {
+    int jt, it, b;
+    where(w, jt, it, b);
+    return RawCoords{sub * RA_D, it * RM, b, RA_E + sub * RA_D, jt * RN, b, RA_D / RK};
+  }
+};
+
 // exp(s / divisor) = 2^(s * log2(e) / divisor): one multiply by the pre-rounded constant and ex2.approx (relative error <= 2^-22
 // + 0.7 * 2^-23 |s / divisor|: ~3 ulp for the |s / divisor| < 1 the division by N produces).  The epilogue is what bounds this
 // kernel: with the library's 1-ulp exp (10 instructions per element, twice per element because the product is recomputed) it
@@ -275,6 +294,65 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         __syncwarp();
         if (lane == 0) mbar_arrive(&acc_empty[as]);
         if (++as == 2) { as = 0; aph ^= 1; }
+      } else if constexpr (std::is_same<JOB, RawAttnJob1>::value) {
+        // ---- one pass: E = exp(s_h / N) out per head, den in registers, R = RN(1 / den) out after the last head
+        const RawAttnArgs& a = job.a;
+        int jt, it, b;
+        job.where(w, jt, it, b);
+        const int col0 = jt * RN + cg * COLS;
+        float den[COLS];
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) den[c] = 0.f;
+#pragma unroll 1
+        for (int h = 0; h < RA_H; ++h) {
+          mbar_wait(&acc_full[as], aph);
+          tc_fence_after();
+          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * RN + cg * COLS);
+#pragma unroll
+          for (int c0 = 0; c0 < COLS; c0 += 8) {
+            uint32_t v[8];
+            tc_ld8(tbase + c0, v);
+            uint8_t* blk = slot + which * 1024;
+            which ^= 1;
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            tc_ld_wait();
+            if (c0 + 8 >= COLS) {                                   // the accumulator is in registers now
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&acc_empty[as]);
+            } else {
+              __syncwarp();
+            }
+            float e[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              e[c] = raw_attn_exp<POW2>(__uint_as_float(v[c]), a.scale);
+              den[c0 + c] = __fadd_rn(den[c0 + c], e[c]);
+            }
+            uint8_t* mine = blk + lane * 32;                       // SWIZZLE_32B: 16-byte chunk j of row r at j ^ ((r >> 2) & 1)
+            *reinterpret_cast<float4*>(mine + ((0 ^ ((lane >> 2) & 1)) << 4)) = make_float4(e[0], e[1], e[2], e[3]);
+            *reinterpret_cast<float4*>(mine + ((1 ^ ((lane >> 2) & 1)) << 4)) = make_float4(e[4], e[5], e[6], e[7]);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
+          }
+          if (++as == 2) { as = 0; aph ^= 1; }
+        }
+#pragma unroll
+        for (int c0 = 0; c0 < COLS; c0 += 8) {
+          uint8_t* blk = slot + which * 1024;
+          which ^= 1;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          uint8_t* mine = blk + lane * 32;
+          *reinterpret_cast<float4*>(mine + ((0 ^ ((lane >> 2) & 1)) << 4)) =
+              make_float4(__frcp_rn(den[c0]), __frcp_rn(den[c0 + 1]), __frcp_rn(den[c0 + 2]), __frcp_rn(den[c0 + 3]));
+          *reinterpret_cast<float4*>(mine + ((1 ^ ((lane >> 2) & 1)) << 4)) =
+              make_float4(__frcp_rn(den[c0 + 4]), __frcp_rn(den[c0 + 5]), __frcp_rn(den[c0 + 6]), __frcp_rn(den[c0 + 7]));
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) tma_store_3d(&map_al, blk, col0 + c0, it * RM + q * 32, b);
+        }
       } else {
         // ---- the GPT-2 example's attention weights: 12 head sub-tiles to build den = sum_h exp(s_h / N) in registers (head
         // order, like `!sum`), then the 12 heads again: p = exp(s_h / N) / den, 32 x 8 blocks through the bulk-copy engine

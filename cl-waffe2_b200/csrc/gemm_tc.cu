@@ -1663,6 +1663,49 @@ int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor,
   return post_launch("wf2cu_attn_heads_softmax");
 }
 
+// One-pass form of the above for wf2cu_attn_fused: E[b,h,i,j] = exp(s_h / divisor) (un-normalised) and R[b,i,j] = RN(1 / sum_h E).
+// E: dense (B H N N), R: dense (B N N), both 16-byte aligned.  Returns 0 or a wf2cu status.
+int attn_scores_onepass(const float* qkv, int64_t batch, int64_t seq, float divisor, float* E, float* R) {
+  if (!tensor_map_encoder()) return WF2CU_ERR_CUDA;
+  const int B = (int)batch, N = (int)seq;
+  static bool attr_set = false;
+  const int bytes = raw_smem(RawAttnJob1::kEpiWarps, RawAttnJob1::kEpiBytes);
+  if (!attr_set) {
+    WF2_CUDA(cudaFuncSetAttribute(gemm_raw_kernel<RawAttnJob1, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    attr_set = true;
+  }
+  CUtensorMap mq, mk, me, mr;
+  {
+    cuuint32_t boxq[3] = {RK, RM, 1}, boxk[3] = {RK, RN, 1}, estr[4] = {1, 1, 1, 1};
+    cuuint64_t dims[3] = {(cuuint64_t)(3 * RA_E), (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)(3 * RA_E) * 4, (cuuint64_t)N * 3 * RA_E * 4};
+    cuuint64_t pd[4] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)RA_H, (cuuint64_t)B};
+    cuuint64_t ps[3] = {(cuuint64_t)N * 4, (cuuint64_t)N * N * 4, (cuuint64_t)RA_H * N * N * 4};
+    cuuint32_t pb[4] = {8, 32, 1, 1};
+    cuuint64_t rd[3] = {(cuuint64_t)N, (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t rs[2] = {(cuuint64_t)N * 4, (cuuint64_t)N * N * 4};
+    cuuint32_t rb[3] = {8, 32, 1};
+    CUresult r[4];
+    r[0] = g_encode(&mq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qkv, dims, strides, boxq, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    r[1] = g_encode(&mk, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)qkv, dims, strides, boxk, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    r[2] = g_encode(&me, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)E, pd, ps, pb, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    r[3] = g_encode(&mr, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)R, rd, rs, rb, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    for (int i = 0; i < 4; ++i)
+      if (r[i] != CUDA_SUCCESS) return set_error(WF2CU_ERR_CUDA, "cuTensorMapEncodeTiled(attention, one pass, map %d) failed (%d)", i, (int)r[i]);
+  }
+  RawAttnJob1 job{RawAttnArgs{B, N, (N + RM - 1) / RM, (N + RN - 1) / RN, (float)(1.4426950408889634 / (double)divisor), 0, 0}};
+  const int items = job.a.B * job.a.tiles_i * job.a.tiles_j, sms = S().sm_count;
+  const int grid = items < sms ? items : sms;
+  // map slots: A = Q, A-lo slot = R (store), B = K, B-lo slot = K (unused), C = E (store)
+  WF2_CUDA(launch_pdl(gemm_raw_kernel<RawAttnJob1, true, true, true>, dim3(grid), dim3(raw_threads(RawAttnJob1::kEpiWarps, true)), bytes,
+                      S().stream, mq, mr, mk, mk, me, job));
+  return post_launch("wf2cu_attn_fused(scores)");
+}
+
 // returns 1 when it handled the problem, 0 when it declines, <0 = -(error code)
 int gemm_tc_fused_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A, int64_t lda, const float* B, int64_t ldb,
                       float* C, int64_t ldc, int64_t batch, int64_t sa, int64_t sb, int64_t sc, const float* bias, int act,

@@ -149,5 +149,7 @@ EncodeTiledFn tensor_map_encoder();
 float* tc_workspace(size_t bytes);
 // the GPT-2 example's attention weights on the raw-operand main loop (gemm_raw.cuh, launched from gemm_tc.cu); 0 or a wf2cu status
 int attn_scores_raw(const float* qkv, int64_t batch, int64_t seq, float divisor, float* P);
+// one pass: un-normalised exponentials E (B H N N) and reciprocal denominators R (B N N) for wf2cu_attn_fused
+int attn_scores_onepass(const float* qkv, int64_t batch, int64_t seq, float divisor, float* E, float* R);
 
 }  // namespace wf2

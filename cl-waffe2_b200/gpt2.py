@@ -111,6 +111,7 @@ def merge_heads(x: CUDATensor) -> CUDATensor:
 
 
 FUSE_ATTENTION = True
+ONE_CALL_ATTENTION = True   # wf2cu_attn_fused: one pass over the heads, the weights never leave the library's workspace normalised
 
 
 def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
@@ -122,8 +123,18 @@ def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
         lib = _lib.load()
         B, N, E3 = qkv.shape
         E = E3 // 3
-        w = make_tensor([B, n_head, N, N])
         off = qkv.lower().offset
+        if ONE_CALL_ATTENTION:
+            out = make_tensor([B, N, E])
+            if EMIT_PLANES:                                  # the output projection is issued next
+                _lib.check(lib.wf2cu_emit_operand_planes(1))
+            rc = lib.wf2cu_attn_fused(qkv.vec.ptr, off, B, N, n_head, E // n_head, float(N), out.vec.ptr, out.lower().offset)
+            if rc == 0:
+                return out
+            if rc != 3:
+                _lib.check(rc)
+            _lib.check(lib.wf2cu_emit_operand_planes(0))
+        w = make_tensor([B, n_head, N, N])
         rc = lib.wf2cu_attn_heads_softmax(qkv.vec.ptr, off, B, N, n_head, E // n_head, float(N), w.vec.ptr, w.lower().offset)
         if rc == 0:
             out = make_tensor([B, N, E])

@@ -132,6 +132,8 @@ The VM wraps any error with the instruction context (`source/vm/vm.lisp:230-256`
 			    (divisor :float) (p :pointer) (p-off :int64)))
 (defwf2 attn-pv ((p :pointer) (p-off :int64) (qkv :pointer) (qkv-off :int64) (batch :int64) (seq :int64) (n-head :int64)
 		 (head-dim :int64) (out :pointer) (out-off :int64)))
+(defwf2 attn-fused ((qkv :pointer) (qkv-off :int64) (batch :int64) (seq :int64) (n-head :int64) (head-dim :int64)
+		    (divisor :float) (out :pointer) (out-off :int64)))
 (defwf2 layernorm ((x :pointer) (x-off :int64) (g :pointer) (g-off :int64) (b :pointer) (b-off :int64)
 		   (out :pointer) (out-off :int64) (rows :int64) (cols :int64) (eps :float)))
 ;; unfold / Conv2D / pooling (csrc/conv.cu)

@@ -634,8 +634,12 @@ pre-pass; ignored when the very next launch is not that product)."
 ;; (batch N 3*n-head*head-dim) result of the c_attn projection.  The library takes n-head 12, head-dim 64, N a multiple of 128
 ;; (the example's 124M configuration) and answers UNSUPPORTED otherwise, which `defwf2` signals as `cuda-backend-error`: call
 ;; the example's own SelfAttention then.  Forward only, like CUDALayerNormNode.
-(define-op (CUDASelfAttentionNode (self n-head)
+;; KEEP-PROBABILITIES nil (the default): one call, wf2cu_attn_fused — the weights only ever exist un-normalised in a workspace of the
+;; library (one pass over the heads, half the Q K^T work), the result is bit-identical.  t: the two launches above, with the
+;; (batch head N N) weights kept in the node's PROBABILITIES slot for inspection.
+(define-op (CUDASelfAttentionNode (self n-head &optional keep-probabilities)
 	    :slots ((n-head :initform 12 :reader n-head-of)
+		    (keep-probabilities :initform nil :reader keep-probabilities-of)
 		    (probabilities :initform nil :accessor probabilities-of))
 	    :where (X[batch n three-e] Out[batch n e] -> Out[batch n e])
 	    :forward ((self x out)
@@ -644,28 +648,35 @@ pre-pass; ignored when the very next launch is not that product)."
 			     (e     (observe (third (shape out))))
 			     (heads (n-head-of self))
 			     (p     (probabilities-of self)))
-			(unless (and p (equal (shape p) (list batch heads n n)))
-			  (setf p (make-tensor (list batch heads n n) :dtype (dtype x) :order (order x))
-				(probabilities-of self) p))
-			(attn-heads-softmax (device-vec-ptr (tensor-vec x)) (tensor-initial-offset x) batch n heads (/ e heads)
-					    (coerce n 'single-float)
-					    (device-vec-ptr (tensor-vec p)) (tensor-initial-offset p))
-			(attn-pv (device-vec-ptr (tensor-vec p)) (tensor-initial-offset p)
-				 (device-vec-ptr (tensor-vec x)) (tensor-initial-offset x) batch n heads (/ e heads)
-				 (device-vec-ptr (tensor-vec out)) (tensor-initial-offset out))
+			(cond
+			  ((not (keep-probabilities-of self))
+			   (attn-fused (device-vec-ptr (tensor-vec x)) (tensor-initial-offset x) batch n heads (/ e heads)
+				       (coerce n 'single-float)
+				       (device-vec-ptr (tensor-vec out)) (tensor-initial-offset out)))
+			  (t
+			   (unless (and p (equal (shape p) (list batch heads n n)))
+			     (setf p (make-tensor (list batch heads n n) :dtype (dtype x) :order (order x))
+				   (probabilities-of self) p))
+			   (attn-heads-softmax (device-vec-ptr (tensor-vec x)) (tensor-initial-offset x) batch n heads (/ e heads)
+					       (coerce n 'single-float)
+					       (device-vec-ptr (tensor-vec p)) (tensor-initial-offset p))
+			   (attn-pv (device-vec-ptr (tensor-vec p)) (tensor-initial-offset p)
+				    (device-vec-ptr (tensor-vec x)) (tensor-initial-offset x) batch n heads (/ e heads)
+				    (device-vec-ptr (tensor-vec out)) (tensor-initial-offset out))))
 			out))
 	    :backward ((self dout)
 		       (declare (ignore dout))
 		       (error "CUDASelfAttentionNode: forward only; differentiate SelfAttention instead")))
-  (setf (slot-value self 'n-head) n-head))
+  (setf (slot-value self 'n-head) n-head
+	(slot-value self 'keep-probabilities) keep-probabilities))
 
-(defun cuda-self-attention (x &key (n-head 12) feeds-matmul)
+(defun cuda-self-attention (x &key (n-head 12) feeds-matmul keep-probabilities)
   "Drop-in for the first value of `(SelfAttention x nil)` on a dense (batch N 3E) CUDATensor.
 FEEDS-MATMUL: as in `cuda-layer-norm` (the output projection follows; the request reaches the second of the two launches
 because the first one is not a producer and leaves the one-shot flag alone)."
   (when feeds-matmul (emit-operand-planes 1))
   (let ((e (/ (car (last (shape x))) 3)))
-    (call (CUDASelfAttentionNode n-head)
+    (call (CUDASelfAttentionNode n-head keep-probabilities)
 	  (->contiguous x)
 	  (make-input (list (first (shape x)) (second (shape x)) e) nil :dtype (dtype x) :order (order x)))))
 

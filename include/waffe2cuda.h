@@ -335,6 +335,15 @@ int  wf2cu_attn_heads_softmax(const void* qkv, int64_t qkv_off, int64_t batch, i
 int  wf2cu_attn_pv(const void* p, int64_t p_off, const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head,
                    int64_t head_dim, void* out, int64_t out_off);
 
+/* The same block as ONE call when the attention weights themselves are not wanted (the example's `SelfAttention` returns only the
+ * merged-heads result): the score kernel makes ONE pass over the 12 heads, writes the UN-normalised e = exp(s / divisor) and the
+ * reciprocal denominators r[b,i,j] = RN(1 / sum_h e) into a workspace of the library, and the P.V kernel forms p = RN(e r) — the very
+ * product wf2cu_attn_heads_softmax forms — on the way into tensor memory.  Half the Q.K^T work and one exp per element instead of
+ * two; out is bit-identical to wf2cu_attn_heads_softmax + wf2cu_attn_pv.  Workspace: (batch n_head seq seq) + (batch seq seq) floats,
+ * grow-only, allocated on first use (not inside wf2cu_graph_begin/end: run once first).  Same shape limits and status codes. */
+int  wf2cu_attn_fused(const void* qkv, int64_t qkv_off, int64_t batch, int64_t seq, int64_t n_head, int64_t head_dim, float divisor,
+                      void* out, int64_t out_off);
+
 /* ===================== unfold / Conv2D / pooling ===================== */
 /* Geometry of one unfold, the argument list of `waffe2_im2col_s_column` / `waffe2_col2im_s_column`
  * (`cl-waffe2-simd/kernels/im2col.c:63-80`; CFFI `cl-waffe2-simd/api.lisp:27-61`; slots of

@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""The GPT-2 example's attention block at B = 8, N = 1024: the two launches (weights written normalised) against wf2cu_attn_fused."""
+import ctypes as C, importlib, os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+wf = importlib.import_module("cl-waffe2_b200"); wf.init(0)
+lib = wf._lib.load(); chk = wf._lib.check
+rng = np.random.default_rng(0)
+B, N, H, D = 8, 1024, 12, 64
+qkv = wf.from_numpy(rng.normal(0, 1, size=(B, N, 3 * H * D)).astype(np.float32))
+P = wf.make_tensor((B, H, N, N)); out = wf.make_tensor((B, N, H * D)); out2 = wf.make_tensor((B, N, H * D))
+def two():
+    chk(lib.wf2cu_attn_heads_softmax(qkv.vec.ptr, 0, B, N, H, D, float(N), P.vec.ptr, 0))
+    chk(lib.wf2cu_attn_pv(P.vec.ptr, 0, qkv.vec.ptr, 0, B, N, H, D, out.vec.ptr, 0))
+def one(): chk(lib.wf2cu_attn_fused(qkv.vec.ptr, 0, B, N, H, D, float(N), out2.vec.ptr, 0))
+def timed(f, n=4):
+    f(); f(); wf.ops.sync(); best = 1e9
+    for _ in range(5):
+        chk(lib.wf2cu_timer_start())
+        for _ in range(n): f()
+        ms = C.c_float(); chk(lib.wf2cu_timer_stop(C.byref(ms))); best = min(best, ms.value / n)
+    return best * 1e3
+t2, t1 = timed(two), timed(one)
+print(f"two launches {t2:.1f} us   wf2cu_attn_fused {t1:.1f} us   identical {bool(np.array_equal(out.to_numpy(), out2.to_numpy()))}")

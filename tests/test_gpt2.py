@@ -203,3 +203,32 @@ def test_attention_divisor_not_a_power_of_two_and_unsupported_shapes(gpu):
     assert lib.wf2cu_attn_heads_softmax(y.vec.ptr, 0, 1, 100, 4, 16, 100.0, q.vec.ptr, 0) == 3
     assert lib.wf2cu_attn_pv(q.vec.ptr, 0, y.vec.ptr, 0, 1, 100, 4, 16, y.vec.ptr, 0) == 3
     assert lib.wf2cu_attn_heads_softmax(x.vec.ptr, 0, B, 200, H, D, 200.0, p_dev.vec.ptr, 0) == 3     # seq not a multiple of 128
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,N", [(1, 128), (2, 384), (3, 1024)])
+def test_one_call_attention_equals_the_two_launches(gpu, B, N):
+    """wf2cu_attn_fused (one pass over the heads: un-normalised exponentials + reciprocal denominators in the library's workspace,
+    p = RN(e r) formed by the P.V kernel) against wf2cu_attn_heads_softmax + wf2cu_attn_pv: the same products in the same order,
+    so the merged-heads result is bit-identical; and both against the oracle's SelfAttention."""
+    import ctypes as C
+    lib = gpu._lib.load()
+    H, D = 12, 64
+    rng = np.random.default_rng(100 + N)
+    qkv = rng.normal(0, 1.0, size=(B, N, 3 * H * D)).astype(np.float32)
+    g = gpu.from_numpy(qkv)
+    P = gpu.make_tensor((B, H, N, N))
+    two = gpu.make_tensor((B, N, H * D))
+    one = gpu.make_tensor((B, N, H * D))
+    gpu._lib.check(lib.wf2cu_attn_heads_softmax(g.vec.ptr, 0, B, N, H, D, float(N), P.vec.ptr, 0))
+    gpu._lib.check(lib.wf2cu_attn_pv(P.vec.ptr, 0, g.vec.ptr, 0, B, N, H, D, two.vec.ptr, 0))
+    for _ in range(2):                                   # twice: the workspace is reused, nothing may depend on its old contents
+        gpu._lib.check(lib.wf2cu_attn_fused(g.vec.ptr, 0, B, N, H, D, float(N), one.vec.ptr, 0))
+    a, b = one.to_numpy(), two.to_numpy()
+    np.testing.assert_array_equal(a, b)
+    # fp64 restatement of examples/gpt-2/utils.lisp:222-244 (scores / N, softmax over the HEADS axis, no mask)
+    x = qkv.astype(np.float64).reshape(B, N, 3, H, D)
+    q, k, v = (np.transpose(x[:, :, i], (0, 2, 1, 3)) for i in range(3))
+    e = np.exp(q @ np.swapaxes(k, -1, -2) / N)
+    want = np.transpose((e / e.sum(axis=1, keepdims=True)) @ v, (0, 2, 1, 3)).reshape(B, N, H * D)
+    assert np.abs(a - want).max() <= 2e-5 * np.abs(want).max()
