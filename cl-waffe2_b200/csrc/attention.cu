@@ -128,7 +128,7 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
         const int bh = t / a.tiles_m, mt = t % a.tiles_m;
@@ -145,7 +145,7 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       int s = 0; uint32_t ph = 0;
       int as = 0; uint32_t aph = 0, n = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {

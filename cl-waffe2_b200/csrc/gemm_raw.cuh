@@ -168,7 +168,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t tx_bytes = R_ATILE + R_BTILE + (A_RAW ? 0 : R_ATILE) + (B_RAW ? 0 : R_BTILE);
       int s = 0; uint32_t ph = 0;
       for (int w = blockIdx.x; w < items; w += gridDim.x) {
@@ -189,7 +189,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    if (elect_one()) {
       int s = 0; uint32_t ph = 0;
       int as = 0; uint32_t aph = 0;
       for (int w = blockIdx.x; w < items; w += gridDim.x) {
@@ -259,6 +259,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   } else {
     // ===================== epilogue =====================
     const int ew = warp - 2 - NCONV, q = warp & 3, cg = ew >> 2;   // TMEM lane quarter (= warp % 4, fixed by the hardware), column group
+    const bool leader = elect_one();                               // the lane that issues (and waits for) this warp's bulk stores
     uint8_t* slot = epi_base + ew * JOB::kEpiBytes;
     uint32_t which = 0;
     int as = 0; uint32_t aph = 0;
@@ -314,7 +315,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             tc_ld8(tbase + c0, v);
             uint8_t* blk = slot + which * 1024;
             which ^= 1;
-            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
             tc_ld_wait();
             if (c0 + 8 >= COLS) {                                   // the accumulator is in registers now
               tc_fence_before();
@@ -334,7 +335,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             *reinterpret_cast<float4*>(mine + ((1 ^ ((lane >> 2) & 1)) << 4)) = make_float4(e[4], e[5], e[6], e[7]);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            if (lane == 0) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
+            if (leader) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
           }
           if (++as == 2) { as = 0; aph ^= 1; }
         }
@@ -342,7 +343,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         for (int c0 = 0; c0 < COLS; c0 += 8) {
           uint8_t* blk = slot + which * 1024;
           which ^= 1;
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
           uint8_t* mine = blk + lane * 32;
           *reinterpret_cast<float4*>(mine + ((0 ^ ((lane >> 2) & 1)) << 4)) =
@@ -351,7 +352,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
               make_float4(__frcp_rn(den[c0 + 4]), __frcp_rn(den[c0 + 5]), __frcp_rn(den[c0 + 6]), __frcp_rn(den[c0 + 7]));
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();
-          if (lane == 0) tma_store_3d(&map_al, blk, col0 + c0, it * RM + q * 32, b);
+          if (leader) tma_store_3d(&map_al, blk, col0 + c0, it * RM + q * 32, b);
         }
       } else {
         // ---- the GPT-2 example's attention weights: 12 head sub-tiles to build den = sum_h exp(s_h / N) in registers (head
@@ -395,7 +396,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
               tc_ld8(tbase + c0, v);
               uint8_t* blk = slot + which * 1024;
               which ^= 1;
-              if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+              if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
               tc_ld_wait();
               if (c0 + 8 >= COLS) {                                   // the accumulator is in registers now
                 tc_fence_before();
@@ -413,14 +414,14 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
               *reinterpret_cast<float4*>(mine + ((1 ^ ((lane >> 2) & 1)) << 4)) = make_float4(p[4], p[5], p[6], p[7]);
               asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
               __syncwarp();
-              if (lane == 0 && !(a.dbg & 1)) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
+              if (leader && !(a.dbg & 1)) tma_store_4d(&map_c, blk, col0 + c0, it * RM + q * 32, h, b);
             }
           }
           if (++as == 2) { as = 0; aph ^= 1; }
         }
       }
     }
-    if (JOB::kEpiBytes > 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (JOB::kEpiBytes > 0 && (leader || lane == 0)) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();

@@ -351,7 +351,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t tx_bytes = a.passes != 1 ? STAGE_BYTES : (A_PLANE_BYTES + B_PLANE_BYTES);
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -374,7 +374,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    if (elect_one()) {
       int s = 0; uint32_t ph = 0;
       int as = 0; uint32_t aph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -521,7 +521,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t tx_bytes = a.passes != 1 ? T2_STAGE_BYTES : T2_PLANE + B_PLANE;
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -543,7 +543,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       int s = 0; uint32_t ph = 0;
       uint32_t aph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -825,7 +825,7 @@ __device__ __forceinline__ void fused_mainloop(const FTile<FM>& ta_, const FTile
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core
         tc_fence_before();
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0) {   // (elect_one() here removes the per-MMA ELECT loops but measured SLOWER: C4 step 90.4 -> 92.3 us)
           tc_fence_after();
           const uint32_t sa = smem_u32(st);
           const uint64_t dah = make_desc_sw128(sa), dal = make_desc_sw128(sa + F_A_PLANE);

@@ -93,7 +93,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t tx_bytes = a.passes != 1 ? P2_STAGE : P2_APLANE + P2_BHALF;
       const uint32_t full0 = mapa_u32(smem_u32(&full[0]), 0);      // the leader's full[0] in the cluster window
       int s = 0; uint32_t ph = 0;
@@ -121,7 +121,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    if (rank == 0 && elect_one()) {
       int s = 0; uint32_t ph = 0;
       uint32_t aph = 0;
       for (int t = pair; t < total_tiles; t += npairs) {

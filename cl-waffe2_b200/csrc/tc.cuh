@@ -46,6 +46,15 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void*
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
+// One lane of a converged warp, chosen by the hardware.  Unlike `lane == 0` the compiler KNOWS that exactly one lane takes the
+// branch, so the warp-uniform instructions inside it (UTCHMMA, UTCBAR, UTMALDG take their operands from uniform registers) are
+// emitted once; under `if (lane == 0)` each of them is wrapped in an ELECT / PLOP3 / BRA.U.ANY loop over the active lanes — five
+// extra dependent instructions per tcgen05.mma, which bounded the P.V kernel (44-cycle MMAs): profiles/r03c ncu source page.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
