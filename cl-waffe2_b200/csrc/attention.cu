@@ -99,7 +99,7 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
                const __grid_constant__ CUtensorMap map_vl, const __grid_constant__ CUtensorMap map_r, const __grid_constant__ PvArgs a) {
   constexpr int P_NS = p_ns(NORM), P_STAGE = p_stage(NORM);          // shadow the two-launch path's constants
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned, and still known to be SHARED (LDS / STS, not generic LD / ST)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P_NS * P_STAGE);
   uint64_t* full = bars;                   // [P_NS] TMA -> converters / MMA
   uint64_t* conv = bars + P_NS;            // [P_NS] converters -> MMA (4 arrivals, one per warp)

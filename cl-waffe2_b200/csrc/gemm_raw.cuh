@@ -136,7 +136,7 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   constexpr int NCONV = CONVERT ? R_CONV_WARPS : 0;
   constexpr int EW = JOB::kEpiWarps, CG = EW / 4, COLS = RN / CG;    // epilogue warps, column groups, columns per warp
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned, and still known to be SHARED (LDS / STS, not generic LD / ST)
   uint8_t* epi_base = smem + R_NS * R_STAGE;
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_base + EW * JOB::kEpiBytes);
   uint64_t* full = bars;                     // [R_NS] TMA -> converters, MMA

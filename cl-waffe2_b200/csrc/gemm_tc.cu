@@ -324,7 +324,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant
                const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte aligned tiles
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned, and still known to be SHARED (LDS / STS, not generic LD / ST)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + EPI_BYTES);
   uint64_t* full = bars;                    // [STAGES]  TMA -> MMA
   uint64_t* empty = bars + STAGES;          // [STAGES]  MMA -> TMA
@@ -494,7 +494,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   constexpr int T2N = NB, T2_STAGES = NST, B_PLANE = t2_bplane(NB), T2_STAGE_BYTES = t2_stage_bytes(NB);
   constexpr uint32_t kIdesc = idesc_tf32(NB), kIdescB = idesc_bf16_mn(128, NB);
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned, and still known to be SHARED (LDS / STS, not generic LD / ST)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_STAGES * T2_STAGE_BYTES + EPI_BYTES);
   uint64_t* full = bars;                       // [T2_STAGES]
   uint64_t* empty = bars + T2_STAGES;          // [T2_STAGES]
@@ -846,7 +846,7 @@ __device__ __forceinline__ void fused_mainloop(const FTile<FM>& ta_, const FTile
 
 __global__ void __launch_bounds__(256, 2) gemm_tc_fused_kernel(const __grid_constant__ FusedGemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned, and still known to be SHARED (LDS / STS, not generic LD / ST)
   uint64_t* freed = reinterpret_cast<uint64_t*>(smem + F_STAGES * F_STAGE);   // [2] MMAs that read stage s have retired
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(freed + F_STAGES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -63,7 +63,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
                   const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned, and still known to be SHARED (LDS / STS, not generic LD / ST)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P2_STAGES * P2_STAGE + EPI_BYTES);
   uint64_t* full = bars;                       // [P2_STAGES]  the leader's are used: its arrival + both CTAs' bytes
   uint64_t* empty = bars + P2_STAGES;          // [P2_STAGES]  per CTA, multicast commit
