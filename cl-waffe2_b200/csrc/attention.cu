@@ -18,7 +18,7 @@
 //       one (i, j), so the first design kept all 12 score tiles of a (128 x 32) tile in TMEM: 144 us with ONE truncated TF32
 //       pass (error 3e-4 on P for N(0, 2) inputs: not acceptable for a library kernel), 271 us with the compensated three —
 //       whether the lo planes came from global memory, from converter warps, or the Q operand lived in tensor memory (294 us).
-//       scripts/micro/mma_rate_test.cu: a kind::tf32 MMA with M = 128 costs max(45, N / 2) cycles, so the 288 N = 32 MMAs of a
+//       scripts/micro/mma_rate_test.cu (first version; its 45-cycle floor was the ELECT loop of the issue path): a kind::tf32 MMA with M = 128 costs max(45, N / 2) cycles, so the 288 N = 32 MMAs of a
 //       tile ran at a third of the tensor rate and the 16-warp exp/divide epilogue could not hide behind them.  With N = 256
 //       per MMA the products of BOTH passes together take 147 us of main loop; the whole kernel runs in 194 us.
 //   wf2cu_attn_pv : out[b,i,h*64:(h+1)*64] = sum_j P[b,h,i,j] V_h[j,:], error-compensated 3xTF32 (as MatmulNode), written

@@ -14,7 +14,8 @@
 // two 256-column accumulators in TMEM so the epilogue of a tile overlaps the main loop of the next:
 //   warp 0      TMA producer       warp 1      MMA issuer (6 x tcgen05.mma 128x256x8 per k-block)
 //   warps 2-5   converters         warps 6-..  epilogue (4 x CG warps: TMEM lane quarter x column group)
-// Measured on B200 (scripts/micro/mma_rate_test.cu): a kind::tf32 MMA with M = 128 costs max(45, N / 2) cycles — N = 256 runs
+// Measured on B200 (scripts/micro/mma_rate_test.cu; see the correction in DESIGN.md 3.5: the 45 was the issue loop of `lane == 0`,
+// with A in shared memory the floor is ~40 cycles, with A in tensor memory N / 2 all the way down): a kind::tf32 MMA with M = 128 costs max(45, N / 2) cycles — N = 256 runs
 // at the nominal rate (128 cycles), anything below N = 96 pays the 45-cycle floor — so tiles are as wide as the instruction
 // allows.  That is also why the GPT-2 example's attention scores run through this main loop (N = 256 keys per MMA) instead of
 // keeping all 12 heads of a narrow tile in TMEM (N = 32 per MMA, 288 MMAs per 128 x 32 tile: 271 us per layer).
