@@ -307,13 +307,39 @@ __global__ void __launch_bounds__(256) allreduce_adam_ll_kernel(const __grid_con
         m = reinterpret_cast<const float4*>(a.m)[i]; v = reinterpret_cast<const float4*>(a.v)[i];
         p = reinterpret_cast<const float4*>(a.param)[i]; own = reinterpret_cast<const float4*>(a.grad)[i];
       }
-      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int r = 0; r < a.world && ok; ++r) {
-        float4 x = own;
-        if (r != a.rank) ok = wait_ll(ll_gstage(me, r, per32, j), e, x, abort_word);
-        if (r == 0) g = x;
-        else { g.x = __fadd_rn(g.x, x.x); g.y = __fadd_rn(g.y, x.y); g.z = __fadd_rn(g.z, x.z); g.w = __fadd_rn(g.w, x.w); }
+      // All peers' words are requested at once and the flags checked afterwards: polling peer after peer made phase B a chain of
+      // world - 1 dependent L2 round trips although the gradients arrive at about the same time.
+      float4 x[kMaxPeers];
+      uint32_t pending = 0;
+#pragma unroll
+      for (int r = 0; r < kMaxPeers; ++r)
+        if (r < a.world && r != a.rank) pending |= 1u << r;
+      {
+        const unsigned long long t0 = now_ns();
+        uint32_t spins = 0;
+        while (pending) {
+          uint4 wa[kMaxPeers], wb[kMaxPeers];
+#pragma unroll
+          for (int r = 0; r < kMaxPeers; ++r)
+            if (pending & (1u << r)) { const uint4* q = ll_gstage(me, r, per32, j); wa[r] = ld_ll(q); wb[r] = ld_ll(q + kLLWord1); }
+#pragma unroll
+          for (int r = 0; r < kMaxPeers; ++r)
+            if ((pending & (1u << r)) && wa[r].y == e && wa[r].w == e && wb[r].y == e && wb[r].w == e) {
+              x[r] = make_float4(__uint_as_float(wa[r].x), __uint_as_float(wa[r].z), __uint_as_float(wb[r].x), __uint_as_float(wb[r].z));
+              pending &= ~(1u << r);
+            }
+          if (pending && (++spins & 255u) == 0 && (ld_acquire_sys(abort_word) != 0 || now_ns() - t0 > kSpinLimitNs)) { ok = false; break; }
+          if (pending && spins > 64) __nanosleep(32);
+        }
       }
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < kMaxPeers; ++r)
+        if (r < a.world) {
+          const float4 xr = r == a.rank ? own : x[r];
+          if (r == 0) g = xr;
+          else { g.x = __fadd_rn(g.x, xr.x); g.y = __fadd_rn(g.y, xr.y); g.z = __fadd_rn(g.z, xr.z); g.w = __fadd_rn(g.w, xr.w); }
+        }
       if (!ok) break;
       if (a.gscale != 1.0f) { g.x = __fmul_rn(g.x, a.gscale); g.y = __fmul_rn(g.y, a.gscale); g.z = __fmul_rn(g.z, a.gscale); g.w = __fmul_rn(g.w, a.gscale); }
       p.x = adam_one(g.x, m.x, v.x, p.x, lr_t, omb1, omb2, a.eps);
@@ -497,7 +523,13 @@ int wf2cu_p2p_allreduce_adam_step(void* param, int64_t p_off, int64_t g_off, voi
     // LL (push) kernel: co-resident grid, every CTA pushes before it polls
     const int64_t n4ll = (n + 3) >> 2;
     int64_t g = (n4ll + 255) / 256;
-    int64_t capll = (int64_t)S().sm_count * 2;
+    // every CTA must be resident (they wait for each other's peers): never more CTAs than the device can hold at once
+    static int per_sm = 0;
+    if (!per_sm) {
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, allreduce_adam_ll_kernel, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+      if (per_sm > 2) per_sm = 2;
+    }
+    int64_t capll = (int64_t)S().sm_count * per_sm;
     if (capll > kLLMaxCtas) capll = kLLMaxCtas;
     if (g > capll) g = capll;
     if (p.ll_grid && p.ll_grid != g)
