@@ -13,6 +13,9 @@ def two():
     chk(lib.wf2cu_attn_heads_softmax(qkv.vec.ptr, 0, B, N, H, D, float(N), P.vec.ptr, 0))
     chk(lib.wf2cu_attn_pv(P.vec.ptr, 0, qkv.vec.ptr, 0, B, N, H, D, out.vec.ptr, 0))
 def one(): chk(lib.wf2cu_attn_fused(qkv.vec.ptr, 0, B, N, H, D, float(N), out2.vec.ptr, 0))
+if len(sys.argv) > 1 and sys.argv[1] == "one":            # the program ncu wraps: only the one-call form
+    for _ in range(3): one()
+    wf.ops.sync(); print("one-call form x 3"); sys.exit(0)
 def timed(f, n=4):
     f(); f(); wf.ops.sync(); best = 1e9
     for _ in range(5):

@@ -11,6 +11,7 @@
 #         benchnopdl       the sweep / fused chains / MLP with WF2CU_PDL=0 (A/B of programmatic dependent launch)
 #         launches         ncu launch list of `bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --fused 1 --no-cpu`
 #         ncu:<regex>:<script.py>[+arg...]   ncu --set full on kernels matching <regex> while running python <script.py> [args]
+#         ab:<script.py>[+arg...]   the script under the built library and under every cl-waffe2_b200/lib/variants/*.so, in one call
 #         ncutime:<script.py>  per-kernel device times of a script (ncu gpu__time_duration, cold-cache, serialised)
 #         py:<script.py>   run a python script, log -> gpurun_out/<tag>_<script>.log
 # Every task runs under its own timeout so that a protocol bug cannot hold the box.
@@ -36,6 +37,12 @@ for task in "$@"; do
               done
               timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29533 scripts/p2p_check.py 2>&1 | grep -v "^W\|^\*\*\*" | tail -$((n + 2)) | tee gpurun_out/${tag}_p2p_check_n${n}.log ;;
     flat)     for v in "" "WF2CU_FLAT_STAGES=3" "WF2CU_FLAT_STAGES=3 WF2CU_FLAT_PDL=2" "WF2CU_FLAT_STAGES=2" "WF2CU_FLAT_STAGES=2 WF2CU_FLAT_PDL=2" "WF2CU_FLAT_STAGES=3 WF2CU_FLAT_PDL=0" "WF2CU_FLAT_STAGES=2 WF2CU_FLAT_CTAS=3" "WF2CU_FLAT_STAGES=3"; do env $v timeout 120 python scripts/flat_variants.py 2>&1 | tail -1; done | tee gpurun_out/${tag}_flat_variants.log ;;
+    ab:*)     script=${task#ab:}; base=$(basename "${script%%+*}" .py)   # every lib/variants/*.so in turn (scripts/build_variant.sh), twice, same box
+              cp cl-waffe2_b200/lib/libwaffe2cuda.so /tmp/libwaffe2cuda_base.so
+              for rep in 1 2; do for v in /tmp/libwaffe2cuda_base.so cl-waffe2_b200/lib/variants/*.so; do
+                cp $v cl-waffe2_b200/lib/libwaffe2cuda.so; echo "== $(basename $v) rep $rep"; timeout 300 python ${script//+/ } 2>&1 | tail -${AB_TAIL:-2}
+              done; done | tee gpurun_out/${tag}_ab_${base}.log
+              cp /tmp/libwaffe2cuda_base.so cl-waffe2_b200/lib/libwaffe2cuda.so ;;
     benchref) timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "benchref rc=$?" ;;
     launches) cmd="python bench.py --steps 2 --warmup 1 --gemm 0 --gpt2 0 --cnn 0 --mlp 0 --no-cpu"
               timeout 300 $cmd > gpurun_out/${tag}_launches_plain.log 2>&1 &&
