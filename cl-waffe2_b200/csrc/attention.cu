@@ -254,6 +254,194 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
   }
 }
 
+// ------------------------------------------------------------------ P . V, six heads per CTA (wf2cu_attn_fused)
+// attn_pv_kernel<true> works on one head at a time, so the reciprocal-denominator tile R[b, i-tile, j-tile] — shared by the 12 heads —
+// is loaded again for every head: as many bytes through the TMA and the shared-memory pipe as E itself.  Here a CTA owns
+// (batch, 128 queries, SIX heads): k-blocks outside, heads inside, six 64-column accumulators in tensor memory (384 columns + the two
+// 64-column P operand buffers = 512), R loaded once per k-block into its own 2-slot ring and held in the converters' registers across the
+// six heads.  Per head the MMAs run in the same order as attn_pv_kernel (k-blocks ascending; lo.hi, hi.lo, hi.hi), so the result is
+// bit-identical to it.  B x tiles x 2 work items (128 at B = 8, N = 1024: one per CTA, the same 192 k-block steps as the busiest CTA before).
+constexpr int P6_G = 6, P6_NS = 6, P6_ACOL = P6_G * P_N;                 // TMEM: [0, 384) accumulators, [384, 512) P operand buffers
+constexpr int P6_RING = P6_NS * P_STAGE;                                 // E | V_hi | V_lo stages, then two R tiles
+constexpr int P6_SMEM = P6_RING + 2 * P_ATILE + 1024 + 256;
+
+__global__ void __launch_bounds__(P_THREADS, 1)
+attn_pv6_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant__ CUtensorMap map_vh,
+                const __grid_constant__ CUtensorMap map_vl, const __grid_constant__ CUtensorMap map_r, const __grid_constant__ PvArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* rbuf = smem + P6_RING;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rbuf + 2 * P_ATILE);
+  uint64_t* full = bars;                   // [P6_NS] TMA -> converters / MMA
+  uint64_t* conv = bars + P6_NS;           // [P6_NS] converters -> MMA (4 arrivals)
+  uint64_t* empty = bars + 2 * P6_NS;      // [P6_NS] MMA -> TMA
+  uint64_t* rfull = bars + 3 * P6_NS;      // [2] TMA -> converters
+  uint64_t* rempty = rfull + 2;            // [2] converters -> TMA (4 arrivals)
+  uint64_t* acc_full = rempty + 2;         // [1] MMA -> epilogue: all six accumulators of the item
+  uint64_t* acc_empty = acc_full + 1;      // [1] epilogue -> MMA (4 arrivals)
+  uint64_t* afree = acc_empty + 1;         // [2] MMA -> converters
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(afree + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = a.batch_heads / AH * a.tiles_m * (AH / P6_G);        // item = (b * tiles_m + mt) * 2 + head group
+  const int nkb = a.N / P_K;
+  pdl_prologue();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P6_NS; ++s) { mbar_init(&full[s], 1); mbar_init(&conv[s], 4); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&rfull[s], 1); mbar_init(&rempty[s], 4); mbar_init(&afree[s], 1); }
+    mbar_init(acc_full, 1); mbar_init(acc_empty, 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int s = 0; uint32_t ph = 0, rn = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int grp = t % (AH / P6_G), bm = t / (AH / P6_G), mt = bm % a.tiles_m, b = bm / a.tiles_m;
+        for (int kb = 0; kb < nkb; ++kb, ++rn) {
+          const uint32_t rs = rn & 1u;
+          mbar_wait(&rempty[rs], ((rn >> 1) & 1u) ^ 1u);
+          mbar_expect_tx(&rfull[rs], P_ATILE);
+          tma_load_3d(&map_r, &rfull[rs], rbuf + rs * P_ATILE, kb * P_K, mt * P_M, b);
+          for (int hh = 0; hh < P6_G; ++hh) {
+            const int bh = b * AH + grp * P6_G + hh;
+            mbar_wait(&empty[s], ph ^ 1);
+            uint8_t* st = smem + s * P_STAGE;
+            mbar_expect_tx(&full[s], P_STAGE);
+            tma_load_3d(&map_p, &full[s], st, kb * P_K, mt * P_M, bh);
+            tma_load_3d(&map_vh, &full[s], st + P_ATILE, kb * P_K, 0, bh);
+            tma_load_3d(&map_vl, &full[s], st + P_ATILE + P_BTILE, kb * P_K, 0, bh);
+            if (++s == P6_NS) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      int s = 0; uint32_t ph = 0, aph = 0, n = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        mbar_wait(acc_empty, aph ^ 1);
+        tc_fence_after();
+        for (int kb = 0; kb < nkb; ++kb) {
+          for (int hh = 0; hh < P6_G; ++hh, ++n) {
+            mbar_wait(&full[s], ph);
+            mbar_wait(&conv[s], ph);
+            tc_fence_after();
+            const uint32_t st = smem_u32(smem + s * P_STAGE);
+            const uint64_t dbh = make_desc_sw128(st + P_ATILE), dbl = make_desc_sw128(st + P_ATILE + P_BTILE);
+            const uint32_t d = tmem_base + (uint32_t)(hh * P_N);
+            const uint32_t ah = tmem_base + (uint32_t)(P6_ACOL + (n & 1u) * 64u), al = ah + 32u;
+#pragma unroll
+            for (int k = 0; k < P_K / UK; ++k) {
+              const uint64_t adv = (uint64_t)((k * UK * 4) >> 4);
+              tc_mma_tf32_ts(d, al + k * UK, dbh + adv, P_IDESC, (kb | k) != 0);
+              tc_mma_tf32_ts(d, ah + k * UK, dbl + adv, P_IDESC, 1);
+              tc_mma_tf32_ts(d, ah + k * UK, dbh + adv, P_IDESC, 1);
+            }
+            tc_commit(&empty[s]);
+            tc_commit(&afree[n & 1u]);
+            if (++s == P6_NS) { s = 0; ph ^= 1; }
+          }
+        }
+        tc_commit(acc_full);
+        aph ^= 1;
+      }
+    }
+  } else if (warp < 6) {
+    const int q = warp & 3, row = q * 32 + lane;
+    int s = 0; uint32_t ph = 0, n = 0, apar = 0, rn = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      for (int kb = 0; kb < nkb; ++kb, ++rn) {
+        const uint32_t rs = rn & 1u;
+        mbar_wait(&rfull[rs], (rn >> 1) & 1u);
+        float4 r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = *reinterpret_cast<const float4*>(rbuf + rs * P_ATILE + row * 128 + ((j ^ (row & 7)) << 4));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&rempty[rs]);                     // the tile lives in registers for the six heads
+        for (int hh = 0; hh < P6_G; ++hh, ++n) {
+          const uint32_t u = n & 1u;
+          mbar_wait(&full[s], ph);
+          const uint8_t* st = smem + s * P_STAGE;
+          uint32_t hi[32], lo[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 x = *reinterpret_cast<const float4*>(st + row * 128 + ((j ^ (row & 7)) << 4));
+            x.x = __fmul_rn(x.x, r[j].x); x.y = __fmul_rn(x.y, r[j].y); x.z = __fmul_rn(x.z, r[j].z); x.w = __fmul_rn(x.w, r[j].w);
+            hi[4 * j] = __float_as_uint(x.x); hi[4 * j + 1] = __float_as_uint(x.y); hi[4 * j + 2] = __float_as_uint(x.z); hi[4 * j + 3] = __float_as_uint(x.w);
+            lo[4 * j] = __float_as_uint(tf32_lo(x.x)); lo[4 * j + 1] = __float_as_uint(tf32_lo(x.y));
+            lo[4 * j + 2] = __float_as_uint(tf32_lo(x.z)); lo[4 * j + 3] = __float_as_uint(tf32_lo(x.w));
+          }
+          mbar_wait(&afree[u], ((apar >> u) & 1u) ^ 1u);
+          apar ^= 1u << u;
+          tc_fence_after();
+          const uint32_t aa = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(P6_ACOL + u * 64u);
+          tc_st32(aa, hi);
+          tc_st32(aa + 32, lo);
+          tc_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&conv[s]);
+          if (++s == P6_NS) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    uint32_t aph = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int grp = t % (AH / P6_G), bm = t / (AH / P6_G), mt = bm % a.tiles_m, b = bm / a.tiles_m;
+      mbar_wait(acc_full, aph);
+      aph ^= 1;
+      tc_fence_after();
+      const int row = mt * P_M + q * 32 + lane;
+#pragma unroll 1
+      for (int hh = 0; hh < P6_G; ++hh) {
+        const int h = grp * P6_G + hh;
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(hh * P_N);
+        uint32_t v0[32], v1[32];
+        tc_ld32(tbase, v0);
+        tc_ld32(tbase + 32, v1);
+        tc_ld_wait();
+        if (row < a.N) {
+          float4* crow = reinterpret_cast<float4*>(a.out + ((size_t)b * a.N + row) * AE + h * AD);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            crow[j] = make_float4(__uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            crow[8 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+          if (a.plane) {
+            float* prow = a.plane + ((size_t)b * a.N + row) * AE;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              plane_store4(prow, h * AD + 4 * j, __uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
+              plane_store4(prow, h * AD + 32 + 4 * j, __uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ host side
 static int encode(CUtensorMap* map, int rank, void* base, const cuuint64_t* dims, const cuuint64_t* strides, const cuuint32_t* box,
                   CUtensorMapSwizzle sw, CUtensorMapL2promotion l2, const char* what) {
@@ -322,13 +510,18 @@ static int launch_pv(float* P, const float* norm_r, const float* x, float* vh, f
   if (!attr_set) {
     WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(false)));
     WF2_CUDA(cudaFuncSetAttribute(attn_pv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(true)));
+    WF2_CUDA(cudaFuncSetAttribute(attn_pv6_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P6_SMEM));
     attr_set = true;
   }
   PvArgs args{O, N, N / P_M, BH, nullptr};
   if (S().emit_next) args.plane = planes_emit_begin(batch * seq, AE);     // wf2cu_emit_operand_planes: one-shot, may decline
   const int total = args.tiles_m * BH;
   const int grid = total < S().sm_count ? total : S().sm_count;
-  if (norm_r) WF2_CUDA(launch_pdl(attn_pv_kernel<true>, dim3(grid), dim3(P_THREADS), p_smem(true), S().stream, mp, mvh, mvl, mr, args));
+  static const bool six = []{ const char* e = getenv("WF2CU_ATTN_PV6"); return !e || atoi(e) != 0; }();   // 0: one head per work item (A/B)
+  if (norm_r && six) {
+    const int items = (int)batch * args.tiles_m * (AH / P6_G);
+    WF2_CUDA(launch_pdl(attn_pv6_kernel, dim3(items < S().sm_count ? items : S().sm_count), dim3(P_THREADS), P6_SMEM, S().stream, mp, mvh, mvl, mr, args));
+  } else if (norm_r) WF2_CUDA(launch_pdl(attn_pv_kernel<true>, dim3(grid), dim3(P_THREADS), p_smem(true), S().stream, mp, mvh, mvl, mr, args));
   else        WF2_CUDA(launch_pdl(attn_pv_kernel<false>, dim3(grid), dim3(P_THREADS), p_smem(false), S().stream, mp, mvh, mvl, mr, args));
   rc = post_launch(who);
   if (!rc && args.plane) planes_emit_publish(O, batch * seq, AE, AE, args.plane);
