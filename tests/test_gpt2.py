@@ -206,7 +206,7 @@ def test_attention_divisor_not_a_power_of_two_and_unsupported_shapes(gpu):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("B,N", [(1, 128), (2, 384), (3, 1024)])
+@pytest.mark.parametrize("B,N", [(1, 128), (2, 384), (3, 1024), (19, 512)])     # (19, 512): 152 six-head work items, so some CTAs take two
 def test_one_call_attention_equals_the_two_launches(gpu, B, N):
     """wf2cu_attn_fused (one pass over the heads: un-normalised exponentials + reciprocal denominators in the library's workspace,
     p = RN(e r) formed by the P.V kernel) against wf2cu_attn_heads_softmax + wf2cu_attn_pv: the same products in the same order,
