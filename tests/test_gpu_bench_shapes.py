@@ -534,7 +534,7 @@ def _launches(gpu) -> int:
 
 
 def test_producer_written_operand_planes_equal_the_prepass(gpu):
-    """wf2cu_emit_operand_planes: LayerNorm / P.V / a gelu projection also write the tensor-core operand plane of their result, and
+    """wf2cu_emit_operand_planes: LayerNorm / P.V also write the tensor-core operand plane of their result, and
     the MatmulNode issued next skips its pre-pass.  Same bits as the pre-pass writes (csrc/common.cuh plane_bits == split_bf), so the
     product — and a whole GPT-2 forward — is bit-identical with and without; the launch count shows the pre-passes are gone; a
     launch between producer and consumer, a different operand, or a transposed use must fall back to the pre-pass silently."""
