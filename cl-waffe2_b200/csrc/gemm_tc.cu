@@ -302,6 +302,35 @@ __device__ __forceinline__ void tc_store32_tma(const TcArgs& a, const CUtensorMa
   if (lane == 0) tma_store_3d(map_c, blk, col0, row0, b);
 }
 
+// The 256-row kernels (gemm_tc256_kernel, gemm_tc2sm_kernel) keep two 256-column accumulators — all of tensor memory — so their
+// epilogue is NOT overlapped with the next tile's main loop; at K = 768 (GPT-2's projections) four epilogue warps made it a third of
+// the tile.  They run EIGHT: two per TMEM lane quarter, half of the tile's columns each, one 4 KiB staging block per warp.
+constexpr int EPI8_WARPS = 8, EPI8_THREADS = 64 + 32 * EPI8_WARPS, EPI8_SLOT = EPI_BYTES / EPI8_WARPS;
+// one staging block per warp: the block is handed to the bulk-copy engine and reused once the engine has read it (the next
+// 32 columns' bias / activation arithmetic runs in between)
+__device__ __forceinline__ void tc_store32_tma1(const TcArgs& a, const CUtensorMap* map_c, uint8_t* blk, const uint32_t (&v)[32], int row0,
+                                                int col0, int b, int lane) {
+  if (col0 >= a.n || row0 >= a.m) return;                   // warp-uniform
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  __syncwarp();
+  uint8_t* mine = blk + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    *reinterpret_cast<float4*>(mine + ((j ^ (lane & 7)) << 4)) =
+        make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  if (lane == 0) tma_store_3d(map_c, blk, col0, row0, b);
+}
+// C cannot go through a tensor map (misaligned base or pitch): per-lane stores of the lane's own row
+__device__ __forceinline__ void tc_store32_rows(const TcArgs& a, float* cbase, const uint32_t (&v)[32], int row0, int col0, int lane) {
+  if (col0 >= a.n || row0 + lane >= a.m) return;
+  float* crow = cbase + (int64_t)(row0 + lane) * a.ldc;
+#pragma unroll
+  for (int j = 0; j < 32; ++j)
+    if (col0 + j < a.n) crow[col0 + j] = __uint_as_float(v[j]);
+}
+
 constexpr int kGroupM = 16;   // raster: 16 m-tiles x all n-tiles per group, m fastest (L2 reuse of B panels)
 
 __device__ __forceinline__ void tile_coords(int t, const TcArgs& a, int& b, int& mt, int& nt) {
@@ -487,7 +516,7 @@ static_assert(t2_smem_bytes(256, 3) <= 232448 && t2_stage_bytes(192) % 1024 == 0
 __host__ __device__ constexpr uint32_t idesc_tf32(int n) { return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24); }
 
 template <int NB, int NST>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(EPI8_THREADS, 1)
 gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
                   const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
@@ -508,7 +537,7 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   if (threadIdx.x == 0) {
     for (int s = 0; s < T2_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
-    mbar_init(acc_empty, 4);
+    mbar_init(acc_empty, EPI8_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -585,10 +614,9 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       }
     }
   } else {
-    const int q = warp & 3;
-    uint8_t* slot = smem + T2_STAGES * T2_STAGE_BYTES + (warp - 2) * EPI_SLOT;
-    float* stage = reinterpret_cast<float*>(slot);
-    uint32_t which = 0;
+    const int q = warp & 3, cgrp = (warp - 2) >> 2;       // TMEM lane quarter (fixed by warp % 4), column half of the tile
+    constexpr int NCH = T2N / 64;                         // 32-column chunks per warp: 4 (256-column tiles) or 3 (192)
+    uint8_t* blk = smem + T2_STAGES * T2_STAGE_BYTES + (warp - 2) * EPI8_SLOT;
     uint32_t aph = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int b, mt, nt;
@@ -598,23 +626,26 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       float* cbase = a.C + (int64_t)b * a.sc;
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256);
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256 + cgrp * (T2N / 2));
+        const int row0 = mt * T2M + h * 128 + q * 32;
         uint32_t v0[32], v1[32];
         tc_ld32(tbase, v0);
 #pragma unroll 1
-        for (int c = 0; c < T2N / 32; c += 2) {
+        for (int c = 0; c < NCH; c += 2) {
           tc_ld_wait();
-          tc_ld32(tbase + (c + 1) * 32, v1);
-          int col0 = nt * T2N + c * 32;
-          if (col0 < a.n) tc_epilogue32(a, v0, mt * T2M + h * 128 + q * 32, col0, lane);
-          if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, mt * T2M + h * 128 + q * 32, col0, b, lane);
-          else tc_store32(a, cbase, stage, v0, mt * T2M + h * 128 + q * 32, col0, lane);
-          tc_ld_wait();
-          if (c + 2 < T2N / 32) tc_ld32(tbase + (c + 2) * 32, v0);
-          col0 += 32;
-          if (col0 < a.n) tc_epilogue32(a, v1, mt * T2M + h * 128 + q * 32, col0, lane);
-          if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, mt * T2M + h * 128 + q * 32, col0, b, lane);
-          else tc_store32(a, cbase, stage, v1, mt * T2M + h * 128 + q * 32, col0, lane);
+          if (c + 1 < NCH) tc_ld32(tbase + (c + 1) * 32, v1);
+          int col0 = nt * T2N + cgrp * (T2N / 2) + c * 32;
+          if (col0 < a.n) tc_epilogue32(a, v0, row0, col0, lane);
+          if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v0, row0, col0, b, lane);
+          else tc_store32_rows(a, cbase, v0, row0, col0, lane);
+          if (c + 1 < NCH) {
+            tc_ld_wait();
+            if (c + 2 < NCH) tc_ld32(tbase + (c + 2) * 32, v0);
+            col0 += 32;
+            if (col0 < a.n) tc_epilogue32(a, v1, row0, col0, lane);
+            if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v1, row0, col0, b, lane);
+            else tc_store32_rows(a, cbase, v1, row0, col0, lane);
+          }
         }
       }
       tc_fence_before();
@@ -1246,10 +1277,13 @@ static int pick_tile256(int64_t kp, int64_t tiles128, int64_t tiles256, int64_t 
     //   8192x768x768: 72 / 66 / 62   8192x3072x768: 171 / 154 / 170   8192x768x3072: 262 / 202 / 193
     // CTA-pair kernel (512 x 256 pair tiles on sms / 2 pairs, r02r, scripts/gemm_pair_bench.py): 4096^3 446 (NT 420), 8192^3 3125,
     //   8192x2304x768 107, 8192x768x768 64, 8192x3072x768 144, 8192x768x3072 179, 2048^3 117
-    c128 = waves(tiles128) * 1.02 * (double)kp;
-    c256 = waves(tiles256) * (1.59 * (double)kp + 240.0);
-    c192 = waves(tiles192) * (1.33 * (double)kp + 180.0);
-    cpair = pair_waves(tiles_pair) * (1.50 * (double)kp + 240.0);
+    // refitted with eight epilogue warps in the 256-row kernels (r03R, scripts/gemm_gpt2_shapes.py with constant weights, kernel only):
+    //   8192x2304x768: 113 / 100 / 120 / 94 us (128x256 / 256x256 / 256x192 / pair)   8192x768x768: 66 / 57 / 52 / 54
+    //   8192x3072x768: 161 / 140 / 152 / 131   8192x768x3072: 252 / 189 / 177 / 164   4096^3: 603 / 463 / 570 / 428   2048^3: 88 / 112 / 103 / 111
+    c128 = waves(tiles128) * (1.02 * (double)kp + 40.0);
+    c256 = waves(tiles256) * (1.36 * (double)kp + 315.0);
+    c192 = waves(tiles192) * (1.26 * (double)kp + 271.0);
+    cpair = pair_waves(tiles_pair) * (1.09 * (double)kp + 449.0);
   } else {
     c128 = waves(tiles128) * 1.30 * (double)kp;
     c256 = waves(tiles256) * (2.00 * (double)kp + 450.0);
@@ -1396,7 +1430,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     }
     const int64_t pairs_max = S().sm_count / 2;
     const int grid = 2 * (int)(total < pairs_max ? total : pairs_max);
-    gemm_tc2sm_kernel<<<grid, GEMM_THREADS, P2_SMEM, S().stream>>>(mah, mal, mbh, mbl, mc, t);
+    gemm_tc2sm_kernel<<<grid, P2_THREADS, P2_SMEM, S().stream>>>(mah, mal, mbh, mbl, mc, t);
     rc = post_launch("wf2cu_gemm(tcgen05 CTA pair)");
     S().gemm_last_path = WF2CU_GEMM_PATH_TC_2SM;
     return rc ? -rc : 1;
@@ -1423,8 +1457,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     const int grid = (int)(total < S().sm_count ? total : S().sm_count);
-    if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, GEMM_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
-    else           gemm_tc256_kernel<192, 3><<<grid, GEMM_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
+    if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, EPI8_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
+    else           gemm_tc256_kernel<192, 3><<<grid, EPI8_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
     rc = post_launch(nb == 256 ? "wf2cu_gemm(tcgen05 256x256)" : "wf2cu_gemm(tcgen05 256x192)");
     S().gemm_last_path = nb == 256 ? WF2CU_GEMM_PATH_TC_256X256 : WF2CU_GEMM_PATH_TC_256X192;
     return rc ? -rc : 1;

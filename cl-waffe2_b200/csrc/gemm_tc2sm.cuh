@@ -13,7 +13,9 @@
 //                          both CTAs' bytes)
 //   warp 1 of the leader  MMA issuer: tcgen05.mma.cta_group::2 (M = 256, N = 256), tcgen05.commit ... multicast::cluster to
 //                          empty[s] / acc_full of both CTAs
-//   warps 2-5 of both     epilogue of the CTA's own 256 rows; acc_empty lives in the leader (8 arrivals, the peer's are remote)
+//   warps 2-9 of both     epilogue of the CTA's own 256 rows, two warps per TMEM lane quarter (128 of the 256 columns each): the two
+//                          accumulators fill tensor memory, so the epilogue is NOT overlapped with the next tile's main loop and at K = 768
+//                          (GPT-2's projections) it was a third of the tile; acc_empty lives in the leader (16 arrivals, the peer's remote)
 // Bounded waits (mbar_wait traps) turn a protocol bug into a CUDA error instead of a hung GPU.
 #pragma once
 
@@ -23,6 +25,7 @@ constexpr int P2_STAGES = 4;
 constexpr int P2_APLANE = 256 * T2K * 4;            // 16 KiB: 256 rows x 64 B
 constexpr int P2_BHALF = 128 * T2K * 4;             // 8 KiB: this CTA's half of the 256 B rows
 constexpr int P2_STAGE = 2 * P2_APLANE + 2 * P2_BHALF;   // A_hi A_lo B_hi B_lo = 48 KiB
+constexpr int P2_EPI_WARPS = EPI8_WARPS, P2_THREADS = EPI8_THREADS, P2_EPI_SLOT = EPI8_SLOT;
 constexpr int P2_SMEM = P2_STAGES * P2_STAGE + 1024 + EPI_BYTES + 256;
 static_assert(P2_SMEM <= 232448 && P2_STAGE % 1024 == 0, "shared-memory budget");
 constexpr uint32_t kIdescTf32P2 = idesc_tf32_mn(256, 256), kIdescBf16P2 = idesc_bf16_mn(256, 256);
@@ -58,7 +61,7 @@ __device__ __forceinline__ void tc_mma_bf16_2sm(uint32_t tmem_d, uint64_t desc_a
 }
 
 // a.tiles_m counts 512-row pair tiles, a.tiles_n 256-column tiles, a.nkb k-blocks of 16; grid = 2 x pairs (even)
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P2_THREADS, 1)
 gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
                   const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ TcArgs a) {
@@ -68,7 +71,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   uint64_t* full = bars;                       // [P2_STAGES]  the leader's are used: its arrival + both CTAs' bytes
   uint64_t* empty = bars + P2_STAGES;          // [P2_STAGES]  per CTA, multicast commit
   uint64_t* acc_full = bars + 2 * P2_STAGES;   // [1]          per CTA, multicast commit
-  uint64_t* acc_empty = acc_full + 1;          // [1]          the leader's is used: 8 arrivals
+  uint64_t* acc_empty = acc_full + 1;          // [1]          the leader's is used: 2 x P2_EPI_WARPS arrivals
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -79,7 +82,7 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
   if (threadIdx.x == 0) {
     for (int s = 0; s < P2_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
-    mbar_init(acc_empty, 8);
+    mbar_init(acc_empty, 2 * P2_EPI_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -162,11 +165,9 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       }
     }
   } else {
-    const int q = warp & 3;
-    uint8_t* slot = smem + P2_STAGES * P2_STAGE + (warp - 2) * EPI_SLOT;
-    float* stage = reinterpret_cast<float*>(slot);
+    const int q = warp & 3, cgrp = (warp - 2) >> 2;       // TMEM lane quarter (fixed by warp % 4), column half of the tile
+    uint8_t* blk = smem + P2_STAGES * P2_STAGE + (warp - 2) * P2_EPI_SLOT;
     const uint32_t acc_empty_leader = mapa_u32(smem_u32(acc_empty), 0);
-    uint32_t which = 0;
     uint32_t aph = 0;
     for (int t = pair; t < total_tiles; t += npairs) {
       int b, mt, nt;
@@ -177,23 +178,24 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
       const int row_base = mt * 512 + (int)rank * 256;
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256);
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256 + cgrp * 128);
+        const int row0 = row_base + h * 128 + q * 32;
         uint32_t v0[32], v1[32];
         tc_ld32(tbase, v0);
 #pragma unroll 1
-        for (int c = 0; c < 256 / 32; c += 2) {
+        for (int c = 0; c < 128 / 32; c += 2) {
           tc_ld_wait();
           tc_ld32(tbase + (c + 1) * 32, v1);
-          int col0 = nt * 256 + c * 32;
-          if (col0 < a.n) tc_epilogue32(a, v0, row_base + h * 128 + q * 32, col0, lane);
-          if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v0, row_base + h * 128 + q * 32, col0, b, lane);
-          else tc_store32(a, cbase, stage, v0, row_base + h * 128 + q * 32, col0, lane);
+          int col0 = nt * 256 + cgrp * 128 + c * 32;
+          if (col0 < a.n) tc_epilogue32(a, v0, row0, col0, lane);
+          if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v0, row0, col0, b, lane);
+          else tc_store32_rows(a, cbase, v0, row0, col0, lane);
           tc_ld_wait();
-          if (c + 2 < 256 / 32) tc_ld32(tbase + (c + 2) * 32, v0);
+          if (c + 2 < 128 / 32) tc_ld32(tbase + (c + 2) * 32, v0);
           col0 += 32;
-          if (col0 < a.n) tc_epilogue32(a, v1, row_base + h * 128 + q * 32, col0, lane);
-          if (a.c_tma) tc_store32_tma(a, &map_c, slot, which, v1, row_base + h * 128 + q * 32, col0, b, lane);
-          else tc_store32(a, cbase, stage, v1, row_base + h * 128 + q * 32, col0, lane);
+          if (col0 < a.n) tc_epilogue32(a, v1, row0, col0, lane);
+          if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v1, row0, col0, b, lane);
+          else tc_store32_rows(a, cbase, v1, row0, col0, lane);
         }
       }
       tc_fence_before();
