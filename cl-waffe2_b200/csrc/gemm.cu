@@ -777,8 +777,10 @@ int wf2cu_gemm_const_stats(int64_t* entries, int64_t* bytes) {
 int wf2cu_gemm(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
                const void* B, int64_t b_off, int64_t ldb, void* C, int64_t c_off, int64_t ldc, int64_t batch,
                int64_t stride_a, int64_t stride_b, int64_t stride_c) {
-  return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, batch, stride_a, stride_b, stride_c,
+  const int rc_ = gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, batch, stride_a, stride_b, stride_c,
                    nullptr, 0, nullptr, 0, "wf2cu_gemm");
+  S().emit_next = 0;      // wf2cu_emit_operand_planes is one shot: a product that could not write the plane drops the request
+  return rc_;
 }
 
 int wf2cu_gemm_ex(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
@@ -786,9 +788,11 @@ int wf2cu_gemm_ex(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, con
                   const void* bias, int64_t bias_off, int act, const void* mask, int64_t mask_off, int64_t ldmask) {
   WF2_CHECK(act == 0 || act == 1, "wf2cu_gemm_ex: act %d not in {0 none, 1 relu}", act);
   WF2_CHECK(!mask || ldmask >= n, "wf2cu_gemm_ex: ldmask %lld < n %lld", (long long)ldmask, (long long)n);
-  return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
+  const int rc_ = gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
                    bias ? (const float*)bias + bias_off : nullptr, act, mask ? (const float*)mask + mask_off : nullptr, ldmask,
                    "wf2cu_gemm_ex");
+  S().emit_next = 0;      // wf2cu_emit_operand_planes is one shot: a product that could not write the plane drops the request
+  return rc_;
 }
 
 int wf2cu_gemm_ex2(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, const void* A, int64_t a_off, int64_t lda,
@@ -796,9 +800,11 @@ int wf2cu_gemm_ex2(int trans_a, int trans_b, int64_t m, int64_t n, int64_t k, co
                    const void* bias, int64_t bias_off, int act, const void* residual, int64_t res_off, int64_t ldres) {
   WF2_CHECK(act >= 0 && act <= 2, "wf2cu_gemm_ex2: act %d not in {0 none, 1 relu, 2 gelu}", act);
   WF2_CHECK(!residual || ldres >= n, "wf2cu_gemm_ex2: ldres %lld < n %lld", (long long)ldres, (long long)n);
-  return gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
+  const int rc_ = gemm_impl(trans_a, trans_b, m, n, k, A, a_off, lda, B, b_off, ldb, C, c_off, ldc, 1, 0, 0, 0,
                    bias ? (const float*)bias + bias_off : nullptr, act, nullptr, 0, "wf2cu_gemm_ex2",
                    residual ? (const float*)residual + res_off : nullptr, ldres);
+  S().emit_next = 0;      // wf2cu_emit_operand_planes is one shot: a product that could not write the plane drops the request
+  return rc_;
 }
 
 }  // extern "C"

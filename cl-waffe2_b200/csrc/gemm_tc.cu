@@ -212,6 +212,8 @@ struct TcArgs {
   int64_t ldres;
   int c_tma;             // C goes out through map_c (bulk tensor stores) instead of per-lane global stores
   int group_m = 0;       // m-tiles per raster group (0 = kGroupM)
+  int plane = 0;         // 1: the epilogue also writes the mixed bf16 operand plane of C through pmap (wf2cu_emit_operand_planes; 256-row kernels)
+  alignas(64) CUtensorMap pmap;   // the plane as an (m x n) fp32-sized tensor, same boxes as map_c
 };
 
 // epilogue of the persistent kernels: 32 consecutive columns of one row per lane; same arithmetic as the separate
@@ -329,6 +331,26 @@ __device__ __forceinline__ void tc_store32_rows(const TcArgs& a, float* cbase, c
 #pragma unroll
   for (int j = 0; j < 32; ++j)
     if (col0 + j < a.n) crow[col0 + j] = __uint_as_float(v[j]);
+}
+
+// C is the K-major left operand of the MatmulNode issued next (GPT-2: gelu(fc h) feeds the second MLP projection): the lane's 32
+// finished values also leave as the mixed bf16 plane that product's pre-pass would write (plane_bits == split_bf<true>, bit for bit),
+// so that pre-pass — a 12-bytes-per-element launch — is not run.  32 columns = two k-blocks of 16 = 128 bytes of plane per row
+// ([16 bf16(x)][16 bf16(x - trunc x)] twice): the same staging block and bulk tensor store as C, through the plane's own map.
+// (Per-lane 8-byte global stores from here cost 93 us per GPT-2 layer against the 38 us pre-pass they replace: 32 L1 tags per
+// instruction.  With four epilogue warps even this form lost, 9.64 -> 9.76 ms per forward; with eight it wins.)
+__device__ __forceinline__ void tc_plane32(const TcArgs& a, uint8_t* blk, const uint32_t (&v)[32], int row0, int col0, int b, int lane) {
+  if (!a.plane) return;
+  uint32_t w[32];
+#pragma unroll
+  for (int c = 0; c < 32; c += 2) {
+    uint32_t h0, l0, h1, l1;
+    plane_bits(__uint_as_float(v[c]), h0, l0);
+    plane_bits(__uint_as_float(v[c + 1]), h1, l1);
+    w[(c >> 4) * 16 + ((c & 15) >> 1)] = h0 | (h1 << 16);
+    w[(c >> 4) * 16 + 8 + ((c & 15) >> 1)] = l0 | (l1 << 16);
+  }
+  tc_store32_tma1(a, &a.pmap, blk, w, row0, col0, b, lane);
 }
 
 constexpr int kGroupM = 16;   // raster: 16 m-tiles x all n-tiles per group, m fastest (L2 reuse of B panels)
@@ -636,14 +658,14 @@ gemm_tc256_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           if (c + 1 < NCH) tc_ld32(tbase + (c + 1) * 32, v1);
           int col0 = nt * T2N + cgrp * (T2N / 2) + c * 32;
           if (col0 < a.n) tc_epilogue32(a, v0, row0, col0, lane);
-          if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v0, row0, col0, b, lane);
+          if (a.c_tma) { tc_store32_tma1(a, &map_c, blk, v0, row0, col0, b, lane); tc_plane32(a, blk, v0, row0, col0, b, lane); }
           else tc_store32_rows(a, cbase, v0, row0, col0, lane);
           if (c + 1 < NCH) {
             tc_ld_wait();
             if (c + 2 < NCH) tc_ld32(tbase + (c + 2) * 32, v0);
             col0 += 32;
             if (col0 < a.n) tc_epilogue32(a, v1, row0, col0, lane);
-            if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v1, row0, col0, b, lane);
+            if (a.c_tma) { tc_store32_tma1(a, &map_c, blk, v1, row0, col0, b, lane); tc_plane32(a, blk, v1, row0, col0, b, lane); }
             else tc_store32_rows(a, cbase, v1, row0, col0, lane);
           }
         }
@@ -1048,7 +1070,8 @@ float* tc_workspace(size_t bytes) {
 // element, one launch) only restates what the producing kernel had in registers.  A producer that is asked to writes the mixed
 // bf16 plane itself (GPT-2 small: LayerNorm -> QKV / fc, P.V -> proj, gelu(fc) -> proj: 4 pre-passes per block, 8 % of the
 // forward).  One grow-only buffer, stream ordered like the workspace; retired buffers stay alive for captured graphs.
-static float* g_emit = nullptr;
+static float* g_emit2[2] = {nullptr, nullptr};   // alternate: the plane being consumed is never the one being written
+static int g_emit_idx = 0;
 static size_t g_emit_bytes = 0;
 int gemm_tc_correction();
 
@@ -1060,17 +1083,23 @@ float* planes_emit_begin(int64_t rows, int64_t k) {
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(S().stream, &cs);
     if (cs != cudaStreamCaptureStatusNone) return nullptr;      // no allocation inside a capture: the consumer runs its pre-pass
-    float* p = nullptr;
-    if (cudaMalloc(&p, need) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-    if (g_emit) g_retired.push_back(g_emit);
-    g_emit = p; g_emit_bytes = need;
+    // two buffers of the same size: a MatmulNode that consumes the plane its producer wrote may itself be asked to write one
+    float* p[2] = {nullptr, nullptr};
+    if (cudaMalloc(&p[0], need) != cudaSuccess || cudaMalloc(&p[1], need) != cudaSuccess) {
+      cudaGetLastError();
+      if (p[0]) cudaFree(p[0]);
+      return nullptr;
+    }
+    for (int i = 0; i < 2; ++i) { if (g_emit2[i]) g_retired.push_back(g_emit2[i]); g_emit2[i] = p[i]; }
+    g_emit_bytes = need;
   }
-  return g_emit;
+  g_emit_idx ^= 1;
+  return g_emit2[g_emit_idx];
 }
 
 void planes_emit_release() {
-  if (g_emit) cudaFree(g_emit);
-  g_emit = nullptr; g_emit_bytes = 0;
+  for (int i = 0; i < 2; ++i) { if (g_emit2[i]) cudaFree(g_emit2[i]); g_emit2[i] = nullptr; }
+  g_emit_bytes = 0;
   S().fresh.ptr = nullptr; S().emit_next = 0;
 }
 
@@ -1314,6 +1343,8 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
   if (S().branch != 0) return 0;
   const State::FreshPlanes fp = S().fresh;                 // planes the producer of A wrote (valid until the next launch)
   S().fresh.ptr = nullptr;
+  const int emit = S().emit_next;                          // wf2cu_emit_operand_planes: this product's result feeds the next one (one shot)
+  S().emit_next = 0;
   if (mode == 0) {
     // the tensor path pays two extra passes over the operands and wants >= 1 wave of 128x256 tiles
     if (m < 64 || n < 64 || k < 32) return 0;
@@ -1394,6 +1425,13 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
       if (fresh[i] && (rc = launch_split(q.src, q.hi, q.lo, q.ld, q.sx, q.rows, (int)k, Kp, q.nb, q.rcontig, bf_blk, q.raw))) return rc;
     }
   }
+  // the result's own operand plane, written by the epilogue of the 256-row kernels (dense C, one batch, n a multiple of 32; declined otherwise)
+  float* eplane = nullptr;
+  CUtensorMap mp;
+  if (emit && (pair2 || nb) && c_tma && batch == 1 && ldc == n && (n & 31) == 0) {
+    eplane = planes_emit_begin(m, n);
+    if (eplane && !make_map_c(&mp, eplane, m, n, n, 0, 1)) eplane = nullptr;
+  }
   // hi maps: the source itself (raw) or the hi plane; lo maps: the second plane
   auto maps = [&](const Prep& q, CUtensorMap* mh, CUtensorMap* ml, int box_k, int box_rows) -> int {
     int r = q.raw ? make_map_k(mh, q.src, k, q.rows, q.ld, q.nb, q.sx, box_k, box_rows)
@@ -1419,7 +1457,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
     t.a_bcast = a_nb == 1 ? 1 : 0;
     t.b_bcast = b_nb == 1 ? 1 : 0;
-    t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
+    t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma; t.plane = eplane ? 1 : 0; if (eplane) t.pmap = mp;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     {
       // raster: 8 m-tiles of 512 rows per group — with 74 pairs in flight that is ~8 x 9 pair tiles sharing A blocks 9-fold and B
@@ -1432,6 +1470,7 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     const int grid = 2 * (int)(total < pairs_max ? total : pairs_max);
     gemm_tc2sm_kernel<<<grid, P2_THREADS, P2_SMEM, S().stream>>>(mah, mal, mbh, mbl, mc, t);
     rc = post_launch("wf2cu_gemm(tcgen05 CTA pair)");
+    if (!rc && eplane) planes_emit_publish(C, m, n, ldc, eplane);
     S().gemm_last_path = WF2CU_GEMM_PATH_TC_2SM;
     return rc ? -rc : 1;
   }
@@ -1454,12 +1493,13 @@ int gemm_tc_try(int ta, int tb, int64_t m, int64_t n, int64_t k, const float* A,
     t.c_vec = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc & 3) == 0 && (sc & 3) == 0) ? 1 : 0;
     t.a_bcast = a_nb == 1 ? 1 : 0;
     t.b_bcast = b_nb == 1 ? 1 : 0;
-    t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma;
+    t.bias = bias; t.act = act; t.res = res; t.ldres = ldres; t.c_tma = c_tma; t.plane = eplane ? 1 : 0; if (eplane) t.pmap = mp;
     const int64_t total = (int64_t)t.tiles_m * t.tiles_n * t.batch;
     const int grid = (int)(total < S().sm_count ? total : S().sm_count);
     if (nb == 256) gemm_tc256_kernel<256, 3><<<grid, EPI8_THREADS, t2_smem_bytes(256, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
     else           gemm_tc256_kernel<192, 3><<<grid, EPI8_THREADS, t2_smem_bytes(192, 3), S().stream>>>(mah, mal, mbh, mbl, mc, t);
     rc = post_launch(nb == 256 ? "wf2cu_gemm(tcgen05 256x256)" : "wf2cu_gemm(tcgen05 256x192)");
+    if (!rc && eplane) planes_emit_publish(C, m, n, ldc, eplane);
     S().gemm_last_path = nb == 256 ? WF2CU_GEMM_PATH_TC_256X256 : WF2CU_GEMM_PATH_TC_256X192;
     return rc ? -rc : 1;
   }

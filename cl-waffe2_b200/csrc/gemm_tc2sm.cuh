@@ -188,13 +188,13 @@ gemm_tc2sm_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_const
           tc_ld32(tbase + (c + 1) * 32, v1);
           int col0 = nt * 256 + cgrp * 128 + c * 32;
           if (col0 < a.n) tc_epilogue32(a, v0, row0, col0, lane);
-          if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v0, row0, col0, b, lane);
+          if (a.c_tma) { tc_store32_tma1(a, &map_c, blk, v0, row0, col0, b, lane); tc_plane32(a, blk, v0, row0, col0, b, lane); }
           else tc_store32_rows(a, cbase, v0, row0, col0, lane);
           tc_ld_wait();
           if (c + 2 < 128 / 32) tc_ld32(tbase + (c + 2) * 32, v0);
           col0 += 32;
           if (col0 < a.n) tc_epilogue32(a, v1, row0, col0, lane);
-          if (a.c_tma) tc_store32_tma1(a, &map_c, blk, v1, row0, col0, b, lane);
+          if (a.c_tma) { tc_store32_tma1(a, &map_c, blk, v1, row0, col0, b, lane); tc_plane32(a, blk, v1, row0, col0, b, lane); }
           else tc_store32_rows(a, cbase, v1, row0, col0, lane);
         }
       }

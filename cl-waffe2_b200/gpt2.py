@@ -17,6 +17,8 @@ composes them — including its quirks, reproduced as written (SURVEY §8 a11/a1
 Each step below is one call of the C ABI (one kernel, or split+GEMM for `!matmul`)."""
 from __future__ import annotations
 
+import os
+
 from typing import Dict, List, Optional
 
 import numpy as np
@@ -62,6 +64,7 @@ def _bcast_keep(stat: CUDATensor, like: CUDATensor) -> CUDATensor:
 
 
 EMIT_PLANES = True      # producers write the operand plane of the MatmulNode that follows (wf2cu_emit_operand_planes)
+EMIT_FROM_GEMM = os.environ.get("WF2CU_EMIT_FROM_GEMM", "1") != "0"   # ... also the gelu projection's epilogue (A/B switch)
 
 
 def layer_norm(x: CUDATensor, g: CUDATensor, b: CUDATensor, eps: float = 1e-5, feeds_matmul: bool = False) -> CUDATensor:
@@ -157,9 +160,12 @@ def self_attention(qkv: CUDATensor, n_head: int) -> CUDATensor:
 FUSE_EPILOGUES = True
 
 
-def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor, gelu: bool = False, residual: Optional[CUDATensor] = None) -> CUDATensor:
+def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor, gelu: bool = False, residual: Optional[CUDATensor] = None,
+            feeds_matmul: bool = False) -> CUDATensor:
     """`(!matmul x w)` + `(!add (%transform b[i] -> [~ i]))` (model.lisp:118-120), optionally followed by the node the block
-    puts next: `!gelu` (after the first MLP projection) or the residual `(!add x ...)` (after both output projections)."""
+    puts next: `!gelu` (after the first MLP projection) or the residual `(!add x ...)` (after both output projections).
+    feeds_matmul: the result is the left operand of the `!matmul` issued next; the epilogue that applies bias / gelu also writes
+    that product's operand plane (wf2cu_emit_operand_planes, as layer_norm does)."""
     if x.dims() == 3 and x.is_contiguous() and not x.permuted_p():
         # W is shared by the batch, so (B N in) . (in out) is one (B*N in) . (in out) product; the bias add rides in the
         # GEMM epilogue (wf2cu_gemm_ex — the MatMul + Add fusion of lisp/fusion.lisp), same arithmetic, one pass less;
@@ -169,6 +175,8 @@ def _linear(x: CUDATensor, w: CUDATensor, b: CUDATensor, gelu: bool = False, res
         fuse = FUSE_EPILOGUES and (gelu or residual is not None) and (residual is None or (residual.is_contiguous() and not residual.permuted_p()))
         if fuse:
             r2 = reshape_contiguous(residual, [B_ * N_, residual.shape[2]]) if residual is not None else None
+            if feeds_matmul and EMIT_PLANES and EMIT_FROM_GEMM:
+                _lib.check(_lib.load().wf2cu_emit_operand_planes(1))
             y = ops.matmul(x2, w, bias=b, gelu=gelu, residual=r2)
             return reshape_contiguous(y, [B_, N_, y.shape[1]])
         y = reshape_contiguous(ops.matmul(x2, w, bias=b), [B_, N_, w.shape[1]])
@@ -201,7 +209,7 @@ class GPT2Layer:
         a = self_attention(qkv, self.n_head)
         x = _linear(a, self.proj_w, self.proj_b, residual=x)            # (!add x (proj a)): residual
         h = layer_norm(x, self.ln_2_g, self.ln_2_b, feeds_matmul=True)
-        m = _linear(h, self.fc_w, self.fc_b, gelu=True)                 # (!gelu (fc h))
+        m = _linear(h, self.fc_w, self.fc_b, gelu=True, feeds_matmul=True)   # (!gelu (fc h)), the left operand of the projection below
         return _linear(m, self.fc_proj_w, self.fc_proj_b, residual=x)   # (!add x (fc-proj m)): residual
 
 

@@ -261,8 +261,9 @@ int  wf2cu_gemm_const_stats(int64_t* entries, int64_t* bytes);
 /* The result of one node is very often the K-major A operand of the MatmulNode that follows it (LinearLayer after LayerNorm,
  * `nn/regression.lisp:14-18` after `examples/gpt-2/utils.lisp:114-127`; the projections of `examples/gpt-2/model.lisp:93-137`).
  * The product's operand pre-pass then only restates what the producing kernel had in registers.  on != 0: the NEXT call of
- * wf2cu_layernorm or wf2cu_attn_pv (one shot; other entry points leave the request pending) also writes the tensor-core operand
- * plane of its result; a
+ * wf2cu_layernorm, wf2cu_attn_pv / wf2cu_attn_fused, or wf2cu_gemm / _ex / _ex2 (one shot: a wf2cu_gemm* call consumes the request
+ * whether or not it can honour it — it can on the 256-row tensor-core kernels, dense unbatched C with n a multiple of 32; other
+ * entry points leave it pending) also writes the tensor-core operand plane of its result; a
  * wf2cu_gemm / _ex / _ex2 call that comes IMMEDIATELY after it (no other launch of this library in between) and reads exactly
  * that result as its untransposed A operand uses the plane instead of running the pre-pass.  Same bits as the pre-pass writes,
  * so the product is bit-identical either way; a producer or a shape that cannot (k not a multiple of 32, TF32 corrections

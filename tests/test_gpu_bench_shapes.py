@@ -579,6 +579,33 @@ def test_producer_written_operand_planes_equal_the_prepass(gpu):
     finally:
         g.EMIT_PLANES = True
         gpu._lib.check(lib.wf2cu_gemm_const_operand(W.vec.ptr, 0, E * n, 0))
+    # a MatmulNode as the producer: gelu(x W1 + b1) written with its plane by the GEMM epilogue, consumed by the next product —
+    # while that GEMM itself consumes the plane LayerNorm wrote (two emit buffers alternate)
+    W1 = gpu.from_numpy((0.02 * rng.normal(size=(E, 3072))).astype(np.float32))
+    b1 = gpu.from_numpy((0.02 * rng.normal(size=(3072,))).astype(np.float32))
+    W2 = gpu.from_numpy((0.02 * rng.normal(size=(3072, E))).astype(np.float32))
+    for w_ in (W1, W2):
+        gpu._lib.check(lib.wf2cu_gemm_const_operand(w_.vec.ptr, 0, w_.numel(), 1))
+    try:
+        def chain(emit):
+            h = g.layer_norm(x, gam, bet, feeds_matmul=True)
+            if emit:
+                gpu._lib.check(lib.wf2cu_emit_operand_planes(1))
+            y = gpu.ops.matmul(h, W1, bias=b1, gelu=True)
+            return y, gpu.ops.matmul(y, W2)
+        chain(False); chain(True)                                 # workspaces grown
+        l0 = _launches(gpu); y0, z0 = chain(False); n0 = _launches(gpu) - l0
+        l0 = _launches(gpu); y1, z1 = chain(True); n1 = _launches(gpu) - l0
+        np.testing.assert_array_equal(y1.to_numpy(), y0.to_numpy())
+        np.testing.assert_array_equal(z1.to_numpy(), z0.to_numpy())
+        assert n1 == n0 - 1, (n1, n0)
+        # the request is one shot: a product that follows without a new request does not write a plane, the next consumer pre-passes
+        l0 = _launches(gpu); y2 = gpu.ops.matmul(g.layer_norm(x, gam, bet, feeds_matmul=True), W1, bias=b1, gelu=True); z2 = gpu.ops.matmul(y2, W2)
+        assert _launches(gpu) - l0 == n0
+        np.testing.assert_array_equal(z2.to_numpy(), z0.to_numpy())
+    finally:
+        for w_ in (W1, W2):
+            gpu._lib.check(lib.wf2cu_gemm_const_operand(w_.vec.ptr, 0, w_.numel(), 0))
     # the whole block chain: GPT-2 (2 layers, full width) with and without producer-written planes
     cfg = dict(n_vocab=211, n_ctx=256, n_emb=768, n_head=12, n_layer=2)
     model = g.GPT2(cfg, seed=3)
