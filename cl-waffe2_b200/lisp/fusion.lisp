@@ -199,9 +199,13 @@ what `(!flexible bias)` becomes inside `step-linear` (`nn/regression.lisp:14-18`
        (= (observe (second (shape tensor))) n)
        (eql (observe (second (tensor-stride tensor))) 1)))
 
-(defun launch-gemm (ta tb a b c &key bias (act 0) residual)
+(defun launch-gemm (ta tb a b c &key bias (act 0) residual feeds-matmul)
   "C <- op(A) op(B) [+ bias] [act] [+ residual] on rank-2 views; TA / TB: the operand is read untransposed and flagged, as
-MatMulNode's implementation does (`read-untransposed`, matrix-ops.lisp:52-56)."
+MatMulNode's implementation does (`read-untransposed`, matrix-ops.lisp:52-56).
+FEEDS-MATMUL: C is the untransposed left operand of the product issued next (the two MLP projections of
+`examples/gpt-2/model.lisp:93-137`): the epilogue also writes that product's tensor-core operand plane
+(wf2cu_emit_operand_planes, one shot; honoured by the 256-row kernels, ignored otherwise; same bits as the pre-pass)."
+  (when feeds-matmul (emit-operand-planes 1))
   (let* ((a* (read-untransposed a))
 	 (b* (read-untransposed b))
 	 (m (observe (first (shape c)))) (n (observe (second (shape c))))
