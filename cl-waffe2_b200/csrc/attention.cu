@@ -91,7 +91,59 @@ __global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restri
   }
 }
 
-struct PvArgs { float* out; int N, tiles_m, batch_heads; float* plane; };   // plane: mixed bf16 operand plane of out (or NULL)
+struct PvArgs { float* out; int N, tiles_m, batch_heads; float* plane; int wide; };   // plane: mixed bf16 operand plane of out (or NULL); wide: out / plane rows are 32-byte aligned
+__device__ __forceinline__ void st_global_v8(float* p, const uint32_t* v) {            // one 256-bit store (STG.E.256)
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]),
+               "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+
+// one head's 64 finished columns of this lane's row: result (merged heads) and, on request, the consumer's operand plane.
+// A store instruction costs one L1 tag per row it touches (lane = row: 32 of them), so the wide form uses 256-bit stores (STG.256):
+// half the instructions for the result, a quarter for the plane.  In attn_pv6_kernel this epilogue runs once per work item with
+// nothing to overlap it: GPT-2 forward 8.82 -> 8.52 ms (profiles/r03X2_ab_gpt2_bench.log).
+__device__ __forceinline__ void pv_store_head(const PvArgs& a, int b, int row, int h, const uint32_t (&v0)[32], const uint32_t (&v1)[32]) {
+  float* crow = a.out + ((size_t)b * a.N + row) * AE + h * AD;
+  if (a.wide) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      st_global_v8(crow + 8 * j, &v0[8 * j]);
+      st_global_v8(crow + 32 + 8 * j, &v1[8 * j]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      reinterpret_cast<float4*>(crow)[j] = make_float4(__uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      reinterpret_cast<float4*>(crow)[8 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+  }
+  if (!a.plane) return;                 // the projection that follows reads this row as its K-major A operand
+  float* prow = a.plane + ((size_t)b * a.N + row) * AE;
+  if (a.wide) {
+    // 32 columns = two k-blocks of 16 = 128 contiguous bytes of plane: [16 bf16(x)][16 bf16(x - trunc x)] twice
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const uint32_t (&v)[32] = half ? v1 : v0;
+      uint32_t w[32];
+#pragma unroll
+      for (int c = 0; c < 32; c += 2) {
+        uint32_t h0, l0, h1, l1;
+        plane_bits(__uint_as_float(v[c]), h0, l0);
+        plane_bits(__uint_as_float(v[c + 1]), h1, l1);
+        w[(c >> 4) * 16 + ((c & 15) >> 1)] = h0 | (h1 << 16);
+        w[(c >> 4) * 16 + 8 + ((c & 15) >> 1)] = l0 | (l1 << 16);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) st_global_v8(prow + h * AD + half * 32 + 8 * j, &w[8 * j]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      plane_store4(prow, h * AD + 4 * j, __uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
+      plane_store4(prow, h * AD + 32 + 4 * j, __uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
+    }
+  }
+}
 
 template <bool NORM>
 __global__ void __launch_bounds__(P_THREADS, 1)
@@ -226,23 +278,7 @@ attn_pv_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[as]);          // the accumulator is in registers now
       const int row = mt * P_M + q * 32 + lane;
-      if (row < a.N) {
-        float4* crow = reinterpret_cast<float4*>(a.out + ((size_t)b * a.N + row) * AE + h * AD);
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          crow[j] = make_float4(__uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          crow[8 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
-        if (a.plane) {                       // the projection that follows reads this row as its K-major A operand
-          float* prow = a.plane + ((size_t)b * a.N + row) * AE;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            plane_store4(prow, h * AD + 4 * j, __uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
-            plane_store4(prow, h * AD + 32 + 4 * j, __uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
-          }
-        }
-      }
+      if (row < a.N) pv_store_head(a, b, row, h, v0, v1);
       if (++as == 2) { as = 0; aph ^= 1; }
     }
   }
@@ -411,23 +447,7 @@ attn_pv6_kernel(const __grid_constant__ CUtensorMap map_p, const __grid_constant
         tc_ld32(tbase, v0);
         tc_ld32(tbase + 32, v1);
         tc_ld_wait();
-        if (row < a.N) {
-          float4* crow = reinterpret_cast<float4*>(a.out + ((size_t)b * a.N + row) * AE + h * AD);
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            crow[j] = make_float4(__uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            crow[8 + j] = make_float4(__uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
-          if (a.plane) {
-            float* prow = a.plane + ((size_t)b * a.N + row) * AE;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              plane_store4(prow, h * AD + 4 * j, __uint_as_float(v0[4 * j]), __uint_as_float(v0[4 * j + 1]), __uint_as_float(v0[4 * j + 2]), __uint_as_float(v0[4 * j + 3]));
-              plane_store4(prow, h * AD + 32 + 4 * j, __uint_as_float(v1[4 * j]), __uint_as_float(v1[4 * j + 1]), __uint_as_float(v1[4 * j + 2]), __uint_as_float(v1[4 * j + 3]));
-            }
-          }
-        }
+        if (row < a.N) pv_store_head(a, b, row, h, v0, v1);
       }
       tc_fence_before();
       __syncwarp();
@@ -513,8 +533,9 @@ static int launch_pv(float* P, const float* norm_r, const float* x, float* vh, f
     WF2_CUDA(cudaFuncSetAttribute(attn_pv6_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P6_SMEM));
     attr_set = true;
   }
-  PvArgs args{O, N, N / P_M, BH, nullptr};
+  PvArgs args{O, N, N / P_M, BH, nullptr, 0};
   if (S().emit_next) args.plane = planes_emit_begin(batch * seq, AE);     // wf2cu_emit_operand_planes: one-shot, may decline
+  args.wide = ((reinterpret_cast<uintptr_t>(O) & 31) == 0 && (reinterpret_cast<uintptr_t>(args.plane) & 31) == 0) ? 1 : 0;
   const int total = args.tiles_m * BH;
   const int grid = total < S().sm_count ? total : S().sm_count;
   static const bool six = []{ const char* e = getenv("WF2CU_ATTN_PV6"); return !e || atoi(e) != 0; }();   // 0: one head per work item (A/B)
