@@ -74,9 +74,15 @@ constexpr int P_SMEM = P_NS * P_STAGE + 1024 + 256;
 constexpr uint32_t P_IDESC = idesc_tf32_mn(P_M, P_N);
 
 // V_h (N x 64 per (b, h), rows 3E apart inside the QKV activation) -> hi / lo planes [b*H + h][64][N], K-major
-__global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restrict__ qkv, float* __restrict__ hi, float* __restrict__ lo, int N) {
+// late = 1 (wf2cu_attn_fused): the kernel launched before this one is the score kernel, which does not produce anything read here and
+// lets its dependents in only after the producer of qkv is complete (gemm_raw_kernel<RawAttnJob1>).  So this grid does not wait at its
+// start — it runs beside the score tiles, which leave half of the issue slots and most of the DRAM bandwidth idle — and ONE of its CTAs
+// waits for the score kernel before it exits: the grid as a whole is complete only then, which is what the P.V kernel's own
+// griddepcontrol.wait relies on for E and R.
+__global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restrict__ qkv, float* __restrict__ hi, float* __restrict__ lo, int N, int late) {
   __shared__ float t[32][65];
-  pdl_prologue();
+  if (late) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  else pdl_prologue();
   const int bh = blockIdx.y, b = bh / AH, h = bh % AH, k0 = blockIdx.x * 32;
   const float* src = qkv + ((size_t)b * N + k0) * (3 * AE) + 2 * AE + h * AD;
   for (int e = threadIdx.x; e < 32 * 64; e += 256) t[e >> 6][e & 63] = src[(size_t)(e >> 6) * (3 * AE) + (e & 63)];   // rows of 64
@@ -89,6 +95,7 @@ __global__ void __launch_bounds__(256) attn_split_v_kernel(const float* __restri
     hi[o] = hv;
     lo[o] = (fabsf(x) <= 3.0e38f) ? x - hv : 0.f;        // inf / nan live in hi only
   }
+  if (late && blockIdx.x == 0 && blockIdx.y == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 struct PvArgs { float* out; int N, tiles_m, batch_heads; float* plane; int wide; };   // plane: mixed bf16 operand plane of out (or NULL); wide: out / plane rows are 32-byte aligned
@@ -502,7 +509,9 @@ int wf2cu_attn_heads_softmax(const void* qkv, int64_t qkv_off, int64_t batch, in
 // P . V for both entry points.  norm_r != NULL: P holds un-normalised exponentials and norm_r the (B N N) reciprocal denominators.
 static int launch_pv(float* P, const float* norm_r, const float* x, float* vh, float* vl, int64_t batch, int64_t seq, float* O, const char* who) {
   const int N = (int)seq, BH = (int)(batch * AH);
-  WF2_CUDA(launch_pdl(attn_split_v_kernel, dim3((unsigned)(N / 32), (unsigned)BH), dim3(256), 0, S().stream, x, vh, vl, N));
+  static const bool overlap = []{ const char* e = getenv("WF2CU_ATTN_SPLIT_OVERLAP"); return !e || atoi(e) != 0; }();   // 0: A/B
+  const int late = (norm_r && overlap && pdl_enabled()) ? 1 : 0;      // only behind the score kernel of wf2cu_attn_fused
+  WF2_CUDA(launch_pdl(attn_split_v_kernel, dim3((unsigned)(N / 32), (unsigned)BH), dim3(256), 0, S().stream, x, vh, vl, N, late));
   int rc = post_launch("wf2cu_attn_pv(split V)");
   if (rc) return rc;
   CUtensorMap mp, mvh, mvl, mr;

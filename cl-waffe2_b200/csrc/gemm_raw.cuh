@@ -151,7 +151,15 @@ gemm_raw_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
   // bf16 corrections only on pre-split (mixed) lo planes: the converter warps are the raw variants' bottleneck, and mixed
   // tiles cost them two scattered 8-byte stores per chunk instead of one 16-byte store (r02f: 194 -> 336 us on attention)
   const bool hyb = (A_RAW || B_RAW) ? false : job.hyb();
-  pdl_prologue();
+  if constexpr (std::is_same<JOB, RawAttnJob1>::value) {
+    // wait FIRST, then let the dependent grid in: the kernel launched after this one in wf2cu_attn_fused (the split of V) does not
+    // depend on this kernel at all, only on qkv — it starts as soon as every CTA here has passed this point, i.e. once the producer
+    // of qkv is known to be complete, and runs beside the score tiles (attn_split_v_kernel, `late`)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  } else {
+    pdl_prologue();
+  }
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < R_NS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); mbar_init(&conv[s], CONVERT ? R_CONV_WARPS : 1); }
