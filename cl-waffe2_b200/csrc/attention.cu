@@ -26,7 +26,11 @@
 //       fp32; converter warps move each tile into tensor memory as the A operand (raw bits = the TF32 hi plane, lo = x -
 //       trunc(x)); V's hi / lo planes are split and transposed once per call (25 MB against 402 MB of P).  warp 0 TMA,
 //       warp 1 MMA (12 x 128x64x8 per k-block into one of two 64-column accumulators), warps 2-5 converters, warps 6-9 epilogue.
-// Both kernels are specialised for 12 heads of 64 features (GPT-2 small); other shapes return WF2CU_ERR_UNSUPPORTED and the
+//   wf2cu_attn_fused : both in one call, the heads visited ONCE: the score kernel (gemm_raw.cuh, RawAttnJob1) writes the un-normalised
+//       exponentials E and the reciprocal denominators R = 1 / sum_h E; attn_pv6_kernel (six heads per CTA, R held in registers across
+//       them) forms p = RN(e r) on the way into tensor memory.  The V split runs BESIDE the score kernel (programmatic dependent launch:
+//       see attn_split_v_kernel).  Bit-identical to the two launches.
+// All kernels are specialised for 12 heads of 64 features (GPT-2 small); other shapes return WF2CU_ERR_UNSUPPORTED and the
 // host issues the nodes one by one, exactly as before.
 #include <cuda.h>
 #include "common.cuh"
