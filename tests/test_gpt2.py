@@ -232,3 +232,30 @@ def test_one_call_attention_equals_the_two_launches(gpu, B, N):
     e = np.exp(q @ np.swapaxes(k, -1, -2) / N)
     want = np.transpose((e / e.sum(axis=1, keepdims=True)) @ v, (0, 2, 1, 3)).reshape(B, N, H * D)
     assert np.abs(a - want).max() <= 2e-5 * np.abs(want).max()
+
+
+@pytest.mark.gpu
+def test_one_call_attention_repeated_behind_other_work(gpu):
+    """wf2cu_attn_fused overlaps its V split with the score kernel through programmatic dependent launch (the split does not wait at its
+    start; one of its CTAs waits for the score kernel before it exits, which is what orders P.V behind BOTH).  A missing edge there would
+    show as a P.V kernel that reads E or the V planes too early — only sometimes.  30 calls, each queued behind a different amount of
+    unrelated work and each overwriting the result buffer first, must all equal the two-launch result bit for bit."""
+    lib = gpu._lib.load()
+    B, N, H, D = 4, 512, 12, 64
+    rng = np.random.default_rng(7)
+    qkv = gpu.from_numpy(rng.normal(0, 1.0, size=(B, N, 3 * H * D)).astype(np.float32))
+    P = gpu.make_tensor((B, H, N, N))
+    two = gpu.make_tensor((B, N, H * D))
+    one = gpu.make_tensor((B, N, H * D))
+    big = gpu.from_numpy(rng.normal(size=(2048, 2048)).astype(np.float32))
+    gpu._lib.check(lib.wf2cu_attn_heads_softmax(qkv.vec.ptr, 0, B, N, H, D, float(N), P.vec.ptr, 0))
+    gpu._lib.check(lib.wf2cu_attn_pv(P.vec.ptr, 0, qkv.vec.ptr, 0, B, N, H, D, two.vec.ptr, 0))
+    want = two.to_numpy()
+    for i in range(30):
+        gpu.ops.fill_(one, float(i))
+        for _ in range(i % 4):
+            gpu.ops.exp(big)
+        if i % 5 == 4:
+            gpu.ops.matmul(big, big)
+        gpu._lib.check(lib.wf2cu_attn_fused(qkv.vec.ptr, 0, B, N, H, D, float(N), one.vec.ptr, 0))
+        np.testing.assert_array_equal(one.to_numpy(), want, err_msg=f"call {i}")
