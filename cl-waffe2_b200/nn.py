@@ -16,6 +16,7 @@ B200-first choices (SURVEY §7 hard parts e, f; §8e, §8f-1/2):
 """
 from __future__ import annotations
 
+import os
 import ctypes as C
 import math
 from typing import Callable, List, Optional, Sequence
@@ -54,6 +55,7 @@ FUSE = True
 # Independent backward instructions on side streams (wf2cu_branch_*): a layer's weight-gradient GEMM and
 # bias-gradient reduction run beside the input-gradient GEMM that the next backward node waits for.
 CONCURRENT = True
+CONSTANT_SEED = os.environ.get("WF2CU_CONSTANT_SEED", "1") != "0"   # A/B switch, see CompiledStep._trace
 _open_branches: List[int] = []
 
 
@@ -571,6 +573,8 @@ class CompiledStep:
         # measurement aid: run the peer-memory exchange kernel on a world of ONE attached rank (what the kernel itself costs
         # against the plain Adam launch, with nothing on the wire; scripts/p2p_world1.py)
         self.p2p_single = False
+        self._seed = make_tensor([1, 1])
+        ops.fill_(self._seed, 1.0)
 
     def _loss(self, out: CUDATensor) -> CUDATensor:
         if self.loss_kind == "softmax-cross-entropy-sum":      # examples/mnist/mlp.lisp:24-28
@@ -589,22 +593,26 @@ class CompiledStep:
         _tape = self.tape
         try:
             with self.pool:
-                seed = None
-                if CONCURRENT:
-                    # the backward seed (dL/dL = 1) does not depend on the forward pass: side stream, joined before backward
-                    seed = make_tensor([1, 1])
+                side_seed = None
+                if CONCURRENT and not CONSTANT_SEED:
+                    # WF2CU_CONSTANT_SEED=0: the seed refilled every step, on a side branch beside the forward pass
+                    side_seed = make_tensor([1, 1])
                     _lib.check(lib.wf2cu_branch_begin(3))
                     try:
-                        ops.fill_(seed, 1.0)
+                        ops.fill_(side_seed, 1.0)
                     finally:
                         _lib.check(lib.wf2cu_branch_end(3))
                 loss = self._loss(self.model(self.x))
-                if seed is not None and loss.shape == seed.shape:
+                if side_seed is not None:
                     _lib.check(lib.wf2cu_branch_join(3))
-                    loss.grad = seed
+                if CONCURRENT and CONSTANT_SEED and tuple(loss.shape) == (1, 1):
+                    # the backward seed (dL/dL = 1) is the same value every step and nothing writes it: it lives outside the step's
+                    # pool, filled once.  (Refilled per step on a side branch it was one launch and two graph edges — a fork and a
+                    # join on the main chain — of a step in which an edge costs about as much as a small kernel.)
+                    loss.grad = self._seed
+                elif side_seed is not None and tuple(loss.shape) == (1, 1):
+                    loss.grad = side_seed
                 else:
-                    if seed is not None:
-                        _lib.check(lib.wf2cu_branch_join(3))
                     loss.grad = make_tensor(loss.shape)
                     ops.fill_(loss.grad, 1.0)
                 loss._has_grad = True
