@@ -65,6 +65,7 @@ PROTOTYPES = {
     "wf2cu_gemm_ex": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i32, vp, i64, i64],
     "wf2cu_gemm_ex2": [i32, i32, i64, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i32, vp, i64, i64],
     "wf2cu_sce_sum_forward": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, f32],
+    "wf2cu_sce_sum_forward_grad": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, f32, vp, i64, vp, i64],
     "wf2cu_sce_backward": [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32],
     "wf2cu_sgd_step": [vp, i64, vp, i64, i64, f32],
     "wf2cu_adam_step": [vp, i64, vp, i64, vp, i64, vp, i64, i64, f32, vp, f32, f32, f32, f32],

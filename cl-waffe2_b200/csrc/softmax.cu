@@ -317,6 +317,7 @@ struct SceArgs {
   const float* x; const float* labels; float* z; float* loss; float* partial; unsigned int* counter;
   int64_t rows, cols;
   float delta;
+  const float* dy; float* dx;   // both or neither: dx = (dy[0] * (z - labels)) / rows written as well (`sce-diff-static` in the same launch)
 };
 
 __global__ void __launch_bounds__(256) sce_sum_forward_kernel(const __grid_constant__ SceArgs a) {
@@ -344,6 +345,7 @@ __global__ void __launch_bounds__(256) sce_sum_forward_kernel(const __grid_const
       if (c < a.cols) {
         const float z = __fdiv_rn(v[k], s);
         zp[c] = z;
+        if (a.dx) a.dx[row * a.cols + c] = __fdiv_rn(__fmul_rn(*a.dy, __fsub_rn(z, lp[c])), (float)a.rows);   // sce_backward_kernel's operations
         rl = __fadd_rn(rl, __fmul_rn(-1.0f, __fmul_rn(lp[c], logf(__fadd_rn(z, a.delta)))));
       }
     }
@@ -583,10 +585,20 @@ extern "C" int wf2cu_layernorm(const void* x, int64_t x_off, const void* g, int6
   return rc;
 }
 
+extern "C" int wf2cu_sce_sum_forward_grad(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
+                                          void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta,
+                                          const void* dy, int64_t dy_off, void* dx, int64_t dx_off);
 extern "C" int wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
                                      void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta) {
+  return wf2cu_sce_sum_forward_grad(x, x_off, labels, l_off, z, z_off, loss, loss_off, rows, cols, delta, nullptr, 0, nullptr, 0);
+}
+
+extern "C" int wf2cu_sce_sum_forward_grad(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
+                                          void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta,
+                                          const void* dy, int64_t dy_off, void* dx, int64_t dx_off) {
   WF2_REQUIRE_INIT();
   WF2_CHECK(x && labels && z && loss && rows >= 0 && cols >= 1, "wf2cu_sce_sum_forward: bad arguments");
+  WF2_CHECK((dy != nullptr) == (dx != nullptr), "wf2cu_sce_sum_forward_grad: dy and dx come together");
   if (cols > 1024) return set_error(WF2CU_ERR_UNSUPPORTED, "wf2cu_sce_sum_forward: %lld classes > 1024; compose softmax, the log chain and !sum instead", (long long)cols);
   const int64_t grid = rows == 0 ? 1 : (rows + 7) / 8;
   WF2_CHECK(grid < (int64_t(1) << 31), "wf2cu_sce_sum_forward: too many rows");
@@ -594,7 +606,7 @@ extern "C" int wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* l
   if (rc) return rc;
   State& s = S();
   SceArgs a{(const float*)x + x_off, (const float*)labels + l_off, (float*)z + z_off, (float*)loss + loss_off, (float*)scratch_base(),
-            counters_base() + 4095, rows, cols, delta};
+            counters_base() + 4095, rows, cols, delta, dy ? (const float*)dy + dy_off : nullptr, dx ? (float*)dx + dx_off : nullptr};
   sce_sum_forward_kernel<<<(unsigned)grid, 256, 0, s.stream>>>(a);
   return post_launch("wf2cu_sce_sum_forward");
 }

@@ -54,6 +54,8 @@ _tape: Optional[Tape] = None
 FUSE = True
 # Independent backward instructions on side streams (wf2cu_branch_*): a layer's weight-gradient GEMM and
 # bias-gradient reduction run beside the input-gradient GEMM that the next backward node waits for.
+FUSE_SCE_GRAD = os.environ.get("WF2CU_FUSE_SCE_GRAD", "1") != "0"   # A/B switch, see softmax_cross_entropy_sum
+_known_seed: Optional["CUDATensor"] = None      # set by CompiledStep._trace around the forward pass
 CONCURRENT = True
 CONSTANT_SEED = os.environ.get("WF2CU_CONSTANT_SEED", "1") != "0"   # A/B switch, see CompiledStep._trace
 _open_branches: List[int] = []
@@ -266,11 +268,25 @@ def softmax_cross_entropy_sum(x: CUDATensor, labels: CUDATensor, delta: float = 
         return reduce_sum(softmax_cross_entropy(x, labels, delta))
     z = make_tensor(x.shape)
     out = make_tensor([1, 1])
-    _lib.check(lib.wf2cu_sce_sum_forward(x.vec.ptr, x.lower().offset, labels.vec.ptr, labels.lower().offset,
-                                         z.vec.ptr, z.lower().offset, out.vec.ptr, out.lower().offset, rows, cols, float(delta)))
+    # A compiled training step seeds the summed loss with a constant it knows before the forward pass (_known_seed): the forward
+    # launch then writes the logits' gradient as well — `sce-diff-static` with the same operations — and the backward node has
+    # nothing to launch (checked there: first contribution, and the loss' incoming gradient IS that seed).
+    seed = _known_seed if (FUSE_SCE_GRAD and _tape is not None and _tracked(x) and x.grad is None) else None
+    if seed is not None:
+        x.grad = make_tensor(x.shape)
+        _lib.check(lib.wf2cu_sce_sum_forward_grad(x.vec.ptr, x.lower().offset, labels.vec.ptr, labels.lower().offset,
+                                                  z.vec.ptr, z.lower().offset, out.vec.ptr, out.lower().offset, rows, cols, float(delta),
+                                                  seed.vec.ptr, seed.lower().offset, x.grad.vec.ptr, x.grad.lower().offset))
+    else:
+        _lib.check(lib.wf2cu_sce_sum_forward(x.vec.ptr, x.lower().offset, labels.vec.ptr, labels.lower().offset,
+                                             z.vec.ptr, z.lower().offset, out.vec.ptr, out.lower().offset, rows, cols, float(delta)))
     if _mark(out, x):
         def bw():
             dy = out.grad
+            if seed is not None and dy is seed and not getattr(x, "_has_grad", False) and not getattr(x, "_relu_out", False):
+                x._has_grad = True                   # written by the forward launch
+                _tape.touched.append(x)
+                return
 
             def f(g, acc):
                 _lib.check(lib.wf2cu_sce_backward(z.vec.ptr, z.lower().offset, labels.vec.ptr, labels.lower().offset,
@@ -602,7 +618,12 @@ class CompiledStep:
                         ops.fill_(side_seed, 1.0)
                     finally:
                         _lib.check(lib.wf2cu_branch_end(3))
-                loss = self._loss(self.model(self.x))
+                global _known_seed
+                _known_seed = self._seed if (CONCURRENT and CONSTANT_SEED) else None
+                try:
+                    loss = self._loss(self.model(self.x))
+                finally:
+                    _known_seed = None
                 if side_seed is not None:
                     _lib.check(lib.wf2cu_branch_join(3))
                 if CONCURRENT and CONSTANT_SEED and tuple(loss.shape) == (1, 1):

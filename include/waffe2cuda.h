@@ -295,6 +295,12 @@ int  wf2cu_sce_sum_forward(const void* x, int64_t x_off, const void* labels, int
                            void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta);
 int  wf2cu_sce_backward(const void* z, int64_t z_off, const void* labels, int64_t l_off, const void* dy, int64_t dy_off,
                         void* dx, int64_t dx_off, int64_t rows, int64_t cols, int accumulate);
+/* Forward and `sce-diff-static` in ONE launch, for an executor that already knows the loss' incoming gradient when it issues the
+ * forward (a training step seeds the summed loss with the constant 1): dx = (dy[0] * (z - labels)) / rows is written beside z, with
+ * the operations of wf2cu_sce_backward (accumulate = 0), so both are bit-identical to the two calls.  dy = dx = NULL: the plain forward. */
+int  wf2cu_sce_sum_forward_grad(const void* x, int64_t x_off, const void* labels, int64_t l_off, void* z, int64_t z_off,
+                                void* loss, int64_t loss_off, int64_t rows, int64_t cols, float delta,
+                                const void* dy, int64_t dy_off, void* dx, int64_t dx_off);
 
 /* ===================== optimizers (fused chains of `optimizers/impls/*.lisp`) ===================== */
 /* p <- p - lr * g        (`sgd.lisp:20-26`) */
